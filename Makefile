@@ -1,0 +1,26 @@
+# Builds libperch_b200.so (product, sm_100a only) and the test oracles.
+NVCC      ?= nvcc
+ARCH      := -gencode arch=compute_100a,code=sm_100a
+CSRC      := perception_b200/csrc
+NVFLAGS   := -std=c++17 -O3 $(ARCH) -lineinfo -Xcompiler -fPIC,-ffp-contract=off -I$(CSRC) -Iinclude
+SRCS      := $(CSRC)/pose_kernels.cu $(CSRC)/cloud.cu $(CSRC)/colour.cu $(CSRC)/capi.cu
+OBJS      := $(SRCS:.cu=.o)
+LIB       := perception_b200/libperch_b200.so
+REF       := /root/reference
+
+all: $(LIB) oracle
+
+$(CSRC)/%.o: $(CSRC)/%.cu $(wildcard $(CSRC)/*.cuh $(CSRC)/*.hpp) include/perch_b200.h
+	$(NVCC) $(NVFLAGS) -c $< -o $@
+
+$(LIB): $(OBJS)
+	$(NVCC) $(ARCH) -shared -o $@ $(OBJS)
+
+oracle:
+	$(MAKE) -C oracle
+
+clean:
+	rm -f $(OBJS) $(LIB)
+	$(MAKE) -C oracle clean
+
+.PHONY: all oracle clean

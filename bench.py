@@ -1,0 +1,433 @@
+#!/usr/bin/env python
+"""bench.py -- scored poses/s of the fused render+cost hot path (BASELINE.json metric) on synthetic inputs.
+
+  python bench.py --gpus N --steps K --warmup W            our arm   (torchrun for N > 1, one rank per GPU)
+  python bench.py --impl reference ...                     the reference's CPU scoring path (oracle port, host cores)
+  python bench.py --impl reference-cuda ...                the reference's own CUDA kernels (oracle/_ref) on the GPU
+
+A step = one pass of the hot path over one batch of candidate poses per GPU (workload C2 of BASELINE.json configs[1]:
+16 384 6-DoF poses of a 20 000-triangle mesh against a 640x480 scene, stride 8, label-restricted cost_type 2).
+`value` times the kernel with inputs resident in HBM (CUDA events on the library's stream, L2 flushed between steps);
+`e2e` times the public host API (pinned host poses in, costs + top-k out, NCCL gather of the per-GPU top-k for N > 1).
+Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "tests"))
+
+METRIC = "scored poses/sec (render+cost, 640x480)"
+UNIT = "poses/s"
+W, H = 640, 480
+
+WORKLOADS = {
+    # name: (description, n_tris, poses per GPU per step, stride, dof6, cost_type, sensor_resolution)
+    "c1": ("C1: 3-DoF, 5k-tri mesh, 2k poses, stride 4, cost_type 0", 5000, 2000, 4, False, 0, 0.0075),
+    "c2": ("C2: 6-DoF render+cost, 16384 poses x 20k-tri mesh, 640x480, stride 8, cost_type 2", 20000, 16384, 8, True, 2, 0.01),
+}
+
+
+def rank_info():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+# ---- clocks --------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu, self.lines, self.proc = gpu_index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                                          "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---- workload ----------------------------------------------------------------------------------------------------------
+def build_workload(name: str, rank: int, device: int, n_poses: int | None, use_product: bool = True):
+    """Everything untimed: mesh, scene, observed cloud, poses.  With use_product the scene is rasterised and
+    back-projected by libperch_b200 (GPU); the reference arms use the CPU oracle instead so that none of this repo's
+    kernels touch their inputs."""
+    from perception_b200 import synth
+    from perception_b200.renderer import Renderer, compute_proj
+
+    desc, n_tris, P, stride, dof6, cost_type, res = WORKLOADS[name]
+    if n_poses:
+        P = n_poses
+    proj = compute_proj(synth.camera_K(), W, H)
+    mesh = synth.make_mesh(n_tris, seed=1000, r0=0.09)
+    r = None
+    if use_product:
+        r = Renderer(device)
+        r.set_camera(W, H, proj, synth.CX, synth.CY, synth.FX, synth.FY, synth.DEPTH_FACTOR)
+
+        def render_fn(tris, counts, poses, pmm):
+            r.set_models(tris, counts)
+            r.set_scene(np.zeros(W * H, np.int32))
+            o = r.render_cuda_multi_unified("RENDER", poses, pmm)
+            return o["result_depth"], o["result_color"]
+    else:
+        from oracle_lib import Oracle
+        orc = Oracle()
+
+        def render_fn(tris, counts, poses, pmm):
+            return orc.render(tris, counts, poses, pmm, W, H, proj)
+
+    scene = synth.make_scene([mesh], render_fn, n_instances=4, seed=42)
+    cam = (synth.CX, synth.CY, synth.FX, synth.FY, synth.DEPTH_FACTOR)
+    lab_img = scene.source_label if dof6 else None
+    bounds = None if dof6 else synth.table_bounds(scene)
+    tf = None if dof6 else np.linalg.inv(scene.T_cam_table)
+    if use_product:
+        r.set_models(scene.tris, scene.tris_model_count)
+        r.set_scene(scene.source_depth, scene.source_color, lab_img)
+        obs = r.depth2cloud_global(scene.source_depth, scene.source_color, W, H, 1, *cam, stride, lab_img, bounds, tf)
+    else:
+        o = orc.depth2cloud(scene.source_depth, scene.source_color, W, H, 1, *cam, stride, label_mask=lab_img, bounds=bounds, cam_tf=tf)
+        obs = {"result_cloud_eigen": o["aos"], "result_cloud_color": o["rgb"], "rendered_cloud_point_num": o["n"],
+               "result_observed_cloud_label": o["label"] if dof6 else None}
+    obs_label = obs["result_observed_cloud_label"] if dof6 else None
+    if use_product:
+        r.set_observed(obs["result_cloud_eigen"], obs["result_cloud_color"], obs_label)
+    n_obs = obs["rendered_cloud_point_num"]
+    if dof6:
+        center = scene.gt_poses[0][:3, 3]
+        poses = synth.poses_6dof(center, P, seed=3 + rank)
+        poses[0] = synth.pose_to_mat4x4(scene.gt_poses[0])
+        plabel = np.zeros(P, np.int32)
+        tot = np.full(P, float((obs_label == 0).sum()), np.float32)
+    else:
+        poses = synth.poses_3dof(scene, 0, P, seed=1 + rank)
+        plabel = None
+        tot = synth.cylinder_counts(scene, obs["result_cloud_eigen"], poses, np.zeros(P, np.int32))
+    pmm = np.zeros(P, np.int32)
+    wl = dict(name=name, desc=desc, n_tris=n_tris, P=P, stride=stride, dof6=dof6, cost_type=cost_type, res=res, n_obs=n_obs,
+              scene=scene, obs=obs, obs_label=obs_label, poses=poses, pmm=pmm, plabel=plabel, tot=tot, proj=proj)
+    return r, wl
+
+
+def algorithmic_bytes_per_pose(n_tris, n_obs):
+    # SURVEY.md 8(d) / BASELINE.md 2c: 40*T_m + 64 + 4*W*H + 15*N_obs + 12
+    return 40 * n_tris + 64 + 4 * W * H + 15 * n_obs + 12
+
+
+def measured_peak_gbs():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        try:
+            return float(json.loads(p.read_text())["hbm_gbs"]), "measured"
+        except Exception:
+            pass
+    return 6650.0, "fallback"
+
+
+# ---- arms ----------------------------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from perception_b200.renderer import topk
+
+    rank, local_rank, world = rank_info()
+    if world > 1:
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    r, wl = build_workload(args.workload, rank, local_rank, args.poses)
+    P = wl["P"]
+    kw = dict(stride=wl["stride"], cost_type=wl["cost_type"], calculate_observed_cost=True, sensor_resolution=wl["res"],
+              color_distance_threshold=20.0, occlusion_threshold=1.0)
+
+    # device-resident inputs/outputs for `value`
+    d_poses = r.device_alloc(P * 64); r.h2d(d_poses, wl["poses"])
+    d_pmm = r.device_alloc(P * 4); r.h2d(d_pmm, wl["pmm"])
+    d_lab = None
+    if wl["plabel"] is not None:
+        d_lab = r.device_alloc(P * 4); r.h2d(d_lab, wl["plabel"])
+    d_tot = r.device_alloc(P * 4); r.h2d(d_tot, wl["tot"])
+    d_costs = r.device_alloc(P * 12)
+    d_counts = r.device_alloc(P * 12)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def device_step():
+        r.l2_flush()
+        r.render_cost_device(d_poses, P, d_pmm, d_lab, d_tot, d_costs, d_counts, **kw)
+        r.synchronize()
+        return r.last_timing()[0]
+
+    for _ in range(args.warmup):
+        device_step()
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    t0 = time.perf_counter()
+    kernel_ms = [device_step() for _ in range(args.steps)]
+    barrier()
+    wall_device_loop = time.perf_counter() - t0
+    total_ms = float(np.sum(kernel_ms))
+
+    # e2e: public host API, pinned host buffers, costs + per-model top-k back on the host, gather across ranks
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory().numpy()  # noqa: E731
+    h_poses, h_pmm, h_tot = pin(wl["poses"]), pin(wl["pmm"]), pin(wl["tot"])
+    h_lab = pin(wl["plabel"]) if wl["plabel"] is not None else None
+    K_TOP = 8
+
+    def e2e_step():
+        out = r.render_cuda_multi_unified("COST", h_poses, h_pmm, h_lab, h_tot, **kw)
+        hits = topk(out["rendered_cost"], out["observed_cost"], h_pmm, 1, k=K_TOP, pose_id_offset=rank * P)
+        if world > 1:
+            t = torch.from_numpy(hits.view(np.int32).reshape(-1).copy()).cuda()
+            g = [torch.empty_like(t) for _ in range(world)]
+            dist.all_gather(g, t)
+            allh = torch.stack(g).cpu().numpy().reshape(world * K_TOP, 4)
+            best = allh[np.lexsort((allh[:, 1], allh[:, 0]))][0]
+        else:
+            best = hits[0, 0]
+        return out, best
+
+    for _ in range(max(1, min(args.warmup, 3))):
+        out, best = e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        out, best = e2e_step()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    clocks = sampler.stop()
+
+    counts = np.zeros((3, P), np.int32)
+    r.d2h(counts, d_counts)
+    work = {"rendered_points_per_pose": float(counts[0].mean()), "n_obs": int(wl["n_obs"])}
+
+    if world > 1:
+        t = torch.tensor([total_ms, e2e_s], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms, e2e_s = float(t[0]), float(t[1])
+
+    line = None
+    if rank == 0:
+        peak, peak_kind = measured_peak_gbs()
+        ms_per_step = total_ms / args.steps
+        value = world * P * args.steps / (total_ms / 1e3)
+        bpp = algorithmic_bytes_per_pose(wl["n_tris"], wl["n_obs"])
+        kern_ms = float(np.mean(kernel_ms))
+        achieved = P * bpp / (kern_ms / 1e3) / 1e9
+        traffic = None
+        tfile = ROOT / "profiles" / "dram_traffic.json"
+        if tfile.exists():
+            try:
+                traffic = json.loads(tfile.read_text()).get(args.workload)
+            except Exception:
+                traffic = None
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic",
+            "config": {"workload": wl["desc"], "poses_per_gpu_per_step": P, "triangles": wl["n_tris"], "image": [W, H],
+                       "stride": wl["stride"], "n_obs": int(wl["n_obs"]), "l2": "flushed between steps (256 MiB memset)",
+                       "timing": "CUDA events on the library stream around the fused kernel, max over ranks"},
+            "clocks": clocks,
+            "e2e": {"value": world * P * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": int(P * (64 + 4 + 4 + (4 if h_lab is not None else 0))),
+                    "d2h_bytes_per_step": int(P * 24), "ms_per_scene": e2e_s / args.steps * 1e3},
+            "gpu_launches": args.steps,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": traffic, "peak_kind": f"{peak_kind} copy bandwidth", "bytes_per_pose": bpp,
+                         "poses_per_launch": P, "kernel": "pose_kernel<MODE_COST>", "kernel_ms": kern_ms},
+            "work": work,
+            "best": {"cost": int(best[0]), "pose_id": int(best[1])},
+            "wall_s_device_loop": wall_device_loop,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline(wl, budget_s=args.cpu_budget)
+        if world == 1 and not args.no_ref_cuda:
+            line["reference_cuda"] = reference_cuda(wl, batch=args.ref_batch)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return line
+
+
+def _baseline_inputs(wl):
+    s = wl["scene"]
+    if wl["dof6"]:
+        return dict(center=None, radius=None, t_tc=None)
+    T_tc = np.linalg.inv(s.T_cam_table)
+    t = wl["poses"][:, :3, 3].astype(np.float64) / 100.0
+    c = (t @ T_tc[:3, :3].T + T_tc[:3, 3])[:, :2].astype(np.float32)
+    return dict(center=np.ascontiguousarray(c), radius=np.full(len(c), s.model_radius[0], np.float32),
+                t_tc=np.ascontiguousarray(T_tc[:3, :4], dtype=np.float32))
+
+
+def cpu_score(wl, n):
+    """Time the CPU port of the reference's non-GPU scoring path (oracle/cpu_baseline.c) on the first n poses."""
+    import ctypes as C
+    from oracle_lib import ORACLE_SO
+    from perception_b200.renderer import TRIANGLE_DTYPE
+    lib = C.CDLL(str(ORACLE_SO))
+    lib.cpu_baseline_threads.restype = C.c_int
+    s = wl["scene"]
+    b = _baseline_inputs(wl)
+    vp = C.c_void_p
+    p = lambda a: None if a is None else a.ctypes.data_as(vp)  # noqa: E731
+    tris = np.ascontiguousarray(s.tris, dtype=TRIANGLE_DTYPE)
+    cnt = np.ascontiguousarray(s.tris_model_count, np.int32)
+    poses = np.ascontiguousarray(wl["poses"][:n], np.float32)
+    pmm = np.ascontiguousarray(wl["pmm"][:n], np.int32)
+    sd = np.ascontiguousarray(s.source_depth, np.int32)
+    sl = np.ascontiguousarray(s.source_label, np.uint8) if wl["dof6"] else None
+    pl = np.ascontiguousarray(wl["plabel"][:n], np.int32) if wl["dof6"] else None
+    ox = np.ascontiguousarray(wl["obs"]["result_cloud_eigen"], np.float32)
+    ol = np.ascontiguousarray(wl["obs_label"], np.int32) if wl["dof6"] else None
+    proj = np.ascontiguousarray(wl["proj"], np.float32)
+    from perception_b200 import synth
+    tc = np.zeros(n, np.int32); scst = np.zeros(n, np.int32)
+    t0 = time.perf_counter()
+    lib.cpu_baseline_score(p(tris), C.c_int(len(tris)), p(poses), C.c_int(n), p(pmm), p(cnt), C.c_int(len(cnt)), C.c_int(W),
+                           C.c_int(H), p(proj), p(sd), p(sl), p(pl), C.c_float(synth.CX), C.c_float(synth.CY), C.c_float(synth.FX),
+                           C.c_float(synth.FY), C.c_float(100.0), C.c_int(wl["stride"]), p(ox), p(ol), C.c_int(len(ox)),
+                           p(b["center"]), p(b["radius"]), p(b["t_tc"]), C.c_float(wl["res"]), C.c_float(1.0), C.c_int(10),
+                           p(tc), p(scst))
+    dt = time.perf_counter() - t0
+    return dt, lib.cpu_baseline_threads(), tc, scst
+
+
+def cpu_baseline(wl, budget_s=15.0):
+    dt, cores, _, _ = cpu_score(wl, 32)
+    n = int(min(wl["P"], max(32, 32 * budget_s / max(dt, 1e-3))))
+    dt, cores, _, _ = cpu_score(wl, n)
+    return {"value": n / dt, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"first {n} poses of the same workload, {dt:.1f} s, OpenMP over poses (oracle/cpu_baseline.c)"}
+
+
+def reference_cuda(wl, batch=700):
+    """The reference's own CUDA kernels (oracle/_ref/libperch_ref.so) on the same inputs: per-call upload + alloc like
+    the reference, shipped gpu_batch_size 700 (pr3_env_config.yaml:10).  Reported beside, same GPU, same job."""
+    from oracle_lib import REF_SO, Reference
+    if not REF_SO.exists():
+        return {"unavailable": "oracle/_ref/libperch_ref.so not built"}
+    ref = Reference()
+    s = wl["scene"]
+    from perception_b200 import synth
+    n = min(batch, wl["P"])
+    a = dict(tris=s.tris, tris_model_count=s.tris_model_count, poses=wl["poses"][:n], pose_model_map=wl["pmm"][:n], width=W,
+             height=H, proj=wl["proj"], source_depth=s.source_depth, source_color=s.source_color,
+             source_label=s.source_label if wl["dof6"] else None, pose_label=wl["plabel"][:n] if wl["dof6"] else None,
+             stride=wl["stride"], depth_factor=100, cx=synth.CX, cy=synth.CY, fx=synth.FX, fy=synth.FY,
+             obs_xyz=wl["obs"]["result_cloud_eigen"], obs_rgb=wl["obs"]["result_cloud_color"],
+             obs_label=wl["obs_label"] if wl["dof6"] else None, pose_obs_total=wl["tot"][:n], cost_type=wl["cost_type"],
+             calc_observed=True, sensor_resolution=wl["res"], color_distance_threshold=20.0, occlusion_threshold=1.0)
+    ref.render_cost(**a)  # warm-up (context, allocator)
+    times, phases = [], []
+    for _ in range(3):
+        t0 = time.perf_counter()
+        q = ref.render_cost(**a)
+        times.append(time.perf_counter() - t0)
+        phases.append(q["ms"])
+    dt = float(np.median(times))
+    ph = np.median(np.array(phases), 0)
+    return {"value": n / dt, "unit": UNIT, "batch": n, "ms_per_batch": dt * 1e3,
+            "phase_ms": {"render": float(ph[0]), "cloud": float(ph[1]), "knn": float(ph[2]), "cost": float(ph[3])},
+            "note": "reference .cuh kernels compiled unmodified for sm_100a + restated orchestration and brute-force NN"}
+
+
+def run_reference_cpu(args):
+    """--impl reference: the reference's CPU scoring path (port) on the host cores, bounded sample per step."""
+    rank, local_rank, world = rank_info()
+    if rank != 0:
+        return
+    r, wl = build_workload(args.workload, 0, local_rank, args.poses, use_product=False)
+    dt, cores, _, _ = cpu_score(wl, 16)
+    per_step = int(min(wl["P"], max(16, 16 * (60.0 / max(args.steps + args.warmup, 1)) / max(dt, 1e-3))))
+    for _ in range(args.warmup):
+        cpu_score(wl, per_step)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        cpu_score(wl, per_step)
+    el = time.perf_counter() - t0
+    v = per_step * args.steps / el
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": el / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": wl["desc"], "poses_per_step_sample": per_step, "triangles": wl["n_tris"], "image": [W, H],
+                       "stride": wl["stride"], "n_obs": int(wl["n_obs"])},
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                             "sample": f"{per_step} poses per step of the same workload (oracle/cpu_baseline.c, OpenMP)"},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def run_reference_cuda(args):
+    rank, local_rank, world = rank_info()
+    if rank != 0:
+        return
+    r, wl = build_workload(args.workload, 0, local_rank, args.poses, use_product=False)
+    out = reference_cuda(wl, batch=args.ref_batch)
+    print(json.dumps({"impl": "reference-cuda", "metric": METRIC, "unit": UNIT, **out,
+                      "config": {"workload": wl["desc"]}}), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "reference-cuda"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--poses", type=int, default=None, help="override poses per GPU per step")
+    ap.add_argument("--cpu-budget", type=float, default=15.0)
+    ap.add_argument("--ref-batch", type=int, default=700)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-ref-cuda", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 0)
+    if args.impl == "reference":
+        return run_reference_cpu(args)
+    if args.impl == "reference-cuda":
+        return run_reference_cuda(args)
+    run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,179 @@
+/*
+ * perch_b200.h -- C-ABI of libperch_b200.so: the B200-native (sm_100a) implementation of PERCH 2.0's
+ * data-parallel hot path (batched candidate-pose rendering + per-pose depth/colour cost, depth->cloud,
+ * KNN and batched GICP refinement).
+ *
+ * This is the drop-in boundary for what sbpl_perception::EnvObjectRecognition calls in the reference's
+ * cuda_renderer package.  Every entry point cites the reference interface it replaces (paths relative to
+ * the reference repo).  Plain pointers and sizes only; all functions return 0 on success and a non-zero
+ * perch_status otherwise (perch_last_error() gives the text); nothing here exit()s or writes to stdout.
+ *
+ * Unlike the reference, which re-uploads meshes and the scene on every call (renderer.cu:1532-1544), state is
+ * held in a context: set the models / camera / scene / observed cloud once, then score batches of poses.
+ *
+ * Units follow the reference: meshes in metres, poses carry a x100 scale in their top three rows
+ * (model.h:89-107) so rendered depth is integer centimetres; depth_factor converts back (100 => metres).
+ */
+#ifndef PERCH_B200_H
+#define PERCH_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PERCH_B200_ABI_VERSION 1
+
+typedef enum perch_status {
+    PERCH_OK = 0,
+    PERCH_ERR_INVALID = 1,   /* bad argument / call order */
+    PERCH_ERR_CUDA = 2,      /* CUDA runtime error (text in perch_last_error) */
+    PERCH_ERR_NO_DEVICE = 3, /* no usable sm_100 device: the library has no CPU fallback */
+    PERCH_ERR_CAPACITY = 4   /* a documented size limit was exceeded */
+} perch_status;
+
+typedef struct perch_ctx perch_ctx;
+
+/* Layout-compatible with cuda_renderer::Model::Triangle (model.h:39-43,52-73): 3 x float3 + 3 x size_t colour. */
+typedef struct perch_triangle {
+    float v0[3], v1[3], v2[3];
+    uint64_t color[3];
+} perch_triangle; /* 64 bytes */
+
+/* Replaces cuda_renderer::gpu_stats (model.h:24-27). */
+typedef struct perch_gpu_stats {
+    float icp_runtime;         /* seconds, max over calls like renderer.cu:1739 */
+    double peak_memory_usage;  /* MiB in use on the device, high-water (utils.cuh:6-24) */
+} perch_gpu_stats;
+
+/* The scalar arguments of render_cuda_multi_unified (renderer.h:221-268 / renderer.cu:1431-1474). */
+typedef struct perch_params {
+    int stride;                      /* @stride: pixel subsampling of the rendered images for clouds/costs */
+    int cost_type;                   /* 0 depth-only (3-DoF), 1 depth+CIEDE2000 colour, 2 6-DoF depth-only */
+    int calculate_observed_cost;     /* @calculate_observed_cost */
+    float sensor_resolution;         /* metres; compared squared against squared NN distance (renderer.cu:1877) */
+    float color_distance_threshold;  /* CIEDE2000 threshold for cost_type 1 */
+    float occlusion_threshold;       /* cm; 3-DoF source-occlusion rule (image_renderer.cuh:163) */
+    int single_result_image;         /* 1: all poses z-tested into one image (RENDER stage only) */
+    int do_icp;                      /* 1: batched GICP refinement before costing (renderer.cu:1688-1817) */
+    int icp_max_iterations;          /* reference hard-codes 150 (renderer.cu:1696); <=0 selects that */
+    int icp_k_correspondences;       /* reference hard-codes 10 (renderer.cu:1697); <=0 selects that */
+    float icp_rotation_epsilon;      /* reference 2e-3 (renderer.cu:1698); <0 selects that */
+    float icp_transformation_epsilon;/* reference 5e-4 (renderer.cu:1699); <0 selects that */
+} perch_params;
+
+/* Host output buffers of one perch_render_cost call.  Every pointer is optional (NULL = not wanted) and
+ * CALLER-provided; use perch_*_count queries or the capacities below.  (The C++ compat wrappers in
+ * perception_b200/csrc/compat reproduce the reference's callee-malloc ownership on top of this.) */
+typedef struct perch_outputs {
+    /* stage RENDER / DEBUG (renderer.cu:1594-1615): P*W*H each (W*H when single_result_image) */
+    int32_t* depth;
+    uint8_t* red;
+    uint8_t* green;
+    uint8_t* blue;
+    /* stage CLOUD / DEBUG (renderer.cu:1821-1847) */
+    float* cloud;          /* 3 x cloud_capacity SoA (row stride = cloud_capacity floats) */
+    uint8_t* cloud_color;  /* 3 x cloud_capacity SoA */
+    int* cloud_pose_map;   /* cloud_capacity */
+    int* dc_index;         /* P*W*H exclusive scan of the sample mask (compute_point_clouds.cuh:290-292) */
+    int cloud_capacity;    /* in: points the three cloud buffers can hold */
+    int cloud_point_num;   /* out: result_cloud_point_num (total points; may exceed capacity => truncated copy) */
+    /* stage COST / DEBUG (renderer.cu:1908-1922): P floats each */
+    float* rendered_cost;
+    float* observed_cost;
+    float* points_diff_cost;
+    /* extra (not in the reference): the integer counters the costs are functions of, 3 x P:
+     * [0..P) rendered points n, [P..2P) unexplained rendered points c, [2P..3P) explained observed points */
+    int32_t* counts;
+    /* do_icp: refined poses, 16 floats each, x100-scaled like the inputs (renderer.cu:1729-1730) */
+    float* adjusted_poses;
+} perch_outputs;
+
+/* ---- context ------------------------------------------------------------------------------------------- */
+/* One context per device (the reference uses the implicit current device, renderer.cu; knncuda.cu:302 forces 0).
+ * Fails with PERCH_ERR_NO_DEVICE when no sm_100-class GPU is present: there is no CPU fallback. */
+int perch_create(int device, perch_ctx** out);
+void perch_destroy(perch_ctx* ctx);
+const char* perch_last_error(void);
+int perch_abi_version(void);
+/* Replaces gpu_stats& stats (renderer.h:268). */
+int perch_get_stats(perch_ctx* ctx, perch_gpu_stats* out);
+/* Device milliseconds (CUDA events on the context's stream) of the last perch_render_cost call and the number
+ * of kernels it launched -- for bench.py's roofline / gpu_launches fields. */
+int perch_last_timing(perch_ctx* ctx, float* kernel_ms, int* kernel_launches);
+
+/* ---- camera -------------------------------------------------------------------------------------------- */
+/* Replaces cuda_renderer::compute_proj (renderer.h:87, renderer.cu:1386-1410).  K is row-major 3x3. Host-only. */
+int perch_compute_proj(const float K[9], int width, int height, float near_, float far_, float out16[16]);
+/* width,height,proj_mat + kCameraCX..FY, depth_factor arguments of render_cuda_multi_unified (renderer.cu:1437,1446-1450). */
+int perch_set_camera(perch_ctx* ctx, int width, int height, const float proj16[16], float cx, float cy, float fx,
+                     float fy, float depth_factor);
+
+/* ---- models / scene ------------------------------------------------------------------------------------- */
+/* @tris, @tris_model_count of render_cuda_multi_unified (renderer.cu:1433,1436): all models' triangles
+ * concatenated, in the reference's 64-byte Triangle layout. */
+int perch_set_models(perch_ctx* ctx, const perch_triangle* tris, int64_t n_tris, const int* tris_model_count,
+                     int n_models);
+/* @source_depth, @source_color (3 planes), @source_mask_label (may be NULL) (renderer.cu:1438-1442). */
+int perch_set_scene(perch_ctx* ctx, const int32_t* source_depth, const uint8_t* source_red,
+                    const uint8_t* source_green, const uint8_t* source_blue, const uint8_t* source_mask_label);
+/* @observed_depth_eigen (N x 3 AoS), @observed_color (3 x N SoA), @result_observed_cloud_label (may be NULL),
+ * @observed_point_num (renderer.cu:1451-1456).  In 6-DoF mode the cloud is stably sorted by label like
+ * renderer.cu:1681 and NN search is restricted to the pose's label range. */
+int perch_set_observed(perch_ctx* ctx, const float* observed_xyz_aos, const uint8_t* observed_color_soa,
+                       const int* observed_label, int n_obs);
+
+/* ---- depth image -> cloud -------------------------------------------------------------------------------- */
+/* Replaces cuda_renderer::depth2cloud_global (renderer.h:131-153, renderer.cu:1936-2070).
+ * Pass 1: all out_* NULL => *point_num receives the count.  Pass 2: buffers sized for that count.
+ * color planes may be NULL (zeros are reported).  camera_transform16 is COLUMN-major (Eigen::Matrix4f storage).
+ * bounds6 = {xmax,xmin,ymax,ymin,zmax,zmin} (compute_point_clouds.cuh:86-88). */
+int perch_depth2cloud(perch_ctx* ctx, const int32_t* depth, const uint8_t* red, const uint8_t* green,
+                      const uint8_t* blue, int width, int height, int num_poses, float cx, float cy, float fx,
+                      float fy, float depth_factor, int stride, const uint8_t* label_mask, const double* bounds6,
+                      const float* camera_transform16, int* point_num, float* out_cloud_soa, float* out_cloud_aos,
+                      uint8_t* out_cloud_color, int* out_dc_index, int* out_cloud_pose_map, int* out_cloud_label);
+
+/* ---- the hot path ----------------------------------------------------------------------------------------- */
+/* Replaces cuda_renderer::render_cuda_multi_unified (renderer.h:221-268, renderer.cu:1431-1934).
+ * stage: "RENDER" | "CLOUD" | "COST" | "DEBUG" with the reference's meaning (renderer.cu:1479).
+ * poses16: P row-major 4x4 (Model::mat4x4 a0..d3).  pose_segmentation_label NULL => 3-DoF occlusion rule.
+ * pose_observed_points_total: P floats (renderer.cu:1455); may be NULL when observed cost is off.
+ * "COST" runs the fused render->cost kernel: no rendered image or cloud is materialised in HBM. */
+int perch_render_cost(perch_ctx* ctx, const char* stage, const float* poses16, int n_poses,
+                      const int* pose_model_map, const int* pose_segmentation_label,
+                      const float* pose_observed_points_total, const perch_params* params, perch_outputs* out);
+
+/* Device-resident variant for benchmarking / pipelining: inputs and the 3xP float + 3xP int outputs are
+ * DEVICE pointers, work is enqueued on the context's stream and NOT synchronised. Stage is COST. */
+int perch_render_cost_device(perch_ctx* ctx, const float* d_poses16, int n_poses, const int* d_pose_model_map,
+                             const int* d_pose_segmentation_label, const float* d_pose_observed_points_total,
+                             const perch_params* params, float* d_costs3p, int32_t* d_counts3p);
+/* Device memory helpers so hosts without a CUDA binding (ctypes) can stage persistent buffers. */
+int perch_device_alloc(perch_ctx* ctx, size_t bytes, void** d_ptr);
+int perch_device_free(perch_ctx* ctx, void* d_ptr);
+int perch_memcpy_h2d(perch_ctx* ctx, void* d_dst, const void* h_src, size_t bytes);
+int perch_memcpy_d2h(perch_ctx* ctx, void* h_dst, const void* d_src, size_t bytes);
+int perch_synchronize(perch_ctx* ctx);
+/* Measurement hygiene: overwrite a buffer larger than the 126 MB L2 on the context's stream (between timed steps). */
+int perch_l2_flush(perch_ctx* ctx);
+
+/* Per-model argmin the caller performs after scoring (search_env.cpp:2542-2583), generalised to top-k:
+ * cost = (int)(rendered + observed), -1 if rendered < 0 (search_env.cpp:2022-2027); candidates with
+ * |rendered - observed| >= 30 or cost < 0 are skipped; ties resolve to the lowest pose id (strict `<`).
+ * Host-side helper; used per GPU before the NCCL gather of (cost, pose-id) records. */
+typedef struct perch_hit {
+    int32_t cost;
+    int32_t pose_id;
+    float rendered_cost;
+    float observed_cost;
+} perch_hit;
+int perch_topk(const float* rendered_cost, const float* observed_cost, const int* pose_model_map, int n_poses,
+               int pose_id_offset, int n_models, int k, perch_hit* out_hits /* n_models*k, cost=INT32_MAX pads */);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PERCH_B200_H */

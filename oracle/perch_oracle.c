@@ -1,0 +1,455 @@
+/*
+ * perch_oracle.c -- TEST INFRASTRUCTURE ONLY.  CPU restatement of the reference's render + cloud + KNN + cost path.
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load this file's
+ * library; the product (libperch_b200.so) never does and has no CPU fallback.
+ *
+ * Parity status: PINNED for the rasterizer, depth->cloud and cost kernels against the reference's own CUDA kernels
+ * compiled unmodified from /root/reference (oracle/ref_harness.cu -> oracle/_ref/libperch_ref.so, compared on a B200
+ * in tests/test_parity_gpu.py).  The reference repository ships no golden vectors for this path.
+ * UNPINNED: the nearest-neighbour tie-break / distance rounding (lives in the un-vendored fast_gicp dependency,
+ * call site renderer.cu:1853-1865) -- lowest index, fma(dz,dz,fma(dy,dy,dx*dx)) is this repo's convention.
+ *
+ * Each function cites the reference lines it follows (paths relative to the reference repository).
+ * Build: gcc -O2 -ffp-contract=off (the float sequences below spell out where the reference's nvcc build fuses
+ * multiply-adds; the compiler must not add or remove any).
+ */
+#include <float.h>
+#include <limits.h>
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+
+typedef struct { float x, y, z; } vec3;
+typedef struct { vec3 v0, v1, v2; uint64_t c0, c1, c2; } tri64; /* cuda_renderer::Model::Triangle, model.h:62-73 */
+
+/* cvt.rzi.s32.f32: what `int32_t(x)` does on the GPU (saturating, NaN -> 0); a plain C cast is UB out of range. */
+static int32_t f2i_sat(float f) {
+    if (f != f) return 0;
+    if (f >= 2147483648.0f) return INT32_MAX;
+    if (f <= -2147483648.0f) return INT32_MIN;
+    return (int32_t)f;
+}
+/* cvt.rzi.u64.f32 for `size_t(x)` */
+static uint64_t f2u64_sat(float f) {
+    if (f != f || f <= 0.0f) return 0;
+    if (f >= 18446744073709551616.0f) return UINT64_MAX;
+    return (uint64_t)f;
+}
+
+/* mat_mul_v, image_renderer.cuh:21-27.  nvcc evaluates m0*x + m1*y + m2*z + m3 as m3 + fma(m2,z,fma(m0,x,m1*y)). */
+static float row_dot(const float* m, float x, float y, float z) {
+    float t = m[1] * y;
+    t = fmaf(m[0], x, t);
+    t = fmaf(m[2], z, t);
+    return m[3] + t;
+}
+static vec3 mat_mul_v(const float* m16, vec3 v) {
+    vec3 r = {row_dot(m16, v.x, v.y, v.z), row_dot(m16 + 4, v.x, v.y, v.z), row_dot(m16 + 8, v.x, v.y, v.z)};
+    return r;
+}
+static float sel_max(float a, float b) { return (a > b) ? a : b; } /* std__max, image_renderer.cuh:14-15 */
+static float sel_min(float a, float b) { return (a < b) ? a : b; } /* std__min, image_renderer.cuh:17-18 */
+
+/* compute_proj, renderer.cu:1386-1410.  K row-major 3x3. */
+void oracle_compute_proj(const float* K, int width, int height, float near_, float far_, float* p) {
+    memset(p, 0, 16 * sizeof(float));
+    p[0] = 2 * K[0] / width;
+    p[1] = -2 * K[1] / width; p[1] = -p[1];
+    p[2] = -2 * K[2] / width + 1; p[2] = -p[2];
+    p[5] = 2 * K[4] / height; p[5] = -p[5];
+    p[6] = 2 * K[5] / height - 1; p[6] = -p[6];
+    p[10] = -(far_ + near_) / (far_ - near_); p[10] = -p[10];
+    p[11] = -2 * far_ * near_ / (far_ - near_);
+    p[14] = -1; p[14] = -p[14];
+}
+
+/*
+ * image_render, image_renderer.cuh:336-496 with kernel render_triangle_multi (212-321) and
+ * rasterization_with_source (59-210), executed SERIALLY in triangle order (the loop skeleton of the reference's own
+ * CPU rasterizer, cuda_renderer/src/renderer.cpp:291-330).  Running the reference's per-fragment z-test +
+ * source-occlusion step one fragment at a time is the race-free meaning of the kernel: the result is independent of
+ * the order (DESIGN.md "canonical raster semantics"), colour ties go to the lowest triangle index (strict `<`, :149).
+ *
+ * out_* are P*W*H (W*H when single_result_image).  pose_label NULL => 3-DoF occlusion rule.
+ */
+void oracle_render(const tri64* tris, int n_tris, const float* poses16, int n_poses, const int* pose_model_map,
+                   const int* tris_model_count, int n_models, int width, int height, const float* proj16,
+                   const int32_t* source_depth, const uint8_t* source_label, const int* pose_label,
+                   float occlusion_threshold, int single_result_image, int32_t* out_depth, uint8_t* out_r,
+                   uint8_t* out_g, uint8_t* out_b) {
+    const size_t npx = (size_t)width * height;
+    const size_t n_img = single_result_image ? 1 : (size_t)n_poses;
+    /* image_renderer.cuh:395-398 */
+    for (size_t i = 0; i < n_img * npx; ++i) { out_depth[i] = INT_MAX; out_r[i] = 0; out_g[i] = 0; out_b[i] = 0; }
+    /* per-model triangle ranges, image_renderer.cuh:371-380 */
+    int* low = (int*)malloc(sizeof(int) * (size_t)n_models);
+    int* high = (int*)malloc(sizeof(int) * (size_t)n_models);
+    int run = 0;
+    for (int m = 0; m < n_models; ++m) { low[m] = run; run += tris_model_count[m]; high[m] = run; }
+    const float wf = (float)(uint64_t)width, hf = (float)(uint64_t)height;
+    const float clamp_max[2] = {(float)(width - 1), (float)(height - 1)};
+    const float clamp_min[2] = {0, 0};
+    const int use_label = pose_label != NULL;
+
+    for (int pi = 0; pi < n_poses; ++pi) {
+        const int model = pose_model_map[pi];
+        const float* pose = poses16 + 16 * (size_t)pi;
+        int32_t* depth_entry = out_depth + (single_result_image ? 0 : (size_t)pi * npx);
+        uint8_t* r_entry = out_r + (single_result_image ? 0 : (size_t)pi * npx);
+        uint8_t* g_entry = out_g + (single_result_image ? 0 : (size_t)pi * npx);
+        uint8_t* b_entry = out_b + (single_result_image ? 0 : (size_t)pi * npx);
+        /* image_renderer.cuh:273-274,287-288: in single-image mode every pose reads label entry 0 */
+        const int this_pose_label = use_label ? pose_label[single_result_image ? 0 : pi] : 0;
+        for (int ti = 0; ti < n_tris; ++ti) {
+            if (!(ti < high[model] && ti >= low[model])) continue; /* :242-243 */
+            const tri64* T = tris + ti;
+            /* :296-305 model transform, last_row, projection */
+            vec3 c0 = mat_mul_v(pose, T->v0), c1 = mat_mul_v(pose, T->v1), c2 = mat_mul_v(pose, T->v2);
+            const float z0 = c0.z, z1 = c1.z, z2 = c2.z;
+            vec3 q0 = mat_mul_v(proj16, c0), q1 = mat_mul_v(proj16, c1), q2 = mat_mul_v(proj16, c2);
+            /* :82-84 viewport: x/z*W/2 + W/2 -> fma(W, 0.5, ((x/z)*W)*0.5) in the nvcc build */
+            float pts[3][2];
+            pts[0][0] = fmaf(wf, 0.5f, ((q0.x / z0) * wf) * 0.5f); pts[0][1] = fmaf(hf, 0.5f, ((q0.y / z0) * hf) * 0.5f);
+            pts[1][0] = fmaf(wf, 0.5f, ((q1.x / z1) * wf) * 0.5f); pts[1][1] = fmaf(hf, 0.5f, ((q1.y / z1) * hf) * 0.5f);
+            pts[2][0] = fmaf(wf, 0.5f, ((q2.x / z2) * wf) * 0.5f); pts[2][1] = fmaf(hf, 0.5f, ((q2.y / z2) * hf) * 0.5f);
+            /* :86-107 */
+            float bboxmin[2] = {FLT_MAX, FLT_MAX}, bboxmax[2] = {-FLT_MAX, -FLT_MAX};
+            for (int i = 0; i < 3; ++i)
+                for (int j = 0; j < 2; ++j) {
+                    bboxmin[j] = sel_max(clamp_min[j], sel_min(bboxmin[j], pts[i][j]));
+                    bboxmax[j] = sel_min(clamp_max[j], sel_max(bboxmax[j], pts[i][j]));
+                }
+            /* calculateSignedArea(A,B,C) :40-42, no fused ops in the nvcc build; base_inv = 1/area :48 */
+            const float* A = pts[0]; const float* B = pts[1]; const float* C = pts[2];
+            const float area = (((C[0] - A[0]) * (B[1] - A[1])) - ((B[0] - A[0]) * (C[1] - A[1]))) * 0.5f;
+            const float base_inv = 1.0f / area;
+            /* :110-111 */
+            for (uint64_t P1 = f2u64_sat(bboxmin[1] + 0.5f); (float)P1 <= bboxmax[1]; ++P1) {
+                for (uint64_t P0 = f2u64_sat(bboxmin[0] + 0.5f); (float)P0 <= bboxmax[0]; ++P0) {
+                    const float fp0 = (float)P0, fp1 = (float)P1;
+                    /* barycentric :44-57: beta = area(A,P,C)*base_inv, gamma = area(A,B,P)*base_inv */
+                    const float aAPC = (((C[0] - A[0]) * (fp1 - A[1])) - ((fp0 - A[0]) * (C[1] - A[1]))) * 0.5f;
+                    const float aABP = (((fp0 - A[0]) * (B[1] - A[1])) - ((B[0] - A[0]) * (fp1 - A[1]))) * 0.5f;
+                    const float beta = base_inv * aAPC;
+                    const float gamma = base_inv * aABP;
+                    const float alpha = (1.0f - beta) - gamma;
+                    /* :114-115 (a NaN coordinate fails every comparison and is therefore NOT rejected) */
+                    if (alpha < -0.0f || beta < -0.0f || gamma < -0.0f || alpha > 1.0f || beta > 1.0f || gamma > 1.0f)
+                        continue;
+                    /* :117-129 */
+                    const float oz0 = alpha / z0, oz1 = beta / z1, oz2 = gamma / z2;
+                    const float frag = (gamma + (beta + alpha)) / (oz2 + (oz1 + oz0));
+                    const int32_t curr = f2i_sat(frag + 0.5f);
+                    const size_t x_to_write = (size_t)P0, y_to_write = (size_t)(height - 1) - (size_t)P1;
+                    const size_t o = x_to_write + y_to_write * (size_t)width;
+                    const int32_t src = source_depth[o];
+                    const int src_label = (use_label && source_label) ? source_label[o] : 0;
+                    /* :146-159 z-test */
+                    if (curr < depth_entry[o]) {
+                        depth_entry[o] = curr;
+                        r_entry[o] = (uint8_t)T->c0; g_entry[o] = (uint8_t)T->c1; b_entry[o] = (uint8_t)T->c2;
+                    }
+                    /* :161-186 source occlusion, evaluated on the CURRENT buffer value */
+                    const int32_t nd = depth_entry[o];
+                    const int64_t diff = (int64_t)nd - (int64_t)src;
+                    const int32_t ad = (int32_t)(diff < 0 ? -diff : diff > INT32_MAX ? INT32_MAX : diff);
+                    int test;
+                    if (!use_label) test = (float)ad > occlusion_threshold;
+                    else test = (this_pose_label != src_label - 1) && ((double)ad > 0.5);
+                    if (test && nd > src && src > 0) {
+                        r_entry[o] = 0; g_entry[o] = 0; b_entry[o] = 0;
+                        depth_entry[o] = INT_MAX; /* atomicMax(&new_depth, INT_MAX) */
+                    }
+                }
+            }
+        }
+    }
+    /* max2zero, :324-333,465-466 */
+    for (size_t i = 0; i < n_img * npx; ++i)
+        if (out_depth[i] == INT_MAX) out_depth[i] = 0;
+    free(low);
+    free(high);
+}
+
+/* transform_point, compute_point_clouds.cuh:14-35 (camera-frame part :20-22; no fused ops in the nvcc build) */
+static void back_project(int x, int y, int32_t d, float cx, float cy, float fx, float fy, float depth_factor, float* px,
+                         float* py, float* pz) {
+    const float z = (float)d / depth_factor;
+    *pz = z;
+    *px = (((float)x - cx) / fx) * z;
+    *py = (((float)y - cy) / fy) * z;
+}
+
+/* world-frame part :25-32 as the nvcc build of the oracle's Eigen stand-in evaluates it:
+ * row = fma(m2,z,fma(m1,y,m0*x)) + t.  (Real Eigen's association is not pinned by any reference test.) */
+static void to_world(const float* m /* column-major 4x4 */, float x, float y, float z, float* w) {
+    for (int r = 0; r < 3; ++r) {
+        float t = m[r] * x;
+        t = fmaf(m[4 + r], y, t);
+        t = fmaf(m[8 + r], z, t);
+        w[r] = t + m[12 + r];
+    }
+}
+
+/*
+ * compute_point_clouds, compute_point_clouds.cuh:188-367 (kernels depth_to_mask :37-93, depth_to_2d_cloud :95-184,
+ * index = exclusive scan of the mask in (image, y, x) order :290-292).  Returns the point count; output pointers may
+ * be NULL.  out_xyz_soa / out_rgb are 3 x count with row stride `count`; dc_index is num_images*W*H.
+ * Buffers the reference zero-fills (:302-305,317) must be zero-filled by the caller.
+ */
+int oracle_depth2cloud(const int32_t* depth, const uint8_t* r, const uint8_t* g, const uint8_t* b, int width, int height,
+                       int num_images, float cx, float cy, float fx, float fy, float depth_factor, int stride,
+                       const uint8_t* label_mask, const int* pose_label, const double* bounds6, const float* cam_tf16,
+                       float* out_xyz_soa, float* out_xyz_aos, uint8_t* out_rgb, int* out_pose_map, int* out_label,
+                       int* out_dc_index, int count_hint) {
+    const int use_bounds = bounds6 != NULL && cam_tf16 != NULL;
+    float fb[6] = {0, 0, 0, 0, 0, 0};
+    if (use_bounds) for (int k = 0; k < 6; ++k) fb[k] = (float)bounds6[k];
+    int count = 0;
+    const size_t npx = (size_t)width * height;
+    for (int n = 0; n < num_images; ++n)
+        for (int y = 0; y < height; ++y)
+            for (int x = 0; x < width; ++x) {
+                const size_t idx = (size_t)n * npx + (size_t)y * width + x;
+                if (out_dc_index) out_dc_index[idx] = count;
+                if (x % stride != 0 || y % stride != 0) continue; /* :47-58 samples x*stride, y*stride */
+                const int32_t d = depth[idx];
+                if (!(d > 0)) continue; /* :64 */
+                int in_bounds = 1;
+                if (use_bounds) {
+                    float px, py, pz, w[3];
+                    back_project(x, y, d, cx, cy, fx, fy, depth_factor, &px, &py, &pz);
+                    to_world(cam_tf16, px, py, pz, w);
+                    if (w[0] > fb[0] || w[0] < fb[1]) in_bounds = 0;
+                    if (w[1] > fb[2] || w[1] < fb[3]) in_bounds = 0;
+                    if (w[2] > fb[4] || w[2] < fb[5]) in_bounds = 0;
+                }
+                int in_mask; /* depth_to_mask :66-91 */
+                if (label_mask == NULL && !use_bounds) in_mask = 1;
+                else if (label_mask != NULL) in_mask = label_mask[idx] > 0;
+                else in_mask = in_bounds;
+                if (!in_mask) continue;
+                const int slot = count++;
+                /* depth_to_2d_cloud :123-139 re-tests label AND bounds before writing */
+                if (label_mask != NULL && !(label_mask[idx] > 0)) continue;
+                if (use_bounds && !in_bounds) continue;
+                if (count_hint <= 0 || slot >= count_hint) continue;
+                float px, py, pz;
+                back_project(x, y, d, cx, cy, fx, fy, depth_factor, &px, &py, &pz);
+                if (out_xyz_soa) {
+                    out_xyz_soa[slot] = px; out_xyz_soa[(size_t)count_hint + slot] = py;
+                    out_xyz_soa[2 * (size_t)count_hint + slot] = pz;
+                }
+                if (out_xyz_aos) { out_xyz_aos[3 * (size_t)slot] = px; out_xyz_aos[3 * (size_t)slot + 1] = py; out_xyz_aos[3 * (size_t)slot + 2] = pz; }
+                if (out_rgb) {
+                    out_rgb[slot] = r ? r[idx] : 0; out_rgb[(size_t)count_hint + slot] = g ? g[idx] : 0;
+                    out_rgb[2 * (size_t)count_hint + slot] = b ? b[idx] : 0;
+                }
+                if (out_pose_map) out_pose_map[slot] = n;
+                if (out_label) { /* :168-178 */
+                    if (label_mask != NULL) out_label[slot] = (int)label_mask[idx] - 1;
+                    else if (pose_label != NULL) out_label[slot] = pose_label[n];
+                }
+            }
+    return count;
+}
+
+/*
+ * fast_gicp::brute_force_knn_search(k=1), call site renderer.cu:1853-1865 (source not in the reference tree; see the
+ * header).  Linear scan, strict `<` => lowest index on ties; restricted to [begin,end) of the source point's label.
+ */
+void oracle_knn_k1(const float* src_aos, int n_src, const float* tgt_aos, int n_tgt, const int* src_label,
+                   const int* label_begin, const int* label_end, int n_labels, float* out_sqdist, int* out_index) {
+    for (int i = 0; i < n_src; ++i) {
+        int b = 0, e = n_tgt;
+        if (src_label) {
+            const int l = src_label[i];
+            if (l < 0 || l >= n_labels) { b = 0; e = 0; } else { b = label_begin[l]; e = label_end[l]; }
+        }
+        const float px = src_aos[3 * (size_t)i], py = src_aos[3 * (size_t)i + 1], pz = src_aos[3 * (size_t)i + 2];
+        float best = FLT_MAX; int best_j = -1;
+        for (int j = b; j < e; ++j) {
+            const float dx = px - tgt_aos[3 * (size_t)j], dy = py - tgt_aos[3 * (size_t)j + 1], dz = pz - tgt_aos[3 * (size_t)j + 2];
+            const float d = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+            if (d < best) { best = d; best_j = j; }
+        }
+        out_sqdist[i] = best;
+        out_index[i] = best_j;
+    }
+}
+
+/* rgb2lab, compute_costs.cuh:57-88 (double precision; host libm pow/cbrt may differ from CUDA's in the last ulp) */
+static void rgb2lab(uint8_t rr, uint8_t gg, uint8_t bbb, float* lab) {
+    double r = rr / 255.0, g = gg / 255.0, b = bbb / 255.0, x, y, z;
+    r = ((r > 0.04045) ? pow((r + 0.055) / 1.055, 2.4) : (r / 12.92)) * 100.0;
+    g = ((g > 0.04045) ? pow((g + 0.055) / 1.055, 2.4) : (g / 12.92)) * 100.0;
+    b = ((b > 0.04045) ? pow((b + 0.055) / 1.055, 2.4) : (b / 12.92)) * 100.0;
+    x = r * 0.4124564 + g * 0.3575761 + b * 0.1804375;
+    y = r * 0.2126729 + g * 0.7151522 + b * 0.0721750;
+    z = r * 0.0193339 + g * 0.1191920 + b * 0.9503041;
+    x = x / 95.047; y = y / 100.00; z = z / 108.883;
+    x = (x > 0.008856) ? cbrt(x) : (7.787 * x + 16.0 / 116.0);
+    y = (y > 0.008856) ? cbrt(y) : (7.787 * y + 16.0 / 116.0);
+    z = (z > 0.008856) ? cbrt(z) : (7.787 * z + 16.0 / 116.0);
+    lab[0] = (float)((116.0 * y) - 16);
+    lab[1] = (float)(500 * (x - y));
+    lab[2] = (float)(200 * (y - z));
+}
+
+#define SQR(x) ((x) * (x))
+#define POW7(x) (((x) * (x) * (x)) * ((x) * (x) * (x)) * (x))
+#define DEG2RAD(x) ((x) * M_PI / 180)
+#define RAD2DEG(x) ((x) / M_PI * 180)
+/* color_distance (CIEDE2000), compute_costs.cuh:90-159, including its two non-exclusive `if`s (:112-123, :133-144):
+ * the low-chroma assignments are always overwritten by the following if/else chain. */
+static double color_distance(float l1, float a1, float b1, float l2, float a2, float b2) {
+    const double eps = 1e-5;
+    double c1 = sqrtf(SQR(a1) + SQR(b1));
+    double c2 = sqrtf(SQR(a2) + SQR(b2));
+    double meanC = (c1 + c2) / 2.0;
+    double meanC7 = POW7(meanC);
+    double g = 0.5 * (1 - sqrtf(meanC7 / (meanC7 + 6103515625.)));
+    double a1p = a1 * (1 + g);
+    double a2p = a2 * (1 + g);
+    c1 = sqrtf(SQR(a1p) + SQR(b1));
+    c2 = sqrtf(SQR(a2p) + SQR(b2));
+    double h1 = fmodf(atan2f(b1, a1p) + 2 * M_PI, 2 * M_PI);
+    double h2 = fmodf(atan2f(b2, a2p) + 2 * M_PI, 2 * M_PI);
+    double deltaL = l2 - l1;
+    double deltaC = c2 - c1;
+    double deltah = 0;
+    if (fabs(h2 - h1) <= M_PI) deltah = h2 - h1;
+    else if (h2 > h1) deltah = h2 - h1 - 2 * M_PI;
+    else deltah = h2 - h1 + 2 * M_PI;
+    double deltaH = 2 * sqrtf(c1 * c2) * sinf(deltah / 2);
+    double meanL = (l1 + l2) / 2;
+    meanC = (c1 + c2) / 2.0;
+    meanC7 = POW7(meanC);
+    double meanH;
+    if (fabs(h1 - h2) <= M_PI + eps) meanH = (h1 + h2) / 2;
+    else if (h1 + h2 < 2 * M_PI) meanH = (h1 + h2 + 2 * M_PI) / 2;
+    else meanH = (h1 + h2 - 2 * M_PI) / 2;
+    double T = 1 - 0.17 * cosf(meanH - DEG2RAD(30)) + 0.24 * cosf(2 * meanH) + 0.32 * cosf(3 * meanH + DEG2RAD(6)) -
+               0.2 * cosf(4 * meanH - DEG2RAD(63));
+    double sl = 1 + (0.015 * SQR(meanL - 50)) / sqrtf(20 + SQR(meanL - 50));
+    double sc = 1 + 0.045 * meanC;
+    double sh = 1 + 0.015 * meanC * T;
+    double rc = 2 * sqrtf(meanC7 / (meanC7 + 6103515625.));
+    double rt = -sinf(DEG2RAD(60 * expf(-SQR((RAD2DEG(meanH) - 275) / 25)))) * rc;
+    return sqrtf(SQR(deltaL / sl) + SQR(deltaC / sc) + SQR(deltaH / sh) + rt * deltaC / sc * deltaH / sh);
+}
+
+/* exported so tests can locate colour pairs whose distance sits next to the threshold (flip-tolerant parity class) */
+double oracle_color_distance_rgb(uint8_t r1, uint8_t g1, uint8_t b1, uint8_t r2, uint8_t g2, uint8_t b2) {
+    float A[3], B[3];
+    rgb2lab(r1, g1, b1, A);
+    rgb2lab(r2, g2, b2, B);
+    return color_distance(A[0], A[1], A[2], B[0], B[1], B[2]);
+}
+
+/*
+ * The COST stage of render_cuda_multi_unified from already-rendered images: renderer.cu:1617-1659 (clouds),
+ * 1668-1686 (6-DoF: stable sort of the observed cloud by label + per-label ranges), 1852-1877 (k=1 search, squared
+ * resolution), 1881-1907 + compute_costs.cuh:293-457 (kernels compute_render_cost :161-273, compute_observed_cost
+ * :274-290, percentage math :364-378,407-446).
+ *
+ * depth/r/g/b: P rendered images.  obs_xyz_aos / obs_rgb_soa / obs_label: observed cloud as handed to the reference
+ * (colours are NOT permuted by the label sort, renderer.cu:1881).  out_counts (3*P ints, optional): rendered points,
+ * unexplained rendered points, explained observed points.  near_thr_flags (P ints, optional): number of colour
+ * comparisons of that pose that fall within color_eps of the threshold (cost_type 1, flip-tolerant class).
+ */
+void oracle_costs(const int32_t* depth, const uint8_t* r, const uint8_t* g, const uint8_t* b, int n_poses, int width,
+                  int height, float cx, float cy, float fx, float fy, float depth_factor, int stride,
+                  const int* pose_label, const float* obs_xyz_aos, const uint8_t* obs_rgb_soa, const int* obs_label,
+                  int n_obs, const float* pose_obs_total, int cost_type, int calc_observed, float sensor_resolution,
+                  float color_distance_threshold, float* rendered_cost, float* observed_cost, float* points_diff_cost,
+                  int32_t* out_counts, int* near_thr_flags, double color_eps) {
+    /* clouds */
+    const int n_rend = oracle_depth2cloud(depth, r, g, b, width, height, n_poses, cx, cy, fx, fy, depth_factor, stride,
+                                          NULL, pose_label, NULL, NULL, NULL, NULL, NULL, NULL, NULL, NULL, 0);
+    const size_t nr = (size_t)(n_rend > 0 ? n_rend : 1);
+    float* c_aos = (float*)calloc(nr * 3, sizeof(float));
+    uint8_t* c_rgb = (uint8_t*)calloc(nr * 3, 1);
+    int* c_map = (int*)calloc(nr, sizeof(int));
+    int* c_label = (int*)calloc(nr, sizeof(int));
+    oracle_depth2cloud(depth, r, g, b, width, height, n_poses, cx, cy, fx, fy, depth_factor, stride, NULL, pose_label,
+                       NULL, NULL, NULL, c_aos, c_rgb, c_map, c_label, NULL, n_rend);
+    /* observed cloud: label sort + ranges (6-DoF only) */
+    const size_t no = (size_t)(n_obs > 0 ? n_obs : 1);
+    float* o_aos = (float*)malloc(no * 3 * sizeof(float));
+    memcpy(o_aos, obs_xyz_aos, (size_t)n_obs * 3 * sizeof(float));
+    int *lb = NULL, *le = NULL, n_labels = 0;
+    if (pose_label) {
+        /* stable counting sort by label */
+        int maxl = -1;
+        for (int i = 0; i < n_obs; ++i) if (obs_label[i] > maxl) maxl = obs_label[i];
+        n_labels = maxl + 1;
+        lb = (int*)calloc((size_t)(n_labels > 0 ? n_labels : 1), sizeof(int));
+        le = (int*)calloc((size_t)(n_labels > 0 ? n_labels : 1), sizeof(int));
+        int* cnt = (int*)calloc((size_t)n_labels + 1, sizeof(int));
+        for (int i = 0; i < n_obs; ++i) cnt[obs_label[i] + 1]++; /* labels are >= 0 here (mask-1 of mask>0 pixels) */
+        for (int l = 0; l < n_labels; ++l) { lb[l] = cnt[l]; cnt[l + 1] += cnt[l]; le[l] = cnt[l + 1]; }
+        int* cur = (int*)malloc(sizeof(int) * (size_t)(n_labels > 0 ? n_labels : 1));
+        for (int l = 0; l < n_labels; ++l) cur[l] = lb[l];
+        for (int i = 0; i < n_obs; ++i) {
+            const int s = cur[obs_label[i]]++;
+            o_aos[3 * (size_t)s] = obs_xyz_aos[3 * (size_t)i];
+            o_aos[3 * (size_t)s + 1] = obs_xyz_aos[3 * (size_t)i + 1];
+            o_aos[3 * (size_t)s + 2] = obs_xyz_aos[3 * (size_t)i + 2];
+        }
+        free(cnt);
+        free(cur);
+    }
+    float* k_dist = (float*)malloc(nr * sizeof(float));
+    int* k_idx = (int*)malloc(nr * sizeof(int));
+    oracle_knn_k1(c_aos, n_rend, o_aos, n_obs, pose_label ? c_label : NULL, lb, le, n_labels, k_dist, k_idx);
+    const float res2 = sensor_resolution * sensor_resolution; /* renderer.cu:1877 */
+
+    const size_t P = (size_t)(n_poses > 0 ? n_poses : 1);
+    float* cost = (float*)calloc(P, sizeof(float));
+    float* num = (float*)calloc(P, sizeof(float));
+    uint8_t* explained = (uint8_t*)calloc(P * no, 1);
+    if (near_thr_flags) memset(near_thr_flags, 0, sizeof(int) * (size_t)n_poses);
+    /* compute_render_cost, compute_costs.cuh:188-272 */
+    for (int i = 0; i < n_rend; ++i) {
+        const int p = c_map[i], o = k_idx[i];
+        num[p] += 1;
+        if (k_dist[i] > res2) { cost[p] += 1.0f; continue; }
+        if (cost_type == 1) {
+            /* :214-229: plane 2 is passed as "red" for both clouds */
+            float lab2[3], lab1[3];
+            rgb2lab(c_rgb[(size_t)i + 2 * n_rend], c_rgb[(size_t)i + n_rend], c_rgb[i], lab2);
+            rgb2lab(obs_rgb_soa[(size_t)o + 2 * n_obs], obs_rgb_soa[(size_t)o + n_obs], obs_rgb_soa[o], lab1);
+            const double cd = color_distance(lab1[0], lab1[1], lab1[2], lab2[0], lab2[1], lab2[2]);
+            if (near_thr_flags && fabs(cd - (double)color_distance_threshold) <= color_eps) near_thr_flags[p]++;
+            if (cd > color_distance_threshold) cost[p] += 1.0f;
+            else explained[(size_t)p * no + o] = 1;
+        } else {
+            explained[(size_t)p * no + o] = 1; /* type 0 and type 2 */
+        }
+    }
+    for (int p = 0; p < n_poses; ++p) {
+        /* :364-378 */
+        const float rendered_explained = num[p] - cost[p];
+        float rc = (num[p] == 0) ? -1 : cost[p] / num[p];
+        rc = (rc == -1) ? -1 : rc * 100;
+        rendered_cost[p] = rc;
+        float expl = 0;
+        for (int o = 0; o < n_obs; ++o) expl += (float)explained[(size_t)p * no + o]; /* compute_observed_cost :284-288 */
+        if (calc_observed) {
+            /* :407-446 */
+            const float tot = pose_obs_total ? pose_obs_total[p] : 0.f;
+            if (points_diff_cost) points_diff_cost[p] = rendered_explained - expl;
+            if (observed_cost) observed_cost[p] = ((tot - expl) / tot) * 100;
+        }
+        if (out_counts) {
+            out_counts[p] = (int32_t)num[p];
+            out_counts[n_poses + p] = (int32_t)cost[p];
+            out_counts[2 * n_poses + p] = (int32_t)expl;
+        }
+    }
+    free(c_aos); free(c_rgb); free(c_map); free(c_label); free(o_aos); free(lb); free(le);
+    free(k_dist); free(k_idx); free(cost); free(num); free(explained);
+}

@@ -1,0 +1,119 @@
+"""ctypes binding of libperch_b200.so -- one Python function per C-ABI entry point in include/perch_b200.h."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+
+LIB_PATH = Path(__file__).resolve().parent / "libperch_b200.so"
+
+PERCH_OK, PERCH_ERR_INVALID, PERCH_ERR_CUDA, PERCH_ERR_NO_DEVICE, PERCH_ERR_CAPACITY = range(5)
+
+
+class PerchError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"perch_b200 error {code}: {msg}")
+        self.code = code
+
+
+class perch_params(C.Structure):
+    _fields_ = [
+        ("stride", C.c_int),
+        ("cost_type", C.c_int),
+        ("calculate_observed_cost", C.c_int),
+        ("sensor_resolution", C.c_float),
+        ("color_distance_threshold", C.c_float),
+        ("occlusion_threshold", C.c_float),
+        ("single_result_image", C.c_int),
+        ("do_icp", C.c_int),
+        ("icp_max_iterations", C.c_int),
+        ("icp_k_correspondences", C.c_int),
+        ("icp_rotation_epsilon", C.c_float),
+        ("icp_transformation_epsilon", C.c_float),
+    ]
+
+
+class perch_outputs(C.Structure):
+    _fields_ = [
+        ("depth", C.c_void_p),
+        ("red", C.c_void_p),
+        ("green", C.c_void_p),
+        ("blue", C.c_void_p),
+        ("cloud", C.c_void_p),
+        ("cloud_color", C.c_void_p),
+        ("cloud_pose_map", C.c_void_p),
+        ("dc_index", C.c_void_p),
+        ("cloud_capacity", C.c_int),
+        ("cloud_point_num", C.c_int),
+        ("rendered_cost", C.c_void_p),
+        ("observed_cost", C.c_void_p),
+        ("points_diff_cost", C.c_void_p),
+        ("counts", C.c_void_p),
+        ("adjusted_poses", C.c_void_p),
+    ]
+
+
+class perch_gpu_stats(C.Structure):
+    _fields_ = [("icp_runtime", C.c_float), ("peak_memory_usage", C.c_double)]
+
+
+class perch_hit(C.Structure):
+    _fields_ = [("cost", C.c_int32), ("pose_id", C.c_int32), ("rendered_cost", C.c_float), ("observed_cost", C.c_float)]
+
+
+# name -> (restype, argtypes); the list doubles as the "every symbol of include/perch_b200.h" check in tests
+_P = C.c_void_p
+SIGNATURES = {
+    "perch_create": (C.c_int, [C.c_int, C.POINTER(_P)]),
+    "perch_destroy": (None, [_P]),
+    "perch_last_error": (C.c_char_p, []),
+    "perch_abi_version": (C.c_int, []),
+    "perch_get_stats": (C.c_int, [_P, C.POINTER(perch_gpu_stats)]),
+    "perch_last_timing": (C.c_int, [_P, C.POINTER(C.c_float), C.POINTER(C.c_int)]),
+    "perch_compute_proj": (C.c_int, [_P, C.c_int, C.c_int, C.c_float, C.c_float, _P]),
+    "perch_set_camera": (C.c_int, [_P, C.c_int, C.c_int, _P, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float]),
+    "perch_set_models": (C.c_int, [_P, _P, C.c_int64, _P, C.c_int]),
+    "perch_set_scene": (C.c_int, [_P, _P, _P, _P, _P, _P]),
+    "perch_set_observed": (C.c_int, [_P, _P, _P, _P, C.c_int]),
+    "perch_depth2cloud": (
+        C.c_int,
+        [_P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int,
+         _P, _P, _P, C.POINTER(C.c_int), _P, _P, _P, _P, _P, _P],
+    ),
+    "perch_render_cost": (C.c_int, [_P, C.c_char_p, _P, C.c_int, _P, _P, _P, C.POINTER(perch_params), C.POINTER(perch_outputs)]),
+    "perch_render_cost_device": (C.c_int, [_P, _P, C.c_int, _P, _P, _P, C.POINTER(perch_params), _P, _P]),
+    "perch_device_alloc": (C.c_int, [_P, C.c_size_t, C.POINTER(_P)]),
+    "perch_device_free": (C.c_int, [_P, _P]),
+    "perch_memcpy_h2d": (C.c_int, [_P, _P, _P, C.c_size_t]),
+    "perch_memcpy_d2h": (C.c_int, [_P, _P, _P, C.c_size_t]),
+    "perch_synchronize": (C.c_int, [_P]),
+    "perch_l2_flush": (C.c_int, [_P]),
+    "perch_topk": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P]),
+}
+
+_lib = None
+
+
+def load_library(path: os.PathLike | None = None) -> C.CDLL:
+    """Load libperch_b200.so (built in-tree by ``make`` / ``__graft_entry__.build()``).  Raises if it is missing."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    p = Path(path) if path else LIB_PATH
+    if not p.exists():
+        raise ImportError(
+            f"{p} not found: build it with `make` (nvcc, sm_100a). perception_b200 has no CPU fallback."
+        )
+    lib = C.CDLL(str(p))
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError here == the library does not export a declared symbol
+        fn.restype = res
+        fn.argtypes = args
+    if path is None:
+        _lib = lib
+    return lib
+
+
+def check(lib: C.CDLL, code: int) -> None:
+    if code != PERCH_OK:
+        raise PerchError(code, lib.perch_last_error().decode("utf-8", "replace"))

@@ -1,0 +1,865 @@
+// C-ABI of libperch_b200.so (include/perch_b200.h): host orchestration of the sm_100a kernels.
+// Mirrors the stage machine of cuda_renderer::render_cuda_multi_unified (renderer.cu:1431-1934) and
+// depth2cloud_global (renderer.cu:1936-2070), with all scene/model state resident in HBM between calls.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <climits>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <numeric>
+#include <string>
+#include <vector>
+
+#include "context.hpp"
+#include "kernels.cuh"
+#include "perch_b200.h"
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CU(call)                                                                                           \
+    do {                                                                                                   \
+        cudaError_t e__ = (call);                                                                          \
+        if (e__ != cudaSuccess)                                                                            \
+            return fail(PERCH_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, \
+                        __LINE__);                                                                         \
+    } while (0)
+
+struct DeviceGuard {
+    int prev = 0;
+    explicit DeviceGuard(int dev) {
+        cudaGetDevice(&prev);
+        cudaSetDevice(dev);
+    }
+    ~DeviceGuard() { cudaSetDevice(prev); }
+};
+
+template <class T>
+int upload(T** dst, const T* src, size_t n, cudaStream_t s) {
+    if (*dst) {
+        cudaFree(*dst);
+        *dst = nullptr;
+    }
+    if (n == 0) return PERCH_OK;
+    CU(cudaMalloc(dst, n * sizeof(T)));
+    if (src) CU(cudaMemcpyAsync(*dst, src, n * sizeof(T), cudaMemcpyHostToDevice, s));
+    return PERCH_OK;
+}
+
+// Bump allocator over the context scratch buffer (256-byte aligned slices).
+struct Scratch {
+    perch_ctx* c;
+    size_t off = 0;
+    explicit Scratch(perch_ctx* ctx) : c(ctx) {}
+    static size_t align(size_t b) { return (b + 255) & ~(size_t)255; }
+    template <class T>
+    T* take(size_t n) {
+        T* p = reinterpret_cast<T*>(static_cast<char*>(c->d_scratch) + off);
+        off += align(n * sizeof(T));
+        return p;
+    }
+};
+
+int ensure_scratch(perch_ctx* c, size_t bytes) {
+    if (bytes <= c->scratch_bytes) return PERCH_OK;
+    if (c->d_scratch) cudaFree(c->d_scratch);
+    c->d_scratch = nullptr;
+    c->scratch_bytes = 0;
+    CU(cudaMalloc(&c->d_scratch, bytes));
+    c->scratch_bytes = bytes;
+    return PERCH_OK;
+}
+
+void note_memory(perch_ctx* c) {
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
+        double used = (double)(total_b - free_b) / 1024.0 / 1024.0;  // MiB like utils.cuh:18-23
+        c->stats.peak_memory_usage = std::max(c->stats.peak_memory_usage, used);
+    }
+}
+
+int env_int(const char* name, int dflt) {
+    const char* v = getenv(name);
+    return (v && *v) ? atoi(v) : dflt;
+}
+
+// ---- observed-cloud grid ------------------------------------------------------------------------------------
+int build_grid(perch_ctx* c, float res) {
+    using namespace perch;
+    const int n = c->n_obs;
+    cudaFree(c->d_grid_pts); c->d_grid_pts = nullptr;
+    cudaFree(c->d_grid_label); c->d_grid_label = nullptr;
+    cudaFree(c->d_cell_start); c->d_cell_start = nullptr;
+    c->grid = ObsGridDev{};
+    c->grid.n_obs = n;
+    c->grid_res = res;
+    if (n == 0) return PERCH_OK;
+    float h = (res > 0.f ? res : 1e-3f) * 1.01f;
+    float mn[3] = {INFINITY, INFINITY, INFINITY}, mx[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (int i = 0; i < n; ++i)
+        for (int k = 0; k < 3; ++k) {
+            float v = c->h_obs_xyz[3 * (size_t)i + k];
+            if (!std::isfinite(v)) return fail(PERCH_ERR_INVALID, "observed cloud contains a non-finite coordinate");
+            mn[k] = std::min(mn[k], v);
+            mx[k] = std::max(mx[k], v);
+        }
+    int dim[3];
+    float org[3], inv_h;
+    for (;;) {
+        inv_h = 1.0f / h;
+        double cells = 1;
+        for (int k = 0; k < 3; ++k) {
+            org[k] = mn[k] - h;
+            dim[k] = (int)std::floor((mx[k] - org[k]) * inv_h) + 2;
+            cells *= dim[k];
+        }
+        if (cells <= 32.0 * 1024 * 1024) break;
+        h *= 1.26f;  // ~2x fewer cells per step; larger cells only add candidates, never lose one
+    }
+    const size_t ncells = (size_t)dim[0] * dim[1] * dim[2];
+    std::vector<uint32_t> cell_of(n), start(ncells + 1, 0);
+    for (int i = 0; i < n; ++i) {
+        int cc[3];
+        for (int k = 0; k < 3; ++k) {
+            float d = c->h_obs_xyz[3 * (size_t)i + k] - org[k];
+            float f = std::floor(d * inv_h);
+            cc[k] = std::min(std::max((int)f, 0), dim[k] - 1);
+        }
+        cell_of[i] = (uint32_t)(((size_t)cc[2] * dim[1] + cc[1]) * dim[0] + cc[0]);
+        start[cell_of[i] + 1]++;
+    }
+    for (size_t k = 0; k < ncells; ++k) start[k + 1] += start[k];
+    std::vector<uint32_t> cursor(start.begin(), start.end() - 1);
+    std::vector<float4> pts(n);
+    std::vector<int> lab(c->obs_has_label ? n : 0);
+    for (int i = 0; i < n; ++i) {  // ascending i => ascending reference index inside every cell
+        uint32_t slot = cursor[cell_of[i]]++;
+        float4 p;
+        p.x = c->h_obs_xyz[3 * (size_t)i];
+        p.y = c->h_obs_xyz[3 * (size_t)i + 1];
+        p.z = c->h_obs_xyz[3 * (size_t)i + 2];
+        int ref = i;
+        memcpy(&p.w, &ref, 4);
+        pts[slot] = p;
+        if (c->obs_has_label) lab[slot] = c->h_obs_label[i];
+    }
+    CU(cudaMalloc(&c->d_grid_pts, n * sizeof(float4)));
+    CU(cudaMemcpyAsync(c->d_grid_pts, pts.data(), n * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
+    if (c->obs_has_label) {
+        CU(cudaMalloc(&c->d_grid_label, n * sizeof(int)));
+        CU(cudaMemcpyAsync(c->d_grid_label, lab.data(), n * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+    }
+    CU(cudaMalloc(&c->d_cell_start, (ncells + 1) * sizeof(uint32_t)));
+    CU(cudaMemcpyAsync(c->d_cell_start, start.data(), (ncells + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice,
+                       c->stream));
+    CU(cudaStreamSynchronize(c->stream));  // host vectors go out of scope
+    c->grid.pts = c->d_grid_pts;
+    c->grid.label = c->d_grid_label;
+    c->grid.cell_start = c->d_cell_start;
+    c->grid.ox = org[0]; c->grid.oy = org[1]; c->grid.oz = org[2];
+    c->grid.inv_h = inv_h;
+    c->grid.dx = dim[0]; c->grid.dy = dim[1]; c->grid.dz = dim[2];
+    return PERCH_OK;
+}
+
+struct ResolvedParams {
+    int stride, cost_type, calc_observed, single_image, do_icp;
+    float res, color_thr, occ_thr;
+};
+
+int check_ready(perch_ctx* c, bool need_obs) {
+    if (!c) return fail(PERCH_ERR_INVALID, "null context");
+    if (!c->have_cam) return fail(PERCH_ERR_INVALID, "perch_set_camera has not been called");
+    if (!c->have_models) return fail(PERCH_ERR_INVALID, "perch_set_models has not been called");
+    if (!c->have_scene) return fail(PERCH_ERR_INVALID, "perch_set_scene has not been called");
+    if (need_obs && !c->have_obs) return fail(PERCH_ERR_INVALID, "perch_set_observed has not been called");
+    return PERCH_OK;
+}
+
+int fill_pose_args(perch_ctx* c, const perch_params* p, perch::PoseArgs& a) {
+    a.models = c->models;
+    a.cam = c->cam;
+    a.scene = c->scene;
+    a.stride = p->stride;
+    a.calc_observed = p->calculate_observed_cost;
+    a.res2 = p->sensor_resolution * p->sensor_resolution;  // renderer.cu:1877
+    a.color_thr = p->color_distance_threshold;
+    a.occlusion_threshold = p->occlusion_threshold;
+    return PERCH_OK;
+}
+
+int prepare_cost_args(perch_ctx* c, const perch_params* p, perch::PoseArgs& a, bool& color) {
+    if (p->stride <= 0 || c->cam.width % p->stride != 0)
+        return fail(PERCH_ERR_INVALID, "stride %d must divide the image width %d (compute_point_clouds.cuh:271)",
+                    p->stride, c->cam.width);
+    if (p->cost_type < 0 || p->cost_type > 2) return fail(PERCH_ERR_INVALID, "cost_type %d not in {0,1,2}", p->cost_type);
+    if (c->grid_res != p->sensor_resolution) {
+        int rc = build_grid(c, p->sensor_resolution);
+        if (rc) return rc;
+    }
+    fill_pose_args(c, p, a);
+    a.grid = c->grid;
+    color = p->cost_type == 1;
+    a.tri_lab = c->d_tri_lab;
+    a.obs_lab = c->d_obs_lab;
+    a.mask_words = (c->n_obs + 31) / 32;
+    const int Lw = c->cam.width / p->stride;
+    int cap = env_int("PERCH_COST_TILE_CAP", 8192);
+    a.tile_cap = std::max(cap, Lw);
+    size_t smem = perch::pose_kernel_smem_bytes(a, false, color);
+    if (smem > (size_t)c->max_smem_optin)
+        return fail(PERCH_ERR_CAPACITY, "observed cloud of %d points needs %zu B of shared memory per CTA (limit %d)",
+                    c->n_obs, smem, c->max_smem_optin);
+    a.err_flag = c->d_err_flag;
+    return PERCH_OK;
+}
+
+int check_err_flag(perch_ctx* c) {
+    int flag = 0;
+    CU(cudaMemcpyAsync(&flag, c->d_err_flag, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    if (flag) {
+        cudaMemsetAsync(c->d_err_flag, 0, sizeof(int), c->stream);
+        return fail(PERCH_ERR_CUDA, "internal error: a fragment fell outside its pose tile (flag %d)", flag);
+    }
+    return PERCH_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* perch_last_error(void) { return g_err.c_str(); }
+int perch_abi_version(void) { return PERCH_B200_ABI_VERSION; }
+
+int perch_create(int device, perch_ctx** out) {
+    if (!out) return fail(PERCH_ERR_INVALID, "out is null");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(PERCH_ERR_NO_DEVICE, "no CUDA device available (%s); libperch_b200 has no CPU fallback",
+                    e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+    if (device < 0 || device >= count) return fail(PERCH_ERR_INVALID, "device %d out of range [0,%d)", device, count);
+    cudaDeviceProp prop;
+    CU(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10)
+        return fail(PERCH_ERR_NO_DEVICE, "device %d is sm_%d%d; this library is built for sm_100a only", device, prop.major,
+                    prop.minor);
+    DeviceGuard g(device);
+    perch_ctx* c = new perch_ctx();
+    c->device = device;
+    c->sm_count = prop.multiProcessorCount;
+    c->max_smem_optin = (int)prop.sharedMemPerBlockOptin;
+    CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    CU(cudaEventCreate(&c->ev0));
+    CU(cudaEventCreate(&c->ev1));
+    CU(cudaMalloc(&c->d_err_flag, sizeof(int)));
+    CU(cudaMemset(c->d_err_flag, 0, sizeof(int)));
+    *out = c;
+    return PERCH_OK;
+}
+
+void perch_destroy(perch_ctx* c) {
+    if (!c) return;
+    DeviceGuard g(c->device);
+    cudaStreamSynchronize(c->stream);
+    void* ptrs[] = {c->d_tri_planes, c->d_tri_color, c->d_model_low, c->d_model_high, c->d_model_aabb, c->d_tri_lab,
+                    c->d_src_depth, c->d_src_label, c->d_src_rgb, c->d_grid_pts, c->d_grid_label, c->d_cell_start,
+                    c->d_obs_lab, c->d_obs_rgb, c->d_scratch, c->d_err_flag, c->d_flush};
+    for (void* p : ptrs)
+        if (p) cudaFree(p);
+    if (c->h_pinned) cudaFreeHost(c->h_pinned);
+    cudaEventDestroy(c->ev0);
+    cudaEventDestroy(c->ev1);
+    cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int perch_get_stats(perch_ctx* c, perch_gpu_stats* out) {
+    if (!c || !out) return fail(PERCH_ERR_INVALID, "null argument");
+    *out = c->stats;
+    return PERCH_OK;
+}
+
+int perch_last_timing(perch_ctx* c, float* ms, int* launches) {
+    if (!c) return fail(PERCH_ERR_INVALID, "null context");
+    if (ms) *ms = c->last_ms;
+    if (launches) *launches = c->last_launches;
+    return PERCH_OK;
+}
+
+int perch_compute_proj(const float K[9], int width, int height, float near_, float far_, float out16[16]) {
+    if (!K || !out16 || width <= 0 || height <= 0) return fail(PERCH_ERR_INVALID, "bad compute_proj argument");
+    // renderer.cu:1386-1410.  The reference writes each flipped entry as -(expr); negation is exact, so the values
+    // below are the same floats.
+    volatile float t;
+    float p[16] = {0};
+    t = 2 * K[0] / width; p[0] = t;
+    t = -2 * K[1] / width; p[1] = -t;
+    t = -2 * K[2] / width; t = t + 1; p[2] = -t;
+    t = 2 * K[4] / height; p[5] = -t;
+    t = 2 * K[5] / height; t = t - 1; p[6] = -t;
+    t = -(far_ + near_) / (far_ - near_); p[10] = -t;
+    t = -2 * far_ * near_ / (far_ - near_); p[11] = t;
+    p[14] = 1;
+    memcpy(out16, p, sizeof(p));
+    return PERCH_OK;
+}
+
+int perch_set_camera(perch_ctx* c, int width, int height, const float proj16[16], float cx, float cy, float fx, float fy,
+                     float depth_factor) {
+    if (!c || !proj16) return fail(PERCH_ERR_INVALID, "null argument");
+    if (width <= 0 || height <= 0 || (int64_t)width * height > (1 << 26))
+        return fail(PERCH_ERR_INVALID, "bad image size %dx%d", width, height);
+    if (c->have_scene && (width != c->cam.width || height != c->cam.height)) c->have_scene = false;
+    c->cam.width = width;
+    c->cam.height = height;
+    memcpy(&c->cam.proj, proj16, 64);
+    c->cam.cx = cx; c->cam.cy = cy; c->cam.fx = fx; c->cam.fy = fy;
+    c->cam.depth_factor = depth_factor;
+    c->have_cam = true;
+    return PERCH_OK;
+}
+
+int perch_set_models(perch_ctx* c, const perch_triangle* tris, int64_t n_tris, const int* tris_model_count, int n_models) {
+    if (!c || (!tris && n_tris > 0) || !tris_model_count || n_models <= 0 || n_tris < 0)
+        return fail(PERCH_ERR_INVALID, "bad set_models argument");
+    if (n_tris > INT_MAX) return fail(PERCH_ERR_CAPACITY, "more than INT_MAX triangles");
+    DeviceGuard g(c->device);
+    std::vector<int> low(n_models), high(n_models);
+    int64_t run = 0;
+    for (int m = 0; m < n_models; ++m) {
+        if (tris_model_count[m] < 0) return fail(PERCH_ERR_INVALID, "negative tris_model_count[%d]", m);
+        low[m] = (int)run;
+        run += tris_model_count[m];
+        high[m] = (int)std::min<int64_t>(run, n_tris);  // the reference also bounds by device_tris_size (image_renderer.cuh:240)
+        low[m] = std::min(low[m], high[m]);
+    }
+    const int64_t stride = (n_tris + 31) & ~(int64_t)31;
+    std::vector<float> planes((size_t)stride * 9, 0.f);
+    std::vector<uint32_t> color((size_t)std::max<int64_t>(n_tris, 1), 0);
+    std::vector<float> aabb((size_t)n_models * 6);
+    for (int m = 0; m < n_models; ++m) {
+        float* bb = &aabb[(size_t)m * 6];
+        bb[0] = bb[1] = bb[2] = INFINITY;
+        bb[3] = bb[4] = bb[5] = -INFINITY;
+        for (int t = low[m]; t < high[m]; ++t) {
+            const float* v = tris[t].v0;  // v0,v1,v2 are contiguous: 9 floats
+            for (int k = 0; k < 9; ++k) {
+                planes[(size_t)k * stride + t] = v[k];
+                bb[k % 3] = std::min(bb[k % 3], v[k]);
+                bb[3 + k % 3] = std::max(bb[3 + k % 3], v[k]);
+            }
+            // (uint8_t)(color.v0) etc. (image_renderer.cuh:152-154)
+            color[t] = (uint32_t)(uint8_t)tris[t].color[0] | ((uint32_t)(uint8_t)tris[t].color[1] << 8) |
+                       ((uint32_t)(uint8_t)tris[t].color[2] << 16);
+        }
+    }
+    int rc;
+    if ((rc = upload(&c->d_tri_planes, planes.data(), planes.size(), c->stream))) return rc;
+    if ((rc = upload(&c->d_tri_color, color.data(), color.size(), c->stream))) return rc;
+    if ((rc = upload(&c->d_model_low, low.data(), low.size(), c->stream))) return rc;
+    if ((rc = upload(&c->d_model_high, high.data(), high.size(), c->stream))) return rc;
+    if ((rc = upload(&c->d_model_aabb, aabb.data(), aabb.size(), c->stream))) return rc;
+    if ((rc = upload<float>(&c->d_tri_lab, nullptr, 3 * color.size(), c->stream))) return rc;
+    CU(perch::launch_rgb2lab_packed(c->d_tri_color, (int)n_tris, c->d_tri_lab, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->models.tri_planes = c->d_tri_planes;
+    c->models.tri_color = c->d_tri_color;
+    c->models.tri_stride = stride;
+    c->models.model_low = c->d_model_low;
+    c->models.model_high = c->d_model_high;
+    c->models.model_aabb = c->d_model_aabb;
+    c->models.n_models = n_models;
+    c->models.n_tris = n_tris;
+    c->h_model_low = low;
+    c->h_model_high = high;
+    c->have_models = true;
+    note_memory(c);
+    return PERCH_OK;
+}
+
+int perch_set_scene(perch_ctx* c, const int32_t* depth, const uint8_t* red, const uint8_t* green, const uint8_t* blue,
+                    const uint8_t* label) {
+    if (!c || !depth) return fail(PERCH_ERR_INVALID, "null argument");
+    if (!c->have_cam) return fail(PERCH_ERR_INVALID, "perch_set_camera must be called before perch_set_scene");
+    DeviceGuard g(c->device);
+    const size_t npx = (size_t)c->cam.width * c->cam.height;
+    int rc;
+    if ((rc = upload(&c->d_src_depth, depth, npx, c->stream))) return rc;
+    if ((rc = upload<uint8_t>(&c->d_src_label, label, label ? npx : 0, c->stream))) return rc;
+    if ((rc = upload<uint8_t>(&c->d_src_rgb, nullptr, 3 * npx, c->stream))) return rc;
+    const uint8_t* planes[3] = {red, green, blue};
+    for (int k = 0; k < 3; ++k) {
+        if (planes[k]) CU(cudaMemcpyAsync(c->d_src_rgb + k * npx, planes[k], npx, cudaMemcpyHostToDevice, c->stream));
+        else CU(cudaMemsetAsync(c->d_src_rgb + k * npx, 0, npx, c->stream));
+    }
+    CU(cudaStreamSynchronize(c->stream));
+    c->scene.depth = c->d_src_depth;
+    c->scene.label = c->d_src_label;
+    c->scene.r = c->d_src_rgb;
+    c->scene.g = c->d_src_rgb + npx;
+    c->scene.b = c->d_src_rgb + 2 * npx;
+    c->have_scene = true;
+    note_memory(c);
+    return PERCH_OK;
+}
+
+int perch_set_observed(perch_ctx* c, const float* xyz_aos, const uint8_t* rgb_soa, const int* label, int n_obs) {
+    if (!c || n_obs < 0 || (n_obs > 0 && !xyz_aos)) return fail(PERCH_ERR_INVALID, "bad set_observed argument");
+    if (n_obs > (1 << 24)) return fail(PERCH_ERR_CAPACITY, "observed cloud larger than 16M points");
+    DeviceGuard g(c->device);
+    c->n_obs = n_obs;
+    c->obs_has_label = label != nullptr;
+    c->h_obs_xyz.assign(xyz_aos, xyz_aos + 3 * (size_t)n_obs);
+    c->h_obs_label.clear();
+    if (label) {
+        // renderer.cu:1681: sort the cloud by label (stable here; thrust's radix sort on int keys is stable too), so
+        // that reference indices -- and with them nearest-neighbour tie-breaks -- follow the sorted order.
+        std::vector<int> order(n_obs);
+        std::iota(order.begin(), order.end(), 0);
+        std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return label[a] < label[b]; });
+        c->h_obs_label.resize(n_obs);
+        for (int i = 0; i < n_obs; ++i) {
+            c->h_obs_label[i] = label[order[i]];
+            for (int k = 0; k < 3; ++k) c->h_obs_xyz[3 * (size_t)i + k] = xyz_aos[3 * (size_t)order[i] + k];
+        }
+    }
+    int rc;
+    if ((rc = upload<uint8_t>(&c->d_obs_rgb, nullptr, 3 * (size_t)std::max(n_obs, 1), c->stream))) return rc;
+    if ((rc = upload<float>(&c->d_obs_lab, nullptr, 3 * (size_t)std::max(n_obs, 1), c->stream))) return rc;
+    if (n_obs > 0) {
+        if (rgb_soa) CU(cudaMemcpyAsync(c->d_obs_rgb, rgb_soa, 3 * (size_t)n_obs, cudaMemcpyHostToDevice, c->stream));
+        else CU(cudaMemsetAsync(c->d_obs_rgb, 0, 3 * (size_t)n_obs, c->stream));
+        // colours stay in the ORIGINAL order and are looked up with (sorted) NN indices, as renderer.cu:1881 does
+        CU(perch::launch_rgb2lab_planes(c->d_obs_rgb, c->d_obs_rgb + n_obs, c->d_obs_rgb + 2 * (size_t)n_obs, n_obs,
+                                        c->d_obs_lab, c->stream));
+    }
+    CU(cudaStreamSynchronize(c->stream));
+    c->grid_res = -1.f;  // grid is (re)built on the next cost call, when sensor_resolution is known
+    c->have_obs = true;
+    note_memory(c);
+    return PERCH_OK;
+}
+
+int perch_depth2cloud(perch_ctx* c, const int32_t* depth, const uint8_t* red, const uint8_t* green, const uint8_t* blue,
+                      int width, int height, int num_poses, float cx, float cy, float fx, float fy, float depth_factor,
+                      int stride, const uint8_t* label_mask, const double* bounds6, const float* camera_transform16,
+                      int* point_num, float* out_cloud_soa, float* out_cloud_aos, uint8_t* out_cloud_color,
+                      int* out_dc_index, int* out_cloud_pose_map, int* out_cloud_label) {
+    if (!c || !depth || !point_num) return fail(PERCH_ERR_INVALID, "null argument");
+    if (width <= 0 || height <= 0 || num_poses <= 0 || stride <= 0) return fail(PERCH_ERR_INVALID, "bad size argument");
+    if (width % stride != 0)
+        return fail(PERCH_ERR_INVALID, "stride %d must divide the image width %d (compute_point_clouds.cuh:271)", stride, width);
+    DeviceGuard g(c->device);
+    const size_t npx = (size_t)width * height * num_poses;
+    if (npx > (size_t)INT_MAX) return fail(PERCH_ERR_CAPACITY, "num_poses*width*height exceeds INT_MAX");
+    const int Lh = (height + stride - 1) / stride;
+    const size_t rows = (size_t)num_poses * Lh;
+    const bool want_out = out_cloud_soa || out_cloud_aos || out_cloud_color || out_cloud_pose_map || out_cloud_label;
+    const int capacity = want_out ? *point_num : 0;
+    if (want_out && capacity < 0) return fail(PERCH_ERR_INVALID, "point_num must hold the buffer capacity on pass 2");
+    // scratch: depth + 3 colour planes + label + row counts + outputs
+    size_t need = Scratch::align(npx * 4) + 4 * Scratch::align(npx) + Scratch::align((rows + 1) * 4) +
+                  2 * Scratch::align((size_t)capacity * 12) + Scratch::align((size_t)capacity * 3) +
+                  2 * Scratch::align((size_t)capacity * 4) + (out_dc_index ? Scratch::align(npx * 4) : 0) + 4096;
+    int rc = ensure_scratch(c, need);
+    if (rc) return rc;
+    Scratch s(c);
+    perch::CloudArgs a;
+    int32_t* d_depth = s.take<int32_t>(npx);
+    CU(cudaMemcpyAsync(d_depth, depth, npx * 4, cudaMemcpyHostToDevice, c->stream));
+    a.depth = d_depth;
+    const uint8_t* planes[3] = {red, green, blue};
+    const uint8_t* d_planes[3] = {nullptr, nullptr, nullptr};
+    for (int k = 0; k < 3; ++k) {
+        uint8_t* p = s.take<uint8_t>(npx);
+        if (planes[k]) {
+            CU(cudaMemcpyAsync(p, planes[k], npx, cudaMemcpyHostToDevice, c->stream));
+            d_planes[k] = p;
+        }
+    }
+    a.red = d_planes[0]; a.green = d_planes[1]; a.blue = d_planes[2];
+    uint8_t* d_label = s.take<uint8_t>(npx);
+    if (label_mask) {
+        CU(cudaMemcpyAsync(d_label, label_mask, npx, cudaMemcpyHostToDevice, c->stream));
+        a.label_mask = d_label;
+    }
+    a.img_w = width; a.img_h = height; a.full_h = height; a.num_images = num_poses;
+    a.stride = stride; a.coord_scale = 1;
+    a.cx = cx; a.cy = cy; a.fx = fx; a.fy = fy; a.depth_factor = depth_factor;
+    a.use_bounds = bounds6 != nullptr && camera_transform16 != nullptr;
+    if (a.use_bounds) {
+        for (int k = 0; k < 6; ++k) a.bounds[k] = (float)bounds6[k];
+        memcpy(a.cam_tf, camera_transform16, 64);
+    }
+    a.row_counts = s.take<int>(rows + 1);
+    a.capacity = capacity;
+    CU(perch::launch_cloud_count(a, c->stream));
+    CU(perch::launch_cloud_scan(a, c->stream));
+    int total = 0;
+    CU(cudaMemcpyAsync(&total, a.row_counts + rows, 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    if (!want_out && !out_dc_index) {
+        *point_num = total;
+        return PERCH_OK;
+    }
+    if (want_out && capacity < total)
+        return fail(PERCH_ERR_CAPACITY, "cloud has %d points but the buffers hold %d", total, capacity);
+    float* d_soa = s.take<float>((size_t)capacity * 3);
+    float* d_aos = s.take<float>((size_t)capacity * 3);
+    uint8_t* d_rgb = s.take<uint8_t>((size_t)capacity * 3);
+    int* d_map = s.take<int>(capacity);
+    int* d_lab = s.take<int>(capacity);
+    int* d_dc = out_dc_index ? s.take<int>(npx) : nullptr;
+    // the reference zero-initialises its outputs (compute_point_clouds.cuh:302-305,317); slots whose pixel fails the
+    // second bounds test stay zero
+    if (capacity > 0) {
+        CU(cudaMemsetAsync(d_soa, 0, (size_t)capacity * 12, c->stream));
+        CU(cudaMemsetAsync(d_aos, 0, (size_t)capacity * 12, c->stream));
+        CU(cudaMemsetAsync(d_rgb, 0, (size_t)capacity * 3, c->stream));
+        CU(cudaMemsetAsync(d_map, 0, (size_t)capacity * 4, c->stream));
+        CU(cudaMemsetAsync(d_lab, 0, (size_t)capacity * 4, c->stream));
+    }
+    a.cloud_soa = out_cloud_soa ? d_soa : nullptr;
+    a.cloud_aos = out_cloud_aos ? d_aos : nullptr;
+    a.cloud_rgb = out_cloud_color ? d_rgb : nullptr;
+    a.pose_map = out_cloud_pose_map ? d_map : nullptr;
+    a.cloud_label = (out_cloud_label && label_mask) ? d_lab : nullptr;
+    a.dc_index = d_dc;
+    CU(perch::launch_cloud_write(a, c->stream));
+    // out_cloud_soa rows are `capacity` floats apart on the device; the host buffer is 3 x total (point_num) like the
+    // reference's cudaMemcpy2D (renderer.cu:2052-2053)
+    for (int k = 0; k < 3 && total > 0; ++k) {
+        if (out_cloud_soa)
+            CU(cudaMemcpyAsync(out_cloud_soa + (size_t)k * total, d_soa + (size_t)k * capacity, (size_t)total * 4,
+                               cudaMemcpyDeviceToHost, c->stream));
+        if (out_cloud_color)
+            CU(cudaMemcpyAsync(out_cloud_color + (size_t)k * total, d_rgb + (size_t)k * capacity, (size_t)total,
+                               cudaMemcpyDeviceToHost, c->stream));
+    }
+    if (out_cloud_aos && total > 0)
+        CU(cudaMemcpyAsync(out_cloud_aos, d_aos, (size_t)total * 12, cudaMemcpyDeviceToHost, c->stream));
+    if (out_cloud_pose_map && total > 0)
+        CU(cudaMemcpyAsync(out_cloud_pose_map, d_map, (size_t)total * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (out_cloud_label && label_mask && total > 0)
+        CU(cudaMemcpyAsync(out_cloud_label, d_lab, (size_t)total * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (out_dc_index) CU(cudaMemcpyAsync(out_dc_index, d_dc, npx * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    *point_num = total;
+    note_memory(c);
+    return PERCH_OK;
+}
+
+int perch_render_cost_device(perch_ctx* c, const float* d_poses16, int n_poses, const int* d_pose_model_map,
+                             const int* d_pose_label, const float* d_pose_obs_total, const perch_params* p,
+                             float* d_costs3p, int32_t* d_counts3p) {
+    int rc = check_ready(c, true);
+    if (rc) return rc;
+    if (!p || !d_poses16 || !d_pose_model_map || !d_costs3p || n_poses < 0)
+        return fail(PERCH_ERR_INVALID, "bad render_cost_device argument");
+    DeviceGuard g(c->device);
+    perch::PoseArgs a;
+    bool color = false;
+    if ((rc = prepare_cost_args(c, p, a, color))) return rc;
+    a.poses = reinterpret_cast<const perch::Mat4*>(d_poses16);
+    a.pose_model_map = d_pose_model_map;
+    a.pose_label = d_pose_label;
+    a.pose_obs_total = d_pose_obs_total;
+    a.n_poses = n_poses;
+    a.out_costs = d_costs3p;
+    a.out_counts = d_counts3p;
+    CU(cudaEventRecord(c->ev0, c->stream));
+    CU(perch::launch_fused_cost(a, color, c->stream));
+    CU(cudaEventRecord(c->ev1, c->stream));
+    c->last_launches = n_poses > 0 ? 1 : 0;
+    c->timing_pending = true;
+    return PERCH_OK;
+}
+
+int perch_device_alloc(perch_ctx* c, size_t bytes, void** d_ptr) {
+    if (!c || !d_ptr) return fail(PERCH_ERR_INVALID, "null argument");
+    DeviceGuard g(c->device);
+    CU(cudaMalloc(d_ptr, bytes ? bytes : 1));
+    return PERCH_OK;
+}
+int perch_device_free(perch_ctx* c, void* d_ptr) {
+    if (!c) return fail(PERCH_ERR_INVALID, "null context");
+    DeviceGuard g(c->device);
+    CU(cudaFree(d_ptr));
+    return PERCH_OK;
+}
+int perch_memcpy_h2d(perch_ctx* c, void* d_dst, const void* h_src, size_t bytes) {
+    if (!c) return fail(PERCH_ERR_INVALID, "null context");
+    DeviceGuard g(c->device);
+    CU(cudaMemcpyAsync(d_dst, h_src, bytes, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return PERCH_OK;
+}
+int perch_memcpy_d2h(perch_ctx* c, void* h_dst, const void* d_src, size_t bytes) {
+    if (!c) return fail(PERCH_ERR_INVALID, "null context");
+    DeviceGuard g(c->device);
+    CU(cudaMemcpyAsync(h_dst, d_src, bytes, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    return PERCH_OK;
+}
+int perch_synchronize(perch_ctx* c) {
+    if (!c) return fail(PERCH_ERR_INVALID, "null context");
+    DeviceGuard g(c->device);
+    CU(cudaStreamSynchronize(c->stream));
+    if (c->timing_pending) {
+        cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1);
+        c->timing_pending = false;
+    }
+    return check_err_flag(c);
+}
+
+int perch_l2_flush(perch_ctx* c) {
+    if (!c) return fail(PERCH_ERR_INVALID, "null context");
+    DeviceGuard g(c->device);
+    const size_t bytes = (size_t)256 << 20;
+    if (!c->d_flush) CU(cudaMalloc(&c->d_flush, bytes));
+    c->flush_value ^= 0xFF;
+    CU(cudaMemsetAsync(c->d_flush, c->flush_value, bytes, c->stream));
+    return PERCH_OK;
+}
+
+int perch_render_cost(perch_ctx* c, const char* stage, const float* poses16, int n_poses, const int* pose_model_map,
+                      const int* pose_label, const float* pose_obs_total, const perch_params* p, perch_outputs* out) {
+    if (!stage || !p || !out) return fail(PERCH_ERR_INVALID, "null argument");
+    const std::string st(stage);
+    const bool s_render = st == "RENDER", s_debug = st == "DEBUG";
+    const bool s_cloud = st.find("CLOUD") != std::string::npos;  // renderer.cu:1821
+    const bool s_cost = st.find("COST") != std::string::npos;    // renderer.cu:1908
+    if (!s_render && !s_debug && !s_cloud && !s_cost) return fail(PERCH_ERR_INVALID, "unknown stage '%s'", stage);
+    const bool do_cost = s_cost || s_debug;
+    int rc = check_ready(c, do_cost);
+    if (rc) return rc;
+    if (n_poses < 0 || (n_poses > 0 && (!poses16 || !pose_model_map))) return fail(PERCH_ERR_INVALID, "bad pose arguments");
+    if (p->do_icp) return fail(PERCH_ERR_INVALID, "do_icp: use perch_gicp_refine + perch_render_cost (see INTEGRATION.md)");
+    DeviceGuard g(c->device);
+    const int W = c->cam.width, H = c->cam.height;
+    const size_t npx = (size_t)W * H;
+    const bool do_images = s_render || s_debug;
+    const bool do_cloud = s_cloud || s_debug;
+    if (p->stride <= 0 || ((do_cloud || do_cost) && W % p->stride != 0))
+        return fail(PERCH_ERR_INVALID, "stride %d must divide the image width %d (compute_point_clouds.cuh:271)", p->stride, W);
+    if (p->single_result_image && (do_cloud || do_cost))
+        return fail(PERCH_ERR_INVALID, "single_result_image is only supported for stage RENDER");
+    const int s = p->stride;
+    const int Lw = W / (do_cloud || do_cost ? s : 1), Lh = (H + s - 1) / s;
+    const size_t P = (size_t)n_poses;
+    const size_t n_img = p->single_result_image ? 1 : P;
+
+    size_t need = Scratch::align(P * 64) + 2 * Scratch::align(P * 4) + Scratch::align(P * 4) + 2 * Scratch::align(P * 12) + 4096;
+    if (do_images) need += Scratch::align(n_img * npx * 4) + 3 * Scratch::align(n_img * npx) + Scratch::align(npx * 8);
+    const size_t lat = (size_t)Lw * Lh;
+    if (do_cloud) need += Scratch::align(P * lat * 4) + 3 * Scratch::align(P * lat) + Scratch::align((P * Lh + 1) * 4);
+    const int cap = do_cloud ? std::max(out->cloud_capacity, 0) : 0;
+    if (do_cloud) need += Scratch::align((size_t)cap * 12) + Scratch::align((size_t)cap * 3) + Scratch::align((size_t)cap * 4) +
+                          (out->dc_index ? Scratch::align(P * npx * 4) : 0);
+    if ((rc = ensure_scratch(c, need))) return rc;
+    Scratch sc(c);
+    float* d_poses = sc.take<float>(P * 16);
+    int* d_pmm = sc.take<int>(P);
+    int* d_plabel = sc.take<int>(P);
+    float* d_tot = sc.take<float>(P);
+    float* d_costs = sc.take<float>(P * 3);
+    int32_t* d_counts = sc.take<int32_t>(P * 3);
+    if (P > 0) {
+        CU(cudaMemcpyAsync(d_poses, poses16, P * 64, cudaMemcpyHostToDevice, c->stream));
+        CU(cudaMemcpyAsync(d_pmm, pose_model_map, P * 4, cudaMemcpyHostToDevice, c->stream));
+        if (pose_label) CU(cudaMemcpyAsync(d_plabel, pose_label, P * 4, cudaMemcpyHostToDevice, c->stream));
+        if (pose_obs_total) CU(cudaMemcpyAsync(d_tot, pose_obs_total, P * 4, cudaMemcpyHostToDevice, c->stream));
+    }
+    int launches = 0;
+    CU(cudaEventRecord(c->ev0, c->stream));
+
+    perch::PoseArgs base;
+    fill_pose_args(c, p, base);
+    base.poses = reinterpret_cast<const perch::Mat4*>(d_poses);
+    base.pose_model_map = d_pmm;
+    base.pose_label = pose_label ? d_plabel : nullptr;
+    base.pose_obs_total = pose_obs_total ? d_tot : nullptr;
+    base.n_poses = n_poses;
+    base.err_flag = c->d_err_flag;
+
+    // ---- images (stage RENDER / DEBUG): renderer.cu:1594-1615 ------------------------------------------------
+    int32_t* d_depth = nullptr;
+    uint8_t *d_r = nullptr, *d_g = nullptr, *d_b = nullptr;
+    if (do_images) {
+        d_depth = sc.take<int32_t>(n_img * npx);
+        d_r = sc.take<uint8_t>(n_img * npx);
+        d_g = sc.take<uint8_t>(n_img * npx);
+        d_b = sc.take<uint8_t>(n_img * npx);
+        unsigned long long* d_keys = sc.take<unsigned long long>(npx);
+        perch::PoseArgs a = base;
+        a.stride = 1;
+        a.img_depth = d_depth; a.img_r = d_r; a.img_g = d_g; a.img_b = d_b;
+        a.tile_cap = std::max(env_int("PERCH_IMAGE_TILE_CAP", 12288), W);
+        if (p->single_result_image) {
+            a.single_keys = d_keys;
+            CU(perch::launch_single_clear(d_keys, (int)npx, c->stream));
+            ++launches;
+        }
+        if (n_poses > 0) {
+            CU(perch::launch_raster_images(a, c->stream));
+            ++launches;
+        }
+        if (p->single_result_image) {
+            CU(perch::launch_resolve_single(a, c->stream));
+            ++launches;
+        }
+    }
+    // ---- clouds (stage CLOUD / DEBUG): renderer.cu:1617-1659,1821-1847 ------------------------------------------
+    int* d_rows = nullptr;
+    float* d_cloud = nullptr;
+    uint8_t* d_cloud_rgb = nullptr;
+    int* d_cloud_map = nullptr;
+    int* d_dc = nullptr;
+    if (do_cloud) {
+        int32_t* l_depth = sc.take<int32_t>(P * lat);
+        uint8_t* l_r = sc.take<uint8_t>(P * lat);
+        uint8_t* l_g = sc.take<uint8_t>(P * lat);
+        uint8_t* l_b = sc.take<uint8_t>(P * lat);
+        d_rows = sc.take<int>(P * Lh + 1);
+        d_cloud = sc.take<float>((size_t)cap * 3);
+        d_cloud_rgb = sc.take<uint8_t>((size_t)cap * 3);
+        d_cloud_map = sc.take<int>(cap);
+        if (out->dc_index) d_dc = sc.take<int>(P * npx);
+        perch::PoseArgs a = base;
+        a.img_depth = l_depth; a.img_r = l_r; a.img_g = l_g; a.img_b = l_b;
+        a.tile_cap = std::max(env_int("PERCH_IMAGE_TILE_CAP", 12288), Lw);
+        if (n_poses > 0) {
+            CU(perch::launch_raster_images(a, c->stream));
+            ++launches;
+        }
+        perch::CloudArgs ca;
+        ca.depth = l_depth; ca.red = l_r; ca.green = l_g; ca.blue = l_b;
+        ca.pose_label = base.pose_label;
+        ca.img_w = Lw; ca.img_h = Lh; ca.full_h = H; ca.num_images = n_poses; ca.stride = 1; ca.coord_scale = s;
+        ca.cx = c->cam.cx; ca.cy = c->cam.cy; ca.fx = c->cam.fx; ca.fy = c->cam.fy; ca.depth_factor = c->cam.depth_factor;
+        ca.row_counts = d_rows;
+        ca.capacity = cap;
+        ca.cloud_soa = out->cloud ? d_cloud : nullptr;
+        ca.cloud_rgb = out->cloud_color ? d_cloud_rgb : nullptr;
+        ca.pose_map = out->cloud_pose_map ? d_cloud_map : nullptr;
+        ca.dc_index = d_dc;
+        if (n_poses > 0) {
+            CU(perch::launch_cloud_count(ca, c->stream));
+            CU(perch::launch_cloud_scan(ca, c->stream));
+            CU(perch::launch_cloud_write(ca, c->stream));
+            launches += 3 + (d_dc ? 1 : 0);
+        } else {
+            CU(cudaMemsetAsync(d_rows, 0, 4, c->stream));
+        }
+    }
+    // ---- costs (stage COST / DEBUG): renderer.cu:1852-1922 ------------------------------------------------------
+    if (do_cost) {
+        perch::PoseArgs a;
+        bool color = false;
+        if ((rc = prepare_cost_args(c, p, a, color))) return rc;
+        a.poses = base.poses; a.pose_model_map = base.pose_model_map; a.pose_label = base.pose_label;
+        a.pose_obs_total = base.pose_obs_total; a.n_poses = n_poses;
+        a.out_costs = d_costs;
+        a.out_counts = d_counts;
+        if (n_poses > 0) {
+            CU(perch::launch_fused_cost(a, color, c->stream));
+            ++launches;
+        }
+    }
+    CU(cudaEventRecord(c->ev1, c->stream));
+
+    // ---- results to the host -------------------------------------------------------------------------------------
+    if (do_images) {
+        if (out->depth) CU(cudaMemcpyAsync(out->depth, d_depth, n_img * npx * 4, cudaMemcpyDeviceToHost, c->stream));
+        if (out->red) CU(cudaMemcpyAsync(out->red, d_r, n_img * npx, cudaMemcpyDeviceToHost, c->stream));
+        if (out->green) CU(cudaMemcpyAsync(out->green, d_g, n_img * npx, cudaMemcpyDeviceToHost, c->stream));
+        if (out->blue) CU(cudaMemcpyAsync(out->blue, d_b, n_img * npx, cudaMemcpyDeviceToHost, c->stream));
+    }
+    if (do_cloud) {
+        int total = 0;
+        CU(cudaMemcpyAsync(&total, d_rows + P * Lh, 4, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        out->cloud_point_num = total;
+        const size_t ncopy = (size_t)std::min(total, cap);
+        if (ncopy > 0) {
+            for (int k = 0; k < 3; ++k) {
+                if (out->cloud)
+                    CU(cudaMemcpyAsync(out->cloud + (size_t)k * cap, d_cloud + (size_t)k * cap, ncopy * 4,
+                                       cudaMemcpyDeviceToHost, c->stream));
+                if (out->cloud_color)
+                    CU(cudaMemcpyAsync(out->cloud_color + (size_t)k * cap, d_cloud_rgb + (size_t)k * cap, ncopy,
+                                       cudaMemcpyDeviceToHost, c->stream));
+            }
+            if (out->cloud_pose_map)
+                CU(cudaMemcpyAsync(out->cloud_pose_map, d_cloud_map, ncopy * 4, cudaMemcpyDeviceToHost, c->stream));
+        }
+        if (out->dc_index && P > 0)
+            CU(cudaMemcpyAsync(out->dc_index, d_dc, P * npx * 4, cudaMemcpyDeviceToHost, c->stream));
+    }
+    if (do_cost && P > 0) {
+        if (out->rendered_cost) CU(cudaMemcpyAsync(out->rendered_cost, d_costs, P * 4, cudaMemcpyDeviceToHost, c->stream));
+        if (p->calculate_observed_cost) {
+            if (out->observed_cost)
+                CU(cudaMemcpyAsync(out->observed_cost, d_costs + P, P * 4, cudaMemcpyDeviceToHost, c->stream));
+            if (out->points_diff_cost)
+                CU(cudaMemcpyAsync(out->points_diff_cost, d_costs + 2 * P, P * 4, cudaMemcpyDeviceToHost, c->stream));
+        }
+        if (out->counts) CU(cudaMemcpyAsync(out->counts, d_counts, P * 12, cudaMemcpyDeviceToHost, c->stream));
+    }
+    CU(cudaStreamSynchronize(c->stream));
+    cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1);
+    c->last_launches = launches;
+    c->timing_pending = false;
+    note_memory(c);
+    return check_err_flag(c);
+}
+
+int perch_topk(const float* rendered, const float* observed, const int* pose_model_map, int n_poses, int pose_id_offset,
+               int n_models, int k, perch_hit* out) {
+    if (!rendered || !observed || !pose_model_map || !out || n_models <= 0 || k <= 0 || n_poses < 0)
+        return fail(PERCH_ERR_INVALID, "bad topk argument");
+    std::vector<std::vector<perch_hit>> per(n_models);
+    for (int i = 0; i < n_poses; ++i) {
+        int m = pose_model_map[i];
+        if (m < 0 || m >= n_models) continue;
+        float r = rendered[i], o = observed[i];
+        if (!(r == r) || !(o == o) || !(std::fabs(r) < 2e9f) || !(std::fabs(o) < 2e9f)) continue;  // NaN/inf: (int) is UB
+        // search_env.cpp:2021-2036: cost = -1 if (int)rendered < 0, else (int)(rendered + observed)
+        if ((int)r < 0) continue;
+        int cost = (int)(r + o);
+        if (cost == -1 || cost == -2) continue;  // search_env.cpp:2555 "Invalid successor"
+        // search_env.cpp:2560-2561: abs(target_cost - source_cost) < 30 on the truncated ints
+        if (!(std::abs((int)r - (int)o) < 30)) continue;
+        per[m].push_back(perch_hit{cost, pose_id_offset + i, r, o});
+    }
+    for (int m = 0; m < n_models; ++m) {
+        auto& v = per[m];
+        size_t kk = std::min<size_t>(k, v.size());
+        std::partial_sort(v.begin(), v.begin() + kk, v.end(), [](const perch_hit& a, const perch_hit& b) {
+            return a.cost != b.cost ? a.cost < b.cost : a.pose_id < b.pose_id;
+        });
+        for (int j = 0; j < k; ++j)
+            out[(size_t)m * k + j] = (size_t)j < kk ? v[j] : perch_hit{INT32_MAX, -1, 0.f, 0.f};
+    }
+    return PERCH_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,113 @@
+// Internal state behind perch_ctx (include/perch_b200.h).  Everything the hot path consults lives in HBM for the
+// lifetime of the context; the reference re-uploads all of it on every call (renderer.cu:1532-1544).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "exact_math.cuh"
+#include "perch_b200.h"
+
+namespace perch {
+
+// Uniform grid over the observed cloud for exact radius-bounded nearest neighbour (replaces the
+// N_rend x N_obs brute force of fast_gicp::brute_force_knn_search at renderer.cu:1853-1865).
+// Cells are h >= 1.001*sensor_resolution wide, so any observed point within sensor_resolution of a query lies in the
+// 3x3x3 cell neighbourhood; points are sorted by cell (x fastest), so each (y,z) row of 3 cells is one range.
+struct ObsGridDev {
+    const float4* pts = nullptr;        // xyz + bit-cast reference index (index in the label-sorted observed cloud)
+    const int* label = nullptr;         // per sorted point; null in 3-DoF mode
+    const uint32_t* cell_start = nullptr;  // ncells + 1
+    float ox = 0, oy = 0, oz = 0;       // grid origin
+    float inv_h = 0;
+    int dx = 0, dy = 0, dz = 0;
+    int n_obs = 0;
+};
+
+struct CameraDev {
+    int width = 0, height = 0;
+    Mat4 proj;
+    float cx = 0, cy = 0, fx = 0, fy = 0, depth_factor = 100.f;
+};
+
+struct ModelsDev {
+    // SoA triangle soup, 9 float planes of stride `tri_stride` + packed colour (r | g<<8 | b<<16):
+    // 40 bytes per triangle instead of the reference's 64-byte AoS Triangle (model.h:62-73).
+    const float* tri_planes = nullptr;
+    const uint32_t* tri_color = nullptr;
+    int64_t tri_stride = 0;
+    const int* model_low = nullptr;   // exclusive scan of tris_model_count (image_renderer.cuh:373-380)
+    const int* model_high = nullptr;  // inclusive scan
+    const float* model_aabb = nullptr;  // 6 floats per model: min xyz, max xyz (object-space)
+    int n_models = 0;
+    int64_t n_tris = 0;
+};
+
+struct SceneDev {
+    const int32_t* depth = nullptr;  // W*H, centimetres
+    const uint8_t* label = nullptr;  // W*H or null
+    const uint8_t* r = nullptr;      // kept for API completeness; the reference reads but never uses them
+    const uint8_t* g = nullptr;
+    const uint8_t* b = nullptr;
+};
+
+}  // namespace perch
+
+struct perch_ctx {
+    int device = 0;
+    int sm_count = 0;
+    int max_smem_optin = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    float last_ms = 0.f;
+    bool timing_pending = false;
+    int* d_err_flag = nullptr;
+    int last_launches = 0;
+    perch_gpu_stats stats{0.f, 0.0};
+
+    perch::CameraDev cam;
+    bool have_cam = false;
+
+    // models
+    float* d_tri_planes = nullptr;
+    uint32_t* d_tri_color = nullptr;
+    int* d_model_low = nullptr;
+    int* d_model_high = nullptr;
+    float* d_model_aabb = nullptr;
+    float* d_tri_lab = nullptr;        // 3 x T CIELAB of the triangle colours (cost_type 1)
+    std::vector<int> h_model_low, h_model_high;
+    perch::ModelsDev models;
+    bool have_models = false;
+
+    // scene
+    int32_t* d_src_depth = nullptr;
+    uint8_t* d_src_label = nullptr;
+    uint8_t* d_src_rgb = nullptr;  // 3 planes
+    perch::SceneDev scene;
+    bool have_scene = false;
+
+    // observed cloud (host copies kept so the grid can be rebuilt when sensor_resolution changes)
+    std::vector<float> h_obs_xyz;      // label-sorted, AoS
+    std::vector<uint8_t> h_obs_rgb;    // original order, 3 x N SoA (reference never permutes colours, renderer.cu:1881)
+    std::vector<int> h_obs_label;      // sorted labels (empty in 3-DoF)
+    bool obs_has_label = false;
+    int n_obs = 0;
+    float grid_res = -1.f;             // sensor_resolution the current grid was built for
+    float4* d_grid_pts = nullptr;
+    int* d_grid_label = nullptr;
+    uint32_t* d_cell_start = nullptr;
+    uint8_t* d_obs_rgb = nullptr;      // 3 x N, original order
+    float* d_obs_lab = nullptr;        // 3 x N CIELAB of observed colours (cost_type 1), indexed by reference index
+    perch::ObsGridDev grid;
+    bool have_obs = false;
+
+    // per-call scratch (grown on demand, never shrunk)
+    void* d_scratch = nullptr;
+    size_t scratch_bytes = 0;
+    void* d_flush = nullptr;           // 256 MiB L2-flush target (perch_l2_flush)
+    int flush_value = 0;
+    void* h_pinned = nullptr;
+    size_t pinned_bytes = 0;
+};

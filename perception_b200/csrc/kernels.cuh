@@ -1,0 +1,89 @@
+// Launch interfaces of the sm_100a kernels behind libperch_b200.so.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+#include "context.hpp"
+
+namespace perch {
+
+// ---- per-pose kernels (pose_kernels.cu): fused render -> cost, and the rasterizer alone ------------------------
+struct PoseArgs {
+    ModelsDev models;
+    CameraDev cam;
+    SceneDev scene;
+    ObsGridDev grid;
+    const Mat4* poses = nullptr;
+    const int* pose_model_map = nullptr;
+    const int* pose_label = nullptr;        // null => 3-DoF occlusion rule, unrestricted NN
+    const float* pose_obs_total = nullptr;  // may be null
+    int n_poses = 0;
+    int stride = 1;                   // lattice pitch in pixels (1 = every pixel)
+    int calc_observed = 0;
+    float res2 = 0.f;                 // sensor_resolution^2 (renderer.cu:1877)
+    float color_thr = 0.f;
+    float occlusion_threshold = 0.f;
+    const float* tri_lab = nullptr;   // 3 floats per triangle (cost_type 1)
+    const float* obs_lab = nullptr;   // 3 floats per observed point (cost_type 1)
+    // MODE_COST outputs
+    float* out_costs = nullptr;       // 3 x P: rendered, observed, points_diff
+    int32_t* out_counts = nullptr;    // 3 x P or null
+    // MODE_IMAGE outputs: P x Lh x Lw lattice images (Lw = W/stride, Lh = ceil(H/stride)); stride 1 = full images
+    int32_t* img_depth = nullptr;
+    uint8_t* img_r = nullptr;
+    uint8_t* img_g = nullptr;
+    uint8_t* img_b = nullptr;
+    // single_result_image (image_renderer.cuh:262-275): all poses z-tested into one W x H key image, resolved by
+    // launch_resolve_single afterwards
+    unsigned long long* single_keys = nullptr;
+    int* err_flag = nullptr;          // set to 1 if a fragment fell outside its pose tile (must never happen)
+    int tile_cap = 0;                 // lattice cells of shared-memory z-buffer per band
+    int mask_words = 0;               // ceil(n_obs / 32) (MODE_COST)
+};
+size_t pose_kernel_smem_bytes(const PoseArgs& a, bool image_mode, bool color);
+cudaError_t launch_fused_cost(const PoseArgs& a, bool color, cudaStream_t stream);
+cudaError_t launch_raster_images(const PoseArgs& a, cudaStream_t stream);
+// single_result_image: clear keys / resolve keys -> depth + rgb with the occlusion rule (label of pose 0, as the
+// reference's pointer arithmetic does, image_renderer.cuh:273-274).
+cudaError_t launch_single_clear(unsigned long long* keys, int n, cudaStream_t stream);
+cudaError_t launch_resolve_single(const PoseArgs& a, cudaStream_t stream);
+
+// ---- depth image(s) -> compacted cloud (cloud.cu) -----------------------------------------------------------
+struct CloudArgs {
+    // Input images are num_images x img_h x img_w.  Samples are taken every `stride` pixels of the input image; a
+    // sample at input pixel (ix,iy) is camera pixel (ix*coord_scale, iy*coord_scale).  Observed image: coord_scale 1,
+    // stride = gpu_stride.  Lattice images written by the rasterizer (stage CLOUD): stride 1, coord_scale = gpu_stride.
+    const int32_t* depth = nullptr;
+    const uint8_t* red = nullptr;    // may be null
+    const uint8_t* green = nullptr;
+    const uint8_t* blue = nullptr;
+    const uint8_t* label_mask = nullptr;  // observed image labels or null
+    const int* pose_label = nullptr;      // rendered: per-pose label or null
+    int img_w = 0, img_h = 0, num_images = 0, stride = 1, coord_scale = 1;
+    int full_h = 0;  // camera image height (for dc_index)
+    float cx = 0, cy = 0, fx = 0, fy = 0, depth_factor = 100.f;
+    bool use_bounds = false;
+    float bounds[6] = {0, 0, 0, 0, 0, 0};  // already cast to float like compute_point_clouds.cuh:86-88
+    float cam_tf[16] = {0};                 // column-major 4x4
+    // scratch / outputs
+    int* row_counts = nullptr;   // num_images * Lh + 1 (exclusive-scanned in place)
+    float* cloud_soa = nullptr;  // 3 x capacity
+    float* cloud_aos = nullptr;  // capacity x 3
+    uint8_t* cloud_rgb = nullptr;
+    int* pose_map = nullptr;
+    int* cloud_label = nullptr;
+    int* dc_index = nullptr;     // num_images*H*W or null
+    int capacity = 0;
+};
+cudaError_t launch_cloud_count(const CloudArgs& a, cudaStream_t stream);
+cudaError_t launch_cloud_scan(const CloudArgs& a, cudaStream_t stream);  // exclusive scan of row_counts, total in last
+cudaError_t launch_cloud_write(const CloudArgs& a, cudaStream_t stream);
+
+// ---- colour preparation (cost_type 1) ------------------------------------------------------------------------
+// lab[3*i..] = rgb2lab(c2[i], c1[i], c0[i]) -- the reference feeds plane 2 as "red" (compute_costs.cuh:214-220).
+cudaError_t launch_rgb2lab_planes(const uint8_t* c0, const uint8_t* c1, const uint8_t* c2, int n, float* lab,
+                                  cudaStream_t stream);
+cudaError_t launch_rgb2lab_packed(const uint32_t* packed_rgb, int n, float* lab, cudaStream_t stream);
+
+}  // namespace perch

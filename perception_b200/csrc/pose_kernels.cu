@@ -1,0 +1,467 @@
+// Per-pose kernels: one CTA renders (and, in COST mode, scores) one candidate pose.
+//
+// MODE_COST  -- fused render -> cost: the COST stage of render_cuda_multi_unified (renderer.cu:1431-1934) without
+//               materialising rendered images, clouds, KNN arrays or the P x N_obs `explained` matrix in HBM.
+// MODE_IMAGE -- the rasterizer alone (image_render, image_renderer.cuh:336-496): writes int32 depth + RGB images,
+//               either full resolution (stage RENDER/DEBUG) or only the stride lattice (stage CLOUD).
+//
+// Steps of one CTA:
+//   1. tile:    conservative screen bbox of the posed model AABB -> rectangle of the stride lattice
+//   2. raster:  every triangle of the pose's model is transformed with the reference's exact float sequence
+//               (exact_math.cuh); only pixels ON the stride lattice can ever reach the cost (compute_point_clouds.cuh
+//               :47-56 samples x*stride,y*stride), so only those are z-tested, with atomicMin into a shared-memory
+//               lattice z-buffer.  Triangles that cover no lattice pixel (the vast majority for fine meshes) are
+//               rejected after the bbox; survivors are compacted into a shared queue and rasterised by dense warps.
+//   3. cost:    per lattice pixel: source-occlusion rule, back-projection, exact nearest observed point through the
+//               uniform grid, explained-bit set in a shared bitmask; warp-shuffle reduction of the three counters;
+//               the reference's percentage formulae (compute_costs.cuh:364-378,407-446).
+#include <cuda_runtime.h>
+
+#include "context.hpp"
+#include "kernels.cuh"
+
+namespace perch {
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kQueueCap = 2048;
+
+template <bool COLOR> struct ZCell;
+template <> struct ZCell<false> {
+    using type = unsigned int;
+    static __device__ __forceinline__ type empty() { return 0xFFFFFFFFu; }
+    // order-preserving map int32 -> uint32 so that atomicMin on the key is a signed min on depth
+    static __device__ __forceinline__ type make(int32_t d, uint32_t) { return (uint32_t)d ^ 0x80000000u; }
+    static __device__ __forceinline__ int32_t depth(type k) { return (int32_t)(k ^ 0x80000000u); }
+    static __device__ __forceinline__ uint32_t tri(type) { return 0; }
+};
+template <> struct ZCell<true> {
+    using type = unsigned long long;
+    static __device__ __forceinline__ type empty() { return ~0ull; }
+    // (depth, triangle index): the lowest-index triangle among equal depths wins the colour (canonical tie-break)
+    static __device__ __forceinline__ type make(int32_t d, uint32_t t) {
+        return ((unsigned long long)((uint32_t)d ^ 0x80000000u) << 32) | t;
+    }
+    static __device__ __forceinline__ int32_t depth(type k) { return (int32_t)((uint32_t)(k >> 32) ^ 0x80000000u); }
+    static __device__ __forceinline__ uint32_t tri(type k) { return (uint32_t)k; }
+};
+
+struct LatticeRect {
+    int x0, x1, y0, y1;  // inclusive lattice coordinates; empty when x0 > x1 or y0 > y1
+};
+
+// Lattice pixels visited by the reference's bbox loops (image_renderer.cuh:110-111) for this triangle.
+__device__ __forceinline__ LatticeRect lattice_rect_of(float bminx, float bmaxx, float bminy, float bmaxy, int W, int H,
+                                                       int s) {
+    LatticeRect r{1, 0, 1, 0};
+    if (!(bmaxx >= 0.f) || !(bmaxy >= 0.f)) return r;  // also rejects NaN upper bounds (loop condition false)
+    unsigned long long p0s = (unsigned long long)__fadd_rn(bminx, 0.5f);  // size_t(bboxmin+0.5f); NaN -> 0
+    unsigned long long p1s = (unsigned long long)__fadd_rn(bminy, 0.5f);
+    if (p0s > (unsigned long long)(W - 1) || p1s > (unsigned long long)(H - 1)) return r;
+    int p0e = (int)bmaxx, p1e = (int)bmaxy;  // <= W-1 / H-1 by the clamp
+    if ((int)p0s > p0e || (int)p1s > p1e) return r;
+    r.x0 = ((int)p0s + s - 1) / s;
+    r.x1 = p0e / s;
+    // raster row P1 is image row H-1-P1 (image_renderer.cuh:128)
+    r.y0 = (H - 1 - p1e + s - 1) / s;
+    r.y1 = (H - 1 - (int)p1s) / s;
+    return r;
+}
+
+__device__ __forceinline__ void load_tri(const ModelsDev& m, int t, float v[9]) {
+#pragma unroll
+    for (int k = 0; k < 9; ++k) v[k] = __ldg(m.tri_planes + (int64_t)k * m.tri_stride + t);
+}
+
+// CIEDE2000 between two CIELAB triples with the reference's mixed float/double evaluation
+// (compute_costs.cuh:90-159): float libm calls on double operands, and the two hue branches that are NOT
+// mutually exclusive with the low-chroma case (the `if` at :112/:133 is overwritten by the following if/else).
+__device__ double ciede2000_ref(float L1, float a1, float b1, float L2, float a2, float b2) {
+    const double kPi = 3.14159265358979323846;
+    double c1 = sqrtf(a1 * a1 + b1 * b1);
+    double c2 = sqrtf(a2 * a2 + b2 * b2);
+    double mc = (c1 + c2) / 2.0;
+    double mc7 = (mc * mc * mc) * (mc * mc * mc) * mc;
+    double g = 0.5 * (1 - sqrtf(mc7 / (mc7 + 6103515625.)));
+    double a1p = a1 * (1 + g);
+    double a2p = a2 * (1 + g);
+    c1 = sqrtf(a1p * a1p + b1 * b1);
+    c2 = sqrtf(a2p * a2p + b2 * b2);
+    double h1 = fmodf(atan2f(b1, a1p) + 2 * kPi, 2 * kPi);
+    double h2 = fmodf(atan2f(b2, a2p) + 2 * kPi, 2 * kPi);
+    double dL = L2 - L1;
+    double dC = c2 - c1;
+    double dh = h2 - h1;
+    if (fabs(dh) > kPi) dh = (h2 > h1) ? dh - 2 * kPi : dh + 2 * kPi;
+    double dH = 2 * sqrtf(c1 * c2) * sinf(dh / 2);
+    double mL = (L1 + L2) / 2;
+    mc = (c1 + c2) / 2.0;
+    mc7 = (mc * mc * mc) * (mc * mc * mc) * mc;
+    double mH;
+    if (fabs(h1 - h2) <= kPi + 1e-5) mH = (h1 + h2) / 2;
+    else if (h1 + h2 < 2 * kPi) mH = (h1 + h2 + 2 * kPi) / 2;
+    else mH = (h1 + h2 - 2 * kPi) / 2;
+    double T = 1 - 0.17 * cosf(mH - (30) * kPi / 180) + 0.24 * cosf(2 * mH) + 0.32 * cosf(3 * mH + (6) * kPi / 180) -
+               0.2 * cosf(4 * mH - (63) * kPi / 180);
+    double dl50 = (mL - 50) * (mL - 50);
+    double sl = 1 + (0.015 * dl50) / sqrtf(20 + dl50);
+    double sc = 1 + 0.045 * mc;
+    double sh = 1 + 0.015 * mc * T;
+    double rc = 2 * sqrtf(mc7 / (mc7 + 6103515625.));
+    double q = ((mH) / kPi * 180 - 275) / 25;
+    double rt = -sinf((60 * expf(-(q * q))) * kPi / 180) * rc;
+    double tl = dL / sl, tc = dC / sc, th = dH / sh;
+    return sqrtf(tl * tl + tc * tc + th * th + rt * dC / sc * dH / sh);
+}
+
+// Exact nearest observed point among those that can lie within sqrt(res2) of q.  Returns the squared distance of the
+// best candidate seen (FLT_MAX if none) and its reference index; lowest reference index wins ties, which is what a
+// strict-`<` linear scan (the brute force this replaces) yields.
+__device__ __forceinline__ void nn_query(const ObsGridDev& g, float qx, float qy, float qz, bool use_label, int label,
+                                         float& best, int& best_ref) {
+    best = FLT_MAX;
+    best_ref = -1;
+    float fx = floorf(__fmul_rn(__fsub_rn(qx, g.ox), g.inv_h));
+    float fy = floorf(__fmul_rn(__fsub_rn(qy, g.oy), g.inv_h));
+    float fz = floorf(__fmul_rn(__fsub_rn(qz, g.oz), g.inv_h));
+    if (!(fx >= -1.f && fx <= (float)g.dx && fy >= -1.f && fy <= (float)g.dy && fz >= -1.f && fz <= (float)g.dz)) return;
+    int cx = (int)fx, cy = (int)fy, cz = (int)fz;
+    int x0 = max(cx - 1, 0), x1 = min(cx + 1, g.dx - 1);
+    if (x0 > x1) return;
+    for (int z = max(cz - 1, 0); z <= min(cz + 1, g.dz - 1); ++z) {
+        for (int y = max(cy - 1, 0); y <= min(cy + 1, g.dy - 1); ++y) {
+            int row = (z * g.dy + y) * g.dx;
+            uint32_t b = __ldg(g.cell_start + row + x0), e = __ldg(g.cell_start + row + x1 + 1);
+            for (uint32_t j = b; j < e; ++j) {
+                if (use_label && __ldg(g.label + j) != label) continue;
+                float4 p = __ldg(g.pts + j);
+                float d = sqdist3(qx, qy, qz, p.x, p.y, p.z);
+                int ref = __float_as_int(p.w);
+                if (d < best || (d == best && ref < best_ref)) {
+                    best = d;
+                    best_ref = ref;
+                }
+            }
+        }
+    }
+}
+
+enum { MODE_COST = 0, MODE_IMAGE = 1 };
+
+template <int MODE, bool COLOR>
+__global__ void __launch_bounds__(kThreads) pose_kernel(PoseArgs a) {
+    using Z = ZCell<COLOR>;
+    using zkey = typename Z::type;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    zkey* zbuf = reinterpret_cast<zkey*>(smem_raw);
+    const int mask_words = (MODE == MODE_COST) ? a.mask_words : 0;
+    uint32_t* mask = reinterpret_cast<uint32_t*>(smem_raw + (size_t)a.tile_cap * sizeof(zkey));
+    int* queue = reinterpret_cast<int*>(mask + mask_words);
+
+    __shared__ Mat4 s_pose;
+    __shared__ int s_rect[4];
+    __shared__ int s_qcount;
+    __shared__ int s_n, s_c, s_e;
+
+    const int pose_i = blockIdx.x;
+    const int tid = threadIdx.x;
+    const int W = a.cam.width, H = a.cam.height, s = a.stride;
+    const int Lw = W / s, Lh = (H + s - 1) / s;
+    const float wf = (float)W, hf = (float)H;  // cvt.rn.f32.u64 of width/height
+    const float cmaxx = (float)(W - 1), cmaxy = (float)(H - 1);
+
+    if (tid < 16) reinterpret_cast<float*>(&s_pose)[tid] = reinterpret_cast<const float*>(a.poses + pose_i)[tid];
+    if (tid == 0) { s_n = 0; s_c = 0; s_e = 0; s_qcount = 0; }
+    for (int w = tid; w < mask_words; w += kThreads) mask[w] = 0u;
+    __syncthreads();
+
+    const int model = a.pose_model_map[pose_i];
+    const bool model_ok = model >= 0 && model < a.models.n_models;
+    const int t_low = model_ok ? a.models.model_low[model] : 0;
+    const int t_high = model_ok ? a.models.model_high[model] : 0;
+    const bool use_label = a.pose_label != nullptr;
+    const int pose_label = use_label ? a.pose_label[pose_i] : 0;
+    const Mat4 pose = s_pose;
+
+    // ---- 1. lattice tile from the posed AABB (first warp) -------------------------------------------------
+    if (tid < 32) {
+        float minx = FLT_MAX, maxx = -FLT_MAX, miny = FLT_MAX, maxy = -FLT_MAX, minz = FLT_MAX;
+        bool bad = false;
+        if (tid < 8 && model_ok) {
+            const float* bb = a.models.model_aabb + 6 * model;
+            float x = bb[(tid & 1) ? 3 : 0], y = bb[(tid & 2) ? 4 : 1], z = bb[(tid & 4) ? 5 : 2];
+            ScreenVertex v = transform_vertex(pose, a.cam.proj, wf, hf, x, y, z);
+            bad = !(v.z > 1e-6f) || !(fabsf(v.sx) < 1e7f) || !(fabsf(v.sy) < 1e7f);
+            minx = maxx = v.sx; miny = maxy = v.sy; minz = v.z;
+        }
+#pragma unroll
+        for (int o = 4; o >= 1; o >>= 1) {
+            minx = fminf(minx, __shfl_xor_sync(0xffffffffu, minx, o));
+            maxx = fmaxf(maxx, __shfl_xor_sync(0xffffffffu, maxx, o));
+            miny = fminf(miny, __shfl_xor_sync(0xffffffffu, miny, o));
+            maxy = fmaxf(maxy, __shfl_xor_sync(0xffffffffu, maxy, o));
+        }
+        bad = __any_sync(0xffffffffu, bad);
+        if (tid == 0) {
+            int x0 = 0, x1 = Lw - 1, y0 = 0, y1 = Lh - 1;
+            if (!model_ok || t_high <= t_low) { x0 = 1; x1 = 0; }
+            else if (!bad) {
+                // 2 px guard band against the float rounding of the per-vertex path; raster row -> image row flip
+                float px0 = floorf(minx) - 2.f, px1 = ceilf(maxx) + 2.f;
+                float py0 = floorf(miny) - 2.f, py1 = ceilf(maxy) + 2.f;
+                int ix0 = (int)fmaxf(px0, 0.f), ix1 = (int)fminf(px1, cmaxx);
+                int r0 = (int)fmaxf(py0, 0.f), r1 = (int)fminf(py1, cmaxy);
+                if (px1 < 0.f || px0 > cmaxx || py1 < 0.f || py0 > cmaxy) { x0 = 1; x1 = 0; }
+                else {
+                    x0 = (ix0 + s - 1) / s; x1 = ix1 / s;
+                    y0 = (H - 1 - r1 + s - 1) / s; y1 = (H - 1 - r0) / s;
+                    x1 = min(x1, Lw - 1); y1 = min(y1, Lh - 1);
+                }
+            }
+            s_rect[0] = x0; s_rect[1] = x1; s_rect[2] = y0; s_rect[3] = y1;
+        }
+    }
+    __syncthreads();
+    const int rx0 = s_rect[0], rx1 = s_rect[1], ry0 = s_rect[2], ry1 = s_rect[3];
+    const int tile_w = rx1 - rx0 + 1;
+    const bool tile_empty = (rx0 > rx1) || (ry0 > ry1);
+    int n_local = 0, c_local = 0;
+
+    if (!tile_empty) {
+        const int band_rows = max(1, a.tile_cap / tile_w);
+        for (int by0 = ry0; by0 <= ry1; by0 += band_rows) {
+            const int by1 = min(by0 + band_rows - 1, ry1);
+            const int band_cells = tile_w * (by1 - by0 + 1);
+            for (int c = tid; c < band_cells; c += kThreads) zbuf[c] = Z::empty();
+            if (tid == 0) s_qcount = 0;
+            __syncthreads();
+
+            // rasterise one triangle into the band's lattice z-buffer
+            auto raster_tri = [&](int t) {
+                float v[9];
+                load_tri(a.models, t, v);
+                ScreenVertex A = transform_vertex(pose, a.cam.proj, wf, hf, v[0], v[1], v[2]);
+                ScreenVertex B = transform_vertex(pose, a.cam.proj, wf, hf, v[3], v[4], v[5]);
+                ScreenVertex C = transform_vertex(pose, a.cam.proj, wf, hf, v[6], v[7], v[8]);
+                float bminx, bmaxx, bminy, bmaxy;
+                bbox_of(A, B, C, cmaxx, cmaxy, bminx, bmaxx, bminy, bmaxy);
+                LatticeRect r = lattice_rect_of(bminx, bmaxx, bminy, bmaxy, W, H, s);
+                int x0 = max(r.x0, rx0), x1 = min(r.x1, rx1), y0 = max(r.y0, by0), y1 = min(r.y1, by1);
+                if (x0 > x1 || y0 > y1) return;
+                TriSetup ts;
+                setup_edges(A, B, C, ts);
+                for (int ly = y0; ly <= y1; ++ly) {
+                    float P1f = (float)(H - 1 - ly * s);
+                    for (int lx = x0; lx <= x1; ++lx) {
+                        int32_t d;
+                        if (fragment_depth(ts, (float)(lx * s), P1f, d))
+                            atomicMin(&zbuf[(ly - by0) * tile_w + (lx - rx0)], Z::make(d, (uint32_t)t));
+                    }
+                }
+            };
+
+            // pass A: bbox test for every triangle, compaction of survivors
+            for (int base = t_low; base < t_high; base += kThreads) {
+                int t = base + tid;
+                bool hit = false;
+                if (t < t_high) {
+                    float v[9];
+                    load_tri(a.models, t, v);
+                    ScreenVertex A = transform_vertex(pose, a.cam.proj, wf, hf, v[0], v[1], v[2]);
+                    ScreenVertex B = transform_vertex(pose, a.cam.proj, wf, hf, v[3], v[4], v[5]);
+                    ScreenVertex C = transform_vertex(pose, a.cam.proj, wf, hf, v[6], v[7], v[8]);
+                    float bminx, bmaxx, bminy, bmaxy;
+                    bbox_of(A, B, C, cmaxx, cmaxy, bminx, bmaxx, bminy, bmaxy);
+                    LatticeRect r = lattice_rect_of(bminx, bmaxx, bminy, bmaxy, W, H, s);
+                    hit = r.x0 <= r.x1 && r.y0 <= r.y1 && r.x0 <= rx1 && r.x1 >= rx0 && r.y0 <= by1 && r.y1 >= by0;
+                    if (hit && (r.x0 < rx0 || r.x1 > rx1 || r.y0 < ry0 || r.y1 > ry1)) atomicOr(a.err_flag, 1);
+                }
+                unsigned ballot = __ballot_sync(0xffffffffu, hit);
+                if (ballot) {
+                    int lane = tid & 31;
+                    int slot = 0;
+                    if (lane == 0) slot = atomicAdd(&s_qcount, __popc(ballot));
+                    slot = __shfl_sync(0xffffffffu, slot, 0) + __popc(ballot & ((1u << lane) - 1u));
+                    if (hit) {
+                        if (slot < kQueueCap) queue[slot] = t;
+                        else raster_tri(t);  // queue full: rasterise in place (rare)
+                    }
+                }
+            }
+            __syncthreads();
+            // pass B: dense rasterisation of the survivors
+            const int qn = min(s_qcount, kQueueCap);
+            for (int e = tid; e < qn; e += kThreads) raster_tri(queue[e]);
+            __syncthreads();
+
+            if (MODE == MODE_IMAGE) {
+                // ---- 3'. resolve the band into the output images (or into the shared key image) -------------
+                for (int c = tid; c < band_cells; c += kThreads) {
+                    zkey k = zbuf[c];
+                    int lx = rx0 + c % tile_w, ly = by0 + c / tile_w;
+                    if (a.single_keys) {
+                        if (k != Z::empty()) atomicMin(a.single_keys + (size_t)ly * Lw + lx, (unsigned long long)k);
+                        continue;
+                    }
+                    int32_t d = 0;
+                    uint32_t rgb = 0;
+                    if (k != Z::empty()) {
+                        d = Z::depth(k);
+                        int u = lx * s, v = ly * s;
+                        int32_t src = __ldg(a.scene.depth + v * W + u);
+                        int src_label = (use_label && a.scene.label) ? (int)__ldg(a.scene.label + v * W + u) : 0;
+                        if (source_occludes(d, src, use_label, pose_label, src_label, a.occlusion_threshold)) d = 0;
+                        else rgb = __ldg(a.models.tri_color + Z::tri(k));
+                        if (d == INT_MAX) d = 0;  // max2zero (image_renderer.cuh:324-333,465-466)
+                    }
+                    size_t o = ((size_t)pose_i * Lh + ly) * Lw + lx;
+                    a.img_depth[o] = d;
+                    if (a.img_r) { a.img_r[o] = (uint8_t)rgb; a.img_g[o] = (uint8_t)(rgb >> 8); a.img_b[o] = (uint8_t)(rgb >> 16); }
+                }
+            } else {
+                // ---- 3. cost over the band's lattice pixels ---------------------------------------------------
+                for (int c = tid; c < band_cells; c += kThreads) {
+                    zkey k = zbuf[c];
+                    if (k == Z::empty()) continue;
+                    int32_t d = Z::depth(k);
+                    int lx = rx0 + c % tile_w, ly = by0 + c / tile_w;
+                    int u = lx * s, v = ly * s;
+                    int32_t src = __ldg(a.scene.depth + v * W + u);
+                    int src_label = (use_label && a.scene.label) ? (int)__ldg(a.scene.label + v * W + u) : 0;
+                    if (source_occludes(d, src, use_label, pose_label, src_label, a.occlusion_threshold)) continue;
+                    if (d <= 0) continue;  // compute_point_clouds.cuh:64,123
+                    ++n_local;
+                    float qx, qy, qz;
+                    back_project(u, v, d, a.cam.cx, a.cam.cy, a.cam.fx, a.cam.fy, a.cam.depth_factor, qx, qy, qz);
+                    float best; int ref;
+                    nn_query(a.grid, qx, qy, qz, use_label, pose_label, best, ref);
+                    if (best > a.res2) { ++c_local; continue; }  // compute_costs.cuh:206-209
+                    if (COLOR) {
+                        uint32_t t = Z::tri(k);
+                        const float* lr = a.tri_lab + 3 * (size_t)t;
+                        const float* lo = a.obs_lab + 3 * (size_t)ref;
+                        double cd = ciede2000_ref(lo[0], lo[1], lo[2], lr[0], lr[1], lr[2]);
+                        if (cd > a.color_thr) { ++c_local; continue; }  // compute_costs.cuh:231-234
+                    }
+                    atomicOr(&mask[ref >> 5], 1u << (ref & 31));  // explained[pose][nn] = 1 (compute_costs.cuh:238,244,268)
+                }
+            }
+            __syncthreads();
+        }
+    }
+
+    if (MODE == MODE_IMAGE) {
+        // every output pixel outside the pose tile is empty: the kernel writes the whole image, no memset pass
+        if (!a.single_keys) {
+            for (int i = tid; i < Lw * Lh; i += kThreads) {
+                int lx = i % Lw, ly = i / Lw;
+                if (!tile_empty && lx >= rx0 && lx <= rx1 && ly >= ry0 && ly <= ry1) continue;
+                size_t o = (size_t)pose_i * Lh * Lw + i;
+                a.img_depth[o] = 0;
+                if (a.img_r) { a.img_r[o] = 0; a.img_g[o] = 0; a.img_b[o] = 0; }
+            }
+        }
+        return;
+    }
+
+    // ---- reduce counters ---------------------------------------------------------------------------------
+    int e_local = 0;
+    for (int w = tid; w < mask_words; w += kThreads) e_local += __popc(mask[w]);
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) {
+        n_local += __shfl_xor_sync(0xffffffffu, n_local, o);
+        c_local += __shfl_xor_sync(0xffffffffu, c_local, o);
+        e_local += __shfl_xor_sync(0xffffffffu, e_local, o);
+    }
+    if ((tid & 31) == 0) {
+        if (n_local) atomicAdd(&s_n, n_local);
+        if (c_local) atomicAdd(&s_c, c_local);
+        if (e_local) atomicAdd(&s_e, e_local);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        const int P = a.n_poses;
+        float n = (float)s_n, c = (float)s_c, e = (float)s_e;
+        // compute_costs.cuh:364-378: explained = n - c; cost = (n == 0) ? -1 : c / n; cost = (cost == -1) ? -1 : cost*100
+        float rendered_explained = __fsub_rn(n, c);
+        float rc = (n == 0.f) ? -1.f : __fdiv_rn(c, n);
+        rc = (rc == -1.f) ? -1.f : __fmul_rn(rc, 100.f);
+        a.out_costs[pose_i] = rc;
+        if (a.calc_observed) {
+            // compute_costs.cuh:407-446: diff = explained - explained_obs; observed = ((tot - explained_obs)/tot)*100
+            float tot = a.pose_obs_total ? a.pose_obs_total[pose_i] : 0.f;
+            a.out_costs[P + pose_i] = __fmul_rn(__fdiv_rn(__fsub_rn(tot, e), tot), 100.f);
+            a.out_costs[2 * P + pose_i] = __fsub_rn(rendered_explained, e);
+        }
+        if (a.out_counts) {
+            a.out_counts[pose_i] = s_n;
+            a.out_counts[P + pose_i] = s_c;
+            a.out_counts[2 * P + pose_i] = s_e;
+        }
+    }
+}
+
+// keys -> images for single_result_image mode
+__global__ void resolve_single_kernel(PoseArgs a) {
+    const int W = a.cam.width, H = a.cam.height;
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= W * H) return;
+    unsigned long long k = a.single_keys[i];
+    int32_t d = 0;
+    uint32_t rgb = 0;
+    if (k != ~0ull) {
+        d = ZCell<true>::depth(k);
+        const bool use_label = a.pose_label != nullptr;
+        int pose_label = use_label ? a.pose_label[0] : 0;
+        int src_label = (use_label && a.scene.label) ? (int)a.scene.label[i] : 0;
+        if (source_occludes(d, a.scene.depth[i], use_label, pose_label, src_label, a.occlusion_threshold)) d = 0;
+        else rgb = a.models.tri_color[ZCell<true>::tri(k)];
+        if (d == INT_MAX) d = 0;
+    }
+    a.img_depth[i] = d;
+    if (a.img_r) { a.img_r[i] = (uint8_t)rgb; a.img_g[i] = (uint8_t)(rgb >> 8); a.img_b[i] = (uint8_t)(rgb >> 16); }
+}
+
+__global__ void fill_keys_kernel(unsigned long long* keys, int n) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) keys[i] = ~0ull;
+}
+
+}  // namespace
+
+size_t pose_kernel_smem_bytes(const PoseArgs& a, bool image_mode, bool color) {
+    return (size_t)a.tile_cap * ((color || image_mode) ? 8 : 4) + (image_mode ? 0 : (size_t)a.mask_words * 4) +
+           (size_t)kQueueCap * 4;
+}
+
+template <int MODE, bool COLOR>
+static cudaError_t launch_pose_kernel(const PoseArgs& a, cudaStream_t stream) {
+    if (a.n_poses <= 0) return cudaSuccess;
+    size_t smem = pose_kernel_smem_bytes(a, MODE == MODE_IMAGE, COLOR);
+    cudaError_t err = cudaFuncSetAttribute(pose_kernel<MODE, COLOR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (err != cudaSuccess) return err;
+    pose_kernel<MODE, COLOR><<<a.n_poses, kThreads, smem, stream>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_fused_cost(const PoseArgs& a, bool color, cudaStream_t stream) {
+    return color ? launch_pose_kernel<MODE_COST, true>(a, stream) : launch_pose_kernel<MODE_COST, false>(a, stream);
+}
+
+cudaError_t launch_raster_images(const PoseArgs& a, cudaStream_t stream) {
+    return launch_pose_kernel<MODE_IMAGE, true>(a, stream);
+}
+
+cudaError_t launch_single_clear(unsigned long long* keys, int n, cudaStream_t stream) {
+    fill_keys_kernel<<<(n + 255) / 256, 256, 0, stream>>>(keys, n);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_resolve_single(const PoseArgs& a, cudaStream_t stream) {
+    int n = a.cam.width * a.cam.height;
+    resolve_single_kernel<<<(n + 255) / 256, 256, 0, stream>>>(a);
+    return cudaGetLastError();
+}
+
+}  // namespace perch

@@ -1,0 +1,317 @@
+"""Host mirror of the reference's ``cuda_renderer`` interface on top of libperch_b200.so.
+
+Names and argument meaning follow cuda_renderer/include/cuda_renderer/renderer.h:
+``compute_proj`` (:87), ``depth2cloud_global`` (:131-153), ``render_cuda_multi_unified`` (:221-268).
+``Renderer`` keeps models / camera / scene / observed cloud resident on the GPU between calls (the reference
+re-uploads them on every call, renderer.cu:1532-1544); the module-level functions with the reference's full argument
+lists are stateless wrappers over it.  Arrays are numpy; nothing here computes on the CPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence
+
+import numpy as np
+
+from . import _capi
+from ._capi import PerchError, perch_outputs, perch_params  # noqa: F401
+
+# cuda_renderer::Model::Triangle (model.h:62-73): 3 x float3, 4 bytes padding, 3 x size_t colour == 64 bytes
+TRIANGLE_DTYPE = np.dtype(
+    {"names": ["v", "color"], "formats": [("<f4", (3, 3)), ("<u8", (3,))], "offsets": [0, 40], "itemsize": 64}
+)
+
+
+def make_triangles(vertices: np.ndarray, colors: np.ndarray) -> np.ndarray:
+    """(T,3,3) float32 vertices + (T,3) colours -> array of 64-byte reference Triangles."""
+    t = np.zeros(len(vertices), dtype=TRIANGLE_DTYPE)
+    t["v"] = np.asarray(vertices, dtype=np.float32)
+    t["color"] = np.asarray(colors, dtype=np.uint64)
+    return t
+
+
+def _ptr(a: Optional[np.ndarray]):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _c(a, dtype) -> Optional[np.ndarray]:
+    if a is None:
+        return None
+    return np.ascontiguousarray(a, dtype=dtype)
+
+
+def compute_proj(K: np.ndarray, width: int, height: int, near: float = 10.0, far: float = 10000.0) -> np.ndarray:
+    """cuda_renderer::compute_proj (renderer.h:87): pinhole K (3x3) -> 4x4 projection (row-major mat4x4)."""
+    lib = _capi.load_library()
+    Kc = _c(K, np.float32).reshape(9)
+    out = np.zeros(16, dtype=np.float32)
+    _capi.check(lib, lib.perch_compute_proj(_ptr(Kc), width, height, near, far, _ptr(out)))
+    return out.reshape(4, 4)
+
+
+def pose_to_mat4x4(pose_in_cam: np.ndarray, scale_factor: float = 100.0) -> np.ndarray:
+    """Model::mat4x4::init_from_eigen (model.h:89-107): double 4x4 -> float, top three rows scaled (m -> cm)."""
+    m = np.asarray(pose_in_cam, dtype=np.float64).copy()
+    m[..., :3, :] *= scale_factor
+    return m.astype(np.float32)
+
+
+class Renderer:
+    """One GPU context (perch_ctx).  Not thread-safe; one per device."""
+
+    def __init__(self, device: int = 0):
+        self._lib = _capi.load_library()
+        h = C.c_void_p()
+        _capi.check(self._lib, self._lib.perch_create(device, C.byref(h)))
+        self._h = h
+        self.width = self.height = 0
+        self.n_models = 0
+
+    # -- lifetime ----------------------------------------------------------------------------------------------
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            self._lib.perch_destroy(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, code: int) -> None:
+        _capi.check(self._lib, code)
+
+    # -- state ---------------------------------------------------------------------------------------------------
+    def set_camera(self, width, height, proj_mat, cx, cy, fx, fy, depth_factor=100.0) -> None:
+        p = _c(proj_mat, np.float32).reshape(16)
+        self._ck(self._lib.perch_set_camera(self._h, width, height, _ptr(p), cx, cy, fx, fy, depth_factor))
+        self.width, self.height = int(width), int(height)
+
+    def set_models(self, tris: np.ndarray, tris_model_count: Sequence[int]) -> None:
+        """@tris / @tris_model_count of render_cuda_multi_unified (renderer.cu:1433,1436)."""
+        t = np.ascontiguousarray(tris, dtype=TRIANGLE_DTYPE)
+        cnt = _c(tris_model_count, np.int32)
+        self._ck(self._lib.perch_set_models(self._h, _ptr(t), len(t), _ptr(cnt), len(cnt)))
+        self.n_models = len(cnt)
+
+    def set_scene(self, source_depth, source_color=None, source_mask_label=None) -> None:
+        """@source_depth (int32 H*W, cm), @source_color (3 planes), @source_mask_label (renderer.cu:1438-1442)."""
+        d = _c(source_depth, np.int32).reshape(-1)
+        assert d.size == self.width * self.height, "source_depth size != width*height"
+        planes = [None, None, None]
+        if source_color is not None:
+            planes = [_c(source_color[k], np.uint8).reshape(-1) for k in range(3)]
+        lab = None if source_mask_label is None or len(source_mask_label) == 0 else _c(source_mask_label, np.uint8).reshape(-1)
+        self._ck(self._lib.perch_set_scene(self._h, _ptr(d), _ptr(planes[0]), _ptr(planes[1]), _ptr(planes[2]), _ptr(lab)))
+
+    def set_observed(self, observed_xyz, observed_color=None, observed_label=None) -> None:
+        """@observed_depth_eigen (N,3), @observed_color (3,N), @result_observed_cloud_label (renderer.cu:1451-1456)."""
+        xyz = _c(observed_xyz, np.float32).reshape(-1, 3)
+        n = len(xyz)
+        col = None if observed_color is None else _c(observed_color, np.uint8).reshape(3, n)
+        lab = None if observed_label is None else _c(observed_label, np.int32).reshape(n)
+        self._ck(self._lib.perch_set_observed(self._h, _ptr(xyz), _ptr(col), _ptr(lab), n))
+        self.n_obs = n
+
+    # -- depth image -> cloud ---------------------------------------------------------------------------------------
+    def depth2cloud_global(self, depth_data, color_data, width, height, num_poses, cx, cy, fx, fy, depth_factor, stride,
+                           label_mask_data=None, observed_cloud_bounds=None, camera_transform=None, want_dc_index=False):
+        """cuda_renderer::depth2cloud_global (renderer.h:131-153).  Returns a dict with the reference's outputs:
+        result_cloud_eigen (N,3), result_cloud (3,N), result_cloud_color (3,N), dc_index, rendered_cloud_point_num,
+        cloud_pose_map, result_observed_cloud_label (labels - 1)."""
+        d = _c(depth_data, np.int32).reshape(-1)
+        planes = [None, None, None]
+        if color_data is not None:
+            planes = [_c(color_data[k], np.uint8).reshape(-1) for k in range(3)]
+        lab = None if label_mask_data is None or len(label_mask_data) == 0 else _c(label_mask_data, np.uint8).reshape(-1)
+        bnd = None if observed_cloud_bounds is None or len(observed_cloud_bounds) == 0 else _c(observed_cloud_bounds, np.float64)
+        # Eigen::Matrix4f is column-major
+        tf = None if camera_transform is None else np.ascontiguousarray(np.asarray(camera_transform, np.float32).T).reshape(16)
+        n = C.c_int(0)
+        args = (width, height, num_poses, cx, cy, fx, fy, depth_factor, stride, _ptr(lab), _ptr(bnd), _ptr(tf))
+        self._ck(self._lib.perch_depth2cloud(self._h, _ptr(d), _ptr(planes[0]), _ptr(planes[1]), _ptr(planes[2]), *args,
+                                             C.byref(n), None, None, None, None, None, None))
+        N = n.value
+        soa = np.zeros((3, N), np.float32)
+        aos = np.zeros((N, 3), np.float32)
+        col = np.zeros((3, N), np.uint8)
+        pmap = np.zeros(N, np.int32)
+        clab = np.zeros(N, np.int32)
+        dc = np.zeros(d.size, np.int32) if want_dc_index else None
+        cap = C.c_int(N)
+        self._ck(self._lib.perch_depth2cloud(self._h, _ptr(d), _ptr(planes[0]), _ptr(planes[1]), _ptr(planes[2]), *args,
+                                             C.byref(cap), _ptr(soa), _ptr(aos), _ptr(col), _ptr(dc), _ptr(pmap), _ptr(clab)))
+        return {
+            "result_cloud_eigen": aos, "result_cloud": soa, "result_cloud_color": col, "dc_index": dc,
+            "rendered_cloud_point_num": N, "cloud_pose_map": pmap,
+            "result_observed_cloud_label": clab if lab is not None else None,
+        }
+
+    # -- the hot path ------------------------------------------------------------------------------------------------
+    def render_cuda_multi_unified(self, stage: str, poses, pose_model_map, pose_segmentation_label=None,
+                                  pose_observed_points_total=None, *, stride=1, cost_type=0,
+                                  calculate_observed_cost=True, sensor_resolution=0.01, color_distance_threshold=20.0,
+                                  occlusion_threshold=1.0, single_result_image=0, do_icp=False,
+                                  cloud_capacity: Optional[int] = None, want_dc_index=False):
+        """cuda_renderer::render_cuda_multi_unified (renderer.h:221-268) against the resident models / scene.
+
+        stage: "RENDER" | "CLOUD" | "COST" | "DEBUG".  poses: (P,4,4) float32 mat4x4 (x100 scaled).  Returns a dict
+        keyed like the reference's output arguments (result_depth, result_color, result_cloud, result_cloud_color,
+        result_cloud_point_num, result_cloud_pose_map, rendered_cost, observed_cost, points_diff_cost) plus `counts`
+        (3,P) int32 = rendered points, unexplained rendered points, explained observed points."""
+        P4 = _c(poses, np.float32).reshape(-1, 16)
+        P = len(P4)
+        pmm = _c(pose_model_map, np.int32).reshape(-1)
+        assert len(pmm) == P, "pose_model_map length != number of poses"
+        plab = None
+        if pose_segmentation_label is not None and len(pose_segmentation_label) > 0:
+            plab = _c(pose_segmentation_label, np.int32).reshape(-1)
+            assert len(plab) == P
+        ptot = None if pose_observed_points_total is None else _c(pose_observed_points_total, np.float32).reshape(-1)
+        prm = perch_params(stride, cost_type, int(bool(calculate_observed_cost)), sensor_resolution, color_distance_threshold,
+                           occlusion_threshold, int(single_result_image), int(bool(do_icp)), 0, 0, -1.0, -1.0)
+        out = perch_outputs()
+        res = {}
+        W, H = self.width, self.height
+        st = stage
+        images = st in ("RENDER", "DEBUG")
+        clouds = st == "DEBUG" or "CLOUD" in st
+        costs = st == "DEBUG" or "COST" in st
+        n_img = 1 if single_result_image else P
+        if images:
+            res["result_depth"] = np.zeros((n_img, H, W), np.int32)
+            res["result_color"] = np.zeros((3, n_img, H, W), np.uint8)
+            out.depth = res["result_depth"].ctypes.data
+            out.red, out.green, out.blue = (res["result_color"][k].ctypes.data for k in range(3))
+        if clouds:
+            if cloud_capacity is None:
+                cloud_capacity = P * (W // stride) * ((H + stride - 1) // stride)
+            cap = int(cloud_capacity)
+            cloud = np.zeros((3, cap), np.float32)
+            ccol = np.zeros((3, cap), np.uint8)
+            cmap = np.zeros(cap, np.int32)
+            out.cloud, out.cloud_color, out.cloud_pose_map = cloud.ctypes.data, ccol.ctypes.data, cmap.ctypes.data
+            out.cloud_capacity = cap
+            if want_dc_index:
+                res["result_dc_index"] = np.zeros(P * W * H, np.int32)
+                out.dc_index = res["result_dc_index"].ctypes.data
+        if costs:
+            res["rendered_cost"] = np.zeros(P, np.float32)
+            res["observed_cost"] = np.zeros(P, np.float32)
+            res["points_diff_cost"] = np.zeros(P, np.float32)
+            res["counts"] = np.zeros((3, P), np.int32)
+            out.rendered_cost = res["rendered_cost"].ctypes.data
+            out.observed_cost = res["observed_cost"].ctypes.data
+            out.points_diff_cost = res["points_diff_cost"].ctypes.data
+            out.counts = res["counts"].ctypes.data
+        self._ck(self._lib.perch_render_cost(self._h, st.encode(), _ptr(P4), P, _ptr(pmm), _ptr(plab), _ptr(ptot),
+                                             C.byref(prm), C.byref(out)))
+        if clouds:
+            n = min(out.cloud_point_num, cap)
+            res["result_cloud_point_num"] = out.cloud_point_num
+            res["result_cloud"] = cloud[:, :n].copy()
+            res["result_cloud_color"] = ccol[:, :n].copy()
+            res["result_cloud_pose_map"] = cmap[:n].copy()
+        return res
+
+    # -- introspection ---------------------------------------------------------------------------------------------
+    def last_timing(self):
+        ms, n = C.c_float(0), C.c_int(0)
+        self._ck(self._lib.perch_last_timing(self._h, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
+    def stats(self):
+        s = _capi.perch_gpu_stats()
+        self._ck(self._lib.perch_get_stats(self._h, C.byref(s)))
+        return {"icp_runtime": s.icp_runtime, "peak_memory_usage": s.peak_memory_usage}
+
+    # -- device-resident scoring (bench / pipelining) ------------------------------------------------------------------
+    def device_alloc(self, nbytes: int) -> int:
+        p = C.c_void_p()
+        self._ck(self._lib.perch_device_alloc(self._h, nbytes, C.byref(p)))
+        return p.value
+
+    def device_free(self, ptr: int) -> None:
+        self._ck(self._lib.perch_device_free(self._h, C.c_void_p(ptr)))
+
+    def h2d(self, dptr: int, arr: np.ndarray) -> None:
+        a = np.ascontiguousarray(arr)
+        self._ck(self._lib.perch_memcpy_h2d(self._h, C.c_void_p(dptr), _ptr(a), a.nbytes))
+
+    def d2h(self, arr: np.ndarray, dptr: int) -> None:
+        assert arr.flags["C_CONTIGUOUS"]
+        self._ck(self._lib.perch_memcpy_d2h(self._h, _ptr(arr), C.c_void_p(dptr), arr.nbytes))
+
+    def render_cost_device(self, d_poses: int, n_poses: int, d_pose_model_map: int, d_pose_label: Optional[int],
+                           d_pose_obs_total: Optional[int], d_costs: int, d_counts: Optional[int], *, stride, cost_type,
+                           calculate_observed_cost=True, sensor_resolution=0.01, color_distance_threshold=20.0,
+                           occlusion_threshold=1.0) -> None:
+        """Enqueue the fused render->cost kernel on device-resident inputs; returns without synchronising."""
+        prm = perch_params(stride, cost_type, int(bool(calculate_observed_cost)), sensor_resolution, color_distance_threshold,
+                           occlusion_threshold, 0, 0, 0, 0, -1.0, -1.0)
+        self._ck(self._lib.perch_render_cost_device(self._h, C.c_void_p(d_poses), n_poses, C.c_void_p(d_pose_model_map),
+                                                    C.c_void_p(d_pose_label) if d_pose_label else None,
+                                                    C.c_void_p(d_pose_obs_total) if d_pose_obs_total else None,
+                                                    C.byref(prm), C.c_void_p(d_costs),
+                                                    C.c_void_p(d_counts) if d_counts else None))
+
+    def synchronize(self) -> None:
+        self._ck(self._lib.perch_synchronize(self._h))
+
+    def l2_flush(self) -> None:
+        self._ck(self._lib.perch_l2_flush(self._h))
+
+
+def topk(rendered_cost, observed_cost, pose_model_map, n_models: int, k: int = 1, pose_id_offset: int = 0) -> np.ndarray:
+    """Per-model best-k candidates by the caller's rule (search_env.cpp:2016-2036, 2542-2583).  Returns a
+    structured array (n_models, k) with fields cost, pose_id, rendered_cost, observed_cost (cost INT32_MAX = empty)."""
+    lib = _capi.load_library()
+    r = _c(rendered_cost, np.float32)
+    o = _c(observed_cost, np.float32)
+    m = _c(pose_model_map, np.int32)
+    dt = np.dtype([("cost", "<i4"), ("pose_id", "<i4"), ("rendered_cost", "<f4"), ("observed_cost", "<f4")])
+    out = np.zeros((n_models, k), dtype=dt)
+    _capi.check(lib, lib.perch_topk(_ptr(r), _ptr(o), _ptr(m), len(r), pose_id_offset, n_models, k, _ptr(out)))
+    return out
+
+
+# ---- stateless wrappers with the reference's full argument lists -------------------------------------------------------
+def depth2cloud_global(depth_data, color_data, width, height, num_poses, pose_occluded, kCameraCX, kCameraCY, kCameraFX,
+                       kCameraFY, depth_factor, stride, point_dim=3, label_mask_data=None, observed_cloud_bounds=None,
+                       camera_transform=None, device=0):
+    """Argument order of cuda_renderer::depth2cloud_global (renderer.h:131-153) minus the output references, which are
+    returned as a dict.  `pose_occluded` and `point_dim` are accepted and ignored like in the reference."""
+    with Renderer(device) as r:
+        return r.depth2cloud_global(depth_data, color_data, width, height, num_poses, kCameraCX, kCameraCY, kCameraFX,
+                                    kCameraFY, depth_factor, stride, label_mask_data, observed_cloud_bounds, camera_transform)
+
+
+def render_cuda_multi_unified(stage, tris, poses, pose_model_map, tris_model_count, width, height, proj_mat, source_depth,
+                              source_color, single_result_image, source_mask_label, pose_segmentation_label, stride,
+                              point_dim, depth_factor, kCameraCX, kCameraCY, kCameraFX, kCameraFY, observed_depth_eigen,
+                              observed_color, observed_point_num, pose_observed_points_total, result_observed_cloud_label,
+                              cost_type, calculate_observed_cost, sensor_resolution, color_distance_threshold,
+                              occlusion_threshold, do_icp=False, device=0):
+    """Argument order of cuda_renderer::render_cuda_multi_unified (renderer.h:221-268) minus outputs (returned as a dict)
+    and minus `observed_depth` (the SoA duplicate of observed_depth_eigen) / `clutter_cost` (USE_CLUTTER is compiled out,
+    model.h:18).  Uploads everything on every call, like the reference."""
+    with Renderer(device) as r:
+        r.set_camera(width, height, proj_mat, kCameraCX, kCameraCY, kCameraFX, kCameraFY, depth_factor)
+        r.set_models(tris, tris_model_count)
+        r.set_scene(source_depth, source_color, source_mask_label)
+        has_label = pose_segmentation_label is not None and len(pose_segmentation_label) > 0
+        xyz = np.asarray(observed_depth_eigen, np.float32).reshape(-1, 3)[:observed_point_num]
+        col = None if observed_color is None else np.asarray(observed_color, np.uint8).reshape(3, -1)[:, :observed_point_num]
+        r.set_observed(xyz, col, result_observed_cloud_label if has_label else None)
+        return r.render_cuda_multi_unified(
+            stage, poses, pose_model_map, pose_segmentation_label, pose_observed_points_total, stride=stride,
+            cost_type=cost_type, calculate_observed_cost=calculate_observed_cost, sensor_resolution=sensor_resolution,
+            color_distance_threshold=color_distance_threshold, occlusion_threshold=occlusion_threshold,
+            single_result_image=single_result_image, do_icp=do_icp)

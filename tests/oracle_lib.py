@@ -1,0 +1,219 @@
+"""ctypes access to the TEST oracles: oracle/_build/libperch_oracle.so (CPU restatement) and
+oracle/_ref/libperch_ref.so (the reference's own CUDA kernels, GPU box only).  Test infrastructure only."""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+import numpy as np
+
+from perception_b200.renderer import TRIANGLE_DTYPE
+
+ROOT = Path(__file__).resolve().parent.parent
+ORACLE_SO = ROOT / "oracle" / "_build" / "libperch_oracle.so"
+REF_SO = ROOT / "oracle" / "_ref" / "libperch_ref.so"
+
+_vp = C.c_void_p
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(_vp)
+
+
+def _c(a, dt):
+    return None if a is None else np.ascontiguousarray(a, dtype=dt)
+
+
+class Oracle:
+    def __init__(self):
+        self.lib = C.CDLL(str(ORACLE_SO))
+        self.lib.oracle_depth2cloud.restype = C.c_int
+        self.lib.oracle_color_distance_rgb.restype = C.c_double
+        self.lib.oracle_color_distance_rgb.argtypes = [C.c_uint8] * 6
+
+    def compute_proj(self, K, w, h, near=10.0, far=10000.0):
+        out = np.zeros(16, np.float32)
+        Kc = _c(K, np.float32).reshape(9)
+        self.lib.oracle_compute_proj(_p(Kc), C.c_int(w), C.c_int(h), C.c_float(near), C.c_float(far), _p(out))
+        return out.reshape(4, 4)
+
+    def render(self, tris, tris_model_count, poses, pose_model_map, width, height, proj, source_depth=None,
+               source_label=None, pose_label=None, occlusion_threshold=1.0, single_result_image=0):
+        tris = np.ascontiguousarray(tris, dtype=TRIANGLE_DTYPE)
+        cnt = _c(tris_model_count, np.int32)
+        P4 = _c(poses, np.float32).reshape(-1, 16)
+        P = len(P4)
+        pmm = _c(pose_model_map, np.int32)
+        proj = _c(proj, np.float32).reshape(16)
+        sd = np.zeros(width * height, np.int32) if source_depth is None else _c(source_depth, np.int32).reshape(-1)
+        sl = None if source_label is None else _c(source_label, np.uint8).reshape(-1)
+        pl = None if pose_label is None else _c(pose_label, np.int32)
+        n_img = 1 if single_result_image else P
+        depth = np.zeros((n_img, height, width), np.int32)
+        rgb = np.zeros((3, n_img, height, width), np.uint8)
+        self.lib.oracle_render(_p(tris), C.c_int(len(tris)), _p(P4), C.c_int(P), _p(pmm), _p(cnt), C.c_int(len(cnt)),
+                               C.c_int(width), C.c_int(height), _p(proj), _p(sd), _p(sl), _p(pl),
+                               C.c_float(occlusion_threshold), C.c_int(single_result_image), _p(depth), _p(rgb[0]),
+                               _p(rgb[1]), _p(rgb[2]))
+        return depth, rgb
+
+    def depth2cloud(self, depth, color, width, height, num_images, cx, cy, fx, fy, depth_factor, stride, label_mask=None,
+                    pose_label=None, bounds=None, cam_tf=None, want_dc_index=False):
+        d = _c(depth, np.int32).reshape(-1)
+        planes = [None] * 3 if color is None else [_c(color[k], np.uint8).reshape(-1) for k in range(3)]
+        lm = None if label_mask is None else _c(label_mask, np.uint8).reshape(-1)
+        pl = None if pose_label is None else _c(pose_label, np.int32)
+        bd = None if bounds is None else _c(bounds, np.float64)
+        tf = None if cam_tf is None else np.ascontiguousarray(np.asarray(cam_tf, np.float32).T).reshape(16)
+        args = (_p(d), _p(planes[0]), _p(planes[1]), _p(planes[2]), C.c_int(width), C.c_int(height), C.c_int(num_images),
+                C.c_float(cx), C.c_float(cy), C.c_float(fx), C.c_float(fy), C.c_float(depth_factor), C.c_int(stride),
+                _p(lm), _p(pl), _p(bd), _p(tf))
+        n = self.lib.oracle_depth2cloud(*args, None, None, None, None, None, None, C.c_int(0))
+        soa = np.zeros((3, n), np.float32)
+        aos = np.zeros((n, 3), np.float32)
+        rgb = np.zeros((3, n), np.uint8)
+        pmap = np.zeros(n, np.int32)
+        lab = np.zeros(n, np.int32)
+        dc = np.zeros(d.size, np.int32) if want_dc_index else None
+        self.lib.oracle_depth2cloud(*args, _p(soa), _p(aos), _p(rgb), _p(pmap), _p(lab), _p(dc), C.c_int(n))
+        return {"n": n, "soa": soa, "aos": aos, "rgb": rgb, "pose_map": pmap, "label": lab, "dc_index": dc}
+
+    def knn_k1(self, src, tgt, src_label=None, label_begin=None, label_end=None):
+        s = _c(src, np.float32).reshape(-1, 3)
+        t = _c(tgt, np.float32).reshape(-1, 3)
+        sl = None if src_label is None else _c(src_label, np.int32)
+        lb = None if label_begin is None else _c(label_begin, np.int32)
+        le = None if label_end is None else _c(label_end, np.int32)
+        dist = np.zeros(len(s), np.float32)
+        idx = np.zeros(len(s), np.int32)
+        self.lib.oracle_knn_k1(_p(s), C.c_int(len(s)), _p(t), C.c_int(len(t)), _p(sl), _p(lb), _p(le),
+                               C.c_int(0 if lb is None else len(lb)), _p(dist), _p(idx))
+        return dist, idx
+
+    def costs(self, depth, color, width, height, cx, cy, fx, fy, depth_factor, stride, pose_label, obs_xyz, obs_rgb,
+              obs_label, pose_obs_total, cost_type, calc_observed, sensor_resolution, color_distance_threshold,
+              color_eps=1e-3):
+        d = _c(depth, np.int32).reshape(-1, height, width)
+        P = len(d)
+        planes = [_c(color[k], np.uint8).reshape(-1) for k in range(3)]
+        pl = None if pose_label is None else _c(pose_label, np.int32)
+        ox = _c(obs_xyz, np.float32).reshape(-1, 3)
+        n_obs = len(ox)
+        orgb = np.zeros((3, n_obs), np.uint8) if obs_rgb is None else _c(obs_rgb, np.uint8).reshape(3, n_obs)
+        ol = None if obs_label is None else _c(obs_label, np.int32)
+        tot = None if pose_obs_total is None else _c(pose_obs_total, np.float32)
+        rc = np.zeros(P, np.float32)
+        oc = np.zeros(P, np.float32)
+        dc = np.zeros(P, np.float32)
+        counts = np.zeros((3, P), np.int32)
+        near = np.zeros(P, np.int32)
+        self.lib.oracle_costs(_p(d), _p(planes[0]), _p(planes[1]), _p(planes[2]), C.c_int(P), C.c_int(width), C.c_int(height),
+                              C.c_float(cx), C.c_float(cy), C.c_float(fx), C.c_float(fy), C.c_float(depth_factor),
+                              C.c_int(stride), _p(pl), _p(ox), _p(orgb), _p(ol), C.c_int(n_obs), _p(tot), C.c_int(cost_type),
+                              C.c_int(int(calc_observed)), C.c_float(sensor_resolution), C.c_float(color_distance_threshold),
+                              _p(rc), _p(oc), _p(dc), _p(counts), _p(near), C.c_double(color_eps))
+        return {"rendered_cost": rc, "observed_cost": oc, "points_diff_cost": dc, "counts": counts, "near_threshold": near}
+
+    def color_distance_rgb(self, c1, c2):
+        return self.lib.oracle_color_distance_rgb(*[int(v) for v in c1], *[int(v) for v in c2])
+
+
+class Reference:
+    """The reference's own CUDA kernels (oracle/ref_harness.cu).  Needs a GPU."""
+
+    def __init__(self):
+        if not REF_SO.exists():
+            raise FileNotFoundError(f"{REF_SO} missing: build with `make -C oracle ref` where /root/reference exists")
+        self.lib = C.CDLL(str(REF_SO))
+
+    def render(self, tris, tris_model_count, poses, pose_model_map, width, height, proj, source_depth=None,
+               source_color=None, source_label=None, pose_label=None, occlusion_threshold=1.0, single_result_image=0):
+        tris = np.ascontiguousarray(tris, dtype=TRIANGLE_DTYPE)
+        cnt = _c(tris_model_count, np.int32)
+        P4 = _c(poses, np.float32).reshape(-1, 16)
+        P = len(P4)
+        pmm = _c(pose_model_map, np.int32)
+        proj = _c(proj, np.float32).reshape(16)
+        npx = width * height
+        sd = np.zeros(npx, np.int32) if source_depth is None else _c(source_depth, np.int32).reshape(-1)
+        sc = [np.zeros(npx, np.uint8)] * 3 if source_color is None else [_c(source_color[k], np.uint8).reshape(-1) for k in range(3)]
+        sl = None if source_label is None else _c(source_label, np.uint8).reshape(-1)
+        pl = None if pose_label is None else _c(pose_label, np.int32)
+        n_img = 1 if single_result_image else P
+        depth = np.zeros((n_img, height, width), np.int32)
+        rgb = np.zeros((3, n_img, height, width), np.uint8)
+        rc = self.lib.ref_render(_p(tris), C.c_int(len(tris)), _p(P4), C.c_int(P), _p(pmm), _p(cnt), C.c_int(len(cnt)),
+                                 C.c_int(width), C.c_int(height), _p(proj), _p(sd), _p(sc[0]), _p(sc[1]), _p(sc[2]), _p(sl),
+                                 _p(pl), C.c_float(occlusion_threshold), C.c_int(single_result_image), _p(depth), _p(rgb[0]),
+                                 _p(rgb[1]), _p(rgb[2]))
+        assert rc == 0, "ref_render failed"
+        return depth, rgb
+
+    def depth2cloud(self, depth, color, width, height, num_images, cx, cy, fx, fy, depth_factor, stride, label_mask=None,
+                    bounds=None, cam_tf=None, want_dc_index=False):
+        d = _c(depth, np.int32).reshape(-1)
+        planes = [np.zeros(d.size, np.uint8)] * 3 if color is None else [_c(color[k], np.uint8).reshape(-1) for k in range(3)]
+        lm = None if label_mask is None else _c(label_mask, np.uint8).reshape(-1)
+        bd = None if bounds is None else _c(bounds, np.float64)
+        tf = None if cam_tf is None else np.ascontiguousarray(np.asarray(cam_tf, np.float32).T).reshape(16)
+        n = C.c_int(0)
+        args = (_p(d), _p(planes[0]), _p(planes[1]), _p(planes[2]), C.c_int(width), C.c_int(height), C.c_int(num_images),
+                C.c_float(cx), C.c_float(cy), C.c_float(fx), C.c_float(fy), C.c_float(depth_factor), C.c_int(stride),
+                _p(lm), _p(bd), _p(tf))
+        rc = self.lib.ref_depth2cloud(*args, C.byref(n), None, None, None, None, None, None)
+        assert rc == 0
+        N = n.value
+        soa = np.zeros((3, N), np.float32)
+        aos = np.zeros((N, 3), np.float32)
+        rgb = np.zeros((3, N), np.uint8)
+        pmap = np.zeros(N, np.int32)
+        lab = np.zeros(N, np.int32)
+        dc = np.zeros(d.size, np.int32) if want_dc_index else None
+        rc = self.lib.ref_depth2cloud(*args, C.byref(n), _p(soa), _p(aos), _p(rgb), _p(pmap), _p(lab), _p(dc))
+        assert rc == 0
+        return {"n": N, "soa": soa, "aos": aos, "rgb": rgb, "pose_map": pmap, "label": lab, "dc_index": dc}
+
+    def render_cost(self, tris, tris_model_count, poses, pose_model_map, width, height, proj, source_depth, source_color,
+                    source_label, pose_label, stride, depth_factor, cx, cy, fx, fy, obs_xyz, obs_rgb, obs_label,
+                    pose_obs_total, cost_type, calc_observed, sensor_resolution, color_distance_threshold,
+                    occlusion_threshold, want_cloud=False):
+        tris = np.ascontiguousarray(tris, dtype=TRIANGLE_DTYPE)
+        cnt = _c(tris_model_count, np.int32)
+        P4 = _c(poses, np.float32).reshape(-1, 16)
+        P = len(P4)
+        pmm = _c(pose_model_map, np.int32)
+        proj = _c(proj, np.float32).reshape(16)
+        npx = width * height
+        sd = _c(source_depth, np.int32).reshape(-1)
+        sc = [np.zeros(npx, np.uint8)] * 3 if source_color is None else [_c(source_color[k], np.uint8).reshape(-1) for k in range(3)]
+        sl = None if source_label is None else _c(source_label, np.uint8).reshape(-1)
+        pl = None if pose_label is None else _c(pose_label, np.int32)
+        ox = _c(obs_xyz, np.float32).reshape(-1, 3)
+        n_obs = len(ox)
+        orgb = np.zeros((3, n_obs), np.uint8) if obs_rgb is None else _c(obs_rgb, np.uint8).reshape(3, n_obs)
+        ol = None if obs_label is None else _c(obs_label, np.int32)
+        tot = np.zeros(P, np.float32) if pose_obs_total is None else _c(pose_obs_total, np.float32)
+        rc_ = np.zeros(P, np.float32)
+        oc = np.zeros(P, np.float32)
+        dc = np.zeros(P, np.float32)
+        n_rend = C.c_int(0)
+        cap = P * (width // stride) * ((height + stride - 1) // stride) if want_cloud else 0
+        cloud = np.zeros((3, max(cap, 1)), np.float32)
+        pmap = np.zeros(max(cap, 1), np.int32)
+        nnd = np.zeros(max(cap, 1), np.float32)
+        nni = np.zeros(max(cap, 1), np.int32)
+        ms = np.zeros(4, np.float32)
+        rc = self.lib.ref_render_cost(
+            _p(tris), C.c_int(len(tris)), _p(P4), C.c_int(P), _p(pmm), _p(cnt), C.c_int(len(cnt)), C.c_int(width),
+            C.c_int(height), _p(proj), _p(sd), _p(sc[0]), _p(sc[1]), _p(sc[2]), _p(sl), _p(pl), C.c_int(stride),
+            C.c_int(int(depth_factor)), C.c_float(cx), C.c_float(cy), C.c_float(fx), C.c_float(fy), _p(ox), _p(orgb), _p(ol),
+            C.c_int(n_obs), _p(tot), C.c_int(cost_type), C.c_int(int(calc_observed)), C.c_float(sensor_resolution),
+            C.c_float(color_distance_threshold), C.c_float(occlusion_threshold), _p(rc_), _p(oc), _p(dc), C.byref(n_rend),
+            _p(cloud) if want_cloud else None, _p(pmap) if want_cloud else None, C.c_int(cap),
+            _p(nnd) if want_cloud else None, _p(nni) if want_cloud else None, _p(ms))
+        assert rc == 0, "ref_render_cost failed"
+        out = {"rendered_cost": rc_, "observed_cost": oc, "points_diff_cost": dc, "n_rend": n_rend.value, "ms": ms}
+        if want_cloud:
+            n = n_rend.value
+            out.update(cloud=cloud[:, :n], pose_map=pmap[:n], nn_sqdist=nnd[:n], nn_index=nni[:n])
+        return out

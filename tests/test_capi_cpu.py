@@ -1,0 +1,75 @@
+"""CPU-side checks of the drop-in boundary: the C-ABI library loads, exports every symbol include/perch_b200.h
+declares, its host-only entry points behave like the reference's host code, and it refuses to run without a GPU."""
+import ctypes as C
+import re
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from conftest import has_gpu
+from oracle_lib import Oracle
+from perception_b200 import _capi, synth
+from perception_b200.renderer import TRIANGLE_DTYPE, compute_proj, topk
+
+ROOT = Path(__file__).resolve().parent.parent
+HEADER = (ROOT / "include" / "perch_b200.h").read_text()
+
+
+def declared_symbols():
+    body = re.sub(r"/\*.*?\*/", "", HEADER, flags=re.S)
+    return sorted(set(re.findall(r"\b(perch_[a-z0-9_]+)\s*\(", body)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = _capi.load_library()
+    names = declared_symbols()
+    assert len(names) >= 20
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/perch_b200.h but not exported"
+        assert n in _capi.SIGNATURES, f"{n} has no ctypes signature"
+    assert lib.perch_abi_version() == int(re.search(r"PERCH_B200_ABI_VERSION (\d+)", HEADER).group(1))
+
+
+def test_struct_layouts_match_reference():
+    # cuda_renderer::Model::Triangle is 64 bytes with the colour at offset 40 (model.h:62-73, size_t alignment)
+    assert TRIANGLE_DTYPE.itemsize == 64 and TRIANGLE_DTYPE.fields["color"][1] == 40
+    assert C.sizeof(_capi.perch_hit) == 16
+    assert C.sizeof(_capi.perch_params) == 48
+
+
+def test_compute_proj_equals_oracle():
+    for K, w, h in [(synth.camera_K(), 640, 480), (np.array([[300.5, 0.25, 161.2], [0, 299.1, 118.7], [0, 0, 1]], np.float32), 320, 240)]:
+        a = compute_proj(K, w, h, 10, 10000)
+        b = Oracle().compute_proj(K, w, h, 10, 10000)
+        assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+
+
+def test_topk_follows_caller_rule():
+    # search_env.cpp:2016-2036 + 2542-2583: cost=(int)(r+o); skip (int)r<0; |int(r)-int(o)| < 30; strict < => first wins
+    r = np.array([10.9, 10.2, -1.0, 50.0, 5.0, 3.5, 3.9], np.float32)
+    o = np.array([10.9, 10.1, 5.0, 10.0, 60.0, 3.0, 3.0], np.float32)
+    m = np.array([0, 0, 0, 0, 0, 1, 1], np.int32)
+    t = topk(r, o, m, n_models=3, k=2, pose_id_offset=100)
+    assert t["cost"][0].tolist() == [20, 21] and t["pose_id"][0].tolist() == [101, 100]
+    assert t["cost"][1].tolist() == [6, 6] and t["pose_id"][1].tolist() == [105, 106]  # tie -> lowest pose id first
+    assert t["cost"][2].tolist() == [2**31 - 1] * 2 and t["pose_id"][2].tolist() == [-1, -1]
+    nan = topk(np.array([1, np.nan], np.float32), np.array([np.nan, 1], np.float32), np.zeros(2, np.int32), 1, 1)
+    assert nan["pose_id"][0, 0] == -1
+
+
+@pytest.mark.skipif(has_gpu(), reason="checks the no-GPU behaviour")
+def test_create_fails_loudly_without_gpu():
+    lib = _capi.load_library()
+    h = C.c_void_p()
+    rc = lib.perch_create(0, C.byref(h))
+    assert rc == _capi.PERCH_ERR_NO_DEVICE and not h.value
+    assert b"no CPU fallback" in lib.perch_last_error()
+    from perception_b200.renderer import Renderer
+    with pytest.raises(_capi.PerchError):
+        Renderer(0)
+
+
+def test_missing_library_raises(tmp_path):
+    with pytest.raises(ImportError):
+        _capi.load_library(tmp_path / "libperch_b200.so")

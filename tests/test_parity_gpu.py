@@ -1,0 +1,353 @@
+"""GPU parity tests: libperch_b200.so (through its C-ABI) vs the CPU oracle and vs the reference's own CUDA kernels
+(oracle/_ref/libperch_ref.so) on identical seeded inputs.
+
+Parity classes: bit-exact int32 depth / masks / point counts; float costs equal (they are exact
+functions of the counts); colour cost flip-tolerant near the threshold.  The reference rasterizer is racy
+(image_renderer.cuh:161-186), so reference-vs-canonical mismatches are counted and bounded, not hidden.
+"""
+import numpy as np
+import pytest
+
+from conftest import has_gpu
+from oracle_lib import REF_SO, Oracle, Reference
+from scenes import make_case, observed_3dof, observed_6dof, poses_near_gt
+
+pytestmark = pytest.mark.gpu
+
+if has_gpu():
+    from perception_b200 import synth
+    from perception_b200.renderer import Renderer, TRIANGLE_DTYPE, make_triangles, pose_to_mat4x4, topk
+
+
+@pytest.fixture(scope="module")
+def orc():
+    return Oracle()
+
+
+@pytest.fixture(scope="module")
+def ref():
+    if not REF_SO.exists():
+        pytest.skip("oracle/_ref/libperch_ref.so not built (needs /root/reference at build time)")
+    return Reference()
+
+
+def make_renderer(case, with_label=False):
+    s = case.scene
+    r = Renderer(0)
+    r.set_camera(case.width, case.height, case.proj, case.cx, case.cy, case.fx, case.fy, synth.DEPTH_FACTOR)
+    r.set_models(s.tris, s.tris_model_count)
+    r.set_scene(s.source_depth, s.source_color, s.source_label if with_label else None)
+    return r
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("size,n_tris", [((640, 480), 600), ((640, 480), 5000), ((160, 120), 300)])
+def test_render_3dof_bit_exact(orc, ref, size, n_tris):
+    case = make_case(n_tris, 3, 42, *size)
+    s = case.scene
+    poses, pmm, _ = poses_near_gt(case, 24)
+    with make_renderer(case) as r:
+        out = r.render_cuda_multi_unified("RENDER", poses, pmm, occlusion_threshold=1.0)
+    d_o, c_o = orc.render(s.tris, s.tris_model_count, poses, pmm, case.width, case.height, case.proj, s.source_depth,
+                          None, None, 1.0)
+    assert np.array_equal(out["result_depth"], d_o), f"{np.count_nonzero(out['result_depth'] != d_o)} depth pixels differ from the oracle"
+    assert np.array_equal(out["result_color"], c_o)
+    assert (d_o > 0).sum() > 1000
+    d_r, c_r = ref.render(s.tris, s.tris_model_count, poses, pmm, case.width, case.height, case.proj, s.source_depth,
+                          s.source_color, None, None, 1.0)
+    bad = np.count_nonzero(d_r != d_o)
+    print(f"reference-vs-canonical depth mismatches: {bad} of {d_o.size} pixels")
+    assert bad <= max(4, d_o.size // 1_000_000), "reference kernel deviates from the canonical semantics beyond its race window"
+    same = d_r == d_o
+    cbad = np.count_nonzero((c_r != c_o).any(0) & same)
+    print(f"reference-vs-canonical colour mismatches (equal-depth ties / races): {cbad}")
+    assert cbad <= (d_o > 0).sum() // 50
+
+
+def test_render_6dof_labels_bit_exact(orc, ref):
+    case = make_case(2000, 4, 7)
+    s = case.scene
+    poses, pmm, lab = poses_near_gt(case, 16)
+    with make_renderer(case, with_label=True) as r:
+        out = r.render_cuda_multi_unified("RENDER", poses, pmm, lab)
+    d_o, c_o = orc.render(s.tris, s.tris_model_count, poses, pmm, case.width, case.height, case.proj, s.source_depth,
+                          s.source_label, lab, 1.0)
+    assert np.array_equal(out["result_depth"], d_o)
+    assert np.array_equal(out["result_color"], c_o)
+    d_r, _ = ref.render(s.tris, s.tris_model_count, poses, pmm, case.width, case.height, case.proj, s.source_depth,
+                        s.source_color, s.source_label, lab, 1.0)
+    assert np.count_nonzero(d_r != d_o) <= 4
+
+
+def test_render_edge_cases(orc):
+    case = make_case(600, 3, 42)
+    s = case.scene
+    T = s.gt_poses[0].copy()
+    poses = []
+    for dx, dz in [(0.0, 0.0), (0.55, 0.0), (-0.6, 0.0), (5.0, 0.0), (0.0, -0.55), (0.0, 3.0)]:
+        Tt = T.copy()
+        Tt[0, 3] += dx
+        Tt[2, 3] += dz
+        poses.append(pose_to_mat4x4(Tt))
+    # box (12 huge triangles) close to the camera, and behind it
+    box = len(s.tris_model_count) - 1
+    Tb = np.eye(4); Tb[:3, 3] = (0.02, 0.01, 0.25)
+    poses.append(pose_to_mat4x4(Tb))
+    Tb2 = np.eye(4); Tb2[:3, 3] = (0.0, 0.0, -0.5)
+    poses.append(pose_to_mat4x4(Tb2))
+    poses = np.stack(poses)
+    pmm = np.array([s.gt_models[0]] * 6 + [box, box], np.int32)
+    with make_renderer(case) as r:
+        out = r.render_cuda_multi_unified("RENDER", poses, pmm)
+        empty = r.render_cuda_multi_unified("RENDER", np.zeros((0, 4, 4), np.float32), np.zeros(0, np.int32))
+    assert empty["result_depth"].shape[0] == 0
+    d_o, c_o = orc.render(s.tris, s.tris_model_count, poses, pmm, case.width, case.height, case.proj, s.source_depth,
+                          None, None, 1.0)
+    for i in range(len(poses)):
+        assert np.array_equal(out["result_depth"][i], d_o[i]), f"pose {i}: {np.count_nonzero(out['result_depth'][i] != d_o[i])} px differ"
+    assert np.array_equal(out["result_color"], c_o)
+    assert (d_o[3] > 0).sum() == 0  # far off screen
+
+
+def test_single_result_image(orc, ref):
+    case = make_case(600, 3, 42)
+    s = case.scene
+    poses = np.stack([pose_to_mat4x4(T) for T in s.gt_poses])
+    pmm = np.array(s.gt_models, np.int32)
+    with make_renderer(case) as r:
+        out = r.render_cuda_multi_unified("RENDER", poses, pmm, single_result_image=1, occlusion_threshold=100.0)
+    d_o, c_o = orc.render(s.tris, s.tris_model_count, poses, pmm, case.width, case.height, case.proj, s.source_depth,
+                          None, None, 100.0, single_result_image=1)
+    assert out["result_depth"].shape == (1, case.height, case.width)
+    assert np.array_equal(out["result_depth"], d_o)
+    assert np.array_equal(out["result_color"], c_o)
+    d_r, _ = ref.render(s.tris, s.tris_model_count, poses, pmm, case.width, case.height, case.proj, s.source_depth,
+                        s.source_color, None, None, 100.0, single_result_image=1)
+    assert np.count_nonzero(d_r != d_o) <= 4
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("mode", ["plain", "label", "bounds"])
+@pytest.mark.parametrize("stride", [1, 4, 8])
+def test_depth2cloud_parity(orc, ref, mode, stride):
+    case = make_case(600, 3, 42)
+    s = case.scene
+    kw = {}
+    if mode == "label":
+        kw["label_mask"] = s.source_label
+    if mode == "bounds":
+        kw["bounds"] = synth.table_bounds(s)
+        kw["cam_tf"] = np.linalg.inv(s.T_cam_table)
+    o = orc.depth2cloud(s.source_depth, s.source_color, case.width, case.height, 1, case.cx, case.cy, case.fx, case.fy,
+                        100.0, stride, want_dc_index=True, **kw)
+    q = ref.depth2cloud(s.source_depth, s.source_color, case.width, case.height, 1, case.cx, case.cy, case.fx, case.fy,
+                        100.0, stride, want_dc_index=True, **kw)
+    with Renderer(0) as r:
+        p = r.depth2cloud_global(s.source_depth, s.source_color, case.width, case.height, 1, case.cx, case.cy, case.fx,
+                                 case.fy, 100.0, stride, kw.get("label_mask"), kw.get("bounds"), kw.get("cam_tf"),
+                                 want_dc_index=True)
+    assert p["rendered_cloud_point_num"] == o["n"] == q["n"] > 0
+    for name, a, b, c in [("soa", p["result_cloud"], o["soa"], q["soa"]), ("aos", p["result_cloud_eigen"], o["aos"], q["aos"]),
+                          ("rgb", p["result_cloud_color"], o["rgb"], q["rgb"]), ("map", p["cloud_pose_map"], o["pose_map"], q["pose_map"]),
+                          ("dc", p["dc_index"], o["dc_index"], q["dc_index"])]:
+        assert np.array_equal(a.view(np.uint8), b.view(np.uint8)), f"{name}: product != oracle"
+        assert np.array_equal(b.view(np.uint8), c.view(np.uint8)), f"{name}: oracle != reference"
+    if mode == "label":
+        assert np.array_equal(p["result_observed_cloud_label"], o["label"])
+        assert np.array_equal(o["label"], q["label"])
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+def _cost_case(orc, n_tris, stride, dof6, n_poses, seed=42):
+    case = make_case(n_tris, 3, seed)
+    s = case.scene
+    obs = observed_6dof(case, stride, orc) if dof6 else observed_3dof(case, stride, orc)
+    poses, pmm, lab = poses_near_gt(case, n_poses)
+    if dof6:
+        cnt = np.bincount(obs["label"], minlength=len(s.gt_poses)).astype(np.float32)
+        tot = cnt[lab]
+    else:
+        tot = synth.cylinder_counts(s, obs["aos"], poses, pmm)
+    return case, obs, poses, pmm, (lab if dof6 else None), tot
+
+
+@pytest.mark.parametrize("n_tris,stride,dof6", [(600, 4, False), (5000, 4, False), (5000, 8, True), (600, 5, False), (2000, 1, True)])
+def test_cost_parity(orc, ref, n_tris, stride, dof6):
+    n_poses = 12 if stride == 1 else 40
+    case, obs, poses, pmm, lab, tot = _cost_case(orc, n_tris, stride, dof6, n_poses)
+    s = case.scene
+    res = 0.01 if dof6 else 0.0075
+    ct = 2 if dof6 else 0
+    with make_renderer(case, with_label=dof6) as r:
+        r.set_observed(obs["aos"], obs["rgb"], obs["label"] if dof6 else None)
+        out = r.render_cuda_multi_unified("COST", poses, pmm, lab, tot, stride=stride, cost_type=ct, sensor_resolution=res,
+                                          occlusion_threshold=1.0)
+    d_o, c_o = orc.render(s.tris, s.tris_model_count, poses, pmm, case.width, case.height, case.proj, s.source_depth,
+                          s.source_label if dof6 else None, lab, 1.0)
+    o = orc.costs(d_o, c_o, case.width, case.height, case.cx, case.cy, case.fx, case.fy, 100.0, stride, lab, obs["aos"],
+                  obs["rgb"], obs["label"] if dof6 else None, tot, ct, True, res, 20.0)
+    assert np.array_equal(out["counts"], o["counts"]), f"counts differ:\n{out['counts']}\n{o['counts']}"
+    assert o["counts"][0].sum() > 0 and o["counts"][2].sum() > 0
+    for k in ("rendered_cost", "observed_cost", "points_diff_cost"):
+        assert np.array_equal(out[k], o[k], equal_nan=True), k
+    q = ref.render_cost(s.tris, s.tris_model_count, poses, pmm, case.width, case.height, case.proj, s.source_depth,
+                        s.source_color, s.source_label if dof6 else None, lab, stride, 100, case.cx, case.cy, case.fx,
+                        case.fy, obs["aos"], obs["rgb"], obs["label"] if dof6 else None, tot, ct, True, res, 20.0, 1.0)
+    for k in ("rendered_cost", "observed_cost", "points_diff_cost"):
+        np.testing.assert_allclose(out[k], q[k], rtol=1e-4, atol=0, equal_nan=True, err_msg=f"{k} vs reference kernels")
+    assert q["n_rend"] == int(o["counts"][0].sum())
+
+
+def test_cost_colour_flip_tolerant(orc, ref):
+    case, obs, poses, pmm, lab, tot = _cost_case(orc, 5000, 4, False, 32)
+    s = case.scene
+    thr = 20.0
+    with make_renderer(case) as r:
+        r.set_observed(obs["aos"], obs["rgb"], None)
+        out = r.render_cuda_multi_unified("COST", poses, pmm, None, tot, stride=4, cost_type=1, sensor_resolution=0.0075,
+                                          color_distance_threshold=thr)
+    d_o, c_o = orc.render(s.tris, s.tris_model_count, poses, pmm, case.width, case.height, case.proj, s.source_depth,
+                          None, None, 1.0)
+    o = orc.costs(d_o, c_o, case.width, case.height, case.cx, case.cy, case.fx, case.fy, 100.0, 4, None, obs["aos"],
+                  obs["rgb"], None, tot, 1, True, 0.0075, thr, color_eps=1e-3)
+    q = ref.render_cost(s.tris, s.tris_model_count, poses, pmm, case.width, case.height, case.proj, s.source_depth,
+                        s.source_color, None, None, 4, 100, case.cx, case.cy, case.fx, case.fy, obs["aos"], obs["rgb"], None,
+                        tot, 1, True, 0.0075, thr, 1.0)
+    assert np.array_equal(out["counts"][0], o["counts"][0])
+    # rendered points whose CIEDE2000 distance is within 1e-3 of the threshold may flip (float libm differs CPU/GPU)
+    slack = o["near_threshold"]
+    assert np.all(np.abs(out["counts"][1] - o["counts"][1]) <= slack)
+    assert np.all(np.abs(out["counts"][2] - o["counts"][2]) <= slack)
+    assert (o["counts"][1] > 0).any() and (o["counts"][2] > 0).any()
+    # same GPU, same math library: equal to the reference kernels
+    np.testing.assert_allclose(out["rendered_cost"], q["rendered_cost"], rtol=1e-4)
+    np.testing.assert_allclose(out["observed_cost"], q["observed_cost"], rtol=1e-4)
+
+
+def test_cloud_stage_parity(orc, ref):
+    case, obs, poses, pmm, lab, tot = _cost_case(orc, 5000, 4, False, 20)
+    s = case.scene
+    with make_renderer(case) as r:
+        out = r.render_cuda_multi_unified("CLOUD", poses, pmm, stride=4)
+    d_o, c_o = orc.render(s.tris, s.tris_model_count, poses, pmm, case.width, case.height, case.proj, s.source_depth,
+                          None, None, 1.0)
+    o = orc.depth2cloud(d_o, c_o, case.width, case.height, len(poses), case.cx, case.cy, case.fx, case.fy, 100.0, 4)
+    assert out["result_cloud_point_num"] == o["n"] > 0
+    assert np.array_equal(out["result_cloud"].view(np.uint32), o["soa"].view(np.uint32))
+    assert np.array_equal(out["result_cloud_color"], o["rgb"])
+    assert np.array_equal(out["result_cloud_pose_map"], o["pose_map"])
+    q = ref.render_cost(s.tris, s.tris_model_count, poses, pmm, case.width, case.height, case.proj, s.source_depth,
+                        s.source_color, None, None, 4, 100, case.cx, case.cy, case.fx, case.fy, obs["aos"], obs["rgb"], None,
+                        tot, 0, True, 0.0075, 20.0, 1.0, want_cloud=True)
+    assert q["n_rend"] == o["n"]
+    assert np.array_equal(q["cloud"].view(np.uint32), o["soa"].view(np.uint32))
+    # nearest-neighbour distances of the brute force the fused kernel replaces
+    d, i = orc.knn_k1(o["aos"], obs["aos"])
+    assert np.array_equal(d.view(np.uint32), q["nn_sqdist"].view(np.uint32))
+    assert np.array_equal(i, q["nn_index"])
+
+
+def test_debug_stage_returns_everything(orc):
+    case, obs, poses, pmm, lab, tot = _cost_case(orc, 600, 4, False, 6)
+    with make_renderer(case) as r:
+        r.set_observed(obs["aos"], obs["rgb"], None)
+        dbg = r.render_cuda_multi_unified("DEBUG", poses, pmm, None, tot, stride=4, sensor_resolution=0.0075)
+        cost = r.render_cuda_multi_unified("COST", poses, pmm, None, tot, stride=4, sensor_resolution=0.0075)
+        img = r.render_cuda_multi_unified("RENDER", poses, pmm)
+    assert np.array_equal(dbg["result_depth"], img["result_depth"])
+    assert np.array_equal(dbg["counts"], cost["counts"])
+    assert dbg["result_cloud_point_num"] == int(cost["counts"][0].sum())
+
+
+def test_cost_edge_cases(orc):
+    case, obs, poses, pmm, lab, tot = _cost_case(orc, 600, 4, False, 8)
+    s = case.scene
+    far = poses[0].copy(); far[0, 3] += 500.0  # 5 m to the right: nothing rendered
+    poses2 = np.concatenate([poses, far[None]])
+    pmm2 = np.concatenate([pmm, pmm[:1]])
+    tot2 = np.concatenate([tot, [0.0]]).astype(np.float32)
+    with make_renderer(case) as r:
+        r.set_observed(obs["aos"], obs["rgb"], None)
+        out = r.render_cuda_multi_unified("COST", poses2, pmm2, None, tot2, stride=4, sensor_resolution=0.0075)
+        assert out["rendered_cost"][-1] == -1.0  # compute_costs.cuh:28-31
+        assert np.isnan(out["observed_cost"][-1])  # 0/0, compute_costs.cuh:435-439
+        assert out["counts"][0, -1] == 0
+        empty = r.render_cuda_multi_unified("COST", np.zeros((0, 4, 4), np.float32), np.zeros(0, np.int32), None,
+                                            np.zeros(0, np.float32), stride=4)
+        assert empty["rendered_cost"].shape == (0,)
+        # batch-split invariance: poses are independent
+        a = r.render_cuda_multi_unified("COST", poses2[:4], pmm2[:4], None, tot2[:4], stride=4, sensor_resolution=0.0075)
+        b = r.render_cuda_multi_unified("COST", poses2[4:], pmm2[4:], None, tot2[4:], stride=4, sensor_resolution=0.0075)
+        assert np.array_equal(np.concatenate([a["counts"], b["counts"]], 1), out["counts"])
+        # empty observed cloud: every rendered point unexplained
+        r.set_observed(np.zeros((0, 3), np.float32), None, None)
+        none = r.render_cuda_multi_unified("COST", poses, pmm, None, tot, stride=4, sensor_resolution=0.0075)
+        assert np.array_equal(none["counts"][0], none["counts"][1]) and none["counts"][2].sum() == 0
+        with pytest.raises(Exception):
+            r.render_cuda_multi_unified("COST", poses, pmm, None, tot, stride=7)  # 640 % 7 != 0
+
+
+def test_triangle_order_invariance():
+    """Depth is a min over fragments: shuffling the triangle soup must not change it (colour may, on ties)."""
+    case = make_case(5000, 3, 42)
+    s = case.scene
+    poses, pmm, _ = poses_near_gt(case, 8)
+    keep = pmm == 0
+    poses, pmm = poses[keep], pmm[keep]
+    n0 = int(s.tris_model_count[0])
+    perm = np.random.default_rng(0).permutation(n0)
+    tris2 = s.tris.copy()
+    tris2[:n0] = s.tris[:n0][perm]
+    with make_renderer(case) as r:
+        a = r.render_cuda_multi_unified("RENDER", poses, pmm)["result_depth"]
+        r.set_models(tris2, s.tris_model_count)
+        b = r.render_cuda_multi_unified("RENDER", poses, pmm)["result_depth"]
+    assert np.array_equal(a, b)
+
+
+def test_full_size_properties(orc):
+    """BASELINE config-2 shape at full size (20k-triangle mesh, 640x480, stride 8, labels): the oracle is too slow
+    here, so check size-independent properties: COST counts == counts recomputed from the RENDER stage images by the
+    oracle's cloud+cost code on a sample, determinism, and top-k consistency."""
+    mesh = synth.make_mesh(20000, seed=1000, r0=0.09)
+    case = make_case(600, 3, 42)  # camera only
+    K = synth.camera_K()
+    proj = orc.compute_proj(K, 640, 480)
+
+    def render_fn(tris, counts, poses, pmm):
+        with Renderer(0) as rr:
+            rr.set_camera(640, 480, proj, synth.CX, synth.CY, synth.FX, synth.FY, 100.0)
+            rr.set_models(tris, counts)
+            rr.set_scene(np.zeros(640 * 480, np.int32))
+            o = rr.render_cuda_multi_unified("RENDER", poses, pmm)
+        return o["result_depth"], o["result_color"]
+
+    scene = synth.make_scene([mesh], render_fn, n_instances=3, seed=11)
+    P = 2048
+    center = scene.gt_poses[0][:3, 3]
+    poses = synth.poses_6dof(center, P, n_views=64, n_inplane=32)
+    poses[0] = pose_to_mat4x4(scene.gt_poses[0])
+    pmm = np.zeros(P, np.int32)
+    lab = np.zeros(P, np.int32)
+    with Renderer(0) as r:
+        r.set_camera(640, 480, proj, synth.CX, synth.CY, synth.FX, synth.FY, 100.0)
+        r.set_models(scene.tris, scene.tris_model_count)
+        r.set_scene(scene.source_depth, scene.source_color, scene.source_label)
+        obs = r.depth2cloud_global(scene.source_depth, scene.source_color, 640, 480, 1, synth.CX, synth.CY, synth.FX,
+                                   synth.FY, 100.0, 8, scene.source_label)
+        r.set_observed(obs["result_cloud_eigen"], obs["result_cloud_color"], obs["result_observed_cloud_label"])
+        tot = np.full(P, float((obs["result_observed_cloud_label"] == 0).sum()), np.float32)
+        a = r.render_cuda_multi_unified("COST", poses, pmm, lab, tot, stride=8, cost_type=2, sensor_resolution=0.01)
+        b = r.render_cuda_multi_unified("COST", poses, pmm, lab, tot, stride=8, cost_type=2, sensor_resolution=0.01)
+        assert np.array_equal(a["counts"], b["counts"])  # deterministic
+        sel = np.arange(0, P, 128)
+        img = r.render_cuda_multi_unified("RENDER", poses[sel], pmm[sel], lab[sel])
+    o = orc.costs(img["result_depth"], img["result_color"], 640, 480, synth.CX, synth.CY, synth.FX, synth.FY, 100.0, 8,
+                  lab[sel], obs["result_cloud_eigen"], obs["result_cloud_color"], obs["result_observed_cloud_label"], tot[sel],
+                  2, True, 0.01, 20.0)
+    assert np.array_equal(a["counts"][:, sel], o["counts"])
+    assert np.array_equal(a["rendered_cost"][sel], o["rendered_cost"])
+    # the ground-truth pose must be the best-scoring candidate region
+    best = topk(a["rendered_cost"], a["observed_cost"], pmm, 1, k=5)
+    assert best["cost"][0, 0] <= int(a["rendered_cost"][0] + a["observed_cost"][0])
+    assert a["rendered_cost"][0] < 35.0
