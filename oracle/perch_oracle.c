@@ -11,8 +11,9 @@
  * call site renderer.cu:1853-1865) -- lowest index, fma(dz,dz,fma(dy,dy,dx*dx)) is this repo's convention.
  *
  * Each function cites the reference lines it follows (paths relative to the reference repository).
- * Build: gcc -O2 -ffp-contract=off (the float sequences below spell out where the reference's nvcc build fuses
- * multiply-adds; the compiler must not add or remove any).
+ * Build: gcc -O2 -ffp-contract=off (the float sequences below spell out where the reference's nvcc 12.9 / sm_100a
+ * build fuses multiply-adds -- by NVVM, visible in PTX, and by ptxas, visible only in `cuobjdump -sass` of
+ * oracle/_ref/libperch_ref.so; the C compiler must not add or remove any).
  */
 #include <float.h>
 #include <limits.h>
@@ -121,17 +122,20 @@ void oracle_render(const tri64* tris, int n_tris, const float* poses16, int n_po
                     bboxmin[j] = sel_max(clamp_min[j], sel_min(bboxmin[j], pts[i][j]));
                     bboxmax[j] = sel_min(clamp_max[j], sel_max(bboxmax[j], pts[i][j]));
                 }
-            /* calculateSignedArea(A,B,C) :40-42, no fused ops in the nvcc build; base_inv = 1/area :48 */
+            /* calculateSignedArea(A,B,C) :40-42; in the sm_100a build the first product is fused into the subtraction
+             * (ptxas contraction, visible in SASS only): fma(C0-A0, B1-A1, -((B0-A0)*(C1-A1))) * 0.5; base_inv = 1/area :48 */
             const float* A = pts[0]; const float* B = pts[1]; const float* C = pts[2];
-            const float area = (((C[0] - A[0]) * (B[1] - A[1])) - ((B[0] - A[0]) * (C[1] - A[1]))) * 0.5f;
+            const float area = fmaf(C[0] - A[0], B[1] - A[1], -((B[0] - A[0]) * (C[1] - A[1]))) * 0.5f;
             const float base_inv = 1.0f / area;
             /* :110-111 */
             for (uint64_t P1 = f2u64_sat(bboxmin[1] + 0.5f); (float)P1 <= bboxmax[1]; ++P1) {
                 for (uint64_t P0 = f2u64_sat(bboxmin[0] + 0.5f); (float)P0 <= bboxmax[0]; ++P0) {
                     const float fp0 = (float)P0, fp1 = (float)P1;
-                    /* barycentric :44-57: beta = area(A,P,C)*base_inv, gamma = area(A,B,P)*base_inv */
-                    const float aAPC = (((C[0] - A[0]) * (fp1 - A[1])) - ((fp0 - A[0]) * (C[1] - A[1]))) * 0.5f;
-                    const float aABP = (((fp0 - A[0]) * (B[1] - A[1])) - ((B[0] - A[0]) * (fp1 - A[1]))) * 0.5f;
+                    /* barycentric :44-57: beta = area(A,P,C)*base_inv, gamma = area(A,B,P)*base_inv.  SASS of the sm_100a
+                     * build: the row products (C0-A0)*(P1-A1) and (P1-A1)*(B0-A0) are hoisted and rounded, the
+                     * per-pixel products are fused: fma(C1-A1, -(P0-A0), row0) and fma(B1-A1, P0-A0, -row1). */
+                    const float aAPC = fmaf(C[1] - A[1], -(fp0 - A[0]), (C[0] - A[0]) * (fp1 - A[1])) * 0.5f;
+                    const float aABP = fmaf(B[1] - A[1], fp0 - A[0], -((fp1 - A[1]) * (B[0] - A[0]))) * 0.5f;
                     const float beta = base_inv * aAPC;
                     const float gamma = base_inv * aABP;
                     const float alpha = (1.0f - beta) - gamma;

@@ -121,7 +121,8 @@ int ref_render(const void* tris64, int n_tris, const float* poses16, int n_poses
                                 height, proj, occlusion_threshold, single_result_image, occ, occ_other, clutter,
                                 total, d_depth, d_r, d_g, d_b, stats);
     if (cudaDeviceSynchronize() != cudaSuccess) return 1;
-    size_t n = npx * n_poses;
+    // in single-image mode the reference still allocates P images but renders everything into the first
+    size_t n = npx * (single_result_image ? 1 : n_poses);
     if (out_depth) cudaMemcpy(out_depth, thrust::raw_pointer_cast(d_depth.data()), n * 4, cudaMemcpyDeviceToHost);
     if (out_r) cudaMemcpy(out_r, thrust::raw_pointer_cast(d_r.data()), n, cudaMemcpyDeviceToHost);
     if (out_g) cudaMemcpy(out_g, thrust::raw_pointer_cast(d_g.data()), n, cudaMemcpyDeviceToHost);
@@ -300,6 +301,79 @@ int ref_render_cost(const void* tris64, int n_tris, const float* poses16, int n_
     if (ms_out)
         for (int i = 0; i < 4; ++i) cudaEventElapsedTime(&ms_out[i], ev[i], ev[i + 1]);
     for (auto& e : ev) cudaEventDestroy(e);
+    cudaFree(cloud2d);
+    return cudaGetLastError() == cudaSuccess ? 0 : 1;
+}
+
+// compute_point_clouds + label sort + k=1 search + compute_costs of the reference (renderer.cu:1617-1659,1668-1686,
+// 1852-1907) on GIVEN rendered images.  The reference rasterizer is not deterministic on sm_70+, so
+// the cloud/cost kernels are pinned separately from it: feed them canonical images and every output is reproducible.
+int ref_cost_from_images(const int32_t* depth, const uint8_t* r, const uint8_t* g, const uint8_t* b, int n_poses, int width,
+                         int height, const int* pose_label, int stride, int depth_factor, float cx, float cy, float fx,
+                         float fy, const float* obs_xyz_aos, const uint8_t* obs_rgb, const int* obs_label, int n_obs,
+                         const float* pose_obs_total, int cost_type, int calc_observed, float sensor_resolution,
+                         float color_distance_threshold, float* rendered_cost, float* observed_cost,
+                         float* points_diff_cost, int* out_n_rend) {
+    quiet_stdout q;
+    size_t n = (size_t)width * height * n_poses;
+    thrust::device_vector<int32_t> d_depth(depth, depth + n);
+    thrust::device_vector<uint8_t> d_r(r, r + n), d_g(g, g + n), d_b(b, b + n);
+    thrust::device_vector<int> occ(n_poses, 0);
+    thrust::device_vector<int> d_pl;
+    if (pose_label) d_pl.assign(pose_label, pose_label + n_poses);
+    gpu_stats stats{0, 0};
+    float* cloud2d = NULL; size_t pitch = 0;
+    thrust::device_vector<Eigen::Vector3f> c_eigen;
+    thrust::device_vector<float> c_flat;
+    thrust::device_vector<uint8_t> c_rgb;
+    thrust::device_vector<int> dc_index, pose_map, c_label;
+    int n_rend = 0;
+    cuda_renderer::compute_point_clouds(d_depth, d_r, d_g, d_b, n_poses, width, height, cx, cy, fx, fy,
+                                        (float)depth_factor, stride, occ, cloud2d, pitch, c_eigen, c_flat, c_rgb,
+                                        n_rend, dc_index, pose_map, c_label, stats, NULL,
+                                        thrust::device_vector<uint8_t>(0), thrust::device_vector<double>(0), d_pl);
+    const Eigen::Vector3f* oe = (const Eigen::Vector3f*)obs_xyz_aos;
+    thrust::device_vector<Eigen::Vector3f> d_obs(oe, oe + n_obs);
+    thrust::device_vector<int> d_obs_label, d_lb, d_le;
+    int n_labels = 0;
+    if (pose_label) {
+        d_obs_label.assign(obs_label, obs_label + n_obs);
+        thrust::stable_sort_by_key(d_obs_label.begin(), d_obs_label.end(), d_obs.begin());
+        std::vector<int> hl(n_obs);
+        thrust::copy(d_obs_label.begin(), d_obs_label.end(), hl.begin());
+        for (int i = 0; i < n_obs; ++i) n_labels = hl[i] + 1 > n_labels ? hl[i] + 1 : n_labels;
+        std::vector<int> lb(n_labels, 0), le(n_labels, 0);
+        for (int i = 0; i < n_obs; ++i) {
+            if (hl[i] < 0) continue;
+            if (i == 0 || hl[i - 1] != hl[i]) lb[hl[i]] = i;
+            le[hl[i]] = i + 1;
+        }
+        d_lb = lb; d_le = le;
+    }
+    thrust::device_vector<float> k_dist(n_rend);
+    thrust::device_vector<int> k_idx(n_rend);
+    if (n_rend > 0)
+        ref_knn_k1<<<(n_rend + 255) / 256, 256>>>(
+            thrust::raw_pointer_cast(c_eigen.data()), n_rend, thrust::raw_pointer_cast(d_obs.data()), n_obs,
+            pose_label ? thrust::raw_pointer_cast(c_label.data()) : NULL,
+            pose_label ? thrust::raw_pointer_cast(d_lb.data()) : NULL,
+            pose_label ? thrust::raw_pointer_cast(d_le.data()) : NULL, n_labels,
+            thrust::raw_pointer_cast(k_dist.data()), thrust::raw_pointer_cast(k_idx.data()));
+    sensor_resolution = sensor_resolution * sensor_resolution;
+    thrust::device_vector<uint8_t> d_obs_rgb(obs_rgb, obs_rgb + 3 * (size_t)n_obs);
+    thrust::device_vector<float> d_tot(pose_obs_total, pose_obs_total + n_poses);
+    thrust::device_vector<float> v_rend, v_obs, v_diff;
+    cuda_renderer::compute_costs(n_poses, cost_type, calc_observed != 0, sensor_resolution, color_distance_threshold,
+                                 d_obs_rgb, d_obs_label, n_obs, c_rgb, pose_map, occ, d_pl, d_tot, n_rend, k_dist,
+                                 k_idx, v_rend, v_obs, v_diff, stats);
+    if (cudaDeviceSynchronize() != cudaSuccess) return 1;
+    if (rendered_cost)
+        cudaMemcpy(rendered_cost, thrust::raw_pointer_cast(v_rend.data()), n_poses * 4, cudaMemcpyDeviceToHost);
+    if (calc_observed && observed_cost)
+        cudaMemcpy(observed_cost, thrust::raw_pointer_cast(v_obs.data()), n_poses * 4, cudaMemcpyDeviceToHost);
+    if (calc_observed && points_diff_cost)
+        cudaMemcpy(points_diff_cost, thrust::raw_pointer_cast(v_diff.data()), n_poses * 4, cudaMemcpyDeviceToHost);
+    if (out_n_rend) *out_n_rend = n_rend;
     cudaFree(cloud2d);
     return cudaGetLastError() == cudaSuccess ? 0 : 1;
 }

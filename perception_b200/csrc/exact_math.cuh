@@ -2,10 +2,12 @@
 //
 // The reference (cuda_renderer/include/cuda_renderer/cuda/image_renderer.cuh:21-57,79-129 and
 // compute_point_clouds.cuh:20-22) is built with nvcc's default -fmad=true (cuda_renderer/CMakeLists.txt:27),
-// so which a*b+c become FMAs is a property of the compiler, not of the source.  The sequences below are the
-// ones nvcc 12.9 -O3 emits for those expressions (oracle/ref_harness.cu -> PTX, see DESIGN.md "arithmetic
-// contract"); they are written with round-to-nearest intrinsics so that this file compiles to the same
-// operations regardless of surrounding code, inlining or flags.  Integer depth parity depends on every one.
+// so which a*b+c become FMAs is a property of the compiler, not of the source: NVVM fuses some (visible in PTX)
+// and ptxas fuses more (`mul.f32`/`add.f32` without .rn may be contracted; visible only in SASS).  The sequences
+// below are the ones in the sm_100a SASS nvcc 12.9 -O3 produces for those expressions (oracle/_ref/libperch_ref.so,
+// `cuobjdump -sass`; see DESIGN.md "arithmetic contract"); they are written with round-to-nearest intrinsics so
+// that this file compiles to the same operations regardless of surrounding code, inlining or flags.  Integer depth
+// parity depends on every one (tests: frag_single_tri golden, one triangle per image => no z-buffer contention).
 #pragma once
 #include <cfloat>
 #include <climits>
@@ -75,8 +77,9 @@ __device__ __forceinline__ void setup_edges(const ScreenVertex& a, const ScreenV
     t.e_b1 = __fsub_rn(b.sy, a.sy);
     t.e_b0 = __fsub_rn(b.sx, a.sx);
     t.e_c1 = __fsub_rn(c.sy, a.sy);
-    // calculateSignedArea(A,B,C) (image_renderer.cuh:40-42): 0.5*((C0-A0)*(B1-A1) - (B0-A0)*(C1-A1)), no FMA
-    float area = __fmul_rn(__fsub_rn(__fmul_rn(t.e_c0, t.e_b1), __fmul_rn(t.e_b0, t.e_c1)), 0.5f);
+    // calculateSignedArea(A,B,C) (image_renderer.cuh:40-42): 0.5*((C0-A0)*(B1-A1) - (B0-A0)*(C1-A1));
+    // SASS: FMUL t = (B0-A0)*(C1-A1); FFMA (C0-A0)*(B1-A1) - t; FMUL 0.5
+    float area = __fmul_rn(__fmaf_rn(t.e_c0, t.e_b1, -__fmul_rn(t.e_b0, t.e_c1)), 0.5f);
     t.base_inv = __frcp_rn(area);  // `1/area` (image_renderer.cuh:48)
     t.z0 = a.z; t.z1 = b.z; t.z2 = c.z;
 }
@@ -88,8 +91,9 @@ __device__ __forceinline__ bool fragment_depth(const TriSetup& t, float P0f, flo
     float r0 = __fmul_rn(t.e_c0, dy);
     float r1 = __fmul_rn(dy, t.e_b0);
     float dx = __fsub_rn(P0f, t.A0);
-    float beta = __fmul_rn(t.base_inv, __fmul_rn(__fsub_rn(r0, __fmul_rn(dx, t.e_c1)), 0.5f));
-    float gamma = __fmul_rn(t.base_inv, __fmul_rn(__fsub_rn(__fmul_rn(dx, t.e_b1), r1), 0.5f));
+    // SASS: FFMA (C1-A1)*(-dx) + r0 ; FFMA (B1-A1)*dx - r1 ; each then FMUL 0.5, FMUL base_inv
+    float beta = __fmul_rn(t.base_inv, __fmul_rn(__fmaf_rn(t.e_c1, -dx, r0), 0.5f));
+    float gamma = __fmul_rn(t.base_inv, __fmul_rn(__fmaf_rn(t.e_b1, dx, -r1), 0.5f));
     float alpha = __fsub_rn(__fsub_rn(1.0f, beta), gamma);
     float mn = fminf(gamma, fminf(beta, alpha));
     float mx = fmaxf(fmaxf(alpha, beta), gamma);

@@ -217,3 +217,28 @@ class Reference:
             n = n_rend.value
             out.update(cloud=cloud[:, :n], pose_map=pmap[:n], nn_sqdist=nnd[:n], nn_index=nni[:n])
         return out
+
+    def cost_from_images(self, depth, color, width, height, cx, cy, fx, fy, depth_factor, stride, pose_label, obs_xyz,
+                         obs_rgb, obs_label, pose_obs_total, cost_type, calc_observed, sensor_resolution,
+                         color_distance_threshold):
+        """Reference compute_point_clouds + (restated k=1 search) + compute_costs on given rendered images."""
+        d = _c(depth, np.int32).reshape(-1, height, width)
+        P = len(d)
+        planes = [_c(color[k], np.uint8).reshape(-1) for k in range(3)]
+        pl = None if pose_label is None else _c(pose_label, np.int32)
+        ox = _c(obs_xyz, np.float32).reshape(-1, 3)
+        n_obs = len(ox)
+        orgb = np.zeros((3, n_obs), np.uint8) if obs_rgb is None else _c(obs_rgb, np.uint8).reshape(3, n_obs)
+        ol = None if obs_label is None else _c(obs_label, np.int32)
+        tot = np.zeros(P, np.float32) if pose_obs_total is None else _c(pose_obs_total, np.float32)
+        rc_ = np.zeros(P, np.float32)
+        oc = np.zeros(P, np.float32)
+        dc = np.zeros(P, np.float32)
+        n_rend = C.c_int(0)
+        rc = self.lib.ref_cost_from_images(
+            _p(d), _p(planes[0]), _p(planes[1]), _p(planes[2]), C.c_int(P), C.c_int(width), C.c_int(height), _p(pl),
+            C.c_int(stride), C.c_int(int(depth_factor)), C.c_float(cx), C.c_float(cy), C.c_float(fx), C.c_float(fy), _p(ox),
+            _p(orgb), _p(ol), C.c_int(n_obs), _p(tot), C.c_int(cost_type), C.c_int(int(calc_observed)),
+            C.c_float(sensor_resolution), C.c_float(color_distance_threshold), _p(rc_), _p(oc), _p(dc), C.byref(n_rend))
+        assert rc == 0, "ref_cost_from_images failed"
+        return {"rendered_cost": rc_, "observed_cost": oc, "points_diff_cost": dc, "n_rend": n_rend.value}

@@ -199,23 +199,32 @@ def test_scene_scores_rank_ground_truth_first(orc):
     assert r["rendered_cost"][:n_gt].max() < np.sort(r["rendered_cost"][n_gt:])[1]
 
 
-@pytest.mark.parametrize("name", ["render_3dof", "render_6dof", "cloud", "cost_3dof", "cost_6dof"])
+import make_golden_inputs as gi  # noqa: E402
+
+
+@pytest.mark.parametrize("name", gi.NAMES)
 def test_oracle_matches_reference_golden(orc, name):
     """Golden vectors = outputs of the reference's own CUDA kernels (oracle/_ref) on seeded inputs, generated on a
-    B200 by tests/golden/make_golden.py.  This is what pins the oracle."""
+    B200 by tests/golden/make_golden.py.  This is what pins the oracle.  EXACT cases must match bit for bit; the
+    full-mesh renders are bounded by the race budget recorded at generation time (the reference rasterizer is not
+    deterministic on sm_70+, see tests/make_golden_inputs.py)."""
     path = GOLDEN / f"{name}.npz"
     if not path.exists():
         pytest.skip(f"{path.name} not generated yet (run tests/golden/make_golden.py on a GPU box)")
-    import make_golden_inputs as gi
     g = np.load(path)
     out = gi.run_oracle(orc, name)
-    for k in g.files:
-        if k.startswith("ref_"):
-            a, b = g[k], out[k[4:]]
-            if k in ("ref_depth", "ref_rgb"):
-                # the reference rasterizer is racy: allow the recorded handful of pixels to differ
-                assert np.count_nonzero(a != b) <= int(g.get("race_budget", 4)), k
-            elif a.dtype.kind == "f":
-                np.testing.assert_allclose(b, a, rtol=1e-6, atol=0, equal_nan=True, err_msg=k)
-            else:
-                assert np.array_equal(a, b), k
+    keys = [k for k in g.files if k.startswith("ref_")]
+    assert keys
+    for k in keys:
+        a, b = g[k], out[k[4:]]
+        assert a.shape == b.shape, k
+        if name in gi.EXACT:
+            assert np.array_equal(np.atleast_1d(a).view(np.uint8), np.atleast_1d(b).astype(a.dtype).view(np.uint8)) \
+                or np.array_equal(a, b, equal_nan=True), \
+                f"{k}: {np.count_nonzero(a != b)} of {a.size} values differ from the reference kernels"
+        elif k == "ref_depth":
+            bad = np.count_nonzero(a != b)
+            assert bad <= int(g["race_budget"]), f"{bad} depth pixels differ, budget {int(g['race_budget'])}"
+            # wherever they agree on depth the colour must agree too, except equal-depth ties
+            same = a == b
+            assert np.count_nonzero((g["ref_rgb"] != out["rgb"]).any(0) & same) <= int(g["race_budget"])

@@ -55,13 +55,22 @@ def test_render_3dof_bit_exact(orc, ref, size, n_tris):
     assert (d_o > 0).sum() > 1000
     d_r, c_r = ref.render(s.tris, s.tris_model_count, poses, pmm, case.width, case.height, case.proj, s.source_depth,
                           s.source_color, None, None, 1.0)
-    bad = np.count_nonzero(d_r != d_o)
-    print(f"reference-vs-canonical depth mismatches: {bad} of {d_o.size} pixels")
-    assert bad <= max(4, d_o.size // 1_000_000), "reference kernel deviates from the canonical semantics beyond its race window"
-    same = d_r == d_o
-    cbad = np.count_nonzero((c_r != c_o).any(0) & same)
-    print(f"reference-vs-canonical colour mismatches (equal-depth ties / races): {cbad}")
-    assert cbad <= (d_o > 0).sum() // 50
+    _check_reference_race_budget(d_r, d_o)
+
+
+def _check_reference_race_budget(d_r, d_o, max_frac=0.15):
+    """The reference rasterizer is not deterministic on sm_70+ (unfenced spin lock + racy occlusion step, see
+    tests/make_golden_inputs.py): report how far it strays from the canonical result and bound it.  Deviations can only
+    make a pixel emptier or farther (a lost z-test / a clobbered min), never nearer than the true minimum."""
+    obj = int((d_o > 0).sum())
+    bad = int(np.count_nonzero(d_r != d_o))
+    cleared = int(np.count_nonzero((d_r == 0) & (d_o > 0)))
+    farther = int(np.count_nonzero((d_r > d_o) & (d_o > 0)))
+    nearer = int(np.count_nonzero((d_r < d_o) & (d_r > 0)))
+    extra = int(np.count_nonzero((d_r > 0) & (d_o == 0)))
+    print(f"reference-vs-canonical: {bad} px differ of {obj} object px (cleared {cleared}, farther {farther}, nearer {nearer}, extra {extra})")
+    assert bad <= max_frac * obj + 16
+    assert nearer == 0, "the reference produced a depth NEARER than the min over fragments: arithmetic mismatch"
 
 
 def test_render_6dof_labels_bit_exact(orc, ref):
@@ -76,7 +85,39 @@ def test_render_6dof_labels_bit_exact(orc, ref):
     assert np.array_equal(out["result_color"], c_o)
     d_r, _ = ref.render(s.tris, s.tris_model_count, poses, pmm, case.width, case.height, case.proj, s.source_depth,
                         s.source_color, s.source_label, lab, 1.0)
-    assert np.count_nonzero(d_r != d_o) <= 4
+    _check_reference_race_budget(d_r, d_o)
+
+
+def test_reference_kernels_exact_on_race_free_cases(orc, ref):
+    """One fragment per pixel => the reference kernel is deterministic: product == oracle == reference, bit for bit."""
+    import make_golden_inputs as gi
+    case, tris, counts, poses, pmm = gi.single_tri_inputs()
+    with Renderer(0) as r:
+        r.set_camera(gi.W, gi.H, case.proj, case.cx, case.cy, case.fx, case.fy, 100.0)
+        r.set_models(tris, counts)
+        r.set_scene(np.zeros(gi.W * gi.H, np.int32))
+        out = r.render_cuda_multi_unified("RENDER", poses, pmm)
+        d_o, c_o = orc.render(tris, counts, poses, pmm, gi.W, gi.H, case.proj)
+        d_r, c_r = ref.render(tris, counts, poses, pmm, gi.W, gi.H, case.proj)
+        assert (d_o > 0).sum() > 10000
+        assert np.array_equal(out["result_depth"], d_o) and np.array_equal(d_r, d_o)
+        assert np.array_equal(out["result_color"], c_o) and np.array_equal(c_r, c_o)
+        case, tris, src, lab, pose = gi.quad_inputs()
+        r.set_models(tris, [2])
+        for thr in (0.0, 0.5, 1.0, 2.5):
+            r.set_scene(src)
+            a = r.render_cuda_multi_unified("RENDER", pose, [0], occlusion_threshold=thr)
+            d_o, c_o = orc.render(tris, [2], pose, [0], gi.W, gi.H, case.proj, src, None, None, thr)
+            d_r, c_r = ref.render(tris, [2], pose, [0], gi.W, gi.H, case.proj, src, None, None, None, thr)
+            assert np.array_equal(a["result_depth"], d_o) and np.array_equal(d_r, d_o), thr
+            assert np.array_equal(a["result_color"], c_o) and np.array_equal(c_r, c_o), thr
+        r.set_scene(src, None, lab)
+        for pl in (0, 1):
+            a = r.render_cuda_multi_unified("RENDER", pose, [0], [pl])
+            d_o, c_o = orc.render(tris, [2], pose, [0], gi.W, gi.H, case.proj, src, lab, [pl], 1.0)
+            d_r, c_r = ref.render(tris, [2], pose, [0], gi.W, gi.H, case.proj, src, None, lab, [pl], 1.0)
+            assert np.array_equal(a["result_depth"], d_o) and np.array_equal(d_r, d_o), pl
+            assert np.array_equal(a["result_color"], c_o) and np.array_equal(c_r, c_o), pl
 
 
 def test_render_edge_cases(orc):
@@ -123,7 +164,7 @@ def test_single_result_image(orc, ref):
     assert np.array_equal(out["result_color"], c_o)
     d_r, _ = ref.render(s.tris, s.tris_model_count, poses, pmm, case.width, case.height, case.proj, s.source_depth,
                         s.source_color, None, None, 100.0, single_result_image=1)
-    assert np.count_nonzero(d_r != d_o) <= 4
+    _check_reference_race_budget(d_r, d_o)
 
 
 # ---------------------------------------------------------------------------------------------------------------------
@@ -190,12 +231,20 @@ def test_cost_parity(orc, ref, n_tris, stride, dof6):
     assert o["counts"][0].sum() > 0 and o["counts"][2].sum() > 0
     for k in ("rendered_cost", "observed_cost", "points_diff_cost"):
         assert np.array_equal(out[k], o[k], equal_nan=True), k
-    q = ref.render_cost(s.tris, s.tris_model_count, poses, pmm, case.width, case.height, case.proj, s.source_depth,
-                        s.source_color, s.source_label if dof6 else None, lab, stride, 100, case.cx, case.cy, case.fx,
-                        case.fy, obs["aos"], obs["rgb"], obs["label"] if dof6 else None, tot, ct, True, res, 20.0, 1.0)
+    # the reference's own compute_point_clouds + compute_costs kernels on the canonical images: exact
+    q = ref.cost_from_images(d_o, c_o, case.width, case.height, case.cx, case.cy, case.fx, case.fy, 100, stride, lab,
+                             obs["aos"], obs["rgb"], obs["label"] if dof6 else None, tot, ct, True, res, 20.0)
+    assert q["n_rend"] == int(o["counts"][0].sum())
     for k in ("rendered_cost", "observed_cost", "points_diff_cost"):
         np.testing.assert_allclose(out[k], q[k], rtol=1e-4, atol=0, equal_nan=True, err_msg=f"{k} vs reference kernels")
-    assert q["n_rend"] == int(o["counts"][0].sum())
+        assert np.array_equal(out[k], q[k], equal_nan=True), k
+    # the reference end to end (its racy rasterizer included): reported, loosely bounded
+    e = ref.render_cost(s.tris, s.tris_model_count, poses, pmm, case.width, case.height, case.proj, s.source_depth,
+                        s.source_color, s.source_label if dof6 else None, lab, stride, 100, case.cx, case.cy, case.fx,
+                        case.fy, obs["aos"], obs["rgb"], obs["label"] if dof6 else None, tot, ct, True, res, 20.0, 1.0)
+    dev = np.abs(e["rendered_cost"] - out["rendered_cost"])
+    print(f"reference end-to-end rendered_cost deviation from canonical: median {np.median(dev):.3f}, max {dev.max():.3f}")
+    assert np.median(dev) < 5.0
 
 
 def test_cost_colour_flip_tolerant(orc, ref):
@@ -210,18 +259,25 @@ def test_cost_colour_flip_tolerant(orc, ref):
                           None, None, 1.0)
     o = orc.costs(d_o, c_o, case.width, case.height, case.cx, case.cy, case.fx, case.fy, 100.0, 4, None, obs["aos"],
                   obs["rgb"], None, tot, 1, True, 0.0075, thr, color_eps=1e-3)
-    q = ref.render_cost(s.tris, s.tris_model_count, poses, pmm, case.width, case.height, case.proj, s.source_depth,
-                        s.source_color, None, None, 4, 100, case.cx, case.cy, case.fx, case.fy, obs["aos"], obs["rgb"], None,
-                        tot, 1, True, 0.0075, thr, 1.0)
+    q = ref.cost_from_images(d_o, c_o, case.width, case.height, case.cx, case.cy, case.fx, case.fy, 100, 4, None, obs["aos"],
+                             obs["rgb"], None, tot, 1, True, 0.0075, thr)
     assert np.array_equal(out["counts"][0], o["counts"][0])
     # rendered points whose CIEDE2000 distance is within 1e-3 of the threshold may flip (float libm differs CPU/GPU)
     slack = o["near_threshold"]
     assert np.all(np.abs(out["counts"][1] - o["counts"][1]) <= slack)
     assert np.all(np.abs(out["counts"][2] - o["counts"][2]) <= slack)
     assert (o["counts"][1] > 0).any() and (o["counts"][2] > 0).any()
+    # colour matters: depth-only scoring of the same poses explains more points
+    assert (out["counts"][1] >= _depth_only_counts(case, obs, poses, pmm, tot)[1]).all()
     # same GPU, same math library: equal to the reference kernels
     np.testing.assert_allclose(out["rendered_cost"], q["rendered_cost"], rtol=1e-4)
     np.testing.assert_allclose(out["observed_cost"], q["observed_cost"], rtol=1e-4)
+
+
+def _depth_only_counts(case, obs, poses, pmm, tot):
+    with make_renderer(case) as r:
+        r.set_observed(obs["aos"], obs["rgb"], None)
+        return r.render_cuda_multi_unified("COST", poses, pmm, None, tot, stride=4, cost_type=0, sensor_resolution=0.0075)["counts"]
 
 
 def test_cloud_stage_parity(orc, ref):
@@ -236,15 +292,10 @@ def test_cloud_stage_parity(orc, ref):
     assert np.array_equal(out["result_cloud"].view(np.uint32), o["soa"].view(np.uint32))
     assert np.array_equal(out["result_cloud_color"], o["rgb"])
     assert np.array_equal(out["result_cloud_pose_map"], o["pose_map"])
-    q = ref.render_cost(s.tris, s.tris_model_count, poses, pmm, case.width, case.height, case.proj, s.source_depth,
-                        s.source_color, None, None, 4, 100, case.cx, case.cy, case.fx, case.fy, obs["aos"], obs["rgb"], None,
-                        tot, 0, True, 0.0075, 20.0, 1.0, want_cloud=True)
-    assert q["n_rend"] == o["n"]
-    assert np.array_equal(q["cloud"].view(np.uint32), o["soa"].view(np.uint32))
-    # nearest-neighbour distances of the brute force the fused kernel replaces
-    d, i = orc.knn_k1(o["aos"], obs["aos"])
-    assert np.array_equal(d.view(np.uint32), q["nn_sqdist"].view(np.uint32))
-    assert np.array_equal(i, q["nn_index"])
+    q = ref.depth2cloud(d_o, c_o, case.width, case.height, len(poses), case.cx, case.cy, case.fx, case.fy, 100.0, 4)
+    assert q["n"] == o["n"]
+    assert np.array_equal(q["soa"].view(np.uint32), o["soa"].view(np.uint32))
+    assert np.array_equal(q["pose_map"], o["pose_map"])
 
 
 def test_debug_stage_returns_everything(orc):
