@@ -25,7 +25,16 @@ namespace perch {
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kQueueCap = 2048;
+constexpr int kQueueCap = 2048;   // candidate triangles per fill phase
+constexpr int kBigCells = 48;     // lattice pixels above which a triangle is rasterised by the whole CTA
+constexpr int kBigCap = 64;
+constexpr float kEps = 0.02f;     // pixels; bound on |approximate - exact| screen coordinates in the candidate test
+
+__device__ __forceinline__ float __frcp_approx(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
 
 template <bool COLOR> struct ZCell;
 template <> struct ZCell<false> {
@@ -161,7 +170,8 @@ __global__ void __launch_bounds__(kThreads) pose_kernel(PoseArgs a) {
 
     __shared__ Mat4 s_pose;
     __shared__ int s_rect[4];
-    __shared__ int s_qcount;
+    __shared__ int s_qcount, s_bigcount;
+    __shared__ int s_big[kBigCap];
     __shared__ int s_n, s_c, s_e;
 
     const int pose_i = blockIdx.x;
@@ -169,10 +179,13 @@ __global__ void __launch_bounds__(kThreads) pose_kernel(PoseArgs a) {
     const int W = a.cam.width, H = a.cam.height, s = a.stride;
     const int Lw = W / s, Lh = (H + s - 1) / s;
     const float wf = (float)W, hf = (float)H;  // cvt.rn.f32.u64 of width/height
+    const float half_w = 0.5f * wf, half_h = 0.5f * hf, s_f = (float)s, inv_s = 1.0f / (float)s;
+    // lattice raster rows are P1 = H-1-k*s == row_phase (mod s) with row_phase in [0, s)
+    const float row_phase = (float)((H - 1) % s);
     const float cmaxx = (float)(W - 1), cmaxy = (float)(H - 1);
 
     if (tid < 16) reinterpret_cast<float*>(&s_pose)[tid] = reinterpret_cast<const float*>(a.poses + pose_i)[tid];
-    if (tid == 0) { s_n = 0; s_c = 0; s_e = 0; s_qcount = 0; }
+    if (tid == 0) { s_n = 0; s_c = 0; s_e = 0; s_qcount = 0; s_bigcount = 0; }
     for (int w = tid; w < mask_words; w += kThreads) mask[w] = 0u;
     __syncthreads();
 
@@ -234,11 +247,16 @@ __global__ void __launch_bounds__(kThreads) pose_kernel(PoseArgs a) {
             const int by1 = min(by0 + band_rows - 1, ry1);
             const int band_cells = tile_w * (by1 - by0 + 1);
             for (int c = tid; c < band_cells; c += kThreads) zbuf[c] = Z::empty();
-            if (tid == 0) s_qcount = 0;
+            if (tid == 0) { s_qcount = 0; s_bigcount = 0; }
             __syncthreads();
+            // band limits in raster coordinates for the candidate test: columns [rx0*s, rx1*s]; raster rows
+            // P1 = H-1-ly*s for ly in [by0, by1]
+            const float band_lo_x = (float)(rx0 * s) - 0.5f, band_hi_x = (float)(rx1 * s);
+            const float band_lo_y = (float)(H - 1 - by1 * s) - 0.5f, band_hi_y = (float)(H - 1 - by0 * s);
 
-            // rasterise one triangle into the band's lattice z-buffer
-            auto raster_tri = [&](int t) {
+            // Exact path for one triangle: the reference's float sequence (exact_math.cuh), its bbox loops restricted
+            // to lattice pixels of this band, z-test with atomicMin.  `coop` = all threads of the CTA share the work.
+            auto raster_tri = [&](int t, bool coop, bool allow_defer) -> bool {
                 float v[9];
                 load_tri(a.models, t, v);
                 ScreenVertex A = transform_vertex(pose, a.cam.proj, wf, hf, v[0], v[1], v[2]);
@@ -247,53 +265,94 @@ __global__ void __launch_bounds__(kThreads) pose_kernel(PoseArgs a) {
                 float bminx, bmaxx, bminy, bmaxy;
                 bbox_of(A, B, C, cmaxx, cmaxy, bminx, bmaxx, bminy, bmaxy);
                 LatticeRect r = lattice_rect_of(bminx, bmaxx, bminy, bmaxy, W, H, s);
+                if (r.x0 > r.x1 || r.y0 > r.y1) return false;
+                if (r.x0 < rx0 || r.x1 > rx1 || r.y0 < ry0 || r.y1 > ry1) atomicOr(a.err_flag, 1);
                 int x0 = max(r.x0, rx0), x1 = min(r.x1, rx1), y0 = max(r.y0, by0), y1 = min(r.y1, by1);
-                if (x0 > x1 || y0 > y1) return;
+                if (x0 > x1 || y0 > y1) return false;
+                const int w = x1 - x0 + 1, cells = w * (y1 - y0 + 1);
+                if (allow_defer && cells > kBigCells) return true;  // caller re-queues it for the cooperative pass
                 TriSetup ts;
                 setup_edges(A, B, C, ts);
-                for (int ly = y0; ly <= y1; ++ly) {
-                    float P1f = (float)(H - 1 - ly * s);
-                    for (int lx = x0; lx <= x1; ++lx) {
-                        int32_t d;
-                        if (fragment_depth(ts, (float)(lx * s), P1f, d))
-                            atomicMin(&zbuf[(ly - by0) * tile_w + (lx - rx0)], Z::make(d, (uint32_t)t));
-                    }
+                const int first = coop ? tid : 0, step = coop ? kThreads : 1;
+                for (int c = first; c < cells; c += step) {
+                    int ly = y0 + c / w, lx = x0 + c % w;
+                    int32_t d;
+                    if (fragment_depth(ts, (float)(lx * s), (float)(H - 1 - ly * s), d))
+                        atomicMin(&zbuf[(ly - by0) * tile_w + (lx - rx0)], Z::make(d, (uint32_t)t));
                 }
+                return false;
             };
 
-            // pass A: bbox test for every triangle, compaction of survivors
-            for (int base = t_low; base < t_high; base += kThreads) {
-                int t = base + tid;
-                bool hit = false;
-                if (t < t_high) {
-                    float v[9];
-                    load_tri(a.models, t, v);
-                    ScreenVertex A = transform_vertex(pose, a.cam.proj, wf, hf, v[0], v[1], v[2]);
-                    ScreenVertex B = transform_vertex(pose, a.cam.proj, wf, hf, v[3], v[4], v[5]);
-                    ScreenVertex C = transform_vertex(pose, a.cam.proj, wf, hf, v[6], v[7], v[8]);
-                    float bminx, bmaxx, bminy, bmaxy;
-                    bbox_of(A, B, C, cmaxx, cmaxy, bminx, bmaxx, bminy, bmaxy);
-                    LatticeRect r = lattice_rect_of(bminx, bmaxx, bminy, bmaxy, W, H, s);
-                    hit = r.x0 <= r.x1 && r.y0 <= r.y1 && r.x0 <= rx1 && r.x1 >= rx0 && r.y0 <= by1 && r.y1 >= by0;
-                    if (hit && (r.x0 < rx0 || r.x1 > rx1 || r.y0 < ry0 || r.y1 > ry1)) atomicOr(a.err_flag, 1);
+            // Conservative candidate test (pass A).  Same fma chains as the exact path up to clip space, then an
+            // APPROXIMATE perspective divide (MUFU.RCP instead of the IEEE divide): screen coordinates are within a
+            // small fraction of kEps pixels of the exact ones, so a bbox grown by kEps that contains no lattice pixel
+            // proves the exact bbox contains none.  Anything else (including NaN/inf coordinates, whose handling by
+            // the reference's select chain is order dependent) goes to the exact path.
+            auto maybe_hits = [&](int t) -> bool {
+                float v[9];
+                load_tri(a.models, t, v);
+                float sx[3], sy[3];
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    float x = v[3 * k], y = v[3 * k + 1], z = v[3 * k + 2];
+                    float X = xf_row(pose.a0, pose.a1, pose.a2, pose.a3, x, y, z);
+                    float Y = xf_row(pose.b0, pose.b1, pose.b2, pose.b3, x, y, z);
+                    float Zc = xf_row(pose.c0, pose.c1, pose.c2, pose.c3, x, y, z);
+                    float px = xf_row(a.cam.proj.a0, a.cam.proj.a1, a.cam.proj.a2, a.cam.proj.a3, X, Y, Zc);
+                    float py = xf_row(a.cam.proj.b0, a.cam.proj.b1, a.cam.proj.b2, a.cam.proj.b3, X, Y, Zc);
+                    float iz = __frcp_approx(Zc);
+                    sx[k] = fmaf(px * iz, half_w, half_w);
+                    sy[k] = fmaf(py * iz, half_h, half_h);
                 }
-                unsigned ballot = __ballot_sync(0xffffffffu, hit);
-                if (ballot) {
-                    int lane = tid & 31;
-                    int slot = 0;
-                    if (lane == 0) slot = atomicAdd(&s_qcount, __popc(ballot));
-                    slot = __shfl_sync(0xffffffffu, slot, 0) + __popc(ballot & ((1u << lane) - 1u));
-                    if (hit) {
-                        if (slot < kQueueCap) queue[slot] = t;
-                        else raster_tri(t);  // queue full: rasterise in place (rare)
+                float sum = (sx[0] + sx[1]) + (sx[2] + sy[0]) + (sy[1] + sy[2]);
+                if (!(fabsf(sum) < 1e30f)) return true;  // NaN / inf / absurd: let the exact path decide
+                // pixels the reference loop can visit: P in (bmin - 0.5, bmax], clamped to the image; grow by kEps
+                float lo_x = fmaxf(fminf(fminf(sx[0], sx[1]), sx[2]) - (0.5f + kEps), band_lo_x);
+                float hi_x = fminf(fmaxf(fmaxf(sx[0], sx[1]), sx[2]) + kEps, band_hi_x);
+                float lo_y = fmaxf(fminf(fminf(sy[0], sy[1]), sy[2]) - (0.5f + kEps), band_lo_y);
+                float hi_y = fminf(fmaxf(fmaxf(sy[0], sy[1]), sy[2]) + kEps, band_hi_y);
+                // first lattice coordinate >= lo (lattice columns are x = k*s; lattice raster rows are P1 = H-1-k*s)
+                float kx = ceilf(fmaf(lo_x, inv_s, -1e-3f));
+                float ky = ceilf(fmaf(lo_y - row_phase, inv_s, -1e-3f));
+                return (kx * s_f <= hi_x) && (fmaf(ky, s_f, row_phase) <= hi_y);
+            };
+
+            const int chunk = kQueueCap;  // triangles per fill phase: can add at most kQueueCap entries
+            for (int cbase = t_low; cbase < t_high; cbase += chunk) {
+                const int cend = min(cbase + chunk, t_high);
+                // pass A: conservative test for every triangle, warp-aggregated compaction of the candidates
+                for (int base = cbase; base < cend; base += kThreads) {
+                    int t = base + tid;
+                    bool hit = (t < cend) && maybe_hits(t);
+                    unsigned ballot = __ballot_sync(0xffffffffu, hit);
+                    if (ballot) {
+                        int lane = tid & 31;
+                        int slot = 0;
+                        if (lane == 0) slot = atomicAdd(&s_qcount, __popc(ballot));
+                        slot = __shfl_sync(0xffffffffu, slot, 0) + __popc(ballot & ((1u << lane) - 1u));
+                        if (hit) queue[slot] = t;
                     }
                 }
+                __syncthreads();
+                const int qn = s_qcount;
+                if (qn + chunk <= kQueueCap && cend < t_high) continue;  // room for another fill phase
+                // pass B: exact rasterisation of the candidates, one triangle per thread; triangles covering many
+                // lattice pixels are deferred to the cooperative pass
+                for (int e = tid; e < qn; e += kThreads) {
+                    int t = queue[e];
+                    if (raster_tri(t, false, true)) {
+                        int bslot = atomicAdd(&s_bigcount, 1);
+                        if (bslot < kBigCap) s_big[bslot] = t;
+                        else raster_tri(t, false, false);
+                    }
+                }
+                __syncthreads();
+                const int nb = min(s_bigcount, kBigCap);
+                for (int e = 0; e < nb; ++e) raster_tri(s_big[e], true, false);
+                __syncthreads();
+                if (tid == 0) { s_qcount = 0; s_bigcount = 0; }
+                __syncthreads();
             }
-            __syncthreads();
-            // pass B: dense rasterisation of the survivors
-            const int qn = min(s_qcount, kQueueCap);
-            for (int e = tid; e < qn; e += kThreads) raster_tri(queue[e]);
-            __syncthreads();
 
             if (MODE == MODE_IMAGE) {
                 // ---- 3'. resolve the band into the output images (or into the shared key image) -------------
