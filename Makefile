@@ -4,7 +4,7 @@ ARCH      := -gencode arch=compute_100a,code=sm_100a
 CSRC      := perception_b200/csrc
 NVFLAGS   := -std=c++17 -O3 $(ARCH) -lineinfo -Xcompiler -fPIC,-ffp-contract=off -I$(CSRC) -Iinclude
 SRCS      := $(CSRC)/pose_kernels.cu $(CSRC)/cloud.cu $(CSRC)/colour.cu $(CSRC)/capi.cu
-OBJS      := $(SRCS:.cu=.o)
+OBJS      := $(SRCS:.cu=.o) $(CSRC)/clusters.o
 LIB       := perception_b200/libperch_b200.so
 REF       := /root/reference
 
@@ -12,6 +12,9 @@ all: $(LIB) oracle
 
 $(CSRC)/%.o: $(CSRC)/%.cu $(wildcard $(CSRC)/*.cuh $(CSRC)/*.hpp) include/perch_b200.h
 	$(NVCC) $(NVFLAGS) -c $< -o $@
+
+$(CSRC)/clusters.o: $(CSRC)/clusters.cpp $(CSRC)/clusters.hpp
+	$(NVCC) $(NVFLAGS) -x cu -c $< -o $@
 
 $(LIB): $(OBJS)
 	$(NVCC) $(ARCH) -shared -o $@ $(OBJS)

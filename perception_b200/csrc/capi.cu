@@ -16,6 +16,7 @@
 
 #include "context.hpp"
 #include "kernels.cuh"
+#include "clusters.hpp"
 #include "perch_b200.h"
 
 namespace {
@@ -219,7 +220,7 @@ int prepare_cost_args(perch_ctx* c, const perch_params* p, perch::PoseArgs& a, b
     a.obs_lab = c->d_obs_lab;
     a.mask_words = (c->n_obs + 31) / 32;
     const int Lw = c->cam.width / p->stride;
-    int cap = env_int("PERCH_COST_TILE_CAP", 8192);
+    int cap = env_int("PERCH_COST_TILE_CAP", 4096);
     a.tile_cap = std::max(cap, Lw);
     size_t smem = perch::pose_kernel_smem_bytes(a, false, color);
     if (smem > (size_t)c->max_smem_optin)
@@ -279,7 +280,8 @@ void perch_destroy(perch_ctx* c) {
     if (!c) return;
     DeviceGuard g(c->device);
     cudaStreamSynchronize(c->stream);
-    void* ptrs[] = {c->d_tri_planes, c->d_tri_color, c->d_model_low, c->d_model_high, c->d_model_aabb, c->d_tri_lab,
+    void* ptrs[] = {c->d_tri_color, c->d_model_low, c->d_model_high, c->d_model_aabb, c->d_tri_lab, c->d_cl_recs, c->d_cl_bounds,
+                    c->d_cl_orig, c->d_cl_low, c->d_cl_high,
                     c->d_src_depth, c->d_src_label, c->d_src_rgb, c->d_grid_pts, c->d_grid_label, c->d_cell_start,
                     c->d_obs_lab, c->d_obs_rgb, c->d_scratch, c->d_err_flag, c->d_flush};
     for (void* p : ptrs)
@@ -351,8 +353,6 @@ int perch_set_models(perch_ctx* c, const perch_triangle* tris, int64_t n_tris, c
         high[m] = (int)std::min<int64_t>(run, n_tris);  // the reference also bounds by device_tris_size (image_renderer.cuh:240)
         low[m] = std::min(low[m], high[m]);
     }
-    const int64_t stride = (n_tris + 31) & ~(int64_t)31;
-    std::vector<float> planes((size_t)stride * 9, 0.f);
     std::vector<uint32_t> color((size_t)std::max<int64_t>(n_tris, 1), 0);
     std::vector<float> aabb((size_t)n_models * 6);
     for (int m = 0; m < n_models; ++m) {
@@ -362,7 +362,6 @@ int perch_set_models(perch_ctx* c, const perch_triangle* tris, int64_t n_tris, c
         for (int t = low[m]; t < high[m]; ++t) {
             const float* v = tris[t].v0;  // v0,v1,v2 are contiguous: 9 floats
             for (int k = 0; k < 9; ++k) {
-                planes[(size_t)k * stride + t] = v[k];
                 bb[k % 3] = std::min(bb[k % 3], v[k]);
                 bb[3 + k % 3] = std::max(bb[3 + k % 3], v[k]);
             }
@@ -372,17 +371,43 @@ int perch_set_models(perch_ctx* c, const perch_triangle* tris, int64_t n_tris, c
         }
     }
     int rc;
-    if ((rc = upload(&c->d_tri_planes, planes.data(), planes.size(), c->stream))) return rc;
     if ((rc = upload(&c->d_tri_color, color.data(), color.size(), c->stream))) return rc;
     if ((rc = upload(&c->d_model_low, low.data(), low.size(), c->stream))) return rc;
     if ((rc = upload(&c->d_model_high, high.data(), high.size(), c->stream))) return rc;
     if ((rc = upload(&c->d_model_aabb, aabb.data(), aabb.size(), c->stream))) return rc;
     if ((rc = upload<float>(&c->d_tri_lab, nullptr, 3 * color.size(), c->stream))) return rc;
     CU(perch::launch_rgb2lab_packed(c->d_tri_color, (int)n_tris, c->d_tri_lab, c->stream));
+    // clusters for the hierarchical candidate test
+    {
+        std::vector<float> tri9((size_t)std::max<int64_t>(n_tris, 1) * 9);
+        for (int64_t t = 0; t < n_tris; ++t) memcpy(&tri9[(size_t)t * 9], tris[t].v0, 36);
+        perch::ClusterSet cs = perch::build_clusters(tri9.data(), low, high);
+        if (env_int("PERCH_DEBUG", 0)) {
+            double rs = 0; size_t nf = 0;
+            for (size_t i = 0; i < cs.bounds.size() / 4; ++i)
+                if (std::isfinite(cs.bounds[4 * i + 3])) { rs += cs.bounds[4 * i + 3]; ++nf; }
+            fprintf(stderr, "[perch] clusters: %zu of %d triangles, mean radius %.5f\n", cs.bounds.size() / 4,
+                    perch::kClusterTris, nf ? rs / nf : 0.0);
+        }
+        if (cs.bounds.empty()) {
+            cs.bounds.assign(4, 0.f);
+            cs.recs.assign(perch::kClusterFloats, 0.f);
+            cs.orig.assign(perch::kClusterTris, 0);
+        }
+        if ((rc = upload(&c->d_cl_recs, cs.recs.data(), cs.recs.size(), c->stream))) return rc;
+        if ((rc = upload(&c->d_cl_bounds, reinterpret_cast<const float4*>(cs.bounds.data()), cs.bounds.size() / 4, c->stream))) return rc;
+        if ((rc = upload(&c->d_cl_orig, cs.orig.data(), cs.orig.size(), c->stream))) return rc;
+        if ((rc = upload(&c->d_cl_low, cs.model_low.data(), cs.model_low.size(), c->stream))) return rc;
+        if ((rc = upload(&c->d_cl_high, cs.model_high.data(), cs.model_high.size(), c->stream))) return rc;
+        CU(cudaStreamSynchronize(c->stream));  // host vectors go out of scope
+        c->models.cl_recs = c->d_cl_recs;
+        c->models.cl_bounds = c->d_cl_bounds;
+        c->models.cl_orig = c->d_cl_orig;
+        c->models.cl_low = c->d_cl_low;
+        c->models.cl_high = c->d_cl_high;
+    }
     CU(cudaStreamSynchronize(c->stream));
-    c->models.tri_planes = c->d_tri_planes;
     c->models.tri_color = c->d_tri_color;
-    c->models.tri_stride = stride;
     c->models.model_low = c->d_model_low;
     c->models.model_high = c->d_model_high;
     c->models.model_aabb = c->d_model_aabb;

@@ -33,14 +33,18 @@ struct CameraDev {
 };
 
 struct ModelsDev {
-    // SoA triangle soup, 9 float planes of stride `tri_stride` + packed colour (r | g<<8 | b<<16):
+    // Triangle soup as cluster records (below) + packed colour (r | g<<8 | b<<16) per ORIGINAL triangle index:
     // 40 bytes per triangle instead of the reference's 64-byte AoS Triangle (model.h:62-73).
-    const float* tri_planes = nullptr;
     const uint32_t* tri_color = nullptr;
-    int64_t tri_stride = 0;
     const int* model_low = nullptr;   // exclusive scan of tris_model_count (image_renderer.cuh:373-380)
     const int* model_high = nullptr;  // inclusive scan
     const float* model_aabb = nullptr;  // 6 floats per model: min xyz, max xyz (object-space)
+    // clusters (clusters.hpp): Morton-ordered groups of kClusterTris triangles with a bounding sphere
+    const float* cl_recs = nullptr;     // n_clusters x 36: rec[c][k][j] = coordinate k of triangle j
+    const float4* cl_bounds = nullptr;  // centre xyz, radius
+    const int* cl_orig = nullptr;       // n_clusters x 4: original triangle index (colour tie-break, colour lookup)
+    const int* cl_low = nullptr;        // cluster range per model
+    const int* cl_high = nullptr;
     int n_models = 0;
     int64_t n_tris = 0;
 };
@@ -71,12 +75,16 @@ struct perch_ctx {
     bool have_cam = false;
 
     // models
-    float* d_tri_planes = nullptr;
     uint32_t* d_tri_color = nullptr;
     int* d_model_low = nullptr;
     int* d_model_high = nullptr;
     float* d_model_aabb = nullptr;
     float* d_tri_lab = nullptr;        // 3 x T CIELAB of the triangle colours (cost_type 1)
+    float* d_cl_recs = nullptr;
+    float4* d_cl_bounds = nullptr;
+    int* d_cl_orig = nullptr;
+    int* d_cl_low = nullptr;
+    int* d_cl_high = nullptr;
     std::vector<int> h_model_low, h_model_high;
     perch::ModelsDev models;
     bool have_models = false;

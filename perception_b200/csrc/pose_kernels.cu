@@ -11,12 +11,14 @@
 //               (exact_math.cuh); only pixels ON the stride lattice can ever reach the cost (compute_point_clouds.cuh
 //               :47-56 samples x*stride,y*stride), so only those are z-tested, with atomicMin into a shared-memory
 //               lattice z-buffer.  Triangles that cover no lattice pixel (the vast majority for fine meshes) are
-//               rejected after the bbox; survivors are compacted into a shared queue and rasterised by dense warps.
+//               culled hierarchically and conservatively (cluster bounding sphere, then an approximate per-triangle
+//               bbox); survivors are compacted into a shared queue and rasterised exactly by dense warps.
 //   3. cost:    per lattice pixel: source-occlusion rule, back-projection, exact nearest observed point through the
 //               uniform grid, explained-bit set in a shared bitmask; warp-shuffle reduction of the three counters;
 //               the reference's percentage formulae (compute_costs.cuh:364-378,407-446).
 #include <cuda_runtime.h>
 
+#include "clusters.hpp"
 #include "context.hpp"
 #include "kernels.cuh"
 
@@ -25,7 +27,12 @@ namespace perch {
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kQueueCap = 2048;   // candidate triangles per fill phase
+constexpr int kWarps = kThreads / 32;
+constexpr int kQueueCap = 4096;   // candidate triangles buffered between exact passes
+constexpr int kClaim = 32;        // clusters tested per warp claim (one per lane)
+constexpr int kPendCap = 64;      // per-warp list of surviving clusters awaiting the per-triangle test
+constexpr int kClaimMaxTris = (kClaim + 8) * 4;  // most candidates one claim can append (incl. carried clusters)
+static_assert(kClusterTris == 4, "lane mapping of the per-triangle test assumes 4 triangles per cluster");
 constexpr int kBigCells = 48;     // lattice pixels above which a triangle is rasterised by the whole CTA
 constexpr int kBigCap = 64;
 constexpr float kEps = 0.02f;     // pixels; bound on |approximate - exact| screen coordinates in the candidate test
@@ -78,9 +85,11 @@ __device__ __forceinline__ LatticeRect lattice_rect_of(float bminx, float bmaxx,
     return r;
 }
 
+// t = 4 * cluster + lane-in-cluster indexes the cluster records (clusters.hpp)
 __device__ __forceinline__ void load_tri(const ModelsDev& m, int t, float v[9]) {
+    const float* rec = m.cl_recs + (int64_t)(t >> 2) * kClusterFloats + (t & 3);
 #pragma unroll
-    for (int k = 0; k < 9; ++k) v[k] = __ldg(m.tri_planes + (int64_t)k * m.tri_stride + t);
+    for (int k = 0; k < 9; ++k) v[k] = __ldg(rec + k * kClusterTris);
 }
 
 // CIEDE2000 between two CIELAB triples with the reference's mixed float/double evaluation
@@ -159,7 +168,7 @@ __device__ __forceinline__ void nn_query(const ObsGridDev& g, float qx, float qy
 enum { MODE_COST = 0, MODE_IMAGE = 1 };
 
 template <int MODE, bool COLOR>
-__global__ void __launch_bounds__(kThreads) pose_kernel(PoseArgs a) {
+__global__ void __launch_bounds__(kThreads, 4) pose_kernel(PoseArgs a) {
     using Z = ZCell<COLOR>;
     using zkey = typename Z::type;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -167,10 +176,12 @@ __global__ void __launch_bounds__(kThreads) pose_kernel(PoseArgs a) {
     const int mask_words = (MODE == MODE_COST) ? a.mask_words : 0;
     uint32_t* mask = reinterpret_cast<uint32_t*>(smem_raw + (size_t)a.tile_cap * sizeof(zkey));
     int* queue = reinterpret_cast<int*>(mask + mask_words);
+    int* wpend = queue + kQueueCap + (threadIdx.x >> 5) * kPendCap;  // per-warp surviving clusters
 
     __shared__ Mat4 s_pose;
     __shared__ int s_rect[4];
-    __shared__ int s_qcount, s_bigcount;
+    __shared__ int s_qcount, s_bigcount, s_next;
+    __shared__ float s_apx[20];
     __shared__ int s_big[kBigCap];
     __shared__ int s_n, s_c, s_e;
 
@@ -179,7 +190,7 @@ __global__ void __launch_bounds__(kThreads) pose_kernel(PoseArgs a) {
     const int W = a.cam.width, H = a.cam.height, s = a.stride;
     const int Lw = W / s, Lh = (H + s - 1) / s;
     const float wf = (float)W, hf = (float)H;  // cvt.rn.f32.u64 of width/height
-    const float half_w = 0.5f * wf, half_h = 0.5f * hf, s_f = (float)s, inv_s = 1.0f / (float)s;
+    const float half_w = 0.5f * wf, half_h = 0.5f * hf, inv_s = 1.0f / (float)s;
     // lattice raster rows are P1 = H-1-k*s == row_phase (mod s) with row_phase in [0, s)
     const float row_phase = (float)((H - 1) % s);
     const float cmaxx = (float)(W - 1), cmaxy = (float)(H - 1);
@@ -193,9 +204,11 @@ __global__ void __launch_bounds__(kThreads) pose_kernel(PoseArgs a) {
     const bool model_ok = model >= 0 && model < a.models.n_models;
     const int t_low = model_ok ? a.models.model_low[model] : 0;
     const int t_high = model_ok ? a.models.model_high[model] : 0;
+    const int cl_low = model_ok ? a.models.cl_low[model] : 0;
+    const int cl_high = model_ok ? a.models.cl_high[model] : 0;
+    const int lane = tid & 31;
     const bool use_label = a.pose_label != nullptr;
     const int pose_label = use_label ? a.pose_label[pose_i] : 0;
-    const Mat4 pose = s_pose;
 
     // ---- 1. lattice tile from the posed AABB (first warp) -------------------------------------------------
     if (tid < 32) {
@@ -204,7 +217,7 @@ __global__ void __launch_bounds__(kThreads) pose_kernel(PoseArgs a) {
         if (tid < 8 && model_ok) {
             const float* bb = a.models.model_aabb + 6 * model;
             float x = bb[(tid & 1) ? 3 : 0], y = bb[(tid & 2) ? 4 : 1], z = bb[(tid & 4) ? 5 : 2];
-            ScreenVertex v = transform_vertex(pose, a.cam.proj, wf, hf, x, y, z);
+            ScreenVertex v = transform_vertex(s_pose, a.cam.proj, wf, hf, x, y, z);
             bad = !(v.z > 1e-6f) || !(fabsf(v.sx) < 1e7f) || !(fabsf(v.sy) < 1e7f);
             minx = maxx = v.sx; miny = maxy = v.sy; minz = v.z;
         }
@@ -218,7 +231,7 @@ __global__ void __launch_bounds__(kThreads) pose_kernel(PoseArgs a) {
         bad = __any_sync(0xffffffffu, bad);
         if (tid == 0) {
             int x0 = 0, x1 = Lw - 1, y0 = 0, y1 = Lh - 1;
-            if (!model_ok || t_high <= t_low) { x0 = 1; x1 = 0; }
+            if (!model_ok || t_high <= t_low || cl_high <= cl_low) { x0 = 1; x1 = 0; }
             else if (!bad) {
                 // 2 px guard band against the float rounding of the per-vertex path; raster row -> image row flip
                 float px0 = floorf(minx) - 2.f, px1 = ceilf(maxx) + 2.f;
@@ -235,6 +248,29 @@ __global__ void __launch_bounds__(kThreads) pose_kernel(PoseArgs a) {
             s_rect[0] = x0; s_rect[1] = x1; s_rect[2] = y0; s_rect[3] = y1;
         }
     }
+    if (tid == 32) {
+        const Mat4& pose = s_pose;
+        // Per-pose constants of the APPROXIMATE transform used by the conservative culling (pass A): lattice
+        // coordinates (ux, uy) = (sx / s, (sy - row_phase) / s), so that lattice pixels are the integer points, as
+        //   ux = (U . (x,y,z,1)) / (C . (x,y,z,1)) + offx,   uy = (V . (x,y,z,1)) / (C . (x,y,z,1)) + offy
+        // with U = hw/s * (P.a0*pose.a + P.a1*pose.b) (+ P.a3 on the translation), offx = hw*(1 + P.a2)/s, C = pose.c
+        // (the exact path, exact_math.cuh, evaluates sx = fma(W, 0.5, ((P.a . cam) / cam.z * W) * 0.5) instead).
+        const Mat4& P = a.cam.proj;
+        const float kx = half_w * inv_s, ky = half_h * inv_s;
+        float* U = s_apx, *V = s_apx + 4, *C = s_apx + 8;
+        U[0] = kx * (P.a0 * pose.a0 + P.a1 * pose.b0); U[1] = kx * (P.a0 * pose.a1 + P.a1 * pose.b1);
+        U[2] = kx * (P.a0 * pose.a2 + P.a1 * pose.b2); U[3] = kx * (P.a0 * pose.a3 + P.a1 * pose.b3 + P.a3);
+        V[0] = ky * (P.b0 * pose.a0 + P.b1 * pose.b0); V[1] = ky * (P.b0 * pose.a1 + P.b1 * pose.b1);
+        V[2] = ky * (P.b0 * pose.a2 + P.b1 * pose.b2); V[3] = ky * (P.b0 * pose.a3 + P.b1 * pose.b3 + P.b3);
+        C[0] = pose.c0; C[1] = pose.c1; C[2] = pose.c2; C[3] = pose.c3;
+        s_apx[12] = (half_w + half_w * P.a2) * inv_s;
+        s_apx[13] = (half_h + half_h * P.b2 - row_phase) * inv_s;
+        // cluster test: a point within r of a centre with numerators (N, Z) moves ux by at most
+        //   r * (|U| + |N/Z| * |C|) / (Z - r*|C|)        (|.| = norm of the 3-vector part)
+        s_apx[14] = sqrtf(U[0] * U[0] + U[1] * U[1] + U[2] * U[2]) * 1.0001f;
+        s_apx[15] = sqrtf(V[0] * V[0] + V[1] * V[1] + V[2] * V[2]) * 1.0001f;
+        s_apx[16] = sqrtf(C[0] * C[0] + C[1] * C[1] + C[2] * C[2]) * 1.0001f;
+    }
     __syncthreads();
     const int rx0 = s_rect[0], rx1 = s_rect[1], ry0 = s_rect[2], ry1 = s_rect[3];
     const int tile_w = rx1 - rx0 + 1;
@@ -249,19 +285,20 @@ __global__ void __launch_bounds__(kThreads) pose_kernel(PoseArgs a) {
             for (int c = tid; c < band_cells; c += kThreads) zbuf[c] = Z::empty();
             if (tid == 0) { s_qcount = 0; s_bigcount = 0; }
             __syncthreads();
-            // band limits in raster coordinates for the candidate test: columns [rx0*s, rx1*s]; raster rows
-            // P1 = H-1-ly*s for ly in [by0, by1]
-            const float band_lo_x = (float)(rx0 * s) - 0.5f, band_hi_x = (float)(rx1 * s);
-            const float band_lo_y = (float)(H - 1 - by1 * s) - 0.5f, band_hi_y = (float)(H - 1 - by0 * s);
+            // band limits in lattice coordinates for the candidate test: columns ux in [rx0, rx1]; raster rows
+            // P1 = H-1-ly*s for ly in [by0, by1], i.e. uy = (H-1-row_phase)/s - ly
+            const float rows_k = (float)((H - 1) / s);
+            const float band_lo_x = (float)rx0 - 0.5f * inv_s, band_hi_x = (float)rx1;
+            const float band_lo_y = (rows_k - (float)by1) - 0.5f * inv_s, band_hi_y = rows_k - (float)by0;
 
             // Exact path for one triangle: the reference's float sequence (exact_math.cuh), its bbox loops restricted
             // to lattice pixels of this band, z-test with atomicMin.  `coop` = all threads of the CTA share the work.
             auto raster_tri = [&](int t, bool coop, bool allow_defer) -> bool {
                 float v[9];
                 load_tri(a.models, t, v);
-                ScreenVertex A = transform_vertex(pose, a.cam.proj, wf, hf, v[0], v[1], v[2]);
-                ScreenVertex B = transform_vertex(pose, a.cam.proj, wf, hf, v[3], v[4], v[5]);
-                ScreenVertex C = transform_vertex(pose, a.cam.proj, wf, hf, v[6], v[7], v[8]);
+                ScreenVertex A = transform_vertex(s_pose, a.cam.proj, wf, hf, v[0], v[1], v[2]);
+                ScreenVertex B = transform_vertex(s_pose, a.cam.proj, wf, hf, v[3], v[4], v[5]);
+                ScreenVertex C = transform_vertex(s_pose, a.cam.proj, wf, hf, v[6], v[7], v[8]);
                 float bminx, bmaxx, bminy, bmaxy;
                 bbox_of(A, B, C, cmaxx, cmaxy, bminx, bmaxx, bminy, bmaxy);
                 LatticeRect r = lattice_rect_of(bminx, bmaxx, bminy, bmaxy, W, H, s);
@@ -273,69 +310,113 @@ __global__ void __launch_bounds__(kThreads) pose_kernel(PoseArgs a) {
                 if (allow_defer && cells > kBigCells) return true;  // caller re-queues it for the cooperative pass
                 TriSetup ts;
                 setup_edges(A, B, C, ts);
+                const uint32_t id = COLOR ? (uint32_t)__ldg(a.models.cl_orig + t) : 0u;  // original triangle index
                 const int first = coop ? tid : 0, step = coop ? kThreads : 1;
                 for (int c = first; c < cells; c += step) {
                     int ly = y0 + c / w, lx = x0 + c % w;
                     int32_t d;
                     if (fragment_depth(ts, (float)(lx * s), (float)(H - 1 - ly * s), d))
-                        atomicMin(&zbuf[(ly - by0) * tile_w + (lx - rx0)], Z::make(d, (uint32_t)t));
+                        atomicMin(&zbuf[(ly - by0) * tile_w + (lx - rx0)], Z::make(d, id));
                 }
                 return false;
             };
 
-            // Conservative candidate test (pass A).  Same fma chains as the exact path up to clip space, then an
-            // APPROXIMATE perspective divide (MUFU.RCP instead of the IEEE divide): screen coordinates are within a
-            // small fraction of kEps pixels of the exact ones, so a bbox grown by kEps that contains no lattice pixel
-            // proves the exact bbox contains none.  Anything else (including NaN/inf coordinates, whose handling by
-            // the reference's select chain is order dependent) goes to the exact path.
-            auto maybe_hits = [&](int t) -> bool {
+            // Conservative culling (pass A), in lattice coordinates.  `lattice_hit`: can the reference's pixel loops,
+            // P in (min-0.5, max] clamped to the image (image_renderer.cuh:110-111), visit a lattice pixel of this band,
+            // when the true bounds may differ from (minx..maxy) by kEps pixels?
+            const float m_lo = (0.5f + kEps) * inv_s, m_hi = kEps * inv_s;
+            auto lattice_hit = [&](float minx, float maxx, float miny, float maxy) -> bool {
+                float lo_x = fmaxf(minx - m_lo, band_lo_x), hi_x = fminf(maxx + m_hi, band_hi_x);
+                float lo_y = fmaxf(miny - m_lo, band_lo_y), hi_y = fminf(maxy + m_hi, band_hi_y);
+                return (ceilf(lo_x - 1e-3f) <= hi_x) && (ceilf(lo_y - 1e-3f) <= hi_y);
+            };
+            const float U0 = s_apx[0], U1 = s_apx[1], U2 = s_apx[2], U3 = s_apx[3];
+            const float V0 = s_apx[4], V1 = s_apx[5], V2 = s_apx[6], V3 = s_apx[7];
+            const float C0 = s_apx[8], C1 = s_apx[9], C2 = s_apx[10], C3 = s_apx[11];
+            const float offx = s_apx[12], offy = s_apx[13];
+            // Level 1: bounding sphere of a cluster.  Anything not provably finite and in front of the camera is kept.
+            auto cluster_hits = [&](int c) -> bool {
+                const float4 b = __ldg(a.models.cl_bounds + c);
+                const float n0 = fmaf(b.z, U2, fmaf(b.y, U1, fmaf(b.x, U0, U3)));
+                const float n1 = fmaf(b.z, V2, fmaf(b.y, V1, fmaf(b.x, V0, V3)));
+                const float zc = fmaf(b.z, C2, fmaf(b.y, C1, fmaf(b.x, C0, C3)));
+                const float iz = __frcp_approx(zc);
+                const float ux0 = n0 * iz, uy0 = n1 * iz;
+                const float nC = s_apx[16];
+                const float zden = fmaf(-b.w, nC, zc);
+                const float rr = b.w * __frcp_approx(zden);
+                const float Rx = fmaf(rr, fmaf(fabsf(ux0), nC, s_apx[14]), m_hi);
+                const float Ry = fmaf(rr, fmaf(fabsf(uy0), nC, s_apx[15]), m_hi);
+                const float ux = ux0 + offx, uy = uy0 + offy;
+                if (!(zden > 1e-6f) || !(fabsf(ux) + fabsf(uy) + Rx + Ry < 1e30f)) return true;
+                return lattice_hit(ux - Rx, ux + Rx, uy - Ry, uy + Ry);
+            };
+            // Level 2: approximate bbox of one triangle.  NaN/inf/absurd coordinates (whose handling by the
+            // reference's select chain is order dependent) go to the exact path, which re-derives everything.
+            auto tri_hits = [&](int t) -> bool {
                 float v[9];
                 load_tri(a.models, t, v);
-                float sx[3], sy[3];
+                float ux[3], uy[3];
 #pragma unroll
                 for (int k = 0; k < 3; ++k) {
-                    float x = v[3 * k], y = v[3 * k + 1], z = v[3 * k + 2];
-                    float X = xf_row(pose.a0, pose.a1, pose.a2, pose.a3, x, y, z);
-                    float Y = xf_row(pose.b0, pose.b1, pose.b2, pose.b3, x, y, z);
-                    float Zc = xf_row(pose.c0, pose.c1, pose.c2, pose.c3, x, y, z);
-                    float px = xf_row(a.cam.proj.a0, a.cam.proj.a1, a.cam.proj.a2, a.cam.proj.a3, X, Y, Zc);
-                    float py = xf_row(a.cam.proj.b0, a.cam.proj.b1, a.cam.proj.b2, a.cam.proj.b3, X, Y, Zc);
-                    float iz = __frcp_approx(Zc);
-                    sx[k] = fmaf(px * iz, half_w, half_w);
-                    sy[k] = fmaf(py * iz, half_h, half_h);
+                    const float x = v[3 * k], y = v[3 * k + 1], z = v[3 * k + 2];
+                    const float n0 = fmaf(z, U2, fmaf(y, U1, fmaf(x, U0, U3)));
+                    const float n1 = fmaf(z, V2, fmaf(y, V1, fmaf(x, V0, V3)));
+                    const float iz = __frcp_approx(fmaf(z, C2, fmaf(y, C1, fmaf(x, C0, C3))));
+                    ux[k] = fmaf(n0, iz, offx);
+                    uy[k] = fmaf(n1, iz, offy);
                 }
-                float sum = (sx[0] + sx[1]) + (sx[2] + sy[0]) + (sy[1] + sy[2]);
-                if (!(fabsf(sum) < 1e30f)) return true;  // NaN / inf / absurd: let the exact path decide
-                // pixels the reference loop can visit: P in (bmin - 0.5, bmax], clamped to the image; grow by kEps
-                float lo_x = fmaxf(fminf(fminf(sx[0], sx[1]), sx[2]) - (0.5f + kEps), band_lo_x);
-                float hi_x = fminf(fmaxf(fmaxf(sx[0], sx[1]), sx[2]) + kEps, band_hi_x);
-                float lo_y = fmaxf(fminf(fminf(sy[0], sy[1]), sy[2]) - (0.5f + kEps), band_lo_y);
-                float hi_y = fminf(fmaxf(fmaxf(sy[0], sy[1]), sy[2]) + kEps, band_hi_y);
-                // first lattice coordinate >= lo (lattice columns are x = k*s; lattice raster rows are P1 = H-1-k*s)
-                float kx = ceilf(fmaf(lo_x, inv_s, -1e-3f));
-                float ky = ceilf(fmaf(lo_y - row_phase, inv_s, -1e-3f));
-                return (kx * s_f <= hi_x) && (fmaf(ky, s_f, row_phase) <= hi_y);
+                float sum = (ux[0] + ux[1]) + (ux[2] + uy[0]) + (uy[1] + uy[2]);
+                if (!(fabsf(sum) < 1e30f)) return true;
+                return lattice_hit(fminf(fminf(ux[0], ux[1]), ux[2]), fmaxf(fmaxf(ux[0], ux[1]), ux[2]),
+                                   fminf(fminf(uy[0], uy[1]), uy[2]), fmaxf(fmaxf(uy[0], uy[1]), uy[2]));
+            };
+            // per-triangle test of 8 pending clusters (4 lanes each); candidates go to the shared queue
+            auto test_pending = [&](int first, int count) {
+                const int e = lane >> 2;
+                bool hit = false;
+                int t = 0;
+                if (e < count) {
+                    t = 4 * wpend[first + e] + (lane & 3);
+                    hit = tri_hits(t);
+                }
+                unsigned ballot = __ballot_sync(0xffffffffu, hit);
+                if (ballot) {
+                    int slot = 0;
+                    if (lane == 0) slot = atomicAdd(&s_qcount, __popc(ballot));
+                    slot = __shfl_sync(0xffffffffu, slot, 0) + __popc(ballot & ((1u << lane) - 1u));
+                    if (hit) queue[slot] = t;
+                }
             };
 
-            const int chunk = kQueueCap;  // triangles per fill phase: can add at most kQueueCap entries
-            for (int cbase = t_low; cbase < t_high; cbase += chunk) {
-                const int cend = min(cbase + chunk, t_high);
-                // pass A: conservative test for every triangle, warp-aggregated compaction of the candidates
-                for (int base = cbase; base < cend; base += kThreads) {
-                    int t = base + tid;
-                    bool hit = (t < cend) && maybe_hits(t);
-                    unsigned ballot = __ballot_sync(0xffffffffu, hit);
-                    if (ballot) {
-                        int lane = tid & 31;
-                        int slot = 0;
-                        if (lane == 0) slot = atomicAdd(&s_qcount, __popc(ballot));
-                        slot = __shfl_sync(0xffffffffu, slot, 0) + __popc(ballot & ((1u << lane) - 1u));
-                        if (hit) queue[slot] = t;
+            // Warps claim groups of kClaim clusters dynamically (no block barrier inside pass A); a warp stops
+            // claiming when the candidate queue could overflow.
+            const int n_groups = (cl_high - cl_low + kClaim - 1) / kClaim;
+            if (tid == 0) s_next = 0;
+            __syncthreads();
+            for (;;) {
+                int npend = 0;  // warp-uniform
+                for (;;) {
+                    int g = 0x7fffffff;
+                    if (lane == 0 && *(volatile int*)&s_qcount <= kQueueCap - kWarps * kClaimMaxTris) g = atomicAdd(&s_next, 1);
+                    g = __shfl_sync(0xffffffffu, g, 0);
+                    if (g >= n_groups) break;
+                    const int c = cl_low + g * kClaim + lane;
+                    const bool keep = (c < cl_high) && cluster_hits(c);
+                    const unsigned ballot = __ballot_sync(0xffffffffu, keep);
+                    if (keep) wpend[npend + __popc(ballot & ((1u << lane) - 1u))] = c;
+                    npend += __popc(ballot);
+                    __syncwarp();
+                    while (npend >= 8) {
+                        npend -= 8;
+                        test_pending(npend, 8);
                     }
+                    __syncwarp();
                 }
+                if (npend > 0) test_pending(0, npend);
                 __syncthreads();
                 const int qn = s_qcount;
-                if (qn + chunk <= kQueueCap && cend < t_high) continue;  // room for another fill phase
+                const bool all_claimed = *(volatile int*)&s_next >= n_groups;
                 // pass B: exact rasterisation of the candidates, one triangle per thread; triangles covering many
                 // lattice pixels are deferred to the cooperative pass
                 for (int e = tid; e < qn; e += kThreads) {
@@ -352,6 +433,7 @@ __global__ void __launch_bounds__(kThreads) pose_kernel(PoseArgs a) {
                 __syncthreads();
                 if (tid == 0) { s_qcount = 0; s_bigcount = 0; }
                 __syncthreads();
+                if (all_claimed) break;
             }
 
             if (MODE == MODE_IMAGE) {
@@ -490,8 +572,9 @@ __global__ void fill_keys_kernel(unsigned long long* keys, int n) {
 }  // namespace
 
 size_t pose_kernel_smem_bytes(const PoseArgs& a, bool image_mode, bool color) {
-    return (size_t)a.tile_cap * ((color || image_mode) ? 8 : 4) + (image_mode ? 0 : (size_t)a.mask_words * 4) +
-           (size_t)kQueueCap * 4;
+    size_t b = (size_t)a.tile_cap * ((color || image_mode) ? 8 : 4) + (image_mode ? 0 : (size_t)a.mask_words * 4) +
+               (size_t)kQueueCap * 4;
+    return b + (size_t)kWarps * kPendCap * sizeof(int);
 }
 
 template <int MODE, bool COLOR>
