@@ -65,8 +65,8 @@ typedef struct perch_params {
 } perch_params;
 
 /* Host output buffers of one perch_render_cost call.  Every pointer is optional (NULL = not wanted) and
- * CALLER-provided; use perch_*_count queries or the capacities below.  (The C++ compat wrappers in
- * perception_b200/csrc/compat reproduce the reference's callee-malloc ownership on top of this.) */
+ * CALLER-provided, sized by the capacities below.  (The C++ backend perception_b200/csrc/compat/cuda_renderer_compat.cpp
+ * reproduces the reference's callee-malloc ownership on top of this.) */
 typedef struct perch_outputs {
     /* stage RENDER / DEBUG (renderer.cu:1594-1615): P*W*H each (W*H when single_result_image) */
     int32_t* depth;
@@ -120,8 +120,9 @@ int perch_set_models(perch_ctx* ctx, const perch_triangle* tris, int64_t n_tris,
 int perch_set_scene(perch_ctx* ctx, const int32_t* source_depth, const uint8_t* source_red,
                     const uint8_t* source_green, const uint8_t* source_blue, const uint8_t* source_mask_label);
 /* @observed_depth_eigen (N x 3 AoS), @observed_color (3 x N SoA), @result_observed_cloud_label (may be NULL),
- * @observed_point_num (renderer.cu:1451-1456).  In 6-DoF mode the cloud is stably sorted by label like
- * renderer.cu:1681 and NN search is restricted to the pose's label range. */
+ * @observed_point_num (renderer.cu:1451-1456).  In 6-DoF mode the nearest-neighbour search is restricted to observed
+ * points carrying the pose's label (the reference sorts by label and searches the label's range, renderer.cu:1668-1686;
+ * same candidate set, and indices keep referring to the caller's order). */
 int perch_set_observed(perch_ctx* ctx, const float* observed_xyz_aos, const uint8_t* observed_color_soa,
                        const int* observed_label, int n_obs);
 

@@ -338,6 +338,66 @@ def test_cost_edge_cases(orc):
             r.render_cuda_multi_unified("COST", poses, pmm, None, tot, stride=7)  # 640 % 7 != 0
 
 
+def test_forced_bands_and_tiny_queues(orc, monkeypatch):
+    """A tile cap far below the tile size cuts every pose into many bands (and IMAGE mode likewise): results must not
+    change.  Exercises the band clamp of the culling tests and the multi-round candidate queue."""
+    case, obs, poses, pmm, lab, tot = _cost_case(orc, 5000, 4, False, 24)
+    with make_renderer(case) as r:
+        r.set_observed(obs["aos"], obs["rgb"], None)
+        a = r.render_cuda_multi_unified("COST", poses, pmm, None, tot, stride=4, sensor_resolution=0.0075)
+        ia = r.render_cuda_multi_unified("RENDER", poses[:6], pmm[:6])
+        monkeypatch.setenv("PERCH_COST_TILE_CAP", "1")   # clamped up to one lattice row per band
+        monkeypatch.setenv("PERCH_IMAGE_TILE_CAP", "1")
+        b = r.render_cuda_multi_unified("COST", poses, pmm, None, tot, stride=4, sensor_resolution=0.0075)
+        ib = r.render_cuda_multi_unified("RENDER", poses[:6], pmm[:6])
+    assert a["counts"][0].sum() > 0
+    assert np.array_equal(a["counts"], b["counts"])
+    assert np.array_equal(ia["result_depth"], ib["result_depth"]) and np.array_equal(ia["result_color"], ib["result_color"])
+
+
+def test_non_finite_vertices_and_degenerate_triangles(orc):
+    """NaN / inf vertices and zero-area triangles must neither crash nor leak through the conservative culling: the
+    exact path decides, exactly like the reference's float sequence (oracle)."""
+    case = make_case(600, 3, 42)
+    s = case.scene
+    tris = s.tris.copy()
+    n0 = int(s.tris_model_count[0])
+    rng = np.random.default_rng(5)
+    bad = rng.choice(n0, 24, replace=False)
+    v = tris["v"]
+    v[bad[:6], 0, 0] = np.nan
+    v[bad[6:12], 1, 2] = np.inf
+    v[bad[12:18], 2] = v[bad[12:18], 1]          # two equal vertices: zero area
+    v[bad[18:24]] = v[bad[18:24], :1]            # a point
+    poses, pmm, _ = poses_near_gt(case, 8)
+    with make_renderer(case) as r:
+        r.set_models(tris, s.tris_model_count)
+        out = r.render_cuda_multi_unified("RENDER", poses, pmm)
+    d_o, c_o = orc.render(tris, s.tris_model_count, poses, pmm, case.width, case.height, case.proj, s.source_depth,
+                          None, None, 1.0)
+    assert (d_o > 0).sum() > 0
+    assert np.array_equal(out["result_depth"], d_o)
+    assert np.array_equal(out["result_color"], c_o)
+
+
+def test_pose_permutation_and_duplicates(orc):
+    """Poses are independent units: permuting the pose list permutes the results, a duplicated pose scores the same."""
+    case, obs, poses, pmm, lab, tot = _cost_case(orc, 2000, 8, True, 32)
+    perm = np.random.default_rng(1).permutation(len(poses))
+    poses2 = np.concatenate([poses[perm], poses[:5]])
+    pmm2 = np.concatenate([pmm[perm], pmm[:5]])
+    lab2 = np.concatenate([lab[perm], lab[:5]])
+    tot2 = np.concatenate([tot[perm], tot[:5]])
+    with make_renderer(case, with_label=True) as r:
+        r.set_observed(obs["aos"], obs["rgb"], obs["label"])
+        a = r.render_cuda_multi_unified("COST", poses, pmm, lab, tot, stride=8, cost_type=2, sensor_resolution=0.01)
+        b = r.render_cuda_multi_unified("COST", poses2, pmm2, lab2, tot2, stride=8, cost_type=2, sensor_resolution=0.01)
+    n = len(poses)
+    assert np.array_equal(b["counts"][:, :n], a["counts"][:, perm])
+    assert np.array_equal(b["counts"][:, n:], a["counts"][:, :5])
+    assert np.array_equal(b["rendered_cost"][:n], a["rendered_cost"][perm])
+
+
 def test_triangle_order_invariance():
     """Depth is a min over fragments: shuffling the triangle soup must not change it (colour may, on ties)."""
     case = make_case(5000, 3, 42)
