@@ -165,6 +165,7 @@ def measured_peak_gbs():
 def run_ours(args):
     import torch
     import torch.distributed as dist
+    from perception_b200 import sharding
     from perception_b200.renderer import topk
 
     rank, local_rank, world = rank_info()
@@ -217,14 +218,7 @@ def run_ours(args):
     def e2e_step():
         out = r.render_cuda_multi_unified("COST", h_poses, h_pmm, h_lab, h_tot, **kw)
         hits = topk(out["rendered_cost"], out["observed_cost"], h_pmm, 1, k=K_TOP, pose_id_offset=rank * P)
-        if world > 1:
-            t = torch.from_numpy(hits.view(np.int32).reshape(-1).copy()).cuda()
-            g = [torch.empty_like(t) for _ in range(world)]
-            dist.all_gather(g, t)
-            allh = torch.stack(g).cpu().numpy().reshape(world * K_TOP, 4)
-            best = allh[np.lexsort((allh[:, 1], allh[:, 0]))][0]
-        else:
-            best = hits[0, 0]
+        best = sharding.merge_hits(sharding.gather_hits(hits), K_TOP)[0, 0]  # all_gather of k x 16 B per rank
         return out, best
 
     for _ in range(max(1, min(args.warmup, 3))):
@@ -276,7 +270,7 @@ def run_ours(args):
                          "traffic": traffic, "peak_kind": f"{peak_kind} copy bandwidth", "bytes_per_pose": bpp,
                          "poses_per_launch": P, "kernel": "pose_kernel<MODE_COST>", "kernel_ms": kern_ms},
             "work": work,
-            "best": {"cost": int(best[0]), "pose_id": int(best[1])},
+            "best": {"cost": int(best["cost"]), "pose_id": int(best["pose_id"])},
             "wall_s_device_loop": wall_device_loop,
         }
         if world == 1 and not args.no_cpu_baseline:

@@ -1,0 +1,85 @@
+"""Host logic of the multi-GPU path on CPU: pose sharding, per-rank top-k (the real perch_topk of libperch_b200.so, a
+host function) and the all_gather + merge over a world_size-2 gloo group must reproduce the single-process argmin."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from perception_b200 import sharding
+from perception_b200.renderer import topk
+
+
+def _costs(n, n_models, seed=0):
+    rng = np.random.default_rng(seed)
+    rendered = rng.uniform(0, 100, n).astype(np.float32)
+    observed = (rendered + rng.uniform(-45, 45, n)).astype(np.float32)
+    rendered[rng.choice(n, n // 20, replace=False)] = -1.0      # poses that rendered nothing
+    observed[rng.choice(n, n // 50, replace=False)] = np.nan    # pose_observed_points_total == 0
+    rendered[:8] = 10.25                                        # ties on the integer cost: lowest pose id must win
+    observed[:8] = 12.5
+    pmm = rng.integers(0, n_models, n).astype(np.int32)
+    return rendered, observed, pmm
+
+
+def test_shard_range_partitions_exactly():
+    for n in (0, 1, 7, 16384, 100003):
+        for world in (1, 2, 3, 8):
+            blocks = [sharding.shard_range(n, r, world) for r in range(world)]
+            assert blocks[0][0] == 0 and blocks[-1][1] == n
+            assert all(blocks[i][1] == blocks[i + 1][0] for i in range(world - 1))
+            sizes = [hi - lo for lo, hi in blocks]
+            assert max(sizes) - min(sizes) <= 1
+    with pytest.raises(ValueError):
+        sharding.shard_range(10, 2, 2)
+
+
+def test_merge_equals_global_topk():
+    n, n_models, k = 5000, 3, 8
+    rendered, observed, pmm = _costs(n, n_models)
+    want = topk(rendered, observed, pmm, n_models, k=k)
+    for world in (1, 2, 5):
+        parts = []
+        for r in range(world):
+            lo, hi = sharding.shard_range(n, r, world)
+            parts.append(topk(rendered[lo:hi], observed[lo:hi], pmm[lo:hi], n_models, k=k, pose_id_offset=lo))
+        got = sharding.merge_hits(np.stack(parts), k)
+        assert np.array_equal(got["cost"], want["cost"]) and np.array_equal(got["pose_id"], want["pose_id"])
+        assert np.array_equal(got["rendered_cost"], want["rendered_cost"])
+
+
+def _worker(rank, world, port, n, n_models, k, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        rendered, observed, pmm = _costs(n, n_models)
+        lo, hi = sharding.shard_range(n, rank, world)
+        hits = topk(rendered[lo:hi], observed[lo:hi], pmm[lo:hi], n_models, k=k, pose_id_offset=lo)
+        merged = sharding.merge_hits(sharding.gather_hits(hits), k)
+        q.put((rank, merged.tobytes()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_gloo_gather_reproduces_single_process_argmin():
+    n, n_models, k, world = 4001, 2, 4, 2
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, n, n_models, k, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    results = dict(q.get(timeout=120) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    rendered, observed, pmm = _costs(n, n_models)
+    want = topk(rendered, observed, pmm, n_models, k=k)
+    for r in range(world):
+        got = np.frombuffer(results[r], dtype=sharding.HIT_DTYPE).reshape(n_models, k)
+        assert np.array_equal(got["cost"], want["cost"]) and np.array_equal(got["pose_id"], want["pose_id"])
+    assert want["pose_id"].min() >= 0 and (want["cost"][:, 0] != sharding.EMPTY_COST).all()
