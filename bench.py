@@ -277,7 +277,7 @@ def run_ours(args):
             line["cpu_baseline"] = cpu_baseline(wl, budget_s=args.cpu_budget)
         if world == 1 and not args.no_ref_cuda:
             line["reference_cuda"] = reference_cuda(wl, batch=args.ref_batch)
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
     return line
@@ -389,7 +389,7 @@ def run_reference_cpu(args):
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                              "sample": f"{per_step} poses per step of the same workload (oracle/cpu_baseline.c, OpenMP)"},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def run_reference_cuda(args):
@@ -398,11 +398,27 @@ def run_reference_cuda(args):
         return
     r, wl = build_workload(args.workload, 0, local_rank, args.poses, use_product=False)
     out = reference_cuda(wl, batch=args.ref_batch)
-    print(json.dumps({"impl": "reference-cuda", "metric": METRIC, "unit": UNIT, **out,
-                      "config": {"workload": wl["desc"]}}), flush=True)
+    emit({"impl": "reference-cuda", "metric": METRIC, "unit": UNIT, **out, "config": {"workload": wl["desc"]}})
+
+
+_REAL_STDOUT = None
+
+
+def emit(line: dict):
+    """The ONE JSON line goes to the process's original stdout; everything else any library prints while the bench
+    runs (e.g. NCCL's version banner) has been routed to stderr by main()."""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
 
 
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=50)
