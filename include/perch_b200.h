@@ -161,6 +161,17 @@ int perch_synchronize(perch_ctx* ctx);
 /* Measurement hygiene: overwrite a buffer larger than the 126 MB L2 on the context's stream (between timed steps). */
 int perch_l2_flush(perch_ctx* ctx);
 
+/* ---- k nearest neighbours (package API of cuda_renderer/knncuda.h) ------------------------------------------ */
+/* Replaces knn_cuda_global / knn_cuda_texture / knn_cublas (knncuda.h:33-100, knncuda.cu:276-421, 424-616, 618-838):
+ * ref is dim x ref_nb and query dim x query_nb, one ROW per dimension (element (d, i) at d*nb + i); outputs are
+ * k x query_nb: knn_dist[j*query_nb + i] = Euclidean distance (square root applied) of query i to its j-th nearest
+ * reference point, knn_index the 0-based index of that point; ascending distance, equal distances by ascending
+ * index.  All four pointers are HOST memory like in the reference.  Distances and indices are bit-identical to
+ * knn_cuda_global's; knn_cublas's differ from both in the last bits (||r||^2+||q||^2-2rq formulation) and are
+ * covered by the package's own acceptance rule (knn_test, knncuda.cu:1001-1090).  k must not exceed ref_nb. */
+int perch_knn(perch_ctx* ctx, const float* ref, int ref_nb, const float* query, int query_nb, int dim, int k,
+              float* knn_dist, int* knn_index);
+
 /* Per-model argmin the caller performs after scoring (search_env.cpp:2542-2583), generalised to top-k:
  * cost = (int)(rendered + observed), -1 if rendered < 0 (search_env.cpp:2022-2027); candidates with
  * |rendered - observed| >= 30 or cost < 0 are skipped; ties resolve to the lowest pose id (strict `<`).

@@ -122,3 +122,19 @@ int compat_render(const char* stage, const void* tris64, int n_tris, const float
 }
 
 }  // extern "C"
+
+// ---- kNN package API through the reference's own <cuda_renderer/knncuda.h> declarations ---------------------------
+#include "cuda_renderer/knncuda.h"
+
+extern "C" int compat_knn(int variant, const float* ref, int ref_nb, const float* query, int query_nb, int dim, int k,
+                          float* knn_dist, int* knn_index) {
+    using namespace cuda_renderer;
+    bool ok = false;
+    switch (variant) {
+        case 0: ok = knn_cuda_global(ref, ref_nb, query, query_nb, dim, k, knn_dist, knn_index); break;
+        case 1: ok = knn_cuda_texture(ref, ref_nb, query, query_nb, dim, k, knn_dist, knn_index); break;
+        case 2: ok = knn_cublas(ref, ref_nb, query, query_nb, dim, k, knn_dist, knn_index); break;
+        default: ok = knn_test(ref, ref_nb, query, query_nb, dim, k, knn_dist, knn_index); break;
+    }
+    return ok ? 0 : 1;
+}

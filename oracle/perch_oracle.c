@@ -457,3 +457,54 @@ void oracle_costs(const int32_t* depth, const uint8_t* r, const uint8_t* g, cons
     free(c_aos); free(c_rgb); free(c_map); free(c_label); free(o_aos); free(lb); free(le);
     free(k_dist); free(k_idx); free(cost); free(num); free(explained);
 }
+
+/*
+ * kNN-CUDA package API (cuda_renderer/knncuda.h:33-100).  Layout: ref is dim x ref_nb, query dim x query_nb (one row
+ * per dimension); outputs k x query_nb, ascending distance, square root applied, 0-based indices.
+ * Selection = knn_c's modified insertion sort (knncuda.cu:882-912, same as the device kernel :149-195): element i is
+ * skipped when i >= k and dist >= dist[k-1]; otherwise it moves left past STRICTLY larger entries only, so equal
+ * distances stay in ascending index order.
+ * fused != 0: squared distance as the device kernel computes it under nvcc's default -fmad, ssd = fma(diff, diff, ssd)
+ *             over the dimensions in order (compute_distances, knncuda.cu:26-96) -> bit-comparable with
+ *             knn_cuda_global / knn_cuda_texture.
+ * fused == 0: knn_c's host arithmetic (compute_distance, knncuda.cu:852-865): separate multiply and add.
+ * Needs k <= ref_nb.
+ */
+int oracle_knn(const float* ref, int ref_nb, const float* query, int query_nb, int dim, int k, int fused,
+               float* knn_dist, int* knn_index) {
+    if (k > ref_nb || k <= 0 || dim <= 0) return 1;
+    float* dist = (float*)malloc((size_t)ref_nb * sizeof(float));
+    int* index = (int*)malloc((size_t)ref_nb * sizeof(int));
+    if (!dist || !index) { free(dist); free(index); return 2; }
+    for (int i = 0; i < query_nb; ++i) {
+        for (int j = 0; j < ref_nb; ++j) {
+            float sum = 0.f;
+            for (int d = 0; d < dim; ++d) {
+                const float diff = ref[(size_t)d * ref_nb + j] - query[(size_t)d * query_nb + i];
+                if (fused) sum = fmaf(diff, diff, sum);
+                else { const float sq = diff * diff; sum = sum + sq; }
+            }
+            /* knn_c takes the root BEFORE the selection (compute_distance :864), the device path after it
+               (compute_sqrt :206-211): two different squared distances that round to the same root are a tie (index
+               order) for the former and ordered for the latter. */
+            dist[j] = fused ? sum : sqrtf(sum);
+            index[j] = j;
+        }
+        index[0] = 0;
+        for (int t = 1; t < ref_nb; ++t) {
+            const float cur = dist[t];
+            if (t >= k && cur >= dist[k - 1]) continue;
+            int j = t < k - 1 ? t : k - 1;
+            while (j > 0 && dist[j - 1] > cur) { dist[j] = dist[j - 1]; index[j] = index[j - 1]; --j; }
+            dist[j] = cur;
+            index[j] = t;
+        }
+        for (int j = 0; j < k; ++j) {
+            knn_dist[(size_t)j * query_nb + i] = fused ? sqrtf(dist[j]) : dist[j];
+            knn_index[(size_t)j * query_nb + i] = index[j];
+        }
+    }
+    free(dist);
+    free(index);
+    return 0;
+}

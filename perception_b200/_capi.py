@@ -63,6 +63,7 @@ class perch_hit(C.Structure):
 
 # name -> (restype, argtypes); the list doubles as the "every symbol of include/perch_b200.h" check in tests
 _P = C.c_void_p
+_V = C.c_void_p
 SIGNATURES = {
     "perch_create": (C.c_int, [C.c_int, C.POINTER(_P)]),
     "perch_destroy": (None, [_P]),
@@ -70,6 +71,7 @@ SIGNATURES = {
     "perch_abi_version": (C.c_int, []),
     "perch_get_stats": (C.c_int, [_P, C.POINTER(perch_gpu_stats)]),
     "perch_last_timing": (C.c_int, [_P, C.POINTER(C.c_float), C.POINTER(C.c_int)]),
+    "perch_knn": (C.c_int, [_P, _V, C.c_int, _V, C.c_int, C.c_int, C.c_int, _V, _V]),
     "perch_compute_proj": (C.c_int, [_P, C.c_int, C.c_int, C.c_float, C.c_float, _P]),
     "perch_set_camera": (C.c_int, [_P, C.c_int, C.c_int, _P, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float]),
     "perch_set_models": (C.c_int, [_P, _P, C.c_int64, _P, C.c_int]),

@@ -665,6 +665,37 @@ int perch_l2_flush(perch_ctx* c) {
     return PERCH_OK;
 }
 
+int perch_knn(perch_ctx* c, const float* ref, int ref_nb, const float* query, int query_nb, int dim, int k,
+              float* knn_dist, int* knn_index) {
+    if (!c) return fail(PERCH_ERR_INVALID, "null context");
+    if (!ref || !query || !knn_dist || !knn_index) return fail(PERCH_ERR_INVALID, "null knn argument");
+    if (ref_nb <= 0 || query_nb < 0 || dim <= 0 || k <= 0) return fail(PERCH_ERR_INVALID, "bad knn sizes");
+    if (k > ref_nb) return fail(PERCH_ERR_INVALID, "k = %d exceeds the number of reference points %d", k, ref_nb);
+    if (query_nb == 0) return PERCH_OK;
+    DeviceGuard g(c->device);
+    const size_t nr = (size_t)dim * ref_nb, nq = (size_t)dim * query_nb, no = (size_t)k * query_nb;
+    int rc = ensure_scratch(c, Scratch::align(nr * 4) + Scratch::align(nq * 4) + 2 * Scratch::align(no * 4) + 1024);
+    if (rc) return rc;
+    Scratch s(c);
+    float* d_ref = s.take<float>(nr);
+    float* d_query = s.take<float>(nq);
+    float* d_dist = s.take<float>(no);
+    int* d_index = s.take<int>(no);
+    CU(cudaMemcpyAsync(d_ref, ref, nr * 4, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(d_query, query, nq * 4, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaEventRecord(c->ev0, c->stream));
+    CU(perch::launch_knn(d_ref, ref_nb, d_query, query_nb, dim, k, d_dist, d_index, c->sm_count, c->stream));
+    CU(cudaEventRecord(c->ev1, c->stream));
+    CU(cudaMemcpyAsync(knn_dist, d_dist, no * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(knn_index, d_index, no * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1);
+    c->last_launches = 1;
+    c->timing_pending = false;
+    note_memory(c);
+    return PERCH_OK;
+}
+
 int perch_render_cost(perch_ctx* c, const char* stage, const float* poses16, int n_poses, const int* pose_model_map,
                       const int* pose_label, const float* pose_obs_total, const perch_params* p, perch_outputs* out) {
     if (!stage || !p || !out) return fail(PERCH_ERR_INVALID, "null argument");

@@ -86,4 +86,9 @@ cudaError_t launch_rgb2lab_planes(const uint8_t* c0, const uint8_t* c1, const ui
                                   cudaStream_t stream);
 cudaError_t launch_rgb2lab_packed(const uint32_t* packed_rgb, int n, float* lab, cudaStream_t stream);
 
+// ---- exact kNN with the knncuda.h contract (knn.cu) -----------------------------------------------------------------
+// d_ref: dim x ref_nb, d_query: dim x query_nb (row per dimension); outputs k x query_nb.  Requires k <= ref_nb.
+cudaError_t launch_knn(const float* d_ref, int ref_nb, const float* d_query, int query_nb, int dim, int k, float* d_dist,
+                       int* d_index, int sm_count, cudaStream_t stream);
+
 }  // namespace perch

@@ -268,6 +268,19 @@ class Renderer:
     def l2_flush(self) -> None:
         self._ck(self._lib.perch_l2_flush(self._h))
 
+    def knn(self, ref, query, k: int):
+        """k nearest reference points of every query point with the kNN-CUDA contract (knncuda.h:33-100).
+        ref: (dim, ref_nb), query: (dim, query_nb), one row per dimension.  Returns (knn_dist, knn_index), both
+        (k, query_nb): Euclidean distances ascending, 0-based indices, ties by ascending index."""
+        r = np.ascontiguousarray(ref, dtype=np.float32)
+        q = np.ascontiguousarray(query, dtype=np.float32)
+        if r.ndim != 2 or q.ndim != 2 or r.shape[0] != q.shape[0]:
+            raise ValueError("ref and query must be (dim, n) arrays of the same dim")
+        dist = np.zeros((k, q.shape[1]), np.float32)
+        index = np.zeros((k, q.shape[1]), np.int32)
+        self._ck(self._lib.perch_knn(self._h, _ptr(r), r.shape[1], _ptr(q), q.shape[1], r.shape[0], k, _ptr(dist), _ptr(index)))
+        return dist, index
+
 
 def topk(rendered_cost, observed_cost, pose_model_map, n_models: int, k: int = 1, pose_id_offset: int = 0) -> np.ndarray:
     """Per-model best-k candidates by the caller's rule (search_env.cpp:2016-2036, 2542-2583).  Returns a
@@ -280,6 +293,29 @@ def topk(rendered_cost, observed_cost, pose_model_map, n_models: int, k: int = 1
     out = np.zeros((n_models, k), dtype=dt)
     _capi.check(lib, lib.perch_topk(_ptr(r), _ptr(o), _ptr(m), len(r), pose_id_offset, n_models, k, _ptr(out)))
     return out
+
+
+def _knn_entry(ref, ref_nb, query, query_nb, dim, k, device=0):
+    r = np.ascontiguousarray(ref, dtype=np.float32).reshape(dim, ref_nb)
+    q = np.ascontiguousarray(query, dtype=np.float32).reshape(dim, query_nb)
+    with Renderer(device) as rr:
+        return rr.knn(r, q, k)
+
+
+def knn_cuda_global(ref, ref_nb, query, query_nb, dim, k, device=0):
+    """cuda_renderer::knn_cuda_global (knncuda.h:33-52) minus the output pointers: returns (knn_dist, knn_index)."""
+    return _knn_entry(ref, ref_nb, query, query_nb, dim, k, device)
+
+
+def knn_cuda_texture(ref, ref_nb, query, query_nb, dim, k, device=0):
+    """cuda_renderer::knn_cuda_texture (knncuda.h:55-74): same contract, same kernel here."""
+    return _knn_entry(ref, ref_nb, query, query_nb, dim, k, device)
+
+
+def knn_cublas(ref, ref_nb, query, query_nb, dim, k, device=0):
+    """cuda_renderer::knn_cublas (knncuda.h:77-100): same contract, same kernel here (no GEMM: K = dim = 3 is no
+    contraction worth a tensor core, and the ||r||^2+||q||^2-2rq form loses precision)."""
+    return _knn_entry(ref, ref_nb, query, query_nb, dim, k, device)
 
 
 # ---- stateless wrappers with the reference's full argument lists -------------------------------------------------------

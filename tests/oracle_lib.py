@@ -118,6 +118,47 @@ class Oracle:
         return self.lib.oracle_color_distance_rgb(*[int(v) for v in c1], *[int(v) for v in c2])
 
 
+    def knn(self, ref, query, k, fused=True):
+        """oracle_knn: kNN-CUDA contract; fused=True = device arithmetic (fma chain, root after selection),
+        fused=False = knn_c's host arithmetic (root before selection)."""
+        r = _c(ref, np.float32)
+        q = _c(query, np.float32)
+        dist = np.zeros((k, q.shape[1]), np.float32)
+        idx = np.zeros((k, q.shape[1]), np.int32)
+        rc = self.lib.oracle_knn(_p(r), C.c_int(r.shape[1]), _p(q), C.c_int(q.shape[1]), C.c_int(r.shape[0]), C.c_int(k),
+                                 C.c_int(1 if fused else 0), _p(dist), _p(idx))
+        assert rc == 0, rc
+        return dist, idx
+
+
+KNN_REF_SO = ROOT / "oracle" / "_ref" / "libknn_ref.so"
+
+
+class ReferenceKnn:
+    """The reference's own kNN package compiled unmodified from cuda_renderer/src/cuda/knncuda.cu (C++ mangled names).
+    knn_c is host code (runs without a GPU); the three device variants need one."""
+    SYMS = {"knn_c": "_ZN13cuda_renderer5knn_cEPKfiS1_iiiPfPi",
+            "knn_cuda_global": "_ZN13cuda_renderer15knn_cuda_globalEPKfiS1_iiiPfPi",
+            "knn_cuda_texture": "_ZN13cuda_renderer16knn_cuda_textureEPKfiS1_iiiPfPi",
+            "knn_cublas": "_ZN13cuda_renderer10knn_cublasEPKfiS1_iiiPfPi"}
+
+    def __init__(self):
+        if not KNN_REF_SO.exists():
+            raise FileNotFoundError(f"{KNN_REF_SO} missing: build with `make -C oracle ref` where /root/reference exists")
+        self.lib = C.CDLL(str(KNN_REF_SO))
+
+    def run(self, which, ref, query, k):
+        fn = getattr(self.lib, self.SYMS[which])
+        fn.restype = C.c_bool
+        r = _c(ref, np.float32)
+        q = _c(query, np.float32)
+        dist = np.zeros((k, q.shape[1]), np.float32)
+        idx = np.zeros((k, q.shape[1]), np.int32)
+        # the reference printf's progress/errors on stdout: keep the test output clean
+        ok = fn(_p(r), C.c_int(r.shape[1]), _p(q), C.c_int(q.shape[1]), C.c_int(r.shape[0]), C.c_int(k), _p(dist), _p(idx))
+        return bool(ok), dist, idx
+
+
 class Reference:
     """The reference's own CUDA kernels (oracle/ref_harness.cu).  Needs a GPU."""
 
