@@ -120,9 +120,9 @@ int perch_set_models(perch_ctx* ctx, const perch_triangle* tris, int64_t n_tris,
 int perch_set_scene(perch_ctx* ctx, const int32_t* source_depth, const uint8_t* source_red,
                     const uint8_t* source_green, const uint8_t* source_blue, const uint8_t* source_mask_label);
 /* @observed_depth_eigen (N x 3 AoS), @observed_color (3 x N SoA), @result_observed_cloud_label (may be NULL),
- * @observed_point_num (renderer.cu:1451-1456).  In 6-DoF mode the nearest-neighbour search is restricted to observed
- * points carrying the pose's label (the reference sorts by label and searches the label's range, renderer.cu:1668-1686;
- * same candidate set, and indices keep referring to the caller's order). */
+ * @observed_point_num (renderer.cu:1451-1456).  In 6-DoF mode the cloud is stably sorted by label like
+ * renderer.cu:1681 (nearest-neighbour indices and their tie-breaks follow the sorted order) and the search is restricted
+ * to observed points carrying the pose's label (the reference searches the label's range, renderer.cu:1668-1686). */
 int perch_set_observed(perch_ctx* ctx, const float* observed_xyz_aos, const uint8_t* observed_color_soa,
                        const int* observed_label, int n_obs);
 
@@ -160,6 +160,18 @@ int perch_memcpy_d2h(perch_ctx* ctx, void* h_dst, const void* d_src, size_t byte
 int perch_synchronize(perch_ctx* ctx);
 /* Measurement hygiene: overwrite a buffer larger than the 126 MB L2 on the context's stream (between timed steps). */
 int perch_l2_flush(perch_ctx* ctx);
+
+/* ---- batched GICP refinement ------------------------------------------------------------------------------------- */
+/* The do_icp block of render_cuda_multi_unified (renderer.cu:1688-1817) as a call of its own: every pose is rendered
+ * on the stride lattice, its cloud is registered against the observed cloud (restricted to pose_segmentation_label in
+ * 6-DoF) by Generalized-ICP, and out_poses16 receives T * pose (x100-scaled like the inputs, renderer.cu:1412-1429).
+ * Optional outputs: out_transforms12 = T per pose (R row-major, then t; metres), out_iterations, out_error (sum of
+ * r^T M r at the last linearisation).  params: stride, sensor_resolution (grid pitch only), occlusion_threshold, icp_*.
+ * perch_render_cost with params->do_icp = 1 runs the same refinement and then clouds / costs the ADJUSTED poses.
+ * fast_gicp, which the reference calls here, is not part of the reference tree and unpinned: see DESIGN.md 5. */
+int perch_gicp(perch_ctx* ctx, const float* poses16, int n_poses, const int* pose_model_map,
+               const int* pose_segmentation_label, const perch_params* params, float* out_poses16,
+               float* out_transforms12, int* out_iterations, float* out_error);
 
 /* ---- k nearest neighbours (package API of cuda_renderer/knncuda.h) ------------------------------------------ */
 /* Replaces knn_cuda_global / knn_cuda_texture / knn_cublas (knncuda.h:33-100, knncuda.cu:276-421, 424-616, 618-838):

@@ -508,3 +508,171 @@ int oracle_knn(const float* ref, int ref_nb, const float* query, int query_nb, i
     free(index);
     return 0;
 }
+
+/* =====================================================================================================================
+ * Generalized-ICP of one source cloud onto a target cloud -- the per-pose work of the reference's do_icp block
+ * (renderer.cu:1688-1817: fast_gicp::FastGICPCudaCore with k_correspondences 10, <= 150 iterations, rotation epsilon
+ * 2e-3, translation epsilon 5e-4).  PARITY UNPINNED: fast_gicp is not in the reference tree and has no pinned version;
+ * this is a double-precision restatement of the published algorithm (Segal et al. 2009; Koide et al. 2021), the
+ * yardstick for perception_b200/csrc/gicp.cu (tolerance 0.1 mm / 0.01 deg, SURVEY.md 8c class 4):
+ *   covariances: k nearest neighbours within the own cloud (self included), regularised to eigenvalues (1,1,1e-3)
+ *                => C = I - (1 - 1e-3) n n^T, n = direction of least variance (n = 0 when fewer than 3 neighbours);
+ *   iteration:   nearest target point (same label only, if labels are given) of every transformed source point, float
+ *                distance fma(dz,dz,fma(dy,dy,dx*dx)), lowest index on ties; M = (C_B + R C_A R^T)^-1;
+ *                r = b - (R a + t); J = [skew(R a + t), -I]; delta = -(sum J^T M J)^-1 sum J^T M r; T <- exp(delta) T;
+ *   stop:        all |exp(delta).R - I| < rotation_epsilon and all |exp(delta).t| < translation_epsilon.
+ * out_T12 = R row-major (9) then t (3), metres.  Returns the number of linearisations performed.
+ */
+static void jacobi_smallest(double a00, double a01, double a02, double a11, double a12, double a22, double n[3]) {
+    double A[3][3] = {{a00, a01, a02}, {a01, a11, a12}, {a02, a12, a22}};
+    double V[3][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
+    for (int sweep = 0; sweep < 12; ++sweep)
+        for (int p = 0; p < 2; ++p)
+            for (int q = p + 1; q < 3; ++q) {
+                const double apq = A[p][q];
+                if (apq == 0) continue;
+                const double theta = (A[q][q] - A[p][p]) / (2 * apq);
+                const double sgn = theta >= 0 ? 1 : -1;
+                const double t = sgn / (sgn * theta + sqrt(theta * theta + 1));
+                const double c = 1 / sqrt(t * t + 1), s = t * c;
+                for (int k = 0; k < 3; ++k) { const double x = A[k][p], y = A[k][q]; A[k][p] = c * x - s * y; A[k][q] = s * x + c * y; }
+                for (int k = 0; k < 3; ++k) { const double x = A[p][k], y = A[q][k]; A[p][k] = c * x - s * y; A[q][k] = s * x + c * y; }
+                for (int k = 0; k < 3; ++k) { const double x = V[k][p], y = V[k][q]; V[k][p] = c * x - s * y; V[k][q] = s * x + c * y; }
+            }
+    int m = 0;
+    if (A[1][1] < A[m][m]) m = 1;
+    if (A[2][2] < A[m][m]) m = 2;
+    n[0] = V[0][m]; n[1] = V[1][m]; n[2] = V[2][m];
+}
+
+/* normals[3*i..] of every point of a cloud from its k nearest neighbours (self included) */
+void oracle_cloud_normals(const float* aos, int n, int k, double* normals) {
+    float* bd = (float*)malloc(sizeof(float) * (size_t)(k > 0 ? k : 1));
+    int* bi = (int*)malloc(sizeof(int) * (size_t)(k > 0 ? k : 1));
+    for (int i = 0; i < n; ++i) {
+        int cnt = 0;
+        for (int j = 0; j < n; ++j) {
+            const float dx = aos[3 * (size_t)i] - aos[3 * (size_t)j], dy = aos[3 * (size_t)i + 1] - aos[3 * (size_t)j + 1],
+                        dz = aos[3 * (size_t)i + 2] - aos[3 * (size_t)j + 2];
+            const float d = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+            if (cnt == k && d >= bd[k - 1]) continue;
+            int pos = cnt < k ? cnt++ : k - 1;
+            while (pos > 0 && bd[pos - 1] > d) { bd[pos] = bd[pos - 1]; bi[pos] = bi[pos - 1]; --pos; }
+            bd[pos] = d; bi[pos] = j;
+        }
+        double* nn = normals + 3 * (size_t)i;
+        nn[0] = nn[1] = nn[2] = 0;
+        if (cnt < 3) continue;
+        double m[3] = {0, 0, 0};
+        for (int j = 0; j < cnt; ++j) for (int a = 0; a < 3; ++a) m[a] += aos[3 * (size_t)bi[j] + a];
+        for (int a = 0; a < 3; ++a) m[a] /= cnt;
+        double c[6] = {0, 0, 0, 0, 0, 0};
+        for (int j = 0; j < cnt; ++j) {
+            const double x = aos[3 * (size_t)bi[j]] - m[0], y = aos[3 * (size_t)bi[j] + 1] - m[1], z = aos[3 * (size_t)bi[j] + 2] - m[2];
+            c[0] += x * x; c[1] += x * y; c[2] += x * z; c[3] += y * y; c[4] += y * z; c[5] += z * z;
+        }
+        jacobi_smallest(c[0] / cnt, c[1] / cnt, c[2] / cnt, c[3] / cnt, c[4] / cnt, c[5] / cnt, nn);
+    }
+    free(bd);
+    free(bi);
+}
+
+static int chol_solve6(const double H[36], const double g[6], double x[6]) {
+    double L[6][6];
+    for (int i = 0; i < 6; ++i)
+        for (int j = 0; j <= i; ++j) {
+            double s = H[i * 6 + j];
+            for (int k = 0; k < j; ++k) s -= L[i][k] * L[j][k];
+            if (i == j) { if (!(s > 1e-300)) return 0; L[i][i] = sqrt(s); } else L[i][j] = s / L[j][j];
+        }
+    double y[6];
+    for (int i = 0; i < 6; ++i) { double s = -g[i]; for (int k = 0; k < i; ++k) s -= L[i][k] * y[k]; y[i] = s / L[i][i]; }
+    for (int i = 5; i >= 0; --i) { double s = y[i]; for (int k = i + 1; k < 6; ++k) s -= L[k][i] * x[k]; x[i] = s / L[i][i]; }
+    return 1;
+}
+
+static void se3_exp_d(const double d[6], double R[9], double t[3]) {
+    const double wx = d[0], wy = d[1], wz = d[2], th2 = wx * wx + wy * wy + wz * wz, th = sqrt(th2);
+    double A, B, C;
+    if (th < 1e-6) { A = 1 - th2 / 6; B = 0.5 - th2 / 24; C = 1.0 / 6 - th2 / 120; }
+    else { A = sin(th) / th; B = (1 - cos(th)) / th2; C = (th - sin(th)) / (th2 * th); }
+    const double K[9] = {0, -wz, wy, wz, 0, -wx, -wy, wx, 0};
+    double K2[9];
+    for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) K2[i * 3 + j] = K[i * 3] * K[j] + K[i * 3 + 1] * K[3 + j] + K[i * 3 + 2] * K[6 + j];
+    double V[9];
+    for (int i = 0; i < 9; ++i) { const double I = (i % 4 == 0); R[i] = I + A * K[i] + B * K2[i]; V[i] = I + B * K[i] + C * K2[i]; }
+    for (int i = 0; i < 3; ++i) t[i] = V[i * 3] * d[3] + V[i * 3 + 1] * d[4] + V[i * 3 + 2] * d[5];
+}
+
+int oracle_gicp(const float* src_aos, int n_src, const float* tgt_aos, int n_tgt, const int* tgt_label, int label,
+                int k, int max_iterations, double rotation_epsilon, double translation_epsilon, double* out_T12,
+                double* out_error) {
+    double T[12] = {1, 0, 0, 0, 1, 0, 0, 0, 1, 0, 0, 0};
+    int iters = 0;
+    double err = 0;
+    if (n_src > 0 && n_tgt > 0) {
+        double* na = (double*)malloc(sizeof(double) * 3 * (size_t)n_src);
+        double* nb = (double*)malloc(sizeof(double) * 3 * (size_t)n_tgt);
+        oracle_cloud_normals(src_aos, n_src, k, na);
+        oracle_cloud_normals(tgt_aos, n_tgt, k, nb);
+        const double w = 1.0 - 1e-3;
+        for (int it = 0; it < max_iterations; ++it) {
+            double H[36], g[6];
+            memset(H, 0, sizeof H); memset(g, 0, sizeof g);
+            err = 0;
+            for (int i = 0; i < n_src; ++i) {
+                const double ax = src_aos[3 * (size_t)i], ay = src_aos[3 * (size_t)i + 1], az = src_aos[3 * (size_t)i + 2];
+                const double p[3] = {T[0] * ax + T[1] * ay + T[2] * az + T[9], T[3] * ax + T[4] * ay + T[5] * az + T[10],
+                                     T[6] * ax + T[7] * ay + T[8] * az + T[11]};
+                const float qx = (float)p[0], qy = (float)p[1], qz = (float)p[2];
+                float best = FLT_MAX; int bj = -1;
+                for (int j = 0; j < n_tgt; ++j) {
+                    if (tgt_label && tgt_label[j] != label) continue;
+                    const float dx = qx - tgt_aos[3 * (size_t)j], dy = qy - tgt_aos[3 * (size_t)j + 1], dz = qz - tgt_aos[3 * (size_t)j + 2];
+                    const float d = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+                    if (d < best) { best = d; bj = j; }
+                }
+                if (bj < 0) continue;
+                const double* a0 = na + 3 * (size_t)i;
+                const double ra[3] = {T[0] * a0[0] + T[1] * a0[1] + T[2] * a0[2], T[3] * a0[0] + T[4] * a0[1] + T[5] * a0[2],
+                                      T[6] * a0[0] + T[7] * a0[1] + T[8] * a0[2]};
+                const double* b0 = nb + 3 * (size_t)bj;
+                /* S = C_B + R C_A R^T = 2I - w (ra ra^T + b0 b0^T); M = S^-1 */
+                const double a = 2 - w * (ra[0] * ra[0] + b0[0] * b0[0]), b = -w * (ra[0] * ra[1] + b0[0] * b0[1]),
+                             c = -w * (ra[0] * ra[2] + b0[0] * b0[2]), d = 2 - w * (ra[1] * ra[1] + b0[1] * b0[1]),
+                             e = -w * (ra[1] * ra[2] + b0[1] * b0[2]), f = 2 - w * (ra[2] * ra[2] + b0[2] * b0[2]);
+                const double Aa = d * f - e * e, Bb = c * e - b * f, Cc = b * e - c * d, inv = 1.0 / (a * Aa + b * Bb + c * Cc);
+                const double M[3][3] = {{Aa * inv, Bb * inv, Cc * inv}, {Bb * inv, (a * f - c * c) * inv, (b * c - a * e) * inv},
+                                        {Cc * inv, (b * c - a * e) * inv, (a * d - b * b) * inv}};
+                const double r[3] = {tgt_aos[3 * (size_t)bj] - p[0], tgt_aos[3 * (size_t)bj + 1] - p[1], tgt_aos[3 * (size_t)bj + 2] - p[2]};
+                const double J[6][3] = {{0, p[2], -p[1]}, {-p[2], 0, p[0]}, {p[1], -p[0], 0}, {-1, 0, 0}, {0, -1, 0}, {0, 0, -1}};
+                double MJ[6][3];
+                for (int q = 0; q < 6; ++q) for (int x = 0; x < 3; ++x) MJ[q][x] = M[x][0] * J[q][0] + M[x][1] * J[q][1] + M[x][2] * J[q][2];
+                for (int q = 0; q < 6; ++q) {
+                    for (int s = 0; s < 6; ++s) H[q * 6 + s] += J[q][0] * MJ[s][0] + J[q][1] * MJ[s][1] + J[q][2] * MJ[s][2];
+                    g[q] += MJ[q][0] * r[0] + MJ[q][1] * r[1] + MJ[q][2] * r[2];
+                }
+                for (int x = 0; x < 3; ++x) err += r[x] * (M[x][0] * r[0] + M[x][1] * r[1] + M[x][2] * r[2]);
+            }
+            iters = it + 1;
+            double x[6];
+            if (!chol_solve6(H, g, x)) break;
+            double dR[9], dt[3], nT[12];
+            se3_exp_d(x, dR, dt);
+            for (int i = 0; i < 3; ++i) {
+                for (int j = 0; j < 3; ++j) nT[i * 3 + j] = dR[i * 3] * T[j] + dR[i * 3 + 1] * T[3 + j] + dR[i * 3 + 2] * T[6 + j];
+                nT[9 + i] = dR[i * 3] * T[9] + dR[i * 3 + 1] * T[10] + dR[i * 3 + 2] * T[11] + dt[i];
+            }
+            memcpy(T, nT, sizeof T);
+            double mr = 0, mt = 0;
+            for (int i = 0; i < 9; ++i) mr = fmax(mr, fabs(dR[i] - (i % 4 == 0)));
+            for (int i = 0; i < 3; ++i) mt = fmax(mt, fabs(dt[i]));
+            if (mr < rotation_epsilon && mt < translation_epsilon) break;
+        }
+        free(na);
+        free(nb);
+    }
+    memcpy(out_T12, T, sizeof T);
+    if (out_error) *out_error = err;
+    return iters;
+}

@@ -230,6 +230,145 @@ int prepare_cost_args(perch_ctx* c, const perch_params* p, perch::PoseArgs& a, b
     return PERCH_OK;
 }
 
+int ensure_gicp_buffer(perch_ctx* c, size_t bytes) {
+    if (bytes <= c->gicp_bytes) return PERCH_OK;
+    if (c->d_gicp) cudaFree(c->d_gicp);
+    c->d_gicp = nullptr;
+    c->gicp_bytes = 0;
+    CU(cudaMalloc(&c->d_gicp, bytes));
+    c->gicp_bytes = bytes;
+    return PERCH_OK;
+}
+
+// Normals of the observed cloud (target covariances of GICP), cached until the cloud or k changes.
+int prepare_target_normals(perch_ctx* c, int k) {
+    const int n = c->n_obs;
+    if (n == 0 || c->tgt_normals_k == k) return PERCH_OK;
+    int rc;
+    if ((rc = upload(&c->d_obs_xyz_aos, c->h_obs_xyz.data(), 3 * (size_t)n, c->stream))) return rc;
+    if ((rc = upload<float>(&c->d_tgt_normals, nullptr, 3 * (size_t)n, c->stream))) return rc;
+    const int kk = std::min(k, n);
+    std::vector<float> soa(3 * (size_t)n);
+    for (int i = 0; i < n; ++i)
+        for (int a = 0; a < 3; ++a) soa[(size_t)a * n + i] = c->h_obs_xyz[3 * (size_t)i + a];
+    if ((rc = ensure_gicp_buffer(c, Scratch::align(3 * (size_t)n * 4) + 2 * Scratch::align((size_t)kk * n * 4) + 1024))) return rc;
+    char* base = static_cast<char*>(c->d_gicp);
+    float* d_soa = reinterpret_cast<float*>(base);
+    float* d_dist = reinterpret_cast<float*>(base + Scratch::align(3 * (size_t)n * 4));
+    int* d_idx = reinterpret_cast<int*>(base + Scratch::align(3 * (size_t)n * 4) + Scratch::align((size_t)kk * n * 4));
+    CU(cudaMemcpyAsync(d_soa, soa.data(), soa.size() * 4, cudaMemcpyHostToDevice, c->stream));
+    CU(perch::launch_knn(d_soa, n, d_soa, n, 3, kk, d_dist, d_idx, c->sm_count, c->stream));
+    CU(perch::launch_target_normals(c->d_obs_xyz_aos, d_idx, n, kk, c->d_tgt_normals, c->stream));
+    CU(cudaStreamSynchronize(c->stream));  // `soa` goes out of scope
+    c->tgt_normals_k = k;
+    return PERCH_OK;
+}
+
+// The do_icp block (renderer.cu:1688-1817): lattice render of every pose -> compacted clouds -> batched GICP against
+// the observed cloud -> adjusted poses in d_poses_out.  `base` carries the device pose arrays.  Adds to *launches.
+int run_gicp(perch_ctx* c, const perch_params* p, const perch::PoseArgs& base, int n_poses, float* d_poses_out,
+             float* d_transforms, int* d_iterations, float* d_error, int* launches) {
+    if (n_poses <= 0) return PERCH_OK;
+    const int W = c->cam.width, H = c->cam.height, s = p->stride;
+    if (s <= 0 || W % s != 0)
+        return fail(PERCH_ERR_INVALID, "stride %d must divide the image width %d (compute_point_clouds.cuh:271)", s, W);
+    int rc;
+    if (c->grid_res != p->sensor_resolution && (rc = build_grid(c, p->sensor_resolution))) return rc;
+    const int k = p->icp_k_correspondences > 0 ? p->icp_k_correspondences : 10;           // renderer.cu:1697
+    if (k > 32) return fail(PERCH_ERR_CAPACITY, "icp_k_correspondences %d exceeds 32", k);
+    if ((rc = prepare_target_normals(c, k))) return rc;
+    const int Lw = W / s, Lh = (H + s - 1) / s;
+    const size_t P = (size_t)n_poses, lat = (size_t)Lw * Lh;
+    // the lattice depth images and row counts live in the context scratch AFTER the caller's slices: use a private buffer
+    const size_t img_bytes = Scratch::align(P * lat * 4), rows_bytes = Scratch::align((P * Lh + 1) * 4 + 64);
+    if ((rc = ensure_gicp_buffer(c, img_bytes + rows_bytes))) return rc;
+    int32_t* l_depth = reinterpret_cast<int32_t*>(c->d_gicp);
+    int* d_rows = reinterpret_cast<int*>(static_cast<char*>(c->d_gicp) + img_bytes);
+    int* d_max = d_rows + P * Lh + 1;
+    perch::PoseArgs a = base;
+    a.stride = s;
+    a.img_depth = l_depth; a.img_r = nullptr; a.img_g = nullptr; a.img_b = nullptr;
+    a.single_keys = nullptr;
+    a.tile_cap = std::max(env_int("PERCH_IMAGE_TILE_CAP", 12288), Lw);
+    CU(perch::launch_raster_images(a, c->stream));
+    perch::CloudArgs ca;
+    ca.depth = l_depth;
+    ca.pose_label = base.pose_label;
+    ca.img_w = Lw; ca.img_h = Lh; ca.full_h = H; ca.num_images = n_poses; ca.stride = 1; ca.coord_scale = s;
+    ca.cx = c->cam.cx; ca.cy = c->cam.cy; ca.fx = c->cam.fx; ca.fy = c->cam.fy; ca.depth_factor = c->cam.depth_factor;
+    ca.row_counts = d_rows;
+    CU(perch::launch_cloud_count(ca, c->stream));
+    CU(perch::launch_cloud_scan(ca, c->stream));
+    CU(cudaMemsetAsync(d_max, 0, 4, c->stream));
+    CU(perch::launch_pose_count_max(d_rows, Lh, n_poses, d_max, c->stream));
+    int total = 0, max_n = 0;
+    CU(cudaMemcpyAsync(&total, d_rows + P * Lh, 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(&max_n, d_max, 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    *launches += 4;
+    // grow the private buffer for cloud + normals without losing the images/rows: they are re-created if it moves
+    const size_t cloud_bytes = Scratch::align((size_t)std::max(total, 1) * 12);
+    const size_t need = img_bytes + rows_bytes + 2 * cloud_bytes;
+    if (need > c->gicp_bytes) {
+        if ((rc = ensure_gicp_buffer(c, need))) return rc;
+        l_depth = reinterpret_cast<int32_t*>(c->d_gicp);
+        d_rows = reinterpret_cast<int*>(static_cast<char*>(c->d_gicp) + img_bytes);
+        a.img_depth = l_depth;
+        ca.depth = l_depth; ca.row_counts = d_rows;
+        CU(perch::launch_raster_images(a, c->stream));
+        CU(perch::launch_cloud_count(ca, c->stream));
+        CU(perch::launch_cloud_scan(ca, c->stream));
+        *launches += 3;
+    }
+    float* d_cloud = reinterpret_cast<float*>(static_cast<char*>(c->d_gicp) + img_bytes + rows_bytes);
+    float* d_src_normals = reinterpret_cast<float*>(static_cast<char*>(c->d_gicp) + img_bytes + rows_bytes + cloud_bytes);
+    ca.cloud_aos = d_cloud;
+    ca.capacity = total;
+    if (total > 0) {
+        CU(perch::launch_cloud_write(ca, c->stream));
+        ++*launches;
+    }
+    perch::GicpArgs ga;
+    ga.cloud_aos = d_cloud;
+    ga.pose_begin = d_rows;
+    ga.rows_per_pose = Lh;
+    ga.src_normals = d_src_normals;
+    ga.grid = c->grid;
+    ga.grid_h = c->grid.inv_h > 0.f ? 1.0f / c->grid.inv_h : 1.f;
+    ga.tgt_normals = c->d_tgt_normals;
+    ga.pose_label = base.pose_label;
+    ga.poses_in = base.poses;
+    ga.poses_out = reinterpret_cast<perch::Mat4*>(d_poses_out);
+    ga.out_transforms = d_transforms;
+    ga.out_iterations = d_iterations;
+    ga.out_error = d_error;
+    // shared memory for the largest pose cloud (rounded up), capped so that at least two CTAs fit an SM
+    const int cap_pts = (int)std::min<size_t>(((size_t)c->max_smem_optin / 2 - 2048) / 24, 4096);
+    ga.smem_points = std::min(std::max((max_n + 63) & ~63, 64), cap_pts);
+    ga.k_correspondences = k;
+    ga.max_iterations = p->icp_max_iterations > 0 ? p->icp_max_iterations : 150;                     // renderer.cu:1696
+    ga.rotation_epsilon = p->icp_rotation_epsilon >= 0.f ? p->icp_rotation_epsilon : 2e-3f;         // renderer.cu:1698
+    ga.translation_epsilon = p->icp_transformation_epsilon >= 0.f ? p->icp_transformation_epsilon : 5e-4f;  // :1699
+    if (c->n_obs == 0) ga.max_iterations = 0;  // no target: poses pass through unchanged
+    cudaEvent_t e0, e1;
+    CU(cudaEventCreate(&e0));
+    CU(cudaEventCreate(&e1));
+    CU(cudaEventRecord(e0, c->stream));
+    cudaError_t le = perch::launch_gicp(ga, n_poses, c->stream);
+    CU(cudaEventRecord(e1, c->stream));
+    ++*launches;
+    cudaError_t se = cudaEventSynchronize(e1);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    CU(le);
+    CU(se);
+    c->stats.icp_runtime = std::max(c->stats.icp_runtime, ms * 1e-3f);  // seconds, max over calls (renderer.cu:1739)
+    c->last_gicp_ms = ms;
+    return PERCH_OK;
+}
+
 int check_err_flag(perch_ctx* c) {
     int flag = 0;
     CU(cudaMemcpyAsync(&flag, c->d_err_flag, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
@@ -283,7 +422,8 @@ void perch_destroy(perch_ctx* c) {
     void* ptrs[] = {c->d_tri_color, c->d_model_low, c->d_model_high, c->d_model_aabb, c->d_tri_lab, c->d_cl_recs, c->d_cl_bounds,
                     c->d_cl_orig, c->d_cl_low, c->d_cl_high,
                     c->d_src_depth, c->d_src_label, c->d_src_rgb, c->d_grid_pts, c->d_grid_label, c->d_cell_start,
-                    c->d_obs_lab, c->d_obs_rgb, c->d_scratch, c->d_err_flag, c->d_flush};
+                    c->d_obs_lab, c->d_obs_rgb, c->d_scratch, c->d_err_flag, c->d_flush, c->d_obs_xyz_aos,
+                    c->d_tgt_normals, c->d_gicp};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
@@ -478,6 +618,7 @@ int perch_set_observed(perch_ctx* c, const float* xyz_aos, const uint8_t* rgb_so
     }
     CU(cudaStreamSynchronize(c->stream));
     c->grid_res = -1.f;  // grid is (re)built on the next cost call, when sensor_resolution is known
+    c->tgt_normals_k = 0;
     c->have_obs = true;
     note_memory(c);
     return PERCH_OK;
@@ -665,6 +806,48 @@ int perch_l2_flush(perch_ctx* c) {
     return PERCH_OK;
 }
 
+int perch_gicp(perch_ctx* c, const float* poses16, int n_poses, const int* pose_model_map, const int* pose_label,
+               const perch_params* p, float* out_poses16, float* out_transforms12, int* out_iterations, float* out_error) {
+    if (!p) return fail(PERCH_ERR_INVALID, "null params");
+    int rc = check_ready(c, true);
+    if (rc) return rc;
+    if (n_poses < 0 || (n_poses > 0 && (!poses16 || !pose_model_map))) return fail(PERCH_ERR_INVALID, "bad pose arguments");
+    if (n_poses == 0) return PERCH_OK;
+    DeviceGuard g(c->device);
+    const size_t P = (size_t)n_poses;
+    if ((rc = ensure_scratch(c, 2 * Scratch::align(P * 64) + 4 * Scratch::align(P * 4) + Scratch::align(P * 48) + 4096))) return rc;
+    Scratch sc(c);
+    float* d_poses = sc.take<float>(P * 16);
+    float* d_adj = sc.take<float>(P * 16);
+    int* d_pmm = sc.take<int>(P);
+    int* d_plabel = sc.take<int>(P);
+    int* d_it = sc.take<int>(P);
+    float* d_err = sc.take<float>(P);
+    float* d_tf = sc.take<float>(P * 12);
+    CU(cudaMemcpyAsync(d_poses, poses16, P * 64, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(d_pmm, pose_model_map, P * 4, cudaMemcpyHostToDevice, c->stream));
+    if (pose_label) CU(cudaMemcpyAsync(d_plabel, pose_label, P * 4, cudaMemcpyHostToDevice, c->stream));
+    perch::PoseArgs base;
+    fill_pose_args(c, p, base);
+    base.poses = reinterpret_cast<const perch::Mat4*>(d_poses);
+    base.pose_model_map = d_pmm;
+    base.pose_label = pose_label ? d_plabel : nullptr;
+    base.n_poses = n_poses;
+    base.err_flag = c->d_err_flag;
+    int launches = 0;
+    if ((rc = run_gicp(c, p, base, n_poses, d_adj, d_tf, d_it, d_err, &launches))) return rc;
+    if (out_poses16) CU(cudaMemcpyAsync(out_poses16, d_adj, P * 64, cudaMemcpyDeviceToHost, c->stream));
+    if (out_transforms12) CU(cudaMemcpyAsync(out_transforms12, d_tf, P * 48, cudaMemcpyDeviceToHost, c->stream));
+    if (out_iterations) CU(cudaMemcpyAsync(out_iterations, d_it, P * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (out_error) CU(cudaMemcpyAsync(out_error, d_err, P * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->last_ms = c->last_gicp_ms;
+    c->last_launches = launches;
+    c->timing_pending = false;
+    note_memory(c);
+    return check_err_flag(c);
+}
+
 int perch_knn(perch_ctx* c, const float* ref, int ref_nb, const float* query, int query_nb, int dim, int k,
               float* knn_dist, int* knn_index) {
     if (!c) return fail(PERCH_ERR_INVALID, "null context");
@@ -708,7 +891,8 @@ int perch_render_cost(perch_ctx* c, const char* stage, const float* poses16, int
     int rc = check_ready(c, do_cost);
     if (rc) return rc;
     if (n_poses < 0 || (n_poses > 0 && (!poses16 || !pose_model_map))) return fail(PERCH_ERR_INVALID, "bad pose arguments");
-    if (p->do_icp) return fail(PERCH_ERR_INVALID, "do_icp: use perch_gicp_refine + perch_render_cost (see INTEGRATION.md)");
+    if (p->do_icp && p->single_result_image) return fail(PERCH_ERR_INVALID, "do_icp with single_result_image is undefined");
+    if (p->do_icp && !c->have_obs) return fail(PERCH_ERR_INVALID, "do_icp needs perch_set_observed (the GICP target)");
     DeviceGuard g(c->device);
     const int W = c->cam.width, H = c->cam.height;
     const size_t npx = (size_t)W * H;
@@ -723,7 +907,7 @@ int perch_render_cost(perch_ctx* c, const char* stage, const float* poses16, int
     const size_t P = (size_t)n_poses;
     const size_t n_img = p->single_result_image ? 1 : P;
 
-    size_t need = Scratch::align(P * 64) + 2 * Scratch::align(P * 4) + Scratch::align(P * 4) + 2 * Scratch::align(P * 12) + 4096;
+    size_t need = 2 * Scratch::align(P * 64) + 2 * Scratch::align(P * 4) + Scratch::align(P * 4) + 2 * Scratch::align(P * 12) + 4096;
     if (do_images) need += Scratch::align(n_img * npx * 4) + 3 * Scratch::align(n_img * npx) + Scratch::align(npx * 8);
     const size_t lat = (size_t)Lw * Lh;
     if (do_cloud) need += Scratch::align(P * lat * 4) + 3 * Scratch::align(P * lat) + Scratch::align((P * Lh + 1) * 4);
@@ -738,6 +922,7 @@ int perch_render_cost(perch_ctx* c, const char* stage, const float* poses16, int
     float* d_tot = sc.take<float>(P);
     float* d_costs = sc.take<float>(P * 3);
     int32_t* d_counts = sc.take<int32_t>(P * 3);
+    float* d_poses_adj = sc.take<float>(P * 16);
     if (P > 0) {
         CU(cudaMemcpyAsync(d_poses, poses16, P * 64, cudaMemcpyHostToDevice, c->stream));
         CU(cudaMemcpyAsync(d_pmm, pose_model_map, P * 4, cudaMemcpyHostToDevice, c->stream));
@@ -782,6 +967,13 @@ int perch_render_cost(perch_ctx* c, const char* stage, const float* poses16, int
             CU(perch::launch_resolve_single(a, c->stream));
             ++launches;
         }
+    }
+    // ---- GICP refinement (do_icp, renderer.cu:1688-1817): clouds and costs below use the adjusted poses -------------
+    if (p->do_icp && (do_cloud || do_cost) && n_poses > 0) {
+        if ((rc = run_gicp(c, p, base, n_poses, d_poses_adj, nullptr, nullptr, nullptr, &launches))) return rc;
+        base.poses = reinterpret_cast<const perch::Mat4*>(d_poses_adj);
+        if (out->adjusted_poses)
+            CU(cudaMemcpyAsync(out->adjusted_poses, d_poses_adj, P * 64, cudaMemcpyDeviceToHost, c->stream));
     }
     // ---- clouds (stage CLOUD / DEBUG): renderer.cu:1617-1659,1821-1847 ------------------------------------------
     int* d_rows = nullptr;

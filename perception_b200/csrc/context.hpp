@@ -66,6 +66,7 @@ struct perch_ctx {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     float last_ms = 0.f;
+    float last_gicp_ms = 0.f;          // device time of the last GICP kernel
     bool timing_pending = false;
     int* d_err_flag = nullptr;
     int last_launches = 0;
@@ -114,6 +115,12 @@ struct perch_ctx {
     // per-call scratch (grown on demand, never shrunk)
     void* d_scratch = nullptr;
     size_t scratch_bytes = 0;
+    // GICP (gicp.cu): target normals are cached per observed cloud; the work buffer grows on demand
+    float* d_obs_xyz_aos = nullptr;    // label-sorted observed cloud, N x 3
+    float* d_tgt_normals = nullptr;    // N x 3
+    int tgt_normals_k = 0;             // k the cached normals were computed with (0 = stale)
+    void* d_gicp = nullptr;
+    size_t gicp_bytes = 0;
     void* d_flush = nullptr;           // 256 MiB L2-flush target (perch_l2_flush)
     int flush_value = 0;
     void* h_pinned = nullptr;

@@ -1,0 +1,430 @@
+// Batched Generalized-ICP refinement of candidate poses: the `do_icp` block of render_cuda_multi_unified
+// (renderer.cu:1688-1817), which hands every pose's rendered cloud (source) and the observed cloud (target, restricted
+// to the pose's segmentation label in 6-DoF) to fast_gicp::FastGICPCudaCore::optimize_multi with
+// k_correspondences = 10, max 150 iterations, rotation epsilon 2e-3, translation epsilon 5e-4 (renderer.cu:1696-1705),
+// and composes the result with the pose (concatenate_transforms, renderer.cu:1412-1429).
+//
+// fast_gicp is an un-vendored dependency of the reference with no pinned version, so this is a
+// restatement of the published algorithm (Segal et al., "Generalized-ICP"; Koide et al., "Voxelized GICP"), pinned
+// against oracle/perch_oracle.c:oracle_gicp (double precision) rather than against reference outputs:
+//   * covariances from the k nearest neighbours of every point within its own cloud (the point itself included),
+//     regularised to eigenvalues (1, 1, 1e-3) -- i.e. C = I - (1 - 1e-3) n n^T with n the direction of least variance,
+//     so only the normal n is stored (3 floats instead of a 6-float covariance);
+//   * per iteration: exact nearest target point of every transformed source point (no distance gate),
+//     M = (C_B + R C_A R^T)^-1, residual r = b - (R a + t), Jacobian [skew(R a + t), -I] (rotation first),
+//     H = sum J^T M J, g = sum J^T M r, delta = -H^-1 g (Cholesky, double), T <- exp(delta) T;
+//     stop when every |exp(delta).R - I| entry < rotation_epsilon and every |exp(delta).t| entry < translation_epsilon.
+//
+// One CTA per pose: source points and normals live in shared memory for the whole optimisation, nearest neighbours go
+// through the observed-cloud grid (ring expansion, exact), the 27 + 1 sums are reduced in a fixed order (warp shuffles,
+// then one thread over the warps) so results are run-to-run deterministic, and the 6x6 solve stays on the device:
+// no host round trip per iteration (the reference's cuda_icp needs two, icp.cu:156-218).
+#include <cuda_runtime.h>
+
+#include <cfloat>
+
+#include "kernels.cuh"
+
+namespace perch {
+namespace {
+
+constexpr int kGicpThreads = 256;
+constexpr int kGicpWarps = kGicpThreads / 32;
+constexpr int kMaxRings = 12;        // nearest-neighbour shells searched before falling back to a linear scan
+constexpr float kPlaneEps = 1e-3f;  // fast_gicp RegularizationMethod::PLANE: singular values (1, 1, 1e-3)
+
+// Eigenvector of the smallest eigenvalue of the symmetric matrix [a00 a01 a02; a01 a11 a12; a02 a12 a22]
+// (cyclic Jacobi, 6 sweeps).  T = float on the device, double in the oracle's copy of this routine.
+template <class T>
+__host__ __device__ inline void smallest_eigenvector(T a00, T a01, T a02, T a11, T a12, T a22, T n[3]) {
+    T A[3][3] = {{a00, a01, a02}, {a01, a11, a12}, {a02, a12, a22}};
+    T V[3][3] = {{1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
+    for (int sweep = 0; sweep < 6; ++sweep) {
+        for (int p = 0; p < 2; ++p)
+            for (int q = p + 1; q < 3; ++q) {
+                const T apq = A[p][q];
+                if (apq == (T)0) continue;
+                const T theta = (A[q][q] - A[p][p]) / ((T)2 * apq);
+                const T sgn = theta >= (T)0 ? (T)1 : (T)-1;
+                const T t = sgn / (sgn * theta + sqrt(theta * theta + (T)1));
+                const T c = (T)1 / sqrt(t * t + (T)1), s = t * c;
+                for (int k = 0; k < 3; ++k) {  // A <- A J
+                    const T akp = A[k][p], akq = A[k][q];
+                    A[k][p] = c * akp - s * akq;
+                    A[k][q] = s * akp + c * akq;
+                }
+                for (int k = 0; k < 3; ++k) {  // A <- J^T A
+                    const T apk = A[p][k], aqk = A[q][k];
+                    A[p][k] = c * apk - s * aqk;
+                    A[q][k] = s * apk + c * aqk;
+                }
+                for (int k = 0; k < 3; ++k) {
+                    const T vkp = V[k][p], vkq = V[k][q];
+                    V[k][p] = c * vkp - s * vkq;
+                    V[k][q] = s * vkp + c * vkq;
+                }
+            }
+    }
+    int m = 0;
+    if (A[1][1] < A[m][m]) m = 1;
+    if (A[2][2] < A[m][m]) m = 2;
+    n[0] = V[0][m]; n[1] = V[1][m]; n[2] = V[2][m];
+}
+
+// normal of point i from its k nearest neighbours (given as indices into xyz AoS); fewer than 3 neighbours => n = 0
+// (covariance = identity, plain point-to-point weighting)
+__device__ inline void normal_from_neighbours(const float* xyz_aos, const int* nbr, int count, float n[3]) {
+    n[0] = n[1] = n[2] = 0.f;
+    if (count < 3) return;
+    float mx = 0, my = 0, mz = 0;
+    for (int j = 0; j < count; ++j) {
+        const float* p = xyz_aos + 3 * (size_t)nbr[j];
+        mx += p[0]; my += p[1]; mz += p[2];
+    }
+    const float inv = 1.0f / (float)count;
+    mx *= inv; my *= inv; mz *= inv;
+    float c00 = 0, c01 = 0, c02 = 0, c11 = 0, c12 = 0, c22 = 0;
+    for (int j = 0; j < count; ++j) {
+        const float* p = xyz_aos + 3 * (size_t)nbr[j];
+        const float x = p[0] - mx, y = p[1] - my, z = p[2] - mz;
+        c00 += x * x; c01 += x * y; c02 += x * z; c11 += y * y; c12 += y * z; c22 += z * z;
+    }
+    smallest_eigenvector<float>(c00 * inv, c01 * inv, c02 * inv, c11 * inv, c12 * inv, c22 * inv, n);
+}
+
+// ---- target normals: neighbours come from launch_knn (k x N index matrix) -------------------------------------------
+__global__ void target_normals_kernel(const float* xyz_aos, const int* knn_index, int n, int k, float* normals) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int nbr[32];
+    const int kk = min(k, 32);
+    for (int j = 0; j < kk; ++j) nbr[j] = knn_index[(size_t)j * n + i];
+    float nn[3];
+    normal_from_neighbours(xyz_aos, nbr, kk, nn);
+    normals[3 * (size_t)i] = nn[0]; normals[3 * (size_t)i + 1] = nn[1]; normals[3 * (size_t)i + 2] = nn[2];
+}
+
+// Exact nearest observed point (optionally of one label) by ring expansion over the uniform grid: after ring r every
+// unvisited point is at least r*h away, so the search stops once the best squared distance is below (r*h)^2.
+// Same distance arithmetic and tie-break (lowest reference index) as the cost stage (exact_math.cuh:sqdist3).
+__device__ inline void nn_unbounded(const ObsGridDev& g, float h, float qx, float qy, float qz, bool use_label, int label,
+                                    float& best, int& best_ref, float4& best_pt) {
+    best = FLT_MAX;
+    best_ref = -1;
+    const int cx = min(max((int)floorf((qx - g.ox) * g.inv_h), 0), g.dx - 1);
+    const int cy = min(max((int)floorf((qy - g.oy) * g.inv_h), 0), g.dy - 1);
+    const int cz = min(max((int)floorf((qz - g.oz) * g.inv_h), 0), g.dz - 1);
+    const int rmax = max(max(max(cx, g.dx - 1 - cx), max(cy, g.dy - 1 - cy)), max(cz, g.dz - 1 - cz));
+    for (int r = 0; r <= rmax; ++r) {
+        if (r > kMaxRings) {
+            // far from every candidate (outlier pose, or a label with few points): a linear scan of the sorted point
+            // array is cheaper than ever larger mostly-empty shells, and just as exact
+            for (int j = 0; j < g.n_obs; ++j) {
+                if (use_label && __ldg(g.label + j) != label) continue;
+                const float4 p = __ldg(g.pts + j);
+                const float d = sqdist3(qx, qy, qz, p.x, p.y, p.z);
+                const int ref = __float_as_int(p.w);
+                if (d < best || (d == best && ref < best_ref)) { best = d; best_ref = ref; best_pt = p; }
+            }
+            return;
+        }
+        if (best_ref >= 0) {
+            const float lim = (float)(r - 1) * h;  // ring r-1 complete => unvisited points are >= (r-1)*h away ... (*)
+            if (r >= 1 && best < lim * lim * 0.9999f) break;
+        }
+        const int z0 = max(cz - r, 0), z1 = min(cz + r, g.dz - 1);
+        const int y0 = max(cy - r, 0), y1 = min(cy + r, g.dy - 1);
+        for (int z = z0; z <= z1; ++z) {
+            const bool zface = (z == cz - r) || (z == cz + r);
+            for (int y = y0; y <= y1; ++y) {
+                const bool face = zface || (y == cy - r) || (y == cy + r);
+                const int row = (z * g.dy + y) * g.dx;
+                // on a face of the ring cube the whole x-run belongs to the ring, otherwise only its two end cells
+                for (int part = 0; part < 2; ++part) {
+                    int xa, xb;
+                    if (face) { if (part) break; xa = max(cx - r, 0); xb = min(cx + r, g.dx - 1); }
+                    else {
+                        if (r == 0) break;
+                        xa = xb = part ? cx + r : cx - r;
+                        if (xa < 0 || xa > g.dx - 1) continue;
+                    }
+                    const uint32_t b = __ldg(g.cell_start + row + xa), e = __ldg(g.cell_start + row + xb + 1);
+                    for (uint32_t j = b; j < e; ++j) {
+                        if (use_label && __ldg(g.label + j) != label) continue;
+                        const float4 p = __ldg(g.pts + j);
+                        const float d = sqdist3(qx, qy, qz, p.x, p.y, p.z);
+                        const int ref = __float_as_int(p.w);
+                        if (d < best || (d == best && ref < best_ref)) { best = d; best_ref = ref; best_pt = p; }
+                    }
+                }
+            }
+        }
+    }
+    // (*) a query inside cell c is at least (rho - 1)*h from any point of a cell at Chebyshev distance rho; after rings
+    // 0..r-1 the unvisited cells have rho >= r, hence the bound (r-1)*h used before visiting ring r.
+}
+
+struct Sym3 { float xx, xy, xz, yy, yz, zz; };
+
+// inverse of the symmetric positive definite 2I - w(na na^T + nb nb^T)
+__device__ inline Sym3 inverse_sum_cov(const float na[3], const float nb[3], float w) {
+    const float a = 2.f - w * (na[0] * na[0] + nb[0] * nb[0]);
+    const float b = -w * (na[0] * na[1] + nb[0] * nb[1]);
+    const float c = -w * (na[0] * na[2] + nb[0] * nb[2]);
+    const float d = 2.f - w * (na[1] * na[1] + nb[1] * nb[1]);
+    const float e = -w * (na[1] * na[2] + nb[1] * nb[2]);
+    const float f = 2.f - w * (na[2] * na[2] + nb[2] * nb[2]);
+    const float A = d * f - e * e, B = c * e - b * f, C = b * e - c * d;
+    const float inv = 1.0f / (a * A + b * B + c * C);
+    Sym3 m;
+    m.xx = A * inv; m.xy = B * inv; m.xz = C * inv;
+    m.yy = (a * f - c * c) * inv; m.yz = (b * c - a * e) * inv; m.zz = (a * d - b * b) * inv;
+    return m;
+}
+
+// Solve H x = -g for symmetric positive definite H (6x6, row-major upper part used) by Cholesky in double.
+// Returns false when H is not positive definite (degenerate geometry): caller stops with delta = 0.
+__device__ inline bool solve6(const double* H, const double* g, double* x) {
+    double L[6][6];
+    for (int i = 0; i < 6; ++i)
+        for (int j = 0; j <= i; ++j) {
+            double s = H[i * 6 + j];
+            for (int k = 0; k < j; ++k) s -= L[i][k] * L[j][k];
+            if (i == j) {
+                if (!(s > 1e-300)) return false;
+                L[i][i] = sqrt(s);
+            } else L[i][j] = s / L[j][j];
+        }
+    double y[6];
+    for (int i = 0; i < 6; ++i) {
+        double s = -g[i];
+        for (int k = 0; k < i; ++k) s -= L[i][k] * y[k];
+        y[i] = s / L[i][i];
+    }
+    for (int i = 5; i >= 0; --i) {
+        double s = y[i];
+        for (int k = i + 1; k < 6; ++k) s -= L[k][i] * x[k];
+        x[i] = s / L[i][i];
+    }
+    return true;
+}
+
+// exp of the twist (omega, v): R = exp([omega]x), t = V v
+__device__ inline void se3_exp(const double* d, double R[9], double t[3]) {
+    const double wx = d[0], wy = d[1], wz = d[2];
+    const double th2 = wx * wx + wy * wy + wz * wz, th = sqrt(th2);
+    double A, B, Cc;  // sin(th)/th, (1-cos th)/th^2, (th - sin th)/th^3
+    if (th < 1e-6) { A = 1.0 - th2 / 6.0; B = 0.5 - th2 / 24.0; Cc = 1.0 / 6.0 - th2 / 120.0; }
+    else { A = sin(th) / th; B = (1.0 - cos(th)) / th2; Cc = (th - sin(th)) / (th2 * th); }
+    const double K[9] = {0, -wz, wy, wz, 0, -wx, -wy, wx, 0};
+    double K2[9];
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) K2[i * 3 + j] = K[i * 3] * K[j] + K[i * 3 + 1] * K[3 + j] + K[i * 3 + 2] * K[6 + j];
+    double V[9];
+    for (int i = 0; i < 9; ++i) {
+        const double I = (i % 4 == 0) ? 1.0 : 0.0;
+        R[i] = I + A * K[i] + B * K2[i];
+        V[i] = I + B * K[i] + Cc * K2[i];
+    }
+    for (int i = 0; i < 3; ++i) t[i] = V[i * 3] * d[3] + V[i * 3 + 1] * d[4] + V[i * 3 + 2] * d[5];
+}
+
+__global__ void pose_count_max_kernel(const int* pose_begin, int rows_per_pose, int n_poses, int* out) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    int n = 0;
+    if (p < n_poses) n = pose_begin[(size_t)(p + 1) * rows_per_pose] - pose_begin[(size_t)p * rows_per_pose];
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) n = max(n, __shfl_xor_sync(0xffffffffu, n, o));
+    if ((threadIdx.x & 31) == 0 && n > 0) atomicMax(out, n);
+}
+
+__global__ void __launch_bounds__(kGicpThreads) gicp_kernel(GicpArgs a) {
+    extern __shared__ __align__(16) unsigned char gicp_smem[];
+    float* s_pts = reinterpret_cast<float*>(gicp_smem);              // 3 x cap
+    float* s_nrm = s_pts + 3 * (size_t)a.smem_points;                // 3 x cap
+    __shared__ double s_T[12];                                       // R row-major (9) + t (3), metres
+    __shared__ float s_part[kGicpWarps][28];
+    __shared__ int s_state;                                          // 0 = iterate, 1 = converged / stop
+    __shared__ int s_iters;
+
+    const int pose_i = blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int begin = a.pose_begin[(size_t)pose_i * a.rows_per_pose];
+    const int end = a.pose_begin[(size_t)(pose_i + 1) * a.rows_per_pose];
+    const int n = end - begin;
+    const bool in_smem = n <= a.smem_points;
+    const float* g_pts = a.cloud_aos + 3 * (size_t)begin;
+    float* g_nrm = a.src_normals + 3 * (size_t)begin;
+    const float* pts = in_smem ? s_pts : g_pts;
+    float* nrm = in_smem ? s_nrm : g_nrm;
+    const bool use_label = a.pose_label != nullptr;
+    const int label = use_label ? a.pose_label[pose_i] : 0;
+
+    if (tid < 12) s_T[tid] = (tid == 0 || tid == 4 || tid == 8) ? 1.0 : 0.0;
+    if (tid == 0) { s_state = (n == 0) ? 1 : 0; s_iters = 0; }
+    if (in_smem)
+        for (int i = tid; i < 3 * n; i += kGicpThreads) s_pts[i] = g_pts[i];
+    __syncthreads();
+
+    // ---- source normals: k nearest neighbours within the pose's own cloud (brute force, point itself included) -----
+    const int k = min(a.k_correspondences, 32);
+    for (int i = tid; i < n; i += kGicpThreads) {
+        float bd[32];
+        int bi[32];
+        int cnt = 0;
+        const float px = pts[3 * i], py = pts[3 * i + 1], pz = pts[3 * i + 2];
+        for (int j = 0; j < n; ++j) {
+            const float d = sqdist3(px, py, pz, pts[3 * j], pts[3 * j + 1], pts[3 * j + 2]);
+            if (cnt == k && d >= bd[k - 1]) continue;
+            int pos = cnt < k ? cnt++ : k - 1;
+            while (pos > 0 && bd[pos - 1] > d) { bd[pos] = bd[pos - 1]; bi[pos] = bi[pos - 1]; --pos; }
+            bd[pos] = d; bi[pos] = j;
+        }
+        float nn[3];
+        normal_from_neighbours(pts, bi, cnt, nn);
+        nrm[3 * i] = nn[0]; nrm[3 * i + 1] = nn[1]; nrm[3 * i + 2] = nn[2];
+    }
+    __syncthreads();
+
+    const float w = 1.0f - kPlaneEps;
+    for (int it = 0; it < a.max_iterations; ++it) {
+        if (s_state) break;
+        float R[9], t[3];
+#pragma unroll
+        for (int i = 0; i < 9; ++i) R[i] = (float)s_T[i];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) t[i] = (float)s_T[9 + i];
+        float acc[28];
+#pragma unroll
+        for (int i = 0; i < 28; ++i) acc[i] = 0.f;
+        for (int i = tid; i < n; i += kGicpThreads) {
+            const float ax = pts[3 * i], ay = pts[3 * i + 1], az = pts[3 * i + 2];
+            const float px = R[0] * ax + R[1] * ay + R[2] * az + t[0];
+            const float py = R[3] * ax + R[4] * ay + R[5] * az + t[1];
+            const float pz = R[6] * ax + R[7] * ay + R[8] * az + t[2];
+            float best; int ref; float4 b;
+            nn_unbounded(a.grid, a.grid_h, px, py, pz, use_label, label, best, ref, b);
+            if (ref < 0) continue;  // no target point carries this label
+            const float nax = nrm[3 * i], nay = nrm[3 * i + 1], naz = nrm[3 * i + 2];
+            const float na[3] = {R[0] * nax + R[1] * nay + R[2] * naz, R[3] * nax + R[4] * nay + R[5] * naz,
+                                 R[6] * nax + R[7] * nay + R[8] * naz};
+            const float nb[3] = {a.tgt_normals[3 * (size_t)ref], a.tgt_normals[3 * (size_t)ref + 1], a.tgt_normals[3 * (size_t)ref + 2]};
+            const Sym3 M = inverse_sum_cov(na, nb, w);
+            const float rx = b.x - px, ry = b.y - py, rz = b.z - pz;
+            // J = [skew(p), -I]: columns 0..2 = skew(p) columns, 3..5 = -e_x,-e_y,-e_z.  skew(p) = [0 -pz py; pz 0 -px; -py px 0]
+            const float J[6][3] = {{0.f, pz, -py}, {-pz, 0.f, px}, {py, -px, 0.f}, {-1.f, 0.f, 0.f}, {0.f, -1.f, 0.f}, {0.f, 0.f, -1.f}};
+            float MJ[6][3];
+#pragma unroll
+            for (int c = 0; c < 6; ++c) {
+                MJ[c][0] = M.xx * J[c][0] + M.xy * J[c][1] + M.xz * J[c][2];
+                MJ[c][1] = M.xy * J[c][0] + M.yy * J[c][1] + M.yz * J[c][2];
+                MJ[c][2] = M.xz * J[c][0] + M.yz * J[c][1] + M.zz * J[c][2];
+            }
+            int o = 0;
+#pragma unroll
+            for (int r2 = 0; r2 < 6; ++r2)
+#pragma unroll
+                for (int c = r2; c < 6; ++c) acc[o++] += J[r2][0] * MJ[c][0] + J[r2][1] * MJ[c][1] + J[r2][2] * MJ[c][2];
+#pragma unroll
+            for (int c = 0; c < 6; ++c) acc[21 + c] += MJ[c][0] * rx + MJ[c][1] * ry + MJ[c][2] * rz;
+            acc[27] += rx * (M.xx * rx + M.xy * ry + M.xz * rz) + ry * (M.xy * rx + M.yy * ry + M.yz * rz) +
+                       rz * (M.xz * rx + M.yz * ry + M.zz * rz);
+        }
+#pragma unroll
+        for (int i = 0; i < 28; ++i) {
+            float v = acc[i];
+#pragma unroll
+            for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if (lane == 0) s_part[warp][i] = v;
+        }
+        __syncthreads();
+        if (tid == 0) {
+            double H[36], g[6], x[6];
+            int o = 0;
+            for (int r2 = 0; r2 < 6; ++r2)
+                for (int c = r2; c < 6; ++c) {
+                    double s = 0;
+                    for (int wv = 0; wv < kGicpWarps; ++wv) s += (double)s_part[wv][o];
+                    H[r2 * 6 + c] = s; H[c * 6 + r2] = s;
+                    ++o;
+                }
+            for (int c = 0; c < 6; ++c) {
+                double s = 0;
+                for (int wv = 0; wv < kGicpWarps; ++wv) s += (double)s_part[wv][21 + c];
+                g[c] = s;
+            }
+            double err = 0;
+            for (int wv = 0; wv < kGicpWarps; ++wv) err += (double)s_part[wv][27];
+            s_iters = it + 1;
+            if (!solve6(H, g, x)) s_state = 1;
+            else {
+                double dR[9], dt[3];
+                se3_exp(x, dR, dt);
+                double nT[12];
+                for (int i = 0; i < 3; ++i) {
+                    for (int j = 0; j < 3; ++j)
+                        nT[i * 3 + j] = dR[i * 3] * s_T[j] + dR[i * 3 + 1] * s_T[3 + j] + dR[i * 3 + 2] * s_T[6 + j];
+                    nT[9 + i] = dR[i * 3] * s_T[9] + dR[i * 3 + 1] * s_T[10] + dR[i * 3 + 2] * s_T[11] + dt[i];
+                }
+                for (int i = 0; i < 12; ++i) s_T[i] = nT[i];
+                double mr = 0, mt = 0;
+                for (int i = 0; i < 9; ++i) mr = fmax(mr, fabs(dR[i] - ((i % 4 == 0) ? 1.0 : 0.0)));
+                for (int i = 0; i < 3; ++i) mt = fmax(mt, fabs(dt[i]));
+                if (mr < (double)a.rotation_epsilon && mt < (double)a.translation_epsilon) s_state = 1;
+            }
+            if (a.out_error) a.out_error[pose_i] = (float)err;
+        }
+        __syncthreads();
+    }
+
+    // ---- outputs: transform (metres) and the adjusted pose (x100, renderer.cu:1412-1429) ---------------------------
+    if (tid == 0) {
+        if (a.out_transforms)
+            for (int i = 0; i < 12; ++i) a.out_transforms[12 * (size_t)pose_i + i] = (float)s_T[i];
+        if (a.out_iterations) a.out_iterations[pose_i] = s_iters;
+        if (n == 0 && a.out_error) a.out_error[pose_i] = 0.f;
+        // pose' = T * to_eigen(pose, 100), re-scaled by 100: float arithmetic like the reference's Matrix4f product
+        const float* P = reinterpret_cast<const float*>(a.poses_in + pose_i);
+        float* O = reinterpret_cast<float*>(a.poses_out + pose_i);
+        float A[12];
+        for (int i = 0; i < 12; ++i) A[i] = P[i] / 100.f;  // rows a, b, c of the mat4x4 (model.h:108-127)
+        float Tf[12];
+        for (int i = 0; i < 12; ++i) Tf[i] = (float)s_T[i];
+        for (int r2 = 0; r2 < 3; ++r2) {
+            for (int c = 0; c < 4; ++c) {
+                float v = Tf[r2 * 3] * A[c] + Tf[r2 * 3 + 1] * A[4 + c] + Tf[r2 * 3 + 2] * A[8 + c];
+                if (c == 3) v += Tf[9 + r2];
+                O[r2 * 4 + c] = (float)((double)v * 100.0);
+            }
+        }
+        O[12] = P[12]; O[13] = P[13]; O[14] = P[14]; O[15] = P[15];
+    }
+}
+
+}  // namespace
+
+cudaError_t launch_target_normals(const float* d_xyz_aos, const int* d_knn_index, int n, int k, float* d_normals,
+                                  cudaStream_t stream) {
+    if (n <= 0) return cudaSuccess;
+    target_normals_kernel<<<(n + 127) / 128, 128, 0, stream>>>(d_xyz_aos, d_knn_index, n, k, d_normals);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_pose_count_max(const int* d_pose_begin, int rows_per_pose, int n_poses, int* d_out, cudaStream_t stream) {
+    if (n_poses <= 0) return cudaSuccess;
+    pose_count_max_kernel<<<(n_poses + 255) / 256, 256, 0, stream>>>(d_pose_begin, rows_per_pose, n_poses, d_out);
+    return cudaGetLastError();
+}
+
+size_t gicp_smem_bytes(int smem_points) { return (size_t)smem_points * 6 * sizeof(float); }
+
+cudaError_t launch_gicp(const GicpArgs& a, int n_poses, cudaStream_t stream) {
+    if (n_poses <= 0) return cudaSuccess;
+    const size_t smem = gicp_smem_bytes(a.smem_points);
+    cudaError_t err = cudaFuncSetAttribute(gicp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (err != cudaSuccess) return err;
+    gicp_kernel<<<n_poses, kGicpThreads, smem, stream>>>(a);
+    return cudaGetLastError();
+}
+
+}  // namespace perch

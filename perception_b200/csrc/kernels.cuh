@@ -91,4 +91,33 @@ cudaError_t launch_rgb2lab_packed(const uint32_t* packed_rgb, int n, float* lab,
 cudaError_t launch_knn(const float* d_ref, int ref_nb, const float* d_query, int query_nb, int dim, int k, float* d_dist,
                        int* d_index, int sm_count, cudaStream_t stream);
 
+// ---- batched GICP refinement (gicp.cu) ---------------------------------------------------------------------------------
+struct GicpArgs {
+    const float* cloud_aos = nullptr;    // rendered clouds of all poses, N x 3 (metres, camera frame), pose-major
+    const int* pose_begin = nullptr;     // exclusive scan of per-lattice-row point counts (cloud.cu): pose p owns
+    int rows_per_pose = 1;               //   points [pose_begin[p*rows_per_pose], pose_begin[(p+1)*rows_per_pose])
+    float* src_normals = nullptr;        // N x 3 scratch (used when a pose's cloud exceeds smem_points)
+    ObsGridDev grid;                     // observed cloud (target)
+    float grid_h = 0.f;                  // cell size of `grid`
+    const float* tgt_normals = nullptr;  // n_obs x 3, indexed like the grid's reference indices
+    const int* pose_label = nullptr;     // null => target unrestricted
+    const Mat4* poses_in = nullptr;
+    Mat4* poses_out = nullptr;           // T * pose, x100-scaled like the inputs (renderer.cu:1412-1429)
+    float* out_transforms = nullptr;     // P x 12 (R row-major, t) in metres, or null
+    int* out_iterations = nullptr;       // or null
+    float* out_error = nullptr;          // sum r^T M r of the last linearisation, or null
+    int smem_points = 0;                 // source points (and normals) a CTA keeps in shared memory
+    int k_correspondences = 10;          // renderer.cu:1697
+    int max_iterations = 150;            // renderer.cu:1696
+    float rotation_epsilon = 2e-3f;      // renderer.cu:1698
+    float translation_epsilon = 5e-4f;   // renderer.cu:1699
+};
+size_t gicp_smem_bytes(int smem_points);
+cudaError_t launch_gicp(const GicpArgs& a, int n_poses, cudaStream_t stream);
+// normals (direction of least variance of the k nearest neighbours, launch_knn's k x n index matrix) of a cloud
+cudaError_t launch_target_normals(const float* d_xyz_aos, const int* d_knn_index, int n, int k, float* d_normals,
+                                  cudaStream_t stream);
+// max over poses of the per-pose point count (pose_begin as above) -> *d_out (must be zeroed)
+cudaError_t launch_pose_count_max(const int* d_pose_begin, int rows_per_pose, int n_poses, int* d_out, cudaStream_t stream);
+
 }  // namespace perch

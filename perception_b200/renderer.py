@@ -159,13 +159,16 @@ class Renderer:
                                   pose_observed_points_total=None, *, stride=1, cost_type=0,
                                   calculate_observed_cost=True, sensor_resolution=0.01, color_distance_threshold=20.0,
                                   occlusion_threshold=1.0, single_result_image=0, do_icp=False,
-                                  cloud_capacity: Optional[int] = None, want_dc_index=False):
+                                  cloud_capacity: Optional[int] = None, want_dc_index=False, icp_max_iterations=0,
+                                  icp_k_correspondences=0, icp_rotation_epsilon=-1.0, icp_transformation_epsilon=-1.0):
         """cuda_renderer::render_cuda_multi_unified (renderer.h:221-268) against the resident models / scene.
 
         stage: "RENDER" | "CLOUD" | "COST" | "DEBUG".  poses: (P,4,4) float32 mat4x4 (x100 scaled).  Returns a dict
         keyed like the reference's output arguments (result_depth, result_color, result_cloud, result_cloud_color,
         result_cloud_point_num, result_cloud_pose_map, rendered_cost, observed_cost, points_diff_cost) plus `counts`
-        (3,P) int32 = rendered points, unexplained rendered points, explained observed points."""
+        (3,P) int32 = rendered points, unexplained rendered points, explained observed points.  With do_icp the poses
+        are first refined by batched GICP (renderer.cu:1688-1817); clouds and costs then refer to `adjusted_poses`
+        (P,4,4), which is returned too.  icp_* <= 0 / < 0 select the reference's hard-coded values."""
         P4 = _c(poses, np.float32).reshape(-1, 16)
         P = len(P4)
         pmm = _c(pose_model_map, np.int32).reshape(-1)
@@ -176,9 +179,13 @@ class Renderer:
             assert len(plab) == P
         ptot = None if pose_observed_points_total is None else _c(pose_observed_points_total, np.float32).reshape(-1)
         prm = perch_params(stride, cost_type, int(bool(calculate_observed_cost)), sensor_resolution, color_distance_threshold,
-                           occlusion_threshold, int(single_result_image), int(bool(do_icp)), 0, 0, -1.0, -1.0)
+                           occlusion_threshold, int(single_result_image), int(bool(do_icp)), int(icp_max_iterations),
+                           int(icp_k_correspondences), float(icp_rotation_epsilon), float(icp_transformation_epsilon))
         out = perch_outputs()
         res = {}
+        if do_icp:
+            res["adjusted_poses"] = P4.reshape(-1, 4, 4).copy()
+            out.adjusted_poses = res["adjusted_poses"].ctypes.data
         W, H = self.width, self.height
         st = stage
         images = st in ("RENDER", "DEBUG")
@@ -220,6 +227,27 @@ class Renderer:
             res["result_cloud_color"] = ccol[:, :n].copy()
             res["result_cloud_pose_map"] = cmap[:n].copy()
         return res
+
+    def gicp(self, poses, pose_model_map, pose_segmentation_label=None, *, stride=1, sensor_resolution=0.01,
+             occlusion_threshold=1.0, icp_max_iterations=0, icp_k_correspondences=0, icp_rotation_epsilon=-1.0,
+             icp_transformation_epsilon=-1.0):
+        """Batched GICP refinement alone (perch_gicp): returns adjusted_poses (P,4,4; x100-scaled), transforms
+        (P,12: R row-major then t, metres), iterations (P,), error (P,)."""
+        P4 = _c(poses, np.float32).reshape(-1, 16)
+        P = len(P4)
+        pmm = _c(pose_model_map, np.int32).reshape(-1)
+        plab = None
+        if pose_segmentation_label is not None and len(pose_segmentation_label) > 0:
+            plab = _c(pose_segmentation_label, np.int32).reshape(-1)
+        prm = perch_params(stride, 0, 0, sensor_resolution, 0.0, occlusion_threshold, 0, 1, int(icp_max_iterations),
+                           int(icp_k_correspondences), float(icp_rotation_epsilon), float(icp_transformation_epsilon))
+        adj = np.zeros((P, 4, 4), np.float32)
+        tf = np.zeros((P, 12), np.float32)
+        it = np.zeros(P, np.int32)
+        err = np.zeros(P, np.float32)
+        self._ck(self._lib.perch_gicp(self._h, _ptr(P4), P, _ptr(pmm), _ptr(plab), C.byref(prm), _ptr(adj), _ptr(tf),
+                                      _ptr(it), _ptr(err)))
+        return {"adjusted_poses": adj, "transforms": tf, "iterations": it, "error": err}
 
     # -- introspection ---------------------------------------------------------------------------------------------
     def last_timing(self):

@@ -131,6 +131,21 @@ class Oracle:
         return dist, idx
 
 
+    def gicp(self, src, tgt, tgt_label=None, label=0, k=10, max_iterations=150, rotation_epsilon=2e-3,
+             translation_epsilon=5e-4):
+        """oracle_gicp (double precision): returns (T12 = R row-major + t, iterations, error)."""
+        s = _c(src, np.float32).reshape(-1, 3)
+        t = _c(tgt, np.float32).reshape(-1, 3)
+        tl = None if tgt_label is None else _c(tgt_label, np.int32)
+        T = np.zeros(12, np.float64)
+        err = C.c_double(0)
+        self.lib.oracle_gicp.restype = C.c_int
+        it = self.lib.oracle_gicp(_p(s), C.c_int(len(s)), _p(t), C.c_int(len(t)), _p(tl), C.c_int(label), C.c_int(k),
+                                  C.c_int(max_iterations), C.c_double(rotation_epsilon), C.c_double(translation_epsilon),
+                                  _p(T), C.byref(err))
+        return T, it, err.value
+
+
 KNN_REF_SO = ROOT / "oracle" / "_ref" / "libknn_ref.so"
 
 
