@@ -273,6 +273,8 @@ def run_ours(args):
             "best": {"cost": int(best["cost"]), "pose_id": int(best["pose_id"])},
             "wall_s_device_loop": wall_device_loop,
         }
+        if world == 1 and not args.no_gicp:
+            line["gicp"] = gicp_leg(r, wl, out, kw)
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(wl, budget_s=args.cpu_budget)
         if world == 1 and not args.no_ref_cuda:
@@ -281,6 +283,33 @@ def run_ours(args):
     if world > 1:
         dist.destroy_process_group()
     return line
+
+
+def gicp_leg(r, wl, out, kw, n_top=4096, iterations=20, reps=3):
+    """SURVEY 8(d) GICP measurement (C4-shaped): the n_top best poses of the scored batch by (rendered + observed) cost,
+    refined by batched GICP with k = 10 and a FIXED number of iterations (epsilons 0 so every iteration runs).
+    Device time of the GICP kernel alone (CUDA events inside the library) and wall time of the whole perch_gicp call
+    (lattice render + clouds + GICP + H2D/D2H)."""
+    P = wl["P"]
+    cost = np.where(out["rendered_cost"] >= 0, out["rendered_cost"] + np.nan_to_num(out["observed_cost"], nan=1e9), 1e9)
+    sel = np.sort(np.argsort(cost, kind="stable")[:min(n_top, P)])
+    poses, pmm = wl["poses"][sel], wl["pmm"][sel]
+    lab = wl["plabel"][sel] if wl["plabel"] is not None else None
+    args = dict(stride=kw["stride"], sensor_resolution=kw["sensor_resolution"], occlusion_threshold=kw["occlusion_threshold"],
+                icp_max_iterations=iterations, icp_k_correspondences=10, icp_rotation_epsilon=0.0, icp_transformation_epsilon=0.0)
+    g = r.gicp(poses, pmm, lab, **args)  # warm-up (target normals are cached after the first call)
+    dev, wall = [], []
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        g = r.gicp(poses, pmm, lab, **args)
+        wall.append(time.perf_counter() - t0)
+        dev.append(r.last_timing()[0])
+    k_ms, w_s = float(np.median(dev)), float(np.median(wall))
+    n = len(sel)
+    return {"refined_poses_per_s": n / w_s, "kernel_poses_per_s": n / (k_ms / 1e3), "poses": n, "iterations": iterations,
+            "kernel_ms": k_ms, "ms_total": w_s * 1e3, "k_correspondences": 10,
+            "mean_iterations_run": float(g["iterations"].mean()), "n_obs": int(wl["n_obs"]),
+            "note": "top poses of the scored batch; fixed iteration count (epsilons 0)"}
 
 
 def _baseline_inputs(wl):
@@ -430,6 +459,7 @@ def main():
     ap.add_argument("--ref-batch", type=int, default=700)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-cuda", action="store_true")
+    ap.add_argument("--no-gicp", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     if args.impl == "reference":

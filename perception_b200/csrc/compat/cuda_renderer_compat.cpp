@@ -99,7 +99,7 @@ void render_cuda_multi_unified(
     bool calculate_observed_cost, float sensor_resolution, float color_distance_threshold, float occlusion_threshold,
     bool do_icp, std::vector<int32_t>& result_depth, std::vector<std::vector<uint8_t>>& result_color,
     float*& result_cloud, uint8_t*& result_cloud_color, int& result_cloud_point_num, int*& result_cloud_pose_map,
-    int*& result_dc_index, std::vector<Model::mat4x4>& /*adjusted_poses*/, float*& rendered_cost, float*& observed_cost,
+    int*& result_dc_index, std::vector<Model::mat4x4>& adjusted_poses, float*& rendered_cost, float*& observed_cost,
     float*& points_diff_cost, gpu_stats& stats) {
     perch_ctx* ctx = context();
     const int P = (int)poses.size();
@@ -166,6 +166,10 @@ void render_cuda_multi_unified(
             out.observed_cost = observed_cost;
             out.points_diff_cost = points_diff_cost;
         }
+    }
+    if (do_icp && (want_cloud || want_cost)) {
+        adjusted_poses.resize(P);  // renderer.cu:1729-1730
+        out.adjusted_poses = reinterpret_cast<float*>(adjusted_poses.data());
     }
     // the stage machine of the C-ABI has the reference's four stage names; composite strings fall back to DEBUG
     const char* st = debug ? "DEBUG" : (stage.compare("RENDER") == 0 ? "RENDER" : (stage.compare("CLOUD") == 0 ? "CLOUD" :
