@@ -220,7 +220,7 @@ int prepare_cost_args(perch_ctx* c, const perch_params* p, perch::PoseArgs& a, b
     a.obs_lab = c->d_obs_lab;
     a.mask_words = (c->n_obs + 31) / 32;
     const int Lw = c->cam.width / p->stride;
-    int cap = env_int("PERCH_COST_TILE_CAP", 4096);
+    int cap = env_int("PERCH_COST_TILE_CAP", 2048);
     a.tile_cap = std::max(cap, Lw);
     size_t smem = perch::pose_kernel_smem_bytes(a, false, color);
     if (smem > (size_t)c->max_smem_optin)
@@ -289,7 +289,7 @@ int run_gicp(perch_ctx* c, const perch_params* p, const perch::PoseArgs& base, i
     a.stride = s;
     a.img_depth = l_depth; a.img_r = nullptr; a.img_g = nullptr; a.img_b = nullptr;
     a.single_keys = nullptr;
-    a.tile_cap = std::max(env_int("PERCH_IMAGE_TILE_CAP", 12288), Lw);
+    a.tile_cap = std::max(env_int("PERCH_IMAGE_TILE_CAP", 6144), Lw);
     CU(perch::launch_raster_images(a, c->stream));
     perch::CloudArgs ca;
     ca.depth = l_depth;
@@ -953,7 +953,7 @@ int perch_render_cost(perch_ctx* c, const char* stage, const float* poses16, int
         perch::PoseArgs a = base;
         a.stride = 1;
         a.img_depth = d_depth; a.img_r = d_r; a.img_g = d_g; a.img_b = d_b;
-        a.tile_cap = std::max(env_int("PERCH_IMAGE_TILE_CAP", 12288), W);
+        a.tile_cap = std::max(env_int("PERCH_IMAGE_TILE_CAP", 6144), W);
         if (p->single_result_image) {
             a.single_keys = d_keys;
             CU(perch::launch_single_clear(d_keys, (int)npx, c->stream));
@@ -993,7 +993,7 @@ int perch_render_cost(perch_ctx* c, const char* stage, const float* poses16, int
         if (out->dc_index) d_dc = sc.take<int>(P * npx);
         perch::PoseArgs a = base;
         a.img_depth = l_depth; a.img_r = l_r; a.img_g = l_g; a.img_b = l_b;
-        a.tile_cap = std::max(env_int("PERCH_IMAGE_TILE_CAP", 12288), Lw);
+        a.tile_cap = std::max(env_int("PERCH_IMAGE_TILE_CAP", 6144), Lw);
         if (n_poses > 0) {
             CU(perch::launch_raster_images(a, c->stream));
             ++launches;

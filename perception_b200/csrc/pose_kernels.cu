@@ -26,9 +26,13 @@ namespace perch {
 
 namespace {
 
-constexpr int kThreads = 256;
+#ifndef PERCH_POSE_THREADS
+#define PERCH_POSE_THREADS 128
+#endif
+constexpr int kThreads = PERCH_POSE_THREADS;
 constexpr int kWarps = kThreads / 32;
-constexpr int kQueueCap = 4096;   // candidate triangles buffered between exact passes
+constexpr int kMinCtas = 1024 / kThreads;  // resident CTAs per SM the register budget is sized for (32 warps)
+constexpr int kQueueCap = 16 * kThreads;   // candidate triangles buffered between exact passes
 constexpr int kClaim = 32;        // clusters tested per warp claim (one per lane)
 constexpr int kPendCap = 64;      // per-warp list of surviving clusters awaiting the per-triangle test
 constexpr int kClaimMaxTris = (kClaim + 8) * 4;  // most candidates one claim can append (incl. carried clusters)
@@ -68,8 +72,17 @@ struct LatticeRect {
 };
 
 // Lattice pixels visited by the reference's bbox loops (image_renderer.cuh:110-111) for this triangle.
+// floor(a / s) for 0 <= a < 2^23 without the integer-division sequence: float estimate, exact correction
+__device__ __forceinline__ int div_floor(int a, int s, float inv_s) {
+    int q = (int)((float)a * inv_s);
+    const int r = a - q * s;
+    if (r < 0) --q;
+    else if (r >= s) ++q;
+    return q;
+}
+
 __device__ __forceinline__ LatticeRect lattice_rect_of(float bminx, float bmaxx, float bminy, float bmaxy, int W, int H,
-                                                       int s) {
+                                                       int s, float inv_s) {
     LatticeRect r{1, 0, 1, 0};
     if (!(bmaxx >= 0.f) || !(bmaxy >= 0.f)) return r;  // also rejects NaN upper bounds (loop condition false)
     unsigned long long p0s = (unsigned long long)__fadd_rn(bminx, 0.5f);  // size_t(bboxmin+0.5f); NaN -> 0
@@ -77,11 +90,11 @@ __device__ __forceinline__ LatticeRect lattice_rect_of(float bminx, float bmaxx,
     if (p0s > (unsigned long long)(W - 1) || p1s > (unsigned long long)(H - 1)) return r;
     int p0e = (int)bmaxx, p1e = (int)bmaxy;  // <= W-1 / H-1 by the clamp
     if ((int)p0s > p0e || (int)p1s > p1e) return r;
-    r.x0 = ((int)p0s + s - 1) / s;
-    r.x1 = p0e / s;
+    r.x0 = div_floor((int)p0s + s - 1, s, inv_s);
+    r.x1 = div_floor(p0e, s, inv_s);
     // raster row P1 is image row H-1-P1 (image_renderer.cuh:128)
-    r.y0 = (H - 1 - p1e + s - 1) / s;
-    r.y1 = (H - 1 - (int)p1s) / s;
+    r.y0 = div_floor(H - 1 - p1e + s - 1, s, inv_s);
+    r.y1 = div_floor(H - 1 - (int)p1s, s, inv_s);
     return r;
 }
 
@@ -168,7 +181,7 @@ __device__ __forceinline__ void nn_query(const ObsGridDev& g, float qx, float qy
 enum { MODE_COST = 0, MODE_IMAGE = 1 };
 
 template <int MODE, bool COLOR>
-__global__ void __launch_bounds__(kThreads, 4) pose_kernel(PoseArgs a) {
+__global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
     using Z = ZCell<COLOR>;
     using zkey = typename Z::type;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -176,7 +189,8 @@ __global__ void __launch_bounds__(kThreads, 4) pose_kernel(PoseArgs a) {
     const int mask_words = (MODE == MODE_COST) ? a.mask_words : 0;
     uint32_t* mask = reinterpret_cast<uint32_t*>(smem_raw + (size_t)a.tile_cap * sizeof(zkey));
     int* queue = reinterpret_cast<int*>(mask + mask_words);
-    int* wpend = queue + kQueueCap + (threadIdx.x >> 5) * kPendCap;  // per-warp surviving clusters
+    int* wpend = queue + kQueueCap + (threadIdx.x >> 5) * (2 * kPendCap);  // per-warp surviving clusters
+    int* wstage = wpend + kPendCap;                                          // per-warp staged candidate triangles
 
     __shared__ Mat4 s_pose;
     __shared__ int s_rect[4];
@@ -301,7 +315,7 @@ __global__ void __launch_bounds__(kThreads, 4) pose_kernel(PoseArgs a) {
                 ScreenVertex C = transform_vertex(s_pose, a.cam.proj, wf, hf, v[6], v[7], v[8]);
                 float bminx, bmaxx, bminy, bmaxy;
                 bbox_of(A, B, C, cmaxx, cmaxy, bminx, bmaxx, bminy, bmaxy);
-                LatticeRect r = lattice_rect_of(bminx, bmaxx, bminy, bmaxy, W, H, s);
+                LatticeRect r = lattice_rect_of(bminx, bmaxx, bminy, bmaxy, W, H, s, inv_s);
                 if (r.x0 > r.x1 || r.y0 > r.y1) return false;
                 if (r.x0 < rx0 || r.x1 > rx1 || r.y0 < ry0 || r.y1 > ry1) atomicOr(a.err_flag, 1);
                 int x0 = max(r.x0, rx0), x1 = min(r.x1, rx1), y0 = max(r.y0, by0), y1 = min(r.y1, by1);
@@ -311,12 +325,20 @@ __global__ void __launch_bounds__(kThreads, 4) pose_kernel(PoseArgs a) {
                 TriSetup ts;
                 setup_edges(A, B, C, ts);
                 const uint32_t id = COLOR ? (uint32_t)__ldg(a.models.cl_orig + t) : 0u;  // original triangle index
-                const int first = coop ? tid : 0, step = coop ? kThreads : 1;
-                for (int c = first; c < cells; c += step) {
-                    int ly = y0 + c / w, lx = x0 + c % w;
-                    int32_t d;
-                    if (fragment_depth(ts, (float)(lx * s), (float)(H - 1 - ly * s), d))
-                        atomicMin(&zbuf[(ly - by0) * tile_w + (lx - rx0)], Z::make(d, id));
+                if (coop) {
+                    for (int c = tid; c < cells; c += kThreads) {
+                        int ly = y0 + c / w, lx = x0 + c % w;
+                        int32_t d;
+                        if (fragment_depth(ts, (float)(lx * s), (float)(H - 1 - ly * s), d))
+                            atomicMin(&zbuf[(ly - by0) * tile_w + (lx - rx0)], Z::make(d, id));
+                    }
+                } else {
+                    for (int ly = y0; ly <= y1; ++ly)
+                        for (int lx = x0; lx <= x1; ++lx) {
+                            int32_t d;
+                            if (fragment_depth(ts, (float)(lx * s), (float)(H - 1 - ly * s), d))
+                                atomicMin(&zbuf[(ly - by0) * tile_w + (lx - rx0)], Z::make(d, id));
+                        }
                 }
                 return false;
             };
@@ -372,6 +394,8 @@ __global__ void __launch_bounds__(kThreads, 4) pose_kernel(PoseArgs a) {
                                    fminf(fminf(uy[0], uy[1]), uy[2]), fmaxf(fmaxf(uy[0], uy[1]), uy[2]));
             };
             // per-triangle test of 8 pending clusters (4 lanes each); candidates go to the shared queue
+            int nstage = 0;  // warp-uniform: staged candidates of this warp
+            const unsigned lt_mask = (1u << lane) - 1u;
             auto test_pending = [&](int first, int count) {
                 const int e = lane >> 2;
                 bool hit = false;
@@ -380,13 +404,22 @@ __global__ void __launch_bounds__(kThreads, 4) pose_kernel(PoseArgs a) {
                     t = 4 * wpend[first + e] + (lane & 3);
                     hit = tri_hits(t);
                 }
-                unsigned ballot = __ballot_sync(0xffffffffu, hit);
-                if (ballot) {
+                // candidates are staged per warp and moved to the shared queue 32 at a time: one atomic per 32 entries
+                const unsigned ballot = __ballot_sync(0xffffffffu, hit);
+                if (hit) wstage[nstage + __popc(ballot & lt_mask)] = t;
+                nstage += __popc(ballot);
+                if (nstage >= 32) {
+                    __syncwarp();
                     int slot = 0;
-                    if (lane == 0) slot = atomicAdd(&s_qcount, __popc(ballot));
-                    slot = __shfl_sync(0xffffffffu, slot, 0) + __popc(ballot & ((1u << lane) - 1u));
-                    if (hit) queue[slot] = t;
+                    if (lane == 0) slot = atomicAdd(&s_qcount, 32);
+                    slot = __shfl_sync(0xffffffffu, slot, 0);
+                    queue[slot + lane] = wstage[lane];
+                    nstage -= 32;
+                    const int carry = (lane < nstage) ? wstage[32 + lane] : 0;
+                    __syncwarp();
+                    if (lane < nstage) wstage[lane] = carry;
                 }
+                __syncwarp();
             };
 
             // Warps claim groups of kClaim clusters dynamically (no block barrier inside pass A); a warp stops
@@ -398,13 +431,13 @@ __global__ void __launch_bounds__(kThreads, 4) pose_kernel(PoseArgs a) {
                 int npend = 0;  // warp-uniform
                 for (;;) {
                     int g = 0x7fffffff;
-                    if (lane == 0 && *(volatile int*)&s_qcount <= kQueueCap - kWarps * kClaimMaxTris) g = atomicAdd(&s_next, 1);
+                    if (lane == 0 && *(volatile int*)&s_qcount <= kQueueCap - kWarps * (kClaimMaxTris + 32)) g = atomicAdd(&s_next, 1);
                     g = __shfl_sync(0xffffffffu, g, 0);
                     if (g >= n_groups) break;
                     const int c = cl_low + g * kClaim + lane;
                     const bool keep = (c < cl_high) && cluster_hits(c);
                     const unsigned ballot = __ballot_sync(0xffffffffu, keep);
-                    if (keep) wpend[npend + __popc(ballot & ((1u << lane) - 1u))] = c;
+                    if (keep) wpend[npend + __popc(ballot & lt_mask)] = c;
                     npend += __popc(ballot);
                     __syncwarp();
                     while (npend >= 8) {
@@ -414,6 +447,13 @@ __global__ void __launch_bounds__(kThreads, 4) pose_kernel(PoseArgs a) {
                     __syncwarp();
                 }
                 if (npend > 0) test_pending(0, npend);
+                if (nstage > 0) {
+                    int slot = 0;
+                    if (lane == 0) slot = atomicAdd(&s_qcount, nstage);
+                    slot = __shfl_sync(0xffffffffu, slot, 0);
+                    if (lane < nstage) queue[slot + lane] = wstage[lane];
+                    nstage = 0;
+                }
                 __syncthreads();
                 const int qn = s_qcount;
                 const bool all_claimed = *(volatile int*)&s_next >= n_groups;
@@ -574,7 +614,7 @@ __global__ void fill_keys_kernel(unsigned long long* keys, int n) {
 size_t pose_kernel_smem_bytes(const PoseArgs& a, bool image_mode, bool color) {
     size_t b = (size_t)a.tile_cap * ((color || image_mode) ? 8 : 4) + (image_mode ? 0 : (size_t)a.mask_words * 4) +
                (size_t)kQueueCap * 4;
-    return b + (size_t)kWarps * kPendCap * sizeof(int);
+    return b + (size_t)kWarps * 2 * kPendCap * sizeof(int);
 }
 
 template <int MODE, bool COLOR>
