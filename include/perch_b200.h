@@ -173,6 +173,24 @@ int perch_gicp(perch_ctx* ctx, const float* poses16, int n_poses, const int* pos
                const int* pose_segmentation_label, const perch_params* params, float* out_poses16,
                float* out_transforms12, int* out_iterations, float* out_error);
 
+/* ---- point-to-plane ICP against a depth image (package API of cuda_icp) -------------------------------------------- */
+/* Replaces Scene_projective::init_Scene_projective_cuda (depth_scene.h:19-25, depth_scene.cpp:3-37): scene_depth is
+ * width*height int32 in cm (the renderer's depth unit, "depth can be int32, if we use our cuda renderer", icp.h:55), K9
+ * the row-major pinhole matrix.  Builds the per-pixel scene points (dep2pcd, common.h:50-66) and normals (get_normal,
+ * scene/common.cpp:17-107) on the device and keeps them in the context; out_pcd / out_normals (width*height*3 floats,
+ * may be NULL) return them to the host. */
+int perch_icp_set_scene(perch_ctx* ctx, const int32_t* scene_depth, int width, int height, const float K9[9],
+                        float max_dist_diff, float* out_pcd, float* out_normals);
+/* Replaces cuda_icp::ICP_Point2Plane_cuda<Scene_projective> (icp.h:92-99, icp.cu:156-218) for a BATCH of clouds:
+ * model_pcd holds all clouds back to back (x,y,z per point, metres), cloud i = points [cloud_offsets[i],
+ * cloud_offsets[i+1]).  Per cloud: RegistrationResult (icp.h:27-38) = transformation_ (row-major 4x4 into
+ * out_transforms16), fitness_, inlier_rmse_; criteria = ICPConvergenceCriteria (icp.h:40-51; reference defaults 1e-5,
+ * 1e-5, 30).  out_pcd (may be NULL) receives the clouds as the reference leaves model_pcd: transformed in place.
+ * Scene_nn (kd-tree association, pcd_scene.h) is not provided: nearest-neighbour registration is perch_gicp. */
+int perch_icp_point2plane(perch_ctx* ctx, const float* model_pcd, const int* cloud_offsets, int n_clouds,
+                          float relative_fitness, float relative_rmse, int max_iteration, float* out_transforms16,
+                          float* out_fitness, float* out_inlier_rmse, int* out_iterations, float* out_pcd);
+
 /* ---- k nearest neighbours (package API of cuda_renderer/knncuda.h) ------------------------------------------ */
 /* Replaces knn_cuda_global / knn_cuda_texture / knn_cublas (knncuda.h:33-100, knncuda.cu:276-421, 424-616, 618-838):
  * ref is dim x ref_nb and query dim x query_nb, one ROW per dimension (element (d, i) at d*nb + i); outputs are

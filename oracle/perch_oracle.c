@@ -676,3 +676,133 @@ int oracle_gicp(const float* src_aos, int n_src, const float* tgt_aos, int n_tgt
     if (out_error) *out_error = err;
     return iters;
 }
+
+/* =====================================================================================================================
+ * cuda_icp package API: point-to-plane ICP of a model cloud against a depth-image scene (projective association).
+ * Scene preparation: Scene_projective::init_Scene_projective_cpu (cuda_icp/scene/depth_scene/depth_scene.cpp:3-37) =
+ * dep2pcd per pixel (include/cuda_icp/common.h:50-66, depth in cm read as unsigned) + get_normal
+ * (cuda_icp/scene/common.cpp:3-15,17-107: depth saturated to 16 bits, 8 neighbours at radius 5, integer bilateral
+ * accumulation in `long`, thresholds 2000 / 50).  Pinned bit-exact against that host code (oracle/_ref/libicp_ref.so).
+ */
+static long sat16l(int32_t d) { return d < 0 ? 0 : (d > 65535 ? 65535 : d); }
+
+void oracle_icp_scene(const int32_t* depth, int W, int H, const float* K9, float* pcd, float* normals) {
+    const float k00 = K9[0], k02 = K9[2], k11 = K9[4], k12 = K9[5];
+    memset(normals, 0, sizeof(float) * 3 * (size_t)W * H);
+    for (int y = 0; y < H; ++y)
+        for (int x = 0; x < W; ++x) {
+            const size_t i = (size_t)y * W + x;
+            const uint32_t dep = (uint32_t)depth[i];
+            float px = 0, py = 0, pz = 0;
+            if (dep != 0) {
+                pz = dep / 100.0f;
+                px = ((float)(size_t)x - k02) / k00 * pz;
+                py = ((float)(size_t)y - k12) / k11 * pz;
+            }
+            pcd[3 * i] = px; pcd[3 * i + 1] = py; pcd[3 * i + 2] = pz;
+        }
+    const int r = 5;
+    for (int y = r; y < H - r - 1; ++y)
+        for (int x = r; x < W - r - 1; ++x) {
+            const size_t i = (size_t)y * W + x;
+            const long d = sat16l(depth[i]);
+            if (!(d < 2000)) continue;
+            long A0 = 0, A1 = 0, A3 = 0, b0 = 0, b1 = 0;
+            for (int dy = -1; dy <= 1; ++dy)
+                for (int dx = -1; dx <= 1; ++dx) {
+                    if (!dx && !dy) continue;
+                    const long ii = dx * r, jj = dy * r;
+                    const long delta = sat16l(depth[(size_t)(y + dy * r) * W + (x + dx * r)]) - d;
+                    const long f = labs(delta) < 50 ? 1 : 0;
+                    A0 += f * ii * ii; A1 += f * ii * jj; A3 += f * jj * jj; b0 += f * ii * delta; b1 += f * jj * delta;
+                }
+            const long det = A0 * A3 - A1 * A1, ddx = A3 * b0 - A1 * b1, ddy = -A1 * b0 + A0 * b1;
+            float nx = (float)(k00 * ddx), ny = (float)(k11 * ddy), nz = (float)(-det * d);
+            const float len = sqrtf(nx * nx + ny * ny + nz * nz);
+            if (len > 0) {
+                const float inv = 1.0f / len;
+                normals[3 * i] = nx * inv; normals[3 * i + 1] = ny * inv; normals[3 * i + 2] = nz * inv;
+            }
+        }
+}
+
+/*
+ * ICP_Point2Plane_{cpu,cuda}<Scene_projective> (icp.cpp:117-179 / icp.cu:156-218): per iteration the 29 sums of
+ * thrust__pcd2Ab (icp.h:129-210) over the points with a valid projective correspondence (Scene_projective::query,
+ * depth_scene.h:29-50; pcd2dep, common.h:68-78), fitness = count / N, inlier_rmse = sqrt(sum b^2 / count); stop when
+ * both change by less than the criteria, or at the extra turn max_iteration; else solve the 6x6 system in double and
+ * apply R = Rz Ry Rx, t (eigen_slover_666 + TransformVector6dToMatrix4d, icp.cpp:7-36) to the cloud in place.
+ * Sums are accumulated serially in float (the reference's order is unspecified: OpenMP / cub reduction), so agreement
+ * with the reference is to float-accumulation accuracy, not bit for bit.  Returns the index of the last turn.
+ */
+int oracle_icp_point2plane(float* pts, int n, const float* scene_pcd, const float* scene_normals, int W, int H,
+                           const float* K9, float max_dist_diff, float relative_fitness, float relative_rmse,
+                           int max_iteration, float* out_T16, float* out_fitness, float* out_rmse) {
+    const float k00 = K9[0], k02 = K9[2], k11 = K9[4], k12 = K9[5];
+    float T[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+    float fit = 0, rmse = 0;
+    int last = 0;
+    for (int iter = 0; iter <= max_iteration && n > 0; ++iter) {
+        float sum[29];
+        memset(sum, 0, sizeof sum);
+        for (int i = 0; i < n; ++i) {
+            const float sx = pts[3 * i], sy = pts[3 * i + 1], sz = pts[3 * i + 2];
+            /* device arithmetic of the path being replaced (nvcc -fmad contracts x/z*K + c): fma, then + 0.5 */
+            const float fu = fmaf(sx / sz, k00, k02) + 0.5f, fv = fmaf(sy / sz, k11, k12) + 0.5f;
+            if (!(fu > -2147483648.0f && fu < 2147483648.0f && fv > -2147483648.0f && fv < 2147483648.0f)) continue;
+            const int u = (int)fu, v = (int)fv;
+            if (u >= W || v >= H || u < 0 || v < 0) continue;
+            const size_t idx = (size_t)u + (size_t)v * W;
+            const float dx = scene_pcd[3 * idx], dy = scene_pcd[3 * idx + 1], dz = scene_pcd[3 * idx + 2];
+            if (dz <= 0 || fabsf(sz - dz) > max_dist_diff) continue;
+            const float nx = scene_normals[3 * idx], ny = scene_normals[3 * idx + 1], nz = scene_normals[3 * idx + 2];
+            const float bt = (dx - sx) * nx + (dy - sy) * ny + (dz - sz) * nz;
+            const float A[6] = {nz * sy - ny * sz, nx * sz - nz * sx, ny * sx - nx * sy, nx, ny, nz};
+            int o = 0;
+            for (int r = 0; r < 6; ++r) for (int c = r; c < 6; ++c) sum[o++] += A[r] * A[c];
+            for (int r = 0; r < 6; ++r) sum[21 + r] += A[r] * bt;
+            sum[27] += bt * bt;
+            sum[28] += 1.0f;
+        }
+        last = iter;
+        if (sum[28] == 0) break;
+        const float pf = fit, pr = rmse;
+        fit = sum[28] / (float)n;
+        rmse = sqrtf(sum[27] / sum[28]);
+        if (iter == max_iteration) break;
+        if (fabsf(fit - pf) < relative_fitness && fabsf(rmse - pr) < relative_rmse) break;
+        double Am[36], b[6], L[6][6], D[6], y[6], x[6] = {0, 0, 0, 0, 0, 0};
+        int o = 0, ok = 1;
+        for (int r = 0; r < 6; ++r) for (int c = r; c < 6; ++c) { Am[r * 6 + c] = sum[o]; Am[c * 6 + r] = sum[o]; ++o; }
+        for (int r = 0; r < 6; ++r) b[r] = sum[21 + r];
+        memset(L, 0, sizeof L);
+        for (int j = 0; j < 6 && ok; ++j) {
+            double s = Am[j * 6 + j];
+            for (int k = 0; k < j; ++k) s -= L[j][k] * L[j][k] * D[k];
+            D[j] = s;
+            if (!(fabs(s) > 1e-300)) { ok = 0; break; }
+            for (int i = j + 1; i < 6; ++i) { double t = Am[i * 6 + j]; for (int k = 0; k < j; ++k) t -= L[i][k] * L[j][k] * D[k]; L[i][j] = t / s; }
+        }
+        if (!ok) break;
+        for (int i = 0; i < 6; ++i) { double s = b[i]; for (int k = 0; k < i; ++k) s -= L[i][k] * y[k]; y[i] = s; }
+        for (int i = 5; i >= 0; --i) { double s = y[i] / D[i]; for (int k = i + 1; k < 6; ++k) s -= L[k][i] * x[k]; x[i] = s; }
+        const double ca = cos(x[0]), sa = sin(x[0]), cb = cos(x[1]), sb = sin(x[1]), cg = cos(x[2]), sg = sin(x[2]);
+        const float E[12] = {(float)(cg * cb), (float)(cg * sb * sa - sg * ca), (float)(cg * sb * ca + sg * sa), (float)x[3],
+                             (float)(sg * cb), (float)(sg * sb * sa + cg * ca), (float)(sg * sb * ca - cg * sa), (float)x[4],
+                             (float)(-sb), (float)(cb * sa), (float)(cb * ca), (float)x[5]};
+        for (int i = 0; i < n; ++i) {
+            const float px = pts[3 * i], py = pts[3 * i + 1], pz = pts[3 * i + 2];
+            pts[3 * i] = E[0] * px + E[1] * py + E[2] * pz + E[3];
+            pts[3 * i + 1] = E[4] * px + E[5] * py + E[6] * pz + E[7];
+            pts[3 * i + 2] = E[8] * px + E[9] * py + E[10] * pz + E[11];
+        }
+        float nT[12];
+        for (int r = 0; r < 3; ++r)
+            for (int c = 0; c < 4; ++c) nT[r * 4 + c] = E[r * 4] * T[c] + E[r * 4 + 1] * T[4 + c] + E[r * 4 + 2] * T[8 + c] + E[r * 4 + 3] * T[12 + c];
+        memcpy(T, nT, sizeof nT);
+    }
+    memcpy(out_T16, T, sizeof T);
+    *out_fitness = fit;
+    *out_rmse = rmse;
+    return last;
+}

@@ -423,7 +423,7 @@ void perch_destroy(perch_ctx* c) {
                     c->d_cl_orig, c->d_cl_low, c->d_cl_high,
                     c->d_src_depth, c->d_src_label, c->d_src_rgb, c->d_grid_pts, c->d_grid_label, c->d_cell_start,
                     c->d_obs_lab, c->d_obs_rgb, c->d_scratch, c->d_err_flag, c->d_flush, c->d_obs_xyz_aos,
-                    c->d_tgt_normals, c->d_gicp};
+                    c->d_tgt_normals, c->d_gicp, c->d_icp_pcd, c->d_icp_normals};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
@@ -846,6 +846,78 @@ int perch_gicp(perch_ctx* c, const float* poses16, int n_poses, const int* pose_
     c->timing_pending = false;
     note_memory(c);
     return check_err_flag(c);
+}
+
+int perch_icp_set_scene(perch_ctx* c, const int32_t* scene_depth, int width, int height, const float K9[9],
+                        float max_dist_diff, float* out_pcd, float* out_normals) {
+    if (!c) return fail(PERCH_ERR_INVALID, "null context");
+    if (!scene_depth || !K9 || width <= 0 || height <= 0) return fail(PERCH_ERR_INVALID, "bad icp scene argument");
+    DeviceGuard g(c->device);
+    const size_t npx = (size_t)width * height;
+    int rc;
+    if ((rc = upload<float>(&c->d_icp_pcd, nullptr, 3 * npx, c->stream))) return rc;
+    if ((rc = upload<float>(&c->d_icp_normals, nullptr, 3 * npx, c->stream))) return rc;
+    if ((rc = ensure_scratch(c, Scratch::align(npx * 4) + 1024))) return rc;
+    Scratch s(c);
+    int32_t* d_depth = s.take<int32_t>(npx);
+    CU(cudaMemcpyAsync(d_depth, scene_depth, npx * 4, cudaMemcpyHostToDevice, c->stream));
+    CU(perch::launch_icp_scene(d_depth, width, height, K9, c->d_icp_pcd, c->d_icp_normals, c->stream));
+    if (out_pcd) CU(cudaMemcpyAsync(out_pcd, c->d_icp_pcd, 3 * npx * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (out_normals) CU(cudaMemcpyAsync(out_normals, c->d_icp_normals, 3 * npx * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    c->icp_w = width; c->icp_h = height;
+    memcpy(c->icp_K, K9, sizeof c->icp_K);
+    c->icp_max_dist = max_dist_diff;
+    note_memory(c);
+    return PERCH_OK;
+}
+
+int perch_icp_point2plane(perch_ctx* c, const float* model_pcd, const int* cloud_offsets, int n_clouds,
+                          float relative_fitness, float relative_rmse, int max_iteration, float* out_transforms16,
+                          float* out_fitness, float* out_inlier_rmse, int* out_iterations, float* out_pcd) {
+    if (!c) return fail(PERCH_ERR_INVALID, "null context");
+    if (c->icp_w == 0) return fail(PERCH_ERR_INVALID, "perch_icp_set_scene has not been called");
+    if (n_clouds < 0 || (n_clouds > 0 && (!cloud_offsets || !out_transforms16 || !out_fitness || !out_inlier_rmse)) || max_iteration < 0)
+        return fail(PERCH_ERR_INVALID, "bad icp argument");
+    if (n_clouds == 0) return PERCH_OK;
+    for (int i = 0; i < n_clouds; ++i)
+        if (cloud_offsets[i + 1] < cloud_offsets[i] || cloud_offsets[0] != 0) return fail(PERCH_ERR_INVALID, "cloud_offsets must ascend from 0");
+    const size_t n = (size_t)cloud_offsets[n_clouds], B = (size_t)n_clouds;
+    if (n > 0 && !model_pcd) return fail(PERCH_ERR_INVALID, "null model_pcd");
+    DeviceGuard g(c->device);
+    int rc;
+    if ((rc = ensure_scratch(c, Scratch::align(std::max<size_t>(n, 1) * 12) + Scratch::align((B + 1) * 4) + Scratch::align(B * 64) +
+                                    3 * Scratch::align(B * 4) + 1024))) return rc;
+    Scratch s(c);
+    perch::IcpArgs a;
+    a.points = s.take<float>(std::max<size_t>(n, 1) * 3);
+    int* d_off = s.take<int>(B + 1);
+    a.offsets = d_off;
+    a.out_T = s.take<float>(B * 16);
+    a.out_fitness = s.take<float>(B);
+    a.out_rmse = s.take<float>(B);
+    a.out_iterations = s.take<int>(B);
+    if (n > 0) CU(cudaMemcpyAsync(a.points, model_pcd, n * 12, cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMemcpyAsync(d_off, cloud_offsets, (B + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+    a.scene_pcd = c->d_icp_pcd; a.scene_normals = c->d_icp_normals;
+    a.width = c->icp_w; a.height = c->icp_h;
+    a.k00 = c->icp_K[0]; a.k02 = c->icp_K[2]; a.k11 = c->icp_K[4]; a.k12 = c->icp_K[5];
+    a.max_dist_diff = c->icp_max_dist;
+    a.relative_fitness = relative_fitness; a.relative_rmse = relative_rmse; a.max_iteration = max_iteration;
+    CU(cudaEventRecord(c->ev0, c->stream));
+    CU(perch::launch_icp_point2plane(a, n_clouds, c->stream));
+    CU(cudaEventRecord(c->ev1, c->stream));
+    CU(cudaMemcpyAsync(out_transforms16, a.out_T, B * 64, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(out_fitness, a.out_fitness, B * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(out_inlier_rmse, a.out_rmse, B * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (out_iterations) CU(cudaMemcpyAsync(out_iterations, a.out_iterations, B * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (out_pcd && n > 0) CU(cudaMemcpyAsync(out_pcd, a.points, n * 12, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1);
+    c->last_launches = 1;
+    c->timing_pending = false;
+    note_memory(c);
+    return PERCH_OK;
 }
 
 int perch_knn(perch_ctx* c, const float* ref, int ref_nb, const float* query, int query_nb, int dim, int k,

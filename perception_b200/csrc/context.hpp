@@ -121,6 +121,12 @@ struct perch_ctx {
     int tgt_normals_k = 0;             // k the cached normals were computed with (0 = stale)
     void* d_gicp = nullptr;
     size_t gicp_bytes = 0;
+    // cuda_icp package API (icp.cu): the prepared depth-image scene
+    float* d_icp_pcd = nullptr;        // W*H x 3
+    float* d_icp_normals = nullptr;    // W*H x 3
+    int icp_w = 0, icp_h = 0;
+    float icp_K[9] = {0};
+    float icp_max_dist = 0.1f;
     void* d_flush = nullptr;           // 256 MiB L2-flush target (perch_l2_flush)
     int flush_value = 0;
     void* h_pinned = nullptr;

@@ -120,4 +120,24 @@ cudaError_t launch_target_normals(const float* d_xyz_aos, const int* d_knn_index
 // max over poses of the per-pose point count (pose_begin as above) -> *d_out (must be zeroed)
 cudaError_t launch_pose_count_max(const int* d_pose_begin, int rows_per_pose, int n_poses, int* d_out, cudaStream_t stream);
 
+// ---- point-to-plane ICP against a depth-image scene, cuda_icp package API (icp.cu) ------------------------------------------
+struct IcpArgs {
+    float* points = nullptr;          // all model clouds, N x 3, transformed IN PLACE (like the reference's model_pcd)
+    const int* offsets = nullptr;     // n_clouds + 1
+    const float* scene_pcd = nullptr; // W*H x 3 (dep2pcd of the scene depth)
+    const float* scene_normals = nullptr;
+    int width = 0, height = 0;
+    float k00 = 0, k02 = 0, k11 = 0, k12 = 0;
+    float max_dist_diff = 0.1f;       // depth_scene.h:9
+    float relative_fitness = 1e-5f, relative_rmse = 1e-5f;  // ICPConvergenceCriteria, icp.h:40-51
+    int max_iteration = 30;
+    float* out_T = nullptr;           // n_clouds x 16, row-major 4x4
+    float* out_fitness = nullptr;
+    float* out_rmse = nullptr;
+    int* out_iterations = nullptr;    // or null
+};
+cudaError_t launch_icp_scene(const int32_t* d_depth, int W, int H, const float K9[9], float* d_pcd, float* d_normals,
+                             cudaStream_t stream);
+cudaError_t launch_icp_point2plane(const IcpArgs& a, int n_clouds, cudaStream_t stream);
+
 }  // namespace perch

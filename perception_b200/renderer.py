@@ -249,6 +249,32 @@ class Renderer:
                                       _ptr(it), _ptr(err)))
         return {"adjusted_poses": adj, "transforms": tf, "iterations": it, "error": err}
 
+    def icp_set_scene(self, scene_depth, width, height, K, max_dist_diff=0.1, want_buffers=False):
+        """Scene_projective::init_Scene_projective_cuda (depth_scene.h:19-25): depth in cm (int32), K 3x3."""
+        d = _c(scene_depth, np.int32).reshape(-1)
+        assert d.size == width * height
+        K9 = _c(K, np.float32).reshape(9)
+        pcd = np.zeros((height * width, 3), np.float32) if want_buffers else None
+        nrm = np.zeros((height * width, 3), np.float32) if want_buffers else None
+        self._ck(self._lib.perch_icp_set_scene(self._h, _ptr(d), width, height, _ptr(K9), max_dist_diff, _ptr(pcd), _ptr(nrm)))
+        return (pcd, nrm) if want_buffers else None
+
+    def icp_point2plane(self, clouds, relative_fitness=1e-5, relative_rmse=1e-5, max_iteration=30):
+        """cuda_icp::ICP_Point2Plane_cuda<Scene_projective> (icp.h:92-99) for a list of (n_i,3) clouds.  Returns
+        transformation (B,4,4), fitness (B,), inlier_rmse (B,), iterations (B,), and the transformed clouds."""
+        clouds = [np.ascontiguousarray(c, np.float32).reshape(-1, 3) for c in clouds]
+        off = np.zeros(len(clouds) + 1, np.int32)
+        off[1:] = np.cumsum([len(c) for c in clouds])
+        pts = np.ascontiguousarray(np.concatenate(clouds) if clouds else np.zeros((0, 3), np.float32), dtype=np.float32)
+        B = len(clouds)
+        T = np.zeros((B, 4, 4), np.float32)
+        fit = np.zeros(B, np.float32); rmse = np.zeros(B, np.float32); it = np.zeros(B, np.int32)
+        out = np.zeros_like(pts)
+        self._ck(self._lib.perch_icp_point2plane(self._h, _ptr(pts), _ptr(off), B, relative_fitness, relative_rmse,
+                                                 max_iteration, _ptr(T), _ptr(fit), _ptr(rmse), _ptr(it), _ptr(out)))
+        return {"transformation": T, "fitness": fit, "inlier_rmse": rmse, "iterations": it,
+                "clouds": [out[off[i]:off[i + 1]] for i in range(B)]}
+
     # -- introspection ---------------------------------------------------------------------------------------------
     def last_timing(self):
         ms, n = C.c_float(0), C.c_int(0)

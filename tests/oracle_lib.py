@@ -146,6 +146,62 @@ class Oracle:
         return T, it, err.value
 
 
+    def icp_scene(self, depth, W, H, K):
+        d = _c(depth, np.int32).reshape(-1)
+        K9 = _c(K, np.float32).reshape(9)
+        pcd = np.zeros((W * H, 3), np.float32)
+        nrm = np.zeros((W * H, 3), np.float32)
+        self.lib.oracle_icp_scene(_p(d), C.c_int(W), C.c_int(H), _p(K9), _p(pcd), _p(nrm))
+        return pcd, nrm
+
+    def icp_point2plane(self, cloud, scene_pcd, scene_normals, W, H, K, max_dist_diff=0.1, relative_fitness=1e-5,
+                        relative_rmse=1e-5, max_iteration=30):
+        pts = np.array(cloud, np.float32, copy=True).reshape(-1, 3)
+        K9 = _c(K, np.float32).reshape(9)
+        T = np.zeros(16, np.float32)
+        fit, rmse = C.c_float(0), C.c_float(0)
+        self.lib.oracle_icp_point2plane.restype = C.c_int
+        it = self.lib.oracle_icp_point2plane(_p(pts), C.c_int(len(pts)), _p(_c(scene_pcd, np.float32)),
+                                             _p(_c(scene_normals, np.float32)), C.c_int(W), C.c_int(H), _p(K9),
+                                             C.c_float(max_dist_diff), C.c_float(relative_fitness), C.c_float(relative_rmse),
+                                             C.c_int(max_iteration), _p(T), C.byref(fit), C.byref(rmse))
+        return {"transformation": T.reshape(4, 4), "fitness": fit.value, "inlier_rmse": rmse.value, "iterations": it, "cloud": pts}
+
+
+ICP_REF_SO = ROOT / "oracle" / "_ref" / "libicp_ref.so"
+
+
+class ReferenceIcp:
+    """The reference's cuda_icp package compiled from its own sources (oracle/ref_icp_harness.cu).  Scene preparation
+    is host code (runs without a GPU); the ICP loop needs one."""
+
+    def __init__(self):
+        if not ICP_REF_SO.exists():
+            raise FileNotFoundError(f"{ICP_REF_SO} missing: build with `make -C oracle ref` where /root/reference exists")
+        self.lib = C.CDLL(str(ICP_REF_SO))
+
+    def scene(self, depth, W, H, K):
+        d = _c(depth, np.int32).reshape(-1)
+        K9 = _c(K, np.float32).reshape(9)
+        pcd = np.zeros((W * H, 3), np.float32)
+        nrm = np.zeros((W * H, 3), np.float32)
+        assert self.lib.ref_icp_scene(_p(d), C.c_int(W), C.c_int(H), _p(K9), _p(pcd), _p(nrm)) == 0
+        return pcd, nrm
+
+    def point2plane(self, cloud, scene_pcd, scene_normals, W, H, K, max_dist_diff=0.1, relative_fitness=1e-5,
+                    relative_rmse=1e-5, max_iteration=30):
+        pts = np.array(cloud, np.float32, copy=True).reshape(-1, 3)
+        K9 = _c(K, np.float32).reshape(9)
+        T = np.zeros(16, np.float32)
+        fit, rmse = C.c_float(0), C.c_float(0)
+        rc = self.lib.ref_icp_point2plane(_p(pts), C.c_int(len(pts)), _p(_c(scene_pcd, np.float32)),
+                                          _p(_c(scene_normals, np.float32)), C.c_int(W), C.c_int(H), _p(K9),
+                                          C.c_float(max_dist_diff), C.c_float(relative_fitness), C.c_float(relative_rmse),
+                                          C.c_int(max_iteration), _p(T), C.byref(fit), C.byref(rmse))
+        assert rc == 0
+        return {"transformation": T.reshape(4, 4), "fitness": fit.value, "inlier_rmse": rmse.value, "cloud": pts}
+
+
 KNN_REF_SO = ROOT / "oracle" / "_ref" / "libknn_ref.so"
 
 
