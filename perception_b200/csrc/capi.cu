@@ -76,16 +76,6 @@ struct Scratch {
     }
 };
 
-int ensure_scratch(perch_ctx* c, size_t bytes) {
-    if (bytes <= c->scratch_bytes) return PERCH_OK;
-    if (c->d_scratch) cudaFree(c->d_scratch);
-    c->d_scratch = nullptr;
-    c->scratch_bytes = 0;
-    CU(cudaMalloc(&c->d_scratch, bytes));
-    c->scratch_bytes = bytes;
-    return PERCH_OK;
-}
-
 void note_memory(perch_ctx* c) {
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
@@ -93,6 +83,18 @@ void note_memory(perch_ctx* c) {
         c->stats.peak_memory_usage = std::max(c->stats.peak_memory_usage, used);
     }
 }
+
+int ensure_scratch(perch_ctx* c, size_t bytes) {
+    if (bytes <= c->scratch_bytes) return PERCH_OK;
+    if (c->d_scratch) cudaFree(c->d_scratch);
+    c->d_scratch = nullptr;
+    c->scratch_bytes = 0;
+    CU(cudaMalloc(&c->d_scratch, bytes));
+    c->scratch_bytes = bytes;
+    note_memory(c);  // high-water mark moves when the scratch grows, not on every call
+    return PERCH_OK;
+}
+
 
 int env_int(const char* name, int dflt) {
     const char* v = getenv(name);
@@ -1144,19 +1146,27 @@ int perch_render_cost(perch_ctx* c, const char* stage, const float* poses16, int
         }
         if (out->counts) CU(cudaMemcpyAsync(out->counts, d_counts, P * 12, cudaMemcpyDeviceToHost, c->stream));
     }
+    int flag = 0;
+    CU(cudaMemcpyAsync(&flag, c->d_err_flag, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     CU(cudaStreamSynchronize(c->stream));
     cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1);
     c->last_launches = launches;
     c->timing_pending = false;
-    note_memory(c);
-    return check_err_flag(c);
+    if (flag) {
+        cudaMemsetAsync(c->d_err_flag, 0, sizeof(int), c->stream);
+        return fail(PERCH_ERR_CUDA, "internal error: a fragment fell outside its pose tile (flag %d)", flag);
+    }
+    return PERCH_OK;
 }
 
 int perch_topk(const float* rendered, const float* observed, const int* pose_model_map, int n_poses, int pose_id_offset,
                int n_models, int k, perch_hit* out) {
     if (!rendered || !observed || !pose_model_map || !out || n_models <= 0 || k <= 0 || n_poses < 0)
         return fail(PERCH_ERR_INVALID, "bad topk argument");
-    std::vector<std::vector<perch_hit>> per(n_models);
+    // bounded insertion per model: one pass, no allocation beyond the k-entry lists
+    const perch_hit empty{INT32_MAX, -1, 0.f, 0.f};
+    for (size_t j = 0; j < (size_t)n_models * k; ++j) out[j] = empty;
+    auto before = [](const perch_hit& a, const perch_hit& b) { return a.cost != b.cost ? a.cost < b.cost : a.pose_id < b.pose_id; };
     for (int i = 0; i < n_poses; ++i) {
         int m = pose_model_map[i];
         if (m < 0 || m >= n_models) continue;
@@ -1168,16 +1178,12 @@ int perch_topk(const float* rendered, const float* observed, const int* pose_mod
         if (cost == -1 || cost == -2) continue;  // search_env.cpp:2555 "Invalid successor"
         // search_env.cpp:2560-2561: abs(target_cost - source_cost) < 30 on the truncated ints
         if (!(std::abs((int)r - (int)o) < 30)) continue;
-        per[m].push_back(perch_hit{cost, pose_id_offset + i, r, o});
-    }
-    for (int m = 0; m < n_models; ++m) {
-        auto& v = per[m];
-        size_t kk = std::min<size_t>(k, v.size());
-        std::partial_sort(v.begin(), v.begin() + kk, v.end(), [](const perch_hit& a, const perch_hit& b) {
-            return a.cost != b.cost ? a.cost < b.cost : a.pose_id < b.pose_id;
-        });
-        for (int j = 0; j < k; ++j)
-            out[(size_t)m * k + j] = (size_t)j < kk ? v[j] : perch_hit{INT32_MAX, -1, 0.f, 0.f};
+        const perch_hit h{cost, pose_id_offset + i, r, o};
+        perch_hit* list = out + (size_t)m * k;
+        if (!before(h, list[k - 1])) continue;
+        int pos = k - 1;
+        while (pos > 0 && before(h, list[pos - 1])) { list[pos] = list[pos - 1]; --pos; }
+        list[pos] = h;
     }
     return PERCH_OK;
 }

@@ -33,8 +33,8 @@ constexpr int kThreads = PERCH_POSE_THREADS;
 constexpr int kWarps = kThreads / 32;
 constexpr int kMinCtas = 1024 / kThreads;  // resident CTAs per SM the register budget is sized for (32 warps)
 constexpr int kQueueCap = 16 * kThreads;   // candidate triangles buffered between exact passes
-constexpr int kClaim = 32;        // clusters tested per warp claim (one per lane)
-constexpr int kPendCap = 64;      // per-warp list of surviving clusters awaiting the per-triangle test
+constexpr int kClaim = 64;        // clusters tested per warp claim (two per lane: independent loads in flight)
+constexpr int kPendCap = 96;      // per-warp list of surviving clusters awaiting the per-triangle test (< 8 carried + 64)
 constexpr int kClaimMaxTris = (kClaim + 8) * 4;  // most candidates one claim can append (incl. carried clusters)
 static_assert(kClusterTris == 4, "lane mapping of the per-triangle test assumes 4 triangles per cluster");
 constexpr int kBigCells = 48;     // lattice pixels above which a triangle is rasterised by the whole CTA
@@ -189,8 +189,8 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
     const int mask_words = (MODE == MODE_COST) ? a.mask_words : 0;
     uint32_t* mask = reinterpret_cast<uint32_t*>(smem_raw + (size_t)a.tile_cap * sizeof(zkey));
     int* queue = reinterpret_cast<int*>(mask + mask_words);
-    int* wpend = queue + kQueueCap + (threadIdx.x >> 5) * (2 * kPendCap);  // per-warp surviving clusters
-    int* wstage = wpend + kPendCap;                                          // per-warp staged candidate triangles
+    int* wpend = queue + kQueueCap + (threadIdx.x >> 5) * (kPendCap + 64);  // per-warp surviving clusters
+    int* wstage = wpend + kPendCap;                                          // per-warp staged candidate triangles (< 64)
 
     __shared__ Mat4 s_pose;
     __shared__ int s_rect[4];
@@ -434,11 +434,13 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                     if (lane == 0 && *(volatile int*)&s_qcount <= kQueueCap - kWarps * (kClaimMaxTris + 32)) g = atomicAdd(&s_next, 1);
                     g = __shfl_sync(0xffffffffu, g, 0);
                     if (g >= n_groups) break;
-                    const int c = cl_low + g * kClaim + lane;
-                    const bool keep = (c < cl_high) && cluster_hits(c);
-                    const unsigned ballot = __ballot_sync(0xffffffffu, keep);
-                    if (keep) wpend[npend + __popc(ballot & lt_mask)] = c;
-                    npend += __popc(ballot);
+                    const int c0 = cl_low + g * kClaim + lane, c1 = c0 + 32;
+                    const bool keep0 = (c0 < cl_high) && cluster_hits(c0);
+                    const bool keep1 = (c1 < cl_high) && cluster_hits(c1);
+                    const unsigned b0 = __ballot_sync(0xffffffffu, keep0), b1 = __ballot_sync(0xffffffffu, keep1);
+                    if (keep0) wpend[npend + __popc(b0 & lt_mask)] = c0;
+                    if (keep1) wpend[npend + __popc(b0) + __popc(b1 & lt_mask)] = c1;
+                    npend += __popc(b0) + __popc(b1);
                     __syncwarp();
                     while (npend >= 8) {
                         npend -= 8;
@@ -614,7 +616,7 @@ __global__ void fill_keys_kernel(unsigned long long* keys, int n) {
 size_t pose_kernel_smem_bytes(const PoseArgs& a, bool image_mode, bool color) {
     size_t b = (size_t)a.tile_cap * ((color || image_mode) ? 8 : 4) + (image_mode ? 0 : (size_t)a.mask_words * 4) +
                (size_t)kQueueCap * 4;
-    return b + (size_t)kWarps * 2 * kPendCap * sizeof(int);
+    return b + (size_t)kWarps * (kPendCap + 64) * sizeof(int);
 }
 
 template <int MODE, bool COLOR>
