@@ -215,6 +215,91 @@ typedef struct perch_hit {
 int perch_topk(const float* rendered_cost, const float* observed_cost, const int* pose_model_map, int n_poses,
                int pose_id_offset, int n_models, int k, perch_hit* out_hits /* n_models*k, cost=INT32_MAX pads */);
 
+/* ==== caller glue: candidate ObjectStates instead of matrices ============================== */
+/* The steps sbpl_perception::EnvObjectRecognition performs on the host, serially, on either side of
+ * render_cuda_multi_unified -- GenerateSuccessorStates + IsValidPose before it (search_env.cpp:7056-7490, 309-528),
+ * the per-pose matrix assembly and pose_observed_points_total inside GetStateImagesUnifiedGPU (1505-1622) -- run here
+ * on the device, so that a scene goes from candidate generation to costs without the pose list visiting the host. */
+
+/* ObjectState (object_state.h) with its ContPose flattened.  The fields hold what ContPose's constructors leave in the
+ * object (object_state.cpp:17-41): angles already normalised to [0, 2pi) for the Euler constructor; qx..qw all zero
+ * means "use the Euler angles" (object_state.cpp:88-93). */
+typedef struct perch_state {
+    double x, y, z;
+    double roll, pitch, yaw;
+    double qx, qy, qz, qw;
+    int32_t model_id;              /* ObjectState::id() */
+    int32_t segmentation_label_id; /* ObjectState::segmentation_label_id(): 1-based label in the mask; -1 = none */
+} perch_state;                     /* 88 bytes */
+
+/* What the glue reads from ObjectModel (object_model.h) and ModelMetaData. */
+typedef struct perch_model_meta {
+    float preprocessing_transform[16]; /* ObjectModel::preprocessing_transform().matrix(), ROW-major */
+    double circumscribed_radius;       /* GetCircumscribedRadius()   (object_model.cpp:460-462) */
+    double circumscribed_radius_3d;    /* GetCircumscribedRadius3D() (464-466) */
+    double inscribed_radius;           /* GetInscribedRadius()       (456-458) */
+    double inflation_factor;           /* GetInflationFactor()       (383) */
+    double search_resolution;          /* ModelMetaData::search_resolution */
+    int32_t symmetric;                 /* ObjectModel::symmetric() */
+    int32_t symmetry_mode;             /* ModelMetaData::symmetry_mode: 0 none, 1 semi (180 deg), 2 full */
+    int32_t footprint_offset;          /* convex_hull_footprint_ (object_model.cpp:361-372): first point ... */
+    int32_t footprint_count;           /* ... and number of points in perch_set_env's footprint array */
+} perch_model_meta;
+
+/* The EnvParams / PerchParams fields the glue reads (search_env.cpp:140-216). */
+typedef struct perch_env {
+    double cam_to_world[16];           /* cam_to_world_.matrix(), ROW-major (the body-frame camera pose) */
+    double x_min, x_max, y_min, y_max; /* table bounds */
+    double table_height;
+    double res;                        /* env_params_.res: translation step of the 3-DoF grid */
+    double theta_res;                  /* env_params_.theta_res: yaw step */
+    double footprint_tolerance;        /* perch_params_.footprint_tolerance */
+    int32_t use_external_pose_list;    /* 1 = 6-DoF mode */
+    int32_t use_cylinder_observed;     /* perch_params_.use_cylinder_observed */
+    int32_t min_neighbor_points_for_valid_pose;
+    int32_t use_adaptive_resolution;
+    int32_t use_model_specific_search_resolution;
+    int32_t min_points_for_constraint_cloud;
+} perch_env;
+
+/* Environment and per-model metadata; footprint_xyz holds every model's convex-hull footprint points (x,y,z floats,
+ * implicitly closed polygons) back to back.  n_models must match perch_set_models when both are set. */
+int perch_set_env(perch_ctx* ctx, const perch_env* env, const perch_model_meta* metas, int n_models,
+                  const float* footprint_xyz, int n_footprint_points);
+/* The clouds the radius searches run in (search_env.cpp:5624-5662): xyz_aos holds n_points points; ranges (may be NULL =
+ * one range holding everything) is 2*n_ranges ints, [begin,end) per range: range 0 is the cloud searched when a state
+ * carries no label (projected_knn_ in 3-DoF, where the caller has already set z = table_height, or knn in 6-DoF), range
+ * 1+l the segmented cloud of label l (segmented_object_knn[l]).  constraint_xyz (may be NULL / 0) = projected
+ * constraint cloud (search_env.cpp:5654-5658).  A uniform grid over (x, y) is built on the device. */
+int perch_set_search_cloud(perch_ctx* ctx, const float* xyz_aos, int n_points, const int* ranges, int n_ranges,
+                           const float* constraint_xyz, int n_constraint);
+/* The loop of GetStateImagesUnifiedGPU (search_env.cpp:1535-1622): per state the camera-frame pose matrix
+ * (cam_to_world * cam_to_body)^-1 * ContPose::GetTransform() * preprocessing_transform in double, x100 on the top three
+ * rows, cast to float (model.h:89-107); pose_model_map; in 6-DoF mode the segmentation label (id - 1) and the label's
+ * observed point count; in 3-DoF mode the number of projected-cloud points inside the model's inflated circumscribed
+ * circle (use_cylinder_observed) or the observed point count.  Outputs are host pointers, each optional. */
+int perch_assemble_states(perch_ctx* ctx, const perch_state* states, int n_states, float* out_poses16,
+                          int* out_pose_model_map, int* out_pose_segmentation_label,
+                          float* out_pose_observed_points_total);
+/* perch_assemble_states followed by perch_render_cost on the assembled, device-resident batch: what
+ * GetStateImagesUnifiedGPU does in one call.  states == NULL scores the list left on the device by the last
+ * perch_generate_states (n_states is then ignored). */
+int perch_score_states(perch_ctx* ctx, const char* stage, const perch_state* states, int n_states,
+                       const perch_params* params, perch_outputs* out);
+/* EnvObjectRecognition::IsValidPose (search_env.cpp:309-528) for a list of candidates against the objects already
+ * placed: enough observed points within the search radius, no overlap of inscribed circles with placed objects,
+ * footprint inside the table bounds (3-DoF), enough constraint-cloud points inside the footprint.  out_valid: one byte
+ * per state. */
+int perch_validate_states(perch_ctx* ctx, const perch_state* states, int n_states, const perch_state* placed,
+                          int n_placed, int after_refinement, uint8_t* out_valid);
+/* The 3-DoF branch of GenerateSuccessorStates (search_env.cpp:7268-7472) for every model not yet in `placed`: the
+ * x / y / yaw grid (steps accumulated in double like the reference's loops), IsValidPose, the symmetry rules
+ * (symmetric / symmetry_mode 2: first valid yaw only; mode 1: stop above pi + theta_res), output in the reference's
+ * order (model, x, y, yaw).  The list stays on the device for perch_score_states(states = NULL); out_states (may be
+ * NULL) receives at most `capacity` of them, *n_out the full count. */
+int perch_generate_states(perch_ctx* ctx, const perch_state* placed, int n_placed, perch_state* out_states,
+                          int capacity, int* n_out);
+
 #ifdef __cplusplus
 }
 #endif

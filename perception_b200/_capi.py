@@ -61,6 +61,48 @@ class perch_hit(C.Structure):
     _fields_ = [("cost", C.c_int32), ("pose_id", C.c_int32), ("rendered_cost", C.c_float), ("observed_cost", C.c_float)]
 
 
+class perch_state(C.Structure):
+    _fields_ = [(n, C.c_double) for n in ("x", "y", "z", "roll", "pitch", "yaw", "qx", "qy", "qz", "qw")] + [
+        ("model_id", C.c_int32),
+        ("segmentation_label_id", C.c_int32),
+    ]
+
+
+class perch_model_meta(C.Structure):
+    _fields_ = [
+        ("preprocessing_transform", C.c_float * 16),
+        ("circumscribed_radius", C.c_double),
+        ("circumscribed_radius_3d", C.c_double),
+        ("inscribed_radius", C.c_double),
+        ("inflation_factor", C.c_double),
+        ("search_resolution", C.c_double),
+        ("symmetric", C.c_int32),
+        ("symmetry_mode", C.c_int32),
+        ("footprint_offset", C.c_int32),
+        ("footprint_count", C.c_int32),
+    ]
+
+
+class perch_env(C.Structure):
+    _fields_ = [
+        ("cam_to_world", C.c_double * 16),
+        ("x_min", C.c_double),
+        ("x_max", C.c_double),
+        ("y_min", C.c_double),
+        ("y_max", C.c_double),
+        ("table_height", C.c_double),
+        ("res", C.c_double),
+        ("theta_res", C.c_double),
+        ("footprint_tolerance", C.c_double),
+        ("use_external_pose_list", C.c_int32),
+        ("use_cylinder_observed", C.c_int32),
+        ("min_neighbor_points_for_valid_pose", C.c_int32),
+        ("use_adaptive_resolution", C.c_int32),
+        ("use_model_specific_search_resolution", C.c_int32),
+        ("min_points_for_constraint_cloud", C.c_int32),
+    ]
+
+
 # name -> (restype, argtypes); the list doubles as the "every symbol of include/perch_b200.h" check in tests
 _P = C.c_void_p
 _V = C.c_void_p
@@ -94,6 +136,12 @@ SIGNATURES = {
     "perch_synchronize": (C.c_int, [_P]),
     "perch_l2_flush": (C.c_int, [_P]),
     "perch_topk": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P]),
+    "perch_set_env": (C.c_int, [_P, C.POINTER(perch_env), _V, C.c_int, _V, C.c_int]),
+    "perch_set_search_cloud": (C.c_int, [_P, _V, C.c_int, _V, C.c_int, _V, C.c_int]),
+    "perch_assemble_states": (C.c_int, [_P, _V, C.c_int, _V, _V, _V, _V]),
+    "perch_score_states": (C.c_int, [_P, C.c_char_p, _V, C.c_int, C.POINTER(perch_params), C.POINTER(perch_outputs)]),
+    "perch_validate_states": (C.c_int, [_P, _V, C.c_int, _V, C.c_int, C.c_int, _V]),
+    "perch_generate_states": (C.c_int, [_P, _V, C.c_int, _V, C.c_int, C.POINTER(C.c_int)]),
 }
 
 _lib = None

@@ -17,12 +17,14 @@
 #include "context.hpp"
 #include "kernels.cuh"
 #include "clusters.hpp"
+#include "capi_common.hpp"
 #include "perch_b200.h"
 
 namespace {
-
 thread_local std::string g_err;
+}
 
+namespace perch_detail {
 int fail(int code, const char* fmt, ...) {
     char buf[512];
     va_list ap;
@@ -32,6 +34,10 @@ int fail(int code, const char* fmt, ...) {
     g_err = buf;
     return code;
 }
+}  // namespace perch_detail
+
+namespace {
+using perch_detail::fail;
 
 #define CU(call)                                                                                           \
     do {                                                                                                   \
@@ -41,14 +47,7 @@ int fail(int code, const char* fmt, ...) {
                         __LINE__);                                                                         \
     } while (0)
 
-struct DeviceGuard {
-    int prev = 0;
-    explicit DeviceGuard(int dev) {
-        cudaGetDevice(&prev);
-        cudaSetDevice(dev);
-    }
-    ~DeviceGuard() { cudaSetDevice(prev); }
-};
+using perch_detail::DeviceGuard;
 
 template <class T>
 int upload(T** dst, const T* src, size_t n, cudaStream_t s) {
@@ -377,6 +376,8 @@ int check_err_flag(perch_ctx* c) {
     CU(cudaStreamSynchronize(c->stream));
     if (flag) {
         cudaMemsetAsync(c->d_err_flag, 0, sizeof(int), c->stream);
+        if (flag & 2) return fail(PERCH_ERR_INVALID, "a state names a model_id outside [0, n_models)");
+        if (flag & 4) return fail(PERCH_ERR_INVALID, "a state's segmentation_label_id has no entry in the observed labels");
         return fail(PERCH_ERR_CUDA, "internal error: a fragment fell outside its pose tile (flag %d)", flag);
     }
     return PERCH_OK;
@@ -429,6 +430,7 @@ void perch_destroy(perch_ctx* c) {
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
+    perch_detail::destroy_states(c);
     cudaEventDestroy(c->ev0);
     cudaEventDestroy(c->ev1);
     cudaStreamDestroy(c->stream);
@@ -622,6 +624,7 @@ int perch_set_observed(perch_ctx* c, const float* xyz_aos, const uint8_t* rgb_so
     c->grid_res = -1.f;  // grid is (re)built on the next cost call, when sensor_resolution is known
     c->tgt_normals_k = 0;
     c->have_obs = true;
+    ++c->obs_version;
     note_memory(c);
     return PERCH_OK;
 }
@@ -955,6 +958,19 @@ int perch_knn(perch_ctx* c, const float* ref, int ref_nb, const float* query, in
 
 int perch_render_cost(perch_ctx* c, const char* stage, const float* poses16, int n_poses, const int* pose_model_map,
                       const int* pose_label, const float* pose_obs_total, const perch_params* p, perch_outputs* out) {
+    perch_detail::PoseInputs in{poses16, pose_model_map, pose_label, pose_obs_total, false};
+    return perch_detail::render_cost_impl(c, stage, in, n_poses, p, out);
+}
+
+}  // extern "C"
+
+// The body of perch_render_cost; `in` may already be device-resident (perch_score_states, capi_states.cu).
+int perch_detail::render_cost_impl(perch_ctx* c, const char* stage, const PoseInputs& in, int n_poses, const perch_params* p,
+                                   perch_outputs* out) {
+    const float* poses16 = in.poses16;
+    const int* pose_model_map = in.model_map;
+    const int* pose_label = in.label;
+    const float* pose_obs_total = in.obs_total;
     if (!stage || !p || !out) return fail(PERCH_ERR_INVALID, "null argument");
     const std::string st(stage);
     const bool s_render = st == "RENDER", s_debug = st == "DEBUG";
@@ -998,10 +1014,11 @@ int perch_render_cost(perch_ctx* c, const char* stage, const float* poses16, int
     int32_t* d_counts = sc.take<int32_t>(P * 3);
     float* d_poses_adj = sc.take<float>(P * 16);
     if (P > 0) {
-        CU(cudaMemcpyAsync(d_poses, poses16, P * 64, cudaMemcpyHostToDevice, c->stream));
-        CU(cudaMemcpyAsync(d_pmm, pose_model_map, P * 4, cudaMemcpyHostToDevice, c->stream));
-        if (pose_label) CU(cudaMemcpyAsync(d_plabel, pose_label, P * 4, cudaMemcpyHostToDevice, c->stream));
-        if (pose_obs_total) CU(cudaMemcpyAsync(d_tot, pose_obs_total, P * 4, cudaMemcpyHostToDevice, c->stream));
+        const cudaMemcpyKind kind = in.on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+        CU(cudaMemcpyAsync(d_poses, poses16, P * 64, kind, c->stream));
+        CU(cudaMemcpyAsync(d_pmm, pose_model_map, P * 4, kind, c->stream));
+        if (pose_label) CU(cudaMemcpyAsync(d_plabel, pose_label, P * 4, kind, c->stream));
+        if (pose_obs_total) CU(cudaMemcpyAsync(d_tot, pose_obs_total, P * 4, kind, c->stream));
     }
     int launches = 0;
     CU(cudaEventRecord(c->ev0, c->stream));
@@ -1154,10 +1171,14 @@ int perch_render_cost(perch_ctx* c, const char* stage, const float* poses16, int
     c->timing_pending = false;
     if (flag) {
         cudaMemsetAsync(c->d_err_flag, 0, sizeof(int), c->stream);
+        if (flag & 2) return fail(PERCH_ERR_INVALID, "a state names a model_id outside [0, n_models)");
+        if (flag & 4) return fail(PERCH_ERR_INVALID, "a state's segmentation_label_id has no entry in the observed labels");
         return fail(PERCH_ERR_CUDA, "internal error: a fragment fell outside its pose tile (flag %d)", flag);
     }
     return PERCH_OK;
 }
+
+extern "C" {
 
 int perch_topk(const float* rendered, const float* observed, const int* pose_model_map, int n_poses, int pose_id_offset,
                int n_models, int k, perch_hit* out) {

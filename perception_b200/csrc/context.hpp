@@ -57,6 +57,8 @@ struct SceneDev {
     const uint8_t* b = nullptr;
 };
 
+struct StatesCtx;  // capi_states.cu
+
 }  // namespace perch
 
 struct perch_ctx {
@@ -127,6 +129,9 @@ struct perch_ctx {
     int icp_w = 0, icp_h = 0;
     float icp_K[9] = {0};
     float icp_max_dist = 0.1f;
+    // caller glue (capi_states.cu): environment, model metadata, search clouds, assembled / generated state lists
+    perch::StatesCtx* states = nullptr;
+    int obs_version = 0;               // bumped by perch_set_observed (per-label point counts are cached against it)
     void* d_flush = nullptr;           // 256 MiB L2-flush target (perch_l2_flush)
     int flush_value = 0;
     void* h_pinned = nullptr;

@@ -68,6 +68,8 @@ class Renderer:
         self.n_models = 0
 
     # -- lifetime ----------------------------------------------------------------------------------------------
+    _n_generated = 0
+
     def close(self) -> None:
         if getattr(self, "_h", None):
             self._lib.perch_destroy(self._h)
@@ -181,12 +183,22 @@ class Renderer:
         prm = perch_params(stride, cost_type, int(bool(calculate_observed_cost)), sensor_resolution, color_distance_threshold,
                            occlusion_threshold, int(single_result_image), int(bool(do_icp)), int(icp_max_iterations),
                            int(icp_k_correspondences), float(icp_rotation_epsilon), float(icp_transformation_epsilon))
+
+        def call(out):
+            return self._lib.perch_render_cost(self._h, stage.encode(), _ptr(P4), P, _ptr(pmm), _ptr(plab), _ptr(ptot),
+                                               C.byref(prm), C.byref(out))
+
+        return self._run_stage(stage, P, prm, call, cloud_capacity, want_dc_index)
+
+    def _run_stage(self, stage: str, P: int, prm, call, cloud_capacity=None, want_dc_index=False):
+        """Allocate the host outputs `stage` produces for P poses, run `call(perch_outputs)`, return them as a dict."""
         out = perch_outputs()
         res = {}
-        if do_icp:
-            res["adjusted_poses"] = P4.reshape(-1, 4, 4).copy()
+        if prm.do_icp:
+            res["adjusted_poses"] = np.zeros((P, 4, 4), np.float32)
             out.adjusted_poses = res["adjusted_poses"].ctypes.data
         W, H = self.width, self.height
+        stride, single_result_image = prm.stride, prm.single_result_image
         st = stage
         images = st in ("RENDER", "DEBUG")
         clouds = st == "DEBUG" or "CLOUD" in st
@@ -218,8 +230,7 @@ class Renderer:
             out.observed_cost = res["observed_cost"].ctypes.data
             out.points_diff_cost = res["points_diff_cost"].ctypes.data
             out.counts = res["counts"].ctypes.data
-        self._ck(self._lib.perch_render_cost(self._h, st.encode(), _ptr(P4), P, _ptr(pmm), _ptr(plab), _ptr(ptot),
-                                             C.byref(prm), C.byref(out)))
+        self._ck(call(out))
         if clouds:
             n = min(out.cloud_point_num, cap)
             res["result_cloud_point_num"] = out.cloud_point_num
@@ -227,6 +238,88 @@ class Renderer:
             res["result_cloud_color"] = ccol[:, :n].copy()
             res["result_cloud_pose_map"] = cmap[:n].copy()
         return res
+
+    # -- caller glue: ObjectState lists (perception_b200/states.py has the host-side types) --------
+    def set_env(self, env, metas) -> None:
+        """EnvParams / PerchParams fields + per-model ObjectModel metadata (states.Env, list of states.ModelMeta)."""
+        from . import states as S
+        e = S.env_struct(env)
+        m, fp = S.meta_array(metas)
+        self._n_env_models = len(metas)
+        self._ck(self._lib.perch_set_env(self._h, C.byref(e), C.cast(m, C.c_void_p), len(metas), _ptr(fp), len(fp)))
+
+    def set_search_cloud(self, xyz, ranges=None, constraint_xyz=None) -> None:
+        """The clouds IsValidPose / the cylinder count search (search_env.cpp:5624-5662); ranges: (R,2) [begin,end)."""
+        pts = _c(xyz, np.float32).reshape(-1, 3)
+        rg = None if ranges is None else _c(ranges, np.int32).reshape(-1, 2)
+        cc = None if constraint_xyz is None else _c(constraint_xyz, np.float32).reshape(-1, 3)
+        self._ck(self._lib.perch_set_search_cloud(self._h, _ptr(pts), len(pts), _ptr(rg), 0 if rg is None else len(rg),
+                                                  _ptr(cc), 0 if cc is None else len(cc)))
+
+    def assemble_states(self, states):
+        """The per-pose loop of GetStateImagesUnifiedGPU (search_env.cpp:1555-1622): returns poses (P,4,4) float32,
+        pose_model_map, pose_segmentation_label, pose_observed_points_total."""
+        from . import states as S
+        st = np.ascontiguousarray(states, dtype=S.STATE_DTYPE)
+        P = len(st)
+        poses = np.zeros((P, 4, 4), np.float32)
+        pmm = np.zeros(P, np.int32)
+        lab = np.zeros(P, np.int32)
+        tot = np.zeros(P, np.float32)
+        self._ck(self._lib.perch_assemble_states(self._h, _ptr(st), P, _ptr(poses), _ptr(pmm), _ptr(lab), _ptr(tot)))
+        return poses, pmm, lab, tot
+
+    def score_states(self, stage: str, states=None, *, stride=1, cost_type=0, calculate_observed_cost=True,
+                     sensor_resolution=0.01, color_distance_threshold=20.0, occlusion_threshold=1.0, do_icp=False,
+                     cloud_capacity=None, icp_max_iterations=0, icp_k_correspondences=0, icp_rotation_epsilon=-1.0,
+                     icp_transformation_epsilon=-1.0):
+        """GetStateImagesUnifiedGPU (search_env.cpp:1505-1717) in one call: assemble the states on the device and run
+        `stage` on them.  states=None scores the list the last generate_states left on the device."""
+        from . import states as S
+        if states is None:
+            st, P = None, self._n_generated
+        else:
+            st = np.ascontiguousarray(states, dtype=S.STATE_DTYPE)
+            P = len(st)
+        prm = perch_params(stride, cost_type, int(bool(calculate_observed_cost)), sensor_resolution, color_distance_threshold,
+                           occlusion_threshold, 0, int(bool(do_icp)), int(icp_max_iterations), int(icp_k_correspondences),
+                           float(icp_rotation_epsilon), float(icp_transformation_epsilon))
+
+        def call(out):
+            return self._lib.perch_score_states(self._h, stage.encode(), _ptr(st), P, C.byref(prm), C.byref(out))
+
+        return self._run_stage(stage, P, prm, call, cloud_capacity)
+
+    def validate_states(self, states, placed=None, after_refinement=False) -> np.ndarray:
+        """EnvObjectRecognition::IsValidPose (search_env.cpp:309-528) per state; returns a bool array."""
+        from . import states as S
+        st = np.ascontiguousarray(states, dtype=S.STATE_DTYPE)
+        pl = None if placed is None or len(placed) == 0 else np.ascontiguousarray(placed, dtype=S.STATE_DTYPE)
+        valid = np.zeros(len(st), np.uint8)
+        self._ck(self._lib.perch_validate_states(self._h, _ptr(st), len(st), _ptr(pl), 0 if pl is None else len(pl),
+                                                 int(bool(after_refinement)), _ptr(valid)))
+        return valid.astype(bool)
+
+    def generate_states(self, placed=None, fetch=True):
+        """The 3-DoF branch of GenerateSuccessorStates (search_env.cpp:7268-7472).  Returns the successor states
+        (states.STATE_DTYPE array; None with fetch=False -- the list stays on the device for score_states(None))."""
+        from . import states as S
+        pl = None if placed is None or len(placed) == 0 else np.ascontiguousarray(placed, dtype=S.STATE_DTYPE)
+        n = C.c_int(0)
+        self._ck(self._lib.perch_generate_states(self._h, _ptr(pl), 0 if pl is None else len(pl), None, 0, C.byref(n)))
+        self._n_generated = n.value
+        if not fetch:
+            return None
+        out = np.zeros(n.value, S.STATE_DTYPE)
+        if n.value:
+            # the list is deterministic: a second pass with a buffer returns the same states
+            self._ck(self._lib.perch_generate_states(self._h, _ptr(pl), 0 if pl is None else len(pl), _ptr(out), n.value,
+                                                     C.byref(n)))
+        return out
+
+    @property
+    def n_generated(self) -> int:
+        return self._n_generated
 
     def gicp(self, poses, pose_model_map, pose_segmentation_label=None, *, stride=1, sensor_resolution=0.01,
              occlusion_threshold=1.0, icp_max_iterations=0, icp_k_correspondences=0, icp_rotation_epsilon=-1.0,

@@ -354,3 +354,65 @@ class Reference:
             C.c_float(sensor_resolution), C.c_float(color_distance_threshold), _p(rc_), _p(oc), _p(dc), C.byref(n_rend))
         assert rc == 0, "ref_cost_from_images failed"
         return {"rendered_cost": rc_, "observed_cost": oc, "points_diff_cost": dc, "n_rend": n_rend.value}
+
+
+class StatesOracle:
+    """oracle/perch_states_oracle.c: CPU restatement of the caller glue (search_env.cpp:309-528, 1505-1622, 7268-7472)."""
+
+    def __init__(self, env, metas, search_xyz=None, ranges=None, constraint_xyz=None):
+        from perception_b200 import states as S
+        self.S = S
+        self.lib = C.CDLL(str(ORACLE_SO))
+        self.lib.oracle_generate_states.restype = C.c_longlong
+        self.lib.oracle_assemble_states.restype = C.c_int
+        self.lib.oracle_validate_states.restype = C.c_int
+        self.env = S.env_struct(env)
+        self.metas, self.fp = S.meta_array(metas)
+        self.n_models = len(metas)
+        self.xyz = np.zeros((0, 3), np.float32) if search_xyz is None else _c(search_xyz, np.float32).reshape(-1, 3)
+        self.ranges = (np.array([[0, len(self.xyz)]], np.int32) if ranges is None else _c(ranges, np.int32).reshape(-1, 2))
+        self.constraint = None if constraint_xyz is None else _c(constraint_xyz, np.float32).reshape(-1, 3)
+
+    def camera_matrix(self):
+        out = np.zeros(16, np.float64)
+        self.lib.oracle_camera_matrix(C.byref(self.env, type(self.env).cam_to_world.offset), _p(out))
+        return out.reshape(4, 4)
+
+    def assemble(self, states, seg_counts=None, observed_point_num=0, num_pixels=640 * 480):
+        st = np.ascontiguousarray(states, dtype=self.S.STATE_DTYPE)
+        P = len(st)
+        sc = np.zeros(1, np.float32) if seg_counts is None else _c(seg_counts, np.float32)
+        poses = np.zeros((P, 4, 4), np.float32)
+        pmm = np.zeros(P, np.int32)
+        lab = np.zeros(P, np.int32)
+        tot = np.zeros(P, np.float32)
+        rc = self.lib.oracle_assemble_states(C.byref(self.env), self.metas, C.c_int(self.n_models), _p(st), C.c_int(P), _p(sc),
+                                             C.c_int(0 if seg_counts is None else len(sc)), C.c_float(observed_point_num),
+                                             C.c_int(num_pixels), _p(self.xyz), _p(self.ranges), C.c_int(len(self.ranges)),
+                                             _p(poses), _p(pmm), _p(lab), _p(tot))
+        assert rc == 0, rc
+        return poses, pmm, lab, tot
+
+    def _search_args(self):
+        nc = 0 if self.constraint is None else len(self.constraint)
+        return (_p(self.fp), _p(self.xyz), _p(self.ranges), C.c_int(len(self.ranges)), _p(self.constraint), C.c_int(nc))
+
+    def validate(self, states, placed=None, after_refinement=False):
+        st = np.ascontiguousarray(states, dtype=self.S.STATE_DTYPE)
+        pl = None if placed is None or len(placed) == 0 else np.ascontiguousarray(placed, dtype=self.S.STATE_DTYPE)
+        valid = np.zeros(len(st), np.uint8)
+        rc = self.lib.oracle_validate_states(C.byref(self.env), self.metas, C.c_int(self.n_models), *self._search_args(),
+                                             _p(st), C.c_int(len(st)), _p(pl), C.c_int(0 if pl is None else len(pl)),
+                                             C.c_int(int(after_refinement)), _p(valid))
+        assert rc == 0, rc
+        return valid.astype(bool)
+
+    def generate(self, placed=None):
+        pl = None if placed is None or len(placed) == 0 else np.ascontiguousarray(placed, dtype=self.S.STATE_DTYPE)
+        args = (C.byref(self.env), self.metas, C.c_int(self.n_models), *self._search_args(), _p(pl),
+                C.c_int(0 if pl is None else len(pl)))
+        n = self.lib.oracle_generate_states(*args, None, C.c_longlong(0))
+        assert n >= 0
+        out = np.zeros(n, self.S.STATE_DTYPE)
+        self.lib.oracle_generate_states(*args, _p(out), C.c_longlong(n))
+        return out
