@@ -277,6 +277,8 @@ def run_ours(args):
             line["gicp"] = gicp_leg(r, wl, out, kw)
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(wl, budget_s=args.cpu_budget)
+        if world == 1 and not args.no_glue:
+            line["glue"] = glue_leg(r, wl, kw)  # last: re-targets the context at a 3-DoF scene
         if world == 1 and not args.no_ref_cuda:
             line["reference_cuda"] = reference_cuda(wl, batch=args.ref_batch)
         emit(line)
@@ -310,6 +312,130 @@ def gicp_leg(r, wl, out, kw, n_top=4096, iterations=20, reps=3):
             "kernel_ms": k_ms, "ms_total": w_s * 1e3, "k_correspondences": 10,
             "mean_iterations_run": float(g["iterations"].mean()), "n_obs": int(wl["n_obs"]),
             "note": "top poses of the scored batch; fixed iteration count (epsilons 0)"}
+
+
+def _quat_from_R(R):
+    """(N,3,3) rotations -> (N,4) quaternions (x, y, z, w), Shepperd's method."""
+    R = np.asarray(R, np.float64)
+    q = np.zeros((len(R), 4))
+    tr = R[:, 0, 0] + R[:, 1, 1] + R[:, 2, 2]
+    for i in range(len(R)):
+        m = R[i]
+        if tr[i] > 0:
+            s = np.sqrt(tr[i] + 1.0) * 2
+            q[i] = [(m[2, 1] - m[1, 2]) / s, (m[0, 2] - m[2, 0]) / s, (m[1, 0] - m[0, 1]) / s, 0.25 * s]
+        else:
+            k = int(np.argmax([m[0, 0], m[1, 1], m[2, 2]]))
+            a, b, c = k, (k + 1) % 3, (k + 2) % 3
+            s = np.sqrt(1.0 + m[a, a] - m[b, b] - m[c, c]) * 2
+            v = np.zeros(4)
+            v[a] = 0.25 * s
+            v[b] = (m[b, a] + m[a, b]) / s
+            v[c] = (m[c, a] + m[a, c]) / s
+            v[3] = (m[c, b] - m[b, c]) / s
+            q[i] = v
+    return q
+
+
+def glue_leg(r, wl, kw, reps=5):
+    """SURVEY 8(f) rows 1-2, measured next to the hot path (N=1):
+    (a) the workload's pose batch as ObjectStates (poses.txt layout: x y z qx qy qz qw, camera frame) through
+        perch_score_states -- matrix assembly + label totals on the device, then the same fused kernel;
+    (b) a 3-DoF scene from nothing: perch_generate_states (grid + IsValidPose on the device) followed by
+        perch_score_states on the resident list, against the CPU restatement of the same two host loops."""
+    from oracle_lib import StatesOracle
+    from perception_b200 import states as S, synth
+    out = {}
+    P, scene = wl["P"], wl["scene"]
+    cam_to_body = np.array([[0, 0, 1, 0], [-1, 0, 0, 0], [0, -1, 0, 0], [0, 0, 0, 1.0]])
+    verts = scene.tris["v"].reshape(-1, 3)
+    if wl["dof6"]:
+        T = wl["poses"].astype(np.float64)
+        q = _quat_from_R(T[:, :3, :3] / 100.0)
+        st = np.zeros(P, S.STATE_DTYPE)
+        st["x"], st["y"], st["z"] = (T[:, k, 3] / 100.0 for k in range(3))
+        st["qx"], st["qy"], st["qz"], st["qw"] = q.T
+        st["segmentation_label_id"] = wl["plabel"] + 1
+        env = S.Env(cam_to_world=np.linalg.inv(cam_to_body), use_external_pose_list=1, min_neighbor_points_for_valid_pose=50)
+        metas = [S.ModelMeta.from_vertices(verts)]
+        r.set_env(env, metas)
+        lab = wl["obs_label"]
+        xyz = wl["obs"]["result_cloud_eigen"]
+        parts, ranges = [xyz], [[0, len(xyz)]]
+        for l in range(int(lab.max()) + 1):
+            pts = xyz[lab == l]
+            ranges.append([ranges[-1][1], ranges[-1][1] + len(pts)])
+            parts.append(pts)
+        r.set_search_cloud(np.concatenate(parts), np.array(ranges, np.int32))
+        r.score_states("COST", st, **kw)
+        t = []
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            o = r.score_states("COST", st, **kw)
+            t.append(time.perf_counter() - t0)
+        ref = r.render_cuda_multi_unified("COST", wl["poses"], wl["pmm"], wl["plabel"], wl["tot"], **kw)
+        t0 = time.perf_counter()
+        valid = r.validate_states(st)
+        t_val = time.perf_counter() - t0
+        orc = StatesOracle(env, metas, np.concatenate(parts), np.array(ranges, np.int32))
+        n_cpu = min(P, 4096)
+        t0 = time.perf_counter()
+        orc.assemble(st[:n_cpu], seg_counts=np.bincount(lab).astype(np.float32))
+        orc.validate(st[:n_cpu])
+        t_cpu = time.perf_counter() - t0
+        out["score_states_6dof"] = {
+            "poses_per_s": P / float(np.median(t)), "ms_per_scene": float(np.median(t)) * 1e3, "states": P,
+            "h2d_bytes_per_step": int(P * 88), "d2h_bytes_per_step": int(P * 24),
+            "rendered_cost_equal_to_matrix_path": float(np.mean(o["rendered_cost"] == ref["rendered_cost"])),
+            "validate_states_per_s": P / t_val, "valid": int(valid.sum()),
+            "cpu_restatement_states_per_s": n_cpu / t_cpu, "cpu_sample": f"assemble + IsValidPose of {n_cpu} states, 1 thread"}
+    # (b) 3-DoF greedy scene: table bounds +-0.3 m at 5 mm, 32 yaws, one model
+    T_table_cam = np.linalg.inv(scene.T_cam_table)
+    cam = (synth.CX, synth.CY, synth.FX, synth.FY, synth.DEPTH_FACTOR)
+    stride = wl["stride"]
+    obs = r.depth2cloud_global(scene.source_depth, scene.source_color, W, H, 1, *cam, stride, None, synth.table_bounds(scene),
+                               T_table_cam)
+    r.set_scene(scene.source_depth, scene.source_color, None)
+    r.set_observed(obs["result_cloud_eigen"], obs["result_cloud_color"], None)
+    zrest = float(scene.model_zrest[0])
+    pre = np.eye(4, dtype=np.float32)
+    pre[2, 3] = zrest
+    vp = (verts.astype(np.float64) + [0, 0, zrest]).astype(np.float32)
+    env = S.Env(cam_to_world=T_table_cam @ np.linalg.inv(cam_to_body), x_min=-0.3, x_max=0.3, y_min=-0.3, y_max=0.3,
+                table_height=0.0, res=0.005, theta_res=np.pi / 16, min_neighbor_points_for_valid_pose=50)
+    metas = [S.ModelMeta.from_vertices(vp, pre)]
+    world = (obs["result_cloud_eigen"].astype(np.float64) @ T_table_cam[:3, :3].T + T_table_cam[:3, 3]).astype(np.float32)
+    world[:, 2] = 0.0
+    r.set_env(env, metas)
+    r.set_search_cloud(world)
+    kw3 = dict(kw, cost_type=0)
+    r.generate_states(fetch=False)
+    r.score_states("COST", None, **kw3)
+    tg, ts = [], []
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        r.generate_states(fetch=False)
+        t1 = time.perf_counter()
+        o = r.score_states("COST", None, **kw3)
+        t2 = time.perf_counter()
+        tg.append(t1 - t0)
+        ts.append(t2 - t1)
+    n_gen = r.n_generated
+    n_cand = 121 * 121 * 32
+    orc = StatesOracle(env, metas, world)
+    t0 = time.perf_counter()
+    gen_cpu = orc.generate()
+    t_cpu_gen = time.perf_counter() - t0
+    assert len(gen_cpu) == n_gen, (len(gen_cpu), n_gen)
+    best = int(np.argmin(np.where(o["rendered_cost"] >= 0, o["rendered_cost"] + o["observed_cost"], 1e9)))
+    out["greedy_3dof"] = {
+        "grid_candidates": n_cand, "valid_states": n_gen, "generate_ms": float(np.median(tg)) * 1e3,
+        "score_ms": float(np.median(ts)) * 1e3, "ms_per_scene": float(np.median(tg) + np.median(ts)) * 1e3,
+        "candidates_per_s": n_cand / float(np.median(tg)), "scored_poses_per_s": n_gen / float(np.median(ts)),
+        "h2d_bytes_per_step": 0, "d2h_bytes_per_step": int(n_gen * 24), "n_obs": int(obs["rendered_cloud_point_num"]),
+        "cpu_restatement_generate_ms": t_cpu_gen * 1e3, "cpu_threads": 1, "best_pose_id": best,
+        "note": "one model, +-0.3 m at 5 mm x 32 yaws; list generated, validated, assembled and scored on the device"}
+    return out
 
 
 def _baseline_inputs(wl):
@@ -460,6 +586,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-cuda", action="store_true")
     ap.add_argument("--no-gicp", action="store_true")
+    ap.add_argument("--no-glue", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
     if args.impl == "reference":
