@@ -300,6 +300,37 @@ int perch_validate_states(perch_ctx* ctx, const perch_state* states, int n_state
 int perch_generate_states(perch_ctx* ctx, const perch_state* placed, int n_placed, perch_state* out_states,
                           int capacity, int* n_out);
 
+/* ==== observed-scene preparation ================================================================ */
+/* The GPU branch of EnvObjectRecognition::SetInput (search_env.cpp:5880-6069) as one call: the decoded input images go
+ * in, the source depth image and the observed cloud stay resident in the context (what perch_set_scene +
+ * perch_depth2cloud + perch_set_observed would do with a host round trip of every buffer in between). */
+typedef struct perch_input {
+    const void* depth;               /* width*height: uint8 when depth_bits == 8 (3-DoF, NDDS images, search_env.cpp:5919)
+                                        or uint16 when 16 (6-DoF, 5890) */
+    int depth_bits;
+    const uint8_t* red;              /* input_color_image_vec[0..2] (5959-5972); each may be NULL */
+    const uint8_t* green;
+    const uint8_t* blue;
+    const uint8_t* predicted_mask;   /* 6-DoF: label mask image (5894-5898), 0 = no object; NULL in 3-DoF */
+    int median_blur_ksize;           /* perch_params_.depth_median_blur (5922): odd, <= 31, applied to 8-bit depth;
+                                        <= 1 = none */
+    float depth_factor;              /* input.depth_factor: depth units per metre of the cloud (6011) */
+    int stride;                      /* gpu_stride */
+    const double* bounds6;           /* 3-DoF: {x_max, x_min, y_max, y_min, table_height + 0.5, table_height}
+                                        (5931-5938); NULL = no bounds filter */
+    const float* camera_transform16; /* with bounds6: (cam_to_world * cam_to_body).cast<float>(), COLUMN-major (5947-5950) */
+    float source_division_factor;    /* input_depth_factor / gpu_depth_factor: the source depth the renderer tests
+                                        occlusion against is depth / factor, truncated (2487-2498); <= 0 = depth as is */
+} perch_input;
+/* Requires perch_set_camera.  *observed_point_num receives the size of the observed cloud. */
+int perch_set_input(perch_ctx* ctx, const perch_input* in, int* observed_point_num);
+/* The observed cloud of the last perch_set_input in the order depth2cloud_global returns it, for the caller's host-side
+ * copies (search_env.cpp:6031-6060): xyz N x 3, colours 3 x N (row stride = *point_num), labels N (NULL allowed;
+ * -1 everywhere in 3-DoF).  capacity = points the buffers hold. */
+int perch_get_observed(perch_ctx* ctx, float* xyz_aos, uint8_t* rgb_soa, int* label, int capacity, int* point_num);
+/* The source depth image as resident after perch_set_input / perch_set_scene (width*height int32). */
+int perch_get_source_depth(perch_ctx* ctx, int32_t* out_depth);
+
 #ifdef __cplusplus
 }
 #endif

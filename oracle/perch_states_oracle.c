@@ -331,3 +331,32 @@ long long oracle_generate_states(const perch_env* env, const perch_model_meta* m
     }
     return n;
 }
+
+/* ---- SetInput's image steps (search_env.cpp:5911-5929, 2487-2498) ---------------------------------------------------- */
+/* cv::medianBlur on CV_8UC1 (search_env.cpp:5922): exact median of the k x k window, BORDER_REPLICATE.  OpenCV is not
+ * part of the reference tree; restated from its documented behaviour (tests pin this against scipy.ndimage). */
+static int cmp_u8(const void* a, const void* b) { return (int)*(const uint8_t*)a - (int)*(const uint8_t*)b; }
+void oracle_median_blur_u8(const uint8_t* in, uint8_t* out, int w, int h, int k) {
+    if (k <= 1) { memcpy(out, in, (size_t)w * h); return; }
+    const int r = k / 2;
+    uint8_t* win = (uint8_t*)malloc((size_t)k * k);
+    for (int y = 0; y < h; ++y)
+        for (int x = 0; x < w; ++x) {
+            int n = 0;
+            for (int dy = -r; dy <= r; ++dy)
+                for (int dx = -r; dx <= r; ++dx) {
+                    int sx = x + dx, sy = y + dy;
+                    sx = sx < 0 ? 0 : (sx >= w ? w - 1 : sx);
+                    sy = sy < 0 ? 0 : (sy >= h ? h - 1 : sy);
+                    win[n++] = in[(size_t)sy * w + sx];
+                }
+            qsort(win, n, 1, cmp_u8);
+            out[(size_t)y * w + x] = win[n / 2];
+        }
+    free(win);
+}
+
+/* input_depth_image_vec[i] /= division_factor: int32 element, float factor (search_env.cpp:2489-2496) */
+void oracle_divide_depth(const int32_t* in, float factor, int32_t* out, int n) {
+    for (int i = 0; i < n; ++i) out[i] = (int32_t)((float)in[i] / factor);
+}

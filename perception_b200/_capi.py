@@ -103,6 +103,23 @@ class perch_env(C.Structure):
     ]
 
 
+class perch_input(C.Structure):
+    _fields_ = [
+        ("depth", C.c_void_p),
+        ("depth_bits", C.c_int),
+        ("red", C.c_void_p),
+        ("green", C.c_void_p),
+        ("blue", C.c_void_p),
+        ("predicted_mask", C.c_void_p),
+        ("median_blur_ksize", C.c_int),
+        ("depth_factor", C.c_float),
+        ("stride", C.c_int),
+        ("bounds6", C.c_void_p),
+        ("camera_transform16", C.c_void_p),
+        ("source_division_factor", C.c_float),
+    ]
+
+
 # name -> (restype, argtypes); the list doubles as the "every symbol of include/perch_b200.h" check in tests
 _P = C.c_void_p
 _V = C.c_void_p
@@ -142,6 +159,9 @@ SIGNATURES = {
     "perch_score_states": (C.c_int, [_P, C.c_char_p, _V, C.c_int, C.POINTER(perch_params), C.POINTER(perch_outputs)]),
     "perch_validate_states": (C.c_int, [_P, _V, C.c_int, _V, C.c_int, C.c_int, _V]),
     "perch_generate_states": (C.c_int, [_P, _V, C.c_int, _V, C.c_int, C.POINTER(C.c_int)]),
+    "perch_set_input": (C.c_int, [_P, C.POINTER(perch_input), C.POINTER(C.c_int)]),
+    "perch_get_observed": (C.c_int, [_P, _V, _V, _V, C.c_int, C.POINTER(C.c_int)]),
+    "perch_get_source_depth": (C.c_int, [_P, _V]),
 }
 
 _lib = None

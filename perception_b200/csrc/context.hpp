@@ -132,6 +132,12 @@ struct perch_ctx {
     // caller glue (capi_states.cu): environment, model metadata, search clouds, assembled / generated state lists
     perch::StatesCtx* states = nullptr;
     int obs_version = 0;               // bumped by perch_set_observed (per-label point counts are cached against it)
+    // perch_set_input (capi_input.cu): the observed cloud in the order depth2cloud_global returns it (for the caller's
+    // host-side copies, search_env.cpp:6031-6060) and the label counts
+    std::vector<float> h_in_xyz;
+    std::vector<uint8_t> h_in_rgb;
+    std::vector<int> h_in_label;
+    bool in_has_label = false;
     void* d_flush = nullptr;           // 256 MiB L2-flush target (perch_l2_flush)
     int flush_value = 0;
     void* h_pinned = nullptr;

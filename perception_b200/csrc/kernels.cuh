@@ -140,4 +140,10 @@ cudaError_t launch_icp_scene(const int32_t* d_depth, int W, int H, const float K
                              cudaStream_t stream);
 cudaError_t launch_icp_point2plane(const IcpArgs& a, int n_clouds, cudaStream_t stream);
 
+// ---- observed-scene preparation (input.cu) -----------------------------------------------------------------------------
+constexpr int kMedianMaxKsize = 31;
+cudaError_t launch_median_blur_u8(const uint8_t* in, uint8_t* out, int w, int h, int ksize, cudaStream_t stream);
+cudaError_t launch_depth_to_i32(const void* in, int bits, int32_t* out, int n, cudaStream_t stream);
+cudaError_t launch_divide_depth(const int32_t* in, float factor, int32_t* out, int n, cudaStream_t stream);
+
 }  // namespace perch

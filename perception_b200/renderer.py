@@ -239,6 +239,51 @@ class Renderer:
             res["result_cloud_pose_map"] = cmap[:n].copy()
         return res
 
+    # -- observed-scene preparation -------------------------------------------------------------------
+    def set_input(self, depth, color=None, predicted_mask=None, *, median_blur_ksize=0, depth_factor=100.0, stride=1,
+                  bounds=None, camera_transform=None, source_division_factor=0.0) -> int:
+        """The GPU branch of EnvObjectRecognition::SetInput (search_env.cpp:5880-6069): depth is the decoded image,
+        uint8 (3-DoF; median-blurred with `median_blur_ksize`) or uint16 (6-DoF); color = 3 planes as
+        input_color_image_vec; bounds = {x_max,x_min,y_max,y_min,z_max,z_min} with camera_transform (4x4, camera optical
+        frame -> world).  Leaves the source depth (depth / source_division_factor) and the observed cloud resident;
+        returns observed_point_num."""
+        from ._capi import perch_input
+        d = np.ascontiguousarray(depth)
+        assert d.dtype in (np.uint8, np.uint16), "depth must be uint8 or uint16"
+        keep = [d.reshape(-1)]
+        inp = perch_input()
+        inp.depth, inp.depth_bits = keep[0].ctypes.data, 8 * d.dtype.itemsize
+        if color is not None:
+            for name, plane in zip(("red", "green", "blue"), color):
+                keep.append(_c(plane, np.uint8).reshape(-1))
+                setattr(inp, name, keep[-1].ctypes.data)
+        if predicted_mask is not None:
+            keep.append(_c(predicted_mask, np.uint8).reshape(-1))
+            inp.predicted_mask = keep[-1].ctypes.data
+        inp.median_blur_ksize, inp.depth_factor, inp.stride = int(median_blur_ksize), float(depth_factor), int(stride)
+        if bounds is not None:
+            keep.append(_c(bounds, np.float64).reshape(6))
+            inp.bounds6 = keep[-1].ctypes.data
+            keep.append(np.ascontiguousarray(np.asarray(camera_transform, np.float32).reshape(4, 4).T).reshape(16))
+            inp.camera_transform16 = keep[-1].ctypes.data
+        inp.source_division_factor = float(source_division_factor)
+        n = C.c_int(0)
+        self._ck(self._lib.perch_set_input(self._h, C.byref(inp), C.byref(n)))
+        return n.value
+
+    def get_observed(self):
+        """The observed cloud of the last set_input, in depth2cloud_global's order: xyz (N,3), rgb (3,N), label (N,)."""
+        n = C.c_int(0)
+        self._ck(self._lib.perch_get_observed(self._h, None, None, None, 0, C.byref(n)))
+        xyz, rgb, lab = np.zeros((n.value, 3), np.float32), np.zeros((3, n.value), np.uint8), np.zeros(n.value, np.int32)
+        self._ck(self._lib.perch_get_observed(self._h, _ptr(xyz), _ptr(rgb), _ptr(lab), n.value, C.byref(n)))
+        return xyz, rgb, lab
+
+    def get_source_depth(self) -> np.ndarray:
+        out = np.zeros((self.height, self.width), np.int32)
+        self._ck(self._lib.perch_get_source_depth(self._h, _ptr(out)))
+        return out
+
     # -- caller glue: ObjectState lists (SURVEY 8(f) rows 1-2; perception_b200/states.py has the host-side types) --------
     def set_env(self, env, metas) -> None:
         """EnvParams / PerchParams fields + per-model ObjectModel metadata (states.Env, list of states.ModelMeta)."""

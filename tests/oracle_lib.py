@@ -416,3 +416,20 @@ class StatesOracle:
         out = np.zeros(n, self.S.STATE_DTYPE)
         self.lib.oracle_generate_states(*args, _p(out), C.c_longlong(n))
         return out
+
+
+def oracle_median_blur_u8(img, k):
+    """oracle_median_blur_u8 (oracle/perch_states_oracle.c): cv::medianBlur restated for CV_8UC1."""
+    lib = C.CDLL(str(ORACLE_SO))
+    a = np.ascontiguousarray(img, np.uint8)
+    out = np.zeros_like(a)
+    lib.oracle_median_blur_u8(_p(a), _p(out), C.c_int(a.shape[1]), C.c_int(a.shape[0]), C.c_int(k))
+    return out
+
+
+def oracle_divide_depth(depth, factor):
+    lib = C.CDLL(str(ORACLE_SO))
+    a = np.ascontiguousarray(depth, np.int32)
+    out = np.zeros_like(a)
+    lib.oracle_divide_depth(_p(a), C.c_float(factor), _p(out), C.c_int(a.size))
+    return out
