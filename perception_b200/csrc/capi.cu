@@ -248,6 +248,24 @@ int prepare_target_normals(perch_ctx* c, int k) {
     int rc;
     if ((rc = upload(&c->d_obs_xyz_aos, c->h_obs_xyz.data(), 3 * (size_t)n, c->stream))) return rc;
     if ((rc = upload<float>(&c->d_tgt_normals, nullptr, 3 * (size_t)n, c->stream))) return rc;
+    {
+        std::vector<float4> xyz4(n);
+        for (int i = 0; i < n; ++i)
+            xyz4[i] = make_float4(c->h_obs_xyz[3 * (size_t)i], c->h_obs_xyz[3 * (size_t)i + 1], c->h_obs_xyz[3 * (size_t)i + 2], 0.f);
+        int n_labels = 0;
+        for (int l : c->h_obs_label) n_labels = std::max(n_labels, l + 1);
+        std::vector<int> range(2 * (size_t)std::max(n_labels, 1), 0);
+        for (int i = 0; i < (int)c->h_obs_label.size(); ++i) {  // labels are sorted ascending
+            const int l = c->h_obs_label[i];
+            if (l < 0) continue;
+            if (range[2 * l + 1] == 0) range[2 * l] = i;
+            range[2 * l + 1] = i + 1;
+        }
+        if ((rc = upload(&c->d_obs_xyz4, xyz4.data(), (size_t)n, c->stream))) return rc;
+        if ((rc = upload(&c->d_label_range, range.data(), range.size(), c->stream))) return rc;
+        CU(cudaStreamSynchronize(c->stream));
+        c->n_label_ranges = n_labels;
+    }
     const int kk = std::min(k, n);
     std::vector<float> soa(3 * (size_t)n);
     for (int i = 0; i < n; ++i)
@@ -337,6 +355,10 @@ int run_gicp(perch_ctx* c, const perch_params* p, const perch::PoseArgs& base, i
     ga.grid = c->grid;
     ga.grid_h = c->grid.inv_h > 0.f ? 1.0f / c->grid.inv_h : 1.f;
     ga.tgt_normals = c->d_tgt_normals;
+    ga.tgt_sorted = c->d_obs_xyz4;
+    ga.label_range = c->d_label_range;
+    ga.n_label_ranges = c->n_label_ranges;
+    ga.stream_max = env_int("PERCH_GICP_STREAM_MAX", 512);
     ga.pose_label = base.pose_label;
     ga.poses_in = base.poses;
     ga.poses_out = reinterpret_cast<perch::Mat4*>(d_poses_out);
@@ -426,7 +448,7 @@ void perch_destroy(perch_ctx* c) {
                     c->d_cl_orig, c->d_cl_low, c->d_cl_high,
                     c->d_src_depth, c->d_src_label, c->d_src_rgb, c->d_grid_pts, c->d_grid_label, c->d_cell_start,
                     c->d_obs_lab, c->d_obs_rgb, c->d_scratch, c->d_err_flag, c->d_flush, c->d_obs_xyz_aos,
-                    c->d_tgt_normals, c->d_gicp, c->d_icp_pcd, c->d_icp_normals};
+                    c->d_tgt_normals, c->d_obs_xyz4, c->d_label_range, c->d_gicp, c->d_icp_pcd, c->d_icp_normals};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);

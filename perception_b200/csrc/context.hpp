@@ -120,6 +120,9 @@ struct perch_ctx {
     // GICP (gicp.cu): target normals are cached per observed cloud; the work buffer grows on demand
     float* d_obs_xyz_aos = nullptr;    // label-sorted observed cloud, N x 3
     float* d_tgt_normals = nullptr;    // N x 3
+    float4* d_obs_xyz4 = nullptr;      // the same cloud as float4 (streaming nearest-neighbour search of short ranges)
+    int* d_label_range = nullptr;      // [begin, end) per label in the sorted cloud
+    int n_label_ranges = 0;
     int tgt_normals_k = 0;             // k the cached normals were computed with (0 = stale)
     void* d_gicp = nullptr;
     size_t gicp_bytes = 0;

@@ -28,7 +28,10 @@
 namespace perch {
 namespace {
 
-constexpr int kGicpThreads = 256;
+#ifndef PERCH_GICP_THREADS
+#define PERCH_GICP_THREADS 32
+#endif
+constexpr int kGicpThreads = PERCH_GICP_THREADS;
 constexpr int kGicpWarps = kGicpThreads / 32;
 constexpr int kMaxRings = 12;        // nearest-neighbour shells searched before falling back to a linear scan
 constexpr float kPlaneEps = 1e-3f;  // fast_gicp RegularizationMethod::PLANE: singular values (1, 1, 1e-3)
@@ -164,6 +167,63 @@ __device__ inline void nn_unbounded(const ObsGridDev& g, float h, float qx, floa
     // 0..r-1 the unvisited cells have rho >= r, hence the bound (r-1)*h used before visiting ring r.
 }
 
+// The same search over a short contiguous range of the label-sorted cloud (a label's points in 6-DoF, the whole cloud
+// in 3-DoF): every lane streams the same points (one broadcast LDG.128 each), no divergence.  Ascending index with a
+// strict `<` keeps the lowest index on ties, so the result is identical to nn_unbounded's.
+__device__ inline void nn_range(const float4* __restrict__ tgt, int lb, int le, float qx, float qy, float qz, float& best,
+                                int& best_ref, float4& best_pt) {
+    best = FLT_MAX;
+    best_ref = -1;
+    int j = lb;
+    for (; j + 4 <= le; j += 4) {
+        const float4 p0 = __ldg(tgt + j), p1 = __ldg(tgt + j + 1), p2 = __ldg(tgt + j + 2), p3 = __ldg(tgt + j + 3);
+        const float d0 = sqdist3(qx, qy, qz, p0.x, p0.y, p0.z), d1 = sqdist3(qx, qy, qz, p1.x, p1.y, p1.z);
+        const float d2 = sqdist3(qx, qy, qz, p2.x, p2.y, p2.z), d3 = sqdist3(qx, qy, qz, p3.x, p3.y, p3.z);
+        if (d0 < best) { best = d0; best_ref = j; }
+        if (d1 < best) { best = d1; best_ref = j + 1; }
+        if (d2 < best) { best = d2; best_ref = j + 2; }
+        if (d3 < best) { best = d3; best_ref = j + 3; }
+    }
+    for (; j < le; ++j) {
+        const float4 p = __ldg(tgt + j);
+        const float d = sqdist3(qx, qy, qz, p.x, p.y, p.z);
+        if (d < best) { best = d; best_ref = j; }
+    }
+    if (best_ref >= 0) best_pt = __ldg(tgt + best_ref);
+}
+
+// k nearest neighbours of point i inside the pose's own cloud (brute force, the point itself included), ascending by
+// (distance, index): the K best live in registers (K is the reference's hard-coded 10 in practice, renderer.cu:1697).
+template <int K>
+__device__ inline int self_knn(const float* pts, int n, int i, int* out_idx) {
+    float bd[K];
+    int bi[K];
+#pragma unroll
+    for (int s = 0; s < K; ++s) { bd[s] = FLT_MAX; bi[s] = -1; }
+    const float px = pts[3 * i], py = pts[3 * i + 1], pz = pts[3 * i + 2];
+    for (int j = 0; j < n; ++j) {
+        const float d = sqdist3(px, py, pz, pts[3 * j], pts[3 * j + 1], pts[3 * j + 2]);
+        if (d >= bd[K - 1]) continue;      // ties keep the earlier (lower) index, like the generic insertion below
+        // insert: shift every slot that is worse than d one place down
+#pragma unroll
+        for (int s = K - 1; s > 0; --s) {
+            const bool shift = bd[s - 1] > d;
+            const bool here = !shift && bd[s] > d;  // first slot from the left whose value exceeds d
+            const float nd = shift ? bd[s - 1] : (here ? d : bd[s]);
+            const int ni = shift ? bi[s - 1] : (here ? j : bi[s]);
+            bd[s] = nd; bi[s] = ni;
+        }
+        if (bd[0] > d) { bd[0] = d; bi[0] = j; }
+    }
+    int cnt = 0;
+#pragma unroll
+    for (int s = 0; s < K; ++s) {
+        out_idx[s] = bi[s];
+        cnt += bi[s] >= 0;
+    }
+    return cnt;
+}
+
 struct Sym3 { float xx, xy, xz, yy, yz, zz; };
 
 // inverse of the symmetric positive definite 2I - w(na na^T + nb nb^T)
@@ -238,7 +298,10 @@ __global__ void pose_count_max_kernel(const int* pose_begin, int rows_per_pose, 
     if ((threadIdx.x & 31) == 0 && n > 0) atomicMax(out, n);
 }
 
-__global__ void __launch_bounds__(kGicpThreads) gicp_kernel(GicpArgs a) {
+#ifndef PERCH_GICP_MIN_BLOCKS
+#define PERCH_GICP_MIN_BLOCKS 1
+#endif
+__global__ void __launch_bounds__(kGicpThreads, PERCH_GICP_MIN_BLOCKS) gicp_kernel(GicpArgs a) {
     extern __shared__ __align__(16) unsigned char gicp_smem[];
     float* s_pts = reinterpret_cast<float*>(gicp_smem);              // 3 x cap
     float* s_nrm = s_pts + 3 * (size_t)a.smem_points;                // 3 x cap
@@ -259,6 +322,14 @@ __global__ void __launch_bounds__(kGicpThreads) gicp_kernel(GicpArgs a) {
     float* nrm = in_smem ? s_nrm : g_nrm;
     const bool use_label = a.pose_label != nullptr;
     const int label = use_label ? a.pose_label[pose_i] : 0;
+    // target range of this pose in the label-sorted cloud; short ranges are searched by streaming (nn_range)
+    int lb = 0, le = a.grid.n_obs;
+    if (use_label) {
+        const bool known = label >= 0 && label < a.n_label_ranges;
+        lb = known ? a.label_range[2 * label] : 0;
+        le = known ? a.label_range[2 * label + 1] : 0;
+    }
+    const bool stream_target = a.tgt_sorted != nullptr && (le - lb) <= a.stream_max;
 
     if (tid < 12) s_T[tid] = (tid == 0 || tid == 4 || tid == 8) ? 1.0 : 0.0;
     if (tid == 0) { s_state = (n == 0) ? 1 : 0; s_iters = 0; }
@@ -269,16 +340,20 @@ __global__ void __launch_bounds__(kGicpThreads) gicp_kernel(GicpArgs a) {
     // ---- source normals: k nearest neighbours within the pose's own cloud (brute force, point itself included) -----
     const int k = min(a.k_correspondences, 32);
     for (int i = tid; i < n; i += kGicpThreads) {
-        float bd[32];
         int bi[32];
         int cnt = 0;
-        const float px = pts[3 * i], py = pts[3 * i + 1], pz = pts[3 * i + 2];
-        for (int j = 0; j < n; ++j) {
-            const float d = sqdist3(px, py, pz, pts[3 * j], pts[3 * j + 1], pts[3 * j + 2]);
-            if (cnt == k && d >= bd[k - 1]) continue;
-            int pos = cnt < k ? cnt++ : k - 1;
-            while (pos > 0 && bd[pos - 1] > d) { bd[pos] = bd[pos - 1]; bi[pos] = bi[pos - 1]; --pos; }
-            bd[pos] = d; bi[pos] = j;
+        if (k == 10) {
+            cnt = self_knn<10>(pts, n, i, bi);
+        } else {
+            float bd[32];
+            const float px = pts[3 * i], py = pts[3 * i + 1], pz = pts[3 * i + 2];
+            for (int j = 0; j < n; ++j) {
+                const float d = sqdist3(px, py, pz, pts[3 * j], pts[3 * j + 1], pts[3 * j + 2]);
+                if (cnt == k && d >= bd[k - 1]) continue;
+                int pos = cnt < k ? cnt++ : k - 1;
+                while (pos > 0 && bd[pos - 1] > d) { bd[pos] = bd[pos - 1]; bi[pos] = bi[pos - 1]; --pos; }
+                bd[pos] = d; bi[pos] = j;
+            }
         }
         float nn[3];
         normal_from_neighbours(pts, bi, cnt, nn);
@@ -303,7 +378,8 @@ __global__ void __launch_bounds__(kGicpThreads) gicp_kernel(GicpArgs a) {
             const float py = R[3] * ax + R[4] * ay + R[5] * az + t[1];
             const float pz = R[6] * ax + R[7] * ay + R[8] * az + t[2];
             float best; int ref; float4 b;
-            nn_unbounded(a.grid, a.grid_h, px, py, pz, use_label, label, best, ref, b);
+            if (stream_target) nn_range(a.tgt_sorted, lb, le, px, py, pz, best, ref, b);
+            else nn_unbounded(a.grid, a.grid_h, px, py, pz, use_label, label, best, ref, b);
             if (ref < 0) continue;  // no target point carries this label
             const float nax = nrm[3 * i], nay = nrm[3 * i + 1], naz = nrm[3 * i + 2];
             const float na[3] = {R[0] * nax + R[1] * nay + R[2] * naz, R[3] * nax + R[4] * nay + R[5] * naz,

@@ -100,6 +100,10 @@ struct GicpArgs {
     ObsGridDev grid;                     // observed cloud (target)
     float grid_h = 0.f;                  // cell size of `grid`
     const float* tgt_normals = nullptr;  // n_obs x 3, indexed like the grid's reference indices
+    const float4* tgt_sorted = nullptr;  // the label-sorted observed cloud itself (index = reference index), or null
+    const int* label_range = nullptr;    // [begin, end) of every label in tgt_sorted (6-DoF)
+    int n_label_ranges = 0;
+    int stream_max = 0;                  // ranges up to this many points are searched by streaming instead of the grid
     const int* pose_label = nullptr;     // null => target unrestricted
     const Mat4* poses_in = nullptr;
     Mat4* poses_out = nullptr;           // T * pose, x100-scaled like the inputs (renderer.cu:1412-1429)

@@ -1,10 +1,11 @@
 """Join an ncu SASS source page (per-instruction counters) with nvdisasm line info of the in-tree cubin, and print the
-hottest source lines.  Usage: python tools/ncu_lines.py REPORT.ncu-rep [kernel-substring] [min-pct]"""
+hottest source lines.  Usage: python tools/ncu_lines.py REPORT.ncu-rep [kernel-substring] [min-pct] [translation-unit]"""
 import csv, re, subprocess, sys, tempfile, os, collections
 
 rep = sys.argv[1]
 ksub = sys.argv[2] if len(sys.argv) > 2 else "pose_kernel<(int)0, (bool)0>"
 minpct = float(sys.argv[3]) if len(sys.argv) > 3 else 0.5
+obj = sys.argv[4] if len(sys.argv) > 4 else "pose_kernels"  # translation unit the kernel lives in (csrc/<obj>.cu)
 root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "sass"], capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
@@ -13,7 +14,7 @@ ie, si = hdr.index("Instructions Executed"), hdr.index("# Samples")
 stall_cols = {h: i for i, h in enumerate(hdr) if h.startswith("stall_") and "Not Issued" not in h}
 inst = [(r[1], float(r[ie] or 0), float(r[si] or 0), {h: float(r[i] or 0) for h, i in stall_cols.items()}) for r in rows[2:] if len(r) > ie]
 tmp = tempfile.mkdtemp()
-subprocess.run(["cuobjdump", "-xelf", "pose_kernels", os.path.join(root, "perception_b200/libperch_b200.so")], cwd=tmp, capture_output=True)
+subprocess.run(["cuobjdump", "-xelf", obj, os.path.join(root, "perception_b200/libperch_b200.so")], cwd=tmp, capture_output=True)
 cub = [f for f in os.listdir(tmp) if f.endswith(".cubin")][0]
 dis = subprocess.run(["nvdisasm", "--print-line-info", os.path.join(tmp, cub)], capture_output=True, text=True).stdout
 # split per function
@@ -40,9 +41,9 @@ if len(lines) != len(inst):
 tot_i = sum(a for _, a, _, _ in inst); tot_s = sum(s for _, _, s, _ in inst)
 agg = collections.OrderedDict()
 for (loc, _), (_, a, s, st) in zip(lines, inst):
-    key = loc[2] if (loc and loc[2] and loc[2][0] == "pose_kernels.cu") else (loc[0], loc[1]) if loc else ("?", 0)
+    key = loc[2] if (loc and loc[2] and loc[2][0] == (obj + ".cu")) else (loc[0], loc[1]) if loc else ("?", 0)
     # attribute to outermost pose_kernels.cu line where possible
-    if loc and loc[0] != "pose_kernels.cu" and loc[2]:
+    if loc and loc[0] != (obj + ".cu") and loc[2]:
         key = loc[2]
     elif loc:
         key = (loc[0], loc[1])
@@ -50,13 +51,13 @@ for (loc, _), (_, a, s, st) in zip(lines, inst):
     e[0] += a; e[1] += s
     for h, v in st.items():
         e[2][h] += v
-src = open(os.path.join(root, "perception_b200/csrc/pose_kernels.cu")).read().splitlines()
+src = open(os.path.join(root, "perception_b200/csrc/" + obj + ".cu")).read().splitlines()
 print(f"total warp-instr {tot_i:.3e}, samples {tot_s:.0f}")
 for key in sorted(agg, key=lambda k: (k[0], k[1])):
     a, s, st = agg[key]
     if 100 * a / tot_i >= minpct or 100 * s / tot_s >= minpct:
         top = ",".join(f"{h[6:]}:{100*v/max(s,1):.0f}" for h, v in st.most_common(3))
-        text = src[key[1] - 1].strip()[:90] if key[0] == "pose_kernels.cu" and 0 < key[1] <= len(src) else ""
+        text = src[key[1] - 1].strip()[:90] if key[0] == (obj + ".cu") and 0 < key[1] <= len(src) else ""
         print(f"{key[0]}:{key[1]:<5} inst {100*a/tot_i:5.1f}%  samp {100*s/tot_s:5.1f}%  [{top}]  {text}")
 
 # ---- segments between barriers -------------------------------------------------------------------------------
@@ -70,7 +71,7 @@ def flush():
 for (loc, txt), (_, a, s, st) in zip(lines, inst):
     seg_a += a; seg_s += s
     for h, v in st.items(): st_acc[h] += v
-    if loc and loc[0] == "pose_kernels.cu":
+    if loc and loc[0] == (obj + ".cu"):
         lo = min(lo, loc[1]); hi = max(hi, loc[1])
     if "BAR.SYNC" in txt:
         flush()

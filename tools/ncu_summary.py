@@ -1,8 +1,9 @@
 """Write profiles/<name>.md from an ncu --set full report: headline metrics of the profiled kernel plus the
 per-source-line / per-barrier-segment breakdown of tools/ncu_lines.py.
-Usage: python tools/ncu_summary.py REPORT.ncu-rep NAME 'kernel substring' 'command that was profiled'"""
+Usage: python tools/ncu_summary.py REPORT.ncu-rep NAME 'kernel substring' 'command that was profiled' [translation unit]"""
 import csv, subprocess, sys, os, json
 rep, name, ksub, cmd = sys.argv[1:5]
+obj = sys.argv[5] if len(sys.argv) > 5 else "pose_kernels"
 root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(out.splitlines()))
@@ -38,7 +39,7 @@ def to_bytes(w):
 traffic = to_bytes("dram__bytes_read.sum") + to_bytes("dram__bytes_write.sum")
 lines += ["", f"DRAM traffic of this launch: {traffic:.0f} bytes (read + write).", "",
           "## Hot source lines and barrier segments (tools/ncu_lines.py)", "", "```"]
-lines += subprocess.run([sys.executable, os.path.join(root, "tools/ncu_lines.py"), rep, ksub, "1.0"], capture_output=True, text=True).stdout.splitlines()
+lines += subprocess.run([sys.executable, os.path.join(root, "tools/ncu_lines.py"), rep, ksub, "1.0", obj], capture_output=True, text=True).stdout.splitlines()
 lines += ["```", ""]
 open(os.path.join(root, "profiles", name + ".md"), "w").write("\n".join(lines))
 print(json.dumps({"traffic_bytes_per_launch": traffic, "kernel_ms": got.get("gpu__time_duration.sum")}))
