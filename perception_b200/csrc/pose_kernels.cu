@@ -39,7 +39,14 @@ constexpr int kClaimMaxTris = (kClaim + 8) * 4;  // most candidates one claim ca
 static_assert(kClusterTris == 4, "lane mapping of the per-triangle test assumes 4 triangles per cluster");
 constexpr int kBigCells = 48;     // lattice pixels above which a triangle is rasterised by the whole CTA
 constexpr int kBigCap = 64;
-constexpr float kEps = 0.02f;     // pixels; bound on |approximate - exact| screen coordinates in the candidate test
+// Bounds on |approximate - exact| screen coordinates (pixels) assumed by the culling levels.  tools/approx_error.cu
+// measures the actual difference: <= 1.3e-3 px over 2e8 in-view vertices of objects 0.2-3 m away, <= 1.9e-4 px beyond;
+// it grows like 1/z for vertices close to the camera plane, so a vertex with |z| <= kNearZ (pose units, cm) sends its
+// triangle to the exact path untested, and level 3 scales its bound by max(1, kRefZ / |z|).
+constexpr float kEps = 0.02f;     // levels 1 and 2 (bbox tests)
+constexpr float kEps3 = 0.006f;   // level 3 (edge-function test)
+constexpr float kNearZ = 1.0f;
+constexpr float kRefZ = 5.0f;
 
 __device__ __forceinline__ float __frcp_approx(float x) {
     float r;
@@ -378,20 +385,59 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
             auto tri_hits = [&](int t) -> bool {
                 float v[9];
                 load_tri(a.models, t, v);
-                float ux[3], uy[3];
+                float ux[3], uy[3], iz[3];
 #pragma unroll
                 for (int k = 0; k < 3; ++k) {
                     const float x = v[3 * k], y = v[3 * k + 1], z = v[3 * k + 2];
                     const float n0 = fmaf(z, U2, fmaf(y, U1, fmaf(x, U0, U3)));
                     const float n1 = fmaf(z, V2, fmaf(y, V1, fmaf(x, V0, V3)));
-                    const float iz = __frcp_approx(fmaf(z, C2, fmaf(y, C1, fmaf(x, C0, C3))));
-                    ux[k] = fmaf(n0, iz, offx);
-                    uy[k] = fmaf(n1, iz, offy);
+                    iz[k] = __frcp_approx(fmaf(z, C2, fmaf(y, C1, fmaf(x, C0, C3))));
+                    ux[k] = fmaf(n0, iz[k], offx);
+                    uy[k] = fmaf(n1, iz[k], offy);
                 }
                 float sum = (ux[0] + ux[1]) + (ux[2] + uy[0]) + (uy[1] + uy[2]);
                 if (!(fabsf(sum) < 1e30f)) return true;
+                if (!(fmaxf(fmaxf(fabsf(iz[0]), fabsf(iz[1])), fabsf(iz[2])) < 1.0f / kNearZ)) return true;  // near the camera plane
                 return lattice_hit(fminf(fminf(ux[0], ux[1]), ux[2]), fmaxf(fmaxf(ux[0], ux[1]), ux[2]),
                                    fminf(fminf(uy[0], uy[1]), uy[2]), fmaxf(fmaxf(uy[0], uy[1]), uy[2]));
+            };
+            // Level 3 (start of pass B, every lane busy): a candidate whose approximate bbox holds exactly ONE lattice
+            // pixel is dropped when that pixel lies clearly outside the triangle.  With approximate vertices within
+            // d px of the exact ones, an edge function cross(Vj - Vi, P - Vi) differs from its exact counterpart
+            // by less than 4.25 * d * D (D >= the largest distance involved; d = kEps3 scaled for near vertices), so `sgn * E < -6 d D` together with
+            // `|2 * area| > 6 d D` (the orientation is then certain) implies a strictly negative exact barycentric, i.e.
+            // the reference rejects the fragment (image_renderer.cuh:114-115).  NaN makes every comparison false: kept.
+            auto pixel_outside = [&](int t) -> bool {
+                float v[9];
+                load_tri(a.models, t, v);
+                float ux[3], uy[3], iz[3];
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    const float x = v[3 * k], y = v[3 * k + 1], z = v[3 * k + 2];
+                    const float n0 = fmaf(z, U2, fmaf(y, U1, fmaf(x, U0, U3)));
+                    const float n1 = fmaf(z, V2, fmaf(y, V1, fmaf(x, V0, V3)));
+                    iz[k] = __frcp_approx(fmaf(z, C2, fmaf(y, C1, fmaf(x, C0, C3))));
+                    ux[k] = fmaf(n0, iz[k], offx);
+                    uy[k] = fmaf(n1, iz[k], offy);
+                }
+                const float near_scale = fmaxf(1.f, kRefZ * fmaxf(fmaxf(fabsf(iz[0]), fabsf(iz[1])), fabsf(iz[2])));
+                const float minx = fminf(fminf(ux[0], ux[1]), ux[2]), maxx = fmaxf(fmaxf(ux[0], ux[1]), ux[2]);
+                const float miny = fminf(fminf(uy[0], uy[1]), uy[2]), maxy = fmaxf(fmaxf(uy[0], uy[1]), uy[2]);
+                const float lo_x = fmaxf(minx - m_lo, band_lo_x), hi_x = fminf(maxx + m_hi, band_hi_x);
+                const float lo_y = fmaxf(miny - m_lo, band_lo_y), hi_y = fminf(maxy + m_hi, band_hi_y);
+                const float px = ceilf(lo_x - 1e-3f), py = ceilf(lo_y - 1e-3f);
+                // exactly one integer in [lo - 1e-3, hi] along each axis
+                const bool single = (px <= hi_x) && (px + 1.f > hi_x) && (py <= hi_y) && (py + 1.f > hi_y);
+                const float ax = ux[1] - ux[0], ay = uy[1] - uy[0], bx = ux[2] - ux[0], by = uy[2] - uy[0];
+                const float area2 = ax * by - bx * ay;
+                const float sgn = area2 < 0.f ? -1.f : 1.f;
+                const float e0 = ax * (py - uy[0]) - ay * (px - ux[0]);
+                const float e1 = (ux[2] - ux[1]) * (py - uy[1]) - (uy[2] - uy[1]) * (px - ux[1]);
+                const float e2 = -bx * (py - uy[2]) + by * (px - ux[2]);
+                const float D = (maxx - minx) + (maxy - miny) + 1.2f * inv_s;
+                const float tol = (6.f * kEps3 * inv_s) * near_scale * D;
+                const float worst = fminf(fminf(e0 * sgn, e1 * sgn), e2 * sgn);
+                return single && (fabsf(area2) > tol) && (worst < -tol) && (tol < 1e6f);
             };
             // per-triangle test of 8 pending clusters (4 lanes each); candidates go to the shared queue
             int nstage = 0;  // warp-uniform: staged candidates of this warp
@@ -459,9 +505,27 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                 __syncthreads();
                 const int qn = s_qcount;
                 const bool all_claimed = *(volatile int*)&s_next >= n_groups;
-                // pass B: exact rasterisation of the candidates, one triangle per thread; triangles covering many
-                // lattice pixels are deferred to the cooperative pass
-                for (int e = tid; e < qn; e += kThreads) {
+                // pass B: every warp owns a contiguous slice of the queue.  First the level-3 test with in-place,
+                // warp-local compaction (writes land at or before the entries already read), then the exact
+                // rasterisation of the survivors, one triangle per thread; triangles covering many lattice pixels are
+                // deferred to the cooperative pass.
+                const int per_warp = (qn + kWarps - 1) / kWarps;
+                const int w0 = min((tid >> 5) * per_warp, qn), w1 = min(w0 + per_warp, qn);
+                int kept = 0;  // warp-uniform
+                for (int e0 = w0; e0 < w1; e0 += 32) {
+                    const int e = e0 + lane;
+                    int t = -1;
+                    bool keep = false;
+                    if (e < w1) {
+                        t = queue[e];
+                        keep = !pixel_outside(t);
+                    }
+                    const unsigned kb = __ballot_sync(0xffffffffu, keep);
+                    if (keep) queue[w0 + kept + __popc(kb & lt_mask)] = t;
+                    kept += __popc(kb);
+                }
+                __syncwarp();
+                for (int e = w0 + lane; e < w0 + kept; e += 32) {
                     int t = queue[e];
                     if (raster_tri(t, false, true)) {
                         int bslot = atomicAdd(&s_bigcount, 1);
