@@ -380,6 +380,63 @@ def test_non_finite_vertices_and_degenerate_triangles(orc):
     assert np.array_equal(out["result_color"], c_o)
 
 
+@pytest.mark.parametrize("stage", ["RENDER", "COST"])
+def test_edge_grazing_triangles(orc, stage):
+    """Adversarial input for the culling levels (pose_kernels.cu pass A / level 3): small triangles whose edges pass
+    within 0 ... 0.05 px of the one pixel their bounding box holds, near-degenerate slivers, and triangles with a vertex
+    on a pixel centre.  Whether such a fragment exists is decided by the reference's float sequence alone (oracle): the
+    approximate tests may only ever drop triangles that sequence rejects."""
+    from perception_b200.renderer import make_triangles, pose_to_mat4x4
+    case = make_case(600, 3, 42)
+    W, H, P = case.width, case.height, case.proj
+    rng = np.random.default_rng(11)
+    step = 1 if stage == "RENDER" else 4
+    n = 6000
+    px = rng.integers(8, W // step - 8, n) * step
+    py = (H - 1) - rng.integers(8, H // step - 8, n) * step           # raster row of a lattice image row (image row = H-1-P1)
+    Z = rng.uniform(40.0, 90.0, n)                                    # cm
+    eps = rng.choice([0.0, 1e-5, 1e-4, 1e-3, 1e-2, 0.05, 0.3], n) * rng.choice([-1.0, 1.0], n)
+    ang = rng.uniform(0, 2 * np.pi, n)
+    size = rng.uniform(0.3, 0.9, n)
+    sliver = rng.uniform(size=n) < 0.2
+    # an edge through (px, py) + eps * normal, direction `ang`; third vertex on either side
+    d = np.stack([np.cos(ang), np.sin(ang)], 1)
+    nrm = np.stack([-d[:, 1], d[:, 0]], 1)
+    c = np.stack([px, py], 1).astype(np.float64) + eps[:, None] * nrm
+    a = c - d * size[:, None] * rng.uniform(0.2, 1.0, n)[:, None]
+    b = c + d * size[:, None] * rng.uniform(0.2, 1.0, n)[:, None]
+    third = c + nrm * np.where(sliver, 1e-3, size)[:, None] * rng.choice([-1.0, 1.0], n)[:, None] + d * rng.uniform(-0.3, 0.3, n)[:, None]
+    on_vertex = rng.uniform(size=n) < 0.1
+    a[on_vertex] = np.stack([px, py], 1)[on_vertex]
+    scr = np.stack([a, b, third], 1)                                  # (n, 3, 2) screen coordinates (raster rows)
+    # un-project: sx = (P.a0*X + P.a2*Z)/Z * W/2 + W/2, sy likewise with row b (image_renderer.cuh:82-84)
+    X = ((scr[..., 0] - W / 2) / (W / 2) - P[0, 2]) * Z[:, None] / P[0, 0]
+    Y = ((scr[..., 1] - H / 2) / (H / 2) - P[1, 2]) * Z[:, None] / P[1, 1]
+    verts = np.stack([X, Y, np.broadcast_to(Z[:, None], X.shape)], -1) / 100.0   # metres; pose scales by 100
+    tris = make_triangles(verts.astype(np.float32), rng.integers(0, 255, (n, 3)))
+    counts = np.array([n], np.int32)
+    poses = pose_to_mat4x4(np.eye(4))[None]
+    pmm = np.zeros(1, np.int32)
+    src = np.zeros((H, W), np.int32)
+    with make_renderer(case) as r:
+        r.set_models(tris, counts)
+        r.set_scene(src)
+        if stage == "RENDER":
+            out = r.render_cuda_multi_unified("RENDER", poses, pmm)
+            d_o, c_o = orc.render(tris, counts, poses, pmm, W, H, P, src, None, None, 1.0)
+            assert 500 < (d_o > 0).sum() < n
+            assert np.array_equal(out["result_depth"], d_o)
+            assert np.array_equal(out["result_color"], c_o)
+        else:
+            out = r.render_cuda_multi_unified("CLOUD", poses, pmm, stride=step)
+            d_o, c_o = orc.render(tris, counts, poses, pmm, W, H, P, src, None, None, 1.0)
+            want = orc.depth2cloud(d_o[0], c_o[:, 0], W, H, 1, case.cx, case.cy, case.fx, case.fy, 100.0, step)
+            assert want["n"] > 300
+            assert out["result_cloud_point_num"] == want["n"]
+            assert np.array_equal(out["result_cloud"], want["soa"])
+            assert np.array_equal(out["result_cloud_color"], want["rgb"])
+
+
 def test_pose_permutation_and_duplicates(orc):
     """Poses are independent units: permuting the pose list permutes the results, a duplicated pose scores the same."""
     case, obs, poses, pmm, lab, tot = _cost_case(orc, 2000, 8, True, 32)
