@@ -214,11 +214,12 @@ def run_ours(args):
     h_poses, h_pmm, h_tot = pin(wl["poses"]), pin(wl["pmm"]), pin(wl["tot"])
     h_lab = pin(wl["plabel"]) if wl["plabel"] is not None else None
     K_TOP = 8
+    exchange = sharding.HitExchange(1, K_TOP)
 
     def e2e_step():
         out = r.render_cuda_multi_unified("COST", h_poses, h_pmm, h_lab, h_tot, **kw)
         hits = topk(out["rendered_cost"], out["observed_cost"], h_pmm, 1, k=K_TOP, pose_id_offset=rank * P)
-        best = sharding.merge_hits(sharding.gather_hits(hits), K_TOP)[0, 0]  # all_gather of k x 16 B per rank
+        best = sharding.merge_hits(exchange.gather(hits), K_TOP)[0, 0]  # all_gather of k x 16 B per rank
         return out, best
 
     for _ in range(max(1, min(args.warmup, 3))):

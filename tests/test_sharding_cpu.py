@@ -58,6 +58,10 @@ def _worker(rank, world, port, n, n_models, k, q):
         lo, hi = sharding.shard_range(n, rank, world)
         hits = topk(rendered[lo:hi], observed[lo:hi], pmm[lo:hi], n_models, k=k, pose_id_offset=lo)
         merged = sharding.merge_hits(sharding.gather_hits(hits), k)
+        # the preallocated exchange bench.py uses gives the same records, step after step
+        ex = sharding.HitExchange(n_models, k)
+        for _ in range(3):
+            assert np.array_equal(sharding.merge_hits(ex.gather(hits), k), merged)
         q.put((rank, merged.tobytes()))
     finally:
         dist.destroy_process_group()
