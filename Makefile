@@ -19,6 +19,11 @@ $(CSRC)/clusters.o: $(CSRC)/clusters.cpp $(CSRC)/clusters.hpp
 $(LIB): $(OBJS)
 	$(NVCC) $(ARCH) -shared -o $@ $(OBJS)
 
+# Debug variant with per-level survivor counters in the per-pose kernel (tools/pose_stats.py); never the product.
+stats: $(OBJS)
+	$(NVCC) $(NVFLAGS) -DPERCH_STATS -c $(CSRC)/pose_kernels.cu -o $(CSRC)/pose_kernels_stats.o
+	$(NVCC) $(ARCH) -shared -o perception_b200/libperch_b200_stats.so $(CSRC)/pose_kernels_stats.o $(filter-out $(CSRC)/pose_kernels.o,$(OBJS))
+
 oracle:
 	$(MAKE) -C oracle
 
@@ -26,4 +31,4 @@ clean:
 	rm -f $(OBJS) $(LIB)
 	$(MAKE) -C oracle clean
 
-.PHONY: all oracle clean
+.PHONY: all oracle clean stats

@@ -172,7 +172,8 @@ def load_library(path: os.PathLike | None = None) -> C.CDLL:
     global _lib
     if _lib is not None and path is None:
         return _lib
-    p = Path(path) if path else LIB_PATH
+    # PERCH_B200_LIB: another build of the same library (tools/: A/B runs of kernel variants, the counters build)
+    p = Path(path) if path else Path(os.environ.get("PERCH_B200_LIB", LIB_PATH))
     if not p.exists():
         raise ImportError(
             f"{p} not found: build it with `make` (nvcc, sm_100a). perception_b200 has no CPU fallback."

@@ -54,6 +54,14 @@ __device__ __forceinline__ float __frcp_approx(float x) {
     return r;
 }
 
+#ifdef PERCH_STATS
+// Counters build only (`make stats`, tools/pose_stats.py): survivors of each culling level, summed over all poses.
+__device__ unsigned long long g_stats[16];
+#define STAT(i, v) atomicAdd(&g_stats[i], (unsigned long long)(v))
+#else
+#define STAT(i, v) ((void)0)
+#endif
+
 template <bool COLOR> struct ZCell;
 template <> struct ZCell<false> {
     using type = unsigned int;
@@ -329,6 +337,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                 if (x0 > x1 || y0 > y1) return false;
                 const int w = x1 - x0 + 1, cells = w * (y1 - y0 + 1);
                 if (allow_defer && cells > kBigCells) return true;  // caller re-queues it for the cooperative pass
+                if (!coop || tid == 0) { STAT(4, 1); STAT(5, cells); if (coop) STAT(7, 1); }
                 TriSetup ts;
                 setup_edges(A, B, C, ts);
                 const uint32_t id = COLOR ? (uint32_t)__ldg(a.models.cl_orig + t) : 0u;  // original triangle index
@@ -343,8 +352,10 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                     for (int ly = y0; ly <= y1; ++ly)
                         for (int lx = x0; lx <= x1; ++lx) {
                             int32_t d;
-                            if (fragment_depth(ts, (float)(lx * s), (float)(H - 1 - ly * s), d))
+                            if (fragment_depth(ts, (float)(lx * s), (float)(H - 1 - ly * s), d)) {
                                 atomicMin(&zbuf[(ly - by0) * tile_w + (lx - rx0)], Z::make(d, id));
+                                STAT(6, 1);
+                            }
                         }
                 }
                 return false;
@@ -454,6 +465,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                 const unsigned ballot = __ballot_sync(0xffffffffu, hit);
                 if (hit) wstage[nstage + __popc(ballot & lt_mask)] = t;
                 nstage += __popc(ballot);
+                if (lane == 0) { STAT(2, __popc(ballot)); STAT(8, 1); }
                 if (nstage >= 32) {
                     __syncwarp();
                     int slot = 0;
@@ -487,6 +499,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                     if (keep0) wpend[npend + __popc(b0 & lt_mask)] = c0;
                     if (keep1) wpend[npend + __popc(b0) + __popc(b1 & lt_mask)] = c1;
                     npend += __popc(b0) + __popc(b1);
+                    if (lane == 0) { STAT(0, min(kClaim, cl_high - (cl_low + g * kClaim))); STAT(1, __popc(b0) + __popc(b1)); }
                     __syncwarp();
                     while (npend >= 8) {
                         npend -= 8;
@@ -521,6 +534,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                         keep = !pixel_outside(t);
                     }
                     const unsigned kb = __ballot_sync(0xffffffffu, keep);
+                    if (lane == 0) { STAT(3, __popc(kb)); STAT(9, 1); }
                     if (keep) queue[w0 + kept + __popc(kb & lt_mask)] = t;
                     kept += __popc(kb);
                 }
@@ -539,8 +553,10 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                 __syncthreads();
                 if (tid == 0) { s_qcount = 0; s_bigcount = 0; }
                 __syncthreads();
+                if (tid == 0) STAT(10, 1);
                 if (all_claimed) break;
             }
+            if (tid == 0) { STAT(11, 1); STAT(12, band_cells); }
 
             if (MODE == MODE_IMAGE) {
                 // ---- 3'. resolve the band into the output images (or into the shared key image) -------------
@@ -713,3 +729,14 @@ cudaError_t launch_resolve_single(const PoseArgs& a, cudaStream_t stream) {
 }
 
 }  // namespace perch
+
+#ifdef PERCH_STATS
+extern "C" int perch_debug_stats(unsigned long long* out16, int reset) {
+    if (out16 && cudaMemcpyFromSymbol(out16, perch::g_stats, sizeof(perch::g_stats)) != cudaSuccess) return 1;
+    if (reset) {
+        unsigned long long z[16] = {0};
+        if (cudaMemcpyToSymbol(perch::g_stats, z, sizeof(z)) != cudaSuccess) return 1;
+    }
+    return 0;
+}
+#endif
