@@ -328,8 +328,45 @@ int perch_set_input(perch_ctx* ctx, const perch_input* in, int* observed_point_n
  * copies (search_env.cpp:6031-6060): xyz N x 3, colours 3 x N (row stride = *point_num), labels N (NULL allowed;
  * -1 everywhere in 3-DoF).  capacity = points the buffers hold. */
 int perch_get_observed(perch_ctx* ctx, float* xyz_aos, uint8_t* rgb_soa, int* label, int capacity, int* point_num);
-/* The source depth image as resident after perch_set_input / perch_set_scene (width*height int32). */
+/* The source depth image the occlusion rule currently tests against: as resident after perch_set_input /
+ * perch_set_scene, or as composed by perch_compose_source (width*height int32). */
 int perch_get_source_depth(perch_ctx* ctx, int32_t* out_depth);
+
+/* The label image the occlusion rule currently tests against (width*height uint8); *has_label = 0 and the buffer
+ * untouched when there is none. */
+int perch_get_source_label(perch_ctx* ctx, uint8_t* out_label, int* has_label);
+
+/* ==== composition mode =========================================================================== */
+/* Multi-object states: the objects already placed are rendered into the source image the occlusion rule of
+ * perch_render_cost tests against (image_renderer.cuh:163-186), so the next object is scored with the placed ones
+ * occluding it.  The reference does this through the host: the state's objects are rendered with
+ * single_result_image = 1 against an empty source (PrintStateGPU, search_env.cpp:1718-1781; the "GPU + Tree" flow of
+ * the deprecated ComputeCostsInParallelGPU, 2054-2460) and the image goes back in as the next call's source_depth.
+ * Here the composed image never leaves the device.
+ *   PERCH_COMPOSE_REPLACE  source := the placed objects alone, 0 elsewhere (the reference's tree flow)
+ *   PERCH_COMPOSE_MERGE    source := per pixel the nearer of the OBSERVED source image and the placed objects
+ *   PERCH_COMPOSE_NONE     back to the observed image (perch_set_scene / perch_set_input do the same)
+ * pose_label (may be NULL): 0-based segmentation label per placed pose; a pixel owned by pose i then carries source
+ * label pose_label[i] + 1, otherwise 0 (a label no candidate shares: the pixel occludes every candidate).  The base of
+ * a MERGE is always the observed image, so composing again replaces the previous composition. */
+enum { PERCH_COMPOSE_NONE = 0, PERCH_COMPOSE_REPLACE = 1, PERCH_COMPOSE_MERGE = 2 };
+int perch_compose_source(perch_ctx* ctx, const float* poses16, int n_poses, const int* pose_model_map,
+                         const int* pose_label, int mode);
+/* Per-pose outputs of the reference's USE_TREE / USE_CLUTTER branches (image_renderer.cuh:187-206, 467-482; compiled
+ * out in the reference as shipped, model.h:17-18), on the full-resolution render of every pose against the current
+ * source image:
+ *   pose_occluded[p]        1 iff the render lies in front of a source pixel by more than the rule's gate
+ *   pose_occluded_other[p]  1 iff a source pixel hides (clears) a rendered pixel
+ *   clutter_cost[p]         100 * cleared pixels / covered pixels, NaN if nothing is covered (the reference's extra
+ *                           condition `source <= new_depth - 5` reads the pixel after it was set to INT_MAX and
+ *                           therefore always holds, image_renderer.cuh:183-195; pinned by tests/golden/tree_single_tri)
+ *   total_points[p]         covered pixels
+ * evaluated per covered pixel on its minimum depth.  The reference evaluates them per fragment on the running minimum,
+ * which depends on the order fragments arrive in (and races); both agree when a pixel receives one fragment.
+ * pose_label NULL = 3-DoF gate (|d - s| > occlusion_threshold), else the 6-DoF gate.  Any output may be NULL. */
+int perch_tree_flags(perch_ctx* ctx, const float* poses16, int n_poses, const int* pose_model_map, const int* pose_label,
+                     float occlusion_threshold, int* pose_occluded, int* pose_occluded_other, float* clutter_cost,
+                     float* total_points);
 
 #ifdef __cplusplus
 }

@@ -75,12 +75,23 @@ void oracle_compute_proj(const float* K, int width, int height, float near_, flo
  *
  * out_* are P*W*H (W*H when single_result_image).  pose_label NULL => 3-DoF occlusion rule.
  */
-void oracle_render(const tri64* tris, int n_tris, const float* poses16, int n_poses, const int* pose_model_map,
-                   const int* tris_model_count, int n_models, int width, int height, const float* proj16,
-                   const int32_t* source_depth, const uint8_t* source_label, const int* pose_label,
-                   float occlusion_threshold, int single_result_image, int32_t* out_depth, uint8_t* out_r,
-                   uint8_t* out_g, uint8_t* out_b) {
+/* Optional per-pose outputs of the USE_TREE / USE_CLUTTER branches (image_renderer.cuh:187-206), two readings:
+ *  serial_*: exactly what the per-fragment code yields when fragments arrive in triangle order (ONE legal execution of
+ *            the kernel; pose_occluded_other and the clutter count depend on that order);
+ *  canon_*:  per covered pixel on its minimum depth -- order independent; what libperch_b200 computes.
+ * The two agree wherever a pixel receives at most one fragment per pose.  Counts are raw (no division). */
+typedef struct {
+    int* serial_occluded; int* serial_occluded_other; float* serial_clutter; float* serial_total;
+    int* canon_occluded; int* canon_occluded_other; float* canon_clutter; float* canon_total;
+} tree_out;
+
+static void render_impl(const tri64* tris, int n_tris, const float* poses16, int n_poses, const int* pose_model_map,
+                        const int* tris_model_count, int n_models, int width, int height, const float* proj16,
+                        const int32_t* source_depth, const uint8_t* source_label, const int* pose_label,
+                        float occlusion_threshold, int single_result_image, int32_t* out_depth, uint8_t* out_r,
+                        uint8_t* out_g, uint8_t* out_b, const tree_out* tree) {
     const size_t npx = (size_t)width * height;
+    int32_t* min_entry = tree ? (int32_t*)malloc(sizeof(int32_t) * npx) : NULL; /* min over fragments, never cleared */
     const size_t n_img = single_result_image ? 1 : (size_t)n_poses;
     /* image_renderer.cuh:395-398 */
     for (size_t i = 0; i < n_img * npx; ++i) { out_depth[i] = INT_MAX; out_r[i] = 0; out_g[i] = 0; out_b[i] = 0; }
@@ -103,6 +114,16 @@ void oracle_render(const tri64* tris, int n_tris, const float* poses16, int n_po
         uint8_t* b_entry = out_b + (single_result_image ? 0 : (size_t)pi * npx);
         /* image_renderer.cuh:273-274,287-288: in single-image mode every pose reads label entry 0 */
         const int this_pose_label = use_label ? pose_label[single_result_image ? 0 : pi] : 0;
+        const int ti_out = single_result_image ? 0 : pi; /* image_renderer.cuh:262-291: entry 0 in single-image mode */
+        if (tree) {
+            for (size_t i = 0; i < npx; ++i) min_entry[i] = INT_MAX;
+            if (!single_result_image || pi == 0) {
+                tree->serial_occluded[ti_out] = 0; tree->serial_occluded_other[ti_out] = 0;
+                tree->serial_clutter[ti_out] = 0; tree->serial_total[ti_out] = 0;
+                tree->canon_occluded[ti_out] = 0; tree->canon_occluded_other[ti_out] = 0;
+                tree->canon_clutter[ti_out] = 0; tree->canon_total[ti_out] = 0;
+            }
+        }
         for (int ti = 0; ti < n_tris; ++ti) {
             if (!(ti < high[model] && ti >= low[model])) continue; /* :242-243 */
             const tri64* T = tris + ti;
@@ -165,6 +186,41 @@ void oracle_render(const tri64* tris, int n_tris, const float* poses16, int n_po
                     if (test && nd > src && src > 0) {
                         r_entry[o] = 0; g_entry[o] = 0; b_entry[o] = 0;
                         depth_entry[o] = INT_MAX; /* atomicMax(&new_depth, INT_MAX) */
+                        if (tree) {
+                            tree->serial_occluded_other[ti_out] |= 1;                       /* :187-188 */
+                            /* :189-195 `source_depth <= new_depth - 5`: new_depth is a REFERENCE to the pixel, which
+                             * the atomicMax above has just set to INT_MAX, so the margin is vacuous and every cleared
+                             * fragment counts (pinned by the golden vectors of the USE_CLUTTER build) */
+                            if ((int64_t)src <= (int64_t)INT_MAX - 5) tree->serial_clutter[ti_out] += 1.0f;
+                        }
+                    } else if (test && nd <= src && src > 0) {
+                        if (tree) tree->serial_occluded[ti_out] |= 1;                       /* :198-203 */
+                    }
+                    if (tree) {
+                        tree->serial_total[ti_out] += 1.0f;                                 /* :205-206 */
+                        if (curr < min_entry[o]) min_entry[o] = curr;
+                    }
+                }
+            }
+        }
+        if (tree) {
+            /* canonical reading: the same branches on each covered pixel's minimum depth */
+            for (size_t o = 0; o < npx; ++o) {
+                const int32_t m = min_entry[o];
+                if (m == INT_MAX) continue;
+                const int32_t src = source_depth[o];
+                const int src_label = (use_label && source_label) ? source_label[o] : 0;
+                const int64_t diff = (int64_t)m - (int64_t)src;
+                const int32_t ad = (int32_t)(diff < 0 ? -diff : diff > INT32_MAX ? INT32_MAX : diff);
+                const int test = use_label ? ((this_pose_label != src_label - 1) && ((double)ad > 0.5))
+                                           : ((float)ad > occlusion_threshold);
+                tree->canon_total[ti_out] += 1.0f;
+                if (test && src > 0) {
+                    if (m > src) {
+                        tree->canon_occluded_other[ti_out] |= 1;
+                        tree->canon_clutter[ti_out] += 1.0f; /* every cleared pixel, see the serial reading */
+                    } else {
+                        tree->canon_occluded[ti_out] |= 1;
                     }
                 }
             }
@@ -175,6 +231,30 @@ void oracle_render(const tri64* tris, int n_tris, const float* poses16, int n_po
         if (out_depth[i] == INT_MAX) out_depth[i] = 0;
     free(low);
     free(high);
+    free(min_entry);
+}
+
+void oracle_render(const tri64* tris, int n_tris, const float* poses16, int n_poses, const int* pose_model_map,
+                   const int* tris_model_count, int n_models, int width, int height, const float* proj16,
+                   const int32_t* source_depth, const uint8_t* source_label, const int* pose_label,
+                   float occlusion_threshold, int single_result_image, int32_t* out_depth, uint8_t* out_r,
+                   uint8_t* out_g, uint8_t* out_b) {
+    render_impl(tris, n_tris, poses16, n_poses, pose_model_map, tris_model_count, n_models, width, height, proj16,
+                source_depth, source_label, pose_label, occlusion_threshold, single_result_image, out_depth, out_r, out_g,
+                out_b, NULL);
+}
+
+/* oracle_render + the tree / clutter vectors (n_poses entries each; raw counts in the float arrays). */
+void oracle_render_tree(const tri64* tris, int n_tris, const float* poses16, int n_poses, const int* pose_model_map,
+                        const int* tris_model_count, int n_models, int width, int height, const float* proj16,
+                        const int32_t* source_depth, const uint8_t* source_label, const int* pose_label,
+                        float occlusion_threshold, int32_t* out_depth, uint8_t* out_r, uint8_t* out_g, uint8_t* out_b,
+                        int* serial_occluded, int* serial_occluded_other, float* serial_clutter, float* serial_total,
+                        int* canon_occluded, int* canon_occluded_other, float* canon_clutter, float* canon_total) {
+    tree_out t = {serial_occluded, serial_occluded_other, serial_clutter, serial_total,
+                  canon_occluded, canon_occluded_other, canon_clutter, canon_total};
+    render_impl(tris, n_tris, poses16, n_poses, pose_model_map, tris_model_count, n_models, width, height, proj16,
+                source_depth, source_label, pose_label, occlusion_threshold, 0, out_depth, out_r, out_g, out_b, &t);
 }
 
 /* transform_point, compute_point_clouds.cuh:14-35 (camera-frame part :20-22; no fused ops in the nvcc build) */

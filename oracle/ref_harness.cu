@@ -26,6 +26,16 @@
 #include <thrust/sort.h>
 #include <thrust/device_vector.h>
 
+#ifdef PERCH_REF_TREE
+// Second build of the same unmodified sources (_ref/libperch_ref_tree.so) with the two switches of model.h:17-18 turned
+// on, so that the USE_TREE / USE_CLUTTER branches of image_renderer.cuh (187-206, 467-482) are compiled in: model.h is
+// read first (its include guard keeps image_renderer.cuh from reading it again), then the macros are redefined.
+#include "cuda_renderer/model.h"
+#undef USE_TREE
+#undef USE_CLUTTER
+#define USE_TREE 1
+#define USE_CLUTTER 1
+#endif
 #include "cuda_renderer/cuda/image_renderer.cuh"
 #include "cuda_renderer/cuda/compute_point_clouds.cuh"
 #include "cuda_renderer/cuda/compute_costs.cuh"
@@ -127,6 +137,47 @@ int ref_render(const void* tris64, int n_tris, const float* poses16, int n_poses
     if (out_r) cudaMemcpy(out_r, thrust::raw_pointer_cast(d_r.data()), n, cudaMemcpyDeviceToHost);
     if (out_g) cudaMemcpy(out_g, thrust::raw_pointer_cast(d_g.data()), n, cudaMemcpyDeviceToHost);
     if (out_b) cudaMemcpy(out_b, thrust::raw_pointer_cast(d_b.data()), n, cudaMemcpyDeviceToHost);
+    return cudaGetLastError() == cudaSuccess ? 0 : 1;
+}
+
+int ref_tree_enabled() { return USE_TREE && USE_CLUTTER; }
+
+// image_render with its four per-pose vectors handed back: pose_occluded, pose_occluded_other, the clutter vector
+// (100 * clutter / total after image_renderer.cuh:467-482 when USE_CLUTTER) and the fragment count.
+int ref_render_tree(const void* tris64, int n_tris, const float* poses16, int n_poses, const int* pose_model_map,
+                    const int* tris_model_count, int n_models, int width, int height, const float* proj16,
+                    const int32_t* source_depth, const uint8_t* source_label, const int* pose_label,
+                    float occlusion_threshold, int32_t* out_depth, int* out_occluded, int* out_occluded_other,
+                    float* out_clutter, float* out_total) {
+    quiet_stdout q;
+    const Model::Triangle* t = (const Model::Triangle*)tris64;
+    const Model::mat4x4* p = (const Model::mat4x4*)poses16;
+    size_t npx = (size_t)width * height;
+    thrust::device_vector<Model::Triangle> d_tris(t, t + n_tris);
+    thrust::device_vector<Model::mat4x4> d_poses(p, p + n_poses);
+    thrust::device_vector<int> d_pmm(pose_model_map, pose_model_map + n_poses);
+    thrust::device_vector<int> d_tmc(tris_model_count, tris_model_count + n_models);
+    thrust::device_vector<int32_t> d_sd(source_depth, source_depth + npx);
+    thrust::device_vector<uint8_t> d_sc(npx, 0);
+    thrust::device_vector<uint8_t> d_sl;
+    if (source_label) d_sl.assign(source_label, source_label + npx);
+    thrust::device_vector<int> d_pl;
+    if (pose_label) d_pl.assign(pose_label, pose_label + n_poses);
+    thrust::device_vector<int> occ, occ_other;
+    thrust::device_vector<float> clutter, total;
+    thrust::device_vector<int32_t> d_depth;
+    thrust::device_vector<uint8_t> d_r, d_g, d_b;
+    Model::mat4x4 proj;
+    proj.init_from_ptr(proj16);
+    gpu_stats stats{0, 0};
+    cuda_renderer::image_render(d_tris, d_poses, d_pmm, d_tmc, d_sd, d_sc, d_sc, d_sc, d_sl, d_pl, n_poses, width, height,
+                                proj, occlusion_threshold, 0, occ, occ_other, clutter, total, d_depth, d_r, d_g, d_b, stats);
+    if (cudaDeviceSynchronize() != cudaSuccess) return 1;
+    if (out_depth) cudaMemcpy(out_depth, thrust::raw_pointer_cast(d_depth.data()), npx * n_poses * 4, cudaMemcpyDeviceToHost);
+    thrust::copy(occ.begin(), occ.end(), out_occluded);
+    thrust::copy(occ_other.begin(), occ_other.end(), out_occluded_other);
+    thrust::copy(clutter.begin(), clutter.end(), out_clutter);
+    thrust::copy(total.begin(), total.end(), out_total);
     return cudaGetLastError() == cudaSuccess ? 0 : 1;
 }
 

@@ -447,6 +447,7 @@ void perch_destroy(perch_ctx* c) {
     void* ptrs[] = {c->d_tri_color, c->d_model_low, c->d_model_high, c->d_model_aabb, c->d_tri_lab, c->d_cl_recs, c->d_cl_bounds,
                     c->d_cl_orig, c->d_cl_low, c->d_cl_high,
                     c->d_src_depth, c->d_src_label, c->d_src_rgb, c->d_grid_pts, c->d_grid_label, c->d_cell_start,
+                    c->d_cmp_depth, c->d_cmp_label,
                     c->d_obs_lab, c->d_obs_rgb, c->d_scratch, c->d_err_flag, c->d_flush, c->d_obs_xyz_aos,
                     c->d_tgt_normals, c->d_obs_xyz4, c->d_label_range, c->d_gicp, c->d_icp_pcd, c->d_icp_normals};
     for (void* p : ptrs)
@@ -495,7 +496,16 @@ int perch_set_camera(perch_ctx* c, int width, int height, const float proj16[16]
     if (!c || !proj16) return fail(PERCH_ERR_INVALID, "null argument");
     if (width <= 0 || height <= 0 || (int64_t)width * height > (1 << 26))
         return fail(PERCH_ERR_INVALID, "bad image size %dx%d", width, height);
-    if (c->have_scene && (width != c->cam.width || height != c->cam.height)) c->have_scene = false;
+    if (width != c->cam.width || height != c->cam.height) {
+        c->have_scene = false;
+        // the composed source images are sized for the camera
+        DeviceGuard g(c->device);
+        if (c->d_cmp_depth) cudaFree(c->d_cmp_depth);
+        if (c->d_cmp_label) cudaFree(c->d_cmp_label);
+        c->d_cmp_depth = nullptr;
+        c->d_cmp_label = nullptr;
+        c->composed = false;
+    }
     c->cam.width = width;
     c->cam.height = height;
     memcpy(&c->cam.proj, proj16, 64);
@@ -604,6 +614,7 @@ int perch_set_scene(perch_ctx* c, const int32_t* depth, const uint8_t* red, cons
     CU(cudaStreamSynchronize(c->stream));
     c->scene.depth = c->d_src_depth;
     c->scene.label = c->d_src_label;
+    c->composed = false;
     c->scene.r = c->d_src_rgb;
     c->scene.g = c->d_src_rgb + npx;
     c->scene.b = c->d_src_rgb + 2 * npx;

@@ -123,6 +123,7 @@ int perch_set_input(perch_ctx* c, const perch_input* in, int* observed_point_num
     }
     PERCH_CU(cudaStreamSynchronize(c->stream));
     c->scene.depth = c->d_src_depth;
+    c->composed = false;
     c->scene.label = in->predicted_mask ? c->d_src_label : nullptr;
     c->scene.r = c->d_src_rgb;
     c->scene.g = c->d_src_rgb + npx;
@@ -148,7 +149,7 @@ int perch_get_source_depth(perch_ctx* c, int32_t* out_depth) {
     if (!c || !out_depth) return fail(PERCH_ERR_INVALID, "null argument");
     if (!c->have_scene) return fail(PERCH_ERR_INVALID, "no scene has been set");
     DeviceGuard g(c->device);
-    PERCH_CU(cudaMemcpyAsync(out_depth, c->d_src_depth, (size_t)c->cam.width * c->cam.height * 4, cudaMemcpyDeviceToHost, c->stream));
+    PERCH_CU(cudaMemcpyAsync(out_depth, c->scene.depth, (size_t)c->cam.width * c->cam.height * 4, cudaMemcpyDeviceToHost, c->stream));
     PERCH_CU(cudaStreamSynchronize(c->stream));
     return PERCH_OK;
 }

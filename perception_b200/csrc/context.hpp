@@ -98,6 +98,11 @@ struct perch_ctx {
     uint8_t* d_src_rgb = nullptr;  // 3 planes
     perch::SceneDev scene;
     bool have_scene = false;
+    // composition mode (capi_compose.cu): while `composed`, scene.depth / scene.label point at these instead of the
+    // observed images above; perch_set_scene / perch_set_input / perch_compose_source(mode NONE) switch back
+    int32_t* d_cmp_depth = nullptr;
+    uint8_t* d_cmp_label = nullptr;
+    bool composed = false;
 
     // observed cloud (host copies kept so the grid can be rebuilt when sensor_resolution changes)
     std::vector<float> h_obs_xyz;      // label-sorted, AoS

@@ -37,6 +37,15 @@ struct PoseArgs {
     // single_result_image (image_renderer.cuh:262-275): all poses z-tested into one W x H key image, resolved by
     // launch_resolve_single afterwards
     unsigned long long* single_keys = nullptr;
+    int key_pose_id = 0;              // single_keys only: the key's low word is the pose index instead of the triangle
+                                      // index (perch_compose_source labels each pixel by the placed object that owns it)
+    // Composition-mode outputs per pose (the reference's USE_TREE / USE_CLUTTER branches, image_renderer.cuh:163-206),
+    // evaluated per covered pixel on its minimum depth; all null unless perch_tree_flags asked for them.  With these
+    // set img_depth may be null (nothing is written but the four vectors).
+    int* tree_occluded = nullptr;        // the render lies in front of a source pixel (by more than the rule's gate)
+    int* tree_occluded_other = nullptr;  // a source pixel hides (clears) a rendered pixel
+    float* tree_clutter = nullptr;       // 100 * cleared pixels / covered pixels
+    float* tree_total = nullptr;         // covered pixels
     int* err_flag = nullptr;          // set to 1 if a fragment fell outside its pose tile (must never happen)
     int tile_cap = 0;                 // lattice cells of shared-memory z-buffer per band
     int mask_words = 0;               // ceil(n_obs / 32) (MODE_COST)
@@ -48,6 +57,19 @@ cudaError_t launch_raster_images(const PoseArgs& a, cudaStream_t stream);
 // reference's pointer arithmetic does, image_renderer.cuh:273-274).
 cudaError_t launch_single_clear(unsigned long long* keys, int n, cudaStream_t stream);
 cudaError_t launch_resolve_single(const PoseArgs& a, cudaStream_t stream);
+
+// ---- composition mode (compose.cu): key image of the placed objects -> source depth (+ label) image ----------------
+struct ComposeArgs {
+    const unsigned long long* keys = nullptr;  // W*H single_result_image keys with key_pose_id
+    const int* pose_label = nullptr;           // per placed pose (0-based, like pose_segmentation_label), or null
+    const int32_t* base_depth = nullptr;       // the observed source image (merge mode), or null
+    const uint8_t* base_label = nullptr;
+    int32_t* out_depth = nullptr;
+    uint8_t* out_label = nullptr;              // or null
+    int n_pixels = 0;
+    int merge = 0;
+};
+cudaError_t launch_compose(const ComposeArgs& a, cudaStream_t stream);
 
 // ---- depth image(s) -> compacted cloud (cloud.cu) -----------------------------------------------------------
 struct CloudArgs {

@@ -305,6 +305,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
     const int tile_w = rx1 - rx0 + 1;
     const bool tile_empty = (rx0 > rx1) || (ry0 > ry1);
     int n_local = 0, c_local = 0;
+    int tree_flags_local = 0, tree_clutter_local = 0, tree_total_local = 0;  // MODE_IMAGE with a.tree_total
 
     if (!tile_empty) {
         const int band_rows = max(1, a.tile_cap / tile_w);
@@ -340,7 +341,9 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                 if (!coop || tid == 0) { STAT(4, 1); STAT(5, cells); if (coop) STAT(7, 1); }
                 TriSetup ts;
                 setup_edges(A, B, C, ts);
-                const uint32_t id = COLOR ? (uint32_t)__ldg(a.models.cl_orig + t) : 0u;  // original triangle index
+                // original triangle index (colour tie-break and lookup), or the pose index for perch_compose_source
+                const uint32_t id = !COLOR ? 0u : (MODE == MODE_IMAGE && a.key_pose_id) ? (uint32_t)pose_i
+                                                                                        : (uint32_t)__ldg(a.models.cl_orig + t);
                 if (coop) {
                     for (int c = tid; c < cells; c += kThreads) {
                         int ly = y0 + c / w, lx = x0 + c % w;
@@ -574,10 +577,29 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                         int u = lx * s, v = ly * s;
                         int32_t src = __ldg(a.scene.depth + v * W + u);
                         int src_label = (use_label && a.scene.label) ? (int)__ldg(a.scene.label + v * W + u) : 0;
+                        if (a.tree_total) {
+                            // image_renderer.cuh:163-206 on the pixel's minimum depth: the gate of the occlusion rule,
+                            // then "source hides render" (cleared, and counted as clutter: the reference's extra
+                            // `source <= new_depth - 5` reads the pixel AFTER it was set to INT_MAX, so it always
+                            // holds) or "render hides source"
+                            ++tree_total_local;
+                            const int ad = abs(d - src);
+                            const bool gate = use_label ? (pose_label != src_label - 1 && ad >= 1)
+                                                        : ((float)ad > a.occlusion_threshold);
+                            if (gate && src > 0) {
+                                if (d > src) {
+                                    tree_flags_local |= 2;
+                                    ++tree_clutter_local;
+                                } else {
+                                    tree_flags_local |= 1;
+                                }
+                            }
+                        }
                         if (source_occludes(d, src, use_label, pose_label, src_label, a.occlusion_threshold)) d = 0;
                         else rgb = __ldg(a.models.tri_color + Z::tri(k));
                         if (d == INT_MAX) d = 0;  // max2zero (image_renderer.cuh:324-333,465-466)
                     }
+                    if (!a.img_depth) continue;
                     size_t o = ((size_t)pose_i * Lh + ly) * Lw + lx;
                     a.img_depth[o] = d;
                     if (a.img_r) { a.img_r[o] = (uint8_t)rgb; a.img_g[o] = (uint8_t)(rgb >> 8); a.img_b[o] = (uint8_t)(rgb >> 16); }
@@ -616,13 +638,35 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
 
     if (MODE == MODE_IMAGE) {
         // every output pixel outside the pose tile is empty: the kernel writes the whole image, no memset pass
-        if (!a.single_keys) {
+        if (!a.single_keys && a.img_depth) {
             for (int i = tid; i < Lw * Lh; i += kThreads) {
                 int lx = i % Lw, ly = i / Lw;
                 if (!tile_empty && lx >= rx0 && lx <= rx1 && ly >= ry0 && ly <= ry1) continue;
                 size_t o = (size_t)pose_i * Lh * Lw + i;
                 a.img_depth[o] = 0;
                 if (a.img_r) { a.img_r[o] = 0; a.img_g[o] = 0; a.img_b[o] = 0; }
+            }
+        }
+        if (a.tree_total) {
+#pragma unroll
+            for (int o = 16; o >= 1; o >>= 1) {
+                tree_flags_local |= __shfl_xor_sync(0xffffffffu, tree_flags_local, o);
+                tree_clutter_local += __shfl_xor_sync(0xffffffffu, tree_clutter_local, o);
+                tree_total_local += __shfl_xor_sync(0xffffffffu, tree_total_local, o);
+            }
+            if ((tid & 31) == 0) {
+                if (tree_flags_local) atomicOr(&s_n, tree_flags_local);
+                if (tree_clutter_local) atomicAdd(&s_c, tree_clutter_local);
+                if (tree_total_local) atomicAdd(&s_e, tree_total_local);
+            }
+            __syncthreads();
+            if (tid == 0) {
+                const float clutter = (float)s_c, total = (float)s_e;
+                if (a.tree_occluded) a.tree_occluded[pose_i] = s_n & 1;
+                if (a.tree_occluded_other) a.tree_occluded_other[pose_i] = (s_n >> 1) & 1;
+                // thrust::divides then multiplies by 100 (image_renderer.cuh:467-482); 0/0 = NaN like the reference
+                if (a.tree_clutter) a.tree_clutter[pose_i] = __fmul_rn(__fdiv_rn(clutter, total), 100.f);
+                a.tree_total[pose_i] = total;
             }
         }
         return;

@@ -284,6 +284,38 @@ class Renderer:
         self._ck(self._lib.perch_get_source_depth(self._h, _ptr(out)))
         return out
 
+    def get_source_label(self):
+        """The label image the occlusion rule currently tests against, or None."""
+        out = np.zeros((self.height, self.width), np.uint8)
+        has = C.c_int(0)
+        self._ck(self._lib.perch_get_source_label(self._h, _ptr(out), C.byref(has)))
+        return out if has.value else None
+
+    # -- composition mode (SURVEY 8(f) row 4): placed objects rendered into the source image on the device -------------
+    def compose_source(self, poses=None, pose_model_map=None, pose_segmentation_label=None, mode="merge") -> None:
+        """Render the already-placed objects into the source depth the occlusion rule tests against.  mode: "replace"
+        (source = placed objects only; the reference's tree flow, search_env.cpp:1718-1781, 2054-2460), "merge" (nearer
+        of the observed image and the placed objects) or "none" (back to the observed image)."""
+        m = {"none": _capi.PERCH_COMPOSE_NONE, "replace": _capi.PERCH_COMPOSE_REPLACE, "merge": _capi.PERCH_COMPOSE_MERGE}[mode]
+        n = 0 if poses is None else len(poses)
+        p = None if n == 0 else _c(poses, np.float32).reshape(n, 16)
+        pm = None if n == 0 else _c(pose_model_map, np.int32)
+        lab = None if (n == 0 or pose_segmentation_label is None) else _c(pose_segmentation_label, np.int32)
+        self._ck(self._lib.perch_compose_source(self._h, _ptr(p), n, _ptr(pm), _ptr(lab), m))
+
+    def tree_flags(self, poses, pose_model_map, pose_segmentation_label=None, occlusion_threshold=1.0) -> dict:
+        """pose_occluded / pose_occluded_other / clutter_cost of the reference's USE_TREE / USE_CLUTTER branches
+        (image_renderer.cuh:187-206, 467-482), per covered pixel on its minimum depth, + the covered-pixel count."""
+        n = len(poses)
+        p = _c(poses, np.float32).reshape(n, 16)
+        pm = _c(pose_model_map, np.int32)
+        lab = None if pose_segmentation_label is None else _c(pose_segmentation_label, np.int32)
+        occ, other = np.zeros(n, np.int32), np.zeros(n, np.int32)
+        clutter, total = np.zeros(n, np.float32), np.zeros(n, np.float32)
+        self._ck(self._lib.perch_tree_flags(self._h, _ptr(p), n, _ptr(pm), _ptr(lab), float(occlusion_threshold), _ptr(occ),
+                                            _ptr(other), _ptr(clutter), _ptr(total)))
+        return {"pose_occluded": occ, "pose_occluded_other": other, "clutter_cost": clutter, "total_points": total}
+
     # -- caller glue: ObjectState lists (SURVEY 8(f) rows 1-2; perception_b200/states.py has the host-side types) --------
     def set_env(self, env, metas) -> None:
         """EnvParams / PerchParams fields + per-model ObjectModel metadata (states.Env, list of states.ModelMeta)."""

@@ -1,6 +1,6 @@
 """Generate tests/golden/*.npz from the reference's OWN CUDA kernels (oracle/_ref/libperch_ref.so, built from
 /root/reference by `make -C oracle ref`).  Needs a GPU: run on the B200 box, e.g.
-    gpurun -- 'python tests/golden/make_golden.py gpurun_out/golden'
+    gpurun -- 'python tests/golden/make_golden.py gpurun_out/golden [case ...]'
 and copy the .npz files into tests/golden/.  EXACT cases (see tests/make_golden_inputs.py) are run twice and must be
 reproducible; BUDGET cases (full-mesh renders, where the reference rasterizer races) are run 3 times and the number of
 pixels that differ between runs / from the canonical oracle is stored as `race_budget`."""
@@ -17,11 +17,11 @@ import make_golden_inputs as gi  # noqa: E402
 from oracle_lib import Oracle, Reference  # noqa: E402
 
 
-def main(out_dir):
+def main(out_dir, only=()):
     out = Path(out_dir)
     out.mkdir(parents=True, exist_ok=True)
     ref, orc = Reference(), Oracle()
-    for name in gi.NAMES:
+    for name in (only or gi.NAMES):
         exact = name in gi.EXACT
         runs = [gi.run_reference(ref, orc, name) for _ in range(2 if exact else 3)]
         save = {f"ref_{k}": v for k, v in runs[0].items()}
@@ -48,4 +48,4 @@ def main(out_dir):
 
 
 if __name__ == "__main__":
-    main(sys.argv[1] if len(sys.argv) > 1 else str(Path(__file__).parent))
+    main(sys.argv[1] if len(sys.argv) > 1 else str(Path(__file__).parent), sys.argv[2:])

@@ -9,6 +9,9 @@ with the z-test, :161-186).  Golden cases are therefore split:
                            transform, viewport, bbox, inside test and depth rounding fragment by fragment
   EXACT  quad_occlusion    one quad (its two triangles meet only on the diagonal, with equal depths) over block-wise
                            varying source depth / labels / thresholds: pins the source-occlusion rule
+  EXACT  tree_single_tri   the one-triangle images again, over block-wise varying source depth / labels, through the
+                           build of the reference kernels with USE_TREE / USE_CLUTTER on (model.h:17-18): pins
+                           pose_occluded, pose_occluded_other, the clutter ratio and the fragment count
   EXACT  cloud             compute_point_clouds in its three modes
   EXACT  cost_3dof/_6dof   reference compute_point_clouds + k=1 search + compute_costs fed with canonical images
   BUDGET render_3dof/_6dof full meshes over a real scene: the reference deviates on a few % of object pixels and from
@@ -21,8 +24,9 @@ from perception_b200.renderer import make_triangles, pose_to_mat4x4
 from scenes import make_case, observed_3dof, observed_6dof, poses_near_gt
 
 W, H = 160, 120
-NAMES = ["frag_single_tri", "quad_occlusion", "render_3dof", "render_6dof", "cloud", "cost_3dof", "cost_6dof"]
-EXACT = {"frag_single_tri", "quad_occlusion", "cloud", "cost_3dof", "cost_6dof"}
+NAMES = ["frag_single_tri", "quad_occlusion", "render_3dof", "render_6dof", "cloud", "cost_3dof", "cost_6dof",
+         "tree_single_tri"]
+EXACT = {"frag_single_tri", "quad_occlusion", "cloud", "cost_3dof", "cost_6dof", "tree_single_tri"}
 
 
 def _case():
@@ -76,17 +80,40 @@ def quad_inputs():
     return case, tris, src, lab, pose
 
 
+def tree_source():
+    """Source depth in vertical stripes around the depths the one-triangle images reach (45-90 cm), labels in bands."""
+    src = np.zeros((H, W), np.int32)
+    vals = [0, 40, 52, 58, 61, 64, 70, 76, 90, 200, 1, 66]
+    for bx in range(W // 3 + 1):
+        src[:, bx * 3:(bx + 1) * 3] = vals[bx % len(vals)]
+    lab = np.zeros((H, W), np.uint8)
+    for by in range(H // 5):
+        lab[by * 5:(by + 1) * 5] = by % 4
+    return src, lab
+
+
 def _cloud_modes(case):
     s = case.scene
     return [("plain", {}), ("label", {"label_mask": s.source_label}),
             ("bounds", {"bounds": synth.table_bounds(s), "cam_tf": np.linalg.inv(s.T_cam_table)})]
 
 
-def _run(render, depth2cloud, cost_fn, orc, name):
+def _run(render, depth2cloud, cost_fn, orc, name, render_tree=None):
     """render(tris, counts, poses, pmm, src_depth, src_label, pose_label, thr) -> depth, rgb
-    depth2cloud(**kw) -> dict; cost_fn(depth, rgb, pose_label, obs, tot, stride, dof6) -> dict"""
+    depth2cloud(**kw) -> dict; cost_fn(depth, rgb, pose_label, obs, tot, stride, dof6) -> dict
+    render_tree(same as render) -> dict with depth, pose_occluded, pose_occluded_other, clutter_cost, total_points"""
     case = _case()
     s = case.scene
+    if name == "tree_single_tri":
+        case, tris, counts, poses, pmm = single_tri_inputs()
+        src, lab = tree_source()
+        out = {}
+        for tag, sl, pl, thr in (("3dof", None, None, 1.0), ("3dof_thr5", None, None, 5.0),
+                                 ("6dof", lab, (np.arange(len(poses)) % 3).astype(np.int32), 1.0)):
+            o = render_tree(tris, counts, poses, pmm, src, sl, pl, thr)
+            for k in ("depth", "pose_occluded", "pose_occluded_other", "clutter_cost", "total_points"):
+                out[f"{tag}_{k}"] = o[k]
+        return out
     if name == "frag_single_tri":
         case, tris, counts, poses, pmm = single_tri_inputs()
         d, c = render(tris, counts, poses, pmm, None, None, None, 1.0)
@@ -141,7 +168,14 @@ def run_oracle(orc, name):
         return {"rendered_cost": r["rendered_cost"], "observed_cost": r["observed_cost"],
                 "points_diff_cost": r["points_diff_cost"], "n_rend": np.array(int(r["counts"][0].sum()))}
 
-    return _run(render, d2c, cost, orc, name)
+    def render_tree(tris, counts, poses, pmm, src, src_label, pose_label, thr):
+        o = orc.render_tree(tris, counts, poses, pmm, W, H, case.proj, src, src_label, pose_label, thr)
+        # one fragment per pixel: the serial (per-fragment) and canonical (per-pixel) readings must coincide
+        for k in ("pose_occluded", "pose_occluded_other", "clutter_points", "total_points"):
+            assert np.array_equal(o["serial"][k], o["canon"][k]), k
+        return {"depth": o["depth"], **o["serial"]}
+
+    return _run(render, d2c, cost, orc, name, render_tree)
 
 
 def run_reference(ref, orc, name):
@@ -161,4 +195,8 @@ def run_reference(ref, orc, name):
         return {"rendered_cost": q["rendered_cost"], "observed_cost": q["observed_cost"],
                 "points_diff_cost": q["points_diff_cost"], "n_rend": np.array(q["n_rend"])}
 
-    return _run(render, d2c, cost, orc, name)
+    def render_tree(tris, counts, poses, pmm, src, src_label, pose_label, thr):
+        from oracle_lib import Reference
+        return Reference(tree=True).render_tree(tris, counts, poses, pmm, W, H, case.proj, src, src_label, pose_label, thr)
+
+    return _run(render, d2c, cost, orc, name, render_tree)

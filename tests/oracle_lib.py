@@ -12,6 +12,7 @@ from perception_b200.renderer import TRIANGLE_DTYPE
 ROOT = Path(__file__).resolve().parent.parent
 ORACLE_SO = ROOT / "oracle" / "_build" / "libperch_oracle.so"
 REF_SO = ROOT / "oracle" / "_ref" / "libperch_ref.so"
+REF_TREE_SO = ROOT / "oracle" / "_ref" / "libperch_ref_tree.so"
 
 _vp = C.c_void_p
 
@@ -56,6 +57,36 @@ class Oracle:
                                C.c_float(occlusion_threshold), C.c_int(single_result_image), _p(depth), _p(rgb[0]),
                                _p(rgb[1]), _p(rgb[2]))
         return depth, rgb
+
+    def render_tree(self, tris, tris_model_count, poses, pose_model_map, width, height, proj, source_depth=None,
+                    source_label=None, pose_label=None, occlusion_threshold=1.0):
+        """oracle_render + the USE_TREE / USE_CLUTTER vectors in both readings (serial triangle order, canonical)."""
+        tris = np.ascontiguousarray(tris, dtype=TRIANGLE_DTYPE)
+        cnt = _c(tris_model_count, np.int32)
+        P4 = _c(poses, np.float32).reshape(-1, 16)
+        P = len(P4)
+        pmm = _c(pose_model_map, np.int32)
+        proj = _c(proj, np.float32).reshape(16)
+        sd = np.zeros(width * height, np.int32) if source_depth is None else _c(source_depth, np.int32).reshape(-1)
+        sl = None if source_label is None else _c(source_label, np.uint8).reshape(-1)
+        pl = None if pose_label is None else _c(pose_label, np.int32)
+        depth = np.zeros((P, height, width), np.int32)
+        rgb = np.zeros((3, P, height, width), np.uint8)
+        out = {}
+        for kind in ("serial", "canon"):
+            out[kind] = {"pose_occluded": np.zeros(P, np.int32), "pose_occluded_other": np.zeros(P, np.int32),
+                         "clutter_points": np.zeros(P, np.float32), "total_points": np.zeros(P, np.float32)}
+        vecs = [_p(out[k][n]) for k in ("serial", "canon")
+                for n in ("pose_occluded", "pose_occluded_other", "clutter_points", "total_points")]
+        self.lib.oracle_render_tree(_p(tris), C.c_int(len(tris)), _p(P4), C.c_int(P), _p(pmm), _p(cnt), C.c_int(len(cnt)),
+                                    C.c_int(width), C.c_int(height), _p(proj), _p(sd), _p(sl), _p(pl),
+                                    C.c_float(occlusion_threshold), _p(depth), _p(rgb[0]), _p(rgb[1]), _p(rgb[2]), *vecs)
+        for k in out:
+            with np.errstate(invalid="ignore", divide="ignore"):
+                # thrust::divides, then multiplies by 100 (image_renderer.cuh:467-482), in float32
+                out[k]["clutter_cost"] = (out[k]["clutter_points"] / out[k]["total_points"]) * np.float32(100)
+        out["depth"] = depth
+        return out
 
     def depth2cloud(self, depth, color, width, height, num_images, cx, cy, fx, fy, depth_factor, stride, label_mask=None,
                     pose_label=None, bounds=None, cam_tf=None, want_dc_index=False):
@@ -231,12 +262,37 @@ class ReferenceKnn:
 
 
 class Reference:
-    """The reference's own CUDA kernels (oracle/ref_harness.cu).  Needs a GPU."""
+    """The reference's own CUDA kernels (oracle/ref_harness.cu).  Needs a GPU.  tree=True loads the build with the
+    reference's USE_TREE / USE_CLUTTER switches on (render_tree)."""
 
-    def __init__(self):
-        if not REF_SO.exists():
-            raise FileNotFoundError(f"{REF_SO} missing: build with `make -C oracle ref` where /root/reference exists")
-        self.lib = C.CDLL(str(REF_SO))
+    def __init__(self, tree=False):
+        so = REF_TREE_SO if tree else REF_SO
+        if not so.exists():
+            raise FileNotFoundError(f"{so} missing: build with `make -C oracle ref` where /root/reference exists")
+        self.lib = C.CDLL(str(so))
+        if tree:
+            assert self.lib.ref_tree_enabled() == 1
+
+    def render_tree(self, tris, tris_model_count, poses, pose_model_map, width, height, proj, source_depth=None,
+                    source_label=None, pose_label=None, occlusion_threshold=1.0):
+        tris = np.ascontiguousarray(tris, dtype=TRIANGLE_DTYPE)
+        cnt = _c(tris_model_count, np.int32)
+        P4 = _c(poses, np.float32).reshape(-1, 16)
+        P = len(P4)
+        pmm = _c(pose_model_map, np.int32)
+        proj = _c(proj, np.float32).reshape(16)
+        sd = np.zeros(width * height, np.int32) if source_depth is None else _c(source_depth, np.int32).reshape(-1)
+        sl = None if source_label is None else _c(source_label, np.uint8).reshape(-1)
+        pl = None if pose_label is None else _c(pose_label, np.int32)
+        depth = np.zeros((P, height, width), np.int32)
+        occ, other = np.zeros(P, np.int32), np.zeros(P, np.int32)
+        clutter, total = np.zeros(P, np.float32), np.zeros(P, np.float32)
+        rc = self.lib.ref_render_tree(_p(tris), C.c_int(len(tris)), _p(P4), C.c_int(P), _p(pmm), _p(cnt), C.c_int(len(cnt)),
+                                      C.c_int(width), C.c_int(height), _p(proj), _p(sd), _p(sl), _p(pl),
+                                      C.c_float(occlusion_threshold), _p(depth), _p(occ), _p(other), _p(clutter), _p(total))
+        assert rc == 0, "ref_render_tree failed"
+        return {"depth": depth, "pose_occluded": occ, "pose_occluded_other": other, "clutter_cost": clutter,
+                "total_points": total}
 
     def render(self, tris, tris_model_count, poses, pose_model_map, width, height, proj, source_depth=None,
                source_color=None, source_label=None, pose_label=None, occlusion_threshold=1.0, single_result_image=0):
