@@ -33,9 +33,14 @@ UNIT = "poses/s"
 W, H = 640, 480
 
 WORKLOADS = {
-    # name: (description, n_tris, poses per GPU per step, stride, dof6, cost_type, sensor_resolution)
-    "c1": ("C1: 3-DoF, 5k-tri mesh, 2k poses, stride 4, cost_type 0", 5000, 2000, 4, False, 0, 0.0075),
-    "c2": ("C2: 6-DoF render+cost, 16384 poses x 20k-tri mesh, 640x480, stride 8, cost_type 2", 20000, 16384, 8, True, 2, 0.01),
+    # name: (description, n_tris per mesh, poses per GPU per step, stride, dof6, cost_type, sensor_resolution, meshes)
+    "c1": ("C1: 3-DoF, 5k-tri mesh, 2k poses, stride 4, cost_type 0", 5000, 2000, 4, False, 0, 0.0075, 1),
+    "c2": ("C2: 6-DoF render+cost, 16384 poses x 20k-tri mesh, 640x480, stride 8, cost_type 2", 20000, 16384, 8, True, 2, 0.01, 1),
+    # BASELINE configs[2] and [4] are quoted over 8 GPUs: the per-GPU share is the default, --poses runs any other size
+    "c3": ("C3: multi-object 3-DoF, 5 meshes x 5k tris, 12500 poses per GPU (100k over 8), stride 4, cost_type 0", 5000, 12500,
+           4, False, 0, 0.0075, 5),
+    "c5": ("C5: 6-DoF sweep, 21 meshes x 20k tris, 125000 poses per GPU (1M over 8), stride 8, cost_type 2", 20000, 125000, 8,
+           True, 2, 0.01, 21),
 }
 
 
@@ -91,11 +96,13 @@ def build_workload(name: str, rank: int, device: int, n_poses: int | None, use_p
     from perception_b200 import synth
     from perception_b200.renderer import Renderer, compute_proj
 
-    desc, n_tris, P, stride, dof6, cost_type, res = WORKLOADS[name]
+    desc, n_tris, P, stride, dof6, cost_type, res, n_models = WORKLOADS[name]
     if n_poses:
         P = n_poses
     proj = compute_proj(synth.camera_K(), W, H)
-    mesh = synth.make_mesh(n_tris, seed=1000, r0=0.09)
+    # mesh variants from seed 1000+m, r0 in [0.04, 0.12] m
+    meshes = [synth.make_mesh(n_tris, seed=1000 + m, r0=0.09 if n_models == 1 else 0.05 + 0.06 * ((m * 7) % n_models) / n_models)
+              for m in range(n_models)]
     r = None
     if use_product:
         r = Renderer(device)
@@ -113,7 +120,7 @@ def build_workload(name: str, rank: int, device: int, n_poses: int | None, use_p
         def render_fn(tris, counts, poses, pmm):
             return orc.render(tris, counts, poses, pmm, W, H, proj)
 
-    scene = synth.make_scene([mesh], render_fn, n_instances=4, seed=42)
+    scene = synth.make_scene(meshes, render_fn, n_instances=4 if n_models == 1 else min(n_models, 8), seed=42)
     cam = (synth.CX, synth.CY, synth.FX, synth.FY, synth.DEPTH_FACTOR)
     lab_img = scene.source_label if dof6 else None
     bounds = None if dof6 else synth.table_bounds(scene)
@@ -130,18 +137,26 @@ def build_workload(name: str, rank: int, device: int, n_poses: int | None, use_p
     if use_product:
         r.set_observed(obs["result_cloud_eigen"], obs["result_cloud_color"], obs_label)
     n_obs = obs["rendered_cloud_point_num"]
+    # pose list in per-model blocks, like the reference's per-model batches (search_env.cpp:2504-2525)
+    pmm = (np.arange(P, dtype=np.int64) * n_models // P).astype(np.int32)
+    n_inst = len(scene.gt_poses)
     if dof6:
-        center = scene.gt_poses[0][:3, 3]
-        poses = synth.poses_6dof(center, P, seed=3 + rank)
-        poses[0] = synth.pose_to_mat4x4(scene.gt_poses[0])
+        # a model is searched around the instance that shows it (models without an instance borrow one)
+        inst_of = [next((g for g in range(n_inst) if scene.gt_models[g] == m), m % n_inst) for m in range(n_models)]
+        poses = np.zeros((P, 4, 4), np.float32)
         plabel = np.zeros(P, np.int32)
-        tot = np.full(P, float((obs_label == 0).sum()), np.float32)
+        for m in range(n_models):
+            sel = np.nonzero(pmm == m)[0]
+            g = inst_of[m]
+            poses[sel] = synth.poses_6dof(scene.gt_poses[g][:3, 3], len(sel), seed=3 + rank + 101 * m)
+            plabel[sel] = g
+        poses[0] = synth.pose_to_mat4x4(scene.gt_poses[inst_of[0]])
+        tot = np.bincount(obs_label, minlength=n_inst).astype(np.float32)[plabel]
     else:
-        poses = synth.poses_3dof(scene, 0, P, seed=1 + rank)
+        poses = np.concatenate([synth.poses_3dof(scene, m, int((pmm == m).sum()), seed=1 + rank) for m in range(n_models)])
         plabel = None
-        tot = synth.cylinder_counts(scene, obs["result_cloud_eigen"], poses, np.zeros(P, np.int32))
-    pmm = np.zeros(P, np.int32)
-    wl = dict(name=name, desc=desc, n_tris=n_tris, P=P, stride=stride, dof6=dof6, cost_type=cost_type, res=res, n_obs=n_obs,
+        tot = synth.cylinder_counts(scene, obs["result_cloud_eigen"], poses, pmm)
+    wl = dict(name=name, desc=desc, n_tris=n_tris, n_models=n_models, P=P, stride=stride, dof6=dof6, cost_type=cost_type, res=res, n_obs=n_obs,
               scene=scene, obs=obs, obs_label=obs_label, poses=poses, pmm=pmm, plabel=plabel, tot=tot, proj=proj)
     return r, wl
 
@@ -260,7 +275,7 @@ def run_ours(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic",
-            "config": {"workload": wl["desc"], "poses_per_gpu_per_step": P, "triangles": wl["n_tris"], "image": [W, H],
+            "config": {"workload": wl["desc"], "poses_per_gpu_per_step": P, "triangles": wl["n_tris"], "meshes": wl["n_models"], "image": [W, H],
                        "stride": wl["stride"], "n_obs": int(wl["n_obs"]), "l2": "flushed between steps (256 MiB memset)",
                        "timing": "CUDA events on the library stream around the fused kernel, max over ranks"},
             "clocks": clocks,
@@ -274,11 +289,12 @@ def run_ours(args):
             "best": {"cost": int(best["cost"]), "pose_id": int(best["pose_id"])},
             "wall_s_device_loop": wall_device_loop,
         }
-        if world == 1 and not args.no_gicp:
+        single = wl["n_models"] == 1  # the GICP / glue legs are written for the one-mesh workloads
+        if world == 1 and not args.no_gicp and single:
             line["gicp"] = gicp_leg(r, wl, out, kw)
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(wl, budget_s=args.cpu_budget)
-        if world == 1 and not args.no_glue:
+        if world == 1 and not args.no_glue and single:
             line["glue"] = glue_leg(r, wl, kw)  # last: re-targets the context at a 3-DoF scene
         if world == 1 and not args.no_ref_cuda:
             line["reference_cuda"] = reference_cuda(wl, batch=args.ref_batch)
@@ -446,7 +462,7 @@ def _baseline_inputs(wl):
     T_tc = np.linalg.inv(s.T_cam_table)
     t = wl["poses"][:, :3, 3].astype(np.float64) / 100.0
     c = (t @ T_tc[:3, :3].T + T_tc[:3, 3])[:, :2].astype(np.float32)
-    return dict(center=np.ascontiguousarray(c), radius=np.full(len(c), s.model_radius[0], np.float32),
+    return dict(center=np.ascontiguousarray(c), radius=np.ascontiguousarray(np.asarray(s.model_radius)[wl["pmm"]], np.float32),
                 t_tc=np.ascontiguousarray(T_tc[:3, :4], dtype=np.float32))
 
 
@@ -463,11 +479,15 @@ def cpu_score(wl, n):
     p = lambda a: None if a is None else a.ctypes.data_as(vp)  # noqa: E731
     tris = np.ascontiguousarray(s.tris, dtype=TRIANGLE_DTYPE)
     cnt = np.ascontiguousarray(s.tris_model_count, np.int32)
-    poses = np.ascontiguousarray(wl["poses"][:n], np.float32)
-    pmm = np.ascontiguousarray(wl["pmm"][:n], np.int32)
+    # the sample: the first n poses of a one-mesh workload, n poses spread evenly over the per-model blocks otherwise
+    sel = np.arange(n) if wl["n_models"] == 1 else np.linspace(0, wl["P"] - 1, n).astype(np.int64)
+    poses = np.ascontiguousarray(wl["poses"][sel], np.float32)
+    pmm = np.ascontiguousarray(wl["pmm"][sel], np.int32)
     sd = np.ascontiguousarray(s.source_depth, np.int32)
     sl = np.ascontiguousarray(s.source_label, np.uint8) if wl["dof6"] else None
-    pl = np.ascontiguousarray(wl["plabel"][:n], np.int32) if wl["dof6"] else None
+    pl = np.ascontiguousarray(wl["plabel"][sel], np.int32) if wl["dof6"] else None
+    if b["center"] is not None:
+        b = dict(b, center=np.ascontiguousarray(b["center"][sel]), radius=np.ascontiguousarray(b["radius"][sel]))
     ox = np.ascontiguousarray(wl["obs"]["result_cloud_eigen"], np.float32)
     ol = np.ascontiguousarray(wl["obs_label"], np.int32) if wl["dof6"] else None
     proj = np.ascontiguousarray(wl["proj"], np.float32)
@@ -488,7 +508,9 @@ def cpu_baseline(wl, budget_s=15.0):
     n = int(min(wl["P"], max(32, 32 * budget_s / max(dt, 1e-3))))
     dt, cores, _, _ = cpu_score(wl, n)
     return {"value": n / dt, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"first {n} poses of the same workload, {dt:.1f} s, OpenMP over poses (oracle/cpu_baseline.c)"}
+            "sample": f"{'first ' if wl['n_models'] == 1 else ''}{n} poses of the same workload"
+                      f"{'' if wl['n_models'] == 1 else ' (evenly over the meshes)'}, {dt:.1f} s, OpenMP over poses "
+                      "(oracle/cpu_baseline.c)"}
 
 
 def reference_cuda(wl, batch=700):

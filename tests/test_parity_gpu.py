@@ -473,6 +473,62 @@ def test_triangle_order_invariance():
     assert np.array_equal(a, b)
 
 
+def test_multi_model_blocks_c5_shape(orc):
+    """BASELINE configs[4] in shape (many meshes, pose list in per-model blocks, labels): every model's block must score
+    exactly as it does in a context that holds that mesh alone, and a sample must equal the oracle."""
+    M, T, per = 7, 1500, 48
+    meshes = [synth.make_mesh(T, seed=1000 + m, r0=0.05 + 0.01 * m) for m in range(M)]
+    K = synth.camera_K()
+    proj = orc.compute_proj(K, 640, 480)
+
+    def render_fn(tris, counts, poses, pmm):
+        with Renderer(0) as rr:
+            rr.set_camera(640, 480, proj, synth.CX, synth.CY, synth.FX, synth.FY, 100.0)
+            rr.set_models(tris, counts)
+            rr.set_scene(np.zeros(640 * 480, np.int32))
+            o = rr.render_cuda_multi_unified("RENDER", poses, pmm)
+        return o["result_depth"], o["result_color"]
+
+    scene = synth.make_scene(meshes, render_fn, n_instances=M, seed=5)
+    P = M * per
+    pmm = np.repeat(np.arange(M, dtype=np.int32), per)
+    poses = np.zeros((P, 4, 4), np.float32)
+    lab = np.zeros(P, np.int32)
+    for m in range(M):
+        # a model the scene has no room for borrows another instance's place and label
+        g = scene.gt_models.index(m) if m in scene.gt_models else m % len(scene.gt_poses)
+        poses[pmm == m] = synth.poses_6dof(scene.gt_poses[g][:3, 3], per, n_views=12, n_inplane=4, seed=m)
+        poses[m * per] = pose_to_mat4x4(scene.gt_poses[g])
+        lab[pmm == m] = g
+    kw = dict(stride=8, cost_type=2, sensor_resolution=0.01)
+    cam = (synth.CX, synth.CY, synth.FX, synth.FY, 100.0)
+    with Renderer(0) as r:
+        r.set_camera(640, 480, proj, *cam)
+        r.set_models(scene.tris, scene.tris_model_count)
+        r.set_scene(scene.source_depth, scene.source_color, scene.source_label)
+        obs = r.depth2cloud_global(scene.source_depth, scene.source_color, 640, 480, 1, *cam, 8, scene.source_label)
+        olab = obs["result_observed_cloud_label"]
+        r.set_observed(obs["result_cloud_eigen"], obs["result_cloud_color"], olab)
+        tot = np.bincount(olab, minlength=len(scene.gt_poses)).astype(np.float32)[lab]
+        full = r.render_cuda_multi_unified("COST", poses, pmm, lab, tot, **kw)
+        sel = np.arange(0, P, 29)
+        img = r.render_cuda_multi_unified("RENDER", poses[sel], pmm[sel], lab[sel])
+    assert len(scene.gt_poses) >= 4 and (full["counts"][0].reshape(M, per)[:, 0] > 20).all()  # first pose of a block = an instance's pose
+    o = orc.costs(img["result_depth"], img["result_color"], 640, 480, *cam, 8, lab[sel], obs["result_cloud_eigen"],
+                  obs["result_cloud_color"], olab, tot[sel], 2, True, 0.01, 20.0)
+    assert np.array_equal(full["counts"][:, sel], o["counts"])
+    for m in range(M):
+        blk = pmm == m
+        with Renderer(0) as r1:
+            r1.set_camera(640, 480, proj, *cam)
+            r1.set_models(meshes[m], [T])
+            r1.set_scene(scene.source_depth, scene.source_color, scene.source_label)
+            r1.set_observed(obs["result_cloud_eigen"], obs["result_cloud_color"], olab)
+            one = r1.render_cuda_multi_unified("COST", poses[blk], np.zeros(per, np.int32), lab[blk], tot[blk], **kw)
+        assert np.array_equal(one["counts"], full["counts"][:, blk]), m
+        assert np.array_equal(one["rendered_cost"], full["rendered_cost"][blk])
+
+
 def test_full_size_properties(orc):
     """BASELINE config-2 shape at full size (20k-triangle mesh, 640x480, stride 8, labels): the oracle is too slow
     here, so check size-independent properties: COST counts == counts recomputed from the RENDER stage images by the
