@@ -101,17 +101,19 @@ int env_int(const char* name, int dflt) {
 }
 
 // ---- observed-cloud grid ------------------------------------------------------------------------------------
-int build_grid(perch_ctx* c, float res) {
+// Uniform grid over the observed cloud with cells at least `h` wide (widened until it has at most max_cells cells):
+// points sorted by cell, x fastest, ascending reference index inside a cell.  *avg_per_cell = points per non-empty cell.
+int build_point_grid(perch_ctx* c, float h, double max_cells, float4** d_pts, int** d_label, uint32_t** d_cell_start,
+                     perch::ObsGridDev* out, double* avg_per_cell) {
     using namespace perch;
     const int n = c->n_obs;
-    cudaFree(c->d_grid_pts); c->d_grid_pts = nullptr;
-    cudaFree(c->d_grid_label); c->d_grid_label = nullptr;
-    cudaFree(c->d_cell_start); c->d_cell_start = nullptr;
-    c->grid = ObsGridDev{};
-    c->grid.n_obs = n;
-    c->grid_res = res;
+    cudaFree(*d_pts); *d_pts = nullptr;
+    cudaFree(*d_label); *d_label = nullptr;
+    cudaFree(*d_cell_start); *d_cell_start = nullptr;
+    *out = ObsGridDev{};
+    out->n_obs = n;
+    if (avg_per_cell) *avg_per_cell = 0.0;
     if (n == 0) return PERCH_OK;
-    float h = (res > 0.f ? res : 1e-3f) * 1.01f;
     float mn[3] = {INFINITY, INFINITY, INFINITY}, mx[3] = {-INFINITY, -INFINITY, -INFINITY};
     for (int i = 0; i < n; ++i)
         for (int k = 0; k < 3; ++k) {
@@ -130,7 +132,7 @@ int build_grid(perch_ctx* c, float res) {
             dim[k] = (int)std::floor((mx[k] - org[k]) * inv_h) + 2;
             cells *= dim[k];
         }
-        if (cells <= 32.0 * 1024 * 1024) break;
+        if (cells <= max_cells) break;
         h *= 1.26f;  // ~2x fewer cells per step; larger cells only add candidates, never lose one
     }
     const size_t ncells = (size_t)dim[0] * dim[1] * dim[2];
@@ -145,7 +147,12 @@ int build_grid(perch_ctx* c, float res) {
         cell_of[i] = (uint32_t)(((size_t)cc[2] * dim[1] + cc[1]) * dim[0] + cc[0]);
         start[cell_of[i] + 1]++;
     }
-    for (size_t k = 0; k < ncells; ++k) start[k + 1] += start[k];
+    size_t nonempty = 0;
+    for (size_t k = 0; k < ncells; ++k) {
+        nonempty += start[k + 1] != 0;
+        start[k + 1] += start[k];
+    }
+    if (avg_per_cell) *avg_per_cell = (double)n / (double)std::max<size_t>(nonempty, 1);
     std::vector<uint32_t> cursor(start.begin(), start.end() - 1);
     std::vector<float4> pts(n);
     std::vector<int> lab(c->obs_has_label ? n : 0);
@@ -160,22 +167,53 @@ int build_grid(perch_ctx* c, float res) {
         pts[slot] = p;
         if (c->obs_has_label) lab[slot] = c->h_obs_label[i];
     }
-    CU(cudaMalloc(&c->d_grid_pts, n * sizeof(float4)));
-    CU(cudaMemcpyAsync(c->d_grid_pts, pts.data(), n * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
+    CU(cudaMalloc(d_pts, n * sizeof(float4)));
+    CU(cudaMemcpyAsync(*d_pts, pts.data(), n * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
     if (c->obs_has_label) {
-        CU(cudaMalloc(&c->d_grid_label, n * sizeof(int)));
-        CU(cudaMemcpyAsync(c->d_grid_label, lab.data(), n * sizeof(int), cudaMemcpyHostToDevice, c->stream));
+        CU(cudaMalloc(d_label, n * sizeof(int)));
+        CU(cudaMemcpyAsync(*d_label, lab.data(), n * sizeof(int), cudaMemcpyHostToDevice, c->stream));
     }
-    CU(cudaMalloc(&c->d_cell_start, (ncells + 1) * sizeof(uint32_t)));
-    CU(cudaMemcpyAsync(c->d_cell_start, start.data(), (ncells + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice,
-                       c->stream));
+    CU(cudaMalloc(d_cell_start, (ncells + 1) * sizeof(uint32_t)));
+    CU(cudaMemcpyAsync(*d_cell_start, start.data(), (ncells + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
     CU(cudaStreamSynchronize(c->stream));  // host vectors go out of scope
-    c->grid.pts = c->d_grid_pts;
-    c->grid.label = c->d_grid_label;
-    c->grid.cell_start = c->d_cell_start;
-    c->grid.ox = org[0]; c->grid.oy = org[1]; c->grid.oz = org[2];
-    c->grid.inv_h = inv_h;
-    c->grid.dx = dim[0]; c->grid.dy = dim[1]; c->grid.dz = dim[2];
+    out->pts = *d_pts;
+    out->label = *d_label;
+    out->cell_start = *d_cell_start;
+    out->ox = org[0]; out->oy = org[1]; out->oz = org[2];
+    out->inv_h = inv_h;
+    out->dx = dim[0]; out->dy = dim[1]; out->dz = dim[2];
+    return PERCH_OK;
+}
+
+// The grid of the cost stage: cells just wider than sensor_resolution, so that the 27 cells around a query hold every
+// observed point within sensor_resolution of it.
+int build_grid(perch_ctx* c, float res) {
+    c->grid_res = res;
+    c->gicp_grid_valid = false;
+    return build_point_grid(c, (res > 0.f ? res : 1e-3f) * 1.01f, 32.0 * 1024 * 1024, &c->d_grid_pts, &c->d_grid_label,
+                            &c->d_cell_start, &c->grid, &c->grid_avg_per_cell);
+}
+
+// The grid GICP searches: its nearest-neighbour queries have no distance gate and always complete rings 0 and 1
+// (27 cells), so on a dense cloud (a full-resolution scene: ~40 points per 1 cm cell) the cost grid makes every query
+// scan hundreds of points.  When the cost grid holds more than 8 points per non-empty cell a second grid is built with
+// cells sized for ~3 points each (points per cell of a surface scale with h^2); otherwise the cost grid is shared.
+int prepare_gicp_grid(perch_ctx* c) {
+    if (c->gicp_grid_valid) return PERCH_OK;
+    const float h_cost = c->grid.inv_h > 0.f ? 1.0f / c->grid.inv_h : 1.f;
+    const double dense = env_int("PERCH_GICP_GRID_DENSITY", 8);
+    if (c->n_obs == 0 || c->grid_avg_per_cell <= dense) {
+        c->gicp_grid = c->grid;
+        c->gicp_grid_h = h_cost;
+    } else {
+        const double target = std::max(1, env_int("PERCH_GICP_GRID_TARGET_X10", 30)) / 10.0;
+        const float h = h_cost * (float)std::sqrt(target / c->grid_avg_per_cell);
+        int rc = build_point_grid(c, h, 64.0 * 1024 * 1024, &c->d_ggrid_pts, &c->d_ggrid_label, &c->d_ggrid_cell_start,
+                                  &c->gicp_grid, nullptr);
+        if (rc) return rc;
+        c->gicp_grid_h = 1.0f / c->gicp_grid.inv_h;
+    }
+    c->gicp_grid_valid = true;
     return PERCH_OK;
 }
 
@@ -352,8 +390,11 @@ int run_gicp(perch_ctx* c, const perch_params* p, const perch::PoseArgs& base, i
     ga.pose_begin = d_rows;
     ga.rows_per_pose = Lh;
     ga.src_normals = d_src_normals;
-    ga.grid = c->grid;
-    ga.grid_h = c->grid.inv_h > 0.f ? 1.0f / c->grid.inv_h : 1.f;
+    if ((rc = prepare_gicp_grid(c))) return rc;
+    ga.grid = c->gicp_grid;
+    ga.grid_h = c->gicp_grid_h;
+    ga.coarse = c->grid;
+    ga.coarse_h = c->grid.inv_h > 0.f ? 1.0f / c->grid.inv_h : 1.f;
     ga.tgt_normals = c->d_tgt_normals;
     ga.tgt_sorted = c->d_obs_xyz4;
     ga.label_range = c->d_label_range;
@@ -447,7 +488,7 @@ void perch_destroy(perch_ctx* c) {
     void* ptrs[] = {c->d_tri_color, c->d_model_low, c->d_model_high, c->d_model_aabb, c->d_tri_lab, c->d_cl_recs, c->d_cl_bounds,
                     c->d_cl_orig, c->d_cl_low, c->d_cl_high,
                     c->d_src_depth, c->d_src_label, c->d_src_rgb, c->d_grid_pts, c->d_grid_label, c->d_cell_start,
-                    c->d_cmp_depth, c->d_cmp_label,
+                    c->d_cmp_depth, c->d_cmp_label, c->d_ggrid_pts, c->d_ggrid_label, c->d_ggrid_cell_start,
                     c->d_obs_lab, c->d_obs_rgb, c->d_scratch, c->d_err_flag, c->d_flush, c->d_obs_xyz_aos,
                     c->d_tgt_normals, c->d_obs_xyz4, c->d_label_range, c->d_gicp, c->d_icp_pcd, c->d_icp_normals};
     for (void* p : ptrs)

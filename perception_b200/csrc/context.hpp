@@ -117,7 +117,15 @@ struct perch_ctx {
     uint8_t* d_obs_rgb = nullptr;      // 3 x N, original order
     float* d_obs_lab = nullptr;        // 3 x N CIELAB of observed colours (cost_type 1), indexed by reference index
     perch::ObsGridDev grid;
+    double grid_avg_per_cell = 0.0;    // points per non-empty cell of `grid`
     bool have_obs = false;
+    // GICP's own grid over the same cloud (finer cells when the cloud is dense; else a copy of `grid`), capi.cu
+    float4* d_ggrid_pts = nullptr;
+    int* d_ggrid_label = nullptr;
+    uint32_t* d_ggrid_cell_start = nullptr;
+    perch::ObsGridDev gicp_grid;
+    float gicp_grid_h = 0.f;
+    bool gicp_grid_valid = false;
 
     // per-call scratch (grown on demand, never shrunk)
     void* d_scratch = nullptr;

@@ -33,7 +33,8 @@ namespace {
 #endif
 constexpr int kGicpThreads = PERCH_GICP_THREADS;
 constexpr int kGicpWarps = kGicpThreads / 32;
-constexpr int kMaxRings = 12;        // nearest-neighbour shells searched before falling back to a linear scan
+constexpr int kMaxRings = 12;        // nearest-neighbour shells of the coarse grid searched before a linear scan
+constexpr int kFineRings = 6;        // shells of the fine grid searched before moving to the coarse one
 constexpr float kPlaneEps = 1e-3f;  // fast_gicp RegularizationMethod::PLANE: singular values (1, 1, 1e-3)
 
 // Eigenvector of the smallest eigenvalue of the symmetric matrix [a00 a01 a02; a01 a11 a12; a02 a12 a22]
@@ -107,34 +108,22 @@ __global__ void target_normals_kernel(const float* xyz_aos, const int* knn_index
     normals[3 * (size_t)i] = nn[0]; normals[3 * (size_t)i + 1] = nn[1]; normals[3 * (size_t)i + 2] = nn[2];
 }
 
-// Exact nearest observed point (optionally of one label) by ring expansion over the uniform grid: after ring r every
-// unvisited point is at least r*h away, so the search stops once the best squared distance is below (r*h)^2.
-// Same distance arithmetic and tie-break (lowest reference index) as the cost stage (exact_math.cuh:sqdist3).
-__device__ inline void nn_unbounded(const ObsGridDev& g, float h, float qx, float qy, float qz, bool use_label, int label,
-                                    float& best, int& best_ref, float4& best_pt) {
-    best = FLT_MAX;
-    best_ref = -1;
+// Ring expansion over one uniform grid, carrying the best candidate in and out.  Returns true when the result is final:
+// the best squared distance is below the bound of the unvisited cells, or every ring of the grid has been visited.
+// Returns false after max_rings rings without that certainty.  Same distance arithmetic and tie-break (lowest reference
+// index) as the cost stage (exact_math.cuh:sqdist3).
+__device__ inline bool ring_search(const ObsGridDev& g, float h, int max_rings, float qx, float qy, float qz, bool use_label,
+                                   int label, float& best, int& best_ref, float4& best_pt) {
     const int cx = min(max((int)floorf((qx - g.ox) * g.inv_h), 0), g.dx - 1);
     const int cy = min(max((int)floorf((qy - g.oy) * g.inv_h), 0), g.dy - 1);
     const int cz = min(max((int)floorf((qz - g.oz) * g.inv_h), 0), g.dz - 1);
     const int rmax = max(max(max(cx, g.dx - 1 - cx), max(cy, g.dy - 1 - cy)), max(cz, g.dz - 1 - cz));
     for (int r = 0; r <= rmax; ++r) {
-        if (r > kMaxRings) {
-            // far from every candidate (outlier pose, or a label with few points): a linear scan of the sorted point
-            // array is cheaper than ever larger mostly-empty shells, and just as exact
-            for (int j = 0; j < g.n_obs; ++j) {
-                if (use_label && __ldg(g.label + j) != label) continue;
-                const float4 p = __ldg(g.pts + j);
-                const float d = sqdist3(qx, qy, qz, p.x, p.y, p.z);
-                const int ref = __float_as_int(p.w);
-                if (d < best || (d == best && ref < best_ref)) { best = d; best_ref = ref; best_pt = p; }
-            }
-            return;
-        }
         if (best_ref >= 0) {
             const float lim = (float)(r - 1) * h;  // ring r-1 complete => unvisited points are >= (r-1)*h away ... (*)
-            if (r >= 1 && best < lim * lim * 0.9999f) break;
+            if (r >= 1 && best < lim * lim * 0.9999f) return true;
         }
+        if (r > max_rings) return false;
         const int z0 = max(cz - r, 0), z1 = min(cz + r, g.dz - 1);
         const int y0 = max(cy - r, 0), y1 = min(cy + r, g.dy - 1);
         for (int z = z0; z <= z1; ++z) {
@@ -163,8 +152,32 @@ __device__ inline void nn_unbounded(const ObsGridDev& g, float h, float qx, floa
             }
         }
     }
-    // (*) a query inside cell c is at least (rho - 1)*h from any point of a cell at Chebyshev distance rho; after rings
-    // 0..r-1 the unvisited cells have rho >= r, hence the bound (r-1)*h used before visiting ring r.
+    return true;
+    // (*) a query inside cell c is at least (rho - 1)*h from any point of a cell at Chebyshev distance rho (also when
+    // the query lies outside the grid and c is the clamped cell); after rings 0..r-1 the unvisited cells have rho >= r,
+    // hence the bound (r-1)*h used before visiting ring r.
+}
+
+// Exact nearest observed point (optionally of one label), no distance gate: ring expansion over the fine grid (cells
+// sized for a few points each), then -- for queries farther from every candidate than its rings reach -- over the
+// coarse grid of the cost stage with the best candidate carried along, and only for outliers beyond that (a pose far
+// from the scene, a label with few points) a linear scan of the point array.  All three give the same answer.
+__device__ inline void nn_unbounded(const ObsGridDev& fine, float h_fine, const ObsGridDev& coarse, float h_coarse,
+                                    float qx, float qy, float qz, bool use_label, int label, float& best, int& best_ref,
+                                    float4& best_pt) {
+    best = FLT_MAX;
+    best_ref = -1;
+    const bool two_level = coarse.pts != fine.pts;
+    if (ring_search(fine, h_fine, two_level ? kFineRings : kMaxRings, qx, qy, qz, use_label, label, best, best_ref, best_pt)) return;
+    if (two_level && ring_search(coarse, h_coarse, kMaxRings, qx, qy, qz, use_label, label, best, best_ref, best_pt))
+        return;
+    for (int j = 0; j < fine.n_obs; ++j) {
+        if (use_label && __ldg(fine.label + j) != label) continue;
+        const float4 p = __ldg(fine.pts + j);
+        const float d = sqdist3(qx, qy, qz, p.x, p.y, p.z);
+        const int ref = __float_as_int(p.w);
+        if (d < best || (d == best && ref < best_ref)) { best = d; best_ref = ref; best_pt = p; }
+    }
 }
 
 // The same search over a short contiguous range of the label-sorted cloud (a label's points in 6-DoF, the whole cloud
@@ -379,7 +392,7 @@ __global__ void __launch_bounds__(kGicpThreads, PERCH_GICP_MIN_BLOCKS) gicp_kern
             const float pz = R[6] * ax + R[7] * ay + R[8] * az + t[2];
             float best; int ref; float4 b;
             if (stream_target) nn_range(a.tgt_sorted, lb, le, px, py, pz, best, ref, b);
-            else nn_unbounded(a.grid, a.grid_h, px, py, pz, use_label, label, best, ref, b);
+            else nn_unbounded(a.grid, a.grid_h, a.coarse, a.coarse_h, px, py, pz, use_label, label, best, ref, b);
             if (ref < 0) continue;  // no target point carries this label
             const float nax = nrm[3 * i], nay = nrm[3 * i + 1], naz = nrm[3 * i + 2];
             const float na[3] = {R[0] * nax + R[1] * nay + R[2] * naz, R[3] * nax + R[4] * nay + R[5] * naz,

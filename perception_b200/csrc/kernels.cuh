@@ -119,8 +119,10 @@ struct GicpArgs {
     const int* pose_begin = nullptr;     // exclusive scan of per-lattice-row point counts (cloud.cu): pose p owns
     int rows_per_pose = 1;               //   points [pose_begin[p*rows_per_pose], pose_begin[(p+1)*rows_per_pose])
     float* src_normals = nullptr;        // N x 3 scratch (used when a pose's cloud exceeds smem_points)
-    ObsGridDev grid;                     // observed cloud (target)
+    ObsGridDev grid;                     // observed cloud (target): cells sized for a few points each
     float grid_h = 0.f;                  // cell size of `grid`
+    ObsGridDev coarse;                   // the cost stage's grid over the same cloud (== grid when the cloud is sparse)
+    float coarse_h = 0.f;
     const float* tgt_normals = nullptr;  // n_obs x 3, indexed like the grid's reference indices
     const float4* tgt_sorted = nullptr;  // the label-sorted observed cloud itself (index = reference index), or null
     const int* label_range = nullptr;    // [begin, end) of every label in tgt_sorted (6-DoF)

@@ -217,3 +217,37 @@ def test_gicp_edge_cases(orc):
         r.set_observed(np.zeros((0, 3), np.float32), None, None)                              # no target at all
         g0 = r.gicp(poses[:1], pmm[:1], None, stride=4, sensor_resolution=0.0075)
         assert g0["iterations"][0] == 0 and np.allclose(g0["adjusted_poses"][0], poses[0], atol=1e-4)
+
+
+@pytest.mark.gpu
+def test_gicp_dense_scene_cloud_grids_agree(orc, monkeypatch):
+    """BASELINE configs[3] in shape: the target is the FULL-resolution scene cloud (stride 1).  GICP then searches its own
+    finer grid, falls back to the cost grid and finally to a linear scan; all three are exact, so the refined poses must
+    not depend on which one answers.  Forced three ways: fine grid (default), cost grid only, and a fine grid so fine
+    that most queries leave it.  (The cost-grid path is the one held to the double-precision oracle by the tests above; the
+    oracle's brute-force normals are O(N^2) and out of reach at 200k points.)"""
+    from perception_b200 import synth
+    from perception_b200.renderer import Renderer
+    case = make_case(600, 3, 42)
+    s = case.scene
+    cam = (case.cx, case.cy, case.fx, case.fy, synth.DEPTH_FACTOR)
+    poses, pmm, _ = poses_near_gt(case, 24, trans_sigma=0.01, rot_sigma=0.05)
+    far = poses[5].copy(); far[2, 3] -= 25.0   # 25 cm in front of everything: beyond the fine grid's rings
+    poses = np.concatenate([poses, far[None]])
+    pmm = np.concatenate([pmm, pmm[5:6]])
+    outs = []
+    for density, target in (("8", "30"), ("1000000", "30"), ("8", "3")):
+        monkeypatch.setenv("PERCH_GICP_GRID_DENSITY", density)
+        monkeypatch.setenv("PERCH_GICP_GRID_TARGET_X10", target)
+        with Renderer(0) as r:
+            r.set_camera(case.width, case.height, case.proj, *cam)
+            r.set_models(s.tris, s.tris_model_count)
+            r.set_scene(s.source_depth, s.source_color, None)
+            obs = r.depth2cloud_global(s.source_depth, s.source_color, case.width, case.height, 1, *cam, 1)
+            assert obs["rendered_cloud_point_num"] > 150000
+            r.set_observed(obs["result_cloud_eigen"], obs["result_cloud_color"], None)
+            outs.append(r.gicp(poses, pmm, None, stride=4, sensor_resolution=0.0075, icp_max_iterations=8))
+    assert outs[0]["iterations"].max() >= 2
+    for o in outs[1:]:
+        assert np.array_equal(o["iterations"], outs[0]["iterations"])
+        assert np.array_equal(o["transforms"], outs[0]["transforms"])
