@@ -606,16 +606,48 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                 }
             } else {
                 // ---- 3. cost over the band's lattice pixels ---------------------------------------------------
-                for (int c = tid; c < band_cells; c += kThreads) {
+                // 3a: covered pixels that survive the source-occlusion rule are compacted into the (now idle) candidate
+                // queue, so that the nearest-neighbour queries below run with every lane busy
+                const bool compact = band_cells <= kQueueCap;
+                if (compact) {
+                    if (tid == 0) s_qcount = 0;
+                    __syncthreads();
+                    for (int c0 = 0; c0 < band_cells; c0 += kThreads) {
+                        const int c = c0 + tid;
+                        bool live = false;
+                        if (c < band_cells) {
+                            const zkey k = zbuf[c];
+                            if (k != Z::empty()) {
+                                const int32_t d = Z::depth(k);
+                                const int u = (rx0 + c % tile_w) * s, v = (by0 + c / tile_w) * s;
+                                const int32_t src = __ldg(a.scene.depth + v * W + u);
+                                const int src_label = (use_label && a.scene.label) ? (int)__ldg(a.scene.label + v * W + u) : 0;
+                                // compute_point_clouds.cuh:64,123: only positive depths become points
+                                live = !source_occludes(d, src, use_label, pose_label, src_label, a.occlusion_threshold) && d > 0;
+                            }
+                        }
+                        const unsigned lb = __ballot_sync(0xffffffffu, live);
+                        int base = 0;
+                        if (lane == 0 && lb) base = atomicAdd(&s_qcount, __popc(lb));
+                        base = __shfl_sync(0xffffffffu, base, 0);
+                        if (live) queue[base + __popc(lb & ((1u << lane) - 1u))] = c;
+                    }
+                    __syncthreads();
+                }
+                const int n_live = compact ? s_qcount : band_cells;
+                for (int e = tid; e < n_live; e += kThreads) {
+                    const int c = compact ? queue[e] : e;
                     zkey k = zbuf[c];
-                    if (k == Z::empty()) continue;
                     int32_t d = Z::depth(k);
                     int lx = rx0 + c % tile_w, ly = by0 + c / tile_w;
                     int u = lx * s, v = ly * s;
-                    int32_t src = __ldg(a.scene.depth + v * W + u);
-                    int src_label = (use_label && a.scene.label) ? (int)__ldg(a.scene.label + v * W + u) : 0;
-                    if (source_occludes(d, src, use_label, pose_label, src_label, a.occlusion_threshold)) continue;
-                    if (d <= 0) continue;  // compute_point_clouds.cuh:64,123
+                    if (!compact) {
+                        if (k == Z::empty()) continue;
+                        int32_t src = __ldg(a.scene.depth + v * W + u);
+                        int src_label = (use_label && a.scene.label) ? (int)__ldg(a.scene.label + v * W + u) : 0;
+                        if (source_occludes(d, src, use_label, pose_label, src_label, a.occlusion_threshold)) continue;
+                        if (d <= 0) continue;  // compute_point_clouds.cuh:64,123
+                    }
                     ++n_local;
                     float qx, qy, qz;
                     back_project(u, v, d, a.cam.cx, a.cam.cy, a.cam.fx, a.cam.fy, a.cam.depth_factor, qx, qy, qz);
