@@ -332,6 +332,13 @@ int perch_get_observed(perch_ctx* ctx, float* xyz_aos, uint8_t* rgb_soa, int* la
  * perch_set_scene, or as composed by perch_compose_source (width*height int32). */
 int perch_get_source_depth(perch_ctx* ctx, int32_t* out_depth);
 
+/* Diagnostic (host only, no device needed): runs the mesh preprocessing of perch_set_models (edge-sharing triangles
+ * paired into quads, quads into clusters with bounding spheres) and checks it.  out = {clusters, triangles stored in
+ * pairs, triangles stored alone, coordinates that differ from the input (must be 0), triangles not stored exactly once
+ * (must be 0), vertices outside their cluster's sphere or triangles filed under the wrong model (must be 0)}. */
+int perch_cluster_stats(const perch_triangle* tris, int64_t n_tris, const int* tris_model_count, int n_models,
+                        int64_t out[6]);
+
 /* The label image the occlusion rule currently tests against (width*height uint8); *has_label = 0 and the buffer
  * untouched when there is none. */
 int perch_get_source_label(perch_ctx* ctx, uint8_t* out_label, int* has_label);

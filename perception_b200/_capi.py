@@ -162,6 +162,7 @@ SIGNATURES = {
     "perch_set_input": (C.c_int, [_P, C.POINTER(perch_input), C.POINTER(C.c_int)]),
     "perch_get_observed": (C.c_int, [_P, _V, _V, _V, C.c_int, C.POINTER(C.c_int)]),
     "perch_get_source_depth": (C.c_int, [_P, _V]),
+    "perch_cluster_stats": (C.c_int, [_V, C.c_int64, _V, C.c_int, _V]),
     "perch_get_source_label": (C.c_int, [_P, _V, C.POINTER(C.c_int)]),
     "perch_compose_source": (C.c_int, [_P, _V, C.c_int, _V, _V, C.c_int]),
     "perch_tree_flags": (C.c_int, [_P, _V, C.c_int, _V, _V, C.c_float, _V, _V, _V, _V]),

@@ -486,7 +486,7 @@ void perch_destroy(perch_ctx* c) {
     DeviceGuard g(c->device);
     cudaStreamSynchronize(c->stream);
     void* ptrs[] = {c->d_tri_color, c->d_model_low, c->d_model_high, c->d_model_aabb, c->d_tri_lab, c->d_cl_recs, c->d_cl_bounds,
-                    c->d_cl_orig, c->d_cl_low, c->d_cl_high,
+                    c->d_cl_orig, c->d_cl_perm, c->d_cl_low, c->d_cl_high,
                     c->d_src_depth, c->d_src_label, c->d_src_rgb, c->d_grid_pts, c->d_grid_label, c->d_cell_start,
                     c->d_cmp_depth, c->d_cmp_label, c->d_ggrid_pts, c->d_ggrid_label, c->d_ggrid_cell_start,
                     c->d_obs_lab, c->d_obs_rgb, c->d_scratch, c->d_err_flag, c->d_flush, c->d_obs_xyz_aos,
@@ -559,7 +559,9 @@ int perch_set_camera(perch_ctx* c, int width, int height, const float proj16[16]
 int perch_set_models(perch_ctx* c, const perch_triangle* tris, int64_t n_tris, const int* tris_model_count, int n_models) {
     if (!c || (!tris && n_tris > 0) || !tris_model_count || n_models <= 0 || n_tris < 0)
         return fail(PERCH_ERR_INVALID, "bad set_models argument");
-    if (n_tris > INT_MAX) return fail(PERCH_ERR_CAPACITY, "more than INT_MAX triangles");
+    // candidate entries carry the triangle slot in 26 bits (pose_kernels.cu) and a model without shared edges needs two
+    // slots per triangle
+    if (n_tris > (1 << 24)) return fail(PERCH_ERR_CAPACITY, "more than 2^24 triangles in one context");
     DeviceGuard g(c->device);
     std::vector<int> low(n_models), high(n_models);
     int64_t run = 0;
@@ -610,16 +612,19 @@ int perch_set_models(perch_ctx* c, const perch_triangle* tris, int64_t n_tris, c
             cs.bounds.assign(4, 0.f);
             cs.recs.assign(perch::kClusterFloats, 0.f);
             cs.orig.assign(perch::kClusterTris, 0);
+            cs.perm.assign(1, 0xFFFFFFu);  // four invalid slots
         }
         if ((rc = upload(&c->d_cl_recs, cs.recs.data(), cs.recs.size(), c->stream))) return rc;
         if ((rc = upload(&c->d_cl_bounds, reinterpret_cast<const float4*>(cs.bounds.data()), cs.bounds.size() / 4, c->stream))) return rc;
         if ((rc = upload(&c->d_cl_orig, cs.orig.data(), cs.orig.size(), c->stream))) return rc;
+        if ((rc = upload(&c->d_cl_perm, cs.perm.data(), cs.perm.size(), c->stream))) return rc;
         if ((rc = upload(&c->d_cl_low, cs.model_low.data(), cs.model_low.size(), c->stream))) return rc;
         if ((rc = upload(&c->d_cl_high, cs.model_high.data(), cs.model_high.size(), c->stream))) return rc;
         CU(cudaStreamSynchronize(c->stream));  // host vectors go out of scope
         c->models.cl_recs = c->d_cl_recs;
         c->models.cl_bounds = c->d_cl_bounds;
         c->models.cl_orig = c->d_cl_orig;
+        c->models.cl_perm = c->d_cl_perm;
         c->models.cl_low = c->d_cl_low;
         c->models.cl_high = c->d_cl_high;
     }
@@ -634,6 +639,57 @@ int perch_set_models(perch_ctx* c, const perch_triangle* tris, int64_t n_tris, c
     c->h_model_high = high;
     c->have_models = true;
     note_memory(c);
+    return PERCH_OK;
+}
+
+int perch_cluster_stats(const perch_triangle* tris, int64_t n_tris, const int* tris_model_count, int n_models,
+                        int64_t out[6]) {
+    if ((!tris && n_tris > 0) || !tris_model_count || n_models <= 0 || n_tris < 0 || !out || n_tris > INT_MAX)
+        return fail(PERCH_ERR_INVALID, "bad cluster_stats argument");
+    std::vector<int> low(n_models), high(n_models);
+    int64_t run = 0;
+    for (int m = 0; m < n_models; ++m) {
+        low[m] = (int)std::min<int64_t>(run, n_tris);
+        run += std::max(tris_model_count[m], 0);
+        high[m] = (int)std::min<int64_t>(run, n_tris);
+    }
+    std::vector<float> tri9((size_t)std::max<int64_t>(n_tris, 1) * 9);
+    for (int64_t t = 0; t < n_tris; ++t) memcpy(&tri9[(size_t)t * 9], tris[t].v0, 36);
+    perch::ClusterSet cs = perch::build_clusters(tri9.data(), low, high);
+    const size_t nc = cs.bounds.size() / 4;
+    std::vector<int> seen((size_t)std::max<int64_t>(n_tris, 1), 0);
+    int64_t paired = 0, single = 0, mismatch = 0, outside = 0;
+    for (size_t c = 0; c < nc; ++c) {
+        int model = -1;
+        for (int m = 0; m < n_models; ++m)
+            if ((int)c >= cs.model_low[m] && (int)c < cs.model_high[m]) model = m;
+        for (int j = 0; j < perch::kClusterTris; ++j) {
+            const uint32_t perm = (cs.perm[c] >> (6 * j)) & 63u;
+            if (perm == perch::kPermInvalid) continue;
+            const int t = cs.orig[c * perch::kClusterTris + j];
+            if (t < 0 || t >= n_tris || model < 0 || t < low[model] || t >= high[model]) { ++outside; continue; }
+            ++seen[t];
+            const uint32_t other = (cs.perm[c] >> (6 * (j ^ 1))) & 63u;
+            (other == perch::kPermInvalid ? single : paired) += 1;
+            const float* rec = &cs.recs[c * perch::kClusterFloats + (j >> 1)];
+            for (int k = 0; k < 3; ++k)
+                for (int a = 0; a < 3; ++a) {
+                    const float got = rec[(((perm >> (2 * k)) & 3u) * 3 + a) * perch::kClusterQuads];
+                    if (memcmp(&got, &tri9[(size_t)t * 9 + 3 * k + a], 4) != 0) ++mismatch;
+                }
+            // every vertex must lie inside the cluster's bounding sphere
+            const float* b = &cs.bounds[4 * c];
+            for (int k = 0; k < 3 && std::isfinite(b[3]); ++k) {
+                double d2 = 0;
+                for (int a = 0; a < 3; ++a) d2 += ((double)tri9[(size_t)t * 9 + 3 * k + a] - b[a]) * ((double)tri9[(size_t)t * 9 + 3 * k + a] - b[a]);
+                if (std::sqrt(d2) > (double)b[3]) ++outside;
+            }
+        }
+    }
+    int64_t missing = 0;
+    for (int m = 0; m < n_models; ++m)
+        for (int t = low[m]; t < high[m]; ++t) missing += seen[t] != 1;
+    out[0] = (int64_t)nc; out[1] = paired; out[2] = single; out[3] = mismatch; out[4] = missing; out[5] = outside;
     return PERCH_OK;
 }
 

@@ -40,7 +40,8 @@ struct ModelsDev {
     const int* model_high = nullptr;  // inclusive scan
     const float* model_aabb = nullptr;  // 6 floats per model: min xyz, max xyz (object-space)
     // clusters (clusters.hpp): Morton-ordered groups of kClusterTris triangles with a bounding sphere
-    const float* cl_recs = nullptr;     // n_clusters x 36: rec[c][k][j] = coordinate k of triangle j
+    const float* cl_recs = nullptr;     // n_clusters x 24: rec[c][3 * i + a][q] = coordinate a of vertex i of quad q
+    const uint32_t* cl_perm = nullptr;  // n_clusters: 6 bits per triangle slot, its three quad vertices in original order
     const float4* cl_bounds = nullptr;  // centre xyz, radius
     const int* cl_orig = nullptr;       // n_clusters x 4: original triangle index (colour tie-break, colour lookup)
     const int* cl_low = nullptr;        // cluster range per model
@@ -84,6 +85,7 @@ struct perch_ctx {
     float* d_model_aabb = nullptr;
     float* d_tri_lab = nullptr;        // 3 x T CIELAB of the triangle colours (cost_type 1)
     float* d_cl_recs = nullptr;
+    uint32_t* d_cl_perm = nullptr;
     float4* d_cl_bounds = nullptr;
     int* d_cl_orig = nullptr;
     int* d_cl_low = nullptr;

@@ -34,9 +34,10 @@ constexpr int kWarps = kThreads / 32;
 constexpr int kMinCtas = 1024 / kThreads;  // resident CTAs per SM the register budget is sized for (32 warps)
 constexpr int kQueueCap = 16 * kThreads;   // candidate triangles buffered between exact passes
 constexpr int kClaim = 64;        // clusters tested per warp claim (two per lane: independent loads in flight)
-constexpr int kPendCap = 96;      // per-warp list of surviving clusters awaiting the per-triangle test (< 8 carried + 64)
-constexpr int kClaimMaxTris = (kClaim + 8) * 4;  // most candidates one claim can append (incl. carried clusters)
-static_assert(kClusterTris == 4, "lane mapping of the per-triangle test assumes 4 triangles per cluster");
+constexpr int kPendStep = 16;     // surviving clusters tested per warp step (two lanes each: one per quad)
+constexpr int kPendCap = 96;      // per-warp list of surviving clusters awaiting the per-triangle test (< 16 carried + 64)
+constexpr int kClaimMaxTris = (kClaim + kPendStep) * 4;  // most candidates one claim can append (incl. carried clusters)
+static_assert(kClusterTris == 4 && kClusterQuads == 2, "lane mapping of the per-triangle test assumes 2 quads of 2 triangles");
 constexpr int kBigCells = 48;     // lattice pixels above which a triangle is rasterised by the whole CTA
 constexpr int kBigCap = 64;
 // Bounds on |approximate - exact| screen coordinates (pixels) assumed by the culling levels.  tools/approx_error.cu
@@ -113,11 +114,23 @@ __device__ __forceinline__ LatticeRect lattice_rect_of(float bminx, float bmaxx,
     return r;
 }
 
-// t = 4 * cluster + lane-in-cluster indexes the cluster records (clusters.hpp)
-__device__ __forceinline__ void load_tri(const ModelsDev& m, int t, float v[9]) {
-    const float* rec = m.cl_recs + (int64_t)(t >> 2) * kClusterFloats + (t & 3);
+// Candidate entry = triangle slot t (4 * cluster + j: triangle j & 1 of quad j >> 1, clusters.hpp) in the low kSlotBits
+// bits and, above them, the slot's 6-bit permutation: which three of the quad's four vertices the triangle uses, in its
+// ORIGINAL order.  Carrying the permutation spares the exact path a dependent load.
+constexpr int kSlotBits = 26;
+constexpr int kSlotMask = (1 << kSlotBits) - 1;
+__device__ __forceinline__ void load_tri(const ModelsDev& m, int entry, float v[9]) {
+    const int t = entry & kSlotMask;
+    const uint32_t perm = (uint32_t)entry >> kSlotBits;
+    const int c = t >> 2, j = t & 3;
+    const float* rec = m.cl_recs + (int64_t)c * kClusterFloats + (j >> 1);
 #pragma unroll
-    for (int k = 0; k < 9; ++k) v[k] = __ldg(rec + k * kClusterTris);
+    for (int k = 0; k < 3; ++k) {
+        const float* p = rec + ((perm >> (2 * k)) & 3u) * (3 * kClusterQuads);
+        v[3 * k] = __ldg(p);
+        v[3 * k + 1] = __ldg(p + kClusterQuads);
+        v[3 * k + 2] = __ldg(p + 2 * kClusterQuads);
+    }
 }
 
 // CIEDE2000 between two CIELAB triples with the reference's mixed float/double evaluation
@@ -323,9 +336,9 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
 
             // Exact path for one triangle: the reference's float sequence (exact_math.cuh), its bbox loops restricted
             // to lattice pixels of this band, z-test with atomicMin.  `coop` = all threads of the CTA share the work.
-            auto raster_tri = [&](int t, bool coop, bool allow_defer) -> bool {
+            auto raster_tri = [&](int entry, bool coop, bool allow_defer) -> bool {
                 float v[9];
-                load_tri(a.models, t, v);
+                load_tri(a.models, entry, v);
                 ScreenVertex A = transform_vertex(s_pose, a.cam.proj, wf, hf, v[0], v[1], v[2]);
                 ScreenVertex B = transform_vertex(s_pose, a.cam.proj, wf, hf, v[3], v[4], v[5]);
                 ScreenVertex C = transform_vertex(s_pose, a.cam.proj, wf, hf, v[6], v[7], v[8]);
@@ -343,7 +356,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                 setup_edges(A, B, C, ts);
                 // original triangle index (colour tie-break and lookup), or the pose index for perch_compose_source
                 const uint32_t id = !COLOR ? 0u : (MODE == MODE_IMAGE && a.key_pose_id) ? (uint32_t)pose_i
-                                                                                        : (uint32_t)__ldg(a.models.cl_orig + t);
+                                                : (uint32_t)__ldg(a.models.cl_orig + (entry & kSlotMask));
                 if (coop) {
                     for (int c = tid; c < cells; c += kThreads) {
                         int ly = y0 + c / w, lx = x0 + c % w;
@@ -394,28 +407,34 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                 if (!(zden > 1e-6f) || !(fabsf(ux) + fabsf(uy) + Rx + Ry < 1e30f)) return true;
                 return lattice_hit(ux - Rx, ux + Rx, uy - Ry, uy + Ry);
             };
-            // Level 2: approximate bbox of one triangle.  NaN/inf/absurd coordinates (whose handling by the
-            // reference's select chain is order dependent) go to the exact path, which re-derives everything.
-            auto tri_hits = [&](int t) -> bool {
-                float v[9];
-                load_tri(a.models, t, v);
-                float ux[3], uy[3], iz[3];
+            // Level 2: approximate bboxes of the two triangles of one quad -- four vertex transforms for two triangles
+            // (vertices 0,1 = shared edge, 2 = first triangle's own, 3 = second's).  Bit 0 / 1 of the result = first /
+            // second triangle is a candidate.  NaN/inf/absurd coordinates (whose handling by the reference's select
+            // chain is order dependent) go to the exact path, which re-derives everything.
+            auto quad_hits = [&](int c, int q) -> unsigned {
+                const float* rec = a.models.cl_recs + (int64_t)c * kClusterFloats + q;
+                float ux[4], uy[4], izmax = 0.f;
 #pragma unroll
-                for (int k = 0; k < 3; ++k) {
-                    const float x = v[3 * k], y = v[3 * k + 1], z = v[3 * k + 2];
+                for (int k = 0; k < 4; ++k) {
+                    const float x = __ldg(rec + (3 * k) * kClusterQuads), y = __ldg(rec + (3 * k + 1) * kClusterQuads),
+                                z = __ldg(rec + (3 * k + 2) * kClusterQuads);
                     const float n0 = fmaf(z, U2, fmaf(y, U1, fmaf(x, U0, U3)));
                     const float n1 = fmaf(z, V2, fmaf(y, V1, fmaf(x, V0, V3)));
-                    iz[k] = __frcp_approx(fmaf(z, C2, fmaf(y, C1, fmaf(x, C0, C3))));
-                    ux[k] = fmaf(n0, iz[k], offx);
-                    uy[k] = fmaf(n1, iz[k], offy);
+                    const float iz = __frcp_approx(fmaf(z, C2, fmaf(y, C1, fmaf(x, C0, C3))));
+                    ux[k] = fmaf(n0, iz, offx);
+                    uy[k] = fmaf(n1, iz, offy);
+                    izmax = fmaxf(izmax, fabsf(iz));
                 }
-                float sum = (ux[0] + ux[1]) + (ux[2] + uy[0]) + (uy[1] + uy[2]);
-                if (!(fabsf(sum) < 1e30f)) return true;
-                if (!(fmaxf(fmaxf(fabsf(iz[0]), fabsf(iz[1])), fabsf(iz[2])) < 1.0f / kNearZ)) return true;  // near the camera plane
-                return lattice_hit(fminf(fminf(ux[0], ux[1]), ux[2]), fmaxf(fmaxf(ux[0], ux[1]), ux[2]),
-                                   fminf(fminf(uy[0], uy[1]), uy[2]), fmaxf(fmaxf(uy[0], uy[1]), uy[2]));
+                const float sum = ((ux[0] + ux[1]) + (ux[2] + ux[3])) + ((uy[0] + uy[1]) + (uy[2] + uy[3]));
+                // not finite, or a vertex near the camera plane: both triangles go to the exact path
+                if (!(fabsf(sum) < 1e30f) || !(izmax < 1.0f / kNearZ)) return 3u;
+                const float ex0 = fminf(ux[0], ux[1]), ex1 = fmaxf(ux[0], ux[1]);
+                const float ey0 = fminf(uy[0], uy[1]), ey1 = fmaxf(uy[0], uy[1]);
+                unsigned r = lattice_hit(fminf(ex0, ux[2]), fmaxf(ex1, ux[2]), fminf(ey0, uy[2]), fmaxf(ey1, uy[2])) ? 1u : 0u;
+                if (lattice_hit(fminf(ex0, ux[3]), fmaxf(ex1, ux[3]), fminf(ey0, uy[3]), fmaxf(ey1, uy[3]))) r |= 2u;
+                return r;
             };
-            // Level 3 (start of pass B, every lane busy): a candidate whose approximate bbox holds exactly ONE lattice
+            // Level 3 (when a warp has 32 candidates staged, every lane busy): a candidate whose approximate bbox holds exactly ONE lattice
             // pixel is dropped when that pixel lies clearly outside the triangle.  With approximate vertices within
             // d px of the exact ones, an edge function cross(Vj - Vi, P - Vi) differs from its exact counterpart
             // by less than 4.25 * d * D (D >= the largest distance involved; d = kEps3 scaled for near vertices), so `sgn * E < -6 d D` together with
@@ -453,34 +472,57 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                 const float worst = fminf(fminf(e0 * sgn, e1 * sgn), e2 * sgn);
                 return single && (fabsf(area2) > tol) && (worst < -tol) && (tol < 1e6f);
             };
-            // per-triangle test of 8 pending clusters (4 lanes each); candidates go to the shared queue
+            // Level-2 survivors are staged per warp; whenever 32 are staged (and at the end of pass A) every lane takes
+            // one through level 3 and the survivors of that go to the CTA's queue with one atomic per batch.
             int nstage = 0;  // warp-uniform: staged candidates of this warp
             const unsigned lt_mask = (1u << lane) - 1u;
-            auto test_pending = [&](int first, int count) {
-                const int e = lane >> 2;
-                bool hit = false;
-                int t = 0;
-                if (e < count) {
-                    t = 4 * wpend[first + e] + (lane & 3);
-                    hit = tri_hits(t);
+            auto flush_stage = [&](int count) {
+                int entry = 0;
+                bool keep = false;
+                if (lane < count) {
+                    entry = wstage[lane];
+                    keep = !pixel_outside(entry);
                 }
-                // candidates are staged per warp and moved to the shared queue 32 at a time: one atomic per 32 entries
+                const unsigned kb = __ballot_sync(0xffffffffu, keep);
+                if (lane == 0) { STAT(3, __popc(kb)); STAT(9, 1); }
+                int slot = 0;
+                if (lane == 0 && kb) slot = atomicAdd(&s_qcount, __popc(kb));
+                slot = __shfl_sync(0xffffffffu, slot, 0);
+                if (keep) queue[slot + __popc(kb & lt_mask)] = entry;
+            };
+            auto stage_hit = [&](bool hit, int entry) {
                 const unsigned ballot = __ballot_sync(0xffffffffu, hit);
-                if (hit) wstage[nstage + __popc(ballot & lt_mask)] = t;
+                if (hit) wstage[nstage + __popc(ballot & lt_mask)] = entry;
                 nstage += __popc(ballot);
                 if (lane == 0) { STAT(2, __popc(ballot)); STAT(8, 1); }
                 if (nstage >= 32) {
                     __syncwarp();
-                    int slot = 0;
-                    if (lane == 0) slot = atomicAdd(&s_qcount, 32);
-                    slot = __shfl_sync(0xffffffffu, slot, 0);
-                    queue[slot + lane] = wstage[lane];
+                    flush_stage(32);
                     nstage -= 32;
                     const int carry = (lane < nstage) ? wstage[32 + lane] : 0;
                     __syncwarp();
                     if (lane < nstage) wstage[lane] = carry;
                 }
                 __syncwarp();
+            };
+            // per-triangle test of kPendStep pending clusters, one lane per quad; a slot that merely repeats its quad's
+            // other triangle (kPermInvalid) is never a candidate
+            auto test_pending = [&](int first, int count) {
+                const int e = lane >> 1, q = lane & 1;
+                unsigned hits = 0;
+                int ea = 0, eb = 0;
+                if (e < count) {
+                    const int c = wpend[first + e];
+                    const uint32_t perm = __ldg(a.models.cl_perm + c) >> (12 * q);
+                    const uint32_t pa = perm & 63u, pb = (perm >> 6) & 63u;
+                    hits = quad_hits(c, q);
+                    if (pa == kPermInvalid) hits &= ~1u;
+                    if (pb == kPermInvalid) hits &= ~2u;
+                    ea = (4 * c + 2 * q) | (int)(pa << kSlotBits);
+                    eb = (4 * c + 2 * q + 1) | (int)(pb << kSlotBits);
+                }
+                stage_hit(hits & 1u, ea);
+                stage_hit(hits & 2u, eb);
             };
 
             // Warps claim groups of kClaim clusters dynamically (no block barrier inside pass A); a warp stops
@@ -504,45 +546,24 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                     npend += __popc(b0) + __popc(b1);
                     if (lane == 0) { STAT(0, min(kClaim, cl_high - (cl_low + g * kClaim))); STAT(1, __popc(b0) + __popc(b1)); }
                     __syncwarp();
-                    while (npend >= 8) {
-                        npend -= 8;
-                        test_pending(npend, 8);
+                    while (npend >= kPendStep) {
+                        npend -= kPendStep;
+                        test_pending(npend, kPendStep);
                     }
                     __syncwarp();
                 }
                 if (npend > 0) test_pending(0, npend);
                 if (nstage > 0) {
-                    int slot = 0;
-                    if (lane == 0) slot = atomicAdd(&s_qcount, nstage);
-                    slot = __shfl_sync(0xffffffffu, slot, 0);
-                    if (lane < nstage) queue[slot + lane] = wstage[lane];
+                    __syncwarp();
+                    flush_stage(nstage);
                     nstage = 0;
                 }
                 __syncthreads();
                 const int qn = s_qcount;
                 const bool all_claimed = *(volatile int*)&s_next >= n_groups;
-                // pass B: every warp owns a contiguous slice of the queue.  First the level-3 test with in-place,
-                // warp-local compaction (writes land at or before the entries already read), then the exact
-                // rasterisation of the survivors, one triangle per thread; triangles covering many lattice pixels are
-                // deferred to the cooperative pass.
-                const int per_warp = (qn + kWarps - 1) / kWarps;
-                const int w0 = min((tid >> 5) * per_warp, qn), w1 = min(w0 + per_warp, qn);
-                int kept = 0;  // warp-uniform
-                for (int e0 = w0; e0 < w1; e0 += 32) {
-                    const int e = e0 + lane;
-                    int t = -1;
-                    bool keep = false;
-                    if (e < w1) {
-                        t = queue[e];
-                        keep = !pixel_outside(t);
-                    }
-                    const unsigned kb = __ballot_sync(0xffffffffu, keep);
-                    if (lane == 0) { STAT(3, __popc(kb)); STAT(9, 1); }
-                    if (keep) queue[w0 + kept + __popc(kb & lt_mask)] = t;
-                    kept += __popc(kb);
-                }
-                __syncwarp();
-                for (int e = w0 + lane; e < w0 + kept; e += 32) {
+                // pass B: exact rasterisation of the queued triangles, one per thread; triangles covering many lattice
+                // pixels are deferred to the cooperative pass.
+                for (int e = tid; e < qn; e += kThreads) {
                     int t = queue[e];
                     if (raster_tri(t, false, true)) {
                         int bslot = atomicAdd(&s_bigcount, 1);

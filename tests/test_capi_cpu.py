@@ -58,6 +58,40 @@ def test_topk_follows_caller_rule():
     assert nan["pose_id"][0, 0] == -1
 
 
+def test_mesh_preprocessing_keeps_every_triangle_bit_for_bit():
+    """perch_set_models re-files the triangle soup as quads (edge-sharing pairs) in clusters: every triangle must be
+    stored exactly once, with its coordinates and vertex ORDER intact (the exact path depends on the order), inside its
+    cluster's bounding sphere -- for closed meshes, soups without shared vertices, degenerate and non-finite input."""
+    lib = _capi.load_library()
+    rng = np.random.default_rng(3)
+    blob, box = synth.make_mesh(2000, seed=1000, r0=0.08), synth.make_box_mesh((0.05, 0.035, 0.06))
+    soup = synth.make_mesh(300, seed=7, r0=0.05).copy()
+    soup["v"] += rng.normal(0, 1e-6, soup["v"].shape).astype(np.float32)      # no two vertices identical any more
+    odd = synth.make_mesh(60, seed=9, r0=0.05).copy()
+    odd["v"][3, 1] = odd["v"][3, 0]                                            # zero-area triangle with a repeated vertex
+    odd["v"][7] = odd["v"][6]                                                  # exact duplicate triangle
+    odd["v"][11, 2, 0] = np.nan
+    odd["v"][12, 0, 1] = np.inf
+    for models in ([blob], [box], [soup], [odd], [blob, box, odd, soup], [blob[:1]], [blob, blob[:0], box]):
+        tris = np.ascontiguousarray(np.concatenate(models), dtype=TRIANGLE_DTYPE)
+        counts = np.array([len(m) for m in models], np.int32)
+        out = np.zeros(6, np.int64)
+        rc = lib.perch_cluster_stats(tris.ctypes.data_as(C.c_void_p), len(tris), counts.ctypes.data_as(C.c_void_p), len(counts),
+                                     out.ctypes.data_as(C.c_void_p))
+        assert rc == 0
+        n_cl, paired, single, mismatch, missing, outside = out.tolist()
+        assert paired + single == len(tris) and mismatch == 0 and missing == 0 and outside == 0, out
+        assert n_cl * 4 >= len(tris)
+    # a closed manifold mesh pairs almost completely, a soup not at all
+    out = np.zeros(6, np.int64)
+    t = np.ascontiguousarray(blob, dtype=TRIANGLE_DTYPE); c1 = np.array([len(t)], np.int32)
+    lib.perch_cluster_stats(t.ctypes.data_as(C.c_void_p), len(t), c1.ctypes.data_as(C.c_void_p), 1, out.ctypes.data_as(C.c_void_p))
+    assert out[1] >= 0.9 * len(t), out
+    t = np.ascontiguousarray(soup, dtype=TRIANGLE_DTYPE); c1 = np.array([len(t)], np.int32)
+    lib.perch_cluster_stats(t.ctypes.data_as(C.c_void_p), len(t), c1.ctypes.data_as(C.c_void_p), 1, out.ctypes.data_as(C.c_void_p))
+    assert out[1] == 0 and out[2] == len(t), out
+
+
 @pytest.mark.skipif(has_gpu(), reason="checks the no-GPU behaviour")
 def test_create_fails_loudly_without_gpu():
     lib = _capi.load_library()
