@@ -671,10 +671,10 @@ int perch_cluster_stats(const perch_triangle* tris, int64_t n_tris, const int* t
             ++seen[t];
             const uint32_t other = (cs.perm[c] >> (6 * (j ^ 1))) & 63u;
             (other == perch::kPermInvalid ? single : paired) += 1;
-            const float* rec = &cs.recs[c * perch::kClusterFloats + (j >> 1)];
+            const float* rec = &cs.recs[c * perch::kClusterFloats + (j >> 1) * perch::kQuadFloats];
             for (int k = 0; k < 3; ++k)
                 for (int a = 0; a < 3; ++a) {
-                    const float got = rec[(((perm >> (2 * k)) & 3u) * 3 + a) * perch::kClusterQuads];
+                    const float got = rec[((perm >> (2 * k)) & 3u) * 3 + a];
                     if (memcmp(&got, &tri9[(size_t)t * 9 + 3 * k + a], 4) != 0) ++mismatch;
                 }
             // every vertex must lie inside the cluster's bounding sphere

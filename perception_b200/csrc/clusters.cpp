@@ -253,7 +253,7 @@ ClusterSet build_clusters(const float* tri9, const std::vector<int>& low, const 
                     if (!used[uorder[oj]]) { second = uorder[oj]; break; }
             }
             if (second >= 0) used[second] = 1;
-            // ---- record: 12 coordinate planes x 2 quads; a cluster without a second quad repeats the first, invalid
+            // ---- record: 2 quads x 12 coordinates; a cluster without a second quad repeats the first, invalid
             const Unit& qa = units[seed];
             const Unit& qb = units[second >= 0 ? second : seed];
             const size_t rec = out.recs.size();
@@ -266,7 +266,7 @@ ClusterSet build_clusters(const float* tri9, const std::vector<int>& low, const 
                 for (int i = 0; i < kQuadVerts; ++i)
                     for (int a = 0; a < 3; ++a) {
                         const float p = u.v[i][a];
-                        out.recs[rec + (size_t)(3 * i + a) * kClusterQuads + q] = p;
+                        out.recs[rec + (size_t)q * kQuadFloats + 3 * i + a] = p;
                         if (!std::isfinite(p)) finite = false;
                         pts[q * kQuadVerts + i][a] = p;
                     }

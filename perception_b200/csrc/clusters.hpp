@@ -20,13 +20,14 @@ namespace perch {
 constexpr int kClusterTris = 4;                      // triangle slots per cluster: slot j belongs to quad j >> 1
 constexpr int kQuadVerts = 4;
 constexpr int kClusterQuads = kClusterTris / 2;
-constexpr int kClusterFloats = 3 * kQuadVerts * kClusterQuads;  // record: 12 coordinate planes x 2 quads
+constexpr int kQuadFloats = 3 * kQuadVerts;                      // one quad: v0.xyz v1.xyz v2.xyz v3.xyz = three float4
+constexpr int kClusterFloats = kQuadFloats * kClusterQuads;      // record: 2 quads, 96 bytes
 constexpr uint32_t kPermInvalid = 63;                // slot that repeats its quad's other triangle (never a candidate)
 
 struct ClusterSet {
-    // n_clusters x kClusterFloats: rec[c][3 * i + a][q] = coordinate a of vertex i of quad q.  Vertices 0 and 1 are the
-    // shared edge, vertex 2 belongs to the quad's first triangle only, vertex 3 to the second only; a quad holding a
-    // single triangle has vertex 3 = vertex 2.
+    // n_clusters x kClusterFloats: rec[c][q][3 * i + a] = coordinate a of vertex i of quad q (a quad is read with three
+    // 16-byte loads).  Vertices 0 and 1 are the shared edge, vertex 2 belongs to the quad's first triangle only, vertex 3
+    // to the second only; a quad holding a single triangle has vertex 3 = vertex 2.
     std::vector<float> recs;
     std::vector<float> bounds;   // n_clusters x 4: centre xyz, radius (inf when a coordinate is not finite)
     std::vector<int> orig;       // n_clusters x kClusterTris: original (global) triangle index of every slot

@@ -40,7 +40,7 @@ struct ModelsDev {
     const int* model_high = nullptr;  // inclusive scan
     const float* model_aabb = nullptr;  // 6 floats per model: min xyz, max xyz (object-space)
     // clusters (clusters.hpp): Morton-ordered groups of kClusterTris triangles with a bounding sphere
-    const float* cl_recs = nullptr;     // n_clusters x 24: rec[c][3 * i + a][q] = coordinate a of vertex i of quad q
+    const float* cl_recs = nullptr;     // n_clusters x 24: rec[c][q][3 * i + a] = coordinate a of vertex i of quad q
     const uint32_t* cl_perm = nullptr;  // n_clusters: 6 bits per triangle slot, its three quad vertices in original order
     const float4* cl_bounds = nullptr;  // centre xyz, radius
     const int* cl_orig = nullptr;       // n_clusters x 4: original triangle index (colour tie-break, colour lookup)

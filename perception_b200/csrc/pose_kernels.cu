@@ -122,14 +122,16 @@ constexpr int kSlotMask = (1 << kSlotBits) - 1;
 __device__ __forceinline__ void load_tri(const ModelsDev& m, int entry, float v[9]) {
     const int t = entry & kSlotMask;
     const uint32_t perm = (uint32_t)entry >> kSlotBits;
-    const int c = t >> 2, j = t & 3;
-    const float* rec = m.cl_recs + (int64_t)c * kClusterFloats + (j >> 1);
+    // the whole quad with three 16-byte loads, then the triangle's three vertices by selects (no dependent address)
+    const float4* rec = reinterpret_cast<const float4*>(m.cl_recs + (int64_t)(t >> 1) * kQuadFloats);
+    const float4 r0 = __ldg(rec), r1 = __ldg(rec + 1), r2 = __ldg(rec + 2);
+    const float qx[4] = {r0.x, r0.w, r1.z, r2.y}, qy[4] = {r0.y, r1.x, r1.w, r2.z}, qz[4] = {r0.z, r1.y, r2.x, r2.w};
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
-        const float* p = rec + ((perm >> (2 * k)) & 3u) * (3 * kClusterQuads);
-        v[3 * k] = __ldg(p);
-        v[3 * k + 1] = __ldg(p + kClusterQuads);
-        v[3 * k + 2] = __ldg(p + 2 * kClusterQuads);
+        const uint32_t i = (perm >> (2 * k)) & 3u;
+        v[3 * k] = i == 0 ? qx[0] : i == 1 ? qx[1] : i == 2 ? qx[2] : qx[3];
+        v[3 * k + 1] = i == 0 ? qy[0] : i == 1 ? qy[1] : i == 2 ? qy[2] : qy[3];
+        v[3 * k + 2] = i == 0 ? qz[0] : i == 1 ? qz[1] : i == 2 ? qz[2] : qz[3];
     }
 }
 
@@ -412,12 +414,13 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
             // second triangle is a candidate.  NaN/inf/absurd coordinates (whose handling by the reference's select
             // chain is order dependent) go to the exact path, which re-derives everything.
             auto quad_hits = [&](int c, int q) -> unsigned {
-                const float* rec = a.models.cl_recs + (int64_t)c * kClusterFloats + q;
+                const float4* rec = reinterpret_cast<const float4*>(a.models.cl_recs + (int64_t)(2 * c + q) * kQuadFloats);
+                const float4 r0 = __ldg(rec), r1 = __ldg(rec + 1), r2 = __ldg(rec + 2);
+                const float qx[4] = {r0.x, r0.w, r1.z, r2.y}, qy[4] = {r0.y, r1.x, r1.w, r2.z}, qz[4] = {r0.z, r1.y, r2.x, r2.w};
                 float ux[4], uy[4], izmax = 0.f;
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
-                    const float x = __ldg(rec + (3 * k) * kClusterQuads), y = __ldg(rec + (3 * k + 1) * kClusterQuads),
-                                z = __ldg(rec + (3 * k + 2) * kClusterQuads);
+                    const float x = qx[k], y = qy[k], z = qz[k];
                     const float n0 = fmaf(z, U2, fmaf(y, U1, fmaf(x, U0, U3)));
                     const float n1 = fmaf(z, V2, fmaf(y, V1, fmaf(x, V0, V3)));
                     const float iz = __frcp_approx(fmaf(z, C2, fmaf(y, C1, fmaf(x, C0, C3))));
