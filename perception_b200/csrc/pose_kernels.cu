@@ -190,13 +190,24 @@ __device__ __forceinline__ void nn_query(const ObsGridDev& g, float qx, float qy
     int cx = (int)fx, cy = (int)fy, cz = (int)fz;
     int x0 = max(cx - 1, 0), x1 = min(cx + 1, g.dx - 1);
     if (x0 > x1) return;
+    const int y0 = max(cy - 1, 0), y1 = min(cy + 1, g.dy - 1);
     for (int z = max(cz - 1, 0); z <= min(cz + 1, g.dz - 1); ++z) {
-        for (int y = max(cy - 1, 0); y <= min(cy + 1, g.dy - 1); ++y) {
-            int row = (z * g.dy + y) * g.dx;
-            uint32_t b = __ldg(g.cell_start + row + x0), e = __ldg(g.cell_start + row + x1 + 1);
-            for (uint32_t j = b; j < e; ++j) {
-                if (use_label && __ldg(g.label + j) != label) continue;
-                float4 p = __ldg(g.pts + j);
+        // the (up to) three x-runs of this z-slice: all six range bounds are requested before any point is read
+        uint32_t rb[3], re[3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const int y = y0 + k;
+            const int row = (z * g.dy + min(y, y1)) * g.dx;
+            rb[k] = __ldg(g.cell_start + row + x0);
+            re[k] = (y <= y1) ? __ldg(g.cell_start + row + x1 + 1) : rb[k];
+        }
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            for (uint32_t j = rb[k]; j < re[k]; ++j) {
+                // label and point are requested together (the label test does not gate the point's load)
+                const int pl = use_label ? __ldg(g.label + j) : label;
+                const float4 p = __ldg(g.pts + j);
+                if (pl != label) continue;
                 float d = sqdist3(qx, qy, qz, p.x, p.y, p.z);
                 int ref = __float_as_int(p.w);
                 if (d < best || (d == best && ref < best_ref)) {
