@@ -31,7 +31,10 @@ namespace {
 #endif
 constexpr int kThreads = PERCH_POSE_THREADS;
 constexpr int kWarps = kThreads / 32;
-constexpr int kMinCtas = 1024 / kThreads;  // resident CTAs per SM the register budget is sized for (32 warps)
+#ifndef PERCH_POSE_MIN_CTAS
+#define PERCH_POSE_MIN_CTAS (1024 / PERCH_POSE_THREADS)
+#endif
+constexpr int kMinCtas = PERCH_POSE_MIN_CTAS;  // resident CTAs per SM the register budget is sized for (32 warps)
 constexpr int kQueueCap = 16 * kThreads;   // candidate triangles buffered between exact passes
 constexpr int kClaim = 64;        // clusters tested per warp claim (two per lane: independent loads in flight)
 constexpr int kPendStep = 16;     // surviving clusters tested per warp step (two lanes each: one per quad)
