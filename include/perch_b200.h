@@ -186,10 +186,19 @@ int perch_icp_set_scene(perch_ctx* ctx, const int32_t* scene_depth, int width, i
  * cloud_offsets[i+1]).  Per cloud: RegistrationResult (icp.h:27-38) = transformation_ (row-major 4x4 into
  * out_transforms16), fitness_, inlier_rmse_; criteria = ICPConvergenceCriteria (icp.h:40-51; reference defaults 1e-5,
  * 1e-5, 30).  out_pcd (may be NULL) receives the clouds as the reference leaves model_pcd: transformed in place.
- * Scene_nn (kd-tree association, pcd_scene.h) is not provided: nearest-neighbour registration is perch_gicp. */
+ * Scene_nn (kd-tree association, pcd_scene.h) is perch_icp_point2plane_nn below. */
 int perch_icp_point2plane(perch_ctx* ctx, const float* model_pcd, const int* cloud_offsets, int n_clouds,
                           float relative_fitness, float relative_rmse, int max_iteration, float* out_transforms16,
                           float* out_fitness, float* out_inlier_rmse, int* out_iterations, float* out_pcd);
+
+/* Replaces cuda_icp::ICP_Point2Plane_cuda<Scene_nn> (icp.h:92-99; Scene_nn::query, pcd_scene.h:60-136): the same loop with
+ * every model point associated to its NEAREST scene point (the reference walks a kd-tree built on the host,
+ * pcd_scene.cpp:40-182; here an exact grid search over the scene set by perch_icp_set_scene), accepted iff the squared
+ * distance is below max_dist_diff^2 (reference: 0.01 m, pcd_scene.h:48).  Arguments as perch_icp_point2plane. */
+int perch_icp_point2plane_nn(perch_ctx* ctx, const float* model_pcd, const int* cloud_offsets, int n_clouds,
+                             float max_dist_diff, float relative_fitness, float relative_rmse, int max_iteration,
+                             float* out_transforms16, float* out_fitness, float* out_inlier_rmse, int* out_iterations,
+                             float* out_pcd);
 
 /* ---- k nearest neighbours (package API of cuda_renderer/knncuda.h) ------------------------------------------ */
 /* Replaces knn_cuda_global / knn_cuda_texture / knn_cublas (knncuda.h:33-100, knncuda.cu:276-421, 424-616, 618-838):

@@ -815,26 +815,51 @@ void oracle_icp_scene(const int32_t* depth, int W, int H, const float* K9, float
  * Sums are accumulated serially in float (the reference's order is unspecified: OpenMP / cub reduction), so agreement
  * with the reference is to float-accumulation accuracy, not bit for bit.  Returns the index of the last turn.
  */
-int oracle_icp_point2plane(float* pts, int n, const float* scene_pcd, const float* scene_normals, int W, int H,
-                           const float* K9, float max_dist_diff, float relative_fitness, float relative_rmse,
-                           int max_iteration, float* out_T16, float* out_fitness, float* out_rmse) {
+/* nn = 0: Scene_projective::query (depth_scene.h:29-50).  nn = 1: Scene_nn::query (pcd_scene.h:60-136) restated as what
+ * its kd-tree walk computes -- the nearest scene point (every pixel with a depth, pcd_scene.cpp:24-33), by brute force,
+ * accepted iff its squared distance is below max_dist_diff^2; equal distances go to the lowest pixel index. */
+static int icp_loop(int nn, float* pts, int n, const float* scene_pcd, const float* scene_normals, int W, int H,
+                    const float* K9, float max_dist_diff, float relative_fitness, float relative_rmse,
+                    int max_iteration, float* out_T16, float* out_fitness, float* out_rmse) {
     const float k00 = K9[0], k02 = K9[2], k11 = K9[4], k12 = K9[5];
+    long* assoc = nn ? (long*)malloc(sizeof(long) * (size_t)(n > 0 ? n : 1)) : NULL;
     float T[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
     float fit = 0, rmse = 0;
     int last = 0;
     for (int iter = 0; iter <= max_iteration && n > 0; ++iter) {
         float sum[29];
         memset(sum, 0, sizeof sum);
+        if (nn) {
+#pragma omp parallel for schedule(static)
+            for (int i = 0; i < n; ++i) {
+                const float sx = pts[3 * i], sy = pts[3 * i + 1], sz = pts[3 * i + 2];
+                float best = FLT_MAX;
+                long bi = -1;
+                for (long j = 0; j < (long)W * H; ++j) {
+                    if (!(scene_pcd[3 * j + 2] > 0)) continue;
+                    const float ex = sx - scene_pcd[3 * j], ey = sy - scene_pcd[3 * j + 1], ez = sz - scene_pcd[3 * j + 2];
+                    const float d = fmaf(ez, ez, fmaf(ey, ey, ex * ex));
+                    if (d < best) { best = d; bi = j; }
+                }
+                assoc[i] = (bi >= 0 && best < max_dist_diff * max_dist_diff) ? bi : -1;
+            }
+        }
         for (int i = 0; i < n; ++i) {
             const float sx = pts[3 * i], sy = pts[3 * i + 1], sz = pts[3 * i + 2];
-            /* device arithmetic of the path being replaced (nvcc -fmad contracts x/z*K + c): fma, then + 0.5 */
-            const float fu = fmaf(sx / sz, k00, k02) + 0.5f, fv = fmaf(sy / sz, k11, k12) + 0.5f;
-            if (!(fu > -2147483648.0f && fu < 2147483648.0f && fv > -2147483648.0f && fv < 2147483648.0f)) continue;
-            const int u = (int)fu, v = (int)fv;
-            if (u >= W || v >= H || u < 0 || v < 0) continue;
-            const size_t idx = (size_t)u + (size_t)v * W;
+            size_t idx;
+            if (nn) {
+                if (assoc[i] < 0) continue;
+                idx = (size_t)assoc[i];
+            } else {
+                /* device arithmetic of the path being replaced (nvcc -fmad contracts x/z*K + c): fma, then + 0.5 */
+                const float fu = fmaf(sx / sz, k00, k02) + 0.5f, fv = fmaf(sy / sz, k11, k12) + 0.5f;
+                if (!(fu > -2147483648.0f && fu < 2147483648.0f && fv > -2147483648.0f && fv < 2147483648.0f)) continue;
+                const int u = (int)fu, v = (int)fv;
+                if (u >= W || v >= H || u < 0 || v < 0) continue;
+                idx = (size_t)u + (size_t)v * W;
+            }
             const float dx = scene_pcd[3 * idx], dy = scene_pcd[3 * idx + 1], dz = scene_pcd[3 * idx + 2];
-            if (dz <= 0 || fabsf(sz - dz) > max_dist_diff) continue;
+            if (!nn && (dz <= 0 || fabsf(sz - dz) > max_dist_diff)) continue;
             const float nx = scene_normals[3 * idx], ny = scene_normals[3 * idx + 1], nz = scene_normals[3 * idx + 2];
             const float bt = (dx - sx) * nx + (dy - sy) * ny + (dz - sz) * nz;
             const float A[6] = {nz * sy - ny * sz, nx * sz - nz * sx, ny * sx - nx * sy, nx, ny, nz};
@@ -884,5 +909,20 @@ int oracle_icp_point2plane(float* pts, int n, const float* scene_pcd, const floa
     memcpy(out_T16, T, sizeof T);
     *out_fitness = fit;
     *out_rmse = rmse;
+    free(assoc);
     return last;
+}
+
+int oracle_icp_point2plane(float* pts, int n, const float* scene_pcd, const float* scene_normals, int W, int H,
+                           const float* K9, float max_dist_diff, float relative_fitness, float relative_rmse,
+                           int max_iteration, float* out_T16, float* out_fitness, float* out_rmse) {
+    return icp_loop(0, pts, n, scene_pcd, scene_normals, W, H, K9, max_dist_diff, relative_fitness, relative_rmse,
+                    max_iteration, out_T16, out_fitness, out_rmse);
+}
+
+int oracle_icp_point2plane_nn(float* pts, int n, const float* scene_pcd, const float* scene_normals, int W, int H,
+                              const float* K9, float max_dist_diff, float relative_fitness, float relative_rmse,
+                              int max_iteration, float* out_T16, float* out_fitness, float* out_rmse) {
+    return icp_loop(1, pts, n, scene_pcd, scene_normals, W, H, K9, max_dist_diff, relative_fitness, relative_rmse,
+                    max_iteration, out_T16, out_fitness, out_rmse);
 }

@@ -3,6 +3,8 @@
 //   cuda_icp/scene/common.cu             device_vector_holder
 //   cuda_icp/scene/common.cpp            get_normal (host)
 //   cuda_icp/scene/depth_scene/depth_scene.cpp   Scene_projective::init_Scene_projective_cpu (host)
+//   cuda_icp/scene/pcd_scene/pcd_scene.cpp, .cu  Scene_nn: scene cloud, KDTree_cpu::build_tree, upload (Scene_nn::query is in
+//                                        pcd_scene.h and runs inside ICP_Point2Plane_cuda<Scene_nn>)
 // behind extern "C" trampolines.  ONE substitution: cuda_icp::eigen_slover_666 (icp.cpp:29-36) needs Eigen's LDLT and
 // AngleAxis, which are not installed here; it is restated below (LDL^T in double, R = Rz Ry Rx, icp.cpp:7-17).
 // cuda_icp/icp.cpp itself (the CPU loop) cannot be built for the same reason.
@@ -11,6 +13,7 @@
 #include <vector>
 
 #include "cuda_icp/icp.h"
+#include "cuda_icp/pcd_scene.h"
 
 namespace cuda_icp {
 Mat4x4f eigen_slover_666(float* A, float* b) {
@@ -71,6 +74,30 @@ int ref_icp_point2plane(float* model_pcd /* n x 3, transformed in place */, int 
     for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) scene.K[i][j] = K9[i * 3 + j];
     scene.pcd_ptr = spcd.data();
     scene.normal_ptr = snrm.data();
+    cuda_icp::RegistrationResult r = cuda_icp::ICP_Point2Plane_cuda(model, scene,
+        cuda_icp::ICPConvergenceCriteria(relative_fitness, relative_rmse, max_iteration));
+    cudaDeviceSynchronize();
+    cudaMemcpy(model_pcd, model.data(), (size_t)n * 12, cudaMemcpyDeviceToHost);
+    for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) out_T16[i * 4 + j] = r.transformation_[i][j];
+    *out_fitness = r.fitness_;
+    *out_rmse = r.inlier_rmse_;
+    return cudaGetLastError() == cudaSuccess ? 0 : 1;
+}
+
+// reference ICP loop with kd-tree association (Scene_nn, pcd_scene.h:47-136): the scene cloud, its normals and the tree
+// are built by the reference's own init_Scene_nn_cuda from the depth image
+int ref_icp_nn_point2plane(float* model_pcd /* n x 3, transformed in place */, int n, const int32_t* depth, int width,
+                           int height, const float* K9, float relative_fitness, float relative_rmse, int max_iteration,
+                           float* out_T16, float* out_fitness, float* out_rmse) {
+    cv::Mat m;
+    m.rows = height; m.cols = width; m.t = CV_32S; m.p = (float*)const_cast<int32_t*>(depth);
+    Mat3x3f K;
+    for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) K[i][j] = K9[i * 3 + j];
+    KDTree_cuda tree;
+    Scene_nn scene;
+    scene.init_Scene_nn_cuda(m, K, tree);
+    device_vector_holder<Vec3f> model((size_t)n);
+    cudaMemcpy(model.data(), model_pcd, (size_t)n * 12, cudaMemcpyHostToDevice);
     cuda_icp::RegistrationResult r = cuda_icp::ICP_Point2Plane_cuda(model, scene,
         cuda_icp::ICPConvergenceCriteria(relative_fitness, relative_rmse, max_iteration));
     cudaDeviceSynchronize();

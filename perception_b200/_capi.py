@@ -133,6 +133,7 @@ SIGNATURES = {
     "perch_gicp": (C.c_int, [_P, _V, C.c_int, _V, _V, C.POINTER(perch_params), _V, _V, _V, _V]),
     "perch_icp_set_scene": (C.c_int, [_P, _V, C.c_int, C.c_int, _V, C.c_float, _V, _V]),
     "perch_icp_point2plane": (C.c_int, [_P, _V, _V, C.c_int, C.c_float, C.c_float, C.c_int, _V, _V, _V, _V, _V]),
+    "perch_icp_point2plane_nn": (C.c_int, [_P, _V, _V, C.c_int, C.c_float, C.c_float, C.c_float, C.c_int, _V, _V, _V, _V, _V]),
     "perch_knn": (C.c_int, [_P, _V, C.c_int, _V, C.c_int, C.c_int, C.c_int, _V, _V]),
     "perch_compute_proj": (C.c_int, [_P, C.c_int, C.c_int, C.c_float, C.c_float, _P]),
     "perch_set_camera": (C.c_int, [_P, C.c_int, C.c_int, _P, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float]),

@@ -101,12 +101,12 @@ int env_int(const char* name, int dflt) {
 }
 
 // ---- observed-cloud grid ------------------------------------------------------------------------------------
-// Uniform grid over the observed cloud with cells at least `h` wide (widened until it has at most max_cells cells):
-// points sorted by cell, x fastest, ascending reference index inside a cell.  *avg_per_cell = points per non-empty cell.
-int build_point_grid(perch_ctx* c, float h, double max_cells, float4** d_pts, int** d_label, uint32_t** d_cell_start,
-                     perch::ObsGridDev* out, double* avg_per_cell) {
+// Uniform grid over a host cloud (xyz: n x 3; ids: the reference index stored with point i, or null for i itself, must
+// ascend; labels: per point or null) with cells at least `h` wide (widened until it has at most max_cells cells): points
+// sorted by cell, x fastest, ascending reference index inside a cell.  *avg_per_cell = points per non-empty cell.
+int build_point_grid_from(perch_ctx* c, const float* xyz, int n, const int* ids, const int* labels, float h, double max_cells,
+                          float4** d_pts, int** d_label, uint32_t** d_cell_start, perch::ObsGridDev* out, double* avg_per_cell) {
     using namespace perch;
-    const int n = c->n_obs;
     cudaFree(*d_pts); *d_pts = nullptr;
     cudaFree(*d_label); *d_label = nullptr;
     cudaFree(*d_cell_start); *d_cell_start = nullptr;
@@ -117,8 +117,8 @@ int build_point_grid(perch_ctx* c, float h, double max_cells, float4** d_pts, in
     float mn[3] = {INFINITY, INFINITY, INFINITY}, mx[3] = {-INFINITY, -INFINITY, -INFINITY};
     for (int i = 0; i < n; ++i)
         for (int k = 0; k < 3; ++k) {
-            float v = c->h_obs_xyz[3 * (size_t)i + k];
-            if (!std::isfinite(v)) return fail(PERCH_ERR_INVALID, "observed cloud contains a non-finite coordinate");
+            float v = xyz[3 * (size_t)i + k];
+            if (!std::isfinite(v)) return fail(PERCH_ERR_INVALID, "cloud contains a non-finite coordinate");
             mn[k] = std::min(mn[k], v);
             mx[k] = std::max(mx[k], v);
         }
@@ -140,7 +140,7 @@ int build_point_grid(perch_ctx* c, float h, double max_cells, float4** d_pts, in
     for (int i = 0; i < n; ++i) {
         int cc[3];
         for (int k = 0; k < 3; ++k) {
-            float d = c->h_obs_xyz[3 * (size_t)i + k] - org[k];
+            float d = xyz[3 * (size_t)i + k] - org[k];
             float f = std::floor(d * inv_h);
             cc[k] = std::min(std::max((int)f, 0), dim[k] - 1);
         }
@@ -155,21 +155,21 @@ int build_point_grid(perch_ctx* c, float h, double max_cells, float4** d_pts, in
     if (avg_per_cell) *avg_per_cell = (double)n / (double)std::max<size_t>(nonempty, 1);
     std::vector<uint32_t> cursor(start.begin(), start.end() - 1);
     std::vector<float4> pts(n);
-    std::vector<int> lab(c->obs_has_label ? n : 0);
+    std::vector<int> lab(labels ? n : 0);
     for (int i = 0; i < n; ++i) {  // ascending i => ascending reference index inside every cell
         uint32_t slot = cursor[cell_of[i]]++;
         float4 p;
-        p.x = c->h_obs_xyz[3 * (size_t)i];
-        p.y = c->h_obs_xyz[3 * (size_t)i + 1];
-        p.z = c->h_obs_xyz[3 * (size_t)i + 2];
-        int ref = i;
+        p.x = xyz[3 * (size_t)i];
+        p.y = xyz[3 * (size_t)i + 1];
+        p.z = xyz[3 * (size_t)i + 2];
+        int ref = ids ? ids[i] : i;
         memcpy(&p.w, &ref, 4);
         pts[slot] = p;
-        if (c->obs_has_label) lab[slot] = c->h_obs_label[i];
+        if (labels) lab[slot] = labels[i];
     }
     CU(cudaMalloc(d_pts, n * sizeof(float4)));
     CU(cudaMemcpyAsync(*d_pts, pts.data(), n * sizeof(float4), cudaMemcpyHostToDevice, c->stream));
-    if (c->obs_has_label) {
+    if (labels) {
         CU(cudaMalloc(d_label, n * sizeof(int)));
         CU(cudaMemcpyAsync(*d_label, lab.data(), n * sizeof(int), cudaMemcpyHostToDevice, c->stream));
     }
@@ -183,6 +183,12 @@ int build_point_grid(perch_ctx* c, float h, double max_cells, float4** d_pts, in
     out->inv_h = inv_h;
     out->dx = dim[0]; out->dy = dim[1]; out->dz = dim[2];
     return PERCH_OK;
+}
+
+int build_point_grid(perch_ctx* c, float h, double max_cells, float4** d_pts, int** d_label, uint32_t** d_cell_start,
+                     perch::ObsGridDev* out, double* avg_per_cell) {
+    return build_point_grid_from(c, c->h_obs_xyz.data(), c->n_obs, nullptr, c->obs_has_label ? c->h_obs_label.data() : nullptr, h,
+                                 max_cells, d_pts, d_label, d_cell_start, out, avg_per_cell);
 }
 
 // The grid of the cost stage: cells just wider than sensor_resolution, so that the 27 cells around a query hold every
@@ -488,7 +494,7 @@ void perch_destroy(perch_ctx* c) {
     void* ptrs[] = {c->d_tri_color, c->d_model_low, c->d_model_high, c->d_model_aabb, c->d_tri_lab, c->d_cl_recs, c->d_cl_bounds,
                     c->d_cl_orig, c->d_cl_perm, c->d_cl_low, c->d_cl_high,
                     c->d_src_depth, c->d_src_label, c->d_src_rgb, c->d_grid_pts, c->d_grid_label, c->d_cell_start,
-                    c->d_cmp_depth, c->d_cmp_label, c->d_ggrid_pts, c->d_ggrid_label, c->d_ggrid_cell_start,
+                    c->d_icp_grid_pts, c->d_icp_grid_label, c->d_icp_grid_cells, c->d_cmp_depth, c->d_cmp_label, c->d_ggrid_pts, c->d_ggrid_label, c->d_ggrid_cell_start,
                     c->d_obs_lab, c->d_obs_rgb, c->d_scratch, c->d_err_flag, c->d_flush, c->d_obs_xyz_aos,
                     c->d_tgt_normals, c->d_obs_xyz4, c->d_label_range, c->d_gicp, c->d_icp_pcd, c->d_icp_normals};
     for (void* p : ptrs)
@@ -1003,13 +1009,42 @@ int perch_icp_set_scene(perch_ctx* c, const int32_t* scene_depth, int width, int
     c->icp_w = width; c->icp_h = height;
     memcpy(c->icp_K, K9, sizeof c->icp_K);
     c->icp_max_dist = max_dist_diff;
+    c->icp_grid_dist = -1.f;
     note_memory(c);
     return PERCH_OK;
 }
 
-int perch_icp_point2plane(perch_ctx* c, const float* model_pcd, const int* cloud_offsets, int n_clouds,
-                          float relative_fitness, float relative_rmse, int max_iteration, float* out_transforms16,
-                          float* out_fitness, float* out_inlier_rmse, int* out_iterations, float* out_pcd) {
+namespace {
+// Scene_nn's cloud (Scene_nn::init_Scene_nn_cpu, pcd_scene.cpp:4-38): every pixel with a depth, row-major; here the
+// pixel index doubles as the point's reference index into the per-pixel pcd / normal buffers.
+int prepare_icp_nn_grid(perch_ctx* c, float max_dist) {
+    if (c->icp_grid_dist == max_dist) return PERCH_OK;
+    const size_t npx = (size_t)c->icp_w * c->icp_h;
+    std::vector<float> pcd(3 * npx);
+    CU(cudaMemcpyAsync(pcd.data(), c->d_icp_pcd, 3 * npx * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    std::vector<float> xyz;
+    std::vector<int> ids;
+    xyz.reserve(3 * npx);
+    ids.reserve(npx);
+    for (size_t i = 0; i < npx; ++i)
+        if (pcd[3 * i + 2] > 0.f) {
+            xyz.insert(xyz.end(), {pcd[3 * i], pcd[3 * i + 1], pcd[3 * i + 2]});
+            ids.push_back((int)i);
+        }
+    const int n = (int)ids.size();
+    int rc = build_point_grid_from(c, xyz.data(), n, ids.data(), nullptr, std::max(max_dist, 1e-4f) * 1.001f, 64.0 * 1024 * 1024,
+                                   &c->d_icp_grid_pts, &c->d_icp_grid_label, &c->d_icp_grid_cells, &c->icp_grid, nullptr);
+    if (rc) return rc;
+    c->icp_grid_dist = max_dist;
+    return PERCH_OK;
+}
+}  // namespace
+
+namespace {
+int icp_point2plane_impl(perch_ctx* c, bool nn, float nn_max_dist, const float* model_pcd, const int* cloud_offsets, int n_clouds,
+                         float relative_fitness, float relative_rmse, int max_iteration, float* out_transforms16,
+                         float* out_fitness, float* out_inlier_rmse, int* out_iterations, float* out_pcd) {
     if (!c) return fail(PERCH_ERR_INVALID, "null context");
     if (c->icp_w == 0) return fail(PERCH_ERR_INVALID, "perch_icp_set_scene has not been called");
     if (n_clouds < 0 || (n_clouds > 0 && (!cloud_offsets || !out_transforms16 || !out_fitness || !out_inlier_rmse)) || max_iteration < 0)
@@ -1038,6 +1073,13 @@ int perch_icp_point2plane(perch_ctx* c, const float* model_pcd, const int* cloud
     a.width = c->icp_w; a.height = c->icp_h;
     a.k00 = c->icp_K[0]; a.k02 = c->icp_K[2]; a.k11 = c->icp_K[4]; a.k12 = c->icp_K[5];
     a.max_dist_diff = c->icp_max_dist;
+    if (nn) {
+        if (!(nn_max_dist > 0.f)) return fail(PERCH_ERR_INVALID, "max_dist_diff must be positive");
+        if ((rc = prepare_icp_nn_grid(c, nn_max_dist))) return rc;
+        a.nn = 1;
+        a.nn_grid = c->icp_grid;
+        a.max_dist_diff = nn_max_dist;
+    }
     a.relative_fitness = relative_fitness; a.relative_rmse = relative_rmse; a.max_iteration = max_iteration;
     CU(cudaEventRecord(c->ev0, c->stream));
     CU(perch::launch_icp_point2plane(a, n_clouds, c->stream));
@@ -1053,6 +1095,21 @@ int perch_icp_point2plane(perch_ctx* c, const float* model_pcd, const int* cloud
     c->timing_pending = false;
     note_memory(c);
     return PERCH_OK;
+}
+}  // namespace
+
+int perch_icp_point2plane(perch_ctx* c, const float* model_pcd, const int* cloud_offsets, int n_clouds,
+                          float relative_fitness, float relative_rmse, int max_iteration, float* out_transforms16,
+                          float* out_fitness, float* out_inlier_rmse, int* out_iterations, float* out_pcd) {
+    return icp_point2plane_impl(c, false, 0.f, model_pcd, cloud_offsets, n_clouds, relative_fitness, relative_rmse, max_iteration,
+                                out_transforms16, out_fitness, out_inlier_rmse, out_iterations, out_pcd);
+}
+
+int perch_icp_point2plane_nn(perch_ctx* c, const float* model_pcd, const int* cloud_offsets, int n_clouds, float max_dist_diff,
+                             float relative_fitness, float relative_rmse, int max_iteration, float* out_transforms16,
+                             float* out_fitness, float* out_inlier_rmse, int* out_iterations, float* out_pcd) {
+    return icp_point2plane_impl(c, true, max_dist_diff, model_pcd, cloud_offsets, n_clouds, relative_fitness, relative_rmse,
+                                max_iteration, out_transforms16, out_fitness, out_inlier_rmse, out_iterations, out_pcd);
 }
 
 int perch_knn(perch_ctx* c, const float* ref, int ref_nb, const float* query, int query_nb, int dim, int k,

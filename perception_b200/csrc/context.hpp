@@ -147,6 +147,12 @@ struct perch_ctx {
     int icp_w = 0, icp_h = 0;
     float icp_K[9] = {0};
     float icp_max_dist = 0.1f;
+    // Scene_nn association: grid over the valid scene points, built on first use for a given max_dist_diff
+    float4* d_icp_grid_pts = nullptr;
+    int* d_icp_grid_label = nullptr;   // unused (the builder's slot)
+    uint32_t* d_icp_grid_cells = nullptr;
+    perch::ObsGridDev icp_grid;
+    float icp_grid_dist = -1.f;        // max_dist_diff the grid was built for (< 0: stale)
     // caller glue (capi_states.cu): environment, model metadata, search clouds, assembled / generated state lists
     perch::StatesCtx* states = nullptr;
     int obs_version = 0;               // bumped by perch_set_observed (per-label point counts are cached against it)

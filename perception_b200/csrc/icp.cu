@@ -10,6 +10,7 @@
 // the reference's cub reduction order is unspecified; results agree within the last bits of float accumulation.
 #include <cuda_runtime.h>
 
+#include <cfloat>
 #include <cstdint>
 
 #include "kernels.cuh"
@@ -100,6 +101,33 @@ __device__ inline bool ldlt_solve6(const double* A, const double* b, double* x) 
     return true;
 }
 
+// Scene_nn::query (pcd_scene.h:60-136): the nearest scene point, accepted iff its squared distance is below
+// max_dist_diff^2.  The reference walks a kd-tree; any exact search gives the same point (equal distances aside: the
+// lowest pixel index wins here, the tree's visiting order there), and a point closer than max_dist_diff lies in the 27
+// cells around the query because cells are wider than that.
+__device__ __forceinline__ bool nn_associate(const ObsGridDev& g, float max_d2, float qx, float qy, float qz, int& idx) {
+    const float fx = floorf((qx - g.ox) * g.inv_h), fy = floorf((qy - g.oy) * g.inv_h), fz = floorf((qz - g.oz) * g.inv_h);
+    if (!(fx >= -1.f && fx <= (float)g.dx && fy >= -1.f && fy <= (float)g.dy && fz >= -1.f && fz <= (float)g.dz)) return false;
+    const int cx = (int)fx, cy = (int)fy, cz = (int)fz;
+    const int x0 = max(cx - 1, 0), x1 = min(cx + 1, g.dx - 1);
+    if (x0 > x1) return false;
+    float best = FLT_MAX;
+    idx = -1;
+    for (int z = max(cz - 1, 0); z <= min(cz + 1, g.dz - 1); ++z)
+        for (int y = max(cy - 1, 0); y <= min(cy + 1, g.dy - 1); ++y) {
+            const int row = (z * g.dy + y) * g.dx;
+            const uint32_t b = __ldg(g.cell_start + row + x0), e = __ldg(g.cell_start + row + x1 + 1);
+            for (uint32_t j = b; j < e; ++j) {
+                const float4 p = __ldg(g.pts + j);
+                const float d = sqdist3(qx, qy, qz, p.x, p.y, p.z);
+                const int ref = __float_as_int(p.w);
+                if (d < best || (d == best && ref < idx)) { best = d; idx = ref; }
+            }
+        }
+    return idx >= 0 && best < max_d2;
+}
+
+template <bool NN>
 __global__ void __launch_bounds__(kIcpThreads) icp_point2plane_kernel(IcpArgs a) {
     __shared__ float s_part[kIcpWarps][29];
     __shared__ float s_T[16];        // accumulated transformation, row-major
@@ -119,13 +147,20 @@ __global__ void __launch_bounds__(kIcpThreads) icp_point2plane_kernel(IcpArgs a)
         for (int i = 0; i < 29; ++i) acc[i] = 0.f;
         for (int i = tid; i < n; i += kIcpThreads) {
             const float sx = pts[3 * i], sy = pts[3 * i + 1], sz = pts[3 * i + 2];
-            // Scene_projective::query (depth_scene.h:29-50) with pcd2dep (common.h:68-78)
-            const int u = (int)(sx / sz * a.k00 + a.k02 + 0.5f);
-            const int v = (int)(sy / sz * a.k11 + a.k12 + 0.5f);
-            if (u >= a.width || v >= a.height || u < 0 || v < 0) continue;
-            const size_t idx = (size_t)u + (size_t)v * a.width;
+            size_t idx;
+            if (NN) {
+                int ref;
+                if (!nn_associate(a.nn_grid, a.max_dist_diff * a.max_dist_diff, sx, sy, sz, ref)) continue;
+                idx = (size_t)ref;
+            } else {
+                // Scene_projective::query (depth_scene.h:29-50) with pcd2dep (common.h:68-78)
+                const int u = (int)(sx / sz * a.k00 + a.k02 + 0.5f);
+                const int v = (int)(sy / sz * a.k11 + a.k12 + 0.5f);
+                if (u >= a.width || v >= a.height || u < 0 || v < 0) continue;
+                idx = (size_t)u + (size_t)v * a.width;
+            }
             const float dx = a.scene_pcd[3 * idx], dy = a.scene_pcd[3 * idx + 1], dz = a.scene_pcd[3 * idx + 2];
-            if (dz <= 0.f || fabsf(sz - dz) > a.max_dist_diff) continue;
+            if (!NN && (dz <= 0.f || fabsf(sz - dz) > a.max_dist_diff)) continue;
             const float nx = a.scene_normals[3 * idx], ny = a.scene_normals[3 * idx + 1], nz = a.scene_normals[3 * idx + 2];
             // thrust__pcd2Ab (icp.h:129-210)
             const float bt = (dx - sx) * nx + (dy - sy) * ny + (dz - sz) * nz;
@@ -222,7 +257,8 @@ cudaError_t launch_icp_scene(const int32_t* d_depth, int W, int H, const float K
 
 cudaError_t launch_icp_point2plane(const IcpArgs& a, int n_clouds, cudaStream_t stream) {
     if (n_clouds <= 0) return cudaSuccess;
-    icp_point2plane_kernel<<<n_clouds, kIcpThreads, 0, stream>>>(a);
+    if (a.nn) icp_point2plane_kernel<true><<<n_clouds, kIcpThreads, 0, stream>>>(a);
+    else icp_point2plane_kernel<false><<<n_clouds, kIcpThreads, 0, stream>>>(a);
     return cudaGetLastError();
 }
 

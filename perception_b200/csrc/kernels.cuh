@@ -156,7 +156,12 @@ struct IcpArgs {
     const float* scene_normals = nullptr;
     int width = 0, height = 0;
     float k00 = 0, k02 = 0, k11 = 0, k12 = 0;
-    float max_dist_diff = 0.1f;       // depth_scene.h:9
+    float max_dist_diff = 0.1f;       // depth_scene.h:9 (projective) / pcd_scene.h:48 (nearest neighbour, 0.01)
+    // Scene_nn (pcd_scene.h:47-136): association by exact nearest scene point within max_dist_diff instead of by
+    // projection; nn_grid holds the valid scene points (w = pixel index into scene_pcd / scene_normals) in cells just
+    // wider than max_dist_diff.  nn = 0 => Scene_projective.
+    int nn = 0;
+    ObsGridDev nn_grid;
     float relative_fitness = 1e-5f, relative_rmse = 1e-5f;  // ICPConvergenceCriteria, icp.h:40-51
     int max_iteration = 30;
     float* out_T = nullptr;           // n_clouds x 16, row-major 4x4

@@ -429,8 +429,9 @@ class Renderer:
         self._ck(self._lib.perch_icp_set_scene(self._h, _ptr(d), width, height, _ptr(K9), max_dist_diff, _ptr(pcd), _ptr(nrm)))
         return (pcd, nrm) if want_buffers else None
 
-    def icp_point2plane(self, clouds, relative_fitness=1e-5, relative_rmse=1e-5, max_iteration=30):
-        """cuda_icp::ICP_Point2Plane_cuda<Scene_projective> (icp.h:92-99) for a list of (n_i,3) clouds.  Returns
+    def icp_point2plane(self, clouds, relative_fitness=1e-5, relative_rmse=1e-5, max_iteration=30, nn_max_dist=None):
+        """cuda_icp::ICP_Point2Plane_cuda<Scene_projective> (icp.h:92-99) for a list of (n_i,3) clouds, or, with
+        nn_max_dist (reference: 0.01 m), ICP_Point2Plane_cuda<Scene_nn>: nearest-scene-point association.  Returns
         transformation (B,4,4), fitness (B,), inlier_rmse (B,), iterations (B,), and the transformed clouds."""
         clouds = [np.ascontiguousarray(c, np.float32).reshape(-1, 3) for c in clouds]
         off = np.zeros(len(clouds) + 1, np.int32)
@@ -440,8 +441,13 @@ class Renderer:
         T = np.zeros((B, 4, 4), np.float32)
         fit = np.zeros(B, np.float32); rmse = np.zeros(B, np.float32); it = np.zeros(B, np.int32)
         out = np.zeros_like(pts)
-        self._ck(self._lib.perch_icp_point2plane(self._h, _ptr(pts), _ptr(off), B, relative_fitness, relative_rmse,
-                                                 max_iteration, _ptr(T), _ptr(fit), _ptr(rmse), _ptr(it), _ptr(out)))
+        if nn_max_dist is None:
+            self._ck(self._lib.perch_icp_point2plane(self._h, _ptr(pts), _ptr(off), B, relative_fitness, relative_rmse,
+                                                     max_iteration, _ptr(T), _ptr(fit), _ptr(rmse), _ptr(it), _ptr(out)))
+        else:
+            self._ck(self._lib.perch_icp_point2plane_nn(self._h, _ptr(pts), _ptr(off), B, float(nn_max_dist), relative_fitness,
+                                                        relative_rmse, max_iteration, _ptr(T), _ptr(fit), _ptr(rmse), _ptr(it),
+                                                        _ptr(out)))
         return {"transformation": T, "fitness": fit, "inlier_rmse": rmse, "iterations": it,
                 "clouds": [out[off[i]:off[i + 1]] for i in range(B)]}
 

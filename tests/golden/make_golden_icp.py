@@ -39,6 +39,22 @@ def main(out_dir):
         save[f"T3_{i}"], save[f"fit3_{i}"], save[f"rmse3_{i}"] = r3["transformation"], np.float32(r3["fitness"]), np.float32(r3["inlier_rmse"])
     np.savez_compressed(out / "icp.npz", **save)
     print("wrote", out / "icp.npz")
+    # Scene_nn (kd-tree association, pcd_scene.h): the reference builds scene cloud, normals and tree itself
+    save = {}
+    for i, c in enumerate(cl):
+        r0 = ref.point2plane_nn(c, s.source_depth, icp_cases.W, icp_cases.H, K, max_iteration=0)   # association only
+        r = ref.point2plane_nn(c, s.source_depth, icp_cases.W, icp_cases.H, K)
+        r2 = ref.point2plane_nn(c, s.source_depth, icp_cases.W, icp_cases.H, K)
+        o0 = orc.icp_point2plane(c, pcd, nrm, icp_cases.W, icp_cases.H, K, max_dist_diff=0.01, max_iteration=0, nn=True)
+        o = orc.icp_point2plane(c, pcd, nrm, icp_cases.W, icp_cases.H, K, max_dist_diff=0.01, nn=True)
+        print(f"nn cloud {i}: ref fitness0 {r0['fitness']:.5f} rmse0 {r0['inlier_rmse']:.6f} | oracle {o0['fitness']:.5f} "
+              f"{o0['inlier_rmse']:.6f} | final ref {r['fitness']:.5f} {r['inlier_rmse']:.6f} oracle {o['fitness']:.5f} "
+              f"{o['inlier_rmse']:.6f} dT {np.abs(o['transformation'] - r['transformation']).max():.2e} reproducible "
+              f"{np.array_equal(r['transformation'], r2['transformation'])} it {o['iterations']}", flush=True)
+        save[f"T{i}"], save[f"fit{i}"], save[f"rmse{i}"] = r["transformation"], np.float32(r["fitness"]), np.float32(r["inlier_rmse"])
+        save[f"fit0_{i}"], save[f"rmse0_{i}"] = np.float32(r0["fitness"]), np.float32(r0["inlier_rmse"])
+    np.savez_compressed(out / "icp_nn.npz", **save)
+    print("wrote", out / "icp_nn.npz")
 
 
 if __name__ == "__main__":

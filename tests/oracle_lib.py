@@ -186,13 +186,15 @@ class Oracle:
         return pcd, nrm
 
     def icp_point2plane(self, cloud, scene_pcd, scene_normals, W, H, K, max_dist_diff=0.1, relative_fitness=1e-5,
-                        relative_rmse=1e-5, max_iteration=30):
+                        relative_rmse=1e-5, max_iteration=30, nn=False):
+        """nn=False: Scene_projective association; nn=True: Scene_nn (nearest scene point within max_dist_diff)."""
         pts = np.array(cloud, np.float32, copy=True).reshape(-1, 3)
         K9 = _c(K, np.float32).reshape(9)
         T = np.zeros(16, np.float32)
         fit, rmse = C.c_float(0), C.c_float(0)
-        self.lib.oracle_icp_point2plane.restype = C.c_int
-        it = self.lib.oracle_icp_point2plane(_p(pts), C.c_int(len(pts)), _p(_c(scene_pcd, np.float32)),
+        fn = self.lib.oracle_icp_point2plane_nn if nn else self.lib.oracle_icp_point2plane
+        fn.restype = C.c_int
+        it = fn(_p(pts), C.c_int(len(pts)), _p(_c(scene_pcd, np.float32)),
                                              _p(_c(scene_normals, np.float32)), C.c_int(W), C.c_int(H), _p(K9),
                                              C.c_float(max_dist_diff), C.c_float(relative_fitness), C.c_float(relative_rmse),
                                              C.c_int(max_iteration), _p(T), C.byref(fit), C.byref(rmse))
@@ -229,6 +231,20 @@ class ReferenceIcp:
                                           _p(_c(scene_normals, np.float32)), C.c_int(W), C.c_int(H), _p(K9),
                                           C.c_float(max_dist_diff), C.c_float(relative_fitness), C.c_float(relative_rmse),
                                           C.c_int(max_iteration), _p(T), C.byref(fit), C.byref(rmse))
+        assert rc == 0
+        return {"transformation": T.reshape(4, 4), "fitness": fit.value, "inlier_rmse": rmse.value, "cloud": pts}
+
+
+    def point2plane_nn(self, cloud, depth, W, H, K, relative_fitness=1e-5, relative_rmse=1e-5, max_iteration=30):
+        """ICP_Point2Plane_cuda<Scene_nn>: scene cloud, normals and kd-tree built by the reference's init_Scene_nn_cuda."""
+        pts = np.array(cloud, np.float32, copy=True).reshape(-1, 3)
+        d = _c(depth, np.int32).reshape(-1)
+        K9 = _c(K, np.float32).reshape(9)
+        T = np.zeros(16, np.float32)
+        fit, rmse = C.c_float(0), C.c_float(0)
+        rc = self.lib.ref_icp_nn_point2plane(_p(pts), C.c_int(len(pts)), _p(d), C.c_int(W), C.c_int(H), _p(K9),
+                                             C.c_float(relative_fitness), C.c_float(relative_rmse), C.c_int(max_iteration),
+                                             _p(T), C.byref(fit), C.byref(rmse))
         assert rc == 0
         return {"transformation": T.reshape(4, 4), "fitness": fit.value, "inlier_rmse": rmse.value, "cloud": pts}
 

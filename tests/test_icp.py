@@ -93,6 +93,26 @@ def test_oracle_icp_matches_reference_golden(orc):
     assert converged >= 2
 
 
+def test_oracle_icp_nn_matches_reference_golden(orc):
+    """Scene_nn association (pcd_scene.h:60-136): golden = the reference's own kd-tree walk inside
+    ICP_Point2Plane_cuda<Scene_nn> (tests/golden/make_golden_icp.py); the oracle finds the same correspondences by brute
+    force."""
+    path = GOLDEN.parent / "icp_nn.npz"
+    if not path.exists():
+        pytest.skip("tests/golden/icp_nn.npz not generated yet")
+    g = np.load(path)
+    case, K = icp_cases.scene()
+    pcd, nrm = orc.icp_scene(case.scene.source_depth, icp_cases.W, icp_cases.H, K)
+    cl, _ = icp_cases.clouds(pcd, case.scene.source_label)
+    for i, c in enumerate(cl[:2]):   # the brute-force association is O(points x pixels) per iteration
+        o0 = orc.icp_point2plane(c, pcd, nrm, icp_cases.W, icp_cases.H, K, max_dist_diff=0.01, max_iteration=0, nn=True)
+        assert abs(o0["fitness"] - float(g[f"fit0_{i}"])) < 1e-6 and abs(o0["inlier_rmse"] - float(g[f"rmse0_{i}"])) < 1e-6
+        o = orc.icp_point2plane(c, pcd, nrm, icp_cases.W, icp_cases.H, K, max_dist_diff=0.01, nn=True)
+        if o["iterations"] < 30:
+            assert _close(o["transformation"], g[f"T{i}"]), i
+            assert abs(o["fitness"] - float(g[f"fit{i}"])) < 5e-3 and abs(o["inlier_rmse"] - float(g[f"rmse{i}"])) < 1e-5
+
+
 # ---- GPU -------------------------------------------------------------------------------------------------------------------
 @pytest.mark.gpu
 def test_icp_scene_bit_exact(orc):
@@ -141,3 +161,47 @@ def test_icp_point2plane_parity(orc):
     n = len(cl)
     assert np.array_equal(batch["transformation"][n], np.eye(4)) and batch["fitness"][n] == 0        # empty cloud
     assert np.array_equal(batch["transformation"][n + 1], np.eye(4)) and batch["fitness"][n + 1] == 0  # nothing valid
+
+
+@pytest.mark.gpu
+def test_icp_nn_parity(orc):
+    """ICP_Point2Plane_cuda<Scene_nn> (kd-tree association, pcd_scene.h:47-136): the association itself (fitness and
+    rmse before any update) must match the reference's kd-tree walk and the oracle's brute force; settled runs agree to
+    0.1 mm / 0.01 deg like the projective variant."""
+    from perception_b200.renderer import Renderer
+    case, K = icp_cases.scene()
+    with Renderer(0) as r:
+        pcd, nrm = r.icp_set_scene(case.scene.source_depth, icp_cases.W, icp_cases.H, K, want_buffers=True)
+        cl, _ = icp_cases.clouds(pcd, case.scene.source_label, n_clouds=4)
+        extra = [np.zeros((0, 3), np.float32), cl[0] + np.float32([0, 0, 5])]
+        first = r.icp_point2plane(cl + extra, max_iteration=0, nn_max_dist=0.01)
+        full = r.icp_point2plane(cl + extra, nn_max_dist=0.01)
+        wide = r.icp_point2plane(cl, max_iteration=0, nn_max_dist=0.03)   # another gate: the grid is rebuilt
+        proj = r.icp_point2plane(cl, max_iteration=0)
+    ref = ReferenceIcp() if ICP_REF_SO.exists() else None
+    g = np.load(GOLDEN.parent / "icp_nn.npz") if (GOLDEN.parent / "icp_nn.npz").exists() else None
+    settled = 0
+    for i, c in enumerate(cl):
+        o0 = orc.icp_point2plane(c, pcd, nrm, icp_cases.W, icp_cases.H, K, max_dist_diff=0.01, max_iteration=0, nn=True)
+        assert first["fitness"][i] == np.float32(o0["fitness"]) > 0.5, i          # same correspondences, counted
+        assert abs(first["inlier_rmse"][i] - o0["inlier_rmse"]) < 1e-6
+        assert wide["fitness"][i] >= first["fitness"][i]
+        if g is not None:
+            assert abs(first["fitness"][i] - float(g[f"fit0_{i}"])) < 1e-6 and abs(first["inlier_rmse"][i] - float(g[f"rmse0_{i}"])) < 1e-6
+        if ref is not None:
+            q0 = ref.point2plane_nn(c, case.scene.source_depth, icp_cases.W, icp_cases.H, K, max_iteration=0)
+            assert abs(first["fitness"][i] - q0["fitness"]) < 1e-6 and abs(first["inlier_rmse"][i] - q0["inlier_rmse"]) < 1e-6
+        o = orc.icp_point2plane(c, pcd, nrm, icp_cases.W, icp_cases.H, K, max_dist_diff=0.01, nn=True)
+        if o["iterations"] >= 30:
+            continue
+        settled += 1
+        assert _close(full["transformation"][i], o["transformation"]), i
+        assert abs(full["fitness"][i] - o["fitness"]) < 5e-3 and abs(full["inlier_rmse"][i] - o["inlier_rmse"]) < 1e-5
+        if ref is not None:
+            q = ref.point2plane_nn(c, case.scene.source_depth, icp_cases.W, icp_cases.H, K)
+            assert _close(full["transformation"][i], q["transformation"]), i
+    assert settled >= 2
+    n = len(cl)
+    assert np.array_equal(full["transformation"][n], np.eye(4)) and full["fitness"][n] == 0
+    assert np.array_equal(full["transformation"][n + 1], np.eye(4)) and full["fitness"][n + 1] == 0
+    assert proj["fitness"].shape == (n,)
