@@ -709,12 +709,42 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
     if (MODE == MODE_IMAGE) {
         // every output pixel outside the pose tile is empty: the kernel writes the whole image, no memset pass
         if (!a.single_keys && a.img_depth) {
-            for (int i = tid; i < Lw * Lh; i += kThreads) {
-                int lx = i % Lw, ly = i / Lw;
-                if (!tile_empty && lx >= rx0 && lx <= rx1 && ly >= ry0 && ly <= ry1) continue;
-                size_t o = (size_t)pose_i * Lh * Lw + i;
-                a.img_depth[o] = 0;
-                if (a.img_r) { a.img_r[o] = 0; a.img_g[o] = 0; a.img_b[o] = 0; }
+            const size_t img0 = (size_t)pose_i * Lh * Lw;
+            const int n_px = Lw * Lh;
+            // groups of four pixels that lie entirely outside the tile are cleared with one 16-byte store (depth) and
+            // three 4-byte stores (colour planes); requires rows and image bases that keep the groups aligned
+            const bool wide = (Lw % 4 == 0) && (img0 % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.img_depth) & 15) == 0) &&
+                              (!a.img_r || (((reinterpret_cast<uintptr_t>(a.img_r) | reinterpret_cast<uintptr_t>(a.img_g) |
+                                              reinterpret_cast<uintptr_t>(a.img_b)) & 3) == 0));
+            if (wide) {
+                const int Lw4 = Lw >> 2;
+                for (int g = tid; g < (n_px >> 2); g += kThreads) {
+                    const int ly = g / Lw4, lx = (g - ly * Lw4) << 2;
+                    const size_t o = img0 + (size_t)g * 4;
+                    const bool row_in = !tile_empty && ly >= ry0 && ly <= ry1;
+                    if (!row_in || lx + 3 < rx0 || lx > rx1) {
+                        *reinterpret_cast<int4*>(a.img_depth + o) = make_int4(0, 0, 0, 0);
+                        if (a.img_r) {
+                            *reinterpret_cast<uint32_t*>(a.img_r + o) = 0u;
+                            *reinterpret_cast<uint32_t*>(a.img_g + o) = 0u;
+                            *reinterpret_cast<uint32_t*>(a.img_b + o) = 0u;
+                        }
+                    } else {
+                        for (int k = 0; k < 4; ++k) {
+                            if (lx + k >= rx0 && lx + k <= rx1) continue;
+                            a.img_depth[o + k] = 0;
+                            if (a.img_r) { a.img_r[o + k] = 0; a.img_g[o + k] = 0; a.img_b[o + k] = 0; }
+                        }
+                    }
+                }
+            } else {
+                for (int i = tid; i < n_px; i += kThreads) {
+                    int lx = i % Lw, ly = i / Lw;
+                    if (!tile_empty && lx >= rx0 && lx <= rx1 && ly >= ry0 && ly <= ry1) continue;
+                    size_t o = img0 + i;
+                    a.img_depth[o] = 0;
+                    if (a.img_r) { a.img_r[o] = 0; a.img_g[o] = 0; a.img_b[o] = 0; }
+                }
             }
         }
         if (a.tree_total) {
