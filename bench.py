@@ -271,6 +271,23 @@ def run_ours(args):
                 traffic = json.loads(tfile.read_text()).get(args.workload)
             except Exception:
                 traffic = None
+        # what actually bounds the kernel: warp-instruction issue.  The per-launch instruction count is the
+        # smsp__inst_executed.sum of the committed ncu capture of this workload (profiles/kernel_counters.json); the rate
+        # is that count over the kernel time measured HERE, against SMs x 4 schedulers x the SM clock sampled in this run.
+        issue = None
+        cfile = ROOT / "profiles" / "kernel_counters.json"
+        if cfile.exists():
+            try:
+                kc = json.loads(cfile.read_text()).get(args.workload)
+                if kc and kc.get("poses") == P and clocks.get("sm_mhz"):
+                    sms = int(kc.get("sm_count", 148))
+                    rate = kc["warp_inst_per_launch"] / (kern_ms / 1e3)
+                    peak_rate = sms * 4 * clocks["sm_mhz"] * 1e6
+                    issue = {"bound": "warp-instruction issue", "warp_inst_per_pose": kc["warp_inst_per_launch"] / P,
+                             "achieved": rate / 1e9, "peak": peak_rate / 1e9, "unit": "G warp-inst/s", "frac": rate / peak_rate,
+                             "source": kc.get("source")}
+            except Exception:
+                issue = None
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
@@ -285,6 +302,7 @@ def run_ours(args):
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "peak_kind": f"{peak_kind} copy bandwidth", "bytes_per_pose": bpp,
                          "poses_per_launch": P, "kernel": "pose_kernel<MODE_COST>", "kernel_ms": kern_ms},
+            "issue_roofline": issue,
             "work": work,
             "best": {"cost": int(best["cost"]), "pose_id": int(best["pose_id"])},
             "wall_s_device_loop": wall_device_loop,
