@@ -494,7 +494,7 @@ void perch_destroy(perch_ctx* c) {
     void* ptrs[] = {c->d_tri_color, c->d_model_low, c->d_model_high, c->d_model_aabb, c->d_tri_lab, c->d_cl_recs, c->d_cl_bounds,
                     c->d_cl_orig, c->d_cl_perm, c->d_cl_low, c->d_cl_high,
                     c->d_src_depth, c->d_src_label, c->d_src_rgb, c->d_grid_pts, c->d_grid_label, c->d_cell_start,
-                    c->d_icp_grid_pts, c->d_icp_grid_label, c->d_icp_grid_cells, c->d_cmp_depth, c->d_cmp_label, c->d_ggrid_pts, c->d_ggrid_label, c->d_ggrid_cell_start,
+                    c->d_icp_grid_pts, c->d_icp_grid_label, c->d_icp_grid_cells, c->d_cmp_depth, c->d_cmp_label, c->d_full_keys, c->d_full_big, c->d_full_count, c->d_full_acc, c->d_ggrid_pts, c->d_ggrid_label, c->d_ggrid_cell_start,
                     c->d_obs_lab, c->d_obs_rgb, c->d_scratch, c->d_err_flag, c->d_flush, c->d_obs_xyz_aos,
                     c->d_tgt_normals, c->d_obs_xyz4, c->d_label_range, c->d_gicp, c->d_icp_pcd, c->d_icp_normals};
     for (void* p : ptrs)
@@ -633,6 +633,9 @@ int perch_set_models(perch_ctx* c, const perch_triangle* tris, int64_t n_tris, c
         c->models.cl_perm = c->d_cl_perm;
         c->models.cl_low = c->d_cl_low;
         c->models.cl_high = c->d_cl_high;
+        c->max_model_quads = 0;
+        for (size_t m = 0; m < cs.model_low.size(); ++m)
+            c->max_model_quads = std::max(c->max_model_quads, perch::kClusterQuads * (cs.model_high[m] - cs.model_low[m]));
     }
     CU(cudaStreamSynchronize(c->stream));
     c->models.tri_color = c->d_tri_color;
@@ -1237,7 +1240,15 @@ int perch_detail::render_cost_impl(perch_ctx* c, const char* stage, const PoseIn
             CU(perch::launch_single_clear(d_keys, (int)npx, c->stream));
             ++launches;
         }
-        if (n_poses > 0) {
+        if (n_poses > 0 && !env_int("PERCH_IMAGE_LEGACY", 0)) {
+            // every pixel: the dedicated rasteriser (raster_full.cu); PERCH_IMAGE_LEGACY=1 keeps the per-pose kernel (A/B)
+            perch::FullJob j;
+            j.poses = base.poses; j.pose_model_map = base.pose_model_map; j.pose_label = base.pose_label;
+            j.n_poses = n_poses; j.occlusion_threshold = base.occlusion_threshold;
+            j.single_keys = p->single_result_image ? d_keys : nullptr;
+            j.img_depth = d_depth; j.img_r = d_r; j.img_g = d_g; j.img_b = d_b;
+            CU(perch::full_raster_job(c, j, &launches));
+        } else if (n_poses > 0) {
             CU(perch::launch_raster_images(a, c->stream));
             ++launches;
         }

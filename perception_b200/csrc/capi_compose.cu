@@ -40,6 +40,12 @@ int check_err_flag(perch_ctx* c) {
     return PERCH_OK;
 }
 
+// PERCH_IMAGE_LEGACY=1: full-resolution work on the per-pose kernel instead of raster_full.cu (A/B tests)
+bool legacy_images() {
+    const char* v = getenv("PERCH_IMAGE_LEGACY");
+    return v && *v && atoi(v) != 0;
+}
+
 }  // namespace
 
 extern "C" {
@@ -89,7 +95,14 @@ int perch_compose_source(perch_ctx* c, const float* poses16, int n_poses, const 
         a.key_pose_id = 1;
         a.err_flag = c->d_err_flag;
         a.tile_cap = image_tile_cap(W);
-        PERCH_CU(perch::launch_raster_images(a, c->stream));
+        if (legacy_images()) {
+            PERCH_CU(perch::launch_raster_images(a, c->stream));
+        } else {
+            perch::FullJob j;
+            j.poses = a.poses; j.pose_model_map = d_pmm; j.n_poses = n_poses;
+            j.single_keys = d_keys; j.key_pose_id = 1;
+            PERCH_CU(perch::full_raster_job(c, j, nullptr));
+        }
     }
     perch::ComposeArgs ca;
     ca.keys = d_keys;
@@ -151,10 +164,20 @@ int perch_tree_flags(perch_ctx* c, const float* poses16, int n_poses, const int*
     a.err_flag = c->d_err_flag;
     a.tile_cap = image_tile_cap(c->cam.width);
     PERCH_CU(cudaEventRecord(c->ev0, c->stream));
-    PERCH_CU(perch::launch_raster_images(a, c->stream));
+    int launches = 0;
+    if (legacy_images()) {
+        PERCH_CU(perch::launch_raster_images(a, c->stream));
+        launches = 1;
+    } else {
+        perch::FullJob j;
+        j.poses = a.poses; j.pose_model_map = d_pmm; j.pose_label = a.pose_label; j.n_poses = n_poses;
+        j.occlusion_threshold = occlusion_threshold;
+        j.tree_occluded = d_occ; j.tree_occluded_other = d_other; j.tree_clutter = d_clutter; j.tree_total = d_total;
+        PERCH_CU(perch::full_raster_job(c, j, &launches));
+    }
     PERCH_CU(cudaEventRecord(c->ev1, c->stream));
     c->timing_pending = true;
-    c->last_launches = 1;
+    c->last_launches = launches;
     if (pose_occluded) PERCH_CU(cudaMemcpyAsync(pose_occluded, d_occ, P * 4, cudaMemcpyDeviceToHost, c->stream));
     if (pose_occluded_other) PERCH_CU(cudaMemcpyAsync(pose_occluded_other, d_other, P * 4, cudaMemcpyDeviceToHost, c->stream));
     if (clutter_cost) PERCH_CU(cudaMemcpyAsync(clutter_cost, d_clutter, P * 4, cudaMemcpyDeviceToHost, c->stream));

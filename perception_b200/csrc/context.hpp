@@ -105,6 +105,14 @@ struct perch_ctx {
     int32_t* d_cmp_depth = nullptr;
     uint8_t* d_cmp_label = nullptr;
     bool composed = false;
+    // full-resolution rasteriser (raster_full.cu): key images of one chunk of poses, deferred-triangle list, counters
+    unsigned long long* d_full_keys = nullptr;
+    size_t full_keys_n = 0;            // keys allocated (all empty between calls)
+    int2* d_full_big = nullptr;
+    int* d_full_count = nullptr;
+    int* d_full_acc = nullptr;
+    size_t full_acc_n = 0;
+    int max_model_quads = 0;
 
     // observed cloud (host copies kept so the grid can be rebuilt when sensor_resolution changes)
     std::vector<float> h_obs_xyz;      // label-sorted, AoS

@@ -58,6 +58,59 @@ cudaError_t launch_raster_images(const PoseArgs& a, cudaStream_t stream);
 cudaError_t launch_single_clear(unsigned long long* keys, int n, cudaStream_t stream);
 cudaError_t launch_resolve_single(const PoseArgs& a, cudaStream_t stream);
 
+// ---- full-resolution rasteriser (raster_full.cu): stages RENDER / DEBUG, composition, perch_tree_flags ---------------
+struct FullRasterArgs {
+    ModelsDev models;
+    CameraDev cam;
+    SceneDev scene;
+    const Mat4* poses = nullptr;
+    const int* pose_model_map = nullptr;
+    const int* pose_label = nullptr;        // null => 3-DoF occlusion rule
+    int n_poses = 0;
+    float occlusion_threshold = 0.f;
+    unsigned long long* keys = nullptr;     // n_poses x W*H (depth, triangle) keys, or ONE image when `single`
+    int single = 0;                         // single_result_image: every pose z-tests into keys[0 .. W*H)
+    int key_pose_id = 0;                    // low word of the key = pose index instead of original triangle index
+    int reset_keys = 0;                     // the resolve pass leaves every key empty again (next chunk needs no fill)
+    int2* big_list = nullptr;               // (pose, triangle slot | perm << 26) of triangles with large bboxes
+    int* big_count = nullptr;
+    int big_cap = 0;
+    int big_ctas = 0;
+    int big_cells = 64;                     // bbox pixels above which a triangle is deferred to the warp-per-triangle kernel
+    // resolve outputs: n_poses x W*H images (any may be null), and the per-pose vectors of PoseArgs::tree_*
+    int32_t* img_depth = nullptr;
+    uint8_t* img_r = nullptr;
+    uint8_t* img_g = nullptr;
+    uint8_t* img_b = nullptr;
+    int wide_stores = 0;                    // W*H % 4 == 0 and every image plane 16/4-byte aligned
+    int* tree_occluded = nullptr;
+    int* tree_occluded_other = nullptr;
+    float* tree_clutter = nullptr;
+    float* tree_total = nullptr;
+    int* tree_acc = nullptr;                // 3 x n_poses scratch (flags, cleared, covered)
+};
+cudaError_t launch_full_raster(const FullRasterArgs& a, int max_model_quads, cudaStream_t stream);
+cudaError_t launch_full_resolve(const FullRasterArgs& a, int n_images, cudaStream_t stream);
+// Host driver: poses in chunks whose key images stay L2-resident (or all poses into `single_keys`, raster only).
+struct FullJob {
+    const Mat4* poses = nullptr;
+    const int* pose_model_map = nullptr;
+    const int* pose_label = nullptr;
+    int n_poses = 0;
+    float occlusion_threshold = 0.f;
+    unsigned long long* single_keys = nullptr;  // cleared by the caller; resolved by the caller (resolve_single / compose)
+    int key_pose_id = 0;
+    int32_t* img_depth = nullptr;
+    uint8_t* img_r = nullptr;
+    uint8_t* img_g = nullptr;
+    uint8_t* img_b = nullptr;
+    int* tree_occluded = nullptr;
+    int* tree_occluded_other = nullptr;
+    float* tree_clutter = nullptr;
+    float* tree_total = nullptr;
+};
+cudaError_t full_raster_job(::perch_ctx* c, const FullJob& j, int* launches);
+
 // ---- composition mode (compose.cu): key image of the placed objects -> source depth (+ label) image ----------------
 struct ComposeArgs {
     const unsigned long long* keys = nullptr;  // W*H single_result_image keys with key_pose_id

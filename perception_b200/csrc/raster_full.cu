@@ -1,0 +1,346 @@
+// Full-resolution rasteriser (stages RENDER / DEBUG, scene composition, perch_tree_flags): image_render
+// (image_renderer.cuh:336-496) for EVERY pixel.
+//
+// The per-pose kernel of pose_kernels.cu is built around the stride lattice: with stride 1 nothing can be culled, every
+// triangle reaches its exact path, and the 64-bit shared z-buffer leaves 3 CTAs per SM
+// (profiles/r1_render_kernel_v1.md: 8 % of the HBM write roofline).  Here the work is spread over (pose, 128 quads) CTAs
+// instead of one CTA per pose:
+//   raster_quads_kernel  one thread per quad: FOUR exact vertex transforms for two triangles, the reference's bbox loops
+//                        and fragment arithmetic (exact_math.cuh), z-test with a 64-bit atomicMin on an order-preserving
+//                        (depth, triangle) key image in global memory (L2-resident atomics);
+//   raster_big_kernel    triangles covering many pixels (a table plane), deferred by the first kernel, one CTA each;
+//   resolve_full_kernel  keys -> int32 depth + RGB with the source-occlusion rule, four pixels per thread (16-byte
+//                        stores), and optionally the per-pose vectors of the USE_TREE / USE_CLUTTER branches.
+// Canonical semantics as everywhere: minimum depth over fragments, lowest original triangle index
+// at that depth wins the colour, occlusion rule on the final depth.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdlib>
+
+#include "clusters.hpp"
+#include "context.hpp"
+#include "kernels.cuh"
+
+namespace perch {
+
+namespace {
+
+constexpr int kFullThreads = 128;
+constexpr int kBigThreads = 256;
+
+__device__ __forceinline__ unsigned long long make_key(int32_t d, uint32_t id) {
+    return ((unsigned long long)((uint32_t)d ^ 0x80000000u) << 32) | id;
+}
+
+struct PixelRect {
+    int x0, x1, r0, r1;  // inclusive pixel columns and RASTER rows (image row = H-1-r); empty when x0 > x1 or r0 > r1
+};
+
+// The pixels the reference's loops visit (image_renderer.cuh:110-111): P from size_t(bboxmin + 0.5f) while P <= bboxmax.
+__device__ __forceinline__ PixelRect pixel_rect_of(float bminx, float bmaxx, float bminy, float bmaxy, int W, int H) {
+    PixelRect r{1, 0, 1, 0};
+    if (!(bmaxx >= 0.f) || !(bmaxy >= 0.f)) return r;  // also rejects NaN upper bounds (loop condition false)
+    const unsigned long long p0 = (unsigned long long)__fadd_rn(bminx, 0.5f);  // NaN -> 0
+    const unsigned long long p1 = (unsigned long long)__fadd_rn(bminy, 0.5f);
+    if (p0 > (unsigned long long)(W - 1) || p1 > (unsigned long long)(H - 1)) return r;
+    r.x0 = (int)p0; r.x1 = (int)bmaxx;  // <= W-1 / H-1 by the clamp of bbox_of
+    r.r0 = (int)p1; r.r1 = (int)bmaxy;
+    return r;
+}
+
+struct Tri3 {
+    ScreenVertex a, b, c;
+};
+
+__device__ __forceinline__ ScreenVertex pick(const ScreenVertex v[4], uint32_t i) {
+    ScreenVertex o;
+    o.sx = i == 0 ? v[0].sx : i == 1 ? v[1].sx : i == 2 ? v[2].sx : v[3].sx;
+    o.sy = i == 0 ? v[0].sy : i == 1 ? v[1].sy : i == 2 ? v[2].sy : v[3].sy;
+    o.z = i == 0 ? v[0].z : i == 1 ? v[1].z : i == 2 ? v[2].z : v[3].z;
+    return o;
+}
+
+__global__ void __launch_bounds__(kFullThreads) raster_quads_kernel(FullRasterArgs a) {
+    __shared__ Mat4 s_pose;
+    const int pose_i = blockIdx.y, tid = threadIdx.x;
+    const int model = a.pose_model_map[pose_i];
+    if (model < 0 || model >= a.models.n_models) return;
+    const int q_low = 2 * a.models.cl_low[model], q_high = 2 * a.models.cl_high[model];
+    if (q_low + (int)blockIdx.x * kFullThreads >= q_high) return;  // whole CTA past this model's quads
+    if (tid < 16) reinterpret_cast<float*>(&s_pose)[tid] = reinterpret_cast<const float*>(a.poses + pose_i)[tid];
+    __syncthreads();
+    const int qi = q_low + blockIdx.x * kFullThreads + tid;
+    if (qi >= q_high) return;
+    const uint32_t perm2 = (__ldg(a.models.cl_perm + (qi >> 1)) >> (12 * (qi & 1))) & 0xFFFu;
+    if ((perm2 & 63u) == kPermInvalid && (perm2 >> 6) == kPermInvalid) return;
+    const int W = a.cam.width, H = a.cam.height;
+    const float wf = (float)W, hf = (float)H, cmaxx = (float)(W - 1), cmaxy = (float)(H - 1);
+    const float4* rec = reinterpret_cast<const float4*>(a.models.cl_recs + (int64_t)qi * kQuadFloats);
+    const float4 r0 = __ldg(rec), r1 = __ldg(rec + 1), r2 = __ldg(rec + 2);
+    ScreenVertex v[4];
+    v[0] = transform_vertex(s_pose, a.cam.proj, wf, hf, r0.x, r0.y, r0.z);
+    v[1] = transform_vertex(s_pose, a.cam.proj, wf, hf, r0.w, r1.x, r1.y);
+    v[2] = transform_vertex(s_pose, a.cam.proj, wf, hf, r1.z, r1.w, r2.x);
+    v[3] = transform_vertex(s_pose, a.cam.proj, wf, hf, r2.y, r2.z, r2.w);
+    unsigned long long* keys = a.keys + (a.single ? 0 : (size_t)pose_i * W * H);
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+        const uint32_t perm = (perm2 >> (6 * j)) & 63u;
+        if (perm == kPermInvalid) continue;
+        const ScreenVertex A = pick(v, perm & 3u), B = pick(v, (perm >> 2) & 3u), C = pick(v, perm >> 4);
+        float bminx, bmaxx, bminy, bmaxy;
+        bbox_of(A, B, C, cmaxx, cmaxy, bminx, bmaxx, bminy, bmaxy);
+        const PixelRect r = pixel_rect_of(bminx, bmaxx, bminy, bmaxy, W, H);
+        if (r.x0 > r.x1 || r.r0 > r.r1) continue;
+        const int t = 2 * qi + j;  // triangle slot
+        const long long cells = (long long)(r.x1 - r.x0 + 1) * (r.r1 - r.r0 + 1);
+        if (cells > a.big_cells) {
+            const int slot = atomicAdd(a.big_count, 1);
+            if (slot < a.big_cap) {
+                a.big_list[slot] = make_int2(pose_i, t | (int)(perm << 26));
+                continue;
+            }
+            // list full: rasterise it here after all (slow, correct)
+        }
+        TriSetup ts;
+        setup_edges(A, B, C, ts);
+        const uint32_t id = a.key_pose_id ? (uint32_t)pose_i : (uint32_t)__ldg(a.models.cl_orig + t);
+        for (int p1 = r.r0; p1 <= r.r1; ++p1) {
+            unsigned long long* row = keys + (size_t)(H - 1 - p1) * W;  // image_renderer.cuh:127-128
+            for (int p0 = r.x0; p0 <= r.x1; ++p0) {
+                int32_t d;
+                if (fragment_depth(ts, (float)p0, (float)p1, d)) atomicMin(row + p0, make_key(d, id));
+            }
+        }
+    }
+}
+
+// One WARP per deferred triangle: the same arithmetic, pixels of the bbox spread over the lanes.
+__global__ void __launch_bounds__(kBigThreads) raster_big_kernel(FullRasterArgs a) {
+    const int n_big = min(*a.big_count, a.big_cap);
+    const int lane = threadIdx.x & 31, warps = gridDim.x * (kBigThreads / 32);
+    for (int e = blockIdx.x * (kBigThreads / 32) + (threadIdx.x >> 5); e < n_big; e += warps) {
+        const int2 item = a.big_list[e];
+        const int pose_i = item.x, t = item.y & ((1 << 26) - 1);
+        const uint32_t perm = (uint32_t)item.y >> 26;
+        const Mat4 pose = a.poses[pose_i];
+        const int W = a.cam.width, H = a.cam.height;
+        const float wf = (float)W, hf = (float)H;
+        const float4* rec = reinterpret_cast<const float4*>(a.models.cl_recs + (int64_t)(t >> 1) * kQuadFloats);
+        const float4 r0 = __ldg(rec), r1 = __ldg(rec + 1), r2 = __ldg(rec + 2);
+        ScreenVertex v[4];
+        v[0] = transform_vertex(pose, a.cam.proj, wf, hf, r0.x, r0.y, r0.z);
+        v[1] = transform_vertex(pose, a.cam.proj, wf, hf, r0.w, r1.x, r1.y);
+        v[2] = transform_vertex(pose, a.cam.proj, wf, hf, r1.z, r1.w, r2.x);
+        v[3] = transform_vertex(pose, a.cam.proj, wf, hf, r2.y, r2.z, r2.w);
+        const ScreenVertex A = pick(v, perm & 3u), B = pick(v, (perm >> 2) & 3u), C = pick(v, perm >> 4);
+        float bminx, bmaxx, bminy, bmaxy;
+        bbox_of(A, B, C, (float)(W - 1), (float)(H - 1), bminx, bmaxx, bminy, bmaxy);
+        const PixelRect r = pixel_rect_of(bminx, bmaxx, bminy, bmaxy, W, H);
+        if (r.x0 > r.x1 || r.r0 > r.r1) continue;
+        TriSetup ts;
+        setup_edges(A, B, C, ts);
+        const uint32_t id = a.key_pose_id ? (uint32_t)pose_i : (uint32_t)__ldg(a.models.cl_orig + t);
+        unsigned long long* keys = a.keys + (a.single ? 0 : (size_t)pose_i * W * H);
+        const int w = r.x1 - r.x0 + 1;
+        const int cells = w * (r.r1 - r.r0 + 1);  // <= W*H
+        for (int c = lane; c < cells; c += 32) {
+            const int p1 = r.r0 + c / w, p0 = r.x0 + c % w;
+            int32_t d;
+            if (fragment_depth(ts, (float)p0, (float)p1, d)) atomicMin(keys + (size_t)(H - 1 - p1) * W + p0, make_key(d, id));
+        }
+    }
+}
+
+// keys -> images, four pixels per thread.  grid.y = image.
+__global__ void __launch_bounds__(256) resolve_full_kernel(FullRasterArgs a) {
+    const int W = a.cam.width, H = a.cam.height, npx = W * H;
+    const int img = blockIdx.y;
+    const bool use_label = a.pose_label != nullptr;
+    const int pose_label = use_label ? a.pose_label[img] : 0;  // single-image mode resolves image 0 with label 0's entry
+    unsigned long long* keys = a.keys + (size_t)img * npx;
+    int flags = 0, clutter = 0, total = 0;
+    for (int g = blockIdx.x * blockDim.x + threadIdx.x; g < (npx + 3) / 4; g += gridDim.x * blockDim.x) {
+        int32_t d4[4] = {0, 0, 0, 0};
+        uint32_t r4 = 0, g4 = 0, b4 = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int i = 4 * g + k;
+            if (i >= npx) break;
+            const unsigned long long key = keys[i];
+            if (key == ~0ull) continue;
+            if (a.reset_keys) keys[i] = ~0ull;
+            int32_t d = (int32_t)((uint32_t)(key >> 32) ^ 0x80000000u);
+            const int32_t src = __ldg(a.scene.depth + i);
+            const int src_label = (use_label && a.scene.label) ? (int)__ldg(a.scene.label + i) : 0;
+            if (a.tree_total) {
+                // image_renderer.cuh:163-206 on the pixel's minimum depth (see pose_kernels.cu / DESIGN 4.11)
+                ++total;
+                const int ad = abs(d - src);
+                const bool gate = use_label ? (pose_label != src_label - 1 && ad >= 1) : ((float)ad > a.occlusion_threshold);
+                if (gate && src > 0) {
+                    if (d > src) { flags |= 2; ++clutter; }
+                    else flags |= 1;
+                }
+            }
+            uint32_t rgb = 0;
+            if (source_occludes(d, src, use_label, pose_label, src_label, a.occlusion_threshold)) d = 0;
+            else rgb = __ldg(a.models.tri_color + (uint32_t)key);
+            if (d == INT_MAX) d = 0;  // max2zero (image_renderer.cuh:324-333,465-466)
+            d4[k] = d;
+            r4 |= (rgb & 0xFFu) << (8 * k);
+            g4 |= ((rgb >> 8) & 0xFFu) << (8 * k);
+            b4 |= ((rgb >> 16) & 0xFFu) << (8 * k);
+        }
+        if (a.img_depth) {
+            const size_t o = (size_t)img * npx + 4 * (size_t)g;
+            if (4 * g + 3 < npx && a.wide_stores) {
+                *reinterpret_cast<int4*>(a.img_depth + o) = make_int4(d4[0], d4[1], d4[2], d4[3]);
+                if (a.img_r) {
+                    *reinterpret_cast<uint32_t*>(a.img_r + o) = r4;
+                    *reinterpret_cast<uint32_t*>(a.img_g + o) = g4;
+                    *reinterpret_cast<uint32_t*>(a.img_b + o) = b4;
+                }
+            } else {
+                for (int k = 0; k < 4 && 4 * g + k < npx; ++k) {
+                    a.img_depth[o + k] = d4[k];
+                    if (a.img_r) {
+                        a.img_r[o + k] = (uint8_t)(r4 >> (8 * k)); a.img_g[o + k] = (uint8_t)(g4 >> (8 * k));
+                        a.img_b[o + k] = (uint8_t)(b4 >> (8 * k));
+                    }
+                }
+            }
+        }
+    }
+    if (a.tree_total) {
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) {
+            flags |= __shfl_xor_sync(0xffffffffu, flags, o);
+            clutter += __shfl_xor_sync(0xffffffffu, clutter, o);
+            total += __shfl_xor_sync(0xffffffffu, total, o);
+        }
+        if ((threadIdx.x & 31) == 0) {
+            if (flags) atomicOr(a.tree_acc + 3 * img, flags);
+            if (clutter) atomicAdd(a.tree_acc + 3 * img + 1, clutter);
+            if (total) atomicAdd(a.tree_acc + 3 * img + 2, total);
+        }
+    }
+}
+
+__global__ void tree_finish_kernel(FullRasterArgs a) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= a.n_poses) return;
+    const int flags = a.tree_acc[3 * p];
+    const float clutter = (float)a.tree_acc[3 * p + 1], total = (float)a.tree_acc[3 * p + 2];
+    if (a.tree_occluded) a.tree_occluded[p] = flags & 1;
+    if (a.tree_occluded_other) a.tree_occluded_other[p] = (flags >> 1) & 1;
+    // thrust::divides then multiplies by 100 (image_renderer.cuh:467-482); 0/0 = NaN like the reference
+    if (a.tree_clutter) a.tree_clutter[p] = __fmul_rn(__fdiv_rn(clutter, total), 100.f);
+    a.tree_total[p] = total;
+}
+
+}  // namespace
+
+cudaError_t launch_full_raster(const FullRasterArgs& a, int max_model_quads, cudaStream_t stream) {
+    if (a.n_poses <= 0 || max_model_quads <= 0) return cudaSuccess;
+    cudaError_t e = cudaMemsetAsync(a.big_count, 0, sizeof(int), stream);
+    if (e != cudaSuccess) return e;
+    dim3 grid((max_model_quads + kFullThreads - 1) / kFullThreads, a.n_poses);
+    raster_quads_kernel<<<grid, kFullThreads, 0, stream>>>(a);
+    raster_big_kernel<<<a.big_ctas, kBigThreads, 0, stream>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_full_resolve(const FullRasterArgs& a, int n_images, cudaStream_t stream) {
+    if (n_images <= 0) return cudaSuccess;
+    const int npx = a.cam.width * a.cam.height;
+    if (a.tree_total) {
+        cudaError_t e = cudaMemsetAsync(a.tree_acc, 0, 3 * sizeof(int) * (size_t)n_images, stream);
+        if (e != cudaSuccess) return e;
+    }
+    dim3 grid(std::min(((npx + 3) / 4 + 255) / 256, 1200), n_images);
+    resolve_full_kernel<<<grid, 256, 0, stream>>>(a);
+    if (a.tree_total) tree_finish_kernel<<<(a.n_poses + 127) / 128, 128, 0, stream>>>(a);
+    return cudaGetLastError();
+}
+
+namespace {
+
+int env_or(const char* name, int dflt) {
+    const char* v = getenv(name);
+    return (v && *v) ? atoi(v) : dflt;
+}
+
+constexpr int kBigCap = 1 << 20;
+
+}  // namespace
+
+cudaError_t full_raster_job(::perch_ctx* c, const FullJob& j, int* launches) {
+    if (j.n_poses <= 0) return cudaSuccess;
+    cudaError_t e;
+    const size_t npx = (size_t)c->cam.width * c->cam.height;
+    if (!c->d_full_big) {
+        if ((e = cudaMalloc(&c->d_full_big, sizeof(int2) * (size_t)kBigCap)) != cudaSuccess) return e;
+        if ((e = cudaMalloc(&c->d_full_count, sizeof(int))) != cudaSuccess) return e;
+    }
+    FullRasterArgs a;
+    a.models = c->models; a.cam = c->cam; a.scene = c->scene;
+    a.occlusion_threshold = j.occlusion_threshold;
+    a.key_pose_id = j.key_pose_id;
+    a.big_list = c->d_full_big; a.big_count = c->d_full_count; a.big_cap = kBigCap;
+    a.big_ctas = 4 * c->sm_count;
+    a.big_cells = std::max(env_or("PERCH_FULL_BIG_CELLS", 64), 1);
+    if (j.single_keys) {
+        a.poses = j.poses; a.pose_model_map = j.pose_model_map; a.pose_label = j.pose_label; a.n_poses = j.n_poses;
+        a.keys = j.single_keys; a.single = 1;
+        if (launches) *launches += 2;
+        return launch_full_raster(a, c->max_model_quads, c->stream);
+    }
+    // chunk of poses whose key images fit the budget (default: half of the 126 MB L2, so that the z-test atomics and the
+    // resolve pass's key reads stay on chip and HBM sees only the output images)
+    const size_t budget = (size_t)std::max(env_or("PERCH_FULL_CHUNK_MB", 64), 1) << 20;
+    const size_t chunk = std::min<size_t>(std::max<size_t>(budget / (npx * 8), 1), (size_t)j.n_poses);
+    if (c->full_keys_n < chunk * npx) {
+        if (c->d_full_keys) cudaFree(c->d_full_keys);
+        c->d_full_keys = nullptr; c->full_keys_n = 0;
+        if ((e = cudaMalloc(&c->d_full_keys, chunk * npx * 8)) != cudaSuccess) return e;
+        if ((e = cudaMemsetAsync(c->d_full_keys, 0xFF, chunk * npx * 8, c->stream)) != cudaSuccess) return e;
+        c->full_keys_n = chunk * npx;
+    }
+    if (j.tree_total && c->full_acc_n < 3 * (size_t)j.n_poses) {
+        if (c->d_full_acc) cudaFree(c->d_full_acc);
+        c->d_full_acc = nullptr; c->full_acc_n = 0;
+        if ((e = cudaMalloc(&c->d_full_acc, 3 * sizeof(int) * (size_t)j.n_poses)) != cudaSuccess) return e;
+        c->full_acc_n = 3 * (size_t)j.n_poses;
+    }
+    a.keys = c->d_full_keys;
+    a.reset_keys = 1;
+    auto aligned = [](const void* p, uintptr_t m) { return (reinterpret_cast<uintptr_t>(p) & (m - 1)) == 0; };
+    a.wide_stores = npx % 4 == 0 && aligned(j.img_depth, 16) && aligned(j.img_r, 4) && aligned(j.img_g, 4) && aligned(j.img_b, 4);
+    for (size_t p0 = 0; p0 < (size_t)j.n_poses; p0 += chunk) {
+        const int n = (int)std::min(chunk, (size_t)j.n_poses - p0);
+        a.poses = j.poses + p0; a.pose_model_map = j.pose_model_map + p0;
+        a.pose_label = j.pose_label ? j.pose_label + p0 : nullptr;
+        a.n_poses = n;
+        a.img_depth = j.img_depth ? j.img_depth + p0 * npx : nullptr;
+        a.img_r = j.img_r ? j.img_r + p0 * npx : nullptr;
+        a.img_g = j.img_g ? j.img_g + p0 * npx : nullptr;
+        a.img_b = j.img_b ? j.img_b + p0 * npx : nullptr;
+        a.tree_occluded = j.tree_occluded ? j.tree_occluded + p0 : nullptr;
+        a.tree_occluded_other = j.tree_occluded_other ? j.tree_occluded_other + p0 : nullptr;
+        a.tree_clutter = j.tree_clutter ? j.tree_clutter + p0 : nullptr;
+        a.tree_total = j.tree_total ? j.tree_total + p0 : nullptr;
+        a.tree_acc = j.tree_total ? c->d_full_acc + 3 * p0 : nullptr;
+        if ((e = launch_full_raster(a, c->max_model_quads, c->stream)) == cudaSuccess) e = launch_full_resolve(a, n, c->stream);
+        if (e != cudaSuccess) {
+            cudaFree(c->d_full_keys);  // the keys may be dirty: start from a fresh, cleared buffer next time
+            c->d_full_keys = nullptr; c->full_keys_n = 0;
+            return e;
+        }
+        if (launches) *launches += 3 + (j.tree_total ? 1 : 0);
+    }
+    return cudaSuccess;
+}
+
+}  // namespace perch
