@@ -20,6 +20,13 @@ $(LIB): $(OBJS)
 	$(NVCC) $(ARCH) -shared -o $@ $(OBJS)
 
 # Debug variant with per-level survivor counters in the per-pose kernel (tools/pose_stats.py); never the product.
+# A/B build of the per-pose kernel with extra -D switches: make variant VARIANT_FLAGS=-DFOO VARIANT=foo
+#   -> perception_b200/_ab/libperch_$(VARIANT).so (tools/ab_cost.py)
+variant: $(OBJS)
+	mkdir -p perception_b200/_ab
+	$(NVCC) $(NVFLAGS) $(VARIANT_FLAGS) -c $(CSRC)/pose_kernels.cu -o $(CSRC)/pose_kernels_variant.o
+	$(NVCC) $(ARCH) -shared -o perception_b200/_ab/libperch_$(VARIANT).so $(CSRC)/pose_kernels_variant.o $(filter-out $(CSRC)/pose_kernels.o,$(OBJS))
+
 stats: $(OBJS)
 	$(NVCC) $(NVFLAGS) -DPERCH_STATS -c $(CSRC)/pose_kernels.cu -o $(CSRC)/pose_kernels_stats.o
 	$(NVCC) $(ARCH) -shared -o perception_b200/libperch_b200_stats.so $(CSRC)/pose_kernels_stats.o $(filter-out $(CSRC)/pose_kernels.o,$(OBJS))

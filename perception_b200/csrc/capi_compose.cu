@@ -182,7 +182,9 @@ int perch_tree_flags(perch_ctx* c, const float* poses16, int n_poses, const int*
     if (pose_occluded_other) PERCH_CU(cudaMemcpyAsync(pose_occluded_other, d_other, P * 4, cudaMemcpyDeviceToHost, c->stream));
     if (clutter_cost) PERCH_CU(cudaMemcpyAsync(clutter_cost, d_clutter, P * 4, cudaMemcpyDeviceToHost, c->stream));
     if (total_points) PERCH_CU(cudaMemcpyAsync(total_points, d_total, P * 4, cudaMemcpyDeviceToHost, c->stream));
-    return check_err_flag(c);
+    rc = check_err_flag(c);  // synchronises the stream
+    if (c->timing_pending && cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1) == cudaSuccess) c->timing_pending = false;
+    return rc;
 }
 
 int perch_get_source_label(perch_ctx* c, uint8_t* out_label, int* has_label) {

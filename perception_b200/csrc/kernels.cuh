@@ -76,7 +76,8 @@ struct FullRasterArgs {
     int* big_count = nullptr;
     int big_cap = 0;
     int big_ctas = 0;
-    int big_cells = 64;                     // bbox pixels above which a triangle is deferred to the warp-per-triangle kernel
+    int big_cells = 4096;                   // bbox pixels above which a triangle is deferred to the warp-per-triangle kernel
+    int lane_cells = 16;                    // bbox pixels up to which a lane walks its own triangle (above: the whole warp)
     // resolve outputs: n_poses x W*H images (any may be null), and the per-pose vectors of PoseArgs::tree_*
     int32_t* img_depth = nullptr;
     uint8_t* img_r = nullptr;

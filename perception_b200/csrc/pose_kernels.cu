@@ -125,16 +125,14 @@ constexpr int kSlotMask = (1 << kSlotBits) - 1;
 __device__ __forceinline__ void load_tri(const ModelsDev& m, int entry, float v[9]) {
     const int t = entry & kSlotMask;
     const uint32_t perm = (uint32_t)entry >> kSlotBits;
-    // the whole quad with three 16-byte loads, then the triangle's three vertices by selects (no dependent address)
-    const float4* rec = reinterpret_cast<const float4*>(m.cl_recs + (int64_t)(t >> 1) * kQuadFloats);
-    const float4 r0 = __ldg(rec), r1 = __ldg(rec + 1), r2 = __ldg(rec + 2);
-    const float qx[4] = {r0.x, r0.w, r1.z, r2.y}, qy[4] = {r0.y, r1.x, r1.w, r2.z}, qz[4] = {r0.z, r1.y, r2.x, r2.w};
+    // nine 4-byte loads at perm-dependent offsets.  (Three 16-byte loads of the whole quad + selects measured slower:
+    // the exact path is issue-bound and the 27 selects cost more than the loads save: C3 1.93 -> 1.71 ms, C2 1.585 ->
+    // 1.509 ms with this form; the level-2 test, which uses all twelve floats, keeps the 16-byte loads.)
+    const float* base = m.cl_recs + (int64_t)(t >> 1) * kQuadFloats;
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
-        const uint32_t i = (perm >> (2 * k)) & 3u;
-        v[3 * k] = i == 0 ? qx[0] : i == 1 ? qx[1] : i == 2 ? qx[2] : qx[3];
-        v[3 * k + 1] = i == 0 ? qy[0] : i == 1 ? qy[1] : i == 2 ? qy[2] : qy[3];
-        v[3 * k + 2] = i == 0 ? qz[0] : i == 1 ? qz[1] : i == 2 ? qz[2] : qz[3];
+        const float* p = base + 3 * ((perm >> (2 * k)) & 3u);
+        v[3 * k] = __ldg(p); v[3 * k + 1] = __ldg(p + 1); v[3 * k + 2] = __ldg(p + 2);
     }
 }
 

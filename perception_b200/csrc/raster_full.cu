@@ -5,10 +5,12 @@
 // triangle reaches its exact path, and the 64-bit shared z-buffer leaves 3 CTAs per SM
 // (profiles/r1_render_kernel_v1.md: 8 % of the HBM write roofline).  Here the work is spread over (pose, 128 quads) CTAs
 // instead of one CTA per pose:
-//   raster_quads_kernel  one thread per quad: FOUR exact vertex transforms for two triangles, the reference's bbox loops
-//                        and fragment arithmetic (exact_math.cuh), z-test with a 64-bit atomicMin on an order-preserving
-//                        (depth, triangle) key image in global memory (L2-resident atomics);
-//   raster_big_kernel    triangles covering many pixels (a table plane), deferred by the first kernel, one CTA each;
+//   raster_quads_kernel  one thread per quad: FOUR exact vertex transforms for two triangles, the reference's bbox and
+//                        inside test (exact_math.cuh); pixels that pass are queued per warp and their perspective
+//                        depths (three IEEE divisions) computed with every lane busy; triangles of more than a few
+//                        pixels are walked by the whole warp; z-test with a 64-bit atomicMin on an order-preserving
+//                        (depth, triangle) key image in global memory (L2 atomics);
+//   raster_big_kernel    triangles covering thousands of pixels, deferred by the first kernel, one warp each;
 //   resolve_full_kernel  keys -> int32 depth + RGB with the source-occlusion rule, four pixels per thread (16-byte
 //                        stores), and optionally the per-pose vectors of the USE_TREE / USE_CLUTTER branches.
 // Canonical semantics as everywhere: minimum depth over fragments, lowest original triangle index
@@ -61,9 +63,66 @@ __device__ __forceinline__ ScreenVertex pick(const ScreenVertex v[4], uint32_t i
     return o;
 }
 
+// ---- fragments in two steps ------------------------------------------------------------------------------------------
+// The inside test (image_renderer.cuh:44-57,114-118) is cheap and fails for most bbox pixels of small triangles; the
+// perspective depth (three IEEE divisions, 119-129) is expensive.  Lanes run the test on their own triangles and queue
+// the few pixels that pass; the warp then computes the depths with every lane busy.  Same operations on the same values
+// as fragment_depth (exact_math.cuh), only regrouped.
+constexpr int kFragCap = 128;  // queue entries per warp; drained when fewer than 32 are free
+
+struct FragQueue {  // SoA, one per warp
+    float beta[kFragCap], gamma[kFragCap], z0[kFragCap], z1[kFragCap], z2[kFragCap];
+    uint32_t pixel[kFragCap], id[kFragCap];
+};
+
+__device__ __forceinline__ bool inside_test(const TriSetup& t, float P0f, float P1f, float& beta, float& gamma) {
+    const float dy = __fsub_rn(P1f, t.A1);
+    const float r0 = __fmul_rn(t.e_c0, dy);
+    const float r1 = __fmul_rn(dy, t.e_b0);
+    const float dx = __fsub_rn(P0f, t.A0);
+    beta = __fmul_rn(t.base_inv, __fmul_rn(__fmaf_rn(t.e_c1, -dx, r0), 0.5f));
+    gamma = __fmul_rn(t.base_inv, __fmul_rn(__fmaf_rn(t.e_b1, dx, -r1), 0.5f));
+    const float alpha = __fsub_rn(__fsub_rn(1.0f, beta), gamma);
+    const float mn = fminf(gamma, fminf(beta, alpha));
+    const float mx = fmaxf(fmaxf(alpha, beta), gamma);
+    return !(mn < 0.0f || mx > 1.0f);
+}
+
+__device__ __forceinline__ void drain(FragQueue& q, int count, int lane, unsigned long long* keys) {
+    __syncwarp();
+    for (int e = lane; e < count; e += 32) {
+        const float beta = q.beta[e], gamma = q.gamma[e];
+        const float alpha = __fsub_rn(__fsub_rn(1.0f, beta), gamma);
+        const float num = __fadd_rn(gamma, __fadd_rn(beta, alpha));
+        const float den = __fadd_rn(__fdiv_rn(gamma, q.z2[e]), __fadd_rn(__fdiv_rn(beta, q.z1[e]), __fdiv_rn(alpha, q.z0[e])));
+        const int32_t d = (int32_t)__fadd_rn(__fdiv_rn(num, den), 0.5f);
+        atomicMin(keys + q.pixel[e], make_key(d, q.id[e]));
+    }
+    __syncwarp();
+}
+
+// Warp-uniform call: lanes with `inside` append their fragment; returns the new (uniform) count.
+__device__ __forceinline__ int append(FragQueue& q, int count, int lane, bool inside, float beta, float gamma,
+                                      const TriSetup& t, uint32_t pixel, uint32_t id, unsigned long long* keys) {
+    const unsigned m = __ballot_sync(0xffffffffu, inside);
+    if (m == 0) return count;
+    if (inside) {
+        const int s = count + __popc(m & ((1u << lane) - 1u));
+        q.beta[s] = beta; q.gamma[s] = gamma; q.z0[s] = t.z0; q.z1[s] = t.z1; q.z2[s] = t.z2;
+        q.pixel[s] = pixel; q.id[s] = id;
+    }
+    count += __popc(m);
+    if (count > kFragCap - 32) {
+        drain(q, count, lane, keys);
+        count = 0;
+    }
+    return count;
+}
+
 __global__ void __launch_bounds__(kFullThreads) raster_quads_kernel(FullRasterArgs a) {
     __shared__ Mat4 s_pose;
-    const int pose_i = blockIdx.y, tid = threadIdx.x;
+    __shared__ FragQueue s_queue[kFullThreads / 32];
+    const int pose_i = blockIdx.y, tid = threadIdx.x, lane = tid & 31;
     const int model = a.pose_model_map[pose_i];
     if (model < 0 || model >= a.models.n_models) return;
     const int q_low = 2 * a.models.cl_low[model], q_high = 2 * a.models.cl_high[model];
@@ -71,49 +130,97 @@ __global__ void __launch_bounds__(kFullThreads) raster_quads_kernel(FullRasterAr
     if (tid < 16) reinterpret_cast<float*>(&s_pose)[tid] = reinterpret_cast<const float*>(a.poses + pose_i)[tid];
     __syncthreads();
     const int qi = q_low + blockIdx.x * kFullThreads + tid;
-    if (qi >= q_high) return;
-    const uint32_t perm2 = (__ldg(a.models.cl_perm + (qi >> 1)) >> (12 * (qi & 1))) & 0xFFFu;
-    if ((perm2 & 63u) == kPermInvalid && (perm2 >> 6) == kPermInvalid) return;
     const int W = a.cam.width, H = a.cam.height;
-    const float wf = (float)W, hf = (float)H, cmaxx = (float)(W - 1), cmaxy = (float)(H - 1);
-    const float4* rec = reinterpret_cast<const float4*>(a.models.cl_recs + (int64_t)qi * kQuadFloats);
-    const float4 r0 = __ldg(rec), r1 = __ldg(rec + 1), r2 = __ldg(rec + 2);
-    ScreenVertex v[4];
-    v[0] = transform_vertex(s_pose, a.cam.proj, wf, hf, r0.x, r0.y, r0.z);
-    v[1] = transform_vertex(s_pose, a.cam.proj, wf, hf, r0.w, r1.x, r1.y);
-    v[2] = transform_vertex(s_pose, a.cam.proj, wf, hf, r1.z, r1.w, r2.x);
-    v[3] = transform_vertex(s_pose, a.cam.proj, wf, hf, r2.y, r2.z, r2.w);
     unsigned long long* keys = a.keys + (a.single ? 0 : (size_t)pose_i * W * H);
+    FragQueue& q = s_queue[tid >> 5];
+    int cells[2] = {0, 0};  // bbox pixels of the lane's two triangles (0: nothing to draw, or deferred)
+    PixelRect rect[2];
+    TriSetup ts[2];
+    uint32_t id[2] = {0, 0};
+    if (qi < q_high) {
+        const uint32_t perm2 = (__ldg(a.models.cl_perm + (qi >> 1)) >> (12 * (qi & 1))) & 0xFFFu;
+        const float wf = (float)W, hf = (float)H, cmaxx = (float)(W - 1), cmaxy = (float)(H - 1);
+        const float4* rec = reinterpret_cast<const float4*>(a.models.cl_recs + (int64_t)qi * kQuadFloats);
+        const float4 r0 = __ldg(rec), r1 = __ldg(rec + 1), r2 = __ldg(rec + 2);
+        ScreenVertex v[4];
+        v[0] = transform_vertex(s_pose, a.cam.proj, wf, hf, r0.x, r0.y, r0.z);
+        v[1] = transform_vertex(s_pose, a.cam.proj, wf, hf, r0.w, r1.x, r1.y);
+        v[2] = transform_vertex(s_pose, a.cam.proj, wf, hf, r1.z, r1.w, r2.x);
+        v[3] = transform_vertex(s_pose, a.cam.proj, wf, hf, r2.y, r2.z, r2.w);
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const uint32_t perm = (perm2 >> (6 * j)) & 63u;
+            if (perm == kPermInvalid) continue;
+            const ScreenVertex A = pick(v, perm & 3u), B = pick(v, (perm >> 2) & 3u), C = pick(v, perm >> 4);
+            float bminx, bmaxx, bminy, bmaxy;
+            bbox_of(A, B, C, cmaxx, cmaxy, bminx, bmaxx, bminy, bmaxy);
+            rect[j] = pixel_rect_of(bminx, bmaxx, bminy, bmaxy, W, H);
+            if (rect[j].x0 > rect[j].x1 || rect[j].r0 > rect[j].r1) continue;
+            const int t = 2 * qi + j;  // triangle slot
+            const long long n = (long long)(rect[j].x1 - rect[j].x0 + 1) * (rect[j].r1 - rect[j].r0 + 1);
+            if (n > a.big_cells) {
+                const int slot = atomicAdd(a.big_count, 1);
+                if (slot < a.big_cap) {
+                    a.big_list[slot] = make_int2(pose_i, t | (int)(perm << 26));
+                    continue;
+                }
+                // list full: the warp rasterises it below after all (slow for a huge triangle, correct)
+            }
+            setup_edges(A, B, C, ts[j]);
+            id[j] = a.key_pose_id ? (uint32_t)pose_i : (uint32_t)__ldg(a.models.cl_orig + t);
+            cells[j] = (int)(n > 0x7fffffffLL ? 0x7fffffffLL : n);  // W*H <= 2^26 (perch_set_camera)
+        }
+    }
+    int count = 0;
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
-        const uint32_t perm = (perm2 >> (6 * j)) & 63u;
-        if (perm == kPermInvalid) continue;
-        const ScreenVertex A = pick(v, perm & 3u), B = pick(v, (perm >> 2) & 3u), C = pick(v, perm >> 4);
-        float bminx, bmaxx, bminy, bmaxy;
-        bbox_of(A, B, C, cmaxx, cmaxy, bminx, bmaxx, bminy, bmaxy);
-        const PixelRect r = pixel_rect_of(bminx, bmaxx, bminy, bmaxy, W, H);
-        if (r.x0 > r.x1 || r.r0 > r.r1) continue;
-        const int t = 2 * qi + j;  // triangle slot
-        const long long cells = (long long)(r.x1 - r.x0 + 1) * (r.r1 - r.r0 + 1);
-        if (cells > a.big_cells) {
-            const int slot = atomicAdd(a.big_count, 1);
-            if (slot < a.big_cap) {
-                a.big_list[slot] = make_int2(pose_i, t | (int)(perm << 26));
-                continue;
+        // (1) triangles of a few pixels: every lane walks its own bbox
+        const int mine = cells[j] <= a.lane_cells ? cells[j] : 0;
+        const int trips = __reduce_max_sync(0xffffffffu, mine);
+        int p0 = rect[j].x0, p1 = rect[j].r0;
+        for (int it = 0; it < trips; ++it) {
+            float beta = 0.f, gamma = 0.f;
+            bool in = false;
+            uint32_t pixel = 0;
+            if (it < mine) {
+                in = inside_test(ts[j], (float)p0, (float)p1, beta, gamma);
+                pixel = (uint32_t)((H - 1 - p1) * W + p0);  // image_renderer.cuh:127-128
+                if (++p0 > rect[j].x1) { p0 = rect[j].x0; ++p1; }
             }
-            // list full: rasterise it here after all (slow, correct)
+            count = append(q, count, lane, in, beta, gamma, ts[j], pixel, id[j], keys);
         }
-        TriSetup ts;
-        setup_edges(A, B, C, ts);
-        const uint32_t id = a.key_pose_id ? (uint32_t)pose_i : (uint32_t)__ldg(a.models.cl_orig + t);
-        for (int p1 = r.r0; p1 <= r.r1; ++p1) {
-            unsigned long long* row = keys + (size_t)(H - 1 - p1) * W;  // image_renderer.cuh:127-128
-            for (int p0 = r.x0; p0 <= r.x1; ++p0) {
-                int32_t d;
-                if (fragment_depth(ts, (float)p0, (float)p1, d)) atomicMin(row + p0, make_key(d, id));
+        // (2) larger ones: the warp takes them one at a time, 32 pixels per step
+        unsigned todo = __ballot_sync(0xffffffffu, cells[j] > a.lane_cells);
+        while (todo) {
+            const int src = __ffs(todo) - 1;
+            todo &= todo - 1;
+            TriSetup t;
+            t.A0 = __shfl_sync(0xffffffffu, ts[j].A0, src); t.A1 = __shfl_sync(0xffffffffu, ts[j].A1, src);
+            t.e_c0 = __shfl_sync(0xffffffffu, ts[j].e_c0, src); t.e_b1 = __shfl_sync(0xffffffffu, ts[j].e_b1, src);
+            t.e_b0 = __shfl_sync(0xffffffffu, ts[j].e_b0, src); t.e_c1 = __shfl_sync(0xffffffffu, ts[j].e_c1, src);
+            t.base_inv = __shfl_sync(0xffffffffu, ts[j].base_inv, src);
+            t.z0 = __shfl_sync(0xffffffffu, ts[j].z0, src); t.z1 = __shfl_sync(0xffffffffu, ts[j].z1, src);
+            t.z2 = __shfl_sync(0xffffffffu, ts[j].z2, src);
+            const int x0 = __shfl_sync(0xffffffffu, rect[j].x0, src), x1 = __shfl_sync(0xffffffffu, rect[j].x1, src);
+            const int r0 = __shfl_sync(0xffffffffu, rect[j].r0, src);
+            const int n = __shfl_sync(0xffffffffu, cells[j], src);
+            const uint32_t tid_ = __shfl_sync(0xffffffffu, id[j], src);
+            const int w = x1 - x0 + 1;
+            for (int c0 = 0; c0 < n; c0 += 32) {
+                const int c = c0 + lane;
+                float beta = 0.f, gamma = 0.f;
+                bool in = false;
+                uint32_t pixel = 0;
+                if (c < n) {
+                    const int row = c / w, px = x0 + (c - row * w), py = r0 + row;
+                    in = inside_test(t, (float)px, (float)py, beta, gamma);
+                    pixel = (uint32_t)((H - 1 - py) * W + px);
+                }
+                count = append(q, count, lane, in, beta, gamma, t, pixel, tid_, keys);
             }
         }
     }
+    drain(q, count, lane, keys);
 }
 
 // One WARP per deferred triangle: the same arithmetic, pixels of the bbox spread over the lanes.
@@ -290,17 +397,18 @@ cudaError_t full_raster_job(::perch_ctx* c, const FullJob& j, int* launches) {
     a.key_pose_id = j.key_pose_id;
     a.big_list = c->d_full_big; a.big_count = c->d_full_count; a.big_cap = kBigCap;
     a.big_ctas = 4 * c->sm_count;
-    a.big_cells = std::max(env_or("PERCH_FULL_BIG_CELLS", 64), 1);
+    a.big_cells = std::max(env_or("PERCH_FULL_BIG_CELLS", 4096), 1);
+    a.lane_cells = std::max(env_or("PERCH_FULL_LANE_CELLS", 16), 0);
     if (j.single_keys) {
         a.poses = j.poses; a.pose_model_map = j.pose_model_map; a.pose_label = j.pose_label; a.n_poses = j.n_poses;
         a.keys = j.single_keys; a.single = 1;
         if (launches) *launches += 2;
         return launch_full_raster(a, c->max_model_quads, c->stream);
     }
-    // chunk of poses whose key images fit the budget (default: half of the 126 MB L2, so that the z-test atomics and the
-    // resolve pass's key reads stay on chip and HBM sees only the output images)
-    const size_t budget = (size_t)std::max(env_or("PERCH_FULL_CHUNK_MB", 64), 1) << 20;
-    const size_t chunk = std::min<size_t>(std::max<size_t>(budget / (npx * 8), 1), (size_t)j.n_poses);
+    // chunk of poses whose key images fit the budget.  Measured on 1024 poses of the C2 mesh (tools/render_probe.py):
+    // 16 MB 5.7 ms, 32 MB 3.2 ms, 64 MB 2.5 ms, 128 MB 2.1 ms, 256 MB 1.8 ms -- few large launches beat L2 residency
+    const size_t budget = (size_t)std::max(env_or("PERCH_FULL_CHUNK_MB", 256), 1) << 20;
+    const size_t chunk = std::min<size_t>({std::max<size_t>(budget / (npx * 8), 1), (size_t)j.n_poses, (size_t)65535});  // grid.y
     if (c->full_keys_n < chunk * npx) {
         if (c->d_full_keys) cudaFree(c->d_full_keys);
         c->d_full_keys = nullptr; c->full_keys_n = 0;

@@ -47,7 +47,9 @@ if len(sys.argv) > 2:  # one variant only (profiling): python tools/render_probe
 base = run("legacy", PERCH_IMAGE_LEGACY=1)
 new = run("full")
 print("bit-equal:", all(np.array_equal(base[k], new[k]) for k in ("result_depth", "result_color")))
-for mb in (16, 32, 128, 256):
+for mb in (64, 128, 512):
     run(f"chunk{mb}", PERCH_FULL_CHUNK_MB=mb)
-for cells in (16, 32, 128, 512):
+for cells in (4, 8, 32, 64):
+    run(f"lane{cells}", PERCH_FULL_LANE_CELLS=cells)
+for cells in (256, 1024, 65536):
     run(f"big{cells}", PERCH_FULL_BIG_CELLS=cells)
