@@ -8,7 +8,8 @@
 A step = one pass of the hot path over one batch of candidate poses per GPU (workload C2 of BASELINE.json configs[1]:
 16 384 6-DoF poses of a 20 000-triangle mesh against a 640x480 scene, stride 8, label-restricted cost_type 2).
 `value` times the kernel with inputs resident in HBM (CUDA events on the library's stream, L2 flushed between steps);
-`e2e` times the public host API (pinned host poses in, costs + top-k out, NCCL gather of the per-GPU top-k for N > 1).
+`e2e` times the public host API (pinned host poses in, costs + top-k out, NCCL gather of the per-GPU top-k for N > 1);
+its steps are spread over --e2e-contexts contexts (default 2, one host thread each) so one step's copies overlap another's kernel.
 Prints ONE JSON line on rank 0.
 """
 from __future__ import annotations
@@ -181,7 +182,8 @@ def run_ours(args):
     import torch
     import torch.distributed as dist
     from perception_b200 import sharding
-    from perception_b200.renderer import topk
+    from perception_b200 import synth
+    from perception_b200.renderer import Renderer, topk
 
     rank, local_rank, world = rank_info()
     if world > 1:
@@ -231,18 +233,71 @@ def run_ours(args):
     K_TOP = 8
     exchange = sharding.HitExchange(1, K_TOP)
 
-    def e2e_step():
-        out = r.render_cuda_multi_unified("COST", h_poses, h_pmm, h_lab, h_tot, **kw)
-        hits = topk(out["rendered_cost"], out["observed_cost"], h_pmm, 1, k=K_TOP, pose_id_offset=rank * P)
-        best = sharding.merge_hits(exchange.gather(hits), K_TOP)[0, 0]  # all_gather of k x 16 B per rank
-        return out, best
+    # Every step is one call of the public API on pinned host buffers (H2D of the step's poses, kernel, D2H of its costs)
+    # followed by the host top-k.  A caller with many batches to score keeps the GPU busy by driving more than one
+    # context (each has its own stream) from its own host thread, so that one step's copies and host work overlap the
+    # other's kernel: --e2e-contexts (default 2) such contexts share the steps round-robin; the top-k gather across
+    # ranks stays on the main thread, in step order.
+    n_ctx = max(1, min(args.e2e_contexts, args.steps))
+    ctxs = [r]
+    for _ in range(n_ctx - 1):
+        r2 = Renderer(local_rank)
+        r2.set_camera(W, H, wl["proj"], synth.CX, synth.CY, synth.FX, synth.FY, synth.DEPTH_FACTOR)
+        r2.set_models(wl["scene"].tris, wl["scene"].tris_model_count)
+        r2.set_scene(wl["scene"].source_depth, wl["scene"].source_color, wl["scene"].source_label if wl["dof6"] else None)
+        r2.set_observed(wl["obs"]["result_cloud_eigen"], wl["obs"]["result_cloud_color"], wl["obs_label"])
+        ctxs.append(r2)
 
-    for _ in range(max(1, min(args.warmup, 3))):
-        out, best = e2e_step()
+    def score_step(rr):
+        out = rr.render_cuda_multi_unified("COST", h_poses, h_pmm, h_lab, h_tot, **kw)
+        return out, topk(out["rendered_cost"], out["observed_cost"], h_pmm, 1, k=K_TOP, pose_id_offset=rank * P)
+
+    def e2e_steps(n_steps):
+        """n_steps steps over the contexts; returns the last step's outputs and merged best hit."""
+        results = [None] * n_steps
+        done = [threading.Event() for _ in range(n_steps)]
+        errors = []
+
+        def worker(j):
+            try:
+                for i in range(j, n_steps, n_ctx):
+                    results[i] = score_step(ctxs[j])
+                    done[i].set()
+            except BaseException as e:  # noqa: BLE001
+                errors.append(e)
+                for d in done:
+                    d.set()
+
+        threads = [threading.Thread(target=worker, args=(j,)) for j in range(1, n_ctx)]
+        for t in threads:
+            t.start()
+        best = None
+        if n_ctx == 1:
+            for i in range(n_steps):
+                results[i] = score_step(r)
+                best = sharding.merge_hits(exchange.gather(results[i][1]), K_TOP)[0, 0]
+        else:
+            # the main thread drives context 0 and gathers finished steps in order (collectives stay ordered across ranks)
+            nxt = 0
+            for i in range(0, n_steps, n_ctx):
+                results[i] = score_step(r)
+                done[i].set()
+                while nxt < n_steps and done[nxt].is_set() and not errors:
+                    best = sharding.merge_hits(exchange.gather(results[nxt][1]), K_TOP)[0, 0]  # all_gather of k x 16 B per rank
+                    nxt += 1
+            for t in threads:
+                t.join()
+            if errors:
+                raise errors[0]
+            while nxt < n_steps:
+                best = sharding.merge_hits(exchange.gather(results[nxt][1]), K_TOP)[0, 0]
+                nxt += 1
+        return results[-1][0], best
+
+    out, best = e2e_steps(max(n_ctx, min(args.warmup, 3)))
     barrier()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        out, best = e2e_step()
+    out, best = e2e_steps(args.steps)
     barrier()
     e2e_s = time.perf_counter() - t0
     clocks = sampler.stop()
@@ -297,7 +352,8 @@ def run_ours(args):
                        "timing": "CUDA events on the library stream around the fused kernel, max over ranks"},
             "clocks": clocks,
             "e2e": {"value": world * P * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": int(P * (64 + 4 + 4 + (4 if h_lab is not None else 0))),
-                    "d2h_bytes_per_step": int(P * 24), "ms_per_scene": e2e_s / args.steps * 1e3},
+                    "d2h_bytes_per_step": int(P * 24), "ms_per_scene": e2e_s / args.steps * 1e3,
+                    "contexts": n_ctx},
             "gpu_launches": args.steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "peak_kind": f"{peak_kind} copy bandwidth", "bytes_per_pose": bpp,
@@ -641,6 +697,8 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--e2e-contexts", type=int, default=2,
+                    help="contexts (one host thread each) the e2e leg spreads its steps over; 1 = strictly serial calls")
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "reference-cuda"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
