@@ -237,7 +237,7 @@ def run_ours(args):
     # followed by the host top-k.  A caller with many batches to score keeps the GPU busy by driving more than one
     # context (each has its own stream) from its own host thread, so that one step's copies and host work overlap the
     # other's kernel: --e2e-contexts (default 2) such contexts share the steps round-robin; the top-k gather across
-    # ranks stays on the main thread, in step order.
+    # ranks runs on the main thread, in step order.
     n_ctx = max(1, min(args.e2e_contexts, args.steps))
     ctxs = [r]
     for _ in range(n_ctx - 1):
@@ -268,30 +268,21 @@ def run_ours(args):
                 for d in done:
                     d.set()
 
-        threads = [threading.Thread(target=worker, args=(j,)) for j in range(1, n_ctx)]
+        threads = [threading.Thread(target=worker, args=(j,)) for j in range(n_ctx)]
         for t in threads:
             t.start()
+        # the main thread gathers the finished steps in step order (collectives stay ordered across ranks) while the
+        # workers are already scoring the next ones
         best = None
-        if n_ctx == 1:
-            for i in range(n_steps):
-                results[i] = score_step(r)
-                best = sharding.merge_hits(exchange.gather(results[i][1]), K_TOP)[0, 0]
-        else:
-            # the main thread drives context 0 and gathers finished steps in order (collectives stay ordered across ranks)
-            nxt = 0
-            for i in range(0, n_steps, n_ctx):
-                results[i] = score_step(r)
-                done[i].set()
-                while nxt < n_steps and done[nxt].is_set() and not errors:
-                    best = sharding.merge_hits(exchange.gather(results[nxt][1]), K_TOP)[0, 0]  # all_gather of k x 16 B per rank
-                    nxt += 1
-            for t in threads:
-                t.join()
+        for i in range(n_steps):
+            done[i].wait()
             if errors:
-                raise errors[0]
-            while nxt < n_steps:
-                best = sharding.merge_hits(exchange.gather(results[nxt][1]), K_TOP)[0, 0]
-                nxt += 1
+                break
+            best = sharding.merge_hits(exchange.gather(results[i][1]), K_TOP)[0, 0]  # all_gather of k x 16 B per rank
+        for t in threads:
+            t.join()
+        if errors:
+            raise errors[0]
         return results[-1][0], best
 
     out, best = e2e_steps(max(n_ctx, min(args.warmup, 3)))
