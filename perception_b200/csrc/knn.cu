@@ -98,6 +98,122 @@ __global__ void __launch_bounds__(kKnnThreads) knn_fixed_kernel(const float* __r
     }
 }
 
+// k <= KMAX <= 16: the k best of a query live in REGISTERS (unrolled, predicated insertion: no memory traffic, no
+// dependent global loads while a warp waits on the one lane that found a closer point) and are written out once, sorted.
+// Same insertion rule as knn_insert, element by element: entry `pos` (= count or k-1) takes the new value, which then
+// moves down past every strictly larger predecessor (NaN compares false and stays where it is, knncuda.cu:149-195).
+template <int KMAX>
+struct RegList {
+    float d[KMAX];
+    int i[KMAX];
+    int count = 0;
+    __device__ __forceinline__ void insert(int k, float d2, int j) {
+        int pos;
+        if (count < k) pos = count++;
+        else pos = k - 1;  // the caller has already applied the skip rule against `worst`
+        bool moving = true;
+#pragma unroll
+        for (int s = KMAX - 1; s >= 1; --s) {
+            if (s > pos || !moving) continue;
+            if (d[s - 1] > d2) {
+                d[s] = d[s - 1];
+                i[s] = i[s - 1];
+            } else {
+                d[s] = d2;
+                i[s] = j;
+                moving = false;
+            }
+        }
+        if (moving) {
+            d[0] = d2;
+            i[0] = j;
+        }
+    }
+    // entry k-1 once the list is full
+    __device__ __forceinline__ float worst(int k) const {
+        float w = d[0];
+#pragma unroll
+        for (int s = 1; s < KMAX; ++s) w = (s == k - 1) ? d[s] : w;
+        return w;
+    }
+};
+
+template <int DIM, int KMAX, int QPT>
+__global__ void __launch_bounds__(kKnnThreads) knn_reg_kernel(const float* __restrict__ ref, int ref_nb,
+                                                              const float* __restrict__ query, int query_nb, int k,
+                                                              float* __restrict__ out_dist, int* __restrict__ out_index) {
+    __shared__ float tile[DIM][kTile];
+    const int q0 = (blockIdx.x * kKnnThreads + threadIdx.x);
+    const int stride_q = gridDim.x * kKnnThreads;
+    float qv[QPT][DIM];
+    float worst[QPT];
+    RegList<KMAX> best[QPT];
+    bool live[QPT];
+#pragma unroll
+    for (int i = 0; i < QPT; ++i) {
+        const int q = q0 + i * stride_q;
+        live[i] = q < query_nb;
+        worst[i] = FLT_MAX;
+#pragma unroll
+        for (int s = 0; s < KMAX; ++s) { best[i].d[s] = FLT_MAX; best[i].i[s] = 0; }
+#pragma unroll
+        for (int d = 0; d < DIM; ++d) qv[i][d] = live[i] ? __ldg(query + (size_t)d * query_nb + q) : 0.f;
+    }
+    for (int base = 0; base < ref_nb; base += kTile) {
+        const int n = min(kTile, ref_nb - base);
+        __syncthreads();
+        for (int t = threadIdx.x; t < n; t += kKnnThreads)
+#pragma unroll
+            for (int d = 0; d < DIM; ++d) tile[d][t] = __ldg(ref + (size_t)d * ref_nb + base + t);
+        __syncthreads();
+        for (int t = 0; t < n; ++t) {
+            float r[DIM];
+#pragma unroll
+            for (int d = 0; d < DIM; ++d) r[d] = tile[d][t];
+#pragma unroll
+            for (int i = 0; i < QPT; ++i) {
+                float ssd = 0.f;
+#pragma unroll
+                for (int d = 0; d < DIM; ++d) {
+                    const float diff = __fsub_rn(r[d], qv[i][d]);
+                    ssd = __fmaf_rn(diff, diff, ssd);
+                }
+                if (live[i] && !(best[i].count == k && ssd >= worst[i])) {
+                    best[i].insert(k, ssd, base + t);
+                    if (best[i].count == k) worst[i] = best[i].worst(k);
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < QPT; ++i) {
+        const int q = q0 + i * stride_q;
+        if (!live[i]) continue;
+#pragma unroll
+        for (int s = 0; s < KMAX; ++s) {
+            if (s >= k) break;
+            out_dist[(size_t)s * query_nb + q] = __fsqrt_rn(best[i].d[s]);
+            out_index[(size_t)s * query_nb + q] = best[i].i[s];
+        }
+    }
+}
+
+template <int DIM>
+static bool launch_knn_reg(const float* d_ref, int ref_nb, const float* d_query, int query_nb, int k, float* d_dist,
+                           int* d_index, int sm_count, cudaStream_t stream) {
+    auto blocks_for = [&](int qpt) {
+        int blocks = (query_nb + kKnnThreads * qpt - 1) / (kKnnThreads * qpt);
+        const int min_blocks = min((query_nb + kKnnThreads - 1) / kKnnThreads, 2 * sm_count);
+        return max(blocks, min_blocks);
+    };
+    if (k == 1) knn_reg_kernel<DIM, 1, 4><<<blocks_for(4), kKnnThreads, 0, stream>>>(d_ref, ref_nb, d_query, query_nb, k, d_dist, d_index);
+    else if (k <= 4) knn_reg_kernel<DIM, 4, 2><<<blocks_for(2), kKnnThreads, 0, stream>>>(d_ref, ref_nb, d_query, query_nb, k, d_dist, d_index);
+    else if (k <= 8) knn_reg_kernel<DIM, 8, 1><<<blocks_for(1), kKnnThreads, 0, stream>>>(d_ref, ref_nb, d_query, query_nb, k, d_dist, d_index);
+    else if (k <= 16) knn_reg_kernel<DIM, 16, 1><<<blocks_for(1), kKnnThreads, 0, stream>>>(d_ref, ref_nb, d_query, query_nb, k, d_dist, d_index);
+    else return false;
+    return true;
+}
+
 // any dimension: one query per thread, its coordinates re-read through L1 (dim x query_nb layout is coalesced)
 __global__ void __launch_bounds__(kKnnThreads) knn_generic_kernel(const float* __restrict__ ref, int ref_nb,
                                                                   const float* __restrict__ query, int query_nb, int dim,
@@ -123,6 +239,16 @@ __global__ void __launch_bounds__(kKnnThreads) knn_generic_kernel(const float* _
 cudaError_t launch_knn(const float* d_ref, int ref_nb, const float* d_query, int query_nb, int dim, int k, float* d_dist,
                        int* d_index, int sm_count, cudaStream_t stream) {
     if (query_nb <= 0) return cudaSuccess;
+    if (dim >= 1 && dim <= 4 && k <= 16) {
+        bool done = false;
+        switch (dim) {
+            case 1: done = launch_knn_reg<1>(d_ref, ref_nb, d_query, query_nb, k, d_dist, d_index, sm_count, stream); break;
+            case 2: done = launch_knn_reg<2>(d_ref, ref_nb, d_query, query_nb, k, d_dist, d_index, sm_count, stream); break;
+            case 3: done = launch_knn_reg<3>(d_ref, ref_nb, d_query, query_nb, k, d_dist, d_index, sm_count, stream); break;
+            default: done = launch_knn_reg<4>(d_ref, ref_nb, d_query, query_nb, k, d_dist, d_index, sm_count, stream); break;
+        }
+        if (done) return cudaGetLastError();
+    }
     if (dim >= 1 && dim <= 4) {
         // enough CTAs to cover the queries kQpt per thread, but at least ~2 waves of the SMs when queries are few
         int blocks = (query_nb + kKnnThreads * kQpt - 1) / (kKnnThreads * kQpt);
