@@ -206,8 +206,12 @@ static bool launch_knn_reg(const float* d_ref, int ref_nb, const float* d_query,
         const int min_blocks = min((query_nb + kKnnThreads - 1) / kKnnThreads, 2 * sm_count);
         return max(blocks, min_blocks);
     };
-    if (k == 1) knn_reg_kernel<DIM, 1, 4><<<blocks_for(4), kKnnThreads, 0, stream>>>(d_ref, ref_nb, d_query, query_nb, k, d_dist, d_index);
-    else if (k <= 4) knn_reg_kernel<DIM, 4, 2><<<blocks_for(2), kKnnThreads, 0, stream>>>(d_ref, ref_nb, d_query, query_nb, k, d_dist, d_index);
+    // Queries per thread: more of them share each broadcast LDS, fewer keep more warps resident.  Measured
+    // (tools/knn_probe.py): one per thread wins until the queries alone fill the machine several times over
+    // (k = 1: 4096 x 262144 0.86 ms vs 1.06 ms with four; 813 x 3M 1.81 vs 1.75 ms; k = 4, 65536 queries: 1.27 vs 1.86 ms).
+    if (k == 1 && query_nb >= (1 << 20)) knn_reg_kernel<DIM, 1, 4><<<blocks_for(4), kKnnThreads, 0, stream>>>(d_ref, ref_nb, d_query, query_nb, k, d_dist, d_index);
+    else if (k == 1) knn_reg_kernel<DIM, 1, 1><<<blocks_for(1), kKnnThreads, 0, stream>>>(d_ref, ref_nb, d_query, query_nb, k, d_dist, d_index);
+    else if (k <= 4) knn_reg_kernel<DIM, 4, 1><<<blocks_for(1), kKnnThreads, 0, stream>>>(d_ref, ref_nb, d_query, query_nb, k, d_dist, d_index);
     else if (k <= 8) knn_reg_kernel<DIM, 8, 1><<<blocks_for(1), kKnnThreads, 0, stream>>>(d_ref, ref_nb, d_query, query_nb, k, d_dist, d_index);
     else if (k <= 16) knn_reg_kernel<DIM, 16, 1><<<blocks_for(1), kKnnThreads, 0, stream>>>(d_ref, ref_nb, d_query, query_nb, k, d_dist, d_index);
     else return false;

@@ -34,7 +34,7 @@ def quiet():  # the reference printf's on stdout
 ref_lib = ReferenceKnn() if KNN_REF_SO.exists() else None
 rng = np.random.default_rng(3)
 with Renderer(0) as r:
-    for ref_nb, query_nb, k in ((4096, 262144, 1), (16384, 65536, 4), (16384, 65536, 10), (16384, 65536, 16), (233098, 233098, 10)):
+    for ref_nb, query_nb, k in ((4096, 262144, 1), (813, 3000000, 1), (16384, 65536, 4), (16384, 65536, 8), (16384, 65536, 10), (233098, 233098, 10)):
         ref = rng.random((3, ref_nb), np.float32)
         qry = rng.random((3, query_nb), np.float32)
         wall, dev = [], []
