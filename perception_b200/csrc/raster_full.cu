@@ -260,59 +260,81 @@ __global__ void __launch_bounds__(kBigThreads) raster_big_kernel(FullRasterArgs 
     }
 }
 
-// keys -> images, four pixels per thread.  grid.y = image.
-__global__ void __launch_bounds__(256) resolve_full_kernel(FullRasterArgs a) {
-    const int W = a.cam.width, H = a.cam.height, npx = W * H;
-    const int img = blockIdx.y;
-    const bool use_label = a.pose_label != nullptr;
-    const int pose_label = use_label ? a.pose_label[img] : 0;  // single-image mode resolves image 0 with label 0's entry
-    unsigned long long* keys = a.keys + (size_t)img * npx;
+struct TreeAcc {
     int flags = 0, clutter = 0, total = 0;
-    for (int g = blockIdx.x * blockDim.x + threadIdx.x; g < (npx + 3) / 4; g += gridDim.x * blockDim.x) {
+};
+
+// One covered pixel: key -> (depth, rgb) with the source-occlusion rule, and the tree statistics of the pose.
+template <bool TREE, bool RGB>
+__device__ __forceinline__ void resolve_pixel(const FullRasterArgs& a, unsigned long long key, int i, bool use_label,
+                                              int pose_label, int32_t& d, uint32_t& rgb, TreeAcc& acc) {
+    d = (int32_t)((uint32_t)(key >> 32) ^ 0x80000000u);
+    const int32_t src = __ldg(a.scene.depth + i);
+    const int src_label = (use_label && a.scene.label) ? (int)__ldg(a.scene.label + i) : 0;
+    if (TREE) {
+        // image_renderer.cuh:163-206 on the pixel's minimum depth (see pose_kernels.cu / DESIGN 4.11)
+        ++acc.total;
+        const int ad = abs(d - src);
+        const bool gate = use_label ? (pose_label != src_label - 1 && ad >= 1) : ((float)ad > a.occlusion_threshold);
+        if (gate && src > 0) {
+            if (d > src) { acc.flags |= 2; ++acc.clutter; }
+            else acc.flags |= 1;
+        }
+    }
+    rgb = 0;
+    if (source_occludes(d, src, use_label, pose_label, src_label, a.occlusion_threshold)) d = 0;
+    else if (RGB) rgb = __ldg(a.models.tri_color + (uint32_t)key);
+    if (d == INT_MAX) d = 0;  // max2zero (image_renderer.cuh:324-333,465-466)
+}
+
+// keys -> images.  grid.y = pose of the chunk; one thread per group of four consecutive pixels (no loop).  The common
+// case -- four empty keys -- is two 16-byte loads, a compare and the zero stores.  Every key read is left empty again.
+template <bool TREE, bool RGB>
+__global__ void __launch_bounds__(256) resolve_full_kernel(FullRasterArgs a) {
+    const int npx = a.cam.width * a.cam.height;
+    const int img = blockIdx.y;
+    const int i0 = 4 * (blockIdx.x * 256 + threadIdx.x);
+    TreeAcc acc;
+    if (i0 < npx) {
+        unsigned long long* keys = a.keys + (size_t)img * npx + i0;
+        unsigned long long key[4] = {~0ull, ~0ull, ~0ull, ~0ull};
+        const bool full = i0 + 3 < npx;
+        if (full && a.wide_stores) {  // npx % 4 == 0: 32-byte aligned group
+            const ulonglong2 k01 = *reinterpret_cast<const ulonglong2*>(keys);
+            const ulonglong2 k23 = *reinterpret_cast<const ulonglong2*>(keys + 2);
+            key[0] = k01.x; key[1] = k01.y; key[2] = k23.x; key[3] = k23.y;
+        } else {
+            for (int k = 0; k < 4 && i0 + k < npx; ++k) key[k] = keys[k];
+        }
         int32_t d4[4] = {0, 0, 0, 0};
         uint32_t r4 = 0, g4 = 0, b4 = 0;
+        if ((key[0] & key[1] & key[2] & key[3]) != ~0ull) {
+            const bool use_label = a.pose_label != nullptr;
+            const int pose_label = use_label ? a.pose_label[img] : 0;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const int i = 4 * g + k;
-            if (i >= npx) break;
-            const unsigned long long key = keys[i];
-            if (key == ~0ull) continue;
-            if (a.reset_keys) keys[i] = ~0ull;
-            int32_t d = (int32_t)((uint32_t)(key >> 32) ^ 0x80000000u);
-            const int32_t src = __ldg(a.scene.depth + i);
-            const int src_label = (use_label && a.scene.label) ? (int)__ldg(a.scene.label + i) : 0;
-            if (a.tree_total) {
-                // image_renderer.cuh:163-206 on the pixel's minimum depth (see pose_kernels.cu / DESIGN 4.11)
-                ++total;
-                const int ad = abs(d - src);
-                const bool gate = use_label ? (pose_label != src_label - 1 && ad >= 1) : ((float)ad > a.occlusion_threshold);
-                if (gate && src > 0) {
-                    if (d > src) { flags |= 2; ++clutter; }
-                    else flags |= 1;
-                }
+            for (int k = 0; k < 4; ++k) {
+                if (key[k] == ~0ull) continue;
+                keys[k] = ~0ull;
+                uint32_t rgb;
+                resolve_pixel<TREE, RGB>(a, key[k], i0 + k, use_label, pose_label, d4[k], rgb, acc);
+                r4 |= (rgb & 0xFFu) << (8 * k);
+                g4 |= ((rgb >> 8) & 0xFFu) << (8 * k);
+                b4 |= ((rgb >> 16) & 0xFFu) << (8 * k);
             }
-            uint32_t rgb = 0;
-            if (source_occludes(d, src, use_label, pose_label, src_label, a.occlusion_threshold)) d = 0;
-            else rgb = __ldg(a.models.tri_color + (uint32_t)key);
-            if (d == INT_MAX) d = 0;  // max2zero (image_renderer.cuh:324-333,465-466)
-            d4[k] = d;
-            r4 |= (rgb & 0xFFu) << (8 * k);
-            g4 |= ((rgb >> 8) & 0xFFu) << (8 * k);
-            b4 |= ((rgb >> 16) & 0xFFu) << (8 * k);
         }
         if (a.img_depth) {
-            const size_t o = (size_t)img * npx + 4 * (size_t)g;
-            if (4 * g + 3 < npx && a.wide_stores) {
+            const size_t o = (size_t)img * npx + (size_t)i0;
+            if (full && a.wide_stores) {
                 *reinterpret_cast<int4*>(a.img_depth + o) = make_int4(d4[0], d4[1], d4[2], d4[3]);
-                if (a.img_r) {
+                if (RGB) {
                     *reinterpret_cast<uint32_t*>(a.img_r + o) = r4;
                     *reinterpret_cast<uint32_t*>(a.img_g + o) = g4;
                     *reinterpret_cast<uint32_t*>(a.img_b + o) = b4;
                 }
             } else {
-                for (int k = 0; k < 4 && 4 * g + k < npx; ++k) {
+                for (int k = 0; k < 4 && i0 + k < npx; ++k) {
                     a.img_depth[o + k] = d4[k];
-                    if (a.img_r) {
+                    if (RGB) {
                         a.img_r[o + k] = (uint8_t)(r4 >> (8 * k)); a.img_g[o + k] = (uint8_t)(g4 >> (8 * k));
                         a.img_b[o + k] = (uint8_t)(b4 >> (8 * k));
                     }
@@ -320,17 +342,17 @@ __global__ void __launch_bounds__(256) resolve_full_kernel(FullRasterArgs a) {
             }
         }
     }
-    if (a.tree_total) {
+    if (TREE) {
 #pragma unroll
         for (int o = 16; o >= 1; o >>= 1) {
-            flags |= __shfl_xor_sync(0xffffffffu, flags, o);
-            clutter += __shfl_xor_sync(0xffffffffu, clutter, o);
-            total += __shfl_xor_sync(0xffffffffu, total, o);
+            acc.flags |= __shfl_xor_sync(0xffffffffu, acc.flags, o);
+            acc.clutter += __shfl_xor_sync(0xffffffffu, acc.clutter, o);
+            acc.total += __shfl_xor_sync(0xffffffffu, acc.total, o);
         }
         if ((threadIdx.x & 31) == 0) {
-            if (flags) atomicOr(a.tree_acc + 3 * img, flags);
-            if (clutter) atomicAdd(a.tree_acc + 3 * img + 1, clutter);
-            if (total) atomicAdd(a.tree_acc + 3 * img + 2, total);
+            if (acc.flags) atomicOr(a.tree_acc + 3 * img, acc.flags);
+            if (acc.clutter) atomicAdd(a.tree_acc + 3 * img + 1, acc.clutter);
+            if (acc.total) atomicAdd(a.tree_acc + 3 * img + 2, acc.total);
         }
     }
 }
@@ -366,8 +388,15 @@ cudaError_t launch_full_resolve(const FullRasterArgs& a, int n_images, cudaStrea
         cudaError_t e = cudaMemsetAsync(a.tree_acc, 0, 3 * sizeof(int) * (size_t)n_images, stream);
         if (e != cudaSuccess) return e;
     }
-    dim3 grid(std::min(((npx + 3) / 4 + 255) / 256, 1200), n_images);
-    resolve_full_kernel<<<grid, 256, 0, stream>>>(a);
+    dim3 grid(((npx + 3) / 4 + 255) / 256, n_images);
+    const bool rgb = a.img_depth && a.img_r;
+    if (a.tree_total) {
+        if (rgb) resolve_full_kernel<true, true><<<grid, 256, 0, stream>>>(a);
+        else resolve_full_kernel<true, false><<<grid, 256, 0, stream>>>(a);
+    } else {
+        if (rgb) resolve_full_kernel<false, true><<<grid, 256, 0, stream>>>(a);
+        else resolve_full_kernel<false, false><<<grid, 256, 0, stream>>>(a);
+    }
     if (a.tree_total) tree_finish_kernel<<<(a.n_poses + 127) / 128, 128, 0, stream>>>(a);
     return cudaGetLastError();
 }
@@ -405,16 +434,28 @@ cudaError_t full_raster_job(::perch_ctx* c, const FullJob& j, int* launches) {
         if (launches) *launches += 2;
         return launch_full_raster(a, c->max_model_quads, c->stream);
     }
-    // chunk of poses whose key images fit the budget.  Measured on 1024 poses of the C2 mesh (tools/render_probe.py):
-    // 16 MB 5.7 ms, 32 MB 3.2 ms, 64 MB 2.5 ms, 128 MB 2.1 ms, 256 MB 1.8 ms -- few large launches beat L2 residency
-    const size_t budget = (size_t)std::max(env_or("PERCH_FULL_CHUNK_MB", 256), 1) << 20;
+    // Poses go through in chunks; chunk i z-tests into half (i & 1) of the key buffer.  The rasterising kernels run on the
+    // context's stream, the resolve kernels on a second, high-priority stream: the first is bound by instruction issue,
+    // the second by DRAM, so resolve(i) runs underneath raster(i + 1) (its CTAs take the slots raster CTAs free).  The gain
+    // is small (1.72 -> 1.68 ms on 1024 poses): the rasterising kernel needs its occupancy, what the resolve takes it loses.
+    // Events: resolve(i) waits for raster(i); raster(i + 2) waits for resolve(i), which has emptied that half again.
+    const size_t budget = (size_t)std::max(env_or("PERCH_FULL_CHUNK_MB", 256), 1) << 20;  // per half
     const size_t chunk = std::min<size_t>({std::max<size_t>(budget / (npx * 8), 1), (size_t)j.n_poses, (size_t)65535});  // grid.y
-    if (c->full_keys_n < chunk * npx) {
+    const bool overlap = env_or("PERCH_FULL_OVERLAP", 1) != 0;
+    if (!c->stream_hi) {
+        int lo = 0, hi = 0;
+        if ((e = cudaDeviceGetStreamPriorityRange(&lo, &hi)) != cudaSuccess) return e;
+        if ((e = cudaStreamCreateWithPriority(&c->stream_hi, cudaStreamNonBlocking, hi)) != cudaSuccess) return e;
+        for (auto& ev : c->ev_full)
+            if ((e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)) != cudaSuccess) return e;
+    }
+    if (c->full_keys_n < 2 * chunk * npx) {
         if (c->d_full_keys) cudaFree(c->d_full_keys);
         c->d_full_keys = nullptr; c->full_keys_n = 0;
-        if ((e = cudaMalloc(&c->d_full_keys, chunk * npx * 8)) != cudaSuccess) return e;
-        if ((e = cudaMemsetAsync(c->d_full_keys, 0xFF, chunk * npx * 8, c->stream)) != cudaSuccess) return e;
-        c->full_keys_n = chunk * npx;
+        if ((e = cudaMalloc(&c->d_full_keys, 2 * chunk * npx * 8)) != cudaSuccess) return e;
+        if ((e = cudaMemsetAsync(c->d_full_keys, 0xFF, 2 * chunk * npx * 8, c->stream)) != cudaSuccess) return e;
+        c->full_keys_n = 2 * chunk * npx;
+        c->full_half_n = chunk * npx;
     }
     if (j.tree_total && c->full_acc_n < 3 * (size_t)j.n_poses) {
         if (c->d_full_acc) cudaFree(c->d_full_acc);
@@ -422,12 +463,21 @@ cudaError_t full_raster_job(::perch_ctx* c, const FullJob& j, int* launches) {
         if ((e = cudaMalloc(&c->d_full_acc, 3 * sizeof(int) * (size_t)j.n_poses)) != cudaSuccess) return e;
         c->full_acc_n = 3 * (size_t)j.n_poses;
     }
-    a.keys = c->d_full_keys;
     a.reset_keys = 1;
     auto aligned = [](const void* p, uintptr_t m) { return (reinterpret_cast<uintptr_t>(p) & (m - 1)) == 0; };
     a.wide_stores = npx % 4 == 0 && aligned(j.img_depth, 16) && aligned(j.img_r, 4) && aligned(j.img_g, 4) && aligned(j.img_b, 4);
-    for (size_t p0 = 0; p0 < (size_t)j.n_poses; p0 += chunk) {
+    cudaStream_t s_res = overlap ? c->stream_hi : c->stream;
+    auto fail = [&](cudaError_t err) {
+        cudaStreamSynchronize(c->stream_hi);
+        cudaFree(c->d_full_keys);  // the keys may be dirty: start from a fresh, cleared buffer next time
+        c->d_full_keys = nullptr; c->full_keys_n = 0;
+        return err;
+    };
+    size_t ci = 0;
+    for (size_t p0 = 0; p0 < (size_t)j.n_poses; p0 += chunk, ++ci) {
         const int n = (int)std::min(chunk, (size_t)j.n_poses - p0);
+        const int half = (int)(ci & 1);
+        a.keys = c->d_full_keys + (size_t)half * c->full_half_n;
         a.poses = j.poses + p0; a.pose_model_map = j.pose_model_map + p0;
         a.pose_label = j.pose_label ? j.pose_label + p0 : nullptr;
         a.n_poses = n;
@@ -440,13 +490,20 @@ cudaError_t full_raster_job(::perch_ctx* c, const FullJob& j, int* launches) {
         a.tree_clutter = j.tree_clutter ? j.tree_clutter + p0 : nullptr;
         a.tree_total = j.tree_total ? j.tree_total + p0 : nullptr;
         a.tree_acc = j.tree_total ? c->d_full_acc + 3 * p0 : nullptr;
-        if ((e = launch_full_raster(a, c->max_model_quads, c->stream)) == cudaSuccess) e = launch_full_resolve(a, n, c->stream);
-        if (e != cudaSuccess) {
-            cudaFree(c->d_full_keys);  // the keys may be dirty: start from a fresh, cleared buffer next time
-            c->d_full_keys = nullptr; c->full_keys_n = 0;
-            return e;
+        // ev_full[half]: raster of this half done; ev_full[2 + half]: resolve of this half done
+        if (overlap && ci >= 2 && (e = cudaStreamWaitEvent(c->stream, c->ev_full[2 + half], 0)) != cudaSuccess) return fail(e);
+        if ((e = launch_full_raster(a, c->max_model_quads, c->stream)) != cudaSuccess) return fail(e);
+        if (overlap) {
+            if ((e = cudaEventRecord(c->ev_full[half], c->stream)) != cudaSuccess) return fail(e);
+            if ((e = cudaStreamWaitEvent(s_res, c->ev_full[half], 0)) != cudaSuccess) return fail(e);
         }
+        if ((e = launch_full_resolve(a, n, s_res)) != cudaSuccess) return fail(e);
+        if (overlap && (e = cudaEventRecord(c->ev_full[2 + half], s_res)) != cudaSuccess) return fail(e);
         if (launches) *launches += 3 + (j.tree_total ? 1 : 0);
+    }
+    if (overlap) {  // everything later on the context's stream comes after the last resolves
+        for (int h = 0; h < 2 && h < (int)ci; ++h)
+            if ((e = cudaStreamWaitEvent(c->stream, c->ev_full[2 + h], 0)) != cudaSuccess) return fail(e);
     }
     return cudaSuccess;
 }

@@ -47,9 +47,7 @@ if len(sys.argv) > 2:  # one variant only (profiling): python tools/render_probe
 base = run("legacy", PERCH_IMAGE_LEGACY=1)
 new = run("full")
 print("bit-equal:", all(np.array_equal(base[k], new[k]) for k in ("result_depth", "result_color")))
-for mb in (64, 128, 512):
+run("serial", PERCH_FULL_OVERLAP=0)
+for mb in (32, 64, 256):
     run(f"chunk{mb}", PERCH_FULL_CHUNK_MB=mb)
-for cells in (4, 8, 32, 64):
-    run(f"lane{cells}", PERCH_FULL_LANE_CELLS=cells)
-for cells in (256, 1024, 65536):
-    run(f"big{cells}", PERCH_FULL_BIG_CELLS=cells)
+    run(f"chunk{mb}_serial", PERCH_FULL_CHUNK_MB=mb, PERCH_FULL_OVERLAP=0)
