@@ -344,7 +344,9 @@ def run_ours(args):
             "clocks": clocks,
             "e2e": {"value": world * P * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": int(P * (64 + 4 + 4 + (4 if h_lab is not None else 0))),
                     "d2h_bytes_per_step": int(P * 24), "ms_per_scene": e2e_s / args.steps * 1e3,
-                    "contexts": n_ctx},
+                    "contexts": n_ctx,
+                    "how": "every step is one blocking call of the public host API (H2D of its poses, kernel, D2H of its costs) "
+                           "+ host top-k; steps alternate between `contexts` contexts, one host thread each"},
             "gpu_launches": args.steps,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "peak_kind": f"{peak_kind} copy bandwidth", "bytes_per_pose": bpp,
