@@ -500,11 +500,6 @@ void perch_destroy(perch_ctx* c) {
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
-    if (c->stream_hi) {
-        cudaStreamDestroy(c->stream_hi);
-        for (cudaEvent_t ev : c->ev_full)
-            if (ev) cudaEventDestroy(ev);
-    }
     perch_detail::destroy_states(c);
     cudaEventDestroy(c->ev0);
     cudaEventDestroy(c->ev1);

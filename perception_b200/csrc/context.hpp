@@ -107,10 +107,7 @@ struct perch_ctx {
     bool composed = false;
     // full-resolution rasteriser (raster_full.cu): key images of one chunk of poses, deferred-triangle list, counters
     unsigned long long* d_full_keys = nullptr;
-    size_t full_keys_n = 0;            // keys allocated (all empty between calls): two halves of full_half_n
-    size_t full_half_n = 0;
-    cudaStream_t stream_hi = nullptr;  // resolve kernels (high priority), overlapping the next chunk's rasterising
-    cudaEvent_t ev_full[4] = {nullptr, nullptr, nullptr, nullptr};
+    size_t full_keys_n = 0;            // keys allocated (all empty between calls)
     int2* d_full_big = nullptr;
     int* d_full_count = nullptr;
     int* d_full_acc = nullptr;

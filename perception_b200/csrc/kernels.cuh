@@ -68,10 +68,10 @@ struct FullRasterArgs {
     const int* pose_label = nullptr;        // null => 3-DoF occlusion rule
     int n_poses = 0;
     float occlusion_threshold = 0.f;
-    unsigned long long* keys = nullptr;     // n_poses x W*H (depth, triangle) keys, or ONE image when `single`
+    unsigned long long* keys = nullptr;     // n_poses x W*H (depth, triangle) keys (the resolve pass leaves every key
+                                            // empty again), or ONE image when `single`
     int single = 0;                         // single_result_image: every pose z-tests into keys[0 .. W*H)
     int key_pose_id = 0;                    // low word of the key = pose index instead of original triangle index
-    int reset_keys = 0;                     // the resolve pass leaves every key empty again (next chunk needs no fill)
     int2* big_list = nullptr;               // (pose, triangle slot | perm << 26) of triangles with large bboxes
     int* big_count = nullptr;
     int big_cap = 0;

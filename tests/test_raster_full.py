@@ -47,7 +47,7 @@ def _renderer(case, with_label):
 
 
 VARIANTS = ({}, {"PERCH_FULL_CHUNK_MB": 5}, {"PERCH_FULL_BIG_CELLS": 1}, {"PERCH_FULL_BIG_CELLS": 1 << 30},
-            {"PERCH_FULL_CHUNK_MB": 1, "PERCH_FULL_BIG_CELLS": 9}, {"PERCH_FULL_LANE_CELLS": 0}, {"PERCH_FULL_OVERLAP": 0}, {"PERCH_FULL_CHUNK_MB": 3},
+            {"PERCH_FULL_CHUNK_MB": 1, "PERCH_FULL_BIG_CELLS": 9}, {"PERCH_FULL_LANE_CELLS": 0}, {"PERCH_FULL_CHUNK_MB": 3},
             {"PERCH_FULL_LANE_CELLS": 1 << 30, "PERCH_FULL_BIG_CELLS": 1 << 30})
 
 

@@ -47,7 +47,5 @@ if len(sys.argv) > 2:  # one variant only (profiling): python tools/render_probe
 base = run("legacy", PERCH_IMAGE_LEGACY=1)
 new = run("full")
 print("bit-equal:", all(np.array_equal(base[k], new[k]) for k in ("result_depth", "result_color")))
-run("serial", PERCH_FULL_OVERLAP=0)
-for mb in (32, 64, 256):
+for mb in (32, 64, 128, 512):
     run(f"chunk{mb}", PERCH_FULL_CHUNK_MB=mb)
-    run(f"chunk{mb}_serial", PERCH_FULL_CHUNK_MB=mb, PERCH_FULL_OVERLAP=0)
