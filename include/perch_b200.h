@@ -137,6 +137,27 @@ int perch_depth2cloud(perch_ctx* ctx, const int32_t* depth, const uint8_t* red, 
                       const float* camera_transform16, int* point_num, float* out_cloud_soa, float* out_cloud_aos,
                       uint8_t* out_cloud_color, int* out_dc_index, int* out_cloud_pose_map, int* out_cloud_label);
 
+/* Allocation-free variant of the depth image -> cloud kernels.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  perch_depth2cloud keeps its per-row counters in the context's cudaMalloc'd scratch; here
+ * they live in a file-scope device array inside the library (PERCH_STATIC_CLOUD_MAX_ROWS + 64 ints = 4 MiB, held by
+ * every GPU that loads the library until exit), so the call performs no cudaMalloc / cudaFree / allocating library call.
+ * Inputs and outputs are CALLER-provided DEVICE pointers on the context's device: d_depth (num_images x height x width
+ * int32), d_label_mask (same shape uint8, may be NULL); outputs (each may be NULL) d_out_cloud_aos (capacity x 3 floats),
+ * d_out_cloud_soa (3 x capacity, row stride = capacity), d_out_cloud_pose_map, d_out_cloud_label (capacity ints; label
+ * only with a mask).  *point_num (host) receives the number of points; values, order and the label rule are those of
+ * perch_depth2cloud without bounds (compute_point_clouds.cuh:37-184).
+ * Limits: num_images * ceil(height / stride) <= PERCH_STATIC_CLOUD_MAX_ROWS, else PERCH_ERR_CAPACITY (nothing launched);
+ * more points than `capacity` => the first `capacity` are written and PERCH_ERR_CAPACITY is returned with *point_num set.
+ * All calls on one device share the array and it keeps the last call's contents (nothing in it needs to start at zero:
+ * every slot a call reads it has written first); calls that OVERLAP on the GPU -- two contexts / streams on the same
+ * device -- race on it.  Runs on the context's stream and synchronises it. */
+#define PERCH_STATIC_CLOUD_MAX_ROWS (1 << 20)
+int perch_depth2cloud_static(perch_ctx* ctx, const int32_t* d_depth, const uint8_t* d_label_mask, int width, int height,
+                             int num_images, float cx, float cy, float fx, float fy, float depth_factor, int stride,
+                             int capacity, float* d_out_cloud_aos, float* d_out_cloud_soa, int* d_out_cloud_pose_map,
+                             int* d_out_cloud_label, int* point_num);
+
 /* ---- the hot path ----------------------------------------------------------------------------------------- */
 /* Replaces cuda_renderer::render_cuda_multi_unified (renderer.h:221-268, renderer.cu:1431-1934).
  * stage: "RENDER" | "CLOUD" | "COST" | "DEBUG" with the reference's meaning (renderer.cu:1479).

@@ -4,7 +4,11 @@
 // full-resolution mask produces, compute_point_clouds.cuh:290-292).
 #include <cuda_runtime.h>
 
+#include <climits>
+
+#include "capi_common.hpp"
 #include "kernels.cuh"
+#include "perch_b200.h"
 
 namespace perch {
 namespace {
@@ -208,3 +212,77 @@ cudaError_t launch_cloud_write(const CloudArgs& a, cudaStream_t stream) {
 }
 
 }  // namespace perch
+
+// ---- allocation-free variant: perch_depth2cloud_static (include/perch_b200.h) -----------------------------------------
+// No counterpart in the reference.  For callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops):
+// the only scratch the cloud kernels need -- one int per lattice row plus the total -- lives in a file-scope device
+// array instead of the context's cudaMalloc'd scratch.  Every GPU that loads the library holds the array
+// (PERCH_STATIC_CLOUD_MAX_ROWS + 64 ints = 4 MiB) until exit.  All calls on one device share it: calls that overlap on
+// the GPU race.  Nothing in it has to start at zero (the count kernel writes every row slot of the call, the scan
+// writes the total), so the previous call's contents are simply overwritten.
+static __device__ __align__(256) int g_static_row_counts[PERCH_STATIC_CLOUD_MAX_ROWS + 64];
+
+namespace {
+constexpr int kMaxDevices = 64;
+int* g_static_rows_dev[kMaxDevices];  // device address of g_static_row_counts per device (host code cannot use the name)
+
+// Must be called with `device` current.  The symbol's name is a host-side stand-in, not a device address.
+cudaError_t static_rows_ptr(int device, int** out) {
+    if (device < 0 || device >= kMaxDevices) return cudaErrorInvalidDevice;
+    int* p = __atomic_load_n(&g_static_rows_dev[device], __ATOMIC_ACQUIRE);
+    if (!p) {
+        cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_static_row_counts);
+        if (e != cudaSuccess) return e;
+        __atomic_store_n(&g_static_rows_dev[device], p, __ATOMIC_RELEASE);  // same value from every thread
+    }
+    *out = p;
+    return cudaSuccess;
+}
+}  // namespace
+
+extern "C" int perch_depth2cloud_static(perch_ctx* c, const int32_t* d_depth, const uint8_t* d_label_mask, int width,
+                                        int height, int num_images, float cx, float cy, float fx, float fy,
+                                        float depth_factor, int stride, int capacity, float* d_out_cloud_aos,
+                                        float* d_out_cloud_soa, int* d_out_cloud_pose_map, int* d_out_cloud_label,
+                                        int* point_num) {
+    using perch_detail::fail;
+    if (!c || !d_depth || !point_num) return fail(PERCH_ERR_INVALID, "null argument");
+    if (width <= 0 || height <= 0 || num_images <= 0 || stride <= 0 || capacity < 0)
+        return fail(PERCH_ERR_INVALID, "bad size argument");
+    if (width % stride != 0)
+        return fail(PERCH_ERR_INVALID, "stride %d must divide the image width %d (compute_point_clouds.cuh:271)", stride, width);
+    if ((size_t)width * height * num_images > (size_t)INT_MAX)
+        return fail(PERCH_ERR_CAPACITY, "num_images*width*height exceeds INT_MAX");
+    const int Lh = (height + stride - 1) / stride;
+    const size_t rows = (size_t)num_images * Lh;
+    if (rows > (size_t)PERCH_STATIC_CLOUD_MAX_ROWS)
+        return fail(PERCH_ERR_CAPACITY,
+                    "perch_depth2cloud_static: %d images x %d lattice rows = %zu rows exceed the static scratch of %d rows "
+                    "(use perch_depth2cloud, which allocates)", num_images, Lh, rows, PERCH_STATIC_CLOUD_MAX_ROWS);
+    perch_detail::DeviceGuard g(c->device);
+    int* d_rows = nullptr;
+    PERCH_CU(static_rows_ptr(c->device, &d_rows));
+    perch::CloudArgs a;
+    a.depth = d_depth;
+    a.label_mask = d_label_mask;
+    a.img_w = width; a.img_h = height; a.full_h = height; a.num_images = num_images;
+    a.stride = stride; a.coord_scale = 1;
+    a.cx = cx; a.cy = cy; a.fx = fx; a.fy = fy; a.depth_factor = depth_factor;
+    a.row_counts = d_rows;
+    a.capacity = capacity;
+    a.cloud_aos = d_out_cloud_aos;
+    a.cloud_soa = d_out_cloud_soa;
+    a.pose_map = d_out_cloud_pose_map;
+    a.cloud_label = d_label_mask ? d_out_cloud_label : nullptr;
+    PERCH_CU(perch::launch_cloud_count(a, c->stream));
+    PERCH_CU(perch::launch_cloud_scan(a, c->stream));
+    if (d_out_cloud_aos || d_out_cloud_soa || d_out_cloud_pose_map || a.cloud_label) PERCH_CU(perch::launch_cloud_write(a, c->stream));
+    int total = 0;
+    PERCH_CU(cudaMemcpyAsync(&total, d_rows + rows, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    PERCH_CU(cudaStreamSynchronize(c->stream));
+    *point_num = total;
+    if (total > capacity && (d_out_cloud_aos || d_out_cloud_soa || d_out_cloud_pose_map || a.cloud_label))
+        return fail(PERCH_ERR_CAPACITY, "cloud has %d points but the buffers hold %d (the first %d were written)", total,
+                    capacity, capacity);
+    return PERCH_OK;
+}
