@@ -173,6 +173,14 @@ int perch_render_cost(perch_ctx* ctx, const char* stage, const float* poses16, i
 int perch_render_cost_device(perch_ctx* ctx, const float* d_poses16, int n_poses, const int* d_pose_model_map,
                              const int* d_pose_segmentation_label, const float* d_pose_observed_points_total,
                              const perch_params* params, float* d_costs3p, int32_t* d_counts3p);
+/* The COST stage computed WITHOUT the fused kernel, in the reference's own structure (renderer.cu:1561-1659, 1852-1907):
+ * every pixel of every pose rasterised (no culling), stride-sampled into clouds, a strict-`<` linear nearest-neighbour
+ * scan over the observed points of the pose's label, then compute_costs' counters.  Arguments and outputs as
+ * perch_render_cost(stage "COST") (rendered_cost, observed_cost, points_diff_cost, counts); cost_type 0 and 2 only.
+ * A self-check and A/B path (every pose of a full-size batch in a few hundred ms), not the product path. */
+int perch_render_cost_unfused(perch_ctx* ctx, const float* poses16, int n_poses, const int* pose_model_map,
+                              const int* pose_segmentation_label, const float* pose_observed_points_total,
+                              const perch_params* params, perch_outputs* out);
 /* Device memory helpers so hosts without a CUDA binding (ctypes) can stage persistent buffers. */
 int perch_device_alloc(perch_ctx* ctx, size_t bytes, void** d_ptr);
 int perch_device_free(perch_ctx* ctx, void* d_ptr);

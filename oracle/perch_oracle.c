@@ -539,6 +539,55 @@ void oracle_costs(const int32_t* depth, const uint8_t* r, const uint8_t* g, cons
 }
 
 /*
+ * render_cuda_multi_unified("COST") for a LIST of poses without keeping their images: per pose, oracle_render into a
+ * thread-local 640x480 image (image_renderer.cuh:59-321 as restated above) followed by oracle_costs on that one image
+ * (compute_point_clouds.cuh:37-184, renderer.cu:1852-1877, compute_costs.cuh:161-290).  Poses are independent in the
+ * reference too (one image, one cloud segment and one `explained` row each), so running them one at a time -- here
+ * with OpenMP over poses -- yields exactly what the batched call yields.  Lets the parity tests and bench.py's
+ * parity_check compare the fused CUDA kernel with the oracle at the full C2 / C3 / C5 sizes (a 20 000-triangle pose
+ * costs ~5 ms of one core).  out_counts is 3 x P like oracle_costs.
+ */
+void oracle_score_poses(const tri64* tris, int n_tris, const float* poses16, int n_poses, const int* pose_model_map,
+                        const int* tris_model_count, int n_models, int width, int height, const float* proj16,
+                        const int32_t* source_depth, const uint8_t* source_label, const int* pose_label,
+                        float occlusion_threshold, float cx, float cy, float fx, float fy, float depth_factor, int stride,
+                        const float* obs_xyz_aos, const uint8_t* obs_rgb_soa, const int* obs_label, int n_obs,
+                        const float* pose_obs_total, int cost_type, int calc_observed, float sensor_resolution,
+                        float color_distance_threshold, float* rendered_cost, float* observed_cost,
+                        float* points_diff_cost, int32_t* out_counts) {
+    const size_t npx = (size_t)width * height;
+#pragma omp parallel
+    {
+        int32_t* d = (int32_t*)malloc(npx * sizeof(int32_t));
+        uint8_t* rgb = (uint8_t*)malloc(3 * npx);
+#pragma omp for schedule(dynamic, 1)
+        for (int p = 0; p < n_poses; ++p) {
+            render_impl(tris, n_tris, poses16 + 16 * (size_t)p, 1, pose_model_map + p, tris_model_count, n_models, width, height,
+                        proj16, source_depth, source_label, pose_label ? pose_label + p : NULL, occlusion_threshold, 0, d,
+                        rgb, rgb + npx, rgb + 2 * npx, NULL);
+            float rc = 0, oc = 0, dc = 0;
+            int32_t cnt[3] = {0, 0, 0};
+            oracle_costs(d, rgb, rgb + npx, rgb + 2 * npx, 1, width, height, cx, cy, fx, fy, depth_factor, stride,
+                         pose_label ? pose_label + p : NULL, obs_xyz_aos, obs_rgb_soa, obs_label, n_obs,
+                         pose_obs_total ? pose_obs_total + p : NULL, cost_type, calc_observed, sensor_resolution,
+                         color_distance_threshold, &rc, &oc, &dc, cnt, NULL, 0.0);
+            rendered_cost[p] = rc;
+            if (calc_observed) {
+                if (observed_cost) observed_cost[p] = oc;
+                if (points_diff_cost) points_diff_cost[p] = dc;
+            }
+            if (out_counts) {
+                out_counts[p] = cnt[0];
+                out_counts[n_poses + p] = cnt[1];
+                out_counts[2 * (size_t)n_poses + p] = cnt[2];
+            }
+        }
+        free(d);
+        free(rgb);
+    }
+}
+
+/*
  * kNN-CUDA package API (cuda_renderer/knncuda.h:33-100).  Layout: ref is dim x ref_nb, query dim x query_nb (one row
  * per dimension); outputs k x query_nb, ascending distance, square root applied, 0-based indices.
  * Selection = knn_c's modified insertion sort (knncuda.cu:882-912, same as the device kernel :149-195): element i is

@@ -151,6 +151,7 @@ SIGNATURES = {
          _P, _P, _P, _P, C.POINTER(C.c_int)],
     ),
     "perch_render_cost": (C.c_int, [_P, C.c_char_p, _P, C.c_int, _P, _P, _P, C.POINTER(perch_params), C.POINTER(perch_outputs)]),
+    "perch_render_cost_unfused": (C.c_int, [_P, _P, C.c_int, _P, _P, _P, C.POINTER(perch_params), C.POINTER(perch_outputs)]),
     "perch_render_cost_device": (C.c_int, [_P, _P, C.c_int, _P, _P, _P, C.POINTER(perch_params), _P, _P]),
     "perch_device_alloc": (C.c_int, [_P, C.c_size_t, C.POINTER(_P)]),
     "perch_device_free": (C.c_int, [_P, _P]),

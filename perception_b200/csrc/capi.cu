@@ -249,11 +249,19 @@ int fill_pose_args(perch_ctx* c, const perch_params* p, perch::PoseArgs& a) {
     return PERCH_OK;
 }
 
+// 6-DoF calls restrict the nearest-neighbour search to the pose's label and read the observed labels on the device: refuse
+// them when perch_set_observed was given none (the kernels would dereference a null label array).
+int fail_unlabelled() {
+    return fail(PERCH_ERR_INVALID, "pose_segmentation_label given but perch_set_observed was called without observed labels");
+}
+
+// `a.pose_label` must already say whether the call is 6-DoF (null = 3-DoF); everything else of `a` is filled here.
 int prepare_cost_args(perch_ctx* c, const perch_params* p, perch::PoseArgs& a, bool& color) {
     if (p->stride <= 0 || c->cam.width % p->stride != 0)
         return fail(PERCH_ERR_INVALID, "stride %d must divide the image width %d (compute_point_clouds.cuh:271)",
                     p->stride, c->cam.width);
     if (p->cost_type < 0 || p->cost_type > 2) return fail(PERCH_ERR_INVALID, "cost_type %d not in {0,1,2}", p->cost_type);
+    if (a.pose_label && c->n_obs > 0 && !c->obs_has_label) return fail_unlabelled();
     if (c->grid_res != p->sensor_resolution) {
         int rc = build_grid(c, p->sensor_resolution);
         if (rc) return rc;
@@ -332,6 +340,7 @@ int prepare_target_normals(perch_ctx* c, int k) {
 int run_gicp(perch_ctx* c, const perch_params* p, const perch::PoseArgs& base, int n_poses, float* d_poses_out,
              float* d_transforms, int* d_iterations, float* d_error, int* launches) {
     if (n_poses <= 0) return PERCH_OK;
+    if (base.pose_label && c->n_obs > 0 && !c->obs_has_label) return fail_unlabelled();
     const int W = c->cam.width, H = c->cam.height, s = p->stride;
     if (s <= 0 || W % s != 0)
         return fail(PERCH_ERR_INVALID, "stride %d must divide the image width %d (compute_point_clouds.cuh:271)", s, W);
@@ -887,10 +896,10 @@ int perch_render_cost_device(perch_ctx* c, const float* d_poses16, int n_poses, 
     DeviceGuard g(c->device);
     perch::PoseArgs a;
     bool color = false;
+    a.pose_label = d_pose_label;
     if ((rc = prepare_cost_args(c, p, a, color))) return rc;
     a.poses = reinterpret_cast<const perch::Mat4*>(d_poses16);
     a.pose_model_map = d_pose_model_map;
-    a.pose_label = d_pose_label;
     a.pose_obs_total = d_pose_obs_total;
     a.n_poses = n_poses;
     a.out_costs = d_costs3p;
@@ -1311,8 +1320,9 @@ int perch_detail::render_cost_impl(perch_ctx* c, const char* stage, const PoseIn
     if (do_cost) {
         perch::PoseArgs a;
         bool color = false;
+        a.pose_label = base.pose_label;
         if ((rc = prepare_cost_args(c, p, a, color))) return rc;
-        a.poses = base.poses; a.pose_model_map = base.pose_model_map; a.pose_label = base.pose_label;
+        a.poses = base.poses; a.pose_model_map = base.pose_model_map;
         a.pose_obs_total = base.pose_obs_total; a.n_poses = n_poses;
         a.out_costs = d_costs;
         a.out_counts = d_counts;

@@ -190,6 +190,27 @@ class Renderer:
 
         return self._run_stage(stage, P, prm, call, cloud_capacity, want_dc_index)
 
+    def render_cost_unfused(self, poses, pose_model_map, pose_segmentation_label=None, pose_observed_points_total=None, *,
+                            stride=1, cost_type=0, calculate_observed_cost=True, sensor_resolution=0.01,
+                            color_distance_threshold=20.0, occlusion_threshold=1.0):
+        """perch_render_cost_unfused: the COST outputs through the unfused kernels (full raster -> cloud -> brute-force
+        nearest neighbour -> counters); a device-side cross-check of the fused kernel at any batch size."""
+        P4 = _c(poses, np.float32).reshape(-1, 16)
+        P = len(P4)
+        pmm = _c(pose_model_map, np.int32).reshape(-1)
+        plab = None
+        if pose_segmentation_label is not None and len(pose_segmentation_label) > 0:
+            plab = _c(pose_segmentation_label, np.int32).reshape(-1)
+        ptot = None if pose_observed_points_total is None else _c(pose_observed_points_total, np.float32).reshape(-1)
+        prm = perch_params(stride, cost_type, int(bool(calculate_observed_cost)), sensor_resolution, color_distance_threshold,
+                           occlusion_threshold, 0, 0, 0, 0, -1.0, -1.0)
+
+        def call(out):
+            return self._lib.perch_render_cost_unfused(self._h, _ptr(P4), P, _ptr(pmm), _ptr(plab), _ptr(ptot), C.byref(prm),
+                                                       C.byref(out))
+
+        return self._run_stage("COST", P, prm, call)
+
     def _run_stage(self, stage: str, P: int, prm, call, cloud_capacity=None, want_dc_index=False):
         """Allocate the host outputs `stage` produces for P poses, run `call(perch_outputs)`, return them as a dict."""
         out = perch_outputs()

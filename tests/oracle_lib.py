@@ -145,6 +145,34 @@ class Oracle:
                               _p(rc), _p(oc), _p(dc), _p(counts), _p(near), C.c_double(color_eps))
         return {"rendered_cost": rc, "observed_cost": oc, "points_diff_cost": dc, "counts": counts, "near_threshold": near}
 
+    def score_poses(self, tris, tris_model_count, poses, pose_model_map, width, height, proj, source_depth, source_label,
+                    pose_label, cx, cy, fx, fy, depth_factor, stride, obs_xyz, obs_rgb, obs_label, pose_obs_total, cost_type,
+                    calc_observed, sensor_resolution, color_distance_threshold, occlusion_threshold=1.0):
+        """oracle_score_poses: render + cost per pose (OpenMP over poses), no images kept -- full-size parity checks."""
+        tris = np.ascontiguousarray(tris, dtype=TRIANGLE_DTYPE)
+        cnt = _c(tris_model_count, np.int32)
+        P4 = _c(poses, np.float32).reshape(-1, 16)
+        P = len(P4)
+        pmm = _c(pose_model_map, np.int32)
+        proj = _c(proj, np.float32).reshape(16)
+        sd = _c(source_depth, np.int32).reshape(-1)
+        sl = None if source_label is None else _c(source_label, np.uint8).reshape(-1)
+        pl = None if pose_label is None else _c(pose_label, np.int32)
+        ox = _c(obs_xyz, np.float32).reshape(-1, 3)
+        n_obs = len(ox)
+        orgb = np.zeros((3, n_obs), np.uint8) if obs_rgb is None else _c(obs_rgb, np.uint8).reshape(3, n_obs)
+        ol = None if obs_label is None else _c(obs_label, np.int32)
+        tot = None if pose_obs_total is None else _c(pose_obs_total, np.float32)
+        rc, oc, dc = np.zeros(P, np.float32), np.zeros(P, np.float32), np.zeros(P, np.float32)
+        counts = np.zeros((3, P), np.int32)
+        self.lib.oracle_score_poses(_p(tris), C.c_int(len(tris)), _p(P4), C.c_int(P), _p(pmm), _p(cnt), C.c_int(len(cnt)),
+                                    C.c_int(width), C.c_int(height), _p(proj), _p(sd), _p(sl), _p(pl),
+                                    C.c_float(occlusion_threshold), C.c_float(cx), C.c_float(cy), C.c_float(fx), C.c_float(fy),
+                                    C.c_float(depth_factor), C.c_int(stride), _p(ox), _p(orgb), _p(ol), C.c_int(n_obs), _p(tot),
+                                    C.c_int(cost_type), C.c_int(int(calc_observed)), C.c_float(sensor_resolution),
+                                    C.c_float(color_distance_threshold), _p(rc), _p(oc), _p(dc), _p(counts))
+        return {"rendered_cost": rc, "observed_cost": oc, "points_diff_cost": dc, "counts": counts}
+
     def color_distance_rgb(self, c1, c2):
         return self.lib.oracle_color_distance_rgb(*[int(v) for v in c1], *[int(v) for v in c2])
 

@@ -228,3 +228,29 @@ def test_oracle_matches_reference_golden(orc, name):
             # wherever they agree on depth the colour must agree too, except equal-depth ties
             same = a == b
             assert np.count_nonzero((g["ref_rgb"] != out["rgb"]).any(0) & same) <= int(g["race_budget"])
+
+
+@pytest.mark.parametrize("dof6", [False, True])
+def test_score_poses_equals_render_then_costs(dof6):
+    """oracle_score_poses (per pose, OpenMP, no images kept -- what the full-size GPU parity tests and bench.py's
+    parity_check call) == oracle_render + oracle_costs on the whole batch, colour cost included."""
+    from scenes import make_case, observed_3dof, observed_6dof, poses_near_gt
+    orc = Oracle()
+    case = make_case(600, 3, 42)
+    s = case.scene
+    stride = 8 if dof6 else 4
+    obs = observed_6dof(case, stride, orc) if dof6 else observed_3dof(case, stride, orc)
+    poses, pmm, lab = poses_near_gt(case, 12)
+    lab = lab if dof6 else None
+    slab = s.source_label if dof6 else None
+    olab = obs["label"] if dof6 else None
+    tot = np.full(12, 100, np.float32)
+    ct = 2 if dof6 else 1
+    d, c = orc.render(s.tris, s.tris_model_count, poses, pmm, case.width, case.height, case.proj, s.source_depth, slab, lab)
+    a = orc.costs(d, c, case.width, case.height, case.cx, case.cy, case.fx, case.fy, 100.0, stride, lab, obs["aos"], obs["rgb"],
+                  olab, tot, ct, True, 0.01, 20.0)
+    b = orc.score_poses(s.tris, s.tris_model_count, poses, pmm, case.width, case.height, case.proj, s.source_depth, slab, lab,
+                        case.cx, case.cy, case.fx, case.fy, 100.0, stride, obs["aos"], obs["rgb"], olab, tot, ct, True, 0.01, 20.0)
+    assert a["counts"][0].sum() > 0
+    for k in ("counts", "rendered_cost", "observed_cost", "points_diff_cost"):
+        assert np.array_equal(a[k], b[k]), k
