@@ -253,6 +253,52 @@ typedef struct perch_hit {
 int perch_topk(const float* rendered_cost, const float* observed_cost, const int* pose_model_map, int n_poses,
                int pose_id_offset, int n_models, int k, perch_hit* out_hits /* n_models*k, cost=INT32_MAX pads */);
 
+/* ==== a scene in one call, pose list sharded over GPUs =================================================== */
+/* The reference scores a scene's candidates in gpu_batch_size batches on one GPU (search_env.cpp:2504-2525) and takes the
+ * per-model argmin on the host afterwards (2542-2583).  perch_score_scene is that loop plus the argmin as ONE call: host
+ * pose batch in (pinned memory makes the copies asynchronous), fused render+cost kernel, per-model top-k ON THE DEVICE
+ * (same rule as perch_topk), and -- when the context belongs to a communicator -- an ncclAllGather of the k x 16 B per
+ * model over NVLink, all on the context's stream with one host synchronisation; the gathered records are merged by
+ * (cost, pose id) on the host, so out_hits (n_models x k, cost = INT32_MAX pads) is the SCENE's result on every rank.
+ * pose_id_offset = global id of this call's first pose (the rank's block offset).  out (may be NULL) receives this
+ * rank's rendered_cost / observed_cost / points_diff_cost / counts as in perch_render_cost; the other fields are ignored.
+ * Limits: n_models <= 255, n_poses <= 2^24 per call, do_icp = 0.  Every rank of a communicator must make the call (an
+ * empty block is fine: n_poses = 0). */
+int perch_score_scene(perch_ctx* ctx, const float* poses16, int n_poses, const int* pose_model_map,
+                      const int* pose_segmentation_label, const float* pose_observed_points_total,
+                      const perch_params* params, int pose_id_offset, int n_models, int k, perch_outputs* out,
+                      perch_hit* out_hits);
+/* One process per GPU (torchrun, MPI -- the reference distributes work over MPI ranks, search_env.cpp:920-1023): rank 0
+ * obtains an id, the launcher's own channel broadcasts the PERCH_COMM_ID_BYTES bytes, every rank attaches its context.
+ * n_ranks = 1 detaches.  Replaces nothing in the reference (it has no multi-GPU path). */
+#define PERCH_COMM_ID_BYTES 128
+int perch_comm_unique_id(void* out_id, size_t bytes);
+int perch_comm_init_rank(perch_ctx* ctx, int n_ranks, int rank, const void* id_bytes);
+int perch_comm_destroy(perch_ctx* ctx);
+/* One process, n devices: one context, one host thread and one stream per device, ncclCommInitAll.  The setters below
+ * replicate models / scene / observed cloud on every device in parallel; perch_multi_context(m, i) exposes device i's
+ * context for anything else (same call on each).  perch_multi_score cuts the pose list into contiguous blocks
+ * [r*P/n, (r+1)*P/n) -- pose ids stay monotone, so the first of equal costs still wins -- scores them concurrently and
+ * returns the merged per-model top-k; `out` arrays are sized for all n_poses (counts: 3 x n_poses). */
+typedef struct perch_multi perch_multi;
+int perch_create_multi(const int* devices, int n_devices, perch_multi** out);
+void perch_destroy_multi(perch_multi* m);
+int perch_multi_size(perch_multi* m);
+perch_ctx* perch_multi_context(perch_multi* m, int i);
+int perch_multi_set_camera(perch_multi* m, int width, int height, const float proj16[16], float cx, float cy, float fx,
+                           float fy, float depth_factor);
+int perch_multi_set_models(perch_multi* m, const perch_triangle* tris, int64_t n_tris, const int* tris_model_count,
+                           int n_models);
+int perch_multi_set_scene(perch_multi* m, const int32_t* source_depth, const uint8_t* source_red,
+                          const uint8_t* source_green, const uint8_t* source_blue, const uint8_t* source_mask_label);
+int perch_multi_set_observed(perch_multi* m, const float* observed_xyz_aos, const uint8_t* observed_color_soa,
+                             const int* observed_label, int n_obs);
+int perch_multi_score(perch_multi* m, const float* poses16, int n_poses, const int* pose_model_map,
+                      const int* pose_segmentation_label, const float* pose_observed_points_total,
+                      const perch_params* params, int n_models, int k, perch_outputs* out, perch_hit* out_hits);
+/* Max over devices of the fused kernel's device time in the last perch_multi_score. */
+int perch_multi_last_timing(perch_multi* m, float* max_kernel_ms);
+
 /* ==== caller glue: candidate ObjectStates instead of matrices ============================== */
 /* The steps sbpl_perception::EnvObjectRecognition performs on the host, serially, on either side of
  * render_cuda_multi_unified -- GenerateSuccessorStates + IsValidPose before it (search_env.cpp:7056-7490, 309-528),

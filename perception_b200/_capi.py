@@ -152,6 +152,22 @@ SIGNATURES = {
     ),
     "perch_render_cost": (C.c_int, [_P, C.c_char_p, _P, C.c_int, _P, _P, _P, C.POINTER(perch_params), C.POINTER(perch_outputs)]),
     "perch_render_cost_unfused": (C.c_int, [_P, _P, C.c_int, _P, _P, _P, C.POINTER(perch_params), C.POINTER(perch_outputs)]),
+    "perch_score_scene": (C.c_int, [_P, _P, C.c_int, _P, _P, _P, C.POINTER(perch_params), C.c_int, C.c_int, C.c_int,
+                                    C.POINTER(perch_outputs), _P]),
+    "perch_comm_unique_id": (C.c_int, [_P, C.c_size_t]),
+    "perch_comm_init_rank": (C.c_int, [_P, C.c_int, C.c_int, _P]),
+    "perch_comm_destroy": (C.c_int, [_P]),
+    "perch_create_multi": (C.c_int, [_P, C.c_int, C.POINTER(_P)]),
+    "perch_destroy_multi": (None, [_P]),
+    "perch_multi_size": (C.c_int, [_P]),
+    "perch_multi_context": (_P, [_P, C.c_int]),
+    "perch_multi_set_camera": (C.c_int, [_P, C.c_int, C.c_int, _P, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float]),
+    "perch_multi_set_models": (C.c_int, [_P, _P, C.c_int64, _P, C.c_int]),
+    "perch_multi_set_scene": (C.c_int, [_P, _P, _P, _P, _P, _P]),
+    "perch_multi_set_observed": (C.c_int, [_P, _P, _P, _P, C.c_int]),
+    "perch_multi_score": (C.c_int, [_P, _P, C.c_int, _P, _P, _P, C.POINTER(perch_params), C.c_int, C.c_int,
+                                    C.POINTER(perch_outputs), _P]),
+    "perch_multi_last_timing": (C.c_int, [_P, C.POINTER(C.c_float)]),
     "perch_render_cost_device": (C.c_int, [_P, _P, C.c_int, _P, _P, _P, C.POINTER(perch_params), _P, _P]),
     "perch_device_alloc": (C.c_int, [_P, C.c_size_t, C.POINTER(_P)]),
     "perch_device_free": (C.c_int, [_P, _P]),
@@ -176,8 +192,25 @@ SIGNATURES = {
 }
 
 PERCH_COMPOSE_NONE, PERCH_COMPOSE_REPLACE, PERCH_COMPOSE_MERGE = range(3)
+PERCH_COMM_ID_BYTES = 128
 
 _lib = None
+
+
+def _preload_nccl() -> None:
+    """libperch_b200.so links libnccl.so.2 (the top-k all-gather of a sharded pose list).  In a process that also imports
+    PyTorch, the NCCL that PyTorch bundles must be the one behind that soname -- libtorch_cuda.so needs symbols the
+    system copy may lack -- whichever of the two libraries is loaded first; so load PyTorch's copy first when there is one.
+    Without PyTorch the system libnccl.so.2 is found by the dynamic linker as usual."""
+    import sys
+    for base in sys.path:
+        cand = Path(base) / "nvidia" / "nccl" / "lib" / "libnccl.so.2"
+        if cand.exists():
+            try:
+                C.CDLL(str(cand), mode=C.RTLD_GLOBAL)
+            except OSError:
+                pass
+            return
 
 
 def load_library(path: os.PathLike | None = None) -> C.CDLL:
@@ -191,6 +224,7 @@ def load_library(path: os.PathLike | None = None) -> C.CDLL:
         raise ImportError(
             f"{p} not found: build it with `make` (nvcc, sm_100a). perception_b200 has no CPU fallback."
         )
+    _preload_nccl()
     lib = C.CDLL(str(p))
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(lib, name)  # AttributeError here == the library does not export a declared symbol

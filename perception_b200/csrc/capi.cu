@@ -36,6 +36,32 @@ int fail(int code, const char* fmt, ...) {
 }
 }  // namespace perch_detail
 
+
+namespace perch_detail {
+int ensure_scratch(perch_ctx* c, size_t bytes) {
+    if (bytes <= c->scratch_bytes) return PERCH_OK;
+    if (c->d_scratch) cudaFree(c->d_scratch);
+    c->d_scratch = nullptr;
+    c->scratch_bytes = 0;
+    PERCH_CU(cudaMalloc(&c->d_scratch, bytes));
+    c->scratch_bytes = bytes;
+    size_t free_b = 0, total_b = 0;  // high-water mark moves when the scratch grows, not on every call (utils.cuh:18-23)
+    if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess)
+        c->stats.peak_memory_usage = std::max(c->stats.peak_memory_usage, (double)(total_b - free_b) / 1024.0 / 1024.0);
+    return PERCH_OK;
+}
+
+int ensure_pinned(perch_ctx* c, size_t bytes) {
+    if (bytes <= c->pinned_bytes) return PERCH_OK;
+    if (c->h_pinned) cudaFreeHost(c->h_pinned);
+    c->h_pinned = nullptr;
+    c->pinned_bytes = 0;
+    PERCH_CU(cudaMallocHost(&c->h_pinned, bytes));
+    c->pinned_bytes = bytes;
+    return PERCH_OK;
+}
+}  // namespace perch_detail
+
 namespace {
 using perch_detail::fail;
 
@@ -61,19 +87,7 @@ int upload(T** dst, const T* src, size_t n, cudaStream_t s) {
     return PERCH_OK;
 }
 
-// Bump allocator over the context scratch buffer (256-byte aligned slices).
-struct Scratch {
-    perch_ctx* c;
-    size_t off = 0;
-    explicit Scratch(perch_ctx* ctx) : c(ctx) {}
-    static size_t align(size_t b) { return (b + 255) & ~(size_t)255; }
-    template <class T>
-    T* take(size_t n) {
-        T* p = reinterpret_cast<T*>(static_cast<char*>(c->d_scratch) + off);
-        off += align(n * sizeof(T));
-        return p;
-    }
-};
+using perch_detail::Scratch;
 
 void note_memory(perch_ctx* c) {
     size_t free_b = 0, total_b = 0;
@@ -83,17 +97,7 @@ void note_memory(perch_ctx* c) {
     }
 }
 
-int ensure_scratch(perch_ctx* c, size_t bytes) {
-    if (bytes <= c->scratch_bytes) return PERCH_OK;
-    if (c->d_scratch) cudaFree(c->d_scratch);
-    c->d_scratch = nullptr;
-    c->scratch_bytes = 0;
-    CU(cudaMalloc(&c->d_scratch, bytes));
-    c->scratch_bytes = bytes;
-    note_memory(c);  // high-water mark moves when the scratch grows, not on every call
-    return PERCH_OK;
-}
-
+using perch_detail::ensure_scratch;
 
 int env_int(const char* name, int dflt) {
     const char* v = getenv(name);
@@ -463,6 +467,20 @@ int check_err_flag(perch_ctx* c) {
 
 }  // namespace
 
+namespace perch_detail {
+int prepare_fused_cost(perch_ctx* c, const perch_params* p, perch::PoseArgs& a, bool& color) {
+    int rc = check_ready(c, true);
+    if (rc) return rc;
+    return prepare_cost_args(c, p, a, color);
+}
+int report_err_flag(int flag) {
+    if (!flag) return PERCH_OK;
+    if (flag & 2) return fail(PERCH_ERR_INVALID, "a state names a model_id outside [0, n_models)");
+    if (flag & 4) return fail(PERCH_ERR_INVALID, "a state's segmentation_label_id has no entry in the observed labels");
+    return fail(PERCH_ERR_CUDA, "internal error: a fragment fell outside its pose tile (flag %d)", flag);
+}
+}  // namespace perch_detail
+
 extern "C" {
 
 const char* perch_last_error(void) { return g_err.c_str(); }
@@ -509,6 +527,7 @@ void perch_destroy(perch_ctx* c) {
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
+    perch_detail::destroy_comm(c);
     perch_detail::destroy_states(c);
     cudaEventDestroy(c->ev0);
     cudaEventDestroy(c->ev1);

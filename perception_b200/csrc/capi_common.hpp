@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 
 #include "context.hpp"
+#include "kernels.cuh"
 #include "perch_b200.h"
 
 namespace perch_detail {
@@ -21,6 +22,26 @@ struct PoseInputs {
 };
 int render_cost_impl(perch_ctx* c, const char* stage, const PoseInputs& in, int n_poses, const perch_params* p,
                      perch_outputs* out);
+
+// Bump allocator over the context scratch buffer (256-byte aligned slices).
+struct Scratch {
+    perch_ctx* c;
+    size_t off = 0;
+    explicit Scratch(perch_ctx* ctx) : c(ctx) {}
+    static size_t align(size_t b) { return (b + 255) & ~(size_t)255; }
+    template <class T>
+    T* take(size_t n) {
+        T* p = reinterpret_cast<T*>(static_cast<char*>(c->d_scratch) + off);
+        off += align(n * sizeof(T));
+        return p;
+    }
+};
+int ensure_scratch(perch_ctx* c, size_t bytes);  // per-call device scratch, grown on demand (capi.cu)
+int ensure_pinned(perch_ctx* c, size_t bytes);   // the context's pinned host staging buffer (capi.cu)
+// readiness checks + grid (re)build + PoseArgs of the fused cost kernel; a.pose_label must be set by the caller first
+int prepare_fused_cost(perch_ctx* c, const perch_params* p, perch::PoseArgs& a, bool& color);
+int report_err_flag(int flag);  // d_err_flag value -> status + message
+void destroy_comm(perch_ctx* c);  // capi_multi.cu
 
 void destroy_states(perch_ctx* c);  // capi_states.cu
 

@@ -174,4 +174,9 @@ struct perch_ctx {
     int flush_value = 0;
     void* h_pinned = nullptr;
     size_t pinned_bytes = 0;
+    // NCCL communicator of a sharded pose list (capi_multi.cu): one rank per context, either one process per GPU
+    // (perch_comm_init_rank) or all devices of one process (perch_create_multi); null = single GPU, no gather
+    void* comm = nullptr;              // ncclComm_t
+    int comm_rank = 0, comm_size = 1;
+    bool comm_owned = false;
 };

@@ -58,6 +58,21 @@ cudaError_t launch_raster_images(const PoseArgs& a, cudaStream_t stream);
 cudaError_t launch_single_clear(unsigned long long* keys, int n, cudaStream_t stream);
 cudaError_t launch_resolve_single(const PoseArgs& a, cudaStream_t stream);
 
+// ---- per-model top-k of a scored batch (topk.cu) -----------------------------------------------------------------------
+constexpr int kTopkMaxModels = 255;       // the key's top byte carries the model; 0xFF marks a skipped pose
+constexpr int kTopkMaxPoses = 1 << 24;    // ... and its low 24 bits the pose's index inside the call
+struct TopkArgs {
+    const float* costs = nullptr;          // 3 x n_poses as the fused kernel writes them: rendered, observed, points_diff
+    const int* pose_model_map = nullptr;
+    int n_poses = 0;
+    int pose_id_offset = 0;                // global id of the call's first pose (rank offset of a sharded list)
+    int n_models = 0;
+    int k = 0;
+    unsigned long long* keys = nullptr;    // n_poses scratch
+    perch_hit* hits = nullptr;             // n_models x k, unordered within a model, cost = INT32_MAX pads
+};
+cudaError_t launch_topk(const TopkArgs& a, cudaStream_t stream);
+
 // ---- full-resolution rasteriser (raster_full.cu): stages RENDER / DEBUG, composition, perch_tree_flags ---------------
 struct FullRasterArgs {
     ModelsDev models;

@@ -513,6 +513,29 @@ class Renderer:
                                                     C.byref(prm), C.c_void_p(d_costs),
                                                     C.c_void_p(d_counts) if d_counts else None))
 
+    # -- a scene in one call: costs + per-model top-k reduced on the device, gathered across ranks ---------------------------
+    def comm_init(self, n_ranks: int, rank: int, comm_id: bytes) -> None:
+        """Attach this context to a communicator of `n_ranks` (one process per GPU): `comm_id` = comm_unique_id() of rank
+        0, distributed by the launcher's own channel.  score_scene then all-gathers the per-rank top-k over NCCL."""
+        assert len(comm_id) == _capi.PERCH_COMM_ID_BYTES
+        buf = (C.c_char * len(comm_id)).from_buffer_copy(comm_id)
+        self._ck(self._lib.perch_comm_init_rank(self._h, n_ranks, rank, C.cast(buf, C.c_void_p)))
+
+    def comm_destroy(self) -> None:
+        self._ck(self._lib.perch_comm_destroy(self._h))
+
+    def score_scene(self, poses, pose_model_map, pose_segmentation_label=None, pose_observed_points_total=None, *,
+                    n_models: int, k: int = 1, pose_id_offset: int = 0, out: Optional[dict] = None, want_costs=True,
+                    stride=1, cost_type=0, calculate_observed_cost=True, sensor_resolution=0.01,
+                    color_distance_threshold=20.0, occlusion_threshold=1.0):
+        """perch_score_scene: this rank's pose block -> fused kernel -> device top-k -> (NCCL all-gather) -> merged
+        per-model best-k of the whole scene.  Returns (hits (n_models, k) structured array, costs dict or None).
+        `out` = preallocated (e.g. pinned) arrays rendered_cost / observed_cost / points_diff_cost (P,) and counts (3,P)."""
+        return _score_scene(self._lib, self._lib.perch_score_scene, self._h, poses, pose_model_map, pose_segmentation_label,
+                            pose_observed_points_total, n_models, k, pose_id_offset, out, want_costs,
+                            perch_params(stride, cost_type, int(bool(calculate_observed_cost)), sensor_resolution,
+                                         color_distance_threshold, occlusion_threshold, 0, 0, 0, 0, -1.0, -1.0))
+
     def synchronize(self) -> None:
         self._ck(self._lib.perch_synchronize(self._h))
 
@@ -533,6 +556,107 @@ class Renderer:
         return dist, index
 
 
+HIT_DTYPE = np.dtype([("cost", "<i4"), ("pose_id", "<i4"), ("rendered_cost", "<f4"), ("observed_cost", "<f4")])
+
+
+def comm_unique_id() -> bytes:
+    """perch_comm_unique_id: the bytes rank 0 hands to every rank's Renderer.comm_init."""
+    lib = _capi.load_library()
+    buf = C.create_string_buffer(_capi.PERCH_COMM_ID_BYTES)
+    _capi.check(lib, lib.perch_comm_unique_id(C.cast(buf, C.c_void_p), _capi.PERCH_COMM_ID_BYTES))
+    return buf.raw
+
+
+def _score_scene(lib, fn, handle, poses, pmm, plab, ptot, n_models, k, pose_id_offset, out, want_costs, prm):
+    P4 = _c(poses, np.float32).reshape(-1, 16)
+    P = len(P4)
+    pmm = _c(pmm, np.int32).reshape(-1)
+    assert len(pmm) == P, "pose_model_map length != number of poses"
+    plab = None if plab is None or len(plab) == 0 else _c(plab, np.int32).reshape(-1)
+    ptot = None if ptot is None else _c(ptot, np.float32).reshape(-1)
+    res = None
+    po = perch_outputs()
+    if want_costs:
+        res = out if out is not None else {"rendered_cost": np.zeros(P, np.float32), "observed_cost": np.zeros(P, np.float32),
+                                           "points_diff_cost": np.zeros(P, np.float32), "counts": np.zeros((3, P), np.int32)}
+        assert res["counts"].shape == (3, P) and res["rendered_cost"].shape == (P,)
+        po.rendered_cost = res["rendered_cost"].ctypes.data
+        po.observed_cost = res["observed_cost"].ctypes.data
+        po.points_diff_cost = res["points_diff_cost"].ctypes.data
+        po.counts = res["counts"].ctypes.data
+    hits = np.zeros((n_models, k), dtype=HIT_DTYPE)
+    args = [handle, _ptr(P4), P, _ptr(pmm), _ptr(plab), _ptr(ptot), C.byref(prm)]
+    if pose_id_offset is not None:
+        args.append(pose_id_offset)
+    _capi.check(lib, fn(*args, n_models, k, C.byref(po) if want_costs else None, _ptr(hits)))
+    return hits, res
+
+
+class MultiRenderer:
+    """perch_multi: one process, several GPUs -- a context, a host thread and a stream per device, the pose list cut
+    into contiguous blocks, per-device top-k all-gathered over NCCL."""
+
+    def __init__(self, devices: Sequence[int]):
+        self._lib = _capi.load_library()
+        dev = np.ascontiguousarray(devices, dtype=np.int32)
+        h = C.c_void_p()
+        _capi.check(self._lib, self._lib.perch_create_multi(_ptr(dev), len(dev), C.byref(h)))
+        self._h = h
+        self.n_devices = len(dev)
+
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            self._lib.perch_destroy_multi(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def _ck(self, code: int) -> None:
+        _capi.check(self._lib, code)
+
+    def set_camera(self, width, height, proj_mat, cx, cy, fx, fy, depth_factor=100.0) -> None:
+        p = _c(proj_mat, np.float32).reshape(16)
+        self._ck(self._lib.perch_multi_set_camera(self._h, width, height, _ptr(p), cx, cy, fx, fy, depth_factor))
+
+    def set_models(self, tris, tris_model_count) -> None:
+        t = np.ascontiguousarray(tris, dtype=TRIANGLE_DTYPE)
+        cnt = _c(tris_model_count, np.int32)
+        self._ck(self._lib.perch_multi_set_models(self._h, _ptr(t), len(t), _ptr(cnt), len(cnt)))
+
+    def set_scene(self, source_depth, source_color=None, source_mask_label=None) -> None:
+        d = _c(source_depth, np.int32).reshape(-1)
+        planes = [None] * 3 if source_color is None else [_c(source_color[k], np.uint8).reshape(-1) for k in range(3)]
+        lab = None if source_mask_label is None or len(source_mask_label) == 0 else _c(source_mask_label, np.uint8).reshape(-1)
+        self._ck(self._lib.perch_multi_set_scene(self._h, _ptr(d), _ptr(planes[0]), _ptr(planes[1]), _ptr(planes[2]), _ptr(lab)))
+
+    def set_observed(self, observed_xyz, observed_color=None, observed_label=None) -> None:
+        xyz = _c(observed_xyz, np.float32).reshape(-1, 3)
+        n = len(xyz)
+        col = None if observed_color is None else _c(observed_color, np.uint8).reshape(3, n)
+        lab = None if observed_label is None else _c(observed_label, np.int32).reshape(n)
+        self._ck(self._lib.perch_multi_set_observed(self._h, _ptr(xyz), _ptr(col), _ptr(lab), n))
+
+    def score_scene(self, poses, pose_model_map, pose_segmentation_label=None, pose_observed_points_total=None, *,
+                    n_models: int, k: int = 1, out: Optional[dict] = None, want_costs=True, stride=1, cost_type=0,
+                    calculate_observed_cost=True, sensor_resolution=0.01, color_distance_threshold=20.0,
+                    occlusion_threshold=1.0):
+        """perch_multi_score on the WHOLE pose list (sharded inside the library).  Returns (hits, costs) like
+        Renderer.score_scene; pose ids are indices into the list."""
+        return _score_scene(self._lib, self._lib.perch_multi_score, self._h, poses, pose_model_map, pose_segmentation_label,
+                            pose_observed_points_total, n_models, k, None, out, want_costs,
+                            perch_params(stride, cost_type, int(bool(calculate_observed_cost)), sensor_resolution,
+                                         color_distance_threshold, occlusion_threshold, 0, 0, 0, 0, -1.0, -1.0))
+
+    def last_kernel_ms(self) -> float:
+        ms = C.c_float(0)
+        self._ck(self._lib.perch_multi_last_timing(self._h, C.byref(ms)))
+        return ms.value
+
+
 def topk(rendered_cost, observed_cost, pose_model_map, n_models: int, k: int = 1, pose_id_offset: int = 0) -> np.ndarray:
     """Per-model best-k candidates by the caller's rule (search_env.cpp:2016-2036, 2542-2583).  Returns a
     structured array (n_models, k) with fields cost, pose_id, rendered_cost, observed_cost (cost INT32_MAX = empty)."""
@@ -540,8 +664,7 @@ def topk(rendered_cost, observed_cost, pose_model_map, n_models: int, k: int = 1
     r = _c(rendered_cost, np.float32)
     o = _c(observed_cost, np.float32)
     m = _c(pose_model_map, np.int32)
-    dt = np.dtype([("cost", "<i4"), ("pose_id", "<i4"), ("rendered_cost", "<f4"), ("observed_cost", "<f4")])
-    out = np.zeros((n_models, k), dtype=dt)
+    out = np.zeros((n_models, k), dtype=HIT_DTYPE)
     _capi.check(lib, lib.perch_topk(_ptr(r), _ptr(o), _ptr(m), len(r), pose_id_offset, n_models, k, _ptr(out)))
     return out
 
