@@ -5,12 +5,16 @@
   python bench.py --impl reference ...                     the reference's CPU scoring path (oracle port, host cores)
   python bench.py --impl reference-cuda ...                the reference's own CUDA kernels (oracle/_ref) on the GPU
 
-A step = one pass of the hot path over one batch of candidate poses per GPU (workload C2 of BASELINE.json configs[1]:
-16 384 6-DoF poses of a 20 000-triangle mesh against a 640x480 scene, stride 8, label-restricted cost_type 2).
-`value` times the kernel with inputs resident in HBM (CUDA events on the library's stream, L2 flushed between steps);
-`e2e` times the public host API (pinned host poses in, costs + top-k out, NCCL gather of the per-GPU top-k for N > 1);
-its steps are spread over --e2e-contexts contexts (default 2, one host thread each) so one step's copies overlap another's kernel.
-Prints ONE JSON line on rank 0.
+Workload C2 of BASELINE.json configs[1]: 16 384 6-DoF poses of a 20 000-triangle mesh against a 640x480 scene, stride 8,
+label-restricted cost_type 2 -- one such batch is a SCENE.  A step = --batches (default 40) scenes with DISTINCT pose
+batches per GPU, so that a step is >= 50 ms of device work and the timed region >= 1 s.
+`value`  : poses resident in HBM, the step's fused-kernel launches back to back on the library stream, CUDA events around
+           them, L2 flushed once per step.
+`e2e`    : every scene through the public host call perch_score_scene: pinned host poses in (H2D), fused kernel, per-model
+           top-k on the device, NCCL all-gather of the per-rank records (N > 1), costs + merged hits back (D2H).  Reported
+           strictly serial (one context, blocking calls) and pipelined (--e2e-contexts contexts, one host thread each).
+After the timed loops rank 0 checks what the timed launch of scene 0 produced against the CPU oracle (`parity_check`) and
+against the library's unfused kernels on every pose (`unfused_check`).  Prints ONE JSON line on rank 0.
 """
 from __future__ import annotations
 
@@ -90,17 +94,21 @@ class ClockSampler:
 
 
 # ---- workload ----------------------------------------------------------------------------------------------------------
-def build_workload(name: str, rank: int, device: int, n_poses: int | None, use_product: bool = True):
+def build_workload(name: str, rank: int, device: int, n_poses: int | None, use_product: bool = True, n_batches: int = 1,
+                   compute_proj_fn=None):
     """Everything untimed: mesh, scene, observed cloud, poses.  With use_product the scene is rasterised and
     back-projected by libperch_b200 (GPU); the reference arms use the CPU oracle instead so that none of this repo's
     kernels touch their inputs."""
     from perception_b200 import synth
-    from perception_b200.renderer import Renderer, compute_proj
 
     desc, n_tris, P, stride, dof6, cost_type, res, n_models = WORKLOADS[name]
     if n_poses:
         P = n_poses
-    proj = compute_proj(synth.camera_K(), W, H)
+    if compute_proj_fn is None:
+        from perception_b200.renderer import compute_proj as compute_proj_fn
+    if use_product:
+        from perception_b200.renderer import Renderer
+    proj = compute_proj_fn(synth.camera_K(), W, H)
     # SURVEY 8(d): mesh variants from seed 1000+m, r0 in [0.04, 0.12] m
     meshes = [synth.make_mesh(n_tris, seed=1000 + m, r0=0.09 if n_models == 1 else 0.05 + 0.06 * ((m * 7) % n_models) / n_models)
               for m in range(n_models)]
@@ -157,8 +165,30 @@ def build_workload(name: str, rank: int, device: int, n_poses: int | None, use_p
         poses = np.concatenate([synth.poses_3dof(scene, m, int((pmm == m).sum()), seed=1 + rank) for m in range(n_models)])
         plabel = None
         tot = synth.cylinder_counts(scene, obs["result_cloud_eigen"], poses, pmm)
+    # further scenes of a step: the same hypotheses displaced (distinct pose batches, same shape of work)
+    poses_b, tot_b = [poses], [tot]
+    for b in range(1, n_batches):
+        rng = np.random.default_rng(7919 * b + rank)
+        pb = poses.copy()
+        if dof6:
+            pb[:, :3, 3] += rng.uniform(-1.0, 1.0, size=(P, 3)).astype(np.float32)          # +-1 cm (pose units are cm)
+            tb = tot
+        else:
+            # rotate every hypothesis about the table normal through the table origin and shift it along the table
+            a = 0.002 * b
+            Rz = np.array([[np.cos(a), -np.sin(a), 0, 0.0005 * b], [np.sin(a), np.cos(a), 0, 0], [0, 0, 1, 0], [0, 0, 0, 1.0]])
+            M = scene.T_cam_table @ Rz @ np.linalg.inv(scene.T_cam_table)
+            q = poses.astype(np.float64)
+            q[:, :3, :] /= 100.0
+            q = M[None] @ q
+            q[:, :3, :] *= 100.0
+            pb = q.astype(np.float32)
+            tb = synth.cylinder_counts(scene, obs["result_cloud_eigen"], pb, pmm)
+        poses_b.append(pb)
+        tot_b.append(tb)
     wl = dict(name=name, desc=desc, n_tris=n_tris, n_models=n_models, P=P, stride=stride, dof6=dof6, cost_type=cost_type, res=res, n_obs=n_obs,
-              scene=scene, obs=obs, obs_label=obs_label, poses=poses, pmm=pmm, plabel=plabel, tot=tot, proj=proj)
+              scene=scene, obs=obs, obs_label=obs_label, poses=poses, pmm=pmm, plabel=plabel, tot=tot, proj=proj,
+              poses_b=poses_b, tot_b=tot_b)
     return r, wl
 
 
@@ -178,31 +208,106 @@ def measured_peak_gbs():
 
 
 # ---- arms ----------------------------------------------------------------------------------------------------------------
+KERNEL_SOURCES = ("perception_b200/csrc/pose_kernels.cu", "perception_b200/csrc/exact_math.cuh", "perception_b200/csrc/kernels.cuh",
+                  "perception_b200/csrc/context.hpp", "perception_b200/csrc/clusters.hpp", "perception_b200/csrc/clusters.cpp", "Makefile")
+
+
+def kernel_source_hash() -> str:
+    """sha256 over the sources that decide the fused kernel's instruction count: the committed ncu counters
+    (profiles/kernel_counters.json) are only used when they were captured from exactly these sources."""
+    import hashlib
+    h = hashlib.sha256()
+    for f in KERNEL_SOURCES:
+        h.update((ROOT / f).read_bytes())
+    return h.hexdigest()[:16]
+
+
+def rooflines(args, wl, P, kern_ms_per_launch, clocks):
+    """The bound that applies (warp-instruction issue) as `roofline`; SURVEY 8(d)'s HBM contract figure kept
+    beside it, labelled for what it is (the working set is L2-resident, so it is not a bound on this design)."""
+    peak, peak_kind = measured_peak_gbs()
+    bpp = algorithmic_bytes_per_pose(wl["n_tris"], wl["n_obs"])
+    achieved = P * bpp / (kern_ms_per_launch / 1e3) / 1e9
+    traffic = None
+    tfile = ROOT / "profiles" / "dram_traffic.json"
+    if tfile.exists():
+        try:
+            traffic = json.loads(tfile.read_text()).get(args.workload)
+        except Exception:
+            traffic = None
+    hbm = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+           "peak_kind": f"{peak_kind} copy bandwidth", "bytes_per_pose": bpp, "poses_per_launch": P,
+           "note": "SURVEY 8(d) algorithmic bytes / kernel time. Inapplicable as a bound: mesh, scene and observed cloud are "
+                   "L2-resident across poses" + (f", measured DRAM traffic {traffic} B per launch" if traffic else "")}
+    roof = dict(hbm, traffic=traffic, kernel="pose_kernel<MODE_COST>", kernel_ms=kern_ms_per_launch)
+    cfile = ROOT / "profiles" / "kernel_counters.json"
+    kc = None
+    if cfile.exists():
+        try:
+            kc = json.loads(cfile.read_text()).get(args.workload)
+        except Exception:
+            kc = None
+    src = kernel_source_hash()
+    if kc and kc.get("poses") == P and kc.get("source_sha16") == src and clocks.get("sm_mhz"):
+        sms = int(kc.get("sm_count", 148))
+        rate = kc["warp_inst_per_launch"] / (kern_ms_per_launch / 1e3)
+        peak_rate = sms * 4 * clocks["sm_mhz"] * 1e6
+        roof = {"bound": "issue", "achieved": rate / 1e9, "peak": peak_rate / 1e9, "unit": "G warp-inst/s",
+                "frac": rate / peak_rate, "traffic": traffic, "kernel": "pose_kernel<MODE_COST>", "kernel_ms": kern_ms_per_launch,
+                "warp_inst_per_pose": kc["warp_inst_per_launch"] / P, "poses_per_launch": P,
+                "peak_kind": f"{sms} SMs x 4 schedulers x {clocks['sm_mhz']:.0f} MHz sampled in this run",
+                "counter_source": kc.get("source"), "source_sha16": src, "hbm_contract": hbm}
+    else:
+        roof["note_issue"] = ("no warp-instruction count for these kernel sources (profiles/kernel_counters.json is for "
+                              f"{kc.get('source_sha16') if kc else None}, sources are {src}): issue roofline omitted")
+    return roof
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
     from perception_b200 import sharding
     from perception_b200 import synth
-    from perception_b200.renderer import Renderer, topk
+    from perception_b200.renderer import HIT_DTYPE, Renderer, comm_unique_id
 
     rank, local_rank, world = rank_info()
     if world > 1:
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    r, wl = build_workload(args.workload, rank, local_rank, args.poses)
+    strong = args.scaling == "strong"
+    B = max(1, args.batches)
+    n_poses = args.poses
+    P_scene = None
+    if strong:
+        # BASELINE configs[2] / [4]: the scene's pose list is fixed and cut into contiguous blocks, one per GPU
+        P_scene = args.poses or {"c3": 100000, "c5": 1000000}.get(args.workload, WORKLOADS[args.workload][2] * 8)
+        lo, hi = sharding.shard_range(P_scene, rank, world)
+        n_poses = hi - lo
+    r, wl = build_workload(args.workload, rank, local_rank, n_poses, n_batches=B)
     P = wl["P"]
+    n_models = wl["n_models"]
     kw = dict(stride=wl["stride"], cost_type=wl["cost_type"], calculate_observed_cost=True, sensor_resolution=wl["res"],
               color_distance_threshold=20.0, occlusion_threshold=1.0)
+    composed = None
+    if args.workload == "c3" and not args.no_compose:
+        # "inter-object occlusion" (BASELINE configs[2]): one object is already placed; it is rendered into the source
+        # image on the device (perch_compose_source, the reference's tree flow) and occludes every candidate behind it
+        sc = wl["scene"]
+        composed = dict(poses=synth.pose_to_mat4x4(sc.gt_poses[0])[None], pmm=np.array([sc.gt_models[0]], np.int32))
+        r.compose_source(composed["poses"], composed["pmm"], None, mode="merge")
+        wl["oracle_source_depth"] = r.get_source_depth().reshape(-1)  # composed image (pinned by tests/test_compose.py)
 
-    # device-resident inputs/outputs for `value`
-    d_poses = r.device_alloc(P * 64); r.h2d(d_poses, wl["poses"])
+    # ---- `value`: device-resident inputs / outputs, B launches per step ---------------------------------------------------
+    d_poses, d_tot, d_costs, d_counts = [], [], [], []
+    for b in range(B):
+        dp = r.device_alloc(P * 64); r.h2d(dp, wl["poses_b"][b]); d_poses.append(dp)
+        dt = r.device_alloc(P * 4); r.h2d(dt, wl["tot_b"][b]); d_tot.append(dt)
+        d_costs.append(r.device_alloc(P * 12))
+        d_counts.append(r.device_alloc(P * 12))
     d_pmm = r.device_alloc(P * 4); r.h2d(d_pmm, wl["pmm"])
     d_lab = None
     if wl["plabel"] is not None:
         d_lab = r.device_alloc(P * 4); r.h2d(d_lab, wl["plabel"])
-    d_tot = r.device_alloc(P * 4); r.h2d(d_tot, wl["tot"])
-    d_costs = r.device_alloc(P * 12)
-    d_counts = r.device_alloc(P * 12)
 
     def barrier():
         if world > 1:
@@ -211,9 +316,12 @@ def run_ours(args):
 
     def device_step():
         r.l2_flush()
-        r.render_cost_device(d_poses, P, d_pmm, d_lab, d_tot, d_costs, d_counts, **kw)
+        r.timer_start()
+        for b in range(B):
+            r.render_cost_device(d_poses[b], P, d_pmm, d_lab, d_tot[b], d_costs[b], d_counts[b], **kw)
+        r.timer_stop()
         r.synchronize()
-        return r.last_timing()[0]
+        return r.timer_elapsed()
 
     for _ in range(args.warmup):
         device_step()
@@ -221,144 +329,159 @@ def run_ours(args):
     barrier()
     sampler.start()
     t0 = time.perf_counter()
-    kernel_ms = [device_step() for _ in range(args.steps)]
+    step_ms = [device_step() for _ in range(args.steps)]
     barrier()
     wall_device_loop = time.perf_counter() - t0
-    total_ms = float(np.sum(kernel_ms))
+    total_ms = float(np.sum(step_ms))
+    counts0 = np.zeros((3, P), np.int32)
+    r.d2h(counts0, d_counts[0])          # what the TIMED launch of scene 0 produced
+    costs0 = np.zeros((3, P), np.float32)
+    r.d2h(costs0, d_costs[0])
 
-    # e2e: public host API, pinned host buffers, costs + per-model top-k back on the host, gather across ranks
+    # ---- `e2e`: the public host call, pinned host buffers in and out --------------------------------------------------------
     pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory().numpy()  # noqa: E731
-    h_poses, h_pmm, h_tot = pin(wl["poses"]), pin(wl["pmm"]), pin(wl["tot"])
+    h_poses = [pin(x) for x in wl["poses_b"]]
+    h_tot = [pin(x) for x in wl["tot_b"]]
+    h_pmm = pin(wl["pmm"])
     h_lab = pin(wl["plabel"]) if wl["plabel"] is not None else None
-    K_TOP = 8
-    exchange = sharding.HitExchange(1, K_TOP)
+    K_TOP = args.topk
+    offset = (sharding.shard_range(P_scene, rank, world)[0] if strong else rank * P)
 
-    # Every step is one call of the public API on pinned host buffers (H2D of the step's poses, kernel, D2H of its costs)
-    # followed by the host top-k.  A caller with many batches to score keeps the GPU busy by driving more than one
-    # context (each has its own stream) from its own host thread, so that one step's copies and host work overlap the
-    # other's kernel: --e2e-contexts (default 2) such contexts share the steps round-robin; the top-k gather across
-    # ranks runs on the main thread, in step order.
-    n_ctx = max(1, min(args.e2e_contexts, args.steps))
-    ctxs = [r]
-    for _ in range(n_ctx - 1):
+    def pinned_out():
+        return {"rendered_cost": pin(np.zeros(P, np.float32)), "observed_cost": pin(np.zeros(P, np.float32)),
+                "points_diff_cost": pin(np.zeros(P, np.float32)), "counts": pin(np.zeros((3, P), np.int32))}
+
+    def new_comm(rr):
+        if world == 1:
+            return
+        ids = [comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0)
+        rr.comm_init(world, rank, ids[0])
+
+    def clone_context():
         r2 = Renderer(local_rank)
         r2.set_camera(W, H, wl["proj"], synth.CX, synth.CY, synth.FX, synth.FY, synth.DEPTH_FACTOR)
         r2.set_models(wl["scene"].tris, wl["scene"].tris_model_count)
         r2.set_scene(wl["scene"].source_depth, wl["scene"].source_color, wl["scene"].source_label if wl["dof6"] else None)
         r2.set_observed(wl["obs"]["result_cloud_eigen"], wl["obs"]["result_cloud_color"], wl["obs_label"])
-        ctxs.append(r2)
+        if composed:
+            r2.compose_source(composed["poses"], composed["pmm"], None, mode="merge")
+        return r2
 
-    def score_step(rr):
-        out = rr.render_cuda_multi_unified("COST", h_poses, h_pmm, h_lab, h_tot, **kw)
-        return out, topk(out["rendered_cost"], out["observed_cost"], h_pmm, 1, k=K_TOP, pose_id_offset=rank * P)
+    n_ctx = max(1, args.e2e_contexts)
+    ctxs = [r] + [clone_context() for _ in range(n_ctx - 1)]
+    outs = [pinned_out() for _ in ctxs]
+    for rr in ctxs:
+        new_comm(rr)
 
-    def e2e_steps(n_steps):
-        """n_steps steps over the contexts; returns the last step's outputs and merged best hit."""
-        results = [None] * n_steps
-        done = [threading.Event() for _ in range(n_steps)]
+    def score_scene(j, b):
+        """One scene = one blocking call of the public API on context j: H2D, kernel, device top-k, all-gather, D2H."""
+        hits, _ = ctxs[j].score_scene(h_poses[b], h_pmm, h_lab, h_tot[b], n_models=n_models, k=K_TOP, pose_id_offset=offset,
+                                      out=outs[j], **kw)
+        return hits
+
+    def e2e_steps(n_steps, n_use):
+        """n_steps x B scenes dealt round-robin to n_use contexts, one host thread each (n_use = 1: the calling thread)."""
+        scenes = [(st, b) for st in range(n_steps) for b in range(B)]
+        last = [None] * n_use
+        if n_use == 1:
+            for _, b in scenes:
+                last[0] = score_scene(0, b)
+            return last[0]
         errors = []
 
         def worker(j):
             try:
-                for i in range(j, n_steps, n_ctx):
-                    results[i] = score_step(ctxs[j])
-                    done[i].set()
+                for i in range(j, len(scenes), n_use):
+                    last[j] = score_scene(j, scenes[i][1])
             except BaseException as e:  # noqa: BLE001
                 errors.append(e)
-                for d in done:
-                    d.set()
 
-        threads = [threading.Thread(target=worker, args=(j,)) for j in range(n_ctx)]
+        threads = [threading.Thread(target=worker, args=(j,)) for j in range(n_use)]
         for t in threads:
             t.start()
-        # the main thread gathers the finished steps in step order (collectives stay ordered across ranks) while the
-        # workers are already scoring the next ones
-        best = None
-        for i in range(n_steps):
-            done[i].wait()
-            if errors:
-                break
-            best = sharding.merge_hits(exchange.gather(results[i][1]), K_TOP)[0, 0]  # all_gather of k x 16 B per rank
         for t in threads:
             t.join()
         if errors:
             raise errors[0]
-        return results[-1][0], best
+        return last[(len(scenes) - 1) % n_use]
 
-    out, best = e2e_steps(max(n_ctx, min(args.warmup, 3)))
-    barrier()
-    t0 = time.perf_counter()
-    out, best = e2e_steps(args.steps)
-    barrier()
-    e2e_s = time.perf_counter() - t0
+    def timed_e2e(n_use):
+        e2e_steps(min(max(args.warmup, 1), 3), n_use)
+        barrier()
+        t0 = time.perf_counter()
+        best = e2e_steps(args.steps, n_use)
+        barrier()
+        return time.perf_counter() - t0, best
+
+    serial_s, best = timed_e2e(1)
+    piped_s = None
+    if n_ctx > 1:
+        piped_s, best = timed_e2e(n_ctx)
     clocks = sampler.stop()
+    e2e_counts_scene_last = outs[0]["counts"].copy()
 
-    counts = np.zeros((3, P), np.int32)
-    r.d2h(counts, d_counts)
-    work = {"rendered_points_per_pose": float(counts[0].mean()), "n_obs": int(wl["n_obs"])}
+    work = {"rendered_points_per_pose": float(counts0[0].mean()), "n_obs": int(wl["n_obs"])}
 
     if world > 1:
-        t = torch.tensor([total_ms, e2e_s], dtype=torch.float64, device="cuda")
+        t = torch.tensor([total_ms, serial_s, piped_s or 0.0], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        total_ms, e2e_s = float(t[0]), float(t[1])
+        total_ms, serial_s = float(t[0]), float(t[1])
+        piped_s = float(t[2]) if piped_s is not None else None
 
     line = None
     if rank == 0:
-        peak, peak_kind = measured_peak_gbs()
+        scenes_per_step = B
+        poses_per_step_all = (P_scene if strong else world * P) * B
         ms_per_step = total_ms / args.steps
-        value = world * P * args.steps / (total_ms / 1e3)
-        bpp = algorithmic_bytes_per_pose(wl["n_tris"], wl["n_obs"])
-        kern_ms = float(np.mean(kernel_ms))
-        achieved = P * bpp / (kern_ms / 1e3) / 1e9
-        traffic = None
-        tfile = ROOT / "profiles" / "dram_traffic.json"
-        if tfile.exists():
-            try:
-                traffic = json.loads(tfile.read_text()).get(args.workload)
-            except Exception:
-                traffic = None
-        # what actually bounds the kernel (DESIGN 4.1): warp-instruction issue.  The per-launch instruction count is the
-        # smsp__inst_executed.sum of the committed ncu capture of this workload (profiles/kernel_counters.json); the rate
-        # is that count over the kernel time measured HERE, against SMs x 4 schedulers x the SM clock sampled in this run.
-        issue = None
-        cfile = ROOT / "profiles" / "kernel_counters.json"
-        if cfile.exists():
-            try:
-                kc = json.loads(cfile.read_text()).get(args.workload)
-                if kc and kc.get("poses") == P and clocks.get("sm_mhz"):
-                    sms = int(kc.get("sm_count", 148))
-                    rate = kc["warp_inst_per_launch"] / (kern_ms / 1e3)
-                    peak_rate = sms * 4 * clocks["sm_mhz"] * 1e6
-                    issue = {"bound": "warp-instruction issue", "warp_inst_per_pose": kc["warp_inst_per_launch"] / P,
-                             "achieved": rate / 1e9, "peak": peak_rate / 1e9, "unit": "G warp-inst/s", "frac": rate / peak_rate,
-                             "source": kc.get("source")}
-            except Exception:
-                issue = None
+        value = poses_per_step_all * args.steps / (total_ms / 1e3)
+        kern_ms = ms_per_step / B  # per launch of P poses
+        e2e_best_s = min(x for x in (serial_s, piped_s) if x is not None)
+        h2d = int(P * (64 + 4 + 4 + (4 if h_lab is not None else 0))) * B
+        d2h = int(P * 24 + n_models * K_TOP * 16 * world) * B
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic",
-            "config": {"workload": wl["desc"], "poses_per_gpu_per_step": P, "triangles": wl["n_tris"], "meshes": wl["n_models"], "image": [W, H],
-                       "stride": wl["stride"], "n_obs": int(wl["n_obs"]), "l2": "flushed between steps (256 MiB memset)",
-                       "timing": "CUDA events on the library stream around the fused kernel, max over ranks"},
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": wl["desc"], "scenes_per_step": scenes_per_step,
+                       "poses_per_gpu_per_scene": P, "poses_per_scene_all_gpus": P_scene if strong else world * P,
+                       "poses_per_gpu_per_step": P * B, "triangles": wl["n_tris"], "meshes": wl["n_models"], "image": [W, H],
+                       "stride": wl["stride"], "n_obs": int(wl["n_obs"]),
+                       "composed_source": bool(composed),
+                       "l2": "flushed once per step (256 MiB memset); the step's scenes use distinct pose batches",
+                       "timing": "CUDA events on the library stream around the step's fused-kernel launches, max over ranks"},
             "clocks": clocks,
-            "e2e": {"value": world * P * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": int(P * (64 + 4 + 4 + (4 if h_lab is not None else 0))),
-                    "d2h_bytes_per_step": int(P * 24), "ms_per_scene": e2e_s / args.steps * 1e3,
-                    "contexts": n_ctx,
-                    "how": "every step is one blocking call of the public host API (H2D of its poses, kernel, D2H of its costs) "
-                           "+ host top-k; steps alternate between `contexts` contexts, one host thread each"},
-            "gpu_launches": args.steps,
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "peak_kind": f"{peak_kind} copy bandwidth", "bytes_per_pose": bpp,
-                         "poses_per_launch": P, "kernel": "pose_kernel<MODE_COST>", "kernel_ms": kern_ms},
-            "issue_roofline": issue,
+            "timed_region_s": total_ms / 1e3,
+            "e2e": {"value": poses_per_step_all * args.steps / e2e_best_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "ms_per_scene": e2e_best_s / (args.steps * B) * 1e3,
+                    "contexts": n_ctx if (piped_s is not None and piped_s <= serial_s) else 1,
+                    "serial": {"value": poses_per_step_all * args.steps / serial_s, "ms_per_scene": serial_s / (args.steps * B) * 1e3,
+                               "contexts": 1},
+                    "pipelined": None if piped_s is None else {"value": poses_per_step_all * args.steps / piped_s,
+                                                               "ms_per_scene": piped_s / (args.steps * B) * 1e3, "contexts": n_ctx},
+                    "topk": K_TOP,
+                    "how": "every scene is one blocking perch_score_scene call: pinned host poses -> H2D -> fused kernel -> "
+                           "per-model top-k on the device -> ncclAllGather of the per-rank records (N > 1) -> D2H of costs, "
+                           "counts and merged hits; `serial` = one context, `pipelined` = scenes alternate between "
+                           "`contexts` contexts, one host thread each; value = the faster of the two"},
+            "gpu_launches": args.steps * B,
+            "roofline": rooflines(args, wl, P, kern_ms, clocks),
             "work": work,
-            "best": {"cost": int(best["cost"]), "pose_id": int(best["pose_id"])},
+            "best": {"cost": int(best["cost"][0, 0]), "pose_id": int(best["pose_id"][0, 0])},
             "wall_s_device_loop": wall_device_loop,
         }
+        if not args.no_parity_check:
+            line["parity_check"] = parity_check(wl, counts0, costs0, n=args.parity_poses)
+        if world == 1 and not args.no_parity_check and wl["cost_type"] != 1:
+            u = r.render_cost_unfused(wl["poses"], wl["pmm"], wl["plabel"], wl["tot"], **kw)
+            bad = int((u["counts"] != counts0).any(0).sum() + (~_feq(u["rendered_cost"], costs0[0])).sum())
+            line["unfused_check"] = {"poses": int(P), "mismatches": bad, "unfused_ms": r.last_timing()[0],
+                                     "what": "scene 0 of the timed step, every pose: fused kernel output vs the library's "
+                                             "unfused kernels (full raster, clouds, brute-force NN)"}
         single = wl["n_models"] == 1  # the GICP / glue legs are written for the one-mesh workloads
         if world == 1 and not args.no_gicp and single:
-            line["gicp"] = gicp_leg(r, wl, out, kw)
+            o0 = {"rendered_cost": costs0[0], "observed_cost": costs0[1]}
+            line["gicp"] = gicp_leg(r, wl, o0, kw)
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(wl, budget_s=args.cpu_budget)
         if world == 1 and not args.no_glue and single:
@@ -367,8 +490,36 @@ def run_ours(args):
             line["reference_cuda"] = reference_cuda(wl, batch=args.ref_batch)
         emit(line)
     if world > 1:
+        for rr in ctxs:
+            rr.comm_destroy()
         dist.destroy_process_group()
     return line
+
+
+def _feq(a, b):
+    return (a == b) | (np.isnan(a) & np.isnan(b))
+
+
+def parity_check(wl, counts0, costs0, n=64):
+    """What the timed launch of scene 0 wrote (counts + three costs, read back from its device buffers) against the CPU
+    oracle (oracle_render + oracle_costs per pose, image_renderer.cuh:59-210, compute_point_clouds.cuh:37-184,
+    compute_costs.cuh:161-290) on n poses spread evenly over the batch."""
+    from oracle_lib import Oracle
+    from perception_b200 import synth
+    P = wl["P"]
+    sel = np.unique(np.linspace(0, P - 1, min(n, P)).astype(np.int64))
+    s = wl["scene"]
+    t0 = time.perf_counter()
+    o = Oracle().score_poses(s.tris, s.tris_model_count, wl["poses"][sel], wl["pmm"][sel], W, H, wl["proj"],
+                             wl.get("oracle_source_depth", s.source_depth), s.source_label if wl["dof6"] else None,
+                             wl["plabel"][sel] if wl["plabel"] is not None else None, synth.CX, synth.CY, synth.FX, synth.FY,
+                             synth.DEPTH_FACTOR, wl["stride"], wl["obs"]["result_cloud_eigen"], wl["obs"]["result_cloud_color"],
+                             wl["obs_label"], wl["tot"][sel], wl["cost_type"], True, wl["res"], 20.0)
+    bad = (o["counts"] != counts0[:, sel]).any(0)
+    for k, name in enumerate(("rendered_cost", "observed_cost", "points_diff_cost")):
+        bad |= ~_feq(o[name], costs0[k, sel])
+    return {"poses": int(len(sel)), "mismatches": int(bad.sum()), "oracle_s": time.perf_counter() - t0,
+            "what": "scene 0 of the timed step: counts and the three costs of the timed launch, bit for bit, vs oracle/perch_oracle.c"}
 
 
 def gicp_leg(r, wl, out, kw, n_top=4096, iterations=20, reps=3):
@@ -563,6 +714,8 @@ def cpu_score(wl, n):
     from perception_b200.renderer import TRIANGLE_DTYPE
     lib = C.CDLL(str(ORACLE_SO))
     lib.cpu_baseline_threads.restype = C.c_int
+    # all host cores this process may run on, whatever OMP_NUM_THREADS says (torchrun sets it to 1)
+    lib.cpu_baseline_set_threads(C.c_int(len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)))
     s = wl["scene"]
     b = _baseline_inputs(wl)
     vp = C.c_void_p
@@ -603,35 +756,51 @@ def cpu_baseline(wl, budget_s=15.0):
                       "(oracle/cpu_baseline.c)"}
 
 
-def reference_cuda(wl, batch=700):
-    """The reference's own CUDA kernels (oracle/_ref/libperch_ref.so) on the same inputs: per-call upload + alloc like
-    the reference, shipped gpu_batch_size 700 (pr3_env_config.yaml:10).  Reported beside, same GPU, same job."""
+def reference_cuda(wl, batch=700, reps=5):
+    """The reference's own CUDA kernels (oracle/_ref/libperch_ref.so) on the same inputs, per-call upload + alloc like the
+    reference (renderer.cu:1532-1544): at the shipped gpu_batch_size 700 (pr3_env_config.yaml:10) AND at
+    min(P, 6 990) -- the largest batch below the reference's int-index overflow at 640x480.  Per batch size:
+    one warm-up call, then `reps` calls; CUDA-event time of the four phases (median over reps) and wall time."""
     from oracle_lib import REF_SO, Reference
     if not REF_SO.exists():
         return {"unavailable": "oracle/_ref/libperch_ref.so not built"}
     ref = Reference()
     s = wl["scene"]
     from perception_b200 import synth
-    n = min(batch, wl["P"])
-    a = dict(tris=s.tris, tris_model_count=s.tris_model_count, poses=wl["poses"][:n], pose_model_map=wl["pmm"][:n], width=W,
-             height=H, proj=wl["proj"], source_depth=s.source_depth, source_color=s.source_color,
-             source_label=s.source_label if wl["dof6"] else None, pose_label=wl["plabel"][:n] if wl["dof6"] else None,
-             stride=wl["stride"], depth_factor=100, cx=synth.CX, cy=synth.CY, fx=synth.FX, fy=synth.FY,
-             obs_xyz=wl["obs"]["result_cloud_eigen"], obs_rgb=wl["obs"]["result_cloud_color"],
-             obs_label=wl["obs_label"] if wl["dof6"] else None, pose_obs_total=wl["tot"][:n], cost_type=wl["cost_type"],
-             calc_observed=True, sensor_resolution=wl["res"], color_distance_threshold=20.0, occlusion_threshold=1.0)
-    ref.render_cost(**a)  # warm-up (context, allocator)
-    times, phases = [], []
-    for _ in range(3):
-        t0 = time.perf_counter()
-        q = ref.render_cost(**a)
-        times.append(time.perf_counter() - t0)
-        phases.append(q["ms"])
-    dt = float(np.median(times))
-    ph = np.median(np.array(phases), 0)
-    return {"value": n / dt, "unit": UNIT, "batch": n, "ms_per_batch": dt * 1e3,
-            "phase_ms": {"render": float(ph[0]), "cloud": float(ph[1]), "knn": float(ph[2]), "cost": float(ph[3])},
-            "note": "reference .cuh kernels compiled unmodified for sm_100a + restated orchestration and brute-force NN"}
+
+    def run(n):
+        a = dict(tris=s.tris, tris_model_count=s.tris_model_count, poses=wl["poses"][:n], pose_model_map=wl["pmm"][:n], width=W,
+                 height=H, proj=wl["proj"], source_depth=s.source_depth, source_color=s.source_color,
+                 source_label=s.source_label if wl["dof6"] else None, pose_label=wl["plabel"][:n] if wl["dof6"] else None,
+                 stride=wl["stride"], depth_factor=100, cx=synth.CX, cy=synth.CY, fx=synth.FX, fy=synth.FY,
+                 obs_xyz=wl["obs"]["result_cloud_eigen"], obs_rgb=wl["obs"]["result_cloud_color"],
+                 obs_label=wl["obs_label"] if wl["dof6"] else None, pose_obs_total=wl["tot"][:n], cost_type=wl["cost_type"],
+                 calc_observed=True, sensor_resolution=wl["res"], color_distance_threshold=20.0, occlusion_threshold=1.0)
+        ref.render_cost(**a)  # warm-up (context, allocator)
+        wall, phases = [], []
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            q = ref.render_cost(**a)
+            wall.append(time.perf_counter() - t0)
+            phases.append(q["ms"])
+        ph = np.median(np.array(phases), 0)
+        ev_ms = float(np.median(np.array(phases).sum(1)))
+        return {"batch": int(n), "value": n / (ev_ms / 1e3), "unit": UNIT, "event_ms_per_batch": ev_ms,
+                "wall_value": n / float(np.median(wall)), "wall_ms_per_batch": float(np.median(wall)) * 1e3,
+                "wall_ms_spread": [float(min(wall)) * 1e3, float(max(wall)) * 1e3], "reps": reps,
+                "phase_ms": {"render": float(ph[0]), "cloud": float(ph[1]), "knn": float(ph[2]), "cost": float(ph[3])}}
+
+    small = run(min(batch, wl["P"]))
+    out = dict(small)
+    big_n = min(wl["P"], 6990)
+    if big_n > small["batch"]:
+        try:
+            out["max_batch"] = run(big_n)
+        except Exception as e:  # noqa: BLE001
+            out["max_batch"] = {"batch": int(big_n), "failed": repr(e)[:200]}
+    out["note"] = ("reference .cuh kernels compiled unmodified for sm_100a + restated orchestration and brute-force NN; value = "
+                   "poses / CUDA-event time of the call's four phases (uploads and allocations included), median of reps")
+    return out
 
 
 def run_reference_cpu(args):
@@ -639,7 +808,8 @@ def run_reference_cpu(args):
     rank, local_rank, world = rank_info()
     if rank != 0:
         return
-    r, wl = build_workload(args.workload, 0, local_rank, args.poses, use_product=False)
+    from oracle_lib import Oracle
+    r, wl = build_workload(args.workload, 0, local_rank, args.poses, use_product=False, compute_proj_fn=Oracle().compute_proj)
     dt, cores, _, _ = cpu_score(wl, 16)
     per_step = int(min(wl["P"], max(16, 16 * (60.0 / max(args.steps + args.warmup, 1)) / max(dt, 1e-3))))
     for _ in range(args.warmup):
@@ -664,7 +834,8 @@ def run_reference_cuda(args):
     rank, local_rank, world = rank_info()
     if rank != 0:
         return
-    r, wl = build_workload(args.workload, 0, local_rank, args.poses, use_product=False)
+    from oracle_lib import Oracle
+    r, wl = build_workload(args.workload, 0, local_rank, args.poses, use_product=False, compute_proj_fn=Oracle().compute_proj)
     out = reference_cuda(wl, batch=args.ref_batch)
     emit({"impl": "reference-cuda", "metric": METRIC, "unit": UNIT, **out, "config": {"workload": wl["desc"]}})
 
@@ -689,7 +860,7 @@ def main():
     os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--e2e-contexts", type=int, default=2,
                     help="contexts (one host thread each) the e2e leg spreads its steps over; 1 = strictly serial calls")
     ap.add_argument("--warmup", type=int, default=3)
@@ -698,6 +869,13 @@ def main():
     ap.add_argument("--poses", type=int, default=None, help="override poses per GPU per step")
     ap.add_argument("--cpu-budget", type=float, default=15.0)
     ap.add_argument("--ref-batch", type=int, default=700)
+    ap.add_argument("--batches", type=int, default=40, help="scenes (distinct pose batches, one fused-kernel launch each) per step")
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="strong: the scene's pose list is fixed (c3: 100k, c5: 1M, or --poses) and sharded over the GPUs")
+    ap.add_argument("--topk", type=int, default=8)
+    ap.add_argument("--parity-poses", type=int, default=64)
+    ap.add_argument("--no-parity-check", action="store_true")
+    ap.add_argument("--no-compose", action="store_true", help="c3: do not place an object into the source image")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-cuda", action="store_true")
     ap.add_argument("--no-gicp", action="store_true")

@@ -187,6 +187,11 @@ int perch_device_free(perch_ctx* ctx, void* d_ptr);
 int perch_memcpy_h2d(perch_ctx* ctx, void* d_dst, const void* h_src, size_t bytes);
 int perch_memcpy_d2h(perch_ctx* ctx, void* h_dst, const void* d_src, size_t bytes);
 int perch_synchronize(perch_ctx* ctx);
+/* Measurement: CUDA events on the context's stream around whatever the caller enqueues in between (several
+ * perch_render_cost_device launches back to back); perch_timer_elapsed waits for the stop event. */
+int perch_timer_start(perch_ctx* ctx);
+int perch_timer_stop(perch_ctx* ctx);
+int perch_timer_elapsed(perch_ctx* ctx, float* ms);
 /* Measurement hygiene: overwrite a buffer larger than the 126 MB L2 on the context's stream (between timed steps). */
 int perch_l2_flush(perch_ctx* ctx);
 

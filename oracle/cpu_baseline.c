@@ -109,6 +109,16 @@ static int grid_any_within(const grid_t* g, const float* q, float r2, int want_l
     return 0;
 }
 
+/* torchrun exports OMP_NUM_THREADS=1 to every rank; the baseline is quoted on ALL host cores, so bench.py sets the
+ * thread count explicitly (n <= 0: leave the OpenMP default). */
+void cpu_baseline_set_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 int cpu_baseline_threads(void) {
 #ifdef _OPENMP
     return omp_get_max_threads();

@@ -175,6 +175,9 @@ SIGNATURES = {
     "perch_memcpy_d2h": (C.c_int, [_P, _P, _P, C.c_size_t]),
     "perch_synchronize": (C.c_int, [_P]),
     "perch_l2_flush": (C.c_int, [_P]),
+    "perch_timer_start": (C.c_int, [_P]),
+    "perch_timer_stop": (C.c_int, [_P]),
+    "perch_timer_elapsed": (C.c_int, [_P, C.POINTER(C.c_float)]),
     "perch_topk": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, _P]),
     "perch_set_env": (C.c_int, [_P, C.POINTER(perch_env), _V, C.c_int, _V, C.c_int]),
     "perch_set_search_cloud": (C.c_int, [_P, _V, C.c_int, _V, C.c_int, _V, C.c_int]),

@@ -508,6 +508,8 @@ int perch_create(int device, perch_ctx** out) {
     CU(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     CU(cudaEventCreate(&c->ev0));
     CU(cudaEventCreate(&c->ev1));
+    CU(cudaEventCreate(&c->ev_t0));
+    CU(cudaEventCreate(&c->ev_t1));
     CU(cudaMalloc(&c->d_err_flag, sizeof(int)));
     CU(cudaMemset(c->d_err_flag, 0, sizeof(int)));
     *out = c;
@@ -531,6 +533,8 @@ void perch_destroy(perch_ctx* c) {
     perch_detail::destroy_states(c);
     cudaEventDestroy(c->ev0);
     cudaEventDestroy(c->ev1);
+    cudaEventDestroy(c->ev_t0);
+    cudaEventDestroy(c->ev_t1);
     cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -966,6 +970,26 @@ int perch_synchronize(perch_ctx* c) {
         c->timing_pending = false;
     }
     return check_err_flag(c);
+}
+
+int perch_timer_start(perch_ctx* c) {
+    if (!c) return fail(PERCH_ERR_INVALID, "null context");
+    DeviceGuard g(c->device);
+    CU(cudaEventRecord(c->ev_t0, c->stream));
+    return PERCH_OK;
+}
+int perch_timer_stop(perch_ctx* c) {
+    if (!c) return fail(PERCH_ERR_INVALID, "null context");
+    DeviceGuard g(c->device);
+    CU(cudaEventRecord(c->ev_t1, c->stream));
+    return PERCH_OK;
+}
+int perch_timer_elapsed(perch_ctx* c, float* ms) {
+    if (!c || !ms) return fail(PERCH_ERR_INVALID, "null argument");
+    DeviceGuard g(c->device);
+    CU(cudaEventSynchronize(c->ev_t1));
+    CU(cudaEventElapsedTime(ms, c->ev_t0, c->ev_t1));
+    return PERCH_OK;
 }
 
 int perch_l2_flush(perch_ctx* c) {

@@ -68,6 +68,7 @@ struct perch_ctx {
     int max_smem_optin = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr;  // perch_timer_start / perch_timer_stop
     float last_ms = 0.f;
     float last_gicp_ms = 0.f;          // device time of the last GICP kernel
     bool timing_pending = false;

@@ -542,6 +542,17 @@ class Renderer:
     def l2_flush(self) -> None:
         self._ck(self._lib.perch_l2_flush(self._h))
 
+    def timer_start(self) -> None:
+        self._ck(self._lib.perch_timer_start(self._h))
+
+    def timer_stop(self) -> None:
+        self._ck(self._lib.perch_timer_stop(self._h))
+
+    def timer_elapsed(self) -> float:
+        ms = C.c_float(0)
+        self._ck(self._lib.perch_timer_elapsed(self._h, C.byref(ms)))
+        return ms.value
+
     def knn(self, ref, query, k: int):
         """k nearest reference points of every query point with the kNN-CUDA contract (knncuda.h:33-100).
         ref: (dim, ref_nb), query: (dim, query_nb), one row per dimension.  Returns (knn_dist, knn_index), both
