@@ -520,7 +520,7 @@ void perch_destroy(perch_ctx* c) {
     if (!c) return;
     DeviceGuard g(c->device);
     cudaStreamSynchronize(c->stream);
-    void* ptrs[] = {c->d_tri_color, c->d_model_low, c->d_model_high, c->d_model_aabb, c->d_tri_lab, c->d_cl_recs, c->d_cl_bounds,
+    void* ptrs[] = {c->d_tri_color, c->d_model_low, c->d_model_high, c->d_model_aabb, c->d_model_qrmax, c->d_tri_lab, c->d_cl_recs, c->d_cl_bounds, c->d_q_bounds,
                     c->d_cl_orig, c->d_cl_perm, c->d_cl_low, c->d_cl_high,
                     c->d_src_depth, c->d_src_label, c->d_src_rgb, c->d_grid_pts, c->d_grid_label, c->d_cell_start,
                     c->d_icp_grid_pts, c->d_icp_grid_label, c->d_icp_grid_cells, c->d_cmp_depth, c->d_cmp_label, c->d_full_keys, c->d_full_big, c->d_full_count, c->d_full_acc, c->d_ggrid_pts, c->d_ggrid_label, c->d_ggrid_cell_start,
@@ -648,12 +648,14 @@ int perch_set_models(perch_ctx* c, const perch_triangle* tris, int64_t n_tris, c
         }
         if (cs.bounds.empty()) {
             cs.bounds.assign(4, 0.f);
+            cs.qbounds.assign(8, 0.f);
             cs.recs.assign(perch::kClusterFloats, 0.f);
             cs.orig.assign(perch::kClusterTris, 0);
             cs.perm.assign(1, 0xFFFFFFu);  // four invalid slots
         }
         if ((rc = upload(&c->d_cl_recs, cs.recs.data(), cs.recs.size(), c->stream))) return rc;
         if ((rc = upload(&c->d_cl_bounds, reinterpret_cast<const float4*>(cs.bounds.data()), cs.bounds.size() / 4, c->stream))) return rc;
+        if ((rc = upload(&c->d_q_bounds, reinterpret_cast<const float4*>(cs.qbounds.data()), cs.qbounds.size() / 4, c->stream))) return rc;
         if ((rc = upload(&c->d_cl_orig, cs.orig.data(), cs.orig.size(), c->stream))) return rc;
         if ((rc = upload(&c->d_cl_perm, cs.perm.data(), cs.perm.size(), c->stream))) return rc;
         if ((rc = upload(&c->d_cl_low, cs.model_low.data(), cs.model_low.size(), c->stream))) return rc;
@@ -661,6 +663,18 @@ int perch_set_models(perch_ctx* c, const perch_triangle* tris, int64_t n_tris, c
         CU(cudaStreamSynchronize(c->stream));  // host vectors go out of scope
         c->models.cl_recs = c->d_cl_recs;
         c->models.cl_bounds = c->d_cl_bounds;
+        c->models.q_bounds = c->d_q_bounds;
+        {
+            std::vector<float> qrmax(cs.model_low.size(), 0.f);
+            for (size_t m = 0; m < cs.model_low.size(); ++m)
+                for (int q = 2 * cs.model_low[m]; q < 2 * cs.model_high[m]; ++q) {
+                    const float r = cs.qbounds[4 * (size_t)q + 3];
+                    if (std::isfinite(r)) qrmax[m] = std::max(qrmax[m], r);
+                }
+            if ((rc = upload(&c->d_model_qrmax, qrmax.data(), qrmax.size(), c->stream))) return rc;
+            CU(cudaStreamSynchronize(c->stream));
+            c->models.model_qrmax = c->d_model_qrmax;
+        }
         c->models.cl_orig = c->d_cl_orig;
         c->models.cl_perm = c->d_cl_perm;
         c->models.cl_low = c->d_cl_low;
@@ -718,7 +732,14 @@ int perch_cluster_stats(const perch_triangle* tris, int64_t n_tris, const int* t
                     const float got = rec[((perm >> (2 * k)) & 3u) * 3 + a];
                     if (memcmp(&got, &tri9[(size_t)t * 9 + 3 * k + a], 4) != 0) ++mismatch;
                 }
-            // every vertex must lie inside the cluster's bounding sphere
+            // every vertex must lie inside its quad's bounding sphere (level 1 of the candidate test) ...
+            const float* qb = &cs.qbounds[4 * (c * perch::kClusterQuads + (j >> 1))];
+            for (int k = 0; k < 3 && std::isfinite(qb[3]); ++k) {
+                double d2 = 0;
+                for (int a = 0; a < 3; ++a) d2 += ((double)tri9[(size_t)t * 9 + 3 * k + a] - qb[a]) * ((double)tri9[(size_t)t * 9 + 3 * k + a] - qb[a]);
+                if (std::sqrt(d2) > (double)qb[3]) ++outside;
+            }
+            // ... and inside the cluster's
             const float* b = &cs.bounds[4 * c];
             for (int k = 0; k < 3 && std::isfinite(b[3]); ++k) {
                 double d2 = 0;

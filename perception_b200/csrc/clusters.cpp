@@ -41,6 +41,42 @@ struct Unit {
     uint32_t perm[2];  // per triangle: quad vertex of its v0, v1, v2
 };
 
+// Near-minimal enclosing ball of np points: start at the AABB centre, walk towards the farthest point
+// (Badoiu-Clarkson); the radius is taken about the ROUNDED (float) centre and rounded up, so that the device test may
+// rely on |vertex - centre| <= radius.  Non-finite input: radius = inf.
+void enclosing_ball(const double (*pts)[3], int np, float out4[4]) {
+    out4[0] = out4[1] = out4[2] = 0.f;
+    out4[3] = INFINITY;
+    for (int i = 0; i < np; ++i)
+        for (int a = 0; a < 3; ++a)
+            if (!std::isfinite(pts[i][a])) return;
+    double lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
+    for (int i = 0; i < np; ++i)
+        for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], pts[i][a]); hi[a] = std::max(hi[a], pts[i][a]); }
+    auto radius2 = [&](const double c[3], int* far) {
+        double r2 = -1;
+        for (int i = 0; i < np; ++i) {
+            double d = (pts[i][0] - c[0]) * (pts[i][0] - c[0]) + (pts[i][1] - c[1]) * (pts[i][1] - c[1]) + (pts[i][2] - c[2]) * (pts[i][2] - c[2]);
+            if (d > r2) { r2 = d; if (far) *far = i; }
+        }
+        return r2;
+    };
+    double c[3] = {0.5 * (lo[0] + hi[0]), 0.5 * (lo[1] + hi[1]), 0.5 * (lo[2] + hi[2])};
+    double bestc[3] = {c[0], c[1], c[2]};
+    double best2 = radius2(c, nullptr);
+    for (int it = 0; it < 96; ++it) {
+        int far = 0;
+        radius2(c, &far);
+        for (int a = 0; a < 3; ++a) c[a] += (pts[far][a] - c[a]) / (it + 2.0);
+        double r2 = radius2(c, nullptr);
+        if (r2 < best2) { best2 = r2; bestc[0] = c[0]; bestc[1] = c[1]; bestc[2] = c[2]; }
+    }
+    out4[0] = (float)bestc[0]; out4[1] = (float)bestc[1]; out4[2] = (float)bestc[2];
+    const double cf[3] = {out4[0], out4[1], out4[2]};
+    float rad = std::nextafter((float)(std::sqrt(radius2(cf, nullptr)) * (1.0 + 1e-6)), std::numeric_limits<float>::infinity());
+    out4[3] = std::isfinite(rad) ? rad : INFINITY;
+}
+
 }  // namespace
 
 ClusterSet build_clusters(const float* tri9, const std::vector<int>& low, const std::vector<int>& high) {
@@ -258,7 +294,6 @@ ClusterSet build_clusters(const float* tri9, const std::vector<int>& low, const 
             const Unit& qb = units[second >= 0 ? second : seed];
             const size_t rec = out.recs.size();
             out.recs.resize(rec + kClusterFloats);
-            bool finite = true;
             double pts[kQuadVerts * kClusterQuads][3];
             uint32_t perm = 0;
             for (int q = 0; q < kClusterQuads; ++q) {
@@ -267,7 +302,6 @@ ClusterSet build_clusters(const float* tri9, const std::vector<int>& low, const 
                     for (int a = 0; a < 3; ++a) {
                         const float p = u.v[i][a];
                         out.recs[rec + (size_t)q * kQuadFloats + 3 * i + a] = p;
-                        if (!std::isfinite(p)) finite = false;
                         pts[q * kQuadVerts + i][a] = p;
                     }
                 const bool repeat = q == 1 && second < 0;
@@ -278,36 +312,15 @@ ClusterSet build_clusters(const float* tri9, const std::vector<int>& low, const 
                 }
             }
             out.perm.push_back(perm);
-            float cx = 0.f, cy = 0.f, cz = 0.f, rad = INFINITY;
-            if (finite) {
-                // near-minimal enclosing ball: start at the AABB centre, walk towards the farthest point (Badoiu-Clarkson)
-                const int np = kQuadVerts * kClusterQuads;
-                double lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY};
-                for (int i = 0; i < np; ++i)
-                    for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], pts[i][a]); hi[a] = std::max(hi[a], pts[i][a]); }
-                auto radius2 = [&](const double c[3], int* far) {
-                    double r2 = -1;
-                    for (int i = 0; i < np; ++i) {
-                        double d = (pts[i][0] - c[0]) * (pts[i][0] - c[0]) + (pts[i][1] - c[1]) * (pts[i][1] - c[1]) + (pts[i][2] - c[2]) * (pts[i][2] - c[2]);
-                        if (d > r2) { r2 = d; if (far) *far = i; }
-                    }
-                    return r2;
-                };
-                double c[3] = {0.5 * (lo[0] + hi[0]), 0.5 * (lo[1] + hi[1]), 0.5 * (lo[2] + hi[2])};
-                double bestc[3] = {c[0], c[1], c[2]};
-                double best2 = radius2(c, nullptr);
-                for (int it = 0; it < 96; ++it) {
-                    int far = 0;
-                    radius2(c, &far);
-                    for (int a = 0; a < 3; ++a) c[a] += (pts[far][a] - c[a]) / (it + 2.0);
-                    double r2 = radius2(c, nullptr);
-                    if (r2 < best2) { best2 = r2; bestc[0] = c[0]; bestc[1] = c[1]; bestc[2] = c[2]; }
-                }
-                cx = (float)bestc[0]; cy = (float)bestc[1]; cz = (float)bestc[2];
-                const double cf[3] = {cx, cy, cz};  // radius about the ROUNDED centre
-                // round up: the device test relies on |vertex - centre| <= radius
-                rad = std::nextafter((float)(std::sqrt(radius2(cf, nullptr)) * (1.0 + 1e-6)), std::numeric_limits<float>::infinity());
-                if (!std::isfinite(rad)) rad = INFINITY;
+            float ball[4];
+            enclosing_ball(pts, kQuadVerts * kClusterQuads, ball);
+            const float cx = ball[0], cy = ball[1], cz = ball[2], rad = ball[3];
+            for (int q = 0; q < kClusterQuads; ++q) {
+                float qb[4];
+                enclosing_ball(pts + q * kQuadVerts, kQuadVerts, qb);
+                // a quad slot without a triangle of its own repeats the cluster's first quad: harmless (level 2 drops
+                // invalid slots) and keeps level 1 free of a special case
+                out.qbounds.insert(out.qbounds.end(), {qb[0], qb[1], qb[2], qb[3]});
             }
             out.bounds.insert(out.bounds.end(), {cx, cy, cz, rad});
         }

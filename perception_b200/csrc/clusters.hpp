@@ -30,6 +30,9 @@ struct ClusterSet {
     // to the second only; a quad holding a single triangle has vertex 3 = vertex 2.
     std::vector<float> recs;
     std::vector<float> bounds;   // n_clusters x 4: centre xyz, radius (inf when a coordinate is not finite)
+    // n_clusters x kClusterQuads x 4: bounding sphere of every QUAD (centre xyz, radius rounded up; inf when a
+    // coordinate is not finite; a slot that holds no triangle of its own repeats quad 0) -- level 1 of the candidate test
+    std::vector<float> qbounds;
     std::vector<int> orig;       // n_clusters x kClusterTris: original (global) triangle index of every slot
     // n_clusters: 6 bits per slot, (i0 | i1 << 2 | i2 << 4) = quad vertices of the triangle's v0, v1, v2 in the
     // ORIGINAL order, or kPermInvalid for a slot without a triangle of its own

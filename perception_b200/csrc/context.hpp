@@ -39,10 +39,12 @@ struct ModelsDev {
     const int* model_low = nullptr;   // exclusive scan of tris_model_count (image_renderer.cuh:373-380)
     const int* model_high = nullptr;  // inclusive scan
     const float* model_aabb = nullptr;  // 6 floats per model: min xyz, max xyz (object-space)
+    const float* model_qrmax = nullptr; // per model: largest finite quad bounding-sphere radius (level-1 scale bound)
     // clusters (clusters.hpp): Morton-ordered groups of kClusterTris triangles with a bounding sphere
     const float* cl_recs = nullptr;     // n_clusters x 24: rec[c][q][3 * i + a] = coordinate a of vertex i of quad q
     const uint32_t* cl_perm = nullptr;  // n_clusters: 6 bits per triangle slot, its three quad vertices in original order
     const float4* cl_bounds = nullptr;  // centre xyz, radius
+    const float4* q_bounds = nullptr;   // 2 per cluster: bounding sphere of each quad
     const int* cl_orig = nullptr;       // n_clusters x 4: original triangle index (colour tie-break, colour lookup)
     const int* cl_low = nullptr;        // cluster range per model
     const int* cl_high = nullptr;
@@ -84,10 +86,12 @@ struct perch_ctx {
     int* d_model_low = nullptr;
     int* d_model_high = nullptr;
     float* d_model_aabb = nullptr;
+    float* d_model_qrmax = nullptr;
     float* d_tri_lab = nullptr;        // 3 x T CIELAB of the triangle colours (cost_type 1)
     float* d_cl_recs = nullptr;
     uint32_t* d_cl_perm = nullptr;
     float4* d_cl_bounds = nullptr;
+    float4* d_q_bounds = nullptr;
     int* d_cl_orig = nullptr;
     int* d_cl_low = nullptr;
     int* d_cl_high = nullptr;

@@ -36,11 +36,11 @@ constexpr int kWarps = kThreads / 32;
 #endif
 constexpr int kMinCtas = PERCH_POSE_MIN_CTAS;  // resident CTAs per SM the register budget is sized for (32 warps)
 constexpr int kQueueCap = 16 * kThreads;   // candidate triangles buffered between exact passes
-constexpr int kClaim = 64;        // clusters tested per warp claim (two per lane: independent loads in flight)
-constexpr int kPendStep = 16;     // surviving clusters tested per warp step (two lanes each: one per quad)
-constexpr int kPendCap = 96;      // per-warp list of surviving clusters awaiting the per-triangle test (< 16 carried + 64)
-constexpr int kClaimMaxTris = (kClaim + kPendStep) * 4;  // most candidates one claim can append (incl. carried clusters)
-static_assert(kClusterTris == 4 && kClusterQuads == 2, "lane mapping of the per-triangle test assumes 2 quads of 2 triangles");
+constexpr int kLaneQuads = 4;     // quads sphere-tested per lane per claim (independent loads in flight)
+constexpr int kClaim = 32 * kLaneQuads;  // quads per warp claim
+constexpr int kPendCap = kClaim + 32;    // per-warp list of surviving quads awaiting the per-triangle test (< 32 carried)
+constexpr int kClaimMaxTris = kPendCap * 2;  // most candidates one claim can append (incl. carried quads)
+static_assert(kClusterTris == 4 && kClusterQuads == 2, "quad q = 2 * cluster + (0 | 1), triangle slot = 2 * q + (0 | 1)");
 constexpr int kBigCells = 48;     // lattice pixels above which a triangle is rasterised by the whole CTA
 constexpr int kBigCap = 64;
 // Bounds on |approximate - exact| screen coordinates (pixels) assumed by the culling levels.  tools/approx_error.cu
@@ -231,8 +231,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
     const int mask_words = (MODE == MODE_COST) ? a.mask_words : 0;
     uint32_t* mask = reinterpret_cast<uint32_t*>(smem_raw + (size_t)a.tile_cap * sizeof(zkey));
     int* queue = reinterpret_cast<int*>(mask + mask_words);
-    int* wpend = queue + kQueueCap + (threadIdx.x >> 5) * (kPendCap + 64);  // per-warp surviving clusters
-    int* wstage = wpend + kPendCap;                                          // per-warp staged candidate triangles (< 64)
+    int* wpend = queue + kQueueCap + (threadIdx.x >> 5) * kPendCap;  // per-warp quads that survived level 1
 
     __shared__ Mat4 s_pose;
     __shared__ int s_rect[4];
@@ -240,6 +239,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
     __shared__ float s_apx[20];
     __shared__ int s_big[kBigCap];
     __shared__ int s_n, s_c, s_e;
+    __shared__ float s_minz;  // smallest camera-space depth of the posed model AABB (0: unknown / not in front)
 
     const int pose_i = blockIdx.x;
     const int tid = threadIdx.x;
@@ -283,9 +283,11 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
             maxx = fmaxf(maxx, __shfl_xor_sync(0xffffffffu, maxx, o));
             miny = fminf(miny, __shfl_xor_sync(0xffffffffu, miny, o));
             maxy = fmaxf(maxy, __shfl_xor_sync(0xffffffffu, maxy, o));
+            minz = fminf(minz, __shfl_xor_sync(0xffffffffu, minz, o));
         }
         bad = __any_sync(0xffffffffu, bad);
         if (tid == 0) {
+            s_minz = (bad || !model_ok) ? 0.f : minz;
             int x0 = 0, x1 = Lw - 1, y0 = 0, y1 = Lh - 1;
             if (!model_ok || t_high <= t_low || cl_high <= cl_low) { x0 = 1; x1 = 0; }
             else if (!bad) {
@@ -401,43 +403,86 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
 
             // Conservative culling (pass A), in lattice coordinates.  `lattice_hit`: can the reference's pixel loops,
             // P in (min-0.5, max] clamped to the image (image_renderer.cuh:110-111), visit a lattice pixel of this band,
-            // when the true bounds may differ from (minx..maxy) by kEps pixels?
+            // when the true bounds may differ from (minx..maxy) by kEps pixels?  I.e. is there an integer in
+            // [min - m_lo - 1e-3, max + m_hi] along both axes, inside the band.
             const float m_lo = (0.5f + kEps) * inv_s, m_hi = kEps * inv_s;
+            const float m_lo3 = m_lo + 1e-3f, clamp_lo_x = band_lo_x - 1e-3f, clamp_lo_y = band_lo_y - 1e-3f;
             auto lattice_hit = [&](float minx, float maxx, float miny, float maxy) -> bool {
-                float lo_x = fmaxf(minx - m_lo, band_lo_x), hi_x = fminf(maxx + m_hi, band_hi_x);
-                float lo_y = fmaxf(miny - m_lo, band_lo_y), hi_y = fminf(maxy + m_hi, band_hi_y);
-                return (ceilf(lo_x - 1e-3f) <= hi_x) && (ceilf(lo_y - 1e-3f) <= hi_y);
+                const float lo_x = fmaxf(minx - m_lo3, clamp_lo_x), hi_x = fminf(maxx + m_hi, band_hi_x);
+                const float lo_y = fmaxf(miny - m_lo3, clamp_lo_y), hi_y = fminf(maxy + m_hi, band_hi_y);
+                return (floorf(hi_x) >= lo_x) && (floorf(hi_y) >= lo_y);
             };
             const float U0 = s_apx[0], U1 = s_apx[1], U2 = s_apx[2], U3 = s_apx[3];
             const float V0 = s_apx[4], V1 = s_apx[5], V2 = s_apx[6], V3 = s_apx[7];
             const float C0 = s_apx[8], C1 = s_apx[9], C2 = s_apx[10], C3 = s_apx[11];
             const float offx = s_apx[12], offy = s_apx[13];
-            // Level 1: bounding sphere of a cluster.  Anything not provably finite and in front of the camera is kept.
-            auto cluster_hits = [&](int c) -> bool {
-                const float4 b = __ldg(a.models.cl_bounds + c);
+            // Level 1: bounding sphere of a QUAD (two edge-sharing triangles; clusters.cpp).  A point within r of a centre c
+            // with camera depth Z_c moves the lattice coordinate ux by at most r (|U| + |ux_c| |C|) / (Z_c - r |C|)   (|.| =
+            // norm of the 3-vector part; ux_c relative to the principal point).  Per pose: centres lie inside the model AABB,
+            // so Z_c >= zmin, the nearest AABB corner; with rmax the model's largest quad radius,
+            // 1 / (Z_c - r |C|) <= g / Z_c for ONE per-pose g = 1 / (1 - rmax |C| / zmin): the second reciprocal of the
+            // textbook form disappears and the projected radius is (r / Z_c) (|U| g + |ux_c| |C| g).  When the AABB is not
+            // safely in front of the camera (zmin <= 4 rmax |C|) g = inf: every quad passes to level 2, which sends
+            // near-plane vertices to the exact path.
+            // NaN / inf anywhere makes the rejecting comparisons false: kept.  (Round 1 tested the spheres of 4-triangle
+            // clusters here: at ~5 px against the 8 px lattice 52 % survived; a quad sphere is ~3.9 px and 30 % survive.)
+            float Kg, KUg, KVg;  // |C| g, |U| g, |V| g
+            {
+                const float nC = s_apx[16], zmin = s_minz;
+                const float rmax = model_ok ? __ldg(a.models.model_qrmax + model) : 0.f;
+                const bool safe = zmin > 4.f * rmax * nC;
+                const float g = safe ? 1.001f / (1.f - rmax * nC / fmaxf(zmin, 1e-30f)) : INFINITY;
+                Kg = nC * g; KUg = s_apx[14] * g; KVg = s_apx[15] * g;
+            }
+            const float offx_lo = offx - m_lo3, offy_lo = offy - m_lo3;
+            auto sphere_rejects = [&](const float4 b) -> bool {
                 const float n0 = fmaf(b.z, U2, fmaf(b.y, U1, fmaf(b.x, U0, U3)));
                 const float n1 = fmaf(b.z, V2, fmaf(b.y, V1, fmaf(b.x, V0, V3)));
-                const float zc = fmaf(b.z, C2, fmaf(b.y, C1, fmaf(b.x, C0, C3)));
-                const float iz = __frcp_approx(zc);
+                const float iz = __frcp_approx(fmaf(b.z, C2, fmaf(b.y, C1, fmaf(b.x, C0, C3))));
                 const float ux0 = n0 * iz, uy0 = n1 * iz;
-                const float nC = s_apx[16];
-                const float zden = fmaf(-b.w, nC, zc);
-                const float rr = b.w * __frcp_approx(zden);
-                const float Rx = fmaf(rr, fmaf(fabsf(ux0), nC, s_apx[14]), m_hi);
-                const float Ry = fmaf(rr, fmaf(fabsf(uy0), nC, s_apx[15]), m_hi);
-                const float ux = ux0 + offx, uy = uy0 + offy;
-                if (!(zden > 1e-6f) || !(fabsf(ux) + fabsf(uy) + Rx + Ry < 1e30f)) return true;
-                return lattice_hit(ux - Rx, ux + Rx, uy - Ry, uy + Ry);
+                const float t = b.w * fabsf(iz);  // |iz|: with g = inf (AABB not safely in front) the radius must be +inf
+                const float Rx = fmaf(t, fmaf(fabsf(ux0), Kg, KUg), m_hi), Ry = fmaf(t, fmaf(fabsf(uy0), Kg, KVg), m_hi);
+                const float hi_x = fminf((ux0 + offx) + Rx, band_hi_x), lo_x = fmaxf((ux0 + offx_lo) - Rx, clamp_lo_x);
+                const float hi_y = fminf((uy0 + offy) + Ry, band_hi_y), lo_y = fmaxf((uy0 + offy_lo) - Ry, clamp_lo_y);
+                return (floorf(hi_x) < lo_x) || (floorf(hi_y) < lo_y);
             };
-            // Level 2: approximate bboxes of the two triangles of one quad -- four vertex transforms for two triangles
-            // (vertices 0,1 = shared edge, 2 = first triangle's own, 3 = second's).  Bit 0 / 1 of the result = first /
-            // second triangle is a candidate.  NaN/inf/absurd coordinates (whose handling by the reference's select
-            // chain is order dependent) go to the exact path, which re-derives everything.
-            auto quad_hits = [&](int c, int q) -> unsigned {
-                const float4* rec = reinterpret_cast<const float4*>(a.models.cl_recs + (int64_t)(2 * c + q) * kQuadFloats);
+            // Level 3 on already-projected vertices: a candidate whose approximate bbox holds exactly ONE lattice pixel is
+            // dropped when that pixel lies clearly outside the triangle.  With approximate vertices within d px of the
+            // exact ones, an edge function cross(Vj - Vi, P - Vi) differs from its exact counterpart by less than
+            // 4.25 * d * D (D >= the largest distance involved; d = kEps3 scaled for near vertices), so `sgn * E < -6 d D`
+            // together with `|2 * area| > 6 d D` (the orientation is then certain) implies a strictly negative exact
+            // barycentric, i.e. the reference rejects the fragment (image_renderer.cuh:114-115).  NaN makes every
+            // comparison false: kept.  The test is symmetric in the vertex order.
+            auto pixel_outside = [&](float x0, float y0, float x1, float y1, float x2, float y2, float izmax) -> bool {
+                const float near_scale = fmaxf(1.f, kRefZ * izmax);
+                const float minx = fminf(fminf(x0, x1), x2), maxx = fmaxf(fmaxf(x0, x1), x2);
+                const float miny = fminf(fminf(y0, y1), y2), maxy = fmaxf(fmaxf(y0, y1), y2);
+                const float lo_x = fmaxf(minx - m_lo3, clamp_lo_x), hi_x = fminf(maxx + m_hi, band_hi_x);
+                const float lo_y = fmaxf(miny - m_lo3, clamp_lo_y), hi_y = fminf(maxy + m_hi, band_hi_y);
+                const float px = ceilf(lo_x), py = ceilf(lo_y);
+                // exactly one integer in [lo - 1e-3, hi] along each axis
+                const bool single = (px <= hi_x) && (px + 1.f > hi_x) && (py <= hi_y) && (py + 1.f > hi_y);
+                const float ax = x1 - x0, ay = y1 - y0, bx = x2 - x0, by = y2 - y0;
+                const float area2 = ax * by - bx * ay;
+                const float sgn = area2 < 0.f ? -1.f : 1.f;
+                const float e0 = ax * (py - y0) - ay * (px - x0);
+                const float e1 = (x2 - x1) * (py - y1) - (y2 - y1) * (px - x1);
+                const float e2 = -bx * (py - y2) + by * (px - x2);
+                const float D = (maxx - minx) + (maxy - miny) + 1.2f * inv_s;
+                const float tol = (6.f * kEps3 * inv_s) * near_scale * D;
+                const float worst = fminf(fminf(e0 * sgn, e1 * sgn), e2 * sgn);
+                return single && (fabsf(area2) > tol) && (worst < -tol) && (tol < 1e6f);
+            };
+            // Levels 2 + 3 of one quad: four vertex transforms for two triangles (vertices 0,1 = shared edge, 2 = first
+            // triangle's own, 3 = second's); approximate bbox per triangle against the lattice (level 2), then the
+            // single-pixel edge test (level 3) on the same projected vertices.  Bit 0 / 1 of the result = first / second
+            // triangle goes to the exact path.  NaN/inf/absurd coordinates or a vertex near the camera plane (whose handling
+            // by the reference's select chain is order dependent) go to the exact path untested.
+            auto quad_candidates = [&](int q) -> unsigned {
+                const float4* rec = reinterpret_cast<const float4*>(a.models.cl_recs + (int64_t)q * kQuadFloats);
                 const float4 r0 = __ldg(rec), r1 = __ldg(rec + 1), r2 = __ldg(rec + 2);
                 const float qx[4] = {r0.x, r0.w, r1.z, r2.y}, qy[4] = {r0.y, r1.x, r1.w, r2.z}, qz[4] = {r0.z, r1.y, r2.x, r2.w};
-                float ux[4], uy[4], izmax = 0.f;
+                float ux[4], uy[4], az[4];
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
                     const float x = qx[k], y = qy[k], z = qz[k];
@@ -446,141 +491,82 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                     const float iz = __frcp_approx(fmaf(z, C2, fmaf(y, C1, fmaf(x, C0, C3))));
                     ux[k] = fmaf(n0, iz, offx);
                     uy[k] = fmaf(n1, iz, offy);
-                    izmax = fmaxf(izmax, fabsf(iz));
+                    az[k] = fabsf(iz);
                 }
                 const float sum = ((ux[0] + ux[1]) + (ux[2] + ux[3])) + ((uy[0] + uy[1]) + (uy[2] + uy[3]));
-                // not finite, or a vertex near the camera plane: both triangles go to the exact path
-                if (!(fabsf(sum) < 1e30f) || !(izmax < 1.0f / kNearZ)) return 3u;
+                const float iz01 = fmaxf(az[0], az[1]);
+                if (!(fabsf(sum) < 1e30f) || !(fmaxf(iz01, fmaxf(az[2], az[3])) < 1.0f / kNearZ)) return 3u;
                 const float ex0 = fminf(ux[0], ux[1]), ex1 = fmaxf(ux[0], ux[1]);
                 const float ey0 = fminf(uy[0], uy[1]), ey1 = fmaxf(uy[0], uy[1]);
-                unsigned r = lattice_hit(fminf(ex0, ux[2]), fmaxf(ex1, ux[2]), fminf(ey0, uy[2]), fmaxf(ey1, uy[2])) ? 1u : 0u;
-                if (lattice_hit(fminf(ex0, ux[3]), fmaxf(ex1, ux[3]), fminf(ey0, uy[3]), fmaxf(ey1, uy[3]))) r |= 2u;
+                unsigned r = 0u;
+                if (lattice_hit(fminf(ex0, ux[2]), fmaxf(ex1, ux[2]), fminf(ey0, uy[2]), fmaxf(ey1, uy[2])) &&
+                    !pixel_outside(ux[0], uy[0], ux[1], uy[1], ux[2], uy[2], fmaxf(iz01, az[2])))
+                    r |= 1u;
+                if (lattice_hit(fminf(ex0, ux[3]), fmaxf(ex1, ux[3]), fminf(ey0, uy[3]), fmaxf(ey1, uy[3])) &&
+                    !pixel_outside(ux[0], uy[0], ux[1], uy[1], ux[3], uy[3], fmaxf(iz01, az[3])))
+                    r |= 2u;
                 return r;
             };
-            // Level 3 (when a warp has 32 candidates staged, every lane busy): a candidate whose approximate bbox holds exactly ONE lattice
-            // pixel is dropped when that pixel lies clearly outside the triangle.  With approximate vertices within
-            // d px of the exact ones, an edge function cross(Vj - Vi, P - Vi) differs from its exact counterpart
-            // by less than 4.25 * d * D (D >= the largest distance involved; d = kEps3 scaled for near vertices), so `sgn * E < -6 d D` together with
-            // `|2 * area| > 6 d D` (the orientation is then certain) implies a strictly negative exact barycentric, i.e.
-            // the reference rejects the fragment (image_renderer.cuh:114-115).  NaN makes every comparison false: kept.
-            auto pixel_outside = [&](int t) -> bool {
-                float v[9];
-                load_tri(a.models, t, v);
-                float ux[3], uy[3], iz[3];
-#pragma unroll
-                for (int k = 0; k < 3; ++k) {
-                    const float x = v[3 * k], y = v[3 * k + 1], z = v[3 * k + 2];
-                    const float n0 = fmaf(z, U2, fmaf(y, U1, fmaf(x, U0, U3)));
-                    const float n1 = fmaf(z, V2, fmaf(y, V1, fmaf(x, V0, V3)));
-                    iz[k] = __frcp_approx(fmaf(z, C2, fmaf(y, C1, fmaf(x, C0, C3))));
-                    ux[k] = fmaf(n0, iz[k], offx);
-                    uy[k] = fmaf(n1, iz[k], offy);
-                }
-                const float near_scale = fmaxf(1.f, kRefZ * fmaxf(fmaxf(fabsf(iz[0]), fabsf(iz[1])), fabsf(iz[2])));
-                const float minx = fminf(fminf(ux[0], ux[1]), ux[2]), maxx = fmaxf(fmaxf(ux[0], ux[1]), ux[2]);
-                const float miny = fminf(fminf(uy[0], uy[1]), uy[2]), maxy = fmaxf(fmaxf(uy[0], uy[1]), uy[2]);
-                const float lo_x = fmaxf(minx - m_lo, band_lo_x), hi_x = fminf(maxx + m_hi, band_hi_x);
-                const float lo_y = fmaxf(miny - m_lo, band_lo_y), hi_y = fminf(maxy + m_hi, band_hi_y);
-                const float px = ceilf(lo_x - 1e-3f), py = ceilf(lo_y - 1e-3f);
-                // exactly one integer in [lo - 1e-3, hi] along each axis
-                const bool single = (px <= hi_x) && (px + 1.f > hi_x) && (py <= hi_y) && (py + 1.f > hi_y);
-                const float ax = ux[1] - ux[0], ay = uy[1] - uy[0], bx = ux[2] - ux[0], by = uy[2] - uy[0];
-                const float area2 = ax * by - bx * ay;
-                const float sgn = area2 < 0.f ? -1.f : 1.f;
-                const float e0 = ax * (py - uy[0]) - ay * (px - ux[0]);
-                const float e1 = (ux[2] - ux[1]) * (py - uy[1]) - (uy[2] - uy[1]) * (px - ux[1]);
-                const float e2 = -bx * (py - uy[2]) + by * (px - ux[2]);
-                const float D = (maxx - minx) + (maxy - miny) + 1.2f * inv_s;
-                const float tol = (6.f * kEps3 * inv_s) * near_scale * D;
-                const float worst = fminf(fminf(e0 * sgn, e1 * sgn), e2 * sgn);
-                return single && (fabsf(area2) > tol) && (worst < -tol) && (tol < 1e6f);
-            };
-            // Level-2 survivors are staged per warp; whenever 32 are staged (and at the end of pass A) every lane takes
-            // one through level 3 and the survivors of that go to the CTA's queue with one atomic per batch.
-            int nstage = 0;  // warp-uniform: staged candidates of this warp
             const unsigned lt_mask = (1u << lane) - 1u;
-            auto flush_stage = [&](int count) {
-                int entry = 0;
-                bool keep = false;
-                if (lane < count) {
-                    entry = wstage[lane];
-                    keep = !pixel_outside(entry);
-                }
-                const unsigned kb = __ballot_sync(0xffffffffu, keep);
-                if (lane == 0) { STAT(3, __popc(kb)); STAT(9, 1); }
-                int slot = 0;
-                if (lane == 0 && kb) slot = atomicAdd(&s_qcount, __popc(kb));
-                slot = __shfl_sync(0xffffffffu, slot, 0);
-                if (keep) queue[slot + __popc(kb & lt_mask)] = entry;
-            };
-            auto stage_hit = [&](bool hit, int entry) {
-                const unsigned ballot = __ballot_sync(0xffffffffu, hit);
-                if (hit) wstage[nstage + __popc(ballot & lt_mask)] = entry;
-                nstage += __popc(ballot);
-                if (lane == 0) { STAT(2, __popc(ballot)); STAT(8, 1); }
-                if (nstage >= 32) {
-                    __syncwarp();
-                    flush_stage(32);
-                    nstage -= 32;
-                    const int carry = (lane < nstage) ? wstage[32 + lane] : 0;
-                    __syncwarp();
-                    if (lane < nstage) wstage[lane] = carry;
-                }
-                __syncwarp();
-            };
-            // per-triangle test of kPendStep pending clusters, one lane per quad; a slot that merely repeats its quad's
-            // other triangle (kPermInvalid) is never a candidate
+            // levels 2 + 3 of `count` <= 32 pending quads, one lane each; the survivors go to the CTA's queue with one
+            // atomic per call.  A slot that merely repeats its quad's other triangle (kPermInvalid) is never a candidate.
             auto test_pending = [&](int first, int count) {
-                const int e = lane >> 1, q = lane & 1;
                 unsigned hits = 0;
                 int ea = 0, eb = 0;
-                if (e < count) {
-                    const int c = wpend[first + e];
-                    const uint32_t perm = __ldg(a.models.cl_perm + c) >> (12 * q);
+                if (lane < count) {
+                    const int q = wpend[first + lane];
+                    const uint32_t perm = __ldg(a.models.cl_perm + (q >> 1)) >> (12 * (q & 1));
                     const uint32_t pa = perm & 63u, pb = (perm >> 6) & 63u;
-                    hits = quad_hits(c, q);
+                    hits = quad_candidates(q);
                     if (pa == kPermInvalid) hits &= ~1u;
                     if (pb == kPermInvalid) hits &= ~2u;
-                    ea = (4 * c + 2 * q) | (int)(pa << kSlotBits);
-                    eb = (4 * c + 2 * q + 1) | (int)(pb << kSlotBits);
+                    ea = (2 * q) | (int)(pa << kSlotBits);
+                    eb = (2 * q + 1) | (int)(pb << kSlotBits);
                 }
-                stage_hit(hits & 1u, ea);
-                stage_hit(hits & 2u, eb);
+                const unsigned b0 = __ballot_sync(0xffffffffu, hits & 1u), b1 = __ballot_sync(0xffffffffu, hits & 2u);
+                const int n0 = __popc(b0), total = n0 + __popc(b1);
+                if (lane == 0) { STAT(1, count); STAT(2, count); STAT(3, total); STAT(9, 1); }
+                int slot = 0;
+                if (lane == 0 && total) slot = atomicAdd(&s_qcount, total);
+                slot = __shfl_sync(0xffffffffu, slot, 0);
+                if (hits & 1u) queue[slot + __popc(b0 & lt_mask)] = ea;
+                if (hits & 2u) queue[slot + n0 + __popc(b1 & lt_mask)] = eb;
             };
 
-            // Warps claim groups of kClaim clusters dynamically (no block barrier inside pass A); a warp stops
-            // claiming when the candidate queue could overflow.
-            const int n_groups = (cl_high - cl_low + kClaim - 1) / kClaim;
+            // Warps claim groups of kClaim quads dynamically (no block barrier inside pass A); a warp stops claiming when
+            // the candidate queue could overflow.
+            const int q_low = 2 * cl_low, q_high = 2 * cl_high;
+            const int n_groups = (q_high - q_low + kClaim - 1) / kClaim;
             if (tid == 0) s_next = 0;
             __syncthreads();
             for (;;) {
                 int npend = 0;  // warp-uniform
                 for (;;) {
                     int g = 0x7fffffff;
-                    if (lane == 0 && *(volatile int*)&s_qcount <= kQueueCap - kWarps * (kClaimMaxTris + 32)) g = atomicAdd(&s_next, 1);
+                    if (lane == 0 && *(volatile int*)&s_qcount <= kQueueCap - kWarps * kClaimMaxTris) g = atomicAdd(&s_next, 1);
                     g = __shfl_sync(0xffffffffu, g, 0);
                     if (g >= n_groups) break;
-                    const int c0 = cl_low + g * kClaim + lane, c1 = c0 + 32;
-                    const bool keep0 = (c0 < cl_high) && cluster_hits(c0);
-                    const bool keep1 = (c1 < cl_high) && cluster_hits(c1);
-                    const unsigned b0 = __ballot_sync(0xffffffffu, keep0), b1 = __ballot_sync(0xffffffffu, keep1);
-                    if (keep0) wpend[npend + __popc(b0 & lt_mask)] = c0;
-                    if (keep1) wpend[npend + __popc(b0) + __popc(b1 & lt_mask)] = c1;
-                    npend += __popc(b0) + __popc(b1);
-                    if (lane == 0) { STAT(0, min(kClaim, cl_high - (cl_low + g * kClaim))); STAT(1, __popc(b0) + __popc(b1)); }
+                    const int qb = q_low + g * kClaim + lane;
+                    float4 bnd[kLaneQuads];
+#pragma unroll
+                    for (int k = 0; k < kLaneQuads; ++k) bnd[k] = __ldg(a.models.q_bounds + min(qb + 32 * k, q_high - 1));
+#pragma unroll
+                    for (int k = 0; k < kLaneQuads; ++k) {
+                        const int q = qb + 32 * k;
+                        const bool keep = (q < q_high) && !sphere_rejects(bnd[k]);
+                        const unsigned bal = __ballot_sync(0xffffffffu, keep);
+                        if (keep) wpend[npend + __popc(bal & lt_mask)] = q;
+                        npend += __popc(bal);
+                    }
+                    if (lane == 0) { STAT(0, min(kClaim, q_high - (q_low + g * kClaim))); }
                     __syncwarp();
-                    while (npend >= kPendStep) {
-                        npend -= kPendStep;
-                        test_pending(npend, kPendStep);
+                    while (npend >= 32) {
+                        npend -= 32;
+                        test_pending(npend, 32);
                     }
                     __syncwarp();
                 }
                 if (npend > 0) test_pending(0, npend);
-                if (nstage > 0) {
-                    __syncwarp();
-                    flush_stage(nstage);
-                    nstage = 0;
-                }
                 __syncthreads();
                 const int qn = s_qcount;
                 const bool all_claimed = *(volatile int*)&s_next >= n_groups;
@@ -843,7 +829,7 @@ __global__ void fill_keys_kernel(unsigned long long* keys, int n) {
 size_t pose_kernel_smem_bytes(const PoseArgs& a, bool image_mode, bool color) {
     size_t b = (size_t)a.tile_cap * ((color || image_mode) ? 8 : 4) + (image_mode ? 0 : (size_t)a.mask_words * 4) +
                (size_t)kQueueCap * 4;
-    return b + (size_t)kWarps * (kPendCap + 64) * sizeof(int);
+    return b + (size_t)kWarps * kPendCap * sizeof(int);
 }
 
 template <int MODE, bool COLOR>

@@ -26,9 +26,9 @@ out = r.render_cuda_multi_unified("COST", wl["poses"], wl["pmm"], wl["plabel"], 
 st = (C.c_ulonglong * 16)()
 lib.perch_debug_stats(st, 0)
 s = np.array(list(st), np.float64) / P
-names = ["clusters tested", "L1 survivors (clusters)", "L2 survivors (triangles)", "L3 survivors (triangles)",
+names = ["quads sphere-tested (L1)", "L1 survivors (quads)", "quads through L2+L3", "L2+L3 survivors (triangles)",
          "exact: triangles with lattice cells", "exact: lattice cells visited", "exact: fragments passing",
-         "cooperative triangles", "L2 warp steps", "L3 warp steps", "pass A/B rounds", "bands", "band cells"]
+         "cooperative triangles", "-", "L2 warp steps", "pass A/B rounds", "bands", "band cells"]
 print(f"workload {name}: P={P}, per pose:")
 for n, v in zip(names, s):
     print(f"  {n:40s} {v:10.1f}")
