@@ -36,7 +36,10 @@ constexpr int kWarps = kThreads / 32;
 #endif
 constexpr int kMinCtas = PERCH_POSE_MIN_CTAS;  // resident CTAs per SM the register budget is sized for (32 warps)
 constexpr int kQueueCap = 16 * kThreads;   // candidate triangles buffered between exact passes
-constexpr int kLaneQuads = 4;     // quads sphere-tested per lane per claim (independent loads in flight)
+#ifndef PERCH_LANE_QUADS
+#define PERCH_LANE_QUADS 4
+#endif
+constexpr int kLaneQuads = PERCH_LANE_QUADS;  // quads sphere-tested per lane per claim (independent loads in flight)
 constexpr int kClaim = 32 * kLaneQuads;  // quads per warp claim
 constexpr int kPendCap = kClaim + 32;    // per-warp list of surviving quads awaiting the per-triangle test (< 32 carried)
 constexpr int kClaimMaxTris = kPendCap * 2;  // most candidates one claim can append (incl. carried quads)
@@ -227,11 +230,15 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
     using Z = ZCell<COLOR>;
     using zkey = typename Z::type;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    zkey* zbuf = reinterpret_cast<zkey*>(smem_raw);
-    const int mask_words = (MODE == MODE_COST) ? a.mask_words : 0;
-    uint32_t* mask = reinterpret_cast<uint32_t*>(smem_raw + (size_t)a.tile_cap * sizeof(zkey));
-    int* queue = reinterpret_cast<int*>(mask + mask_words);
+    // layout: [candidate queue][per-warp pending quads] at compile-time offsets (the hot loops of pass A address them
+    // without pointer arithmetic), then the z-buffer (tile_cap cells) and the explained-point bitmask (run-time sizes)
+    int* queue = reinterpret_cast<int*>(smem_raw);
     int* wpend = queue + kQueueCap + (threadIdx.x >> 5) * kPendCap;  // per-warp quads that survived level 1
+    constexpr size_t kFixedBytes = (size_t)(kQueueCap + kWarps * kPendCap) * sizeof(int);
+    static_assert(kFixedBytes % 16 == 0, "the z-buffer behind the fixed part must stay 16-byte aligned");
+    zkey* zbuf = reinterpret_cast<zkey*>(smem_raw + kFixedBytes);
+    const int mask_words = (MODE == MODE_COST) ? a.mask_words : 0;
+    uint32_t* mask = reinterpret_cast<uint32_t*>(smem_raw + kFixedBytes + (size_t)a.tile_cap * sizeof(zkey));
 
     __shared__ Mat4 s_pose;
     __shared__ int s_rect[4];
@@ -401,17 +408,12 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                 }
             };
 
-            // Conservative culling (pass A), in lattice coordinates.  `lattice_hit`: can the reference's pixel loops,
+            // Conservative culling (pass A), in lattice coordinates.  The question at every level: can the reference's pixel loops,
             // P in (min-0.5, max] clamped to the image (image_renderer.cuh:110-111), visit a lattice pixel of this band,
             // when the true bounds may differ from (minx..maxy) by kEps pixels?  I.e. is there an integer in
             // [min - m_lo - 1e-3, max + m_hi] along both axes, inside the band.
             const float m_lo = (0.5f + kEps) * inv_s, m_hi = kEps * inv_s;
             const float m_lo3 = m_lo + 1e-3f, clamp_lo_x = band_lo_x - 1e-3f, clamp_lo_y = band_lo_y - 1e-3f;
-            auto lattice_hit = [&](float minx, float maxx, float miny, float maxy) -> bool {
-                const float lo_x = fmaxf(minx - m_lo3, clamp_lo_x), hi_x = fminf(maxx + m_hi, band_hi_x);
-                const float lo_y = fmaxf(miny - m_lo3, clamp_lo_y), hi_y = fminf(maxy + m_hi, band_hi_y);
-                return (floorf(hi_x) >= lo_x) && (floorf(hi_y) >= lo_y);
-            };
             const float U0 = s_apx[0], U1 = s_apx[1], U2 = s_apx[2], U3 = s_apx[3];
             const float V0 = s_apx[4], V1 = s_apx[5], V2 = s_apx[6], V3 = s_apx[7];
             const float C0 = s_apx[8], C1 = s_apx[9], C2 = s_apx[10], C3 = s_apx[11];
@@ -446,22 +448,21 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                 const float hi_y = fminf((uy0 + offy) + Ry, band_hi_y), lo_y = fmaxf((uy0 + offy_lo) - Ry, clamp_lo_y);
                 return (floorf(hi_x) < lo_x) || (floorf(hi_y) < lo_y);
             };
-            // Level 3 on already-projected vertices: a candidate whose approximate bbox holds exactly ONE lattice pixel is
-            // dropped when that pixel lies clearly outside the triangle.  With approximate vertices within d px of the
-            // exact ones, an edge function cross(Vj - Vi, P - Vi) differs from its exact counterpart by less than
-            // 4.25 * d * D (D >= the largest distance involved; d = kEps3 scaled for near vertices), so `sgn * E < -6 d D`
-            // together with `|2 * area| > 6 d D` (the orientation is then certain) implies a strictly negative exact
-            // barycentric, i.e. the reference rejects the fragment (image_renderer.cuh:114-115).  NaN makes every
-            // comparison false: kept.  The test is symmetric in the vertex order.
-            auto pixel_outside = [&](float x0, float y0, float x1, float y1, float x2, float y2, float izmax) -> bool {
-                const float near_scale = fmaxf(1.f, kRefZ * izmax);
-                const float minx = fminf(fminf(x0, x1), x2), maxx = fmaxf(fmaxf(x0, x1), x2);
-                const float miny = fminf(fminf(y0, y1), y2), maxy = fmaxf(fmaxf(y0, y1), y2);
+            // Levels 2 + 3 for one triangle given its projected vertices.  Level 2: can the approximate bbox hold a lattice
+            // pixel of this band?  Level 3: if it holds exactly ONE, is that pixel clearly outside the triangle?  With
+            // approximate vertices within d px of the exact ones, an edge function cross(Vj - Vi, P - Vi) differs from its
+            // exact counterpart by less than 4.25 * d * D (D >= the largest distance involved; d = kEps3 scaled for near
+            // vertices), so `sgn * E < -6 d D` together with `|2 * area| > 6 d D` (the orientation is then certain) implies a
+            // strictly negative exact barycentric, i.e. the reference rejects the fragment (image_renderer.cuh:114-115).
+            // Every rejecting comparison is false on NaN, so non-finite coordinates are kept (the exact path re-derives
+            // everything); the test is symmetric in the vertex order.  Returns true = candidate for the exact path.
+            auto tri_candidate = [&](float x0, float y0, float x1, float y1, float x2, float y2, float minx, float maxx,
+                                     float miny, float maxy, float izmax) -> bool {
                 const float lo_x = fmaxf(minx - m_lo3, clamp_lo_x), hi_x = fminf(maxx + m_hi, band_hi_x);
                 const float lo_y = fmaxf(miny - m_lo3, clamp_lo_y), hi_y = fminf(maxy + m_hi, band_hi_y);
-                const float px = ceilf(lo_x), py = ceilf(lo_y);
-                // exactly one integer in [lo - 1e-3, hi] along each axis
-                const bool single = (px <= hi_x) && (px + 1.f > hi_x) && (py <= hi_y) && (py + 1.f > hi_y);
+                const float px = ceilf(lo_x), py = ceilf(lo_y);  // first integer of [lo, hi] along each axis, if any
+                if ((px > hi_x) || (py > hi_y)) return false;    // level 2: no lattice pixel
+                const bool single = (px + 1.f > hi_x) && (py + 1.f > hi_y);
                 const float ax = x1 - x0, ay = y1 - y0, bx = x2 - x0, by = y2 - y0;
                 const float area2 = ax * by - bx * ay;
                 const float sgn = area2 < 0.f ? -1.f : 1.f;
@@ -469,15 +470,13 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                 const float e1 = (x2 - x1) * (py - y1) - (y2 - y1) * (px - x1);
                 const float e2 = -bx * (py - y2) + by * (px - x2);
                 const float D = (maxx - minx) + (maxy - miny) + 1.2f * inv_s;
-                const float tol = (6.f * kEps3 * inv_s) * near_scale * D;
+                const float tol = (6.f * kEps3 * inv_s) * fmaxf(1.f, kRefZ * izmax) * D;
                 const float worst = fminf(fminf(e0 * sgn, e1 * sgn), e2 * sgn);
-                return single && (fabsf(area2) > tol) && (worst < -tol) && (tol < 1e6f);
+                return !(single && (fabsf(area2) > tol) && (worst < -tol) && (tol < 1e6f));
             };
-            // Levels 2 + 3 of one quad: four vertex transforms for two triangles (vertices 0,1 = shared edge, 2 = first
-            // triangle's own, 3 = second's); approximate bbox per triangle against the lattice (level 2), then the
-            // single-pixel edge test (level 3) on the same projected vertices.  Bit 0 / 1 of the result = first / second
-            // triangle goes to the exact path.  NaN/inf/absurd coordinates or a vertex near the camera plane (whose handling
-            // by the reference's select chain is order dependent) go to the exact path untested.
+            // One quad: four vertex transforms for two triangles (vertices 0,1 = shared edge, 2 = first triangle's own,
+            // 3 = second's).  Bit 0 / 1 of the result = first / second triangle goes to the exact path.  A vertex near the
+            // camera plane (the approximation's error bound grows like 1/z) sends both there untested.
             auto quad_candidates = [&](int q) -> unsigned {
                 const float4* rec = reinterpret_cast<const float4*>(a.models.cl_recs + (int64_t)q * kQuadFloats);
                 const float4 r0 = __ldg(rec), r1 = __ldg(rec + 1), r2 = __ldg(rec + 2);
@@ -493,17 +492,19 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                     uy[k] = fmaf(n1, iz, offy);
                     az[k] = fabsf(iz);
                 }
+                // a NaN coordinate would be skipped by the min / max below (and its handling by the reference's select chain
+                // is order dependent): both triangles go to the exact path, which re-derives everything
                 const float sum = ((ux[0] + ux[1]) + (ux[2] + ux[3])) + ((uy[0] + uy[1]) + (uy[2] + uy[3]));
                 const float iz01 = fmaxf(az[0], az[1]);
-                if (!(fabsf(sum) < 1e30f) || !(fmaxf(iz01, fmaxf(az[2], az[3])) < 1.0f / kNearZ)) return 3u;
+                if (!(sum == sum) || !(fmaxf(iz01, fmaxf(az[2], az[3])) < 1.0f / kNearZ)) return 3u;
                 const float ex0 = fminf(ux[0], ux[1]), ex1 = fmaxf(ux[0], ux[1]);
                 const float ey0 = fminf(uy[0], uy[1]), ey1 = fmaxf(uy[0], uy[1]);
                 unsigned r = 0u;
-                if (lattice_hit(fminf(ex0, ux[2]), fmaxf(ex1, ux[2]), fminf(ey0, uy[2]), fmaxf(ey1, uy[2])) &&
-                    !pixel_outside(ux[0], uy[0], ux[1], uy[1], ux[2], uy[2], fmaxf(iz01, az[2])))
+                if (tri_candidate(ux[0], uy[0], ux[1], uy[1], ux[2], uy[2], fminf(ex0, ux[2]), fmaxf(ex1, ux[2]),
+                                  fminf(ey0, uy[2]), fmaxf(ey1, uy[2]), fmaxf(iz01, az[2])))
                     r |= 1u;
-                if (lattice_hit(fminf(ex0, ux[3]), fmaxf(ex1, ux[3]), fminf(ey0, uy[3]), fmaxf(ey1, uy[3])) &&
-                    !pixel_outside(ux[0], uy[0], ux[1], uy[1], ux[3], uy[3], fmaxf(iz01, az[3])))
+                if (tri_candidate(ux[0], uy[0], ux[1], uy[1], ux[3], uy[3], fminf(ex0, ux[3]), fmaxf(ex1, ux[3]),
+                                  fminf(ey0, uy[3]), fmaxf(ey1, uy[3]), fmaxf(iz01, az[3])))
                     r |= 2u;
                 return r;
             };
