@@ -234,6 +234,27 @@ int perch_icp_point2plane_nn(perch_ctx* ctx, const float* model_pcd, const int* 
                              float* out_transforms16, float* out_fitness, float* out_inlier_rmse, int* out_iterations,
                              float* out_pcd);
 
+/* Device-pointer forms behind the C++ backend for the reference's unchanged <cuda_icp/icp.h>
+ * (perception_b200/csrc/compat/cuda_icp_compat.cpp), where clouds and scenes live in device_vector_holder<Vec3f>:
+ * perch_icp_get_scene_device  the per-pixel scene points / normals perch_icp_set_scene left on the device;
+ * perch_icp_point2plane_device  ICP_Point2Plane_cuda (icp.h:92-99, icp.cu:156-218) of ONE device-resident cloud
+ *     (n_points x 3 floats, transformed in place) against device-resident scene buffers (d_scene_pcd = NULL: the resident
+ *     scene); nearest_neighbour = 1 selects Scene_nn's association, which needs the resident scene;
+ * perch_icp_depth2cloud_device  cuda_icp::depth2cloud_cuda<uint16_t | int32_t> (icp.h:83-90, icp.cu:225-297): valid
+ *     pixels (depth > 0) of every stride-th row / column, row-major, z = depth / 100, x = (column_index + tl_x - K02) /
+ *     K00 * z with the LATTICE column index like the reference.  Pass d_out_xyz = NULL to count.  (The reference's
+ *     mask index `x + y * width` overruns its `width * height / stride^2` mask for stride > 1; here the rows are
+ *     compacted in the order that index implies.) */
+int perch_icp_get_scene_device(perch_ctx* ctx, const float** d_pcd, const float** d_normals, int* width, int* height);
+int perch_icp_point2plane_device(perch_ctx* ctx, float* d_model_pcd, int n_points, const float* d_scene_pcd,
+                                 const float* d_scene_normals, int width, int height, const float K9[9],
+                                 float max_dist_diff, int nearest_neighbour, float relative_fitness, float relative_rmse,
+                                 int max_iteration, float out_transform16[16], float* out_fitness, float* out_inlier_rmse,
+                                 int* out_iterations);
+int perch_icp_depth2cloud_device(perch_ctx* ctx, const void* d_depth, int depth_bits, int width, int height,
+                                 const float K9[9], int stride, int tl_x, int tl_y, float* d_out_xyz, int capacity,
+                                 int* n_points);
+
 /* ---- k nearest neighbours (package API of cuda_renderer/knncuda.h) ------------------------------------------ */
 /* Replaces knn_cuda_global / knn_cuda_texture / knn_cublas (knncuda.h:33-100, knncuda.cu:276-421, 424-616, 618-838):
  * ref is dim x ref_nb and query dim x query_nb, one ROW per dimension (element (d, i) at d*nb + i); outputs are
@@ -456,7 +477,10 @@ int perch_compose_source(perch_ctx* ctx, const float* poses16, int n_poses, cons
  *   clutter_cost[p]         100 * cleared pixels / covered pixels, NaN if nothing is covered (the reference's extra
  *                           condition `source <= new_depth - 5` reads the pixel after it was set to INT_MAX and
  *                           therefore always holds, image_renderer.cuh:183-195; pinned by tests/golden/tree_single_tri)
- *   total_points[p]         covered pixels
+ *   total_points[p]         covered pixels.  DELIBERATE DEVIATION: the reference's USE_CLUTTER branch adds 1 per inside
+ *                           FRAGMENT (image_renderer.cuh:190-205), i.e. at least 2 per pixel of a closed mesh, so its
+ *                           clutter ratio is systematically smaller on multi-triangle meshes; the per-pixel count is
+ *                           the one that does not depend on tessellation or fragment order.
  * evaluated per covered pixel on its minimum depth.  The reference evaluates them per fragment on the running minimum,
  * which depends on the order fragments arrive in (and races); both agree when a pixel receives one fragment.
  * pose_label NULL = 3-DoF gate (|d - s| > occlusion_threshold), else the 6-DoF gate.  Any output may be NULL. */

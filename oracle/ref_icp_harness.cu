@@ -108,4 +108,27 @@ int ref_icp_nn_point2plane(float* model_pcd /* n x 3, transformed in place */, i
     return cudaGetLastError() == cudaSuccess ? 0 : 1;
 }
 
+// reference cuda_icp::depth2cloud_cuda<int32_t | uint16_t> (icp.cu:225-297) on a host depth image; returns the count.
+// Only stride 1 is meaningful: for stride > 1 the reference indexes its width*height/stride^2 mask with x + y*width.
+int ref_icp_depth2cloud(const void* depth, int bits, int width, int height, const float* K9, int stride, int tl_x, int tl_y,
+                        float* out_xyz, int capacity, int* out_n) {
+    Mat3x3f K;
+    for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) K[i][j] = K9[i * 3 + j];
+    void* d = NULL;
+    const size_t bytes = (size_t)width * height * (bits / 8);
+    cudaMalloc(&d, bytes);
+    cudaMemcpy(d, depth, bytes, cudaMemcpyHostToDevice);
+    {
+        device_vector_holder<Vec3f> cloud = bits == 16
+            ? cuda_icp::depth2cloud_cuda((uint16_t*)d, (uint32_t)width, (uint32_t)height, K, (uint32_t)stride, (uint32_t)tl_x, (uint32_t)tl_y)
+            : cuda_icp::depth2cloud_cuda((int32_t*)d, (uint32_t)width, (uint32_t)height, K, (uint32_t)stride, (uint32_t)tl_x, (uint32_t)tl_y);
+        cudaDeviceSynchronize();
+        *out_n = (int)cloud.size();
+        const size_t m = cloud.size() < (size_t)capacity ? cloud.size() : (size_t)capacity;
+        if (m) cudaMemcpy(out_xyz, cloud.data(), m * 12, cudaMemcpyDeviceToHost);
+    }
+    cudaFree(d);
+    return cudaGetLastError() == cudaSuccess ? 0 : 1;
+}
+
 }  // extern "C"

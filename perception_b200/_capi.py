@@ -134,6 +134,11 @@ SIGNATURES = {
     "perch_icp_set_scene": (C.c_int, [_P, _V, C.c_int, C.c_int, _V, C.c_float, _V, _V]),
     "perch_icp_point2plane": (C.c_int, [_P, _V, _V, C.c_int, C.c_float, C.c_float, C.c_int, _V, _V, _V, _V, _V]),
     "perch_icp_point2plane_nn": (C.c_int, [_P, _V, _V, C.c_int, C.c_float, C.c_float, C.c_float, C.c_int, _V, _V, _V, _V, _V]),
+    "perch_icp_get_scene_device": (C.c_int, [_P, C.POINTER(_P), C.POINTER(_P), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "perch_icp_point2plane_device": (C.c_int, [_P, _V, C.c_int, _V, _V, C.c_int, C.c_int, _V, C.c_float, C.c_int, C.c_float,
+                                               C.c_float, C.c_int, _V, _V, _V, _V]),
+    "perch_icp_depth2cloud_device": (C.c_int, [_P, _V, C.c_int, C.c_int, C.c_int, _V, C.c_int, C.c_int, C.c_int, _V, C.c_int,
+                                               C.POINTER(C.c_int)]),
     "perch_knn": (C.c_int, [_P, _V, C.c_int, _V, C.c_int, C.c_int, C.c_int, _V, _V]),
     "perch_compute_proj": (C.c_int, [_P, C.c_int, C.c_int, C.c_float, C.c_float, _P]),
     "perch_set_camera": (C.c_int, [_P, C.c_int, C.c_int, _P, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float]),

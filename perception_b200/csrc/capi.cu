@@ -1174,6 +1174,107 @@ int icp_point2plane_impl(perch_ctx* c, bool nn, float nn_max_dist, const float* 
 }
 }  // namespace
 
+int perch_icp_get_scene_device(perch_ctx* c, const float** d_pcd, const float** d_normals, int* width, int* height) {
+    if (!c) return fail(PERCH_ERR_INVALID, "null context");
+    if (c->icp_w == 0) return fail(PERCH_ERR_INVALID, "perch_icp_set_scene has not been called");
+    if (d_pcd) *d_pcd = c->d_icp_pcd;
+    if (d_normals) *d_normals = c->d_icp_normals;
+    if (width) *width = c->icp_w;
+    if (height) *height = c->icp_h;
+    return PERCH_OK;
+}
+
+int perch_icp_point2plane_device(perch_ctx* c, float* d_model_pcd, int n_points, const float* d_scene_pcd,
+                                 const float* d_scene_normals, int width, int height, const float K9[9], float max_dist_diff,
+                                 int nearest_neighbour, float relative_fitness, float relative_rmse, int max_iteration,
+                                 float out_transform16[16], float* out_fitness, float* out_inlier_rmse, int* out_iterations) {
+    if (!c) return fail(PERCH_ERR_INVALID, "null context");
+    if (n_points < 0 || (n_points > 0 && !d_model_pcd) || !out_transform16 || !out_fitness || !out_inlier_rmse || max_iteration < 0)
+        return fail(PERCH_ERR_INVALID, "bad icp argument");
+    const bool own_scene = d_scene_pcd == nullptr;
+    if (own_scene && c->icp_w == 0) return fail(PERCH_ERR_INVALID, "perch_icp_set_scene has not been called");
+    if (!own_scene && (!d_scene_normals || !K9 || width <= 0 || height <= 0)) return fail(PERCH_ERR_INVALID, "bad icp scene argument");
+    if (nearest_neighbour && !own_scene && d_scene_pcd != c->d_icp_pcd)
+        return fail(PERCH_ERR_INVALID, "nearest-neighbour association runs against the scene of perch_icp_set_scene");
+    if (nearest_neighbour && c->icp_w == 0) return fail(PERCH_ERR_INVALID, "perch_icp_set_scene has not been called");
+    DeviceGuard g(c->device);
+    int rc;
+    if ((rc = ensure_scratch(c, Scratch::align(2 * 4) + Scratch::align(64) + 3 * Scratch::align(4) + 1024))) return rc;
+    Scratch s(c);
+    perch::IcpArgs a;
+    a.points = d_model_pcd;
+    int* d_off = s.take<int>(2);
+    a.offsets = d_off;
+    a.out_T = s.take<float>(16);
+    a.out_fitness = s.take<float>(1);
+    a.out_rmse = s.take<float>(1);
+    a.out_iterations = s.take<int>(1);
+    const int off[2] = {0, n_points};
+    CU(cudaMemcpyAsync(d_off, off, sizeof off, cudaMemcpyHostToDevice, c->stream));
+    const float* K = own_scene || nearest_neighbour ? c->icp_K : K9;
+    a.scene_pcd = own_scene ? c->d_icp_pcd : d_scene_pcd;
+    a.scene_normals = own_scene ? c->d_icp_normals : d_scene_normals;
+    a.width = own_scene ? c->icp_w : width;
+    a.height = own_scene ? c->icp_h : height;
+    a.k00 = K[0]; a.k02 = K[2]; a.k11 = K[4]; a.k12 = K[5];
+    a.max_dist_diff = max_dist_diff;
+    if (nearest_neighbour) {
+        if (!(max_dist_diff > 0.f)) return fail(PERCH_ERR_INVALID, "max_dist_diff must be positive");
+        if ((rc = prepare_icp_nn_grid(c, max_dist_diff))) return rc;
+        a.nn = 1;
+        a.nn_grid = c->icp_grid;
+    }
+    a.relative_fitness = relative_fitness; a.relative_rmse = relative_rmse; a.max_iteration = max_iteration;
+    CU(cudaEventRecord(c->ev0, c->stream));
+    CU(perch::launch_icp_point2plane(a, 1, c->stream));
+    CU(cudaEventRecord(c->ev1, c->stream));
+    CU(cudaMemcpyAsync(out_transform16, a.out_T, 64, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(out_fitness, a.out_fitness, 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaMemcpyAsync(out_inlier_rmse, a.out_rmse, 4, cudaMemcpyDeviceToHost, c->stream));
+    if (out_iterations) CU(cudaMemcpyAsync(out_iterations, a.out_iterations, 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    cudaEventElapsedTime(&c->last_ms, c->ev0, c->ev1);
+    c->last_launches = 1;
+    c->timing_pending = false;
+    return PERCH_OK;
+}
+
+int perch_icp_depth2cloud_device(perch_ctx* c, const void* d_depth, int depth_bits, int width, int height, const float K9[9],
+                                 int stride, int tl_x, int tl_y, float* d_out_xyz, int capacity, int* n_points) {
+    if (!c || !d_depth || !K9 || !n_points) return fail(PERCH_ERR_INVALID, "null argument");
+    if ((depth_bits != 16 && depth_bits != 32) || width <= 0 || height <= 0 || stride <= 0 || capacity < 0 || width % stride != 0)
+        return fail(PERCH_ERR_INVALID, "bad depth2cloud argument (depth_bits 16 | 32; stride must divide the width)");
+    DeviceGuard g(c->device);
+    const size_t npx = (size_t)width * height;
+    const int Lh = (height + stride - 1) / stride;
+    int rc;
+    if ((rc = ensure_scratch(c, Scratch::align(npx * 4) + Scratch::align(((size_t)Lh + 1) * 4) + 1024))) return rc;
+    Scratch s(c);
+    int32_t* d32 = s.take<int32_t>(npx);
+    perch::CloudArgs a;
+    if (depth_bits == 16) {
+        CU(perch::launch_depth_to_i32(d_depth, 16, d32, (int)npx, c->stream));
+        a.depth = d32;
+    } else {
+        a.depth = static_cast<const int32_t*>(d_depth);
+    }
+    a.img_w = width; a.img_h = height; a.full_h = height; a.num_images = 1; a.stride = stride; a.coord_scale = 1;
+    a.lattice_coords = 1; a.u_off = tl_x; a.v_off = tl_y;                 // icp.cu:252-253: (x + tl_x - K02) / K00 * z
+    a.cx = K9[2]; a.cy = K9[5]; a.fx = K9[0]; a.fy = K9[4]; a.depth_factor = 100.f;  // icp.cu:251: depth / 100.0f
+    a.row_counts = s.take<int>((size_t)Lh + 1);
+    a.capacity = capacity;
+    a.cloud_aos = d_out_xyz;
+    CU(perch::launch_cloud_count(a, c->stream));
+    CU(perch::launch_cloud_scan(a, c->stream));
+    if (d_out_xyz && capacity > 0) CU(perch::launch_cloud_write(a, c->stream));
+    int total = 0;
+    CU(cudaMemcpyAsync(&total, a.row_counts + Lh, 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    *n_points = total;
+    if (d_out_xyz && total > capacity) return fail(PERCH_ERR_CAPACITY, "cloud has %d points but the buffer holds %d", total, capacity);
+    return PERCH_OK;
+}
+
 int perch_icp_point2plane(perch_ctx* c, const float* model_pcd, const int* cloud_offsets, int n_clouds,
                           float relative_fitness, float relative_rmse, int max_iteration, float* out_transforms16,
                           float* out_fitness, float* out_inlier_rmse, int* out_iterations, float* out_pcd) {
@@ -1263,6 +1364,12 @@ int perch_detail::render_cost_impl(perch_ctx* c, const char* stage, const PoseIn
     size_t need = 2 * Scratch::align(P * 64) + 2 * Scratch::align(P * 4) + Scratch::align(P * 4) + 2 * Scratch::align(P * 12) + 4096;
     if (do_images) need += Scratch::align(n_img * npx * 4) + 3 * Scratch::align(n_img * npx) + Scratch::align(npx * 8);
     const size_t lat = (size_t)Lw * Lh;
+    // row counters, the scan total, cloud_capacity and dc_index entries are ints (like the reference's, which overflow at
+    // >= 6 991 poses of 640x480, compute_point_clouds.cuh:60,119): refuse instead of wrapping
+    if (do_cloud && (P * lat > (size_t)INT_MAX || (out->dc_index && P * npx > (size_t)INT_MAX)))
+        return fail(PERCH_ERR_CAPACITY, "stage %s: n_poses * lattice (or image, with dc_index) size exceeds INT_MAX; use smaller batches", stage);
+    if (do_images && n_img * npx > (size_t)INT_MAX * 4)
+        return fail(PERCH_ERR_CAPACITY, "stage %s: n_poses * width * height exceeds 2^33 pixels; use smaller batches", stage);
     if (do_cloud) need += Scratch::align(P * lat * 4) + 3 * Scratch::align(P * lat) + Scratch::align((P * Lh + 1) * 4);
     const int cap = do_cloud ? std::max(out->cloud_capacity, 0) : 0;
     if (do_cloud) need += Scratch::align((size_t)cap * 12) + Scratch::align((size_t)cap * 3) + Scratch::align((size_t)cap * 4) +

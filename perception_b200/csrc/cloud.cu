@@ -44,8 +44,8 @@ __device__ __forceinline__ bool inside_bounds(const CloudArgs& a, int u, int v, 
 __device__ __forceinline__ Sample sample_at(const CloudArgs& a, int img, int lx, int ly) {
     Sample s;
     const int ix = lx * a.stride, iy = ly * a.stride;  // position inside the input image
-    s.u = ix * a.coord_scale;
-    s.v = iy * a.coord_scale;
+    s.u = (a.lattice_coords ? lx : ix * a.coord_scale) + a.u_off;
+    s.v = (a.lattice_coords ? ly : iy * a.coord_scale) + a.v_off;
     size_t idx = ((size_t)img * a.img_h + iy) * a.img_w + ix;
     s.d = a.depth[idx];
     s.in_mask = false;

@@ -15,6 +15,7 @@
 #include "cuda_renderer/renderer.h"
 
 #include <cstdlib>
+#include <climits>
 #include <cstring>
 #include <stdexcept>
 #include <string>
@@ -120,7 +121,8 @@ void render_cuda_multi_unified(
                           have_rgb ? source_color[1].data() : nullptr, have_rgb ? source_color[2].data() : nullptr,
                           source_mask_label.empty() ? nullptr : source_mask_label.data()));
     const bool six_dof = !pose_segmentation_label.empty();
-    if (want_cost)
+    // the GICP target of do_icp is the observed cloud of THIS call (renderer.cu:1688-1720), cost stage or not
+    if ((want_cost || do_icp) && observed_point_num > 0)
         check(perch_set_observed(ctx, reinterpret_cast<const float*>(observed_depth_eigen), observed_color,
                                  six_dof ? result_observed_cloud_label : nullptr, observed_point_num));
 
@@ -151,6 +153,9 @@ void render_cuda_multi_unified(
     size_t cap = 0;
     if (want_cloud) {
         cap = (size_t)P * (W / std::max(stride, 1)) * ((H + stride - 1) / std::max(stride, 1));
+        if (cap > (size_t)INT_MAX || (size_t)P * W * H > (size_t)INT_MAX)
+            throw std::runtime_error("render_cuda_multi_unified: poses * width * height exceeds INT_MAX (the reference "
+                                     "overflows its int indices here too, compute_point_clouds.cuh:60,119): use smaller batches");
         cloud_tmp.resize(3 * cap); cloud_rgb_tmp.resize(3 * cap); cloud_map_tmp.resize(cap);
         result_dc_index = alloc<int>((size_t)P * W * H);
         out.cloud = cloud_tmp.data(); out.cloud_color = cloud_rgb_tmp.data(); out.cloud_pose_map = cloud_map_tmp.data();

@@ -510,7 +510,16 @@ size_t gicp_smem_bytes(int smem_points) { return (size_t)smem_points * 6 * sizeo
 cudaError_t launch_gicp(const GicpArgs& a, int n_poses, cudaStream_t stream) {
     if (n_poses <= 0) return cudaSuccess;
     const size_t smem = gicp_smem_bytes(a.smem_points);
-    cudaError_t err = cudaFuncSetAttribute(gicp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    // per function and per device, not per context: always the device's opt-in limit (see launch_pose_kernel)
+    int dev = 0, limit = 0;
+    cudaError_t err = cudaGetDevice(&dev);
+    if (err == cudaSuccess) err = cudaDeviceGetAttribute(&limit, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    if (err != cudaSuccess) return err;
+    cudaFuncAttributes fa;
+    if ((err = cudaFuncGetAttributes(&fa, gicp_kernel)) != cudaSuccess) return err;
+    limit -= (int)fa.sharedSizeBytes;  // the opt-in limit covers static + dynamic shared memory
+    if (smem > (size_t)limit) return cudaErrorInvalidValue;
+    err = cudaFuncSetAttribute(gicp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, limit);
     if (err != cudaSuccess) return err;
     gicp_kernel<<<n_poses, kGicpThreads, smem, stream>>>(a);
     return cudaGetLastError();

@@ -153,6 +153,9 @@ struct CloudArgs {
     const int* pose_label = nullptr;      // rendered: per-pose label or null
     int img_w = 0, img_h = 0, num_images = 0, stride = 1, coord_scale = 1;
     int full_h = 0;  // camera image height (for dc_index)
+    // cuda_icp::depth2cloud_cuda's coordinates (icp.cu:239-257): camera pixel = LATTICE index + offset (x + tl_x, not
+    // x * stride + tl_x) -- lattice_coords = 1; u_off / v_off are added in either mode
+    int lattice_coords = 0, u_off = 0, v_off = 0;
     float cx = 0, cy = 0, fx = 0, fy = 0, depth_factor = 100.f;
     bool use_bounds = false;
     float bounds[6] = {0, 0, 0, 0, 0, 0};  // already cast to float like compute_point_clouds.cuh:86-88

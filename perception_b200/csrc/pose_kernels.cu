@@ -837,8 +837,23 @@ template <int MODE, bool COLOR>
 static cudaError_t launch_pose_kernel(const PoseArgs& a, cudaStream_t stream) {
     if (a.n_poses <= 0) return cudaSuccess;
     size_t smem = pose_kernel_smem_bytes(a, MODE == MODE_IMAGE, COLOR);
-    cudaError_t err = cudaFuncSetAttribute(pose_kernel<MODE, COLOR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    // The attribute is per function and per device, not per context: always set it to the device's opt-in limit (the same
+    // value from every thread and context) instead of this launch's size, so that concurrent contexts with different
+    // sizes cannot lower it under each other's launches.  The caller has checked smem against the limit.
+    int dev = 0, limit = 0;
+    cudaError_t err = cudaGetDevice(&dev);
+    if (err == cudaSuccess) err = cudaDeviceGetAttribute(&limit, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
     if (err != cudaSuccess) return err;
+    cudaFuncAttributes fa;
+    if ((err = cudaFuncGetAttributes(&fa, pose_kernel<MODE, COLOR>)) != cudaSuccess) return err;
+    limit -= (int)fa.sharedSizeBytes;  // the opt-in limit covers static + dynamic shared memory
+    if (smem > (size_t)limit) return cudaErrorInvalidValue;
+    static int s_set[64][2][2];  // [device][MODE][COLOR]: attribute already raised (benign race: same value)
+    if (dev < 0 || dev >= 64 || !s_set[dev][MODE][COLOR]) {
+        err = cudaFuncSetAttribute(pose_kernel<MODE, COLOR>, cudaFuncAttributeMaxDynamicSharedMemorySize, limit);
+        if (err != cudaSuccess) return err;
+        if (dev >= 0 && dev < 64) s_set[dev][MODE][COLOR] = 1;
+    }
     pose_kernel<MODE, COLOR><<<a.n_poses, kThreads, smem, stream>>>(a);
     return cudaGetLastError();
 }

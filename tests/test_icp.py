@@ -205,3 +205,96 @@ def test_icp_nn_parity(orc):
     assert np.array_equal(full["transformation"][n], np.eye(4)) and full["fitness"][n] == 0
     assert np.array_equal(full["transformation"][n + 1], np.eye(4)) and full["fitness"][n + 1] == 0
     assert proj["fitness"].shape == (n,)
+
+
+# ---- the C++ backend for the reference's unchanged <cuda_icp/icp.h> (perception_b200/csrc/compat/cuda_icp_compat.cpp) -------
+ICP_COMPAT_SO = Path(__file__).resolve().parent.parent / "oracle" / "_ref" / "libcuda_icp_compat.so"
+
+
+def _compat():
+    import ctypes as C
+    if not ICP_COMPAT_SO.exists():
+        pytest.skip("oracle/_ref/libcuda_icp_compat.so not built (needs the reference headers)")
+    from perception_b200 import _capi
+    _capi.load_library()  # libnccl preload order, see _capi._preload_nccl
+    lib = C.CDLL(str(ICP_COMPAT_SO))
+    lib.compat_icp_last_error.restype = C.c_char_p
+    return lib
+
+
+def _vp(a):
+    import ctypes as C
+    return a.ctypes.data_as(C.c_void_p)
+
+
+@pytest.mark.gpu
+def test_cuda_icp_cpp_signatures_projective_and_nn(orc):
+    """cuda_icp::ICP_Point2Plane_cuda<Scene_projective | Scene_nn> and Scene_*::init_*_cuda called through the
+    reference's own declarations (device_vector_holder<Vec3f>, cv::Mat, Mat3x3f) == the C-ABI on the same inputs."""
+    import ctypes as C
+    from perception_b200.renderer import Renderer
+    lib = _compat()
+    case, K = icp_cases.scene()
+    W, H = icp_cases.W, icp_cases.H
+    depth = np.ascontiguousarray(case.scene.source_depth, np.int32).reshape(-1)
+    K9 = np.ascontiguousarray(K, np.float32).reshape(9)
+    with Renderer(0) as r:
+        pcd, nrm = r.icp_set_scene(depth, W, H, K, want_buffers=True)
+        cl, _ = icp_cases.clouds(pcd, case.scene.source_label, n_clouds=3)
+        want_p = r.icp_point2plane(cl)
+        want_n = r.icp_point2plane(cl, nn_max_dist=0.01)
+    n_valid = int((depth > 0).sum())
+    for i, c in enumerate(cl):
+        pts = np.ascontiguousarray(c, np.float32).copy()
+        T = np.zeros(16, np.float32); fit = C.c_float(0); rmse = C.c_float(0)
+        s_pcd, s_nrm = np.zeros((W * H, 3), np.float32), np.zeros((W * H, 3), np.float32)
+        rc = lib.compat_icp_projective(_vp(pts), len(pts), _vp(depth), W, H, _vp(K9), C.c_float(0.1), C.c_float(1e-5), C.c_float(1e-5),
+                                       30, _vp(T), C.byref(fit), C.byref(rmse), _vp(s_pcd), _vp(s_nrm))
+        assert rc == 0, lib.compat_icp_last_error()
+        assert np.array_equal(s_pcd, pcd) and np.array_equal(s_nrm, nrm)            # scene prepared on the device
+        assert np.array_equal(T.reshape(4, 4), want_p["transformation"][i])
+        assert fit.value == want_p["fitness"][i] and rmse.value == want_p["inlier_rmse"][i]
+        assert np.array_equal(pts, want_p["clouds"][i])                              # model_pcd transformed in place
+        pts = np.ascontiguousarray(c, np.float32).copy()
+        n_scene = C.c_int(0)
+        rc = lib.compat_icp_nn(_vp(pts), len(pts), _vp(depth), W, H, _vp(K9), C.c_float(1e-5), C.c_float(1e-5), 30, _vp(T),
+                               C.byref(fit), C.byref(rmse), C.byref(n_scene))
+        assert rc == 0, lib.compat_icp_last_error()
+        assert n_scene.value == n_valid
+        assert np.array_equal(T.reshape(4, 4), want_n["transformation"][i])
+        assert fit.value == want_n["fitness"][i] and rmse.value == want_n["inlier_rmse"][i]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("bits", [32, 16])
+def test_cuda_icp_depth2cloud_cuda(bits):
+    """cuda_icp::depth2cloud_cuda<int32_t | uint16_t> (icp.h:83-90, icp.cu:225-297) through the reference's declaration:
+    == the reference's own kernels at stride 1 (live, oracle/_ref/libicp_ref.so), == the float32 formula at any stride."""
+    import ctypes as C
+    lib = _compat()
+    case, K = icp_cases.scene()
+    W, H = icp_cases.W, icp_cases.H
+    d32 = np.ascontiguousarray(case.scene.source_depth, np.int32).reshape(H, W)
+    depth = d32 if bits == 32 else np.clip(d32, 0, 65535).astype(np.uint16)
+    K9 = np.ascontiguousarray(K, np.float32).reshape(9)
+    ref = None
+    if ICP_REF_SO.exists():
+        ref = C.CDLL(str(ICP_REF_SO))
+    for stride, tl_x, tl_y in [(1, 0, 0), (1, 17, 5), (4, 0, 0), (8, 3, 2)]:
+        n = C.c_int(0)
+        cap = W * H
+        out = np.zeros((cap, 3), np.float32)
+        rc = lib.compat_icp_depth2cloud(_vp(depth), bits, W, H, _vp(K9), stride, tl_x, tl_y, _vp(out), cap, C.byref(n))
+        assert rc == 0, lib.compat_icp_last_error()
+        sub = depth[::stride, ::stride]
+        ys, xs = np.nonzero(sub > 0)                       # row-major order of the lattice
+        assert n.value == len(xs) > 0
+        z = sub[ys, xs].astype(np.float32) / np.float32(100.0)
+        x = ((xs + tl_x).astype(np.float32) - K9[2]) / K9[0] * z
+        y = ((ys + tl_y).astype(np.float32) - K9[5]) / K9[4] * z
+        assert np.array_equal(out[:n.value], np.stack([x, y, z], 1))
+        if ref is not None and stride == 1:
+            q = np.zeros((cap, 3), np.float32)
+            qn = C.c_int(0)
+            assert ref.ref_icp_depth2cloud(_vp(depth), bits, W, H, _vp(K9), stride, tl_x, tl_y, _vp(q), cap, C.byref(qn)) == 0
+            assert qn.value == n.value and np.array_equal(q[:qn.value], out[:n.value])

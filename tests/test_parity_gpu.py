@@ -575,3 +575,29 @@ def test_full_size_properties(orc):
     best = topk(a["rendered_cost"], a["observed_cost"], pmm, 1, k=5)
     assert best["cost"][0, 0] <= int(a["rendered_cost"][0] + a["observed_cost"][0])
     assert a["rendered_cost"][0] < 35.0
+
+
+def test_observed_order_within_a_label_does_not_change_counts(orc):
+    """The reference sorts the observed cloud by label with thrust::sort_by_key (renderer.cu:1681), which leaves the order
+    INSIDE a label unspecified; this library and the oracle harness sort stably.  Nearest-neighbour indices (and their
+    tie-breaks) follow that order, but `explained` is a set of POINTS, so for cost_type 0 / 2 every count and cost must
+    be the same for any order -- checked by shuffling the observed cloud (with exact duplicates in it, i.e. real distance
+    ties) before handing it over.  (cost_type 1 looks colours up by index in the UNSORTED colour array, renderer.cu:1881:
+    there the order matters in the reference itself, which is why it is not part of this property.)"""
+    case, obs, poses, pmm, lab, tot = _cost_case(orc, 5000, 8, True, 40)
+    rng = np.random.default_rng(11)
+    xyz, rgb, olab = obs["aos"].copy(), obs["rgb"].copy(), obs["label"].copy()
+    dup = rng.choice(len(xyz), 60, replace=False)          # exact duplicates => equal distances => index tie-breaks
+    xyz = np.concatenate([xyz, xyz[dup]]); rgb = np.concatenate([rgb, rgb[:, dup]], 1); olab = np.concatenate([olab, olab[dup]])
+    tot = np.bincount(olab, minlength=lab.max() + 1).astype(np.float32)[lab]
+    outs = []
+    for trial in range(3):
+        perm = np.arange(len(xyz)) if trial == 0 else rng.permutation(len(xyz))
+        with make_renderer(case, with_label=True) as r:
+            r.set_observed(xyz[perm], rgb[:, perm], olab[perm])
+            outs.append(r.render_cuda_multi_unified("COST", poses, pmm, lab, tot, stride=8, cost_type=2, sensor_resolution=0.01))
+    assert outs[0]["counts"][2].sum() > 0
+    for o in outs[1:]:
+        assert np.array_equal(o["counts"], outs[0]["counts"])
+        for k in ("rendered_cost", "observed_cost", "points_diff_cost"):
+            assert np.array_equal(o[k], outs[0][k], equal_nan=True), k
