@@ -410,6 +410,16 @@ int perch_validate_states(perch_ctx* ctx, const perch_state* states, int n_state
 int perch_generate_states(perch_ctx* ctx, const perch_state* placed, int n_placed, perch_state* out_states,
                           int capacity, int* n_out);
 
+/* The 6-DoF branch of GenerateSuccessorStates reads its candidates from <rendered_root_dir>/<model>/poses.txt
+ * (search_env.cpp:7099-7146): one pose per line, `x y z qx qy qz qw`, single spaces, parsed with std::stod into
+ * ContPose(x, y, z, qx, qy, qz, qw) and then ObjectState(model, symmetric, pose, required_object_id + 1).  This parses the
+ * text of such a file into perch_state records (Euler fields 0: ContPose::GetTransform uses the quaternion,
+ * object_state.cpp:88-93) ready for perch_validate_states / perch_score_states.  *n_out = poses in the text; at most
+ * `capacity` are written (pass 0 / NULL to count).  A malformed line is PERCH_ERR_INVALID with its line number (the
+ * reference dies with an uncaught std::invalid_argument there).  Host-only. */
+int perch_parse_pose_list(const char* text, size_t length, int model_id, int segmentation_label_id, perch_state* out_states,
+                          int capacity, int* n_out);
+
 /* ==== observed-scene preparation ================================================================ */
 /* The GPU branch of EnvObjectRecognition::SetInput (search_env.cpp:5880-6069) as one call: the decoded input images go
  * in, the source depth image and the observed cloud stay resident in the context (what perch_set_scene +

@@ -190,6 +190,7 @@ SIGNATURES = {
     "perch_score_states": (C.c_int, [_P, C.c_char_p, _V, C.c_int, C.POINTER(perch_params), C.POINTER(perch_outputs)]),
     "perch_validate_states": (C.c_int, [_P, _V, C.c_int, _V, C.c_int, C.c_int, _V]),
     "perch_generate_states": (C.c_int, [_P, _V, C.c_int, _V, C.c_int, C.POINTER(C.c_int)]),
+    "perch_parse_pose_list": (C.c_int, [C.c_char_p, C.c_size_t, C.c_int, C.c_int, _V, C.c_int, C.POINTER(C.c_int)]),
     "perch_set_input": (C.c_int, [_P, C.POINTER(perch_input), C.POINTER(C.c_int)]),
     "perch_get_observed": (C.c_int, [_P, _V, _V, _V, C.c_int, C.POINTER(C.c_int)]),
     "perch_get_source_depth": (C.c_int, [_P, _V]),

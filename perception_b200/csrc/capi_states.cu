@@ -2,6 +2,9 @@
 // Reference: sbpl_perception/src/search_env.cpp:309-528, 1505-1622, 7056-7490 (see states.cu).
 #include <cuda_runtime.h>
 
+#include <cstring>
+#include <string>
+
 #include <algorithm>
 #include <cmath>
 #include <cstring>
@@ -508,3 +511,58 @@ int perch_generate_states(perch_ctx* c, const perch_state* placed, int n_placed,
 }
 
 }  // extern "C"
+
+// ---- 6-DoF candidate intake: the poses.txt reader of GenerateSuccessorStates (search_env.cpp:7109-7146) ---------------------
+// Each line holds `x y z qx qy qz qw` separated by single spaces; the reference splits on ' ' (boost::is_any_of(" "), no token
+// compression), converts every token with std::stod and builds ContPose(x, y, z, qx, qy, qz, qw) from the first seven
+// (object_state.cpp:24-41).  A token std::stod would throw on (empty after a double space, not a number) is an error here
+// instead of an uncaught exception; a trailing '\r' is ignored like stod ignores it.  Host-only.
+extern "C" int perch_parse_pose_list(const char* text, size_t length, int model_id, int segmentation_label_id, perch_state* out_states,
+                                     int capacity, int* n_out) {
+    using perch_detail::fail;
+    if ((!text && length > 0) || !n_out || capacity < 0 || (capacity > 0 && !out_states))
+        return fail(PERCH_ERR_INVALID, "bad parse_pose_list argument");
+    int n = 0, line_no = 0;
+    size_t pos = 0;
+    while (pos < length) {
+        size_t eol = pos;
+        while (eol < length && text[eol] != '\n') ++eol;
+        ++line_no;
+        double v[7];
+        int nv = 0;
+        size_t tok = pos;
+        bool any = eol > pos;
+        while (any && tok <= eol) {
+            size_t end = tok;
+            while (end < eol && text[end] != ' ') ++end;
+            if (nv < 7) {
+                std::string t(text + tok, end - tok);
+                size_t used = 0;
+                try {
+                    v[nv] = std::stod(t, &used);
+                } catch (...) {
+                    return fail(PERCH_ERR_INVALID, "pose list line %d: token %d ('%s') is not a number", line_no, nv + 1, t.c_str());
+                }
+            }
+            ++nv;
+            if (end >= eol) break;
+            tok = end + 1;
+        }
+        if (any) {
+            if (nv < 7) return fail(PERCH_ERR_INVALID, "pose list line %d: %d values, expected x y z qx qy qz qw", line_no, nv);
+            if (n < capacity) {
+                perch_state st;
+                memset(&st, 0, sizeof st);
+                st.x = v[0]; st.y = v[1]; st.z = v[2];
+                st.qx = v[3]; st.qy = v[4]; st.qz = v[5]; st.qw = v[6];
+                st.model_id = model_id;
+                st.segmentation_label_id = segmentation_label_id;
+                out_states[n] = st;
+            }
+            ++n;
+        }
+        pos = eol + 1;
+    }
+    *n_out = n;
+    return PERCH_OK;
+}

@@ -62,6 +62,26 @@ def states_from_pose_lines(model_id: int, lines: np.ndarray, segmentation_label_
     return s
 
 
+def load_pose_list(path_or_text, model_id: int, segmentation_label_id: int) -> np.ndarray:
+    """perch_parse_pose_list: a poses.txt file (or its text) of the 6-DoF flow (search_env.cpp:7099-7146) -> states."""
+    import ctypes as C
+    import os
+    from . import _capi
+    lib = _capi.load_library()
+    if isinstance(path_or_text, (bytes, bytearray)):
+        text = bytes(path_or_text)
+    elif isinstance(path_or_text, str) and "\n" not in path_or_text and os.path.exists(path_or_text):
+        text = open(path_or_text, "rb").read()
+    else:
+        text = str(path_or_text).encode()
+    n = C.c_int(0)
+    _capi.check(lib, lib.perch_parse_pose_list(text, len(text), model_id, segmentation_label_id, None, 0, C.byref(n)))
+    out = np.zeros(n.value, STATE_DTYPE)
+    _capi.check(lib, lib.perch_parse_pose_list(text, len(text), model_id, segmentation_label_id, out.ctypes.data_as(C.c_void_p),
+                                               n.value, C.byref(n)))
+    return out
+
+
 def convex_hull_xy(points_xy: np.ndarray) -> np.ndarray:
     """Convex hull of the projected mesh vertices (object_model.cpp:361-372 uses pcl::ConvexHull, dimension 2):
     Andrew's monotone chain, counter-clockwise, no repeated end point (an implicitly closed polygon)."""

@@ -107,3 +107,25 @@ def test_create_fails_loudly_without_gpu():
 def test_missing_library_raises(tmp_path):
     with pytest.raises(ImportError):
         _capi.load_library(tmp_path / "libperch_b200.so")
+
+
+def test_pose_list_intake_round_trip(tmp_path):
+    """poses.txt of the 6-DoF flow (search_env.cpp:7109-7130): `x y z qx qy qz qw` per line -> perch_state records."""
+    from perception_b200 import states as S
+    rng = np.random.default_rng(2)
+    rows = rng.normal(0, 1, (50, 7))
+    rows[:, 3:] /= np.linalg.norm(rows[:, 3:], axis=1, keepdims=True)
+    text = "\n".join(" ".join(repr(float(v)) for v in r) for r in rows) + "\n"
+    p = tmp_path / "poses.txt"
+    p.write_text(text)
+    got = S.load_pose_list(str(p), 3, 2)
+    want = S.states_from_pose_lines(3, rows, 2)
+    assert got.tobytes() == want.tobytes()          # std::stod round-trips repr() exactly
+    # windows line ends, no trailing newline, extra columns (the reference reads the first seven), scientific notation
+    got2 = S.load_pose_list("1 2 3 0 0 0 1 99\r\n1e-1 -2.5E0 +3 0.5 0.5 0.5 0.5", 0, -1)
+    assert len(got2) == 2 and got2["x"].tolist() == [1.0, 0.1] and got2["y"][1] == -2.5 and got2["qw"].tolist() == [1.0, 0.5]
+    assert len(S.load_pose_list("", 0, -1)) == 0
+    for bad in ("1 2 3 4 5 6\n", "1 2 3 0 0  0 1\n", "1 2 x 0 0 0 1\n"):
+        with pytest.raises(_capi.PerchError) as e:
+            S.load_pose_list(bad, 0, -1)
+        assert e.value.code == _capi.PERCH_ERR_INVALID and "line 1" in str(e.value)
