@@ -20,6 +20,7 @@
 #include <math.h>
 #include <stdint.h>
 #include <stdlib.h>
+#include <stdio.h>
 #include <string.h>
 
 typedef struct { float x, y, z; } vec3;
@@ -648,8 +649,16 @@ int oracle_knn(const float* ref, int ref_nb, const float* query, int query_nb, i
  *                => C = I - (1 - 1e-3) n n^T, n = direction of least variance (n = 0 when fewer than 3 neighbours);
  *   iteration:   nearest target point (same label only, if labels are given) of every transformed source point, float
  *                distance fma(dz,dz,fma(dy,dy,dx*dx)), lowest index on ties; M = (C_B + R C_A R^T)^-1;
- *                r = b - (R a + t); J = [skew(R a + t), -I]; delta = -(sum J^T M J)^-1 sum J^T M r; T <- exp(delta) T;
- *   stop:        all |exp(delta).R - I| < rotation_epsilon and all |exp(delta).t| < translation_epsilon.
+ *                r = b - (R a + t); J = [skew(R a + t), -I]; H = sum J^T M J, g = sum J^T M r, y0 = sum r^T M r;
+ *   step:        Levenberg-Marquardt as in fast_gicp's LsqRegistration::step_lm (the optimiser FastGICP runs by
+ *                default; lambda starts at 1e-9 max diag H): up to 10 trials, delta = -(H + lambda I)^-1 g, trial error
+ *                y' of exp(delta) T with the correspondences and M of the linearisation frozen, gain ratio
+ *                rho = (y0 - y') / (delta . (lambda delta - g)); rho >= 0: accept, lambda *= max(1/3, 1 - (2 rho - 1)^3);
+ *                rho < 0: lambda *= nu, nu *= 2 (or stop as converged when exp(delta) is below the epsilons);
+ *   stop:        all |exp(delta).R - I| < rotation_epsilon and all |exp(delta).t| < translation_epsilon; or (extension,
+ *                not in fast_gicp: hard assignment makes some poses cycle through a few correspondence sets for ever) the
+ *                linearisation error has not improved on its best value by 1e-3 for 8 linearisations: the transform of
+ *                that best linearisation is returned (PERCH_GICP_STALL_WINDOW, 0 = off).
  * out_T12 = R row-major (9) then t (3), metres.  Returns the number of linearisations performed.
  */
 static void jacobi_smallest(double a00, double a01, double a02, double a11, double a12, double a22, double n[3]) {
@@ -742,10 +751,17 @@ int oracle_gicp(const float* src_aos, int n_src, const float* tgt_aos, int n_tgt
     if (n_src > 0 && n_tgt > 0) {
         double* na = (double*)malloc(sizeof(double) * 3 * (size_t)n_src);
         double* nb = (double*)malloc(sizeof(double) * 3 * (size_t)n_tgt);
+        int* corr = (int*)malloc(sizeof(int) * (size_t)n_src);
+        double* Ms = (double*)malloc(sizeof(double) * 9 * (size_t)n_src);
         oracle_cloud_normals(src_aos, n_src, k, na);
         oracle_cloud_normals(tgt_aos, n_tgt, k, nb);
         const double w = 1.0 - 1e-3;
+        double lambda = -1.0, best_y = 1e300, best_T[12];
+        int since_best = 0;
+        const char* sw = getenv("PERCH_GICP_STALL_WINDOW");
+        const int stall_window = sw && *sw ? atoi(sw) : 8;
         for (int it = 0; it < max_iterations; ++it) {
+            /* ---- linearise at T: correspondences, Mahalanobis matrices, H, g, y0 (LsqRegistration::linearize) */
             double H[36], g[6];
             memset(H, 0, sizeof H); memset(g, 0, sizeof g);
             err = 0;
@@ -761,6 +777,7 @@ int oracle_gicp(const float* src_aos, int n_src, const float* tgt_aos, int n_tgt
                     const float d = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
                     if (d < best) { best = d; bj = j; }
                 }
+                corr[i] = bj;
                 if (bj < 0) continue;
                 const double* a0 = na + 3 * (size_t)i;
                 const double ra[3] = {T[0] * a0[0] + T[1] * a0[1] + T[2] * a0[2], T[3] * a0[0] + T[4] * a0[1] + T[5] * a0[2],
@@ -773,6 +790,7 @@ int oracle_gicp(const float* src_aos, int n_src, const float* tgt_aos, int n_tgt
                 const double Aa = d * f - e * e, Bb = c * e - b * f, Cc = b * e - c * d, inv = 1.0 / (a * Aa + b * Bb + c * Cc);
                 const double M[3][3] = {{Aa * inv, Bb * inv, Cc * inv}, {Bb * inv, (a * f - c * c) * inv, (b * c - a * e) * inv},
                                         {Cc * inv, (b * c - a * e) * inv, (a * d - b * b) * inv}};
+                memcpy(Ms + 9 * (size_t)i, M, sizeof M);
                 const double r[3] = {tgt_aos[3 * (size_t)bj] - p[0], tgt_aos[3 * (size_t)bj + 1] - p[1], tgt_aos[3 * (size_t)bj + 2] - p[2]};
                 const double J[6][3] = {{0, p[2], -p[1]}, {-p[2], 0, p[0]}, {p[1], -p[0], 0}, {-1, 0, 0}, {0, -1, 0}, {0, 0, -1}};
                 double MJ[6][3];
@@ -784,22 +802,71 @@ int oracle_gicp(const float* src_aos, int n_src, const float* tgt_aos, int n_tgt
                 for (int x = 0; x < 3; ++x) err += r[x] * (M[x][0] * r[0] + M[x][1] * r[1] + M[x][2] * r[2]);
             }
             iters = it + 1;
-            double x[6];
-            if (!chol_solve6(H, g, x)) break;
-            double dR[9], dt[3], nT[12];
-            se3_exp_d(x, dR, dt);
-            for (int i = 0; i < 3; ++i) {
-                for (int j = 0; j < 3; ++j) nT[i * 3 + j] = dR[i * 3] * T[j] + dR[i * 3 + 1] * T[3 + j] + dR[i * 3 + 2] * T[6 + j];
-                nT[9 + i] = dR[i * 3] * T[9] + dR[i * 3 + 1] * T[10] + dR[i * 3 + 2] * T[11] + dt[i];
+            const double y0 = err;
+            /* stall detection (extension, see GicpArgs::stall_window): no improvement of the linearisation error on its best
+             * value by 1e-3 (relative) for `stall_window` linearisations => back to that best point and stop */
+            if (stall_window > 0) {
+                if (y0 < best_y * (1.0 - 1e-3)) { best_y = y0; memcpy(best_T, T, sizeof T); since_best = 0; }
+                else if (++since_best >= stall_window) { memcpy(T, best_T, sizeof T); err = best_y; break; }
             }
-            memcpy(T, nT, sizeof T);
-            double mr = 0, mt = 0;
-            for (int i = 0; i < 9; ++i) mr = fmax(mr, fabs(dR[i] - (i % 4 == 0)));
-            for (int i = 0; i < 3; ++i) mt = fmax(mt, fabs(dt[i]));
-            if (mr < rotation_epsilon && mt < translation_epsilon) break;
+            /* ---- Levenberg-Marquardt step (fast_gicp LsqRegistration::step_lm; defaults lm_init_lambda_factor 1e-9,
+             * lm_max_iterations 10): trial error with the correspondences and M of the linearisation frozen
+             * (FastGICP::compute_error), gain ratio rho = (y0 - yi) / (d . (lambda d - b)) */
+            if (lambda < 0) {
+                double mx = 0;
+                for (int c = 0; c < 6; ++c) mx = fmax(mx, H[c * 7]);
+                lambda = 1e-9 * mx;
+            }
+            double nu = 2.0;
+            int decided = 0, converged = 0;
+            for (int trial = 0; trial < 10 && !decided; ++trial) {
+                double Hd[36], x[6];
+                memcpy(Hd, H, sizeof H);
+                for (int c = 0; c < 6; ++c) Hd[c * 7] += lambda;
+                if (!chol_solve6(Hd, g, x)) { decided = 1; converged = 1; break; }
+                double dR[9], dt[3], nT[12];
+                se3_exp_d(x, dR, dt);
+                for (int i = 0; i < 3; ++i) {
+                    for (int j = 0; j < 3; ++j) nT[i * 3 + j] = dR[i * 3] * T[j] + dR[i * 3 + 1] * T[3 + j] + dR[i * 3 + 2] * T[6 + j];
+                    nT[9 + i] = dR[i * 3] * T[9] + dR[i * 3 + 1] * T[10] + dR[i * 3 + 2] * T[11] + dt[i];
+                }
+                double yi = 0;
+                for (int i = 0; i < n_src; ++i) {
+                    const int bj = corr[i];
+                    if (bj < 0) continue;
+                    const double ax = src_aos[3 * (size_t)i], ay = src_aos[3 * (size_t)i + 1], az = src_aos[3 * (size_t)i + 2];
+                    const double r[3] = {tgt_aos[3 * (size_t)bj] - (nT[0] * ax + nT[1] * ay + nT[2] * az + nT[9]),
+                                         tgt_aos[3 * (size_t)bj + 1] - (nT[3] * ax + nT[4] * ay + nT[5] * az + nT[10]),
+                                         tgt_aos[3 * (size_t)bj + 2] - (nT[6] * ax + nT[7] * ay + nT[8] * az + nT[11])};
+                    const double* M = Ms + 9 * (size_t)i;
+                    for (int x2 = 0; x2 < 3; ++x2) yi += r[x2] * (M[3 * x2] * r[0] + M[3 * x2 + 1] * r[1] + M[3 * x2 + 2] * r[2]);
+                }
+                double den = 0, mr = 0, mt = 0;
+                for (int c = 0; c < 6; ++c) den += x[c] * (lambda * x[c] - g[c]);
+                for (int i = 0; i < 9; ++i) mr = fmax(mr, fabs(dR[i] - (i % 4 == 0)));
+                for (int i = 0; i < 3; ++i) mt = fmax(mt, fabs(dt[i]));
+                const int small = mr < rotation_epsilon && mt < translation_epsilon;
+                const double rho = (y0 - yi) / den;
+                if (rho < 0) {
+                    if (small) { decided = 1; converged = 1; }
+                    else { lambda *= nu; nu *= 2; }
+                } else {
+                    memcpy(T, nT, sizeof T);
+                    const double q = 2 * rho - 1;
+                    lambda *= fmax(1.0 / 3.0, 1 - q * q * q);
+                    decided = 1;
+                    converged = small;
+                }
+            }
+            if (getenv("PERCH_ORACLE_GICP_TRACE"))
+                fprintf(stderr, "  it %3d y0 %.6e lambda %.3e decided %d converged %d t=(%.5f %.5f %.5f)\n", it, y0, lambda, decided,
+                        converged, T[9], T[10], T[11]);
+            if (!decided || converged) break;  /* ten rejected trials ("lm not converged") or a step below the epsilons */
         }
         free(na);
         free(nb);
+        free(corr);
+        free(Ms);
     }
     memcpy(out_T12, T, sizeof T);
     if (out_error) *out_error = err;

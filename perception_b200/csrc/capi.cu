@@ -384,7 +384,8 @@ int run_gicp(perch_ctx* c, const perch_params* p, const perch::PoseArgs& base, i
     *launches += 4;
     // grow the private buffer for cloud + normals without losing the images/rows: they are re-created if it moves
     const size_t cloud_bytes = Scratch::align((size_t)std::max(total, 1) * 12);
-    const size_t need = img_bytes + rows_bytes + 2 * cloud_bytes;
+    const size_t ref_bytes = Scratch::align((size_t)std::max(total, 1) * 4);
+    const size_t need = img_bytes + rows_bytes + 2 * cloud_bytes + ref_bytes;
     if (need > c->gicp_bytes) {
         if ((rc = ensure_gicp_buffer(c, need))) return rc;
         l_depth = reinterpret_cast<int32_t*>(c->d_gicp);
@@ -409,6 +410,7 @@ int run_gicp(perch_ctx* c, const perch_params* p, const perch::PoseArgs& base, i
     ga.pose_begin = d_rows;
     ga.rows_per_pose = Lh;
     ga.src_normals = d_src_normals;
+    ga.src_ref = reinterpret_cast<int*>(static_cast<char*>(c->d_gicp) + img_bytes + rows_bytes + 2 * cloud_bytes);
     if ((rc = prepare_gicp_grid(c))) return rc;
     ga.grid = c->gicp_grid;
     ga.grid_h = c->gicp_grid_h;
@@ -426,12 +428,13 @@ int run_gicp(perch_ctx* c, const perch_params* p, const perch::PoseArgs& base, i
     ga.out_iterations = d_iterations;
     ga.out_error = d_error;
     // shared memory for the largest pose cloud (rounded up), capped so that at least two CTAs fit an SM
-    const int cap_pts = (int)std::min<size_t>(((size_t)c->max_smem_optin / 2 - 2048) / 24, 4096);
+    const int cap_pts = (int)std::min<size_t>(((size_t)c->max_smem_optin / 2 - 2048) / 28, 4096);
     ga.smem_points = std::min(std::max((max_n + 63) & ~63, 64), cap_pts);
     ga.k_correspondences = k;
     ga.max_iterations = p->icp_max_iterations > 0 ? p->icp_max_iterations : 150;                     // renderer.cu:1696
     ga.rotation_epsilon = p->icp_rotation_epsilon >= 0.f ? p->icp_rotation_epsilon : 2e-3f;         // renderer.cu:1698
     ga.translation_epsilon = p->icp_transformation_epsilon >= 0.f ? p->icp_transformation_epsilon : 5e-4f;  // :1699
+    ga.stall_window = std::max(env_int("PERCH_GICP_STALL_WINDOW", 8), 0);  // 0 = off: iterate to the cap like fast_gicp
     if (c->n_obs == 0) ga.max_iterations = 0;  // no target: poses pass through unchanged
     cudaEvent_t e0, e1;
     CU(cudaEventCreate(&e0));

@@ -318,9 +318,16 @@ __global__ void __launch_bounds__(kGicpThreads, PERCH_GICP_MIN_BLOCKS) gicp_kern
     extern __shared__ __align__(16) unsigned char gicp_smem[];
     float* s_pts = reinterpret_cast<float*>(gicp_smem);              // 3 x cap
     float* s_nrm = s_pts + 3 * (size_t)a.smem_points;                // 3 x cap
+    int* s_ref = reinterpret_cast<int*>(s_nrm + 3 * (size_t)a.smem_points);  // correspondence of the last linearisation
     __shared__ double s_T[12];                                       // R row-major (9) + t (3), metres
+    __shared__ double s_Tt[12];                                      // trial transform of the Levenberg-Marquardt step
+    __shared__ double s_H[36], s_g[6], s_d[6];
+    __shared__ double s_y0, s_den, s_lambda, s_nu;
+    __shared__ double s_best_y, s_best_T[12];                        // stall detection (GicpArgs::stall_window)
+    __shared__ int s_since_best;
     __shared__ float s_part[kGicpWarps][28];
     __shared__ int s_state;                                          // 0 = iterate, 1 = converged / stop
+    __shared__ int s_lm;                                             // trial loop: 0 = try again, 1 = step decided, 2 = abort
     __shared__ int s_iters;
 
     const int pose_i = blockIdx.x;
@@ -333,6 +340,7 @@ __global__ void __launch_bounds__(kGicpThreads, PERCH_GICP_MIN_BLOCKS) gicp_kern
     float* g_nrm = a.src_normals + 3 * (size_t)begin;
     const float* pts = in_smem ? s_pts : g_pts;
     float* nrm = in_smem ? s_nrm : g_nrm;
+    int* refs = in_smem ? s_ref : a.src_ref + begin;
     const bool use_label = a.pose_label != nullptr;
     const int label = use_label ? a.pose_label[pose_i] : 0;
     // target range of this pose in the label-sorted cloud; short ranges are searched by streaming (nn_range)
@@ -345,7 +353,7 @@ __global__ void __launch_bounds__(kGicpThreads, PERCH_GICP_MIN_BLOCKS) gicp_kern
     const bool stream_target = a.tgt_sorted != nullptr && (le - lb) <= a.stream_max;
 
     if (tid < 12) s_T[tid] = (tid == 0 || tid == 4 || tid == 8) ? 1.0 : 0.0;
-    if (tid == 0) { s_state = (n == 0) ? 1 : 0; s_iters = 0; }
+    if (tid == 0) { s_state = (n == 0) ? 1 : 0; s_iters = 0; s_lambda = -1.0; s_best_y = 1e300; s_since_best = 0; }
     if (in_smem)
         for (int i = tid; i < 3 * n; i += kGicpThreads) s_pts[i] = g_pts[i];
     __syncthreads();
@@ -393,6 +401,7 @@ __global__ void __launch_bounds__(kGicpThreads, PERCH_GICP_MIN_BLOCKS) gicp_kern
             float best; int ref; float4 b;
             if (stream_target) nn_range(a.tgt_sorted, lb, le, px, py, pz, best, ref, b);
             else nn_unbounded(a.grid, a.grid_h, a.coarse, a.coarse_h, px, py, pz, use_label, label, best, ref, b);
+            refs[i] = ref;
             if (ref < 0) continue;  // no target point carries this label
             const float nax = nrm[3 * i], nay = nrm[3 * i + 1], naz = nrm[3 * i + 2];
             const float na[3] = {R[0] * nax + R[1] * nay + R[2] * naz, R[3] * nax + R[4] * nay + R[5] * naz,
@@ -428,41 +437,126 @@ __global__ void __launch_bounds__(kGicpThreads, PERCH_GICP_MIN_BLOCKS) gicp_kern
         }
         __syncthreads();
         if (tid == 0) {
-            double H[36], g[6], x[6];
             int o = 0;
             for (int r2 = 0; r2 < 6; ++r2)
                 for (int c = r2; c < 6; ++c) {
-                    double s = 0;
-                    for (int wv = 0; wv < kGicpWarps; ++wv) s += (double)s_part[wv][o];
-                    H[r2 * 6 + c] = s; H[c * 6 + r2] = s;
+                    double sum = 0;
+                    for (int wv = 0; wv < kGicpWarps; ++wv) sum += (double)s_part[wv][o];
+                    s_H[r2 * 6 + c] = sum; s_H[c * 6 + r2] = sum;
                     ++o;
                 }
             for (int c = 0; c < 6; ++c) {
-                double s = 0;
-                for (int wv = 0; wv < kGicpWarps; ++wv) s += (double)s_part[wv][21 + c];
-                g[c] = s;
+                double sum = 0;
+                for (int wv = 0; wv < kGicpWarps; ++wv) sum += (double)s_part[wv][21 + c];
+                s_g[c] = sum;
             }
             double err = 0;
             for (int wv = 0; wv < kGicpWarps; ++wv) err += (double)s_part[wv][27];
+            s_y0 = err;
             s_iters = it + 1;
-            if (!solve6(H, g, x)) s_state = 1;
-            else {
-                double dR[9], dt[3];
-                se3_exp(x, dR, dt);
-                double nT[12];
-                for (int i = 0; i < 3; ++i) {
-                    for (int j = 0; j < 3; ++j)
-                        nT[i * 3 + j] = dR[i * 3] * s_T[j] + dR[i * 3 + 1] * s_T[3 + j] + dR[i * 3 + 2] * s_T[6 + j];
-                    nT[9 + i] = dR[i * 3] * s_T[9] + dR[i * 3 + 1] * s_T[10] + dR[i * 3 + 2] * s_T[11] + dt[i];
+            if (s_lambda < 0.0) {  // LsqRegistration: lm_lambda = lm_init_lambda_factor (1e-9) * H.diagonal().maxCoeff()
+                double mx = 0;
+                for (int c = 0; c < 6; ++c) mx = fmax(mx, s_H[c * 7]);
+                s_lambda = 1e-9 * mx;
+            }
+            s_nu = 2.0;
+            s_lm = 0;
+            if (a.out_error) a.out_error[pose_i] = (float)err;
+            if (a.stall_window > 0) {
+                if (err < s_best_y * (1.0 - (double)a.stall_rel)) {
+                    s_best_y = err;
+                    for (int i = 0; i < 12; ++i) s_best_T[i] = s_T[i];
+                    s_since_best = 0;
+                } else if (++s_since_best >= a.stall_window) {
+                    for (int i = 0; i < 12; ++i) s_T[i] = s_best_T[i];  // cycling: back to the best linearisation point
+                    if (a.out_error) a.out_error[pose_i] = (float)s_best_y;
+                    s_state = 1;
+                    s_lm = 2;
                 }
-                for (int i = 0; i < 12; ++i) s_T[i] = nT[i];
+            }
+        }
+        __syncthreads();
+        if (s_lm == 2) break;
+        // ---- Levenberg-Marquardt step (fast_gicp LsqRegistration::step_lm): up to 10 damped trials.  A trial solves
+        // (H + lambda I) d = -g, evaluates the error of exp(d) T with the correspondences and Mahalanobis matrices of the
+        // linearisation FROZEN (FastGICP::compute_error), and is accepted when the gain ratio
+        // rho = (y0 - y') / (d . (lambda d - g)) is not negative; a rejected trial multiplies lambda by nu (2, 4, 8 ...).
+        for (int trial = 0; trial < 10; ++trial) {
+            if (tid == 0) {
+                double Hd[36], x[6];
+                for (int i = 0; i < 36; ++i) Hd[i] = s_H[i];
+                for (int c = 0; c < 6; ++c) Hd[c * 7] += s_lambda;
+                if (!solve6(Hd, s_g, x)) {
+                    s_state = 1;
+                    s_lm = 2;
+                } else {
+                    double dR[9], dt[3];
+                    se3_exp(x, dR, dt);
+                    for (int i = 0; i < 3; ++i) {
+                        for (int j = 0; j < 3; ++j)
+                            s_Tt[i * 3 + j] = dR[i * 3] * s_T[j] + dR[i * 3 + 1] * s_T[3 + j] + dR[i * 3 + 2] * s_T[6 + j];
+                        s_Tt[9 + i] = dR[i * 3] * s_T[9] + dR[i * 3 + 1] * s_T[10] + dR[i * 3 + 2] * s_T[11] + dt[i];
+                    }
+                    double den = 0;
+                    for (int c = 0; c < 6; ++c) { s_d[c] = x[c]; den += x[c] * (s_lambda * x[c] - s_g[c]); }
+                    s_den = den;
+                }
+            }
+            __syncthreads();
+            if (s_lm == 2) break;
+            float Rt[9], tt[3];
+#pragma unroll
+            for (int i = 0; i < 9; ++i) Rt[i] = (float)s_Tt[i];
+#pragma unroll
+            for (int i = 0; i < 3; ++i) tt[i] = (float)s_Tt[9 + i];
+            float yt = 0.f;
+            for (int i = tid; i < n; i += kGicpThreads) {
+                const int ref = refs[i];
+                if (ref < 0) continue;
+                const float ax = pts[3 * i], ay = pts[3 * i + 1], az = pts[3 * i + 2];
+                const float4 b = __ldg(a.tgt_sorted + ref);
+                const float rx = b.x - (Rt[0] * ax + Rt[1] * ay + Rt[2] * az + tt[0]);
+                const float ry = b.y - (Rt[3] * ax + Rt[4] * ay + Rt[5] * az + tt[1]);
+                const float rz = b.z - (Rt[6] * ax + Rt[7] * ay + Rt[8] * az + tt[2]);
+                const float nax = nrm[3 * i], nay = nrm[3 * i + 1], naz = nrm[3 * i + 2];
+                const float na[3] = {R[0] * nax + R[1] * nay + R[2] * naz, R[3] * nax + R[4] * nay + R[5] * naz,
+                                     R[6] * nax + R[7] * nay + R[8] * naz};  // R of the linearisation: M is frozen
+                const float nb[3] = {a.tgt_normals[3 * (size_t)ref], a.tgt_normals[3 * (size_t)ref + 1], a.tgt_normals[3 * (size_t)ref + 2]};
+                const Sym3 M = inverse_sum_cov(na, nb, w);
+                yt += rx * (M.xx * rx + M.xy * ry + M.xz * rz) + ry * (M.xy * rx + M.yy * ry + M.yz * rz) +
+                      rz * (M.xz * rx + M.yz * ry + M.zz * rz);
+            }
+#pragma unroll
+            for (int o = 16; o >= 1; o >>= 1) yt += __shfl_xor_sync(0xffffffffu, yt, o);
+            if (lane == 0) s_part[warp][0] = yt;
+            __syncthreads();
+            if (tid == 0) {
+                double yi = 0;
+                for (int wv = 0; wv < kGicpWarps; ++wv) yi += (double)s_part[wv][0];
+                double dR[9], dt[3];
+                se3_exp(s_d, dR, dt);
                 double mr = 0, mt = 0;
                 for (int i = 0; i < 9; ++i) mr = fmax(mr, fabs(dR[i] - ((i % 4 == 0) ? 1.0 : 0.0)));
                 for (int i = 0; i < 3; ++i) mt = fmax(mt, fabs(dt[i]));
-                if (mr < (double)a.rotation_epsilon && mt < (double)a.translation_epsilon) s_state = 1;
+                const bool small = mr < (double)a.rotation_epsilon && mt < (double)a.translation_epsilon;
+                const double rho = (s_y0 - yi) / s_den;
+                if (rho < 0.0) {
+                    if (small) { s_state = 1; s_lm = 1; }        // rejected, but the step is below the epsilons: converged
+                    else { s_lambda *= s_nu; s_nu *= 2.0; }
+                } else {
+                    for (int i = 0; i < 12; ++i) s_T[i] = s_Tt[i];
+                    const double q = 2.0 * rho - 1.0;
+                    s_lambda *= fmax(1.0 / 3.0, 1.0 - q * q * q);
+                    s_lm = 1;
+                    if (small) s_state = 1;
+                }
             }
-            if (a.out_error) a.out_error[pose_i] = (float)err;
+            __syncthreads();
+            const int lm = s_lm;
+            __syncthreads();  // everyone has read s_lm before thread 0 may overwrite it in the next trial
+            if (lm) break;
         }
+        if (tid == 0 && s_lm == 0) s_state = 1;  // ten rejected trials: "lm not converged", the pose keeps its last accepted T
         __syncthreads();
     }
 
@@ -505,7 +599,7 @@ cudaError_t launch_pose_count_max(const int* d_pose_begin, int rows_per_pose, in
     return cudaGetLastError();
 }
 
-size_t gicp_smem_bytes(int smem_points) { return (size_t)smem_points * 6 * sizeof(float); }
+size_t gicp_smem_bytes(int smem_points) { return (size_t)smem_points * 7 * sizeof(float); }  // xyz, normal, correspondence
 
 cudaError_t launch_gicp(const GicpArgs& a, int n_poses, cudaStream_t stream) {
     if (n_poses <= 0) return cudaSuccess;

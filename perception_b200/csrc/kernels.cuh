@@ -191,6 +191,7 @@ struct GicpArgs {
     const int* pose_begin = nullptr;     // exclusive scan of per-lattice-row point counts (cloud.cu): pose p owns
     int rows_per_pose = 1;               //   points [pose_begin[p*rows_per_pose], pose_begin[(p+1)*rows_per_pose])
     float* src_normals = nullptr;        // N x 3 scratch (used when a pose's cloud exceeds smem_points)
+    int* src_ref = nullptr;              // N scratch: correspondences of the last linearisation (same condition)
     ObsGridDev grid;                     // observed cloud (target): cells sized for a few points each
     float grid_h = 0.f;                  // cell size of `grid`
     ObsGridDev coarse;                   // the cost stage's grid over the same cloud (== grid when the cloud is sparse)
@@ -211,6 +212,12 @@ struct GicpArgs {
     int max_iterations = 150;            // renderer.cu:1696
     float rotation_epsilon = 2e-3f;      // renderer.cu:1698
     float translation_epsilon = 5e-4f;   // renderer.cu:1699
+    // Extension (not in fast_gicp): hard nearest-neighbour assignment makes some poses cycle through the same few
+    // correspondence sets for ever, each step above the epsilons, until the iteration cap.  When the error of the
+    // linearisation point has not improved on its best value by stall_rel (relative) for stall_window consecutive
+    // linearisations, the pose stops and returns the transform of that best linearisation.  stall_window = 0: off.
+    int stall_window = 8;
+    float stall_rel = 1e-3f;
 };
 size_t gicp_smem_bytes(int smem_points);
 cudaError_t launch_gicp(const GicpArgs& a, int n_poses, cudaStream_t stream);

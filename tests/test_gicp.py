@@ -251,3 +251,33 @@ def test_gicp_dense_scene_cloud_grids_agree(orc, monkeypatch):
     for o in outs[1:]:
         assert np.array_equal(o["iterations"], outs[0]["iterations"])
         assert np.array_equal(o["transforms"], outs[0]["transforms"])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dof6", [False, True])
+def test_gicp_converges_before_the_iteration_cap(orc, dof6):
+    """With the Levenberg-Marquardt step (fast_gicp's default optimiser) strongly perturbed poses settle instead of
+    switching correspondences until the 150-iteration cap (round 1: plain Gauss-Newton, about a third never stopped):
+    >= 95 % of 60 perturbed poses must stop before the cap at the reference's settings (renderer.cu:1696-1699), and the
+    refinement must actually register them (lower final error than after the first linearisation)."""
+    from perception_b200 import synth
+    from perception_b200.renderer import Renderer
+    case = make_case(2000, 3, 42)
+    s = case.scene
+    stride = 4
+    obs = observed_6dof(case, stride, orc) if dof6 else observed_3dof(case, stride, orc)
+    poses, pmm, lab = _perturbed(case, 60, seed=9)
+    with Renderer(0) as r:
+        r.set_camera(case.width, case.height, case.proj, case.cx, case.cy, case.fx, case.fy, synth.DEPTH_FACTOR)
+        r.set_models(s.tris, s.tris_model_count)
+        r.set_scene(s.source_depth, s.source_color, s.source_label if dof6 else None)
+        r.set_observed(obs["aos"], obs["rgb"], obs["label"] if dof6 else None)
+        kw = dict(stride=stride, sensor_resolution=0.01, occlusion_threshold=1.0)
+        g1 = r.gicp(poses, pmm, lab if dof6 else None, icp_max_iterations=1, **kw)
+        g = r.gicp(poses, pmm, lab if dof6 else None, **kw)   # reference settings: 150 iterations, 2e-3 / 5e-4
+    it = g["iterations"]
+    stopped = (it < 150).mean()
+    print(f"GICP iterations: median {np.median(it)}, max {it.max()}, stopped before the cap: {100 * stopped:.1f} %")
+    assert stopped >= 0.95
+    assert (g["error"] <= g1["error"] * 1.0001 + 1e-12).mean() >= 0.9
+    assert np.median(it) < 40
