@@ -3,7 +3,7 @@ NVCC      ?= nvcc
 ARCH      := -gencode arch=compute_100a,code=sm_100a
 CSRC      := perception_b200/csrc
 NVFLAGS   := -std=c++17 -O3 $(ARCH) -lineinfo -Xcompiler -fPIC,-ffp-contract=off -I$(CSRC) -Iinclude
-SRCS      := $(CSRC)/pose_kernels.cu $(CSRC)/cloud.cu $(CSRC)/colour.cu $(CSRC)/knn.cu $(CSRC)/gicp.cu $(CSRC)/icp.cu $(CSRC)/states.cu $(CSRC)/input.cu $(CSRC)/compose.cu $(CSRC)/raster_full.cu $(CSRC)/verify.cu $(CSRC)/topk.cu $(CSRC)/capi.cu $(CSRC)/capi_multi.cu $(CSRC)/capi_states.cu $(CSRC)/capi_input.cu $(CSRC)/capi_compose.cu
+SRCS      := $(CSRC)/pose_kernels.cu $(CSRC)/cloud.cu $(CSRC)/colour.cu $(CSRC)/knn.cu $(CSRC)/gicp.cu $(CSRC)/icp.cu $(CSRC)/states.cu $(CSRC)/input.cu $(CSRC)/compose.cu $(CSRC)/raster_full.cu $(CSRC)/verify.cu $(CSRC)/obs_grid.cu $(CSRC)/topk.cu $(CSRC)/capi.cu $(CSRC)/capi_multi.cu $(CSRC)/capi_states.cu $(CSRC)/capi_input.cu $(CSRC)/capi_compose.cu
 OBJS      := $(SRCS:.cu=.o) $(CSRC)/clusters.o
 LIB       := perception_b200/libperch_b200.so
 REF       := /root/reference

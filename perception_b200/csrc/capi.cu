@@ -189,10 +189,69 @@ int build_point_grid_from(perch_ctx* c, const float* xyz, int n, const int* ids,
     return PERCH_OK;
 }
 
+int ensure_obs_tmp(perch_ctx* c, size_t n_ints) {
+    if (n_ints <= c->obs_tmp_n) return PERCH_OK;
+    if (c->d_obs_tmp) cudaFree(c->d_obs_tmp);
+    c->d_obs_tmp = nullptr;
+    c->obs_tmp_n = 0;
+    CU(cudaMalloc(&c->d_obs_tmp, n_ints * sizeof(int)));
+    c->obs_tmp_n = n_ints;
+    return PERCH_OK;
+}
+
+// Uniform grid over the resident observed cloud (d_obs_xyz4, label-sorted) with cells at least `h` wide (widened until it
+// has at most max_cells cells), built ON THE DEVICE (obs_grid.cu: count -> scan -> scatter); only the number of non-empty
+// cells comes back (4 bytes), for *avg_per_cell = points per non-empty cell.
 int build_point_grid(perch_ctx* c, float h, double max_cells, float4** d_pts, int** d_label, uint32_t** d_cell_start,
                      perch::ObsGridDev* out, double* avg_per_cell) {
-    return build_point_grid_from(c, c->h_obs_xyz.data(), c->n_obs, nullptr, c->obs_has_label ? c->h_obs_label.data() : nullptr, h,
-                                 max_cells, d_pts, d_label, d_cell_start, out, avg_per_cell);
+    using namespace perch;
+    cudaFree(*d_pts); *d_pts = nullptr;
+    cudaFree(*d_label); *d_label = nullptr;
+    cudaFree(*d_cell_start); *d_cell_start = nullptr;
+    *out = ObsGridDev{};
+    const int n = c->n_obs;
+    out->n_obs = n;
+    if (avg_per_cell) *avg_per_cell = 0.0;
+    if (n == 0) return PERCH_OK;
+    if (c->obs_nonfinite) return fail(PERCH_ERR_INVALID, "cloud contains a non-finite coordinate");
+    int dim[3];
+    float org[3], inv_h;
+    for (;;) {
+        inv_h = 1.0f / h;
+        double cells = 1;
+        for (int k = 0; k < 3; ++k) {
+            org[k] = c->obs_min[k] - h;
+            dim[k] = (int)std::floor((c->obs_max[k] - org[k]) * inv_h) + 2;
+            cells *= dim[k];
+        }
+        if (cells <= max_cells) break;
+        h *= 1.26f;  // ~2x fewer cells per step; larger cells only add candidates, never lose one
+    }
+    const size_t ncells = (size_t)dim[0] * dim[1] * dim[2];
+    ObsGridDev g;
+    g.ox = org[0]; g.oy = org[1]; g.oz = org[2];
+    g.inv_h = inv_h;
+    g.dx = dim[0]; g.dy = dim[1]; g.dz = dim[2];
+    g.n_obs = n;
+    int rc;
+    if ((rc = ensure_obs_tmp(c, ncells + 64))) return rc;
+    CU(cudaMalloc(d_pts, (size_t)n * sizeof(float4)));
+    if (c->obs_has_label) CU(cudaMalloc(d_label, (size_t)n * sizeof(int)));
+    CU(cudaMalloc(d_cell_start, (ncells + 1) * sizeof(uint32_t)));
+    int* d_nonempty = c->d_obs_tmp + ncells;
+    CU(perch::launch_obs_grid_build(c->d_obs_xyz4, c->obs_has_label ? c->d_obs_label_sorted : nullptr, n, g, *d_cell_start,
+                                    c->d_obs_tmp, *d_pts, *d_label, avg_per_cell ? d_nonempty : nullptr, c->stream));
+    if (avg_per_cell) {
+        int nonempty = 0;
+        CU(cudaMemcpyAsync(&nonempty, d_nonempty, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        *avg_per_cell = (double)n / (double)std::max(nonempty, 1);
+    }
+    g.pts = *d_pts;
+    g.label = *d_label;
+    g.cell_start = *d_cell_start;
+    *out = g;
+    return PERCH_OK;
 }
 
 // The grid of the cost stage: cells just wider than sensor_resolution, so that the 27 cells around a query hold every
@@ -302,26 +361,9 @@ int prepare_target_normals(perch_ctx* c, int k) {
     const int n = c->n_obs;
     if (n == 0 || c->tgt_normals_k == k) return PERCH_OK;
     int rc;
+    if ((rc = perch_detail::ensure_obs_host(c))) return rc;
     if ((rc = upload(&c->d_obs_xyz_aos, c->h_obs_xyz.data(), 3 * (size_t)n, c->stream))) return rc;
     if ((rc = upload<float>(&c->d_tgt_normals, nullptr, 3 * (size_t)n, c->stream))) return rc;
-    {
-        std::vector<float4> xyz4(n);
-        for (int i = 0; i < n; ++i)
-            xyz4[i] = make_float4(c->h_obs_xyz[3 * (size_t)i], c->h_obs_xyz[3 * (size_t)i + 1], c->h_obs_xyz[3 * (size_t)i + 2], 0.f);
-        int n_labels = 0;
-        for (int l : c->h_obs_label) n_labels = std::max(n_labels, l + 1);
-        std::vector<int> range(2 * (size_t)std::max(n_labels, 1), 0);
-        for (int i = 0; i < (int)c->h_obs_label.size(); ++i) {  // labels are sorted ascending
-            const int l = c->h_obs_label[i];
-            if (l < 0) continue;
-            if (range[2 * l + 1] == 0) range[2 * l] = i;
-            range[2 * l + 1] = i + 1;
-        }
-        if ((rc = upload(&c->d_obs_xyz4, xyz4.data(), (size_t)n, c->stream))) return rc;
-        if ((rc = upload(&c->d_label_range, range.data(), range.size(), c->stream))) return rc;
-        CU(cudaStreamSynchronize(c->stream));
-        c->n_label_ranges = n_labels;
-    }
     const int kk = std::min(k, n);
     std::vector<float> soa(3 * (size_t)n);
     for (int i = 0; i < n; ++i)
@@ -528,7 +570,7 @@ void perch_destroy(perch_ctx* c) {
                     c->d_src_depth, c->d_src_label, c->d_src_rgb, c->d_grid_pts, c->d_grid_label, c->d_cell_start,
                     c->d_icp_grid_pts, c->d_icp_grid_label, c->d_icp_grid_cells, c->d_cmp_depth, c->d_cmp_label, c->d_full_keys, c->d_full_big, c->d_full_count, c->d_full_acc, c->d_ggrid_pts, c->d_ggrid_label, c->d_ggrid_cell_start,
                     c->d_obs_lab, c->d_obs_rgb, c->d_scratch, c->d_err_flag, c->d_flush, c->d_obs_xyz_aos,
-                    c->d_tgt_normals, c->d_obs_xyz4, c->d_label_range, c->d_gicp, c->d_icp_pcd, c->d_icp_normals};
+                    c->d_tgt_normals, c->d_obs_xyz4, c->d_obs_label_sorted, c->d_obs_tmp, c->d_in_xyz, c->d_in_rgb, c->d_in_label, c->d_label_range, c->d_gicp, c->d_icp_pcd, c->d_icp_normals};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (c->h_pinned) cudaFreeHost(c->h_pinned);
@@ -806,6 +848,37 @@ int perch_set_observed(perch_ctx* c, const float* xyz_aos, const uint8_t* rgb_so
         }
     }
     int rc;
+    // the label-sorted cloud, its labels and the per-label ranges live on the device from here on
+    {
+        std::vector<float4> xyz4((size_t)std::max(n_obs, 1));
+        c->obs_nonfinite = false;
+        for (int k = 0; k < 3; ++k) { c->obs_min[k] = INFINITY; c->obs_max[k] = -INFINITY; }
+        for (int i = 0; i < n_obs; ++i) {
+            const float* v = &c->h_obs_xyz[3 * (size_t)i];
+            xyz4[i] = make_float4(v[0], v[1], v[2], 0.f);
+            for (int k = 0; k < 3; ++k) {
+                if (!std::isfinite(v[k])) c->obs_nonfinite = true;
+                c->obs_min[k] = std::min(c->obs_min[k], v[k]);
+                c->obs_max[k] = std::max(c->obs_max[k], v[k]);
+            }
+        }
+        int n_labels = 0;
+        for (int l : c->h_obs_label) n_labels = std::max(n_labels, l + 1);
+        std::vector<int> range(2 * (size_t)std::max(n_labels, 1), 0);
+        for (int i = 0; i < (int)c->h_obs_label.size(); ++i) {  // labels are sorted ascending
+            const int l = c->h_obs_label[i];
+            if (l < 0) continue;
+            if (range[2 * l + 1] == 0) range[2 * l] = i;
+            range[2 * l + 1] = i + 1;
+        }
+        if ((rc = upload(&c->d_obs_xyz4, xyz4.data(), xyz4.size(), c->stream))) return rc;
+        if ((rc = upload(&c->d_obs_label_sorted, label ? c->h_obs_label.data() : nullptr, label ? (size_t)std::max(n_obs, 1) : 0, c->stream))) return rc;
+        if ((rc = upload(&c->d_label_range, range.data(), range.size(), c->stream))) return rc;
+        CU(cudaStreamSynchronize(c->stream));  // host vectors go out of scope
+        c->n_label_ranges = n_labels;
+        c->obs_host_valid = true;
+        c->in_on_device = false;
+    }
     if ((rc = upload<uint8_t>(&c->d_obs_rgb, nullptr, 3 * (size_t)std::max(n_obs, 1), c->stream))) return rc;
     if ((rc = upload<float>(&c->d_obs_lab, nullptr, 3 * (size_t)std::max(n_obs, 1), c->stream))) return rc;
     if (n_obs > 0) {
@@ -823,6 +896,86 @@ int perch_set_observed(perch_ctx* c, const float* xyz_aos, const uint8_t* rgb_so
     note_memory(c);
     return PERCH_OK;
 }
+
+}  // extern "C"
+
+// The host mirrors of the label-sorted cloud (h_obs_xyz, h_obs_label): valid after perch_set_observed, fetched from the
+// device on first use after perch_set_input (GICP's target-normal preparation, the unfused check path, label counts).
+int perch_detail::ensure_obs_host(perch_ctx* c) {
+    if (c->obs_host_valid) return PERCH_OK;
+    const int n = c->n_obs;
+    std::vector<float4> xyz4((size_t)std::max(n, 1));
+    c->h_obs_xyz.assign(3 * (size_t)n, 0.f);
+    c->h_obs_label.assign(c->obs_has_label ? n : 0, 0);
+    if (n > 0) {
+        CU(cudaMemcpyAsync(xyz4.data(), c->d_obs_xyz4, (size_t)n * sizeof(float4), cudaMemcpyDeviceToHost, c->stream));
+        if (c->obs_has_label)
+            CU(cudaMemcpyAsync(c->h_obs_label.data(), c->d_obs_label_sorted, (size_t)n * 4, cudaMemcpyDeviceToHost, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        for (int i = 0; i < n; ++i) {
+            c->h_obs_xyz[3 * (size_t)i] = xyz4[i].x; c->h_obs_xyz[3 * (size_t)i + 1] = xyz4[i].y; c->h_obs_xyz[3 * (size_t)i + 2] = xyz4[i].z;
+        }
+    }
+    c->obs_host_valid = true;
+    return PERCH_OK;
+}
+
+// perch_set_observed for a cloud that is already on the device (perch_set_input): d_aos n x 3, colours as three planes
+// `rgb_stride` bytes apart, d_label (may be null) in [0, 256).  Stable sort by label, colours / CIELAB in the original
+// order, bounding box, per-label ranges -- all on the context's stream; 24 bytes (the box) + 4 (the label check) come back.
+int perch_detail::install_observed_device(perch_ctx* c, const float* d_aos, const uint8_t* d_rgb, size_t rgb_stride,
+                                          const int* d_label, int n) {
+    if (n > (1 << 24)) return fail(PERCH_ERR_CAPACITY, "observed cloud larger than 16M points");
+    c->n_obs = n;
+    c->obs_has_label = d_label != nullptr;
+    c->obs_nonfinite = false;
+    const size_t N = (size_t)std::max(n, 1);
+    int rc;
+    if ((rc = upload<float4>(&c->d_obs_xyz4, nullptr, N, c->stream))) return rc;
+    if ((rc = upload<int>(&c->d_obs_label_sorted, nullptr, d_label ? N : 0, c->stream))) return rc;
+    if ((rc = upload<int>(&c->d_label_range, nullptr, 512, c->stream))) return rc;
+    if ((rc = upload<uint8_t>(&c->d_obs_rgb, nullptr, 3 * N, c->stream))) return rc;
+    if ((rc = upload<float>(&c->d_obs_lab, nullptr, 3 * N, c->stream))) return rc;
+    const size_t hist_n = (size_t)perch::label_sort_chunks(n) * 256;
+    if ((rc = ensure_obs_tmp(c, hist_n + 64))) return rc;
+    int* d_small = c->d_obs_tmp + hist_n;  // [0..5] bounding box, [6] bad-label flag
+    CU(perch::launch_obs_bbox(d_aos, n, d_small, c->stream));
+    if (d_label) {
+        CU(perch::launch_label_sort(d_aos, d_label, n, c->d_obs_tmp, c->d_label_range, d_small + 6, c->d_obs_xyz4,
+                                    c->d_obs_label_sorted, c->stream));
+        c->n_label_ranges = 256;
+    } else {
+        CU(perch::launch_aos_to_xyz4(d_aos, n, c->d_obs_xyz4, c->stream));
+        CU(cudaMemsetAsync(c->d_label_range, 0, 512 * sizeof(int), c->stream));
+        CU(cudaMemsetAsync(d_small + 6, 0, sizeof(int), c->stream));
+        c->n_label_ranges = 0;
+    }
+    if (n > 0) {
+        for (int ch = 0; ch < 3; ++ch)
+            CU(cudaMemcpyAsync(c->d_obs_rgb + (size_t)ch * n, d_rgb + (size_t)ch * rgb_stride, (size_t)n, cudaMemcpyDeviceToDevice, c->stream));
+        // colours stay in the ORIGINAL order and are looked up with (sorted) NN indices, as renderer.cu:1881 does
+        CU(perch::launch_rgb2lab_planes(c->d_obs_rgb, c->d_obs_rgb + n, c->d_obs_rgb + 2 * (size_t)n, n, c->d_obs_lab, c->stream));
+    }
+    int small[7] = {0, 0, 0, 0, 0, 0, 0};
+    CU(cudaMemcpyAsync(small, d_small, sizeof small, cudaMemcpyDeviceToHost, c->stream));
+    CU(cudaStreamSynchronize(c->stream));
+    if (small[6]) return fail(PERCH_ERR_INVALID, "an observed label lies outside [0, 256)");
+    for (int k = 0; k < 3; ++k) {
+        c->obs_min[k] = n > 0 ? perch::obs_bbox_decode(small[k]) : 0.f;
+        c->obs_max[k] = n > 0 ? perch::obs_bbox_decode(small[3 + k]) : 0.f;
+    }
+    c->h_obs_xyz.clear();
+    c->h_obs_label.clear();
+    c->obs_host_valid = n == 0;
+    c->grid_res = -1.f;  // grid is (re)built on the next cost call, when sensor_resolution is known
+    c->tgt_normals_k = 0;
+    c->have_obs = true;
+    ++c->obs_version;
+    note_memory(c);
+    return PERCH_OK;
+}
+
+extern "C" {
 
 int perch_depth2cloud(perch_ctx* c, const int32_t* depth, const uint8_t* red, const uint8_t* green, const uint8_t* blue,
                       int width, int height, int num_poses, float cx, float cy, float fx, float fy, float depth_factor,

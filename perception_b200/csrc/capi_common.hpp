@@ -42,6 +42,9 @@ int ensure_pinned(perch_ctx* c, size_t bytes);   // the context's pinned host st
 int prepare_fused_cost(perch_ctx* c, const perch_params* p, perch::PoseArgs& a, bool& color);
 int report_err_flag(int flag);  // d_err_flag value -> status + message
 void destroy_comm(perch_ctx* c);  // capi_multi.cu
+int ensure_obs_host(perch_ctx* c);  // host mirrors of the label-sorted observed cloud, fetched on demand (capi.cu)
+int install_observed_device(perch_ctx* c, const float* d_aos, const uint8_t* d_rgb, size_t rgb_stride, const int* d_label,
+                            int n);  // perch_set_observed for a device-resident cloud (capi.cu)
 
 void destroy_states(perch_ctx* c);  // capi_states.cu
 

@@ -105,23 +105,28 @@ int perch_set_input(perch_ctx* c, const perch_input* in, int* observed_point_num
     for (int ch = 0; ch < 3; ++ch)
         PERCH_CU(cudaMemcpyAsync(c->d_src_rgb + ch * npx, d_planes[ch], npx, cudaMemcpyDeviceToDevice, c->stream));
     if (in->predicted_mask) PERCH_CU(cudaMemcpyAsync(c->d_src_label, d_mask, npx, cudaMemcpyDeviceToDevice, c->stream));
-    // 4. the compact cloud (tens of KB) visits the host once: the nearest-neighbour grid is built there (capi.cu)
+    // 4. the observed cloud stays on the device: only its size comes back here; label sort, colours, bounding box and
+    // (at the first cost call) the nearest-neighbour grid are device work (perch_detail::install_observed_device,
+    // obs_grid.cu).  A copy in depth2cloud_global's order is kept on the device for perch_get_observed.
     int total = 0;
     PERCH_CU(cudaMemcpyAsync(&total, d_rows + Lh, 4, cudaMemcpyDeviceToHost, c->stream));
     PERCH_CU(cudaStreamSynchronize(c->stream));
-    c->h_in_xyz.assign(3 * (size_t)total, 0.f);
-    c->h_in_rgb.assign(3 * (size_t)total, 0);
-    c->h_in_label.assign(total, -1);
     c->in_has_label = in->predicted_mask != nullptr;
+    for (void* q : {(void*)c->d_in_xyz, (void*)c->d_in_rgb, (void*)c->d_in_label}) cudaFree(q);
+    c->d_in_xyz = nullptr; c->d_in_rgb = nullptr; c->d_in_label = nullptr;
+    const size_t N = (size_t)std::max(total, 1);
+    PERCH_CU(cudaMalloc(&c->d_in_xyz, N * 12));
+    PERCH_CU(cudaMalloc(&c->d_in_rgb, N * 3));
+    PERCH_CU(cudaMalloc(&c->d_in_label, N * 4));
     if (total > 0) {
-        PERCH_CU(cudaMemcpyAsync(c->h_in_xyz.data(), d_aos, (size_t)total * 12, cudaMemcpyDeviceToHost, c->stream));
+        PERCH_CU(cudaMemcpyAsync(c->d_in_xyz, d_aos, (size_t)total * 12, cudaMemcpyDeviceToDevice, c->stream));
         for (int ch = 0; ch < 3; ++ch)
-            PERCH_CU(cudaMemcpyAsync(c->h_in_rgb.data() + (size_t)ch * total, d_rgb + (size_t)ch * cap, total,
-                                     cudaMemcpyDeviceToHost, c->stream));
-        if (c->in_has_label)
-            PERCH_CU(cudaMemcpyAsync(c->h_in_label.data(), d_lab, (size_t)total * 4, cudaMemcpyDeviceToHost, c->stream));
+            PERCH_CU(cudaMemcpyAsync(c->d_in_rgb + (size_t)ch * total, d_rgb + (size_t)ch * cap, total, cudaMemcpyDeviceToDevice, c->stream));
+        if (c->in_has_label) PERCH_CU(cudaMemcpyAsync(c->d_in_label, d_lab, (size_t)total * 4, cudaMemcpyDeviceToDevice, c->stream));
     }
-    PERCH_CU(cudaStreamSynchronize(c->stream));
+    c->in_n = total;
+    c->in_on_device = true;
+    c->h_in_xyz.clear(); c->h_in_rgb.clear(); c->h_in_label.clear();
     c->scene.depth = c->d_src_depth;
     c->composed = false;
     c->scene.label = in->predicted_mask ? c->d_src_label : nullptr;
@@ -130,18 +135,27 @@ int perch_set_input(perch_ctx* c, const perch_input* in, int* observed_point_num
     c->scene.b = c->d_src_rgb + 2 * npx;
     c->have_scene = true;
     *observed_point_num = total;
-    return perch_set_observed(c, c->h_in_xyz.data(), c->h_in_rgb.data(), c->in_has_label ? c->h_in_label.data() : nullptr, total);
+    int rc = perch_detail::install_observed_device(c, c->d_in_xyz, c->d_in_rgb, (size_t)total, c->in_has_label ? c->d_in_label : nullptr, total);
+    c->in_on_device = rc == PERCH_OK;
+    return rc;
 }
 
 int perch_get_observed(perch_ctx* c, float* xyz_aos, uint8_t* rgb_soa, int* label, int capacity, int* point_num) {
     if (!c || !point_num) return fail(PERCH_ERR_INVALID, "null argument");
-    const int n = (int)c->h_in_label.size();
+    if (!c->in_on_device) return fail(PERCH_ERR_INVALID, "perch_set_input has not been called (or perch_set_observed replaced its cloud)");
+    const int n = c->in_n;
     *point_num = n;
     if (!xyz_aos && !rgb_soa && !label) return PERCH_OK;
     if (capacity < n) return fail(PERCH_ERR_CAPACITY, "the observed cloud has %d points, the buffers hold %d", n, capacity);
-    if (xyz_aos) std::copy(c->h_in_xyz.begin(), c->h_in_xyz.end(), xyz_aos);
-    if (rgb_soa) std::copy(c->h_in_rgb.begin(), c->h_in_rgb.end(), rgb_soa);
-    if (label) std::copy(c->h_in_label.begin(), c->h_in_label.end(), label);
+    if (n == 0) return PERCH_OK;
+    DeviceGuard g(c->device);
+    if (xyz_aos) PERCH_CU(cudaMemcpyAsync(xyz_aos, c->d_in_xyz, (size_t)n * 12, cudaMemcpyDeviceToHost, c->stream));
+    if (rgb_soa) PERCH_CU(cudaMemcpyAsync(rgb_soa, c->d_in_rgb, (size_t)n * 3, cudaMemcpyDeviceToHost, c->stream));
+    if (label) {
+        if (c->in_has_label) PERCH_CU(cudaMemcpyAsync(label, c->d_in_label, (size_t)n * 4, cudaMemcpyDeviceToHost, c->stream));
+        else std::fill(label, label + n, -1);
+    }
+    PERCH_CU(cudaStreamSynchronize(c->stream));
     return PERCH_OK;
 }
 

@@ -122,6 +122,10 @@ double normalize_angle_positive(double a) { return std::fmod(std::fmod(a, 2.0 * 
 int refresh_seg_counts(perch_ctx* c, perch::StatesCtx* st) {
     if (st->seg_version == c->obs_version) return PERCH_OK;
     // search_env.cpp:6024-6059: number of observed points per label
+    {
+        const int rc0 = perch_detail::ensure_obs_host(c);
+        if (rc0) return rc0;
+    }
     int n_labels = 0;
     if (c->obs_has_label)
         for (int l : c->h_obs_label) n_labels = std::max(n_labels, l + 1);

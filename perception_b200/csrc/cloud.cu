@@ -197,6 +197,11 @@ cudaError_t launch_cloud_scan(const CloudArgs& a, cudaStream_t stream) {
     return cudaGetLastError();
 }
 
+cudaError_t launch_exclusive_scan(int* d_data, int n, cudaStream_t stream) {
+    scan_kernel<<<1, 1024, 0, stream>>>(d_data, n);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_cloud_write(const CloudArgs& a, cudaStream_t stream) {
     const int Lh = (a.img_h + a.stride - 1) / a.stride;
     if (a.num_images <= 0 || Lh <= 0) return cudaSuccess;

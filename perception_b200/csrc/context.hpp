@@ -120,6 +120,21 @@ struct perch_ctx {
     int max_model_quads = 0;
 
     // observed cloud (host copies kept so the grid can be rebuilt when sensor_resolution changes)
+    // The label-sorted cloud lives on the device (d_obs_xyz4 / d_obs_label_sorted below); the host mirrors are filled by
+    // perch_set_observed (host input) and only on demand after perch_set_input (perch_detail::ensure_obs_host)
+    bool obs_host_valid = true;
+    bool obs_nonfinite = false;        // a coordinate of the host cloud was not finite (reported when the grid is built)
+    float obs_min[3] = {0, 0, 0}, obs_max[3] = {0, 0, 0};  // bounding box of the cloud
+    int* d_obs_label_sorted = nullptr; // sorted labels (null in 3-DoF)
+    int* d_obs_tmp = nullptr;          // label-sort histograms / grid cursors / small readbacks
+    size_t obs_tmp_n = 0;
+    // perch_set_input: the compact cloud in the order depth2cloud_global returns it, kept on the device for
+    // perch_get_observed (xyz in_n x 3, colours 3 x in_n, labels in_n)
+    float* d_in_xyz = nullptr;
+    uint8_t* d_in_rgb = nullptr;
+    int* d_in_label = nullptr;
+    int in_n = 0;
+    bool in_on_device = false;
     std::vector<float> h_obs_xyz;      // label-sorted, AoS
     std::vector<uint8_t> h_obs_rgb;    // original order, 3 x N SoA (reference never permutes colours, renderer.cu:1881)
     std::vector<int> h_obs_label;      // sorted labels (empty in 3-DoF)

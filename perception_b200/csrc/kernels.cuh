@@ -174,6 +174,23 @@ cudaError_t launch_cloud_count(const CloudArgs& a, cudaStream_t stream);
 cudaError_t launch_cloud_scan(const CloudArgs& a, cudaStream_t stream);  // exclusive scan of row_counts, total in last
 cudaError_t launch_cloud_write(const CloudArgs& a, cudaStream_t stream);
 
+// in-place exclusive scan of n ints by one CTA; element n receives the total (cloud.cu)
+cudaError_t launch_exclusive_scan(int* d_data, int n, cudaStream_t stream);
+
+// ---- the observed cloud on the device (obs_grid.cu): bounding box, stable label sort, uniform grid ------------------------
+cudaError_t launch_obs_bbox(const float* d_aos, int n, int* d_out6, cudaStream_t stream);  // 6 order-encoded ints
+float obs_bbox_decode(int ord);
+int label_sort_chunks(int n);
+// stable sort by label in [0, 256): d_hist = label_sort_chunks(n) x 256 ints of scratch, d_ranges = 512 ints ([begin, end) per
+// label), *d_bad is set when a label is out of range
+cudaError_t launch_label_sort(const float* d_aos, const int* d_label, int n, int* d_hist, int* d_ranges, int* d_bad,
+                              float4* d_out_xyz4, int* d_out_label, cudaStream_t stream);
+cudaError_t launch_aos_to_xyz4(const float* d_aos, int n, float4* d_out, cudaStream_t stream);
+// uniform grid over the (label-sorted) cloud; g carries origin / inv_h / dims; d_cell_start ncells + 1, d_cursor ncells scratch
+cudaError_t launch_obs_grid_build(const float4* d_sorted, const int* d_sorted_label, int n, const ObsGridDev& g,
+                                  uint32_t* d_cell_start, int* d_cursor, float4* d_out_pts, int* d_out_label, int* d_nonempty,
+                                  cudaStream_t stream);  // *d_nonempty (may be null) = number of non-empty cells
+
 // ---- colour preparation (cost_type 1) ------------------------------------------------------------------------
 // lab[3*i..] = rgb2lab(c2[i], c1[i], c0[i]) -- the reference feeds plane 2 as "red" (compute_costs.cuh:214-220).
 cudaError_t launch_rgb2lab_planes(const uint8_t* c0, const uint8_t* c1, const uint8_t* c2, int n, float* lab,

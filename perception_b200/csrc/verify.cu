@@ -122,6 +122,10 @@ extern "C" int perch_render_cost_unfused(perch_ctx* c, const float* poses16, int
         return fail(PERCH_ERR_INVALID, "pose_segmentation_label given but the observed cloud was set without labels");
     if (n_poses == 0) return PERCH_OK;
     perch_detail::DeviceGuard g(c->device);
+    {
+        const int rc = perch_detail::ensure_obs_host(c);
+        if (rc) return rc;
+    }
     const size_t P = (size_t)n_poses, npx = (size_t)W * H;
     const int Lw = W / s, Lh = (H + s - 1) / s;
     const int n_obs = c->n_obs, words = std::max((n_obs + 31) / 32, 1);
