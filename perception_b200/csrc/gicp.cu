@@ -126,10 +126,26 @@ __device__ inline bool ring_search(const ObsGridDev& g, float h, int max_rings, 
         if (r > max_rings) return false;
         const int z0 = max(cz - r, 0), z1 = min(cz + r, g.dz - 1);
         const int y0 = max(cy - r, 0), y1 = min(cy + r, g.dy - 1);
+        // Cells are pruned by their exact distance from the query: a point of cell (x, y, z) is at least
+        // gap(qx, x)^2 + gap(qy, y)^2 + gap(qz, z)^2 away, gap = distance from the coordinate to the cell's interval
+        // [o + i h, o + (i + 1) h].  A row (y, z) whose bound exceeds the best distance so far is skipped without a load,
+        // and the x-run of a visited row is shortened from both ends the same way: after the query's own cell (ring 0)
+        // a dense cloud needs a handful of the 26 cells of ring 1 instead of all of them.  (1.0002: the bound is computed
+        // in float; `>` keeps equal distances, which the lowest-index tie-break needs; every gap is shortened by 0.1 % of
+        // a cell, far more than the rounding of a point's cell assignment (floor((p - o) * inv_h), inv_h ~ 1 / h).)
+        const float slack = 1e-3f * h;
+        auto gap2 = [&](float q, float o, int i) {
+            const float lo = fmaf((float)i, h, o), d = fmaxf(fmaxf(lo - q, q - (lo + h)) - slack, 0.f);
+            return d * d;
+        };
         for (int z = z0; z <= z1; ++z) {
             const bool zface = (z == cz - r) || (z == cz + r);
+            const float gz = gap2(qz, g.oz, z);
+            if (gz > best * 1.0002f) continue;
             for (int y = y0; y <= y1; ++y) {
                 const bool face = zface || (y == cy - r) || (y == cy + r);
+                const float gyz = gz + gap2(qy, g.oy, y);
+                if (gyz > best * 1.0002f) continue;
                 const int row = (z * g.dy + y) * g.dx;
                 // on a face of the ring cube the whole x-run belongs to the ring, otherwise only its two end cells
                 for (int part = 0; part < 2; ++part) {
@@ -140,6 +156,9 @@ __device__ inline bool ring_search(const ObsGridDev& g, float h, int max_rings, 
                         xa = xb = part ? cx + r : cx - r;
                         if (xa < 0 || xa > g.dx - 1) continue;
                     }
+                    while (xa <= xb && gyz + gap2(qx, g.ox, xa) > best * 1.0002f) ++xa;
+                    while (xb >= xa && gyz + gap2(qx, g.ox, xb) > best * 1.0002f) --xb;
+                    if (xa > xb) continue;
                     const uint32_t b = __ldg(g.cell_start + row + xa), e = __ldg(g.cell_start + row + xb + 1);
                     for (uint32_t j = b; j < e; ++j) {
                         if (use_label && __ldg(g.label + j) != label) continue;
@@ -156,6 +175,45 @@ __device__ inline bool ring_search(const ObsGridDev& g, float h, int max_rings, 
     // (*) a query inside cell c is at least (rho - 1)*h from any point of a cell at Chebyshev distance rho (also when
     // the query lies outside the grid and c is the clamped cell); after rings 0..r-1 the unvisited cells have rho >= r,
     // hence the bound (r-1)*h used before visiting ring r.
+}
+
+#ifndef PERCH_GICP_WARM_CELLS
+#define PERCH_GICP_WARM_CELLS 3.0f
+#endif
+constexpr float kWarmCells = PERCH_GICP_WARM_CELLS;  // warm start when the previous correspondence is within this many cell widths
+
+// Exact nearest neighbour when a candidate within a few cell widths is already known (the correspondence of the previous
+// linearisation: poses move little between iterations): only the cells that intersect the ball of the candidate's distance
+// around the query can hold a nearer point (or an equally near one with a lower reference index) -- typically 1-4 cells
+// instead of the 27 a cold search must visit, and one dependent load chain instead of three rings of them.  `best` /
+// `best_ref` / `best_pt` carry the candidate in and the nearest neighbour out; same distance arithmetic and tie-break as
+// ring_search.
+__device__ inline void ball_search(const ObsGridDev& g, float h, float qx, float qy, float qz, bool use_label, int label,
+                                   float& best, int& best_ref, float4& best_pt) {
+    const float slack = 1e-3f * h;
+    const float r = sqrtf(best) * 1.0001f + slack;
+    const int x0 = min(max((int)floorf((qx - r - g.ox) * g.inv_h), 0), g.dx - 1), x1 = min(max((int)floorf((qx + r - g.ox) * g.inv_h), 0), g.dx - 1);
+    const int y0 = min(max((int)floorf((qy - r - g.oy) * g.inv_h), 0), g.dy - 1), y1 = min(max((int)floorf((qy + r - g.oy) * g.inv_h), 0), g.dy - 1);
+    const int z0 = min(max((int)floorf((qz - r - g.oz) * g.inv_h), 0), g.dz - 1), z1 = min(max((int)floorf((qz + r - g.oz) * g.inv_h), 0), g.dz - 1);
+    auto gap2 = [&](float q, float o, int i) {
+        const float lo = fmaf((float)i, h, o), d = fmaxf(fmaxf(lo - q, q - (lo + h)) - slack, 0.f);
+        return d * d;
+    };
+    for (int z = z0; z <= z1; ++z) {
+        const float gz = gap2(qz, g.oz, z);
+        for (int y = y0; y <= y1; ++y) {
+            if (gz + gap2(qy, g.oy, y) > best * 1.0002f) continue;
+            const int row = (z * g.dy + y) * g.dx;
+            const uint32_t b = __ldg(g.cell_start + row + x0), e = __ldg(g.cell_start + row + x1 + 1);
+            for (uint32_t j = b; j < e; ++j) {
+                if (use_label && __ldg(g.label + j) != label) continue;
+                const float4 p = __ldg(g.pts + j);
+                const float d = sqdist3(qx, qy, qz, p.x, p.y, p.z);
+                const int ref = __float_as_int(p.w);
+                if (d < best || (d == best && ref < best_ref)) { best = d; best_ref = ref; best_pt = p; }
+            }
+        }
+    }
 }
 
 // Exact nearest observed point (optionally of one label), no distance gate: ring expansion over the fine grid (cells
@@ -400,7 +458,21 @@ __global__ void __launch_bounds__(kGicpThreads, PERCH_GICP_MIN_BLOCKS) gicp_kern
             const float pz = R[6] * ax + R[7] * ay + R[8] * az + t[2];
             float best; int ref; float4 b;
             if (stream_target) nn_range(a.tgt_sorted, lb, le, px, py, pz, best, ref, b);
-            else nn_unbounded(a.grid, a.grid_h, a.coarse, a.coarse_h, px, py, pz, use_label, label, best, ref, b);
+            else {
+                // warm start from the previous linearisation's correspondence when it is within a cell width
+                bool warm = false;
+                if (it > 0 && refs[i] >= 0) {
+                    const int r0 = refs[i];
+                    const float4 p0 = __ldg(a.tgt_sorted + r0);
+                    const float d0 = sqdist3(px, py, pz, p0.x, p0.y, p0.z);
+                    if (d0 < a.grid_h * a.grid_h * kWarmCells * kWarmCells) {
+                        best = d0; ref = r0; b = p0;
+                        ball_search(a.grid, a.grid_h, px, py, pz, use_label, label, best, ref, b);
+                        warm = true;
+                    }
+                }
+                if (!warm) nn_unbounded(a.grid, a.grid_h, a.coarse, a.coarse_h, px, py, pz, use_label, label, best, ref, b);
+            }
             refs[i] = ref;
             if (ref < 0) continue;  // no target point carries this label
             const float nax = nrm[3 * i], nay = nrm[3 * i + 1], naz = nrm[3 * i + 2];
