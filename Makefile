@@ -31,6 +31,11 @@ stats: $(OBJS)
 	$(NVCC) $(NVFLAGS) -DPERCH_STATS -c $(CSRC)/pose_kernels.cu -o $(CSRC)/pose_kernels_stats.o
 	$(NVCC) $(ARCH) -shared -o perception_b200/libperch_b200_stats.so $(CSRC)/pose_kernels_stats.o $(filter-out $(CSRC)/pose_kernels.o,$(OBJS)) -lnccl
 
+# Bounds-checked build of the per-pose kernel (tools/bounds_check.py): compute-sanitizer is closed on this pool.
+check: $(OBJS)
+	$(NVCC) $(NVFLAGS) -DPERCH_BOUNDS_CHECK -c $(CSRC)/pose_kernels.cu -o $(CSRC)/pose_kernels_check.o
+	$(NVCC) $(ARCH) -shared -o perception_b200/libperch_b200_check.so $(CSRC)/pose_kernels_check.o $(filter-out $(CSRC)/pose_kernels.o,$(OBJS)) -lnccl
+
 oracle:
 	$(MAKE) -C oracle
 
@@ -38,4 +43,4 @@ clean:
 	rm -f $(OBJS) $(LIB)
 	$(MAKE) -C oracle clean
 
-.PHONY: all oracle clean stats
+.PHONY: all oracle clean stats check variant

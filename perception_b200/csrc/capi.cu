@@ -335,6 +335,9 @@ int prepare_cost_args(perch_ctx* c, const perch_params* p, perch::PoseArgs& a, b
     a.tri_lab = c->d_tri_lab;
     a.obs_lab = c->d_obs_lab;
     a.mask_words = (c->n_obs + 31) / 32;
+    a.obs_sorted = c->d_obs_xyz4;
+    a.label_range = c->d_label_range;
+    a.n_label_ranges = c->n_label_ranges;
     const int Lw = c->cam.width / p->stride;
     int cap = env_int("PERCH_COST_TILE_CAP", 2048);
     a.tile_cap = std::max(cap, Lw);
@@ -522,6 +525,7 @@ int report_err_flag(int flag) {
     if (!flag) return PERCH_OK;
     if (flag & 2) return fail(PERCH_ERR_INVALID, "a state names a model_id outside [0, n_models)");
     if (flag & 4) return fail(PERCH_ERR_INVALID, "a state's segmentation_label_id has no entry in the observed labels");
+    if (flag & 256) return fail(PERCH_ERR_CUDA, "internal error: a shared-memory index of the per-pose kernel was out of range (bounds-check build, flag %d)", flag);
     return fail(PERCH_ERR_CUDA, "internal error: a fragment fell outside its pose tile (flag %d)", flag);
 }
 }  // namespace perch_detail
@@ -568,7 +572,7 @@ void perch_destroy(perch_ctx* c) {
     void* ptrs[] = {c->d_tri_color, c->d_model_low, c->d_model_high, c->d_model_aabb, c->d_model_qrmax, c->d_tri_lab, c->d_cl_recs, c->d_cl_bounds, c->d_q_bounds,
                     c->d_cl_orig, c->d_cl_perm, c->d_cl_low, c->d_cl_high,
                     c->d_src_depth, c->d_src_label, c->d_src_rgb, c->d_grid_pts, c->d_grid_label, c->d_cell_start,
-                    c->d_icp_grid_pts, c->d_icp_grid_label, c->d_icp_grid_cells, c->d_cmp_depth, c->d_cmp_label, c->d_full_keys, c->d_full_big, c->d_full_count, c->d_full_acc, c->d_ggrid_pts, c->d_ggrid_label, c->d_ggrid_cell_start,
+                    c->d_icp_grid_pts, c->d_icp_grid_label, c->d_icp_grid_cells, c->d_cmp_depth, c->d_cmp_label, c->d_full_keys, c->d_full_big, c->d_full_count, c->d_full_acc, c->d_full_rects, c->d_ggrid_pts, c->d_ggrid_label, c->d_ggrid_cell_start,
                     c->d_obs_lab, c->d_obs_rgb, c->d_scratch, c->d_err_flag, c->d_flush, c->d_obs_xyz_aos,
                     c->d_tgt_normals, c->d_obs_xyz4, c->d_obs_label_sorted, c->d_obs_tmp, c->d_in_xyz, c->d_in_rgb, c->d_in_label, c->d_label_range, c->d_gicp, c->d_icp_pcd, c->d_icp_normals};
     for (void* p : ptrs)

@@ -116,6 +116,8 @@ struct perch_ctx {
     int2* d_full_big = nullptr;
     int* d_full_count = nullptr;
     int* d_full_acc = nullptr;
+    int* d_full_rects = nullptr;       // 4 ints per pose of a chunk: key-image rectangle the pose touched
+    size_t full_rects_n = 0;
     size_t full_acc_n = 0;
     int max_model_quads = 0;
 

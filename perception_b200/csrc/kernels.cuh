@@ -49,6 +49,11 @@ struct PoseArgs {
     int* err_flag = nullptr;          // set to 1 if a fragment fell outside its pose tile (must never happen)
     int tile_cap = 0;                 // lattice cells of shared-memory z-buffer per band
     int mask_words = 0;               // ceil(n_obs / 32) (MODE_COST)
+    // A/B variant PERCH_COST_SMEM_OBS only (the mechanism BASELINE.json's north_star names): the observed points of the
+    // pose's label are bulk-copied (cp.async.bulk) into shared memory and searched linearly from there
+    const float4* obs_sorted = nullptr;   // label-sorted observed cloud (index = reference index)
+    const int* label_range = nullptr;     // [begin, end) per label
+    int n_label_ranges = 0;
 };
 size_t pose_kernel_smem_bytes(const PoseArgs& a, bool image_mode, bool color);
 cudaError_t launch_fused_cost(const PoseArgs& a, bool color, cudaStream_t stream);
@@ -104,6 +109,11 @@ struct FullRasterArgs {
     float* tree_clutter = nullptr;
     float* tree_total = nullptr;
     int* tree_acc = nullptr;                // 3 x n_poses scratch (flags, cleared, covered)
+    // bounding rectangle (image columns / rows) of everything the rasterising kernels z-tested for each pose of the chunk:
+    // rect_min = 2 ints per pose (x, y; initialised 0x7f7f7f7f), rect_max = 2 per pose (initialised 0x80808080).  The
+    // resolve pass reads keys only inside it (all keys outside are empty) -- or everywhere when null.
+    int* rect_min = nullptr;
+    int* rect_max = nullptr;
 };
 cudaError_t launch_full_raster(const FullRasterArgs& a, int max_model_quads, cudaStream_t stream);
 cudaError_t launch_full_resolve(const FullRasterArgs& a, int n_images, cudaStream_t stream);

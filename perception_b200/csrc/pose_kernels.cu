@@ -61,6 +61,15 @@ __device__ __forceinline__ float __frcp_approx(float x) {
     return r;
 }
 
+// `make check` build (tools/bounds_check.py): every data-dependent index into the kernel's shared-memory arrays is range
+// checked; a violation sets bit 8 of PoseArgs::err_flag (reported as PERCH_ERR_CUDA) and the access is skipped.  Stands in
+// for compute-sanitizer memcheck, which is closed on this pool.  The product build compiles the checks away.
+#ifdef PERCH_BOUNDS_CHECK
+#define IDX_OK(i, cap) (((i) >= 0 && (i) < (cap)) ? true : (atomicOr(a.err_flag, 256), false))
+#else
+#define IDX_OK(i, cap) true
+#endif
+
 #ifdef PERCH_STATS
 // Counters build only (`make stats`, tools/pose_stats.py): survivors of each culling level, summed over all poses.
 __device__ unsigned long long g_stats[16];
@@ -379,7 +388,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                     // many lattice pixels: left to the cooperative pass (unless its list is full)
                     const int bslot = atomicAdd(&s_bigcount, 1);
                     if (bslot < kBigCap) {
-                        s_big[bslot] = entry;
+                        if (IDX_OK(bslot, kBigCap)) s_big[bslot] = entry;
                         return;
                     }
                 }
@@ -400,7 +409,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                 for (; c < cells; c += step) {
                     int32_t d;
                     if (fragment_depth(ts, (float)(lx * s), (float)(H - 1 - ly * s), d)) {
-                        atomicMin(&zbuf[(ly - by0) * tile_w + (lx - rx0)], Z::make(d, id));
+                        if (IDX_OK((ly - by0) * tile_w + (lx - rx0), a.tile_cap)) atomicMin(&zbuf[(ly - by0) * tile_w + (lx - rx0)], Z::make(d, id));
                         STAT(6, 1);
                     }
                     lx += step_cols; ly += step_rows;
@@ -515,7 +524,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                 unsigned hits = 0;
                 int ea = 0, eb = 0;
                 if (lane < count) {
-                    const int q = wpend[first + lane];
+                    const int q = IDX_OK(first + lane, kPendCap) ? wpend[first + lane] : 2 * cl_low;
                     const uint32_t perm = __ldg(a.models.cl_perm + (q >> 1)) >> (12 * (q & 1));
                     const uint32_t pa = perm & 63u, pb = (perm >> 6) & 63u;
                     hits = quad_candidates(q);
@@ -530,8 +539,8 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                 int slot = 0;
                 if (lane == 0 && total) slot = atomicAdd(&s_qcount, total);
                 slot = __shfl_sync(0xffffffffu, slot, 0);
-                if (hits & 1u) queue[slot + __popc(b0 & lt_mask)] = ea;
-                if (hits & 2u) queue[slot + n0 + __popc(b1 & lt_mask)] = eb;
+                if ((hits & 1u) && IDX_OK(slot + __popc(b0 & lt_mask), kQueueCap)) queue[slot + __popc(b0 & lt_mask)] = ea;
+                if ((hits & 2u) && IDX_OK(slot + n0 + __popc(b1 & lt_mask), kQueueCap)) queue[slot + n0 + __popc(b1 & lt_mask)] = eb;
             };
 
             // Warps claim groups of kClaim quads dynamically (no block barrier inside pass A); a warp stops claiming when
@@ -556,7 +565,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                         const int q = qb + 32 * k;
                         const bool keep = (q < q_high) && !sphere_rejects(bnd[k]);
                         const unsigned bal = __ballot_sync(0xffffffffu, keep);
-                        if (keep) wpend[npend + __popc(bal & lt_mask)] = q;
+                        if (keep && IDX_OK(npend + __popc(bal & lt_mask), kPendCap)) wpend[npend + __popc(bal & lt_mask)] = q;
                         npend += __popc(bal);
                     }
                     if (lane == 0) { STAT(0, min(kClaim, q_high - (q_low + g * kClaim))); }
@@ -633,6 +642,40 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                     if (a.img_r) { a.img_r[o] = (uint8_t)rgb; a.img_g[o] = (uint8_t)(rgb >> 8); a.img_b[o] = (uint8_t)(rgb >> 16); }
                 }
             } else {
+#ifdef PERCH_COST_SMEM_OBS
+                // A/B variant: the pose's label range of the sorted observed cloud -> shared memory with one bulk copy
+                // (cp.async.bulk + mbarrier), then a linear scan from shared memory instead of the grid query
+                float4* s_obs = reinterpret_cast<float4*>((reinterpret_cast<uintptr_t>(mask + mask_words) + 15) & ~(uintptr_t)15);
+                __shared__ int s_obs_n, s_obs_lb;
+                __shared__ __align__(8) unsigned long long s_bar;
+                if (tid == 0) {
+                    int lb = 0, le = a.grid.n_obs;
+                    if (use_label) {
+                        const bool known = pose_label >= 0 && pose_label < a.n_label_ranges;
+                        lb = known ? a.label_range[2 * pose_label] : 0;
+                        le = known ? a.label_range[2 * pose_label + 1] : 0;
+                    }
+                    s_obs_lb = lb;
+                    s_obs_n = (le - lb) <= PERCH_COST_SMEM_OBS ? le - lb : -1;  // too large: the grid query
+                    const unsigned bar = (unsigned)__cvta_generic_to_shared(&s_bar);
+                    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+                    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+                    if (s_obs_n > 0) {
+                        const unsigned bytes = (unsigned)s_obs_n * 16u;
+                        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+                        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                                     ::"r"((unsigned)__cvta_generic_to_shared(s_obs)), "l"(a.obs_sorted + lb), "r"(bytes), "r"(bar) : "memory");
+                    }
+                }
+                __syncthreads();
+                if (s_obs_n > 0) {
+                    const unsigned bar = (unsigned)__cvta_generic_to_shared(&s_bar);
+                    unsigned done = 0;
+                    while (!done)
+                        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }"
+                                     : "=r"(done) : "r"(bar) : "memory");
+                }
+#endif
                 // ---- 3. cost over the band's lattice pixels ---------------------------------------------------
                 // 3a: covered pixels that survive the source-occlusion rule are compacted into the (now idle) candidate
                 // queue, so that the nearest-neighbour queries below run with every lane busy
@@ -658,7 +701,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                         int base = 0;
                         if (lane == 0 && lb) base = atomicAdd(&s_qcount, __popc(lb));
                         base = __shfl_sync(0xffffffffu, base, 0);
-                        if (live) queue[base + __popc(lb & ((1u << lane) - 1u))] = c;
+                        if (live && IDX_OK(base + __popc(lb & ((1u << lane) - 1u)), kQueueCap)) queue[base + __popc(lb & ((1u << lane) - 1u))] = c;
                     }
                     __syncthreads();
                 }
@@ -680,6 +723,16 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                     float qx, qy, qz;
                     back_project(u, v, d, a.cam.cx, a.cam.cy, a.cam.fx, a.cam.fy, a.cam.depth_factor, qx, qy, qz);
                     float best; int ref;
+#ifdef PERCH_COST_SMEM_OBS
+                    if (s_obs_n >= 0) {
+                        best = FLT_MAX; ref = -1;
+                        for (int j = 0; j < s_obs_n; ++j) {
+                            const float4 p = s_obs[j];
+                            const float dd = sqdist3(qx, qy, qz, p.x, p.y, p.z);
+                            if (dd < best) { best = dd; ref = s_obs_lb + j; }
+                        }
+                    } else
+#endif
                     nn_query(a.grid, qx, qy, qz, use_label, pose_label, best, ref);
                     if (best > a.res2) { ++c_local; continue; }  // compute_costs.cuh:206-209
                     if (COLOR) {
@@ -689,7 +742,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                         double cd = ciede2000_ref(lo[0], lo[1], lo[2], lr[0], lr[1], lr[2]);
                         if (cd > a.color_thr) { ++c_local; continue; }  // compute_costs.cuh:231-234
                     }
-                    atomicOr(&mask[ref >> 5], 1u << (ref & 31));  // explained[pose][nn] = 1 (compute_costs.cuh:238,244,268)
+                    if (IDX_OK(ref >> 5, mask_words)) atomicOr(&mask[ref >> 5], 1u << (ref & 31));  // explained[pose][nn] = 1 (compute_costs.cuh:238,244,268)
                 }
             }
             __syncthreads();
@@ -830,6 +883,9 @@ __global__ void fill_keys_kernel(unsigned long long* keys, int n) {
 size_t pose_kernel_smem_bytes(const PoseArgs& a, bool image_mode, bool color) {
     size_t b = (size_t)a.tile_cap * ((color || image_mode) ? 8 : 4) + (image_mode ? 0 : (size_t)a.mask_words * 4) +
                (size_t)kQueueCap * 4;
+#ifdef PERCH_COST_SMEM_OBS
+    if (!image_mode) b += (size_t)PERCH_COST_SMEM_OBS * sizeof(float4) + 16;
+#endif
     return b + (size_t)kWarps * kPendCap * sizeof(int);
 }
 

@@ -18,6 +18,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <climits>
 #include <cstdio>
 #include <cstdlib>
 
@@ -135,7 +136,7 @@ __global__ void __launch_bounds__(kFullThreads) raster_quads_kernel(FullRasterAr
     unsigned long long* keys = a.keys + (a.single ? 0 : (size_t)pose_i * W * H);
     FragQueue& q = s_queue[tid >> 5];
     int cells[2] = {0, 0};  // bbox pixels of the lane's two triangles (0: nothing to draw, or deferred)
-    PixelRect rect[2];
+    PixelRect rect[2] = {{1, 0, 1, 0}, {1, 0, 1, 0}};
     TriSetup ts[2];
     uint32_t id[2] = {0, 0};
     if (qi < q_high) {
@@ -170,6 +171,23 @@ __global__ void __launch_bounds__(kFullThreads) raster_quads_kernel(FullRasterAr
             setup_edges(A, B, C, ts[j]);
             id[j] = a.key_pose_id ? (uint32_t)pose_i : (uint32_t)__ldg(a.models.cl_orig + t);
             cells[j] = (int)(n > 0x7fffffffLL ? 0x7fffffffLL : n);  // W*H <= 2^26 (perch_set_camera)
+        }
+    }
+    if (a.rect_min) {
+        // rectangle of key pixels this warp's triangles can touch (deferred ones included), image rows: H-1-r
+        int mnx = INT_MAX, mny = INT_MAX, mxx = INT_MIN, mxy = INT_MIN;
+#pragma unroll
+        for (int j = 0; j < 2; ++j)
+            if (qi < q_high && rect[j].x0 <= rect[j].x1 && rect[j].r0 <= rect[j].r1) {
+                mnx = min(mnx, rect[j].x0); mxx = max(mxx, rect[j].x1);
+                mny = min(mny, H - 1 - rect[j].r1); mxy = max(mxy, H - 1 - rect[j].r0);
+            }
+        mnx = __reduce_min_sync(0xffffffffu, mnx); mny = __reduce_min_sync(0xffffffffu, mny);
+        mxx = __reduce_max_sync(0xffffffffu, mxx); mxy = __reduce_max_sync(0xffffffffu, mxy);
+        if (lane == 0 && mnx <= mxx) {
+            const int r = a.single ? 0 : pose_i;
+            atomicMin(a.rect_min + 2 * r, mnx); atomicMin(a.rect_min + 2 * r + 1, mny);
+            atomicMax(a.rect_max + 2 * r, mxx); atomicMax(a.rect_max + 2 * r + 1, mxy);
         }
     }
     int count = 0;
@@ -300,7 +318,17 @@ __global__ void __launch_bounds__(256) resolve_full_kernel(FullRasterArgs a) {
         unsigned long long* keys = a.keys + (size_t)img * npx + i0;
         unsigned long long key[4] = {~0ull, ~0ull, ~0ull, ~0ull};
         const bool full = i0 + 3 < npx;
-        if (full && a.wide_stores) {  // npx % 4 == 0: 32-byte aligned group
+        // keys outside the rectangle the rasterising kernels touched for this pose are empty: not even read
+        bool touched = true;
+        if (a.rect_min) {
+            const int W = a.cam.width;
+            const int y0 = i0 / W, x0 = i0 - y0 * W, y1 = (i0 + 3) / W, x1 = x0 + 3;
+            const int rx0 = a.rect_min[2 * img], ry0 = a.rect_min[2 * img + 1], rx1 = a.rect_max[2 * img], ry1 = a.rect_max[2 * img + 1];
+            // a group that wraps into the next row (W % 4 != 0) is treated as spanning both rows and every column
+            touched = (y1 >= ry0 && y0 <= ry1) && (y0 != y1 || (x1 >= rx0 && x0 <= rx1));
+        }
+        if (!touched) {
+        } else if (full && a.wide_stores) {  // npx % 4 == 0: 32-byte aligned group
             const ulonglong2 k01 = *reinterpret_cast<const ulonglong2*>(keys);
             const ulonglong2 k23 = *reinterpret_cast<const ulonglong2*>(keys + 2);
             key[0] = k01.x; key[1] = k01.y; key[2] = k23.x; key[3] = k23.y;
@@ -455,6 +483,14 @@ cudaError_t full_raster_job(::perch_ctx* c, const FullJob& j, int* launches) {
         c->full_acc_n = 3 * (size_t)j.n_poses;
     }
     a.keys = c->d_full_keys;
+    if (c->full_rects_n < 4 * chunk) {
+        if (c->d_full_rects) cudaFree(c->d_full_rects);
+        c->d_full_rects = nullptr; c->full_rects_n = 0;
+        if ((e = cudaMalloc(&c->d_full_rects, 4 * sizeof(int) * chunk)) != cudaSuccess) return e;
+        c->full_rects_n = 4 * chunk;
+    }
+    a.rect_min = c->d_full_rects;
+    a.rect_max = c->d_full_rects + 2 * chunk;
     auto aligned = [](const void* p, uintptr_t m) { return (reinterpret_cast<uintptr_t>(p) & (m - 1)) == 0; };
     a.wide_stores = npx % 4 == 0 && aligned(j.img_depth, 16) && aligned(j.img_r, 4) && aligned(j.img_g, 4) && aligned(j.img_b, 4);
     for (size_t p0 = 0; p0 < (size_t)j.n_poses; p0 += chunk) {
@@ -471,6 +507,8 @@ cudaError_t full_raster_job(::perch_ctx* c, const FullJob& j, int* launches) {
         a.tree_clutter = j.tree_clutter ? j.tree_clutter + p0 : nullptr;
         a.tree_total = j.tree_total ? j.tree_total + p0 : nullptr;
         a.tree_acc = j.tree_total ? c->d_full_acc + 3 * p0 : nullptr;
+        if ((e = cudaMemsetAsync(a.rect_min, 0x7f, 2 * sizeof(int) * chunk, c->stream)) != cudaSuccess) return e;
+        if ((e = cudaMemsetAsync(a.rect_max, 0x80, 2 * sizeof(int) * chunk, c->stream)) != cudaSuccess) return e;
         if ((e = launch_full_raster(a, c->max_model_quads, c->stream)) == cudaSuccess) e = launch_full_resolve(a, n, c->stream);
         if (e != cudaSuccess) {
             cudaFree(c->d_full_keys);  // the keys may be dirty: start from a fresh, cleared buffer next time
