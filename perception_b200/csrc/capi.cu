@@ -479,6 +479,7 @@ int run_gicp(perch_ctx* c, const perch_params* p, const perch::PoseArgs& base, i
     ga.max_iterations = p->icp_max_iterations > 0 ? p->icp_max_iterations : 150;                     // renderer.cu:1696
     ga.rotation_epsilon = p->icp_rotation_epsilon >= 0.f ? p->icp_rotation_epsilon : 2e-3f;         // renderer.cu:1698
     ga.translation_epsilon = p->icp_transformation_epsilon >= 0.f ? p->icp_transformation_epsilon : 5e-4f;  // :1699
+    ga.warm_cells = (float)std::max(env_int("PERCH_GICP_WARM_CELLS", 1000000), 0);
     ga.stall_window = std::max(env_int("PERCH_GICP_STALL_WINDOW", 8), 0);  // 0 = off: iterate to the cap like fast_gicp
     if (c->n_obs == 0) ga.max_iterations = 0;  // no target: poses pass through unchanged
     cudaEvent_t e0, e1;

@@ -35,6 +35,17 @@ constexpr int kGicpThreads = PERCH_GICP_THREADS;
 constexpr int kGicpWarps = kGicpThreads / 32;
 constexpr int kMaxRings = 12;        // nearest-neighbour shells of the coarse grid searched before a linear scan
 constexpr int kFineRings = 6;        // shells of the fine grid searched before moving to the coarse one
+// Measured on the 233k-point scene cloud (tools/gicp_dense_probe.py, 4096 poses x 20 linearisations): rows per group
+// 1 / 2 / 4 / 8 -> 8.86 / 8.80 / 9.42 / 10.8 ms (pruning by the running best beats loads in flight); point loads per
+// round 2 / 4 / 8 -> 10.5 / 8.80 / 8.86 ms; 16 / 20 / 24 resident warps per SM (124 / 96 / 80 registers) -> 9.97 / 9.42 / 9.29 ms.
+#ifndef PERCH_GICP_BALL_ROWS
+#define PERCH_GICP_BALL_ROWS 2
+#endif
+constexpr int kBallRows = PERCH_GICP_BALL_ROWS;
+#ifndef PERCH_GICP_SCAN_UNROLL
+#define PERCH_GICP_SCAN_UNROLL 4
+#endif
+constexpr int kScanUnroll = PERCH_GICP_SCAN_UNROLL;  // point loads in flight per lane while scanning a grid run
 constexpr float kPlaneEps = 1e-3f;  // fast_gicp RegularizationMethod::PLANE: singular values (1, 1, 1e-3)
 
 // Eigenvector of the smallest eigenvalue of the symmetric matrix [a00 a01 a02; a01 a11 a12; a02 a12 a22]
@@ -108,6 +119,30 @@ __global__ void target_normals_kernel(const float* xyz_aos, const int* knn_index
     normals[3 * (size_t)i] = nn[0]; normals[3 * (size_t)i + 1] = nn[1]; normals[3 * (size_t)i + 2] = nn[2];
 }
 
+// Distance test of the grid points [b, e) of one x-run: four independent 16-byte loads in flight (a lane's search is a
+// chain of dependent latencies otherwise; profiles/r2_gicp_dense_v2.md: 55 % of the stall samples on this load).  The tail
+// re-reads point e - 1, which cannot change the result (strict `<`, equal distance only wins with a lower index).
+__device__ __forceinline__ void scan_run(const ObsGridDev& g, uint32_t b, uint32_t e, float qx, float qy, float qz, bool use_label,
+                                         int label, float& best, int& best_ref, float4& best_pt) {
+    for (uint32_t j = b; j < e; j += kScanUnroll) {
+        float4 p[kScanUnroll];
+        int lab[kScanUnroll];
+#pragma unroll
+        for (int u = 0; u < kScanUnroll; ++u) {
+            const uint32_t jj = min(j + u, e - 1);
+            p[u] = __ldg(g.pts + jj);
+            lab[u] = use_label ? __ldg(g.label + jj) : label;
+        }
+#pragma unroll
+        for (int u = 0; u < kScanUnroll; ++u) {
+            if (lab[u] != label) continue;
+            const float d = sqdist3(qx, qy, qz, p[u].x, p[u].y, p[u].z);
+            const int ref = __float_as_int(p[u].w);
+            if (d < best || (d == best && ref < best_ref)) { best = d; best_ref = ref; best_pt = p[u]; }
+        }
+    }
+}
+
 // Ring expansion over one uniform grid, carrying the best candidate in and out.  Returns true when the result is final:
 // the best squared distance is below the bound of the unvisited cells, or every ring of the grid has been visited.
 // Returns false after max_rings rings without that certainty.  Same distance arithmetic and tie-break (lowest reference
@@ -160,13 +195,7 @@ __device__ inline bool ring_search(const ObsGridDev& g, float h, int max_rings, 
                     while (xb >= xa && gyz + gap2(qx, g.ox, xb) > best * 1.0002f) --xb;
                     if (xa > xb) continue;
                     const uint32_t b = __ldg(g.cell_start + row + xa), e = __ldg(g.cell_start + row + xb + 1);
-                    for (uint32_t j = b; j < e; ++j) {
-                        if (use_label && __ldg(g.label + j) != label) continue;
-                        const float4 p = __ldg(g.pts + j);
-                        const float d = sqdist3(qx, qy, qz, p.x, p.y, p.z);
-                        const int ref = __float_as_int(p.w);
-                        if (d < best || (d == best && ref < best_ref)) { best = d; best_ref = ref; best_pt = p; }
-                    }
+                    scan_run(g, b, e, qx, qy, qz, use_label, label, best, best_ref, best_pt);
                 }
             }
         }
@@ -176,11 +205,6 @@ __device__ inline bool ring_search(const ObsGridDev& g, float h, int max_rings, 
     // the query lies outside the grid and c is the clamped cell); after rings 0..r-1 the unvisited cells have rho >= r,
     // hence the bound (r-1)*h used before visiting ring r.
 }
-
-#ifndef PERCH_GICP_WARM_CELLS
-#define PERCH_GICP_WARM_CELLS 3.0f
-#endif
-constexpr float kWarmCells = PERCH_GICP_WARM_CELLS;  // warm start when the previous correspondence is within this many cell widths
 
 // Exact nearest neighbour when a candidate within a few cell widths is already known (the correspondence of the previous
 // linearisation: poses move little between iterations): only the cells that intersect the ball of the candidate's distance
@@ -201,17 +225,21 @@ __device__ inline void ball_search(const ObsGridDev& g, float h, float qx, float
     };
     for (int z = z0; z <= z1; ++z) {
         const float gz = gap2(qz, g.oz, z);
-        for (int y = y0; y <= y1; ++y) {
-            if (gz + gap2(qy, g.oy, y) > best * 1.0002f) continue;
-            const int row = (z * g.dy + y) * g.dx;
-            const uint32_t b = __ldg(g.cell_start + row + x0), e = __ldg(g.cell_start + row + x1 + 1);
-            for (uint32_t j = b; j < e; ++j) {
-                if (use_label && __ldg(g.label + j) != label) continue;
-                const float4 p = __ldg(g.pts + j);
-                const float d = sqdist3(qx, qy, qz, p.x, p.y, p.z);
-                const int ref = __float_as_int(p.w);
-                if (d < best || (d == best && ref < best_ref)) { best = d; best_ref = ref; best_pt = p; }
+        if (gz > best * 1.0002f) continue;
+        // rows in groups of kBallRows: their range bounds are requested together, then scanned (a row pruned by a bound that
+        // an earlier row of its group would have tightened is scanned needlessly, never wrongly)
+        for (int yb = y0; yb <= y1; yb += kBallRows) {
+            uint32_t rb[kBallRows], re[kBallRows];
+#pragma unroll
+            for (int u = 0; u < kBallRows; ++u) {
+                const int y = yb + u;
+                const bool live = y <= y1 && !(gz + gap2(qy, g.oy, y) > best * 1.0002f);
+                const int row = (z * g.dy + min(y, y1)) * g.dx;
+                rb[u] = live ? __ldg(g.cell_start + row + x0) : 0u;
+                re[u] = live ? __ldg(g.cell_start + row + x1 + 1) : 0u;
             }
+#pragma unroll
+            for (int u = 0; u < kBallRows; ++u) scan_run(g, rb[u], re[u], qx, qy, qz, use_label, label, best, best_ref, best_pt);
         }
     }
 }
@@ -370,7 +398,7 @@ __global__ void pose_count_max_kernel(const int* pose_begin, int rows_per_pose, 
 }
 
 #ifndef PERCH_GICP_MIN_BLOCKS
-#define PERCH_GICP_MIN_BLOCKS 1
+#define PERCH_GICP_MIN_BLOCKS 20
 #endif
 __global__ void __launch_bounds__(kGicpThreads, PERCH_GICP_MIN_BLOCKS) gicp_kernel(GicpArgs a) {
     extern __shared__ __align__(16) unsigned char gicp_smem[];
@@ -465,7 +493,7 @@ __global__ void __launch_bounds__(kGicpThreads, PERCH_GICP_MIN_BLOCKS) gicp_kern
                     const int r0 = refs[i];
                     const float4 p0 = __ldg(a.tgt_sorted + r0);
                     const float d0 = sqdist3(px, py, pz, p0.x, p0.y, p0.z);
-                    if (d0 < a.grid_h * a.grid_h * kWarmCells * kWarmCells) {
+                    if (d0 < a.grid_h * a.grid_h * a.warm_cells * a.warm_cells) {
                         best = d0; ref = r0; b = p0;
                         ball_search(a.grid, a.grid_h, px, py, pz, use_label, label, best, ref, b);
                         warm = true;

@@ -244,6 +244,9 @@ struct GicpArgs {
     // linearisation point has not improved on its best value by stall_rel (relative) for stall_window consecutive
     // linearisations, the pose stops and returns the transform of that best linearisation.  stall_window = 0: off.
     int stall_window = 8;
+    // warm start of the nearest-neighbour search from the previous linearisation's correspondence when it lies within
+    // this many (fine) cell widths of the moved point; beyond it the search starts cold (PERCH_GICP_WARM_CELLS)
+    float warm_cells = 1e6f;
     float stall_rel = 1e-3f;
 };
 size_t gicp_smem_bytes(int smem_points);

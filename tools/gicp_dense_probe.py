@@ -21,6 +21,18 @@ ms = []
 for _ in range(3):
     g = r.gicp(wl["poses"], wl["pmm"], None, **args); ms.append(r.last_timing()[0])
 print("n_obs", dense["rendered_cloud_point_num"], "kernel ms", np.median(ms), "iterations", g["iterations"].mean())
+# warm-start radius (in fine cells) beyond which a search starts cold: PERCH_GICP_WARM_CELLS
+default_wc = os.environ.get("PERCH_GICP_WARM_CELLS")
+for wc in ([] if os.environ.get("PERCH_PROBE_NO_SWEEP") else (0, 3, 6, 12, 24, 48, 100000)):
+    os.environ["PERCH_GICP_WARM_CELLS"] = str(wc)
+    ms2 = []
+    for _ in range(3):
+        g2 = r.gicp(wl["poses"], wl["pmm"], None, **args); ms2.append(r.last_timing()[0])
+    print("warm cells", wc, "kernel ms", np.median(ms2), "same transforms", np.array_equal(g2["transforms"], g["transforms"]))
+if default_wc is None:
+    os.environ.pop("PERCH_GICP_WARM_CELLS", None)
+else:
+    os.environ["PERCH_GICP_WARM_CELLS"] = default_wc
 n = 256
 os.environ["PERCH_GICP_STREAM_MAX"] = str(1 << 30)
 t0 = time.time()
