@@ -463,7 +463,9 @@ def run_ours(args):
                     "how": "every scene is one blocking perch_score_scene call: pinned host poses -> H2D -> fused kernel -> "
                            "per-model top-k on the device -> ncclAllGather of the per-rank records (N > 1) -> D2H of costs, "
                            "counts and merged hits; `serial` = one context, `pipelined` = scenes alternate between "
-                           "`contexts` contexts, one host thread each; value = the faster of the two"},
+                           "`contexts` contexts, one host thread each; value = the faster of the two.  Pipelined scenes run on separate "
+                           "streams, so kernels of two scenes can share the GPU: where one scene does not fill it (C1: 2 000 CTAs = 1.7 "
+                           "waves) the pipelined rate can exceed `value`, which times the launches of ONE stream back to back"},
             "gpu_launches": args.steps * B,
             "roofline": rooflines(args, wl, P, kern_ms, clocks),
             "work": work,

@@ -266,7 +266,9 @@ int build_grid(perch_ctx* c, float res) {
 // The grid GICP searches: its nearest-neighbour queries have no distance gate and always complete rings 0 and 1
 // (27 cells), so on a dense cloud (a full-resolution scene: ~40 points per 1 cm cell) the cost grid makes every query
 // scan hundreds of points.  When the cost grid holds more than 8 points per non-empty cell a second grid is built with
-// cells sized for ~3 points each (points per cell of a surface scale with h^2); otherwise the cost grid is shared.
+// cells sized for ~6 points each (points per cell of a surface scale with h^2; measured optimum of the warp-wide warm
+// search on a 233k-point cloud: 1 / 2 / 3 / 5 / 8 / 12 points per cell -> 12.9 / 8.8 / 7.5 / 6.6 / 6.5 / 7.2 ms); otherwise the
+// cost grid is shared.
 int prepare_gicp_grid(perch_ctx* c) {
     if (c->gicp_grid_valid) return PERCH_OK;
     const float h_cost = c->grid.inv_h > 0.f ? 1.0f / c->grid.inv_h : 1.f;
@@ -275,7 +277,7 @@ int prepare_gicp_grid(perch_ctx* c) {
         c->gicp_grid = c->grid;
         c->gicp_grid_h = h_cost;
     } else {
-        const double target = std::max(1, env_int("PERCH_GICP_GRID_TARGET_X10", 30)) / 10.0;
+        const double target = std::max(1, env_int("PERCH_GICP_GRID_TARGET_X10", 60)) / 10.0;
         const float h = h_cost * (float)std::sqrt(target / c->grid_avg_per_cell);
         int rc = build_point_grid(c, h, 64.0 * 1024 * 1024, &c->d_ggrid_pts, &c->d_ggrid_label, &c->d_ggrid_cell_start,
                                   &c->gicp_grid, nullptr);

@@ -266,6 +266,102 @@ __device__ inline void nn_unbounded(const ObsGridDev& fine, float h_fine, const 
     }
 }
 
+// ball_search for all points of a pose at once, by one warp, with every lane busy.  A per-lane ball_search leaves most of
+// the warp idle: the queries of a round need very different numbers of rows and points (ncu, 233k-point cloud: 8 of 32
+// lanes active on average).  Here the search is a flat loop in which every lane performs ONE step per trip -- open the next
+// grid row of its ball, or test up to kScanUnroll points of the row it has open -- and a lane whose query is finished takes
+// the next unassigned point of the pose in the same trip, so the warp stays convergent and lanes run dry only at the very
+// end.  Per query the visiting order, the pruning rule and the arithmetic are ball_search's (rows pruned one at a time by
+// the running best), so refs[] is exactly what the per-lane search returns.  Points whose previous correspondence is -1
+// (no target point carries the label) are searched cold, by their lane alone.
+__device__ inline void warm_search_warp(const GicpArgs& a, const float* pts, int n, const float* R, const float* t, int* refs,
+                                        bool use_label, int label, int lane, int warp) {
+    const ObsGridDev& g = a.grid;
+    const float h = a.grid_h, slack = 1e-3f * h;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const int n_mine = (n - warp + kGicpWarps - 1) / kGicpWarps;  // this warp owns points warp, warp + kGicpWarps, ...
+    auto gap2 = [&](float q, float o, int i) {
+        const float lo = fmaf((float)i, h, o), d = fmaxf(fmaxf(lo - q, q - (lo + h)) - slack, 0.f);
+        return d * d;
+    };
+    int next = 0;  // warp-uniform: points handed out so far
+    bool active = false;
+    int i = 0, best_ref = -1;
+    float qx = 0.f, qy = 0.f, qz = 0.f, best = 0.f, gz = 0.f;
+    int x0 = 0, x1 = 0, y0 = 0, y1 = 0, z1 = 0, y = 0, z = 0;
+    uint32_t j = 0, e = 0;
+    for (;;) {
+        const unsigned idle = __ballot_sync(0xffffffffu, !active);
+        if (idle) {
+            const int my = next + __popc(idle & lt_mask);
+            next += __popc(idle);
+            if (!active && my < n_mine) {
+                i = warp + kGicpWarps * my;
+                const float ax = pts[3 * i], ay = pts[3 * i + 1], az = pts[3 * i + 2];
+                qx = R[0] * ax + R[1] * ay + R[2] * az + t[0];
+                qy = R[3] * ax + R[4] * ay + R[5] * az + t[1];
+                qz = R[6] * ax + R[7] * ay + R[8] * az + t[2];
+                const int r0 = refs[i];
+                if (r0 < 0) {
+                    float4 bp;
+                    nn_unbounded(a.grid, a.grid_h, a.coarse, a.coarse_h, qx, qy, qz, use_label, label, best, best_ref, bp);
+                    refs[i] = best_ref;
+                } else {
+                    const float4 p0 = __ldg(a.tgt_sorted + r0);
+                    best = sqdist3(qx, qy, qz, p0.x, p0.y, p0.z);
+                    best_ref = r0;
+                    const float r = sqrtf(best) * 1.0001f + slack;
+                    x0 = min(max((int)floorf((qx - r - g.ox) * g.inv_h), 0), g.dx - 1); x1 = min(max((int)floorf((qx + r - g.ox) * g.inv_h), 0), g.dx - 1);
+                    y0 = min(max((int)floorf((qy - r - g.oy) * g.inv_h), 0), g.dy - 1); y1 = min(max((int)floorf((qy + r - g.oy) * g.inv_h), 0), g.dy - 1);
+                    z = min(max((int)floorf((qz - r - g.oz) * g.inv_h), 0), g.dz - 1); z1 = min(max((int)floorf((qz + r - g.oz) * g.inv_h), 0), g.dz - 1);
+                    y = y0 - 1;
+                    gz = gap2(qz, g.oz, z);
+                    j = e = 0;
+                    active = true;
+                }
+            }
+        }
+        if (next >= n_mine && __ballot_sync(0xffffffffu, active) == 0u) break;
+        if (active && j >= e) {
+            // open the next row of the ball (one candidate per trip; a pruned row costs a trip without a load)
+            ++y;
+            if (y > y1) {
+                ++z;
+                y = y0;
+                if (z <= z1) gz = gap2(qz, g.oz, z);
+            }
+            if (z > z1) {
+                refs[i] = best_ref;
+                active = false;
+            } else if (gz > best * 1.0002f) {
+                y = y1;  // the whole slice is out of reach: the next trip moves on to z + 1
+            } else if (!(gz + gap2(qy, g.oy, y) > best * 1.0002f)) {
+                const int row = (z * g.dy + y) * g.dx;
+                j = __ldg(g.cell_start + row + x0);
+                e = __ldg(g.cell_start + row + x1 + 1);
+            }
+        }
+        if (active && j < e) {
+            float4 p[kScanUnroll];
+            int lab[kScanUnroll];
+#pragma unroll
+            for (int u = 0; u < kScanUnroll; ++u) {
+                const uint32_t jj = min(j + u, e - 1);
+                p[u] = __ldg(g.pts + jj);
+                lab[u] = use_label ? __ldg(g.label + jj) : label;
+            }
+#pragma unroll
+            for (int u = 0; u < kScanUnroll; ++u) {
+                if (lab[u] != label) continue;
+                const float d = sqdist3(qx, qy, qz, p[u].x, p[u].y, p[u].z);
+                const int ref = __float_as_int(p[u].w);
+                if (d < best || (d == best && ref < best_ref)) { best = d; best_ref = ref; }
+            }
+            j += kScanUnroll;
+        }
+    }
+}
+
 // The same search over a short contiguous range of the label-sorted cloud (a label's points in 6-DoF, the whole cloud
 // in 3-DoF): every lane streams the same points (one broadcast LDG.128 each), no divergence.  Ascending index with a
 // strict `<` keeps the lowest index on ties, so the result is identical to nn_unbounded's.
@@ -476,33 +572,49 @@ __global__ void __launch_bounds__(kGicpThreads, PERCH_GICP_MIN_BLOCKS) gicp_kern
         for (int i = 0; i < 9; ++i) R[i] = (float)s_T[i];
 #pragma unroll
         for (int i = 0; i < 3; ++i) t[i] = (float)s_T[9 + i];
+        // ---- phase 1: correspondences of this linearisation -> refs[] ------------------------------------------------
+        const bool flat = !stream_target && it > 0 && a.tgt_sorted != nullptr && a.warm_cells >= 1e5f;
+        if (flat) {
+            warm_search_warp(a, pts, n, R, t, refs, use_label, label, lane, warp);
+        } else {
+            for (int i = tid; i < n; i += kGicpThreads) {
+                const float ax = pts[3 * i], ay = pts[3 * i + 1], az = pts[3 * i + 2];
+                const float px = R[0] * ax + R[1] * ay + R[2] * az + t[0];
+                const float py = R[3] * ax + R[4] * ay + R[5] * az + t[1];
+                const float pz = R[6] * ax + R[7] * ay + R[8] * az + t[2];
+                float best; int ref; float4 b;
+                if (stream_target) nn_range(a.tgt_sorted, lb, le, px, py, pz, best, ref, b);
+                else {
+                    // warm start from the previous linearisation's correspondence when it is within warm_cells cell widths
+                    bool warm = false;
+                    if (it > 0 && refs[i] >= 0) {
+                        const int r0 = refs[i];
+                        const float4 p0 = __ldg(a.tgt_sorted + r0);
+                        const float d0 = sqdist3(px, py, pz, p0.x, p0.y, p0.z);
+                        if (d0 < a.grid_h * a.grid_h * a.warm_cells * a.warm_cells) {
+                            best = d0; ref = r0; b = p0;
+                            ball_search(a.grid, a.grid_h, px, py, pz, use_label, label, best, ref, b);
+                            warm = true;
+                        }
+                    }
+                    if (!warm) nn_unbounded(a.grid, a.grid_h, a.coarse, a.coarse_h, px, py, pz, use_label, label, best, ref, b);
+                }
+                refs[i] = ref;
+            }
+        }
+        __syncthreads();
+        // ---- phase 2: the 21 + 6 + 1 sums of the linearisation (fixed assignment of points to lanes, fixed order) ---------
         float acc[28];
 #pragma unroll
         for (int i = 0; i < 28; ++i) acc[i] = 0.f;
         for (int i = tid; i < n; i += kGicpThreads) {
+            const int ref = refs[i];
+            if (ref < 0) continue;  // no target point carries this label
             const float ax = pts[3 * i], ay = pts[3 * i + 1], az = pts[3 * i + 2];
             const float px = R[0] * ax + R[1] * ay + R[2] * az + t[0];
             const float py = R[3] * ax + R[4] * ay + R[5] * az + t[1];
             const float pz = R[6] * ax + R[7] * ay + R[8] * az + t[2];
-            float best; int ref; float4 b;
-            if (stream_target) nn_range(a.tgt_sorted, lb, le, px, py, pz, best, ref, b);
-            else {
-                // warm start from the previous linearisation's correspondence when it is within a cell width
-                bool warm = false;
-                if (it > 0 && refs[i] >= 0) {
-                    const int r0 = refs[i];
-                    const float4 p0 = __ldg(a.tgt_sorted + r0);
-                    const float d0 = sqdist3(px, py, pz, p0.x, p0.y, p0.z);
-                    if (d0 < a.grid_h * a.grid_h * a.warm_cells * a.warm_cells) {
-                        best = d0; ref = r0; b = p0;
-                        ball_search(a.grid, a.grid_h, px, py, pz, use_label, label, best, ref, b);
-                        warm = true;
-                    }
-                }
-                if (!warm) nn_unbounded(a.grid, a.grid_h, a.coarse, a.coarse_h, px, py, pz, use_label, label, best, ref, b);
-            }
-            refs[i] = ref;
-            if (ref < 0) continue;  // no target point carries this label
+            const float4 b = __ldg((a.tgt_sorted ? a.tgt_sorted : a.grid.pts) + ref);
             const float nax = nrm[3 * i], nay = nrm[3 * i + 1], naz = nrm[3 * i + 2];
             const float na[3] = {R[0] * nax + R[1] * nay + R[2] * naz, R[3] * nax + R[4] * nay + R[5] * naz,
                                  R[6] * nax + R[7] * nay + R[8] * naz};

@@ -63,6 +63,24 @@ def test_bench_workload_vs_oracle_and_unfused(name):
         r.close()
 
 
+@pytest.mark.parametrize("name", ["c2", "c5"])
+def test_scene_call_topk_at_full_size(name):
+    """perch_score_scene on the bench batches: C2's 16 384 poses are exactly what the select kernel keeps in registers
+    (every slot used), C5's 125 000 poses x 21 models take its streaming path; both must return what the caller's rule
+    (perch_topk, search_env.cpp:2542-2583) returns on the same costs."""
+    from perception_b200.renderer import topk
+    r, wl = bench.build_workload(name, 0, 0, None)
+    try:
+        n_models = len(wl["scene"].tris_model_count)
+        hits, costs = r.score_scene(wl["poses"], wl["pmm"], wl["plabel"], wl["tot"], n_models=n_models, k=8, **_kw(wl))
+        want = topk(costs["rendered_cost"], costs["observed_cost"], wl["pmm"], n_models, k=8)
+        assert np.array_equal(hits, want)
+        # (some models of C5 have no pose that passes the caller's |rendered - observed| < 30 gate: their rows are all pads)
+        assert (want["cost"][:, 0] < np.iinfo(np.int32).max).mean() > 0.5, "most models of the workload have a valid best pose"
+    finally:
+        r.close()
+
+
 def test_pose_labels_without_observed_labels_is_an_error_not_a_fault():
     """6-DoF call (pose labels) after set_observed(label=None): PERCH_ERR_INVALID, and the context stays usable."""
     from scenes import make_case, observed_3dof, poses_near_gt

@@ -33,6 +33,16 @@ if default_wc is None:
     os.environ.pop("PERCH_GICP_WARM_CELLS", None)
 else:
     os.environ["PERCH_GICP_WARM_CELLS"] = default_wc
+# points per cell (x10) of the finer grid GICP builds for dense clouds: PERCH_GICP_GRID_TARGET_X10 (read when the grid is built)
+for tgt in ([] if not os.environ.get("PERCH_PROBE_GRID_SWEEP") else (10, 20, 30, 50, 80, 120)):
+    os.environ["PERCH_GICP_GRID_TARGET_X10"] = str(tgt)
+    r.set_observed(dense["result_cloud_eigen"], dense["result_cloud_color"], None)
+    ms2 = []
+    for _ in range(4):
+        g2 = r.gicp(wl["poses"], wl["pmm"], None, **args); ms2.append(r.last_timing()[0])
+    print("grid target x10", tgt, "kernel ms", np.median(ms2[1:]), "same transforms", np.array_equal(g2["transforms"], g["transforms"]))
+os.environ.pop("PERCH_GICP_GRID_TARGET_X10", None)
+r.set_observed(dense["result_cloud_eigen"], dense["result_cloud_color"], None)
 n = 256
 os.environ["PERCH_GICP_STREAM_MAX"] = str(1 << 30)
 t0 = time.time()

@@ -14,19 +14,23 @@ ie, si = hdr.index("Instructions Executed"), hdr.index("# Samples")
 stall_cols = {h: i for i, h in enumerate(hdr) if h.startswith("stall_") and "Not Issued" not in h}
 inst = [(r[1], float(r[ie] or 0), float(r[si] or 0), {h: float(r[i] or 0) for h, i in stall_cols.items()}) for r in rows[2:] if len(r) > ie]
 tmp = tempfile.mkdtemp()
-subprocess.run(["cuobjdump", "-xelf", obj, os.path.join(root, "perception_b200/libperch_b200.so")], cwd=tmp, capture_output=True)
+subprocess.run(["cuobjdump", "-xelf", obj, os.environ.get("PERCH_LINES_LIB", os.path.join(root, "perception_b200/libperch_b200.so"))], cwd=tmp, capture_output=True)
 cub = [f for f in os.listdir(tmp) if f.endswith(".cubin")][0]
 dis = subprocess.run(["nvdisasm", "--print-line-info", os.path.join(tmp, cub)], capture_output=True, text=True).stdout
 # split per function
 want_mode = re.search(r"\(int\)(\d), \(bool\)(\d)", ksub)
 mangled = f"ILi{want_mode.group(1)}ELb{want_mode.group(2)}E" if want_mode else ksub
-lines, cur, on = [], None, False
+# every function whose mangled name matches; the profiled one is recognised by its instruction count (a substring such as
+# "pose_kernel" matches all template instantiations: joining the wrong one misattributes every line)
+funcs, cur, name = collections.OrderedDict(), None, None
 for l in dis.splitlines():
     m = re.match(r"\s*\.text\.(\S+):", l) or re.match(r"\s*\.section\s+\.text\.(\S+),", l)
     if m:
-        on = mangled in m.group(1)
+        name = m.group(1).split(",")[0] if mangled in m.group(1) else None
+        if name:
+            funcs.setdefault(name, [])
         continue
-    if not on:
+    if not name:
         continue
     m = re.search(r"//## File \"([^\"]+)\", line (\d+)(.*)", l)
     if m:
@@ -35,9 +39,13 @@ for l in dis.splitlines():
         continue
     m = re.match(r"\s*/\*([0-9a-f]{4,})\*/\s+(.*?);", l)
     if m:
-        lines.append((cur, m.group(2)))
-if len(lines) != len(inst):
-    print(f"warning: {len(lines)} disassembled vs {len(inst)} profiled instructions", file=sys.stderr)
+        funcs[name].append((cur, m.group(2)))
+match = [n for n, v in funcs.items() if len(v) == len(inst)]
+if len(match) != 1:
+    sys.exit(f"error: no unique function with {len(inst)} instructions among {[(n[-40:], len(v)) for n, v in funcs.items()]}: "
+             "the library on disk is not the build that was profiled (PERCH_LINES_LIB=path of the right one)")
+lines = funcs[match[0]]
+print(f"function {match[0]} ({len(lines)} instructions)")
 tot_i = sum(a for _, a, _, _ in inst); tot_s = sum(s for _, _, s, _ in inst)
 agg = collections.OrderedDict()
 for (loc, _), (_, a, s, st) in zip(lines, inst):
