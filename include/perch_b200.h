@@ -289,7 +289,9 @@ int perch_topk(const float* rendered_cost, const float* observed_cost, const int
  * pose_id_offset = global id of this call's first pose (the rank's block offset).  out (may be NULL) receives this
  * rank's rendered_cost / observed_cost / points_diff_cost / counts as in perch_render_cost; the other fields are ignored.
  * Limits: n_models <= 255, n_poses <= 2^24 per call, do_icp = 0.  Every rank of a communicator must make the call (an
- * empty block is fine: n_poses = 0). */
+ * empty block is fine: n_poses = 0) with the same n_models and k; like any collective, a rank whose call fails validation
+ * before the gather leaves the others waiting in it -- validate the scene-level arguments (n_models, k, params) once,
+ * before the ranks split the pose list. */
 int perch_score_scene(perch_ctx* ctx, const float* poses16, int n_poses, const int* pose_model_map,
                       const int* pose_segmentation_label, const float* pose_observed_points_total,
                       const perch_params* params, int pose_id_offset, int n_models, int k, perch_outputs* out,
