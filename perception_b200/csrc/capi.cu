@@ -366,6 +366,15 @@ int prepare_target_normals(perch_ctx* c, int k) {
     const int n = c->n_obs;
     if (n == 0 || c->tgt_normals_k == k) return PERCH_OK;
     int rc;
+    // k = 10 (the reference's value): ring search through GICP's own grid, on the device (gicp.cu).  Other k, or
+    // PERCH_GICP_NORMALS_BRUTE=1 (A/B tests): the N x N k-NN kernel on a host-transposed copy of the cloud.
+    if (k == 10 && c->d_obs_xyz4 && !env_int("PERCH_GICP_NORMALS_BRUTE", 0)) {
+        if ((rc = prepare_gicp_grid(c))) return rc;
+        if ((rc = upload<float>(&c->d_tgt_normals, nullptr, 3 * (size_t)n, c->stream))) return rc;
+        CU(perch::launch_target_normals_grid(c->gicp_grid, c->gicp_grid_h, c->d_obs_xyz4, n, c->d_tgt_normals, c->stream));
+        c->tgt_normals_k = k;
+        return PERCH_OK;
+    }
     if ((rc = perch_detail::ensure_obs_host(c))) return rc;
     if ((rc = upload(&c->d_obs_xyz_aos, c->h_obs_xyz.data(), 3 * (size_t)n, c->stream))) return rc;
     if ((rc = upload<float>(&c->d_tgt_normals, nullptr, 3 * (size_t)n, c->stream))) return rc;

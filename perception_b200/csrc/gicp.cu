@@ -107,6 +107,26 @@ __device__ inline void normal_from_neighbours(const float* xyz_aos, const int* n
     smallest_eigenvector<float>(c00 * inv, c01 * inv, c02 * inv, c11 * inv, c12 * inv, c22 * inv, n);
 }
 
+// the same on the float4 cloud (x, y, z, .): identical operations in identical order
+__device__ inline void normal_from_neighbours4(const float4* xyz4, const int* nbr, int count, float n[3]) {
+    n[0] = n[1] = n[2] = 0.f;
+    if (count < 3) return;
+    float mx = 0, my = 0, mz = 0;
+    for (int j = 0; j < count; ++j) {
+        const float4 p = __ldg(xyz4 + nbr[j]);
+        mx += p.x; my += p.y; mz += p.z;
+    }
+    const float inv = 1.0f / (float)count;
+    mx *= inv; my *= inv; mz *= inv;
+    float c00 = 0, c01 = 0, c02 = 0, c11 = 0, c12 = 0, c22 = 0;
+    for (int j = 0; j < count; ++j) {
+        const float4 p = __ldg(xyz4 + nbr[j]);
+        const float x = p.x - mx, y = p.y - my, z = p.z - mz;
+        c00 += x * x; c01 += x * y; c02 += x * z; c11 += y * y; c12 += y * z; c22 += z * z;
+    }
+    smallest_eigenvector<float>(c00 * inv, c01 * inv, c02 * inv, c11 * inv, c12 * inv, c22 * inv, n);
+}
+
 // ---- target normals: neighbours come from launch_knn (k x N index matrix) -------------------------------------------
 __global__ void target_normals_kernel(const float* xyz_aos, const int* knn_index, int n, int k, float* normals) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -116,6 +136,96 @@ __global__ void target_normals_kernel(const float* xyz_aos, const int* knn_index
     for (int j = 0; j < kk; ++j) nbr[j] = knn_index[(size_t)j * n + i];
     float nn[3];
     normal_from_neighbours(xyz_aos, nbr, kk, nn);
+    normals[3 * (size_t)i] = nn[0]; normals[3 * (size_t)i + 1] = nn[1]; normals[3 * (size_t)i + 2] = nn[2];
+}
+
+// ---- target normals through the search grid (k = 10, the reference's hard-coded value) --------------------------------
+// The same K nearest neighbours as the brute-force k-NN above finds -- ascending (squared distance, index), the point
+// itself included, labels ignored -- but gathered by ring expansion around the point's cell, so a 300k-point scene cloud
+// costs milliseconds instead of the ~80 ms of an N x N scan and never leaves the device.  The K best live in registers;
+// insertion compares (distance, index) explicitly, so the list does not depend on the order cells are visited in.
+// After ring r the unvisited points are at least r * h away: the search stops once the K-th distance is below that.  A
+// point whose neighbourhood is still incomplete after kNormalRings rings (an isolated point) starts over with a linear
+// scan of the cloud -- same result, rare.
+constexpr int kNormalRings = 8;
+
+template <int K>
+struct KBest {
+    float bd[K];
+    int bi[K];
+    __device__ void clear() {
+#pragma unroll
+        for (int s = 0; s < K; ++s) { bd[s] = FLT_MAX; bi[s] = 0x7fffffff; }
+    }
+    __device__ void offer(float d, int j) {
+        if (d > bd[K - 1] || (d == bd[K - 1] && j >= bi[K - 1])) return;
+#pragma unroll
+        for (int s = K - 1; s > 0; --s) {
+            const bool shift = bd[s - 1] > d || (bd[s - 1] == d && bi[s - 1] > j);   // slot s-1 is worse than (d, j)
+            const bool here = !shift && (bd[s] > d || (bd[s] == d && bi[s] > j));   // first slot from the left that is worse
+            const float nd = shift ? bd[s - 1] : (here ? d : bd[s]);
+            const int ni = shift ? bi[s - 1] : (here ? j : bi[s]);
+            bd[s] = nd; bi[s] = ni;
+        }
+        if (bd[0] > d || (bd[0] == d && bi[0] > j)) { bd[0] = d; bi[0] = j; }
+    }
+};
+
+template <int K>
+__global__ void target_normals_grid_kernel(ObsGridDev g, float h, const float4* __restrict__ pts_sorted, int n, float* normals) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 q = __ldg(pts_sorted + i);
+    KBest<K> kb;
+    kb.clear();
+    const int cx = min(max((int)floorf((q.x - g.ox) * g.inv_h), 0), g.dx - 1);
+    const int cy = min(max((int)floorf((q.y - g.oy) * g.inv_h), 0), g.dy - 1);
+    const int cz = min(max((int)floorf((q.z - g.oz) * g.inv_h), 0), g.dz - 1);
+    const int rmax = max(max(max(cx, g.dx - 1 - cx), max(cy, g.dy - 1 - cy)), max(cz, g.dz - 1 - cz));
+    bool done = false;
+    for (int r = 0; r <= min(rmax, kNormalRings) && !done; ++r) {
+        const int z0 = max(cz - r, 0), z1 = min(cz + r, g.dz - 1);
+        const int y0 = max(cy - r, 0), y1 = min(cy + r, g.dy - 1);
+        for (int z = z0; z <= z1; ++z) {
+            const bool zface = (z == cz - r) || (z == cz + r);
+            for (int y = y0; y <= y1; ++y) {
+                const bool face = zface || (y == cy - r) || (y == cy + r);
+                const int row = (z * g.dy + y) * g.dx;
+                for (int part = 0; part < 2; ++part) {
+                    int xa, xb;
+                    if (face) { if (part) break; xa = max(cx - r, 0); xb = min(cx + r, g.dx - 1); }
+                    else {
+                        if (r == 0) break;
+                        xa = xb = part ? cx + r : cx - r;
+                        if (xa < 0 || xa > g.dx - 1) continue;
+                    }
+                    const uint32_t b = __ldg(g.cell_start + row + xa), e = __ldg(g.cell_start + row + xb + 1);
+                    for (uint32_t j = b; j < e; ++j) {
+                        const float4 p = __ldg(g.pts + j);
+                        kb.offer(sqdist3(q.x, q.y, q.z, p.x, p.y, p.z), __float_as_int(p.w));
+                    }
+                }
+            }
+        }
+        // rings 0..r complete: every unvisited point is at least r * h away (ring_search's bound, one ring later)
+        const float lim = (float)r * h;
+        done = (kb.bi[K - 1] != 0x7fffffff && kb.bd[K - 1] < lim * lim * 0.9999f) || r == rmax;
+    }
+    if (!done) {
+        kb.clear();
+        for (int j = 0; j < n; ++j) {
+            const float4 p = __ldg(pts_sorted + j);
+            kb.offer(sqdist3(q.x, q.y, q.z, p.x, p.y, p.z), j);
+        }
+    }
+    int nbr[K], cnt = 0;
+#pragma unroll
+    for (int s = 0; s < K; ++s) {
+        nbr[s] = kb.bi[s];
+        cnt += kb.bi[s] != 0x7fffffff;
+    }
+    float nn[3];
+    normal_from_neighbours4(pts_sorted, nbr, cnt, nn);
     normals[3 * (size_t)i] = nn[0]; normals[3 * (size_t)i + 1] = nn[1]; normals[3 * (size_t)i + 2] = nn[2];
 }
 
@@ -802,6 +912,13 @@ cudaError_t launch_target_normals(const float* d_xyz_aos, const int* d_knn_index
                                   cudaStream_t stream) {
     if (n <= 0) return cudaSuccess;
     target_normals_kernel<<<(n + 127) / 128, 128, 0, stream>>>(d_xyz_aos, d_knn_index, n, k, d_normals);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_target_normals_grid(const ObsGridDev& grid, float cell, const float4* d_pts_sorted, int n, float* d_normals,
+                                       cudaStream_t stream) {
+    if (n <= 0) return cudaSuccess;
+    target_normals_grid_kernel<10><<<(n + 127) / 128, 128, 0, stream>>>(grid, cell, d_pts_sorted, n, d_normals);
     return cudaGetLastError();
 }
 

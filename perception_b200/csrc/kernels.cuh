@@ -254,6 +254,9 @@ cudaError_t launch_gicp(const GicpArgs& a, int n_poses, cudaStream_t stream);
 // normals (direction of least variance of the k nearest neighbours, launch_knn's k x n index matrix) of a cloud
 cudaError_t launch_target_normals(const float* d_xyz_aos, const int* d_knn_index, int n, int k, float* d_normals,
                                   cudaStream_t stream);
+// k = 10 through the search grid (same neighbours, same order as the brute-force k-NN; nothing visits the host)
+cudaError_t launch_target_normals_grid(const ObsGridDev& grid, float cell, const float4* d_pts_sorted, int n, float* d_normals,
+                                       cudaStream_t stream);
 // max over poses of the per-pose point count (pose_begin as above) -> *d_out (must be zeroed)
 cudaError_t launch_pose_count_max(const int* d_pose_begin, int rows_per_pose, int n_poses, int* d_out, cudaStream_t stream);
 

@@ -236,9 +236,12 @@ def test_gicp_dense_scene_cloud_grids_agree(orc, monkeypatch):
     poses = np.concatenate([poses, far[None]])
     pmm = np.concatenate([pmm, pmm[5:6]])
     outs = []
-    for density, target in (("8", "30"), ("1000000", "30"), ("8", "3")):
+    # last entry: target normals from the N x N k-NN kernel instead of the ring search through the grid (same 10 neighbours
+    # in the same order => bit-identical normals => identical poses)
+    for density, target, brute in (("8", "60", "0"), ("1000000", "60", "0"), ("8", "3", "0"), ("8", "60", "1"), ("8", "200", "0")):
         monkeypatch.setenv("PERCH_GICP_GRID_DENSITY", density)
         monkeypatch.setenv("PERCH_GICP_GRID_TARGET_X10", target)
+        monkeypatch.setenv("PERCH_GICP_NORMALS_BRUTE", brute)
         with Renderer(0) as r:
             r.set_camera(case.width, case.height, case.proj, *cam)
             r.set_models(s.tris, s.tris_model_count)
