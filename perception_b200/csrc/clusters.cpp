@@ -5,6 +5,7 @@
 #include <cstring>
 #include <limits>
 #include <numeric>
+#include <thread>
 #include <unordered_map>
 
 namespace perch {
@@ -80,17 +81,12 @@ void enclosing_ball(const double (*pts)[3], int np, float out4[4]) {
 }  // namespace
 
 ClusterSet build_clusters(const float* tri9, const std::vector<int>& low, const std::vector<int>& high) {
-    ClusterSet out;
     const int n_models = (int)low.size();
-    out.model_low.resize(n_models);
-    out.model_high.resize(n_models);
-    for (int m = 0; m < n_models; ++m) {
+    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    // one model: triangles paired into quads, quads into clusters, records written (bounding spheres: pass 4 below)
+    auto build_one = [&](int m, ClusterSet& out) {
         const int t0 = low[m], nt = high[m] - low[m];
-        out.model_low[m] = (int)(out.bounds.size() / 4);
-        if (nt <= 0) {
-            out.model_high[m] = out.model_low[m];
-            continue;
-        }
+        if (nt <= 0) return;
         const float* T9 = tri9 + (size_t)t0 * 9;
         float mn[3] = {INFINITY, INFINITY, INFINITY}, mx[3] = {-INFINITY, -INFINITY, -INFINITY};
         for (int t = 0; t < nt; ++t)
@@ -294,7 +290,6 @@ ClusterSet build_clusters(const float* tri9, const std::vector<int>& low, const 
             const Unit& qb = units[second >= 0 ? second : seed];
             const size_t rec = out.recs.size();
             out.recs.resize(rec + kClusterFloats);
-            double pts[kQuadVerts * kClusterQuads][3];
             uint32_t perm = 0;
             for (int q = 0; q < kClusterQuads; ++q) {
                 const Unit& u = q ? qb : qa;
@@ -302,7 +297,6 @@ ClusterSet build_clusters(const float* tri9, const std::vector<int>& low, const 
                     for (int a = 0; a < 3; ++a) {
                         const float p = u.v[i][a];
                         out.recs[rec + (size_t)q * kQuadFloats + 3 * i + a] = p;
-                        pts[q * kQuadVerts + i][a] = p;
                     }
                 const bool repeat = q == 1 && second < 0;
                 for (int j = 0; j < 2; ++j) {
@@ -312,19 +306,58 @@ ClusterSet build_clusters(const float* tri9, const std::vector<int>& low, const 
                 }
             }
             out.perm.push_back(perm);
-            float ball[4];
-            enclosing_ball(pts, kQuadVerts * kClusterQuads, ball);
-            const float cx = ball[0], cy = ball[1], cz = ball[2], rad = ball[3];
-            for (int q = 0; q < kClusterQuads; ++q) {
-                float qb[4];
-                enclosing_ball(pts + q * kQuadVerts, kQuadVerts, qb);
-                // a quad slot without a triangle of its own repeats the cluster's first quad: harmless (level 2 drops
-                // invalid slots) and keeps level 1 free of a special case
-                out.qbounds.insert(out.qbounds.end(), {qb[0], qb[1], qb[2], qb[3]});
-            }
-            out.bounds.insert(out.bounds.end(), {cx, cy, cz, rad});
+            // bounding spheres: filled in by the parallel pass below (they are 90 % of this function's time)
+            out.qbounds.resize(out.qbounds.size() + 4 * kClusterQuads, 0.f);
+            out.bounds.resize(out.bounds.size() + 4, 0.f);
         }
+    };
+    // models are independent: filed by a pool of threads, concatenated in model order (same result as one after another)
+    std::vector<ClusterSet> parts(n_models);
+    {
+        const int n_thr = (int)std::min<size_t>(std::min<unsigned>(hw, 16), (size_t)n_models);
+        if (n_thr <= 1) {
+            for (int m = 0; m < n_models; ++m) build_one(m, parts[m]);
+        } else {
+            std::vector<std::thread> pool;
+            for (int i = 0; i < n_thr; ++i)
+                pool.emplace_back([&, i] { for (int m = i; m < n_models; m += n_thr) build_one(m, parts[m]); });
+            for (auto& th : pool) th.join();
+        }
+    }
+    ClusterSet out;
+    out.model_low.resize(n_models);
+    out.model_high.resize(n_models);
+    for (int m = 0; m < n_models; ++m) {
+        ClusterSet& pm = parts[m];
+        out.model_low[m] = (int)(out.bounds.size() / 4);
+        out.recs.insert(out.recs.end(), pm.recs.begin(), pm.recs.end());
+        out.orig.insert(out.orig.end(), pm.orig.begin(), pm.orig.end());
+        out.perm.insert(out.perm.end(), pm.perm.begin(), pm.perm.end());
+        out.bounds.insert(out.bounds.end(), pm.bounds.begin(), pm.bounds.end());
+        out.qbounds.insert(out.qbounds.end(), pm.qbounds.begin(), pm.qbounds.end());
         out.model_high[m] = (int)(out.bounds.size() / 4);
+        pm = ClusterSet();
+    }
+    // ---- 4. bounding spheres of every cluster and of its quads, from the records (threads over cluster ranges; each
+    // sphere depends on its own record only, so the result does not depend on the thread count) -----------------------
+    const size_t n_clusters = out.bounds.size() / 4;
+    auto balls = [&](size_t c0, size_t c1) {
+        for (size_t c = c0; c < c1; ++c) {
+            double pts[kQuadVerts * kClusterQuads][3];
+            for (int i = 0; i < kQuadVerts * kClusterQuads; ++i)
+                for (int a = 0; a < 3; ++a) pts[i][a] = out.recs[c * kClusterFloats + 3 * (size_t)i + a];
+            enclosing_ball(pts, kQuadVerts * kClusterQuads, &out.bounds[4 * c]);
+            // a quad slot without a triangle of its own repeats the cluster's first quad (its record does): harmless (level
+            // 2 drops invalid slots) and keeps level 1 free of a special case
+            for (int q = 0; q < kClusterQuads; ++q) enclosing_ball(pts + q * kQuadVerts, kQuadVerts, &out.qbounds[4 * (kClusterQuads * c + q)]);
+        }
+    };
+    const size_t n_thr = std::min<size_t>(std::min<size_t>(hw, 16), n_clusters / 512 + 1);
+    if (n_thr <= 1) balls(0, n_clusters);
+    else {
+        std::vector<std::thread> pool;
+        for (size_t i = 0; i < n_thr; ++i) pool.emplace_back(balls, n_clusters * i / n_thr, n_clusters * (i + 1) / n_thr);
+        for (auto& th : pool) th.join();
     }
     return out;
 }

@@ -65,6 +65,8 @@ struct StatesCtx;  // capi_states.cu
 }  // namespace perch
 
 struct perch_ctx {
+    // 128-bit digest of the last perch_set_models input (triangles + counts): an identical call returns at once
+    uint64_t models_digest[2] = {0, 0};
     int device = 0;
     int sm_count = 0;
     int max_smem_optin = 0;
