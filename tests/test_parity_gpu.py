@@ -601,3 +601,33 @@ def test_observed_order_within_a_label_does_not_change_counts(orc):
         assert np.array_equal(o["counts"], outs[0]["counts"])
         for k in ("rendered_cost", "observed_cost", "points_diff_cost"):
             assert np.array_equal(o[k], outs[0][k], equal_nan=True), k
+
+
+@pytest.mark.gpu
+def test_set_models_is_idempotent_and_notices_changes(orc):
+    """The reference passes the meshes with every render call (renderer.cu:1532-1544), so the drop-in backend calls
+    perch_set_models every time: an unchanged mesh set must be recognised (digest) and left in place, a changed one of
+    the same size must be re-filed -- one moved vertex is enough to change the result."""
+    import time
+    case, obs, poses, pmm, lab, tot = _cost_case(orc, 5000, 8, True, 24)
+    s = case.scene
+    kw = dict(stride=8, cost_type=2, sensor_resolution=0.01)
+    moved = s.tris.copy()
+    big = int(np.argmax(s.tris_model_count))
+    lo = int(np.sum(s.tris_model_count[:big]))
+    moved["v"][lo:lo + int(s.tris_model_count[big]), 0, :] += np.float32(0.02)   # first vertex of every triangle of one model: 2 cm
+    with make_renderer(case, with_label=True) as r:
+        r.set_observed(obs["aos"], obs["rgb"], obs["label"])
+        a = r.render_cuda_multi_unified("COST", poses, pmm, lab, tot, **kw)
+        t0 = time.perf_counter(); r.set_models(s.tris, s.tris_model_count); t_same = time.perf_counter() - t0
+        a2 = r.render_cuda_multi_unified("COST", poses, pmm, lab, tot, **kw)
+        t0 = time.perf_counter(); r.set_models(moved, s.tris_model_count); t_new = time.perf_counter() - t0
+        b = r.render_cuda_multi_unified("COST", poses, pmm, lab, tot, **kw)
+    with make_renderer(case, with_label=True) as r:
+        r.set_models(moved, s.tris_model_count)
+        r.set_observed(obs["aos"], obs["rgb"], obs["label"])
+        b_fresh = r.render_cuda_multi_unified("COST", poses, pmm, lab, tot, **kw)
+    assert np.array_equal(a["counts"], a2["counts"])
+    assert np.array_equal(b["counts"], b_fresh["counts"]) and np.array_equal(b["rendered_cost"], b_fresh["rendered_cost"])
+    assert not np.array_equal(a["counts"], b["counts"]), "the moved mesh must score differently"
+    assert t_same < t_new, (t_same, t_new)
