@@ -276,13 +276,40 @@ int prepare_gicp_grid(perch_ctx* c) {
     if (c->n_obs == 0 || c->grid_avg_per_cell <= dense) {
         c->gicp_grid = c->grid;
         c->gicp_grid_h = h_cost;
+        c->gicp_grid_avg = c->grid_avg_per_cell;
     } else {
         const double target = std::max(1, env_int("PERCH_GICP_GRID_TARGET_X10", 60)) / 10.0;
         const float h = h_cost * (float)std::sqrt(target / c->grid_avg_per_cell);
         int rc = build_point_grid(c, h, 64.0 * 1024 * 1024, &c->d_ggrid_pts, &c->d_ggrid_label, &c->d_ggrid_cell_start,
-                                  &c->gicp_grid, nullptr);
+                                  &c->gicp_grid, &c->gicp_grid_avg);
         if (rc) return rc;
         c->gicp_grid_h = 1.0f / c->gicp_grid.inv_h;
+    }
+    // pyramid: cells doubling per level until a level has at most two cells per axis (gicp.cu: pyramid_search_warp)
+    c->gicp_n_levels = 0;
+    // Built for sparse targets only (the cost grid doubles as level 0): there a far query opens hundreds of near-empty rows
+    // on the finest grid (C1's label cloud: 47 -> 25 ms per 2 000 poses x 20).  On a dense cloud with its own fine grid the
+    // coarser levels' cells hold too many points to pay (233k points: 6.5 ms without, 6.8-7.1 ms with): PERCH_GICP_PYRAMID=2
+    // forces it on, 0 off.
+    const int pyramid = env_int("PERCH_GICP_PYRAMID", 1);
+    if (c->n_obs > 0 && (pyramid == 2 || (pyramid == 1 && c->gicp_grid.pts == c->grid.pts))) {
+        std::vector<perch::ObsGridDev> lv{c->gicp_grid};
+        float h = c->gicp_grid_h;
+        while ((int)lv.size() < perch_ctx::kGicpMaxLevels && std::max(lv.back().dx, std::max(lv.back().dy, lv.back().dz)) > 3) {
+            h *= 2.f;
+            const int l = (int)lv.size();
+            perch::ObsGridDev g;
+            int rc = build_point_grid(c, h, 64.0 * 1024 * 1024, &c->d_lvl_pts[l], &c->d_lvl_label[l], &c->d_lvl_cell_start[l], &g, nullptr);
+            if (rc) return rc;
+            h = 1.0f / g.inv_h;
+            lv.push_back(g);
+        }
+        cudaFree(c->d_gicp_levels);
+        c->d_gicp_levels = nullptr;
+        CU(cudaMalloc(&c->d_gicp_levels, lv.size() * sizeof(perch::ObsGridDev)));
+        CU(cudaMemcpyAsync(c->d_gicp_levels, lv.data(), lv.size() * sizeof(perch::ObsGridDev), cudaMemcpyHostToDevice, c->stream));
+        CU(cudaStreamSynchronize(c->stream));
+        c->gicp_n_levels = (int)lv.size();
     }
     c->gicp_grid_valid = true;
     return PERCH_OK;
@@ -470,6 +497,9 @@ int run_gicp(perch_ctx* c, const perch_params* p, const perch::PoseArgs& base, i
     if ((rc = prepare_gicp_grid(c))) return rc;
     ga.grid = c->gicp_grid;
     ga.grid_h = c->gicp_grid_h;
+    ga.levels = c->gicp_n_levels > 1 ? c->d_gicp_levels : nullptr;
+    ga.n_levels = c->gicp_n_levels;
+    ga.level_k = (float)(env_int("PERCH_GICP_LEVEL_KAPPA_X10", 40) / 10.0 * c->gicp_grid_h * c->gicp_grid_h / std::max(c->gicp_grid_avg, 1.0));
     ga.coarse = c->grid;
     ga.coarse_h = c->grid.inv_h > 0.f ? 1.0f / c->grid.inv_h : 1.f;
     ga.tgt_normals = c->d_tgt_normals;
@@ -483,8 +513,12 @@ int run_gicp(perch_ctx* c, const perch_params* p, const perch::PoseArgs& base, i
     ga.out_transforms = d_transforms;
     ga.out_iterations = d_iterations;
     ga.out_error = d_error;
-    // shared memory for the largest pose cloud (rounded up), capped so that at least two CTAs fit an SM
-    const int cap_pts = (int)std::min<size_t>(((size_t)c->max_smem_optin / 2 - 2048) / 28, 4096);
+    // Shared memory for the largest pose cloud (rounded up), but never more than lets the register-limited 20 one-warp
+    // CTAs share an SM (28 B per point => 384 points): the kernel is latency-bound and lives on resident warps; a pose
+    // with more points keeps its arrays in global memory (L1 / L2) instead.  (C1, 626 points per pose on average, 1 216 at
+    // most: 34 KB per CTA left 6 warps per SM -- ncu sm__warps_active 6.9 % -- and cost 46 ms per 2 000 poses x 20.)
+    const int cap_pts = std::min((int)std::min<size_t>(((size_t)c->max_smem_optin / 2 - 2048) / 28, 4096),
+                                 std::max(env_int("PERCH_GICP_SMEM_POINTS", 384), 64));
     ga.smem_points = std::min(std::max((max_n + 63) & ~63, 64), cap_pts);
     ga.k_correspondences = k;
     ga.max_iterations = p->icp_max_iterations > 0 ? p->icp_max_iterations : 150;                     // renderer.cu:1696
@@ -581,10 +615,13 @@ void perch_destroy(perch_ctx* c) {
     if (!c) return;
     DeviceGuard g(c->device);
     cudaStreamSynchronize(c->stream);
+    for (int l = 0; l < perch_ctx::kGicpMaxLevels; ++l) {
+        cudaFree(c->d_lvl_pts[l]); cudaFree(c->d_lvl_label[l]); cudaFree(c->d_lvl_cell_start[l]);
+    }
     void* ptrs[] = {c->d_tri_color, c->d_model_low, c->d_model_high, c->d_model_aabb, c->d_model_qrmax, c->d_tri_lab, c->d_cl_recs, c->d_cl_bounds, c->d_q_bounds,
                     c->d_cl_orig, c->d_cl_perm, c->d_cl_low, c->d_cl_high,
                     c->d_src_depth, c->d_src_label, c->d_src_rgb, c->d_grid_pts, c->d_grid_label, c->d_cell_start,
-                    c->d_icp_grid_pts, c->d_icp_grid_label, c->d_icp_grid_cells, c->d_cmp_depth, c->d_cmp_label, c->d_full_keys, c->d_full_big, c->d_full_count, c->d_full_acc, c->d_full_rects, c->d_ggrid_pts, c->d_ggrid_label, c->d_ggrid_cell_start,
+                    c->d_icp_grid_pts, c->d_icp_grid_label, c->d_icp_grid_cells, c->d_cmp_depth, c->d_cmp_label, c->d_full_keys, c->d_full_big, c->d_full_count, c->d_full_acc, c->d_full_rects, c->d_ggrid_pts, c->d_ggrid_label, c->d_ggrid_cell_start, c->d_gicp_levels,
                     c->d_obs_lab, c->d_obs_rgb, c->d_scratch, c->d_err_flag, c->d_flush, c->d_obs_xyz_aos,
                     c->d_tgt_normals, c->d_obs_xyz4, c->d_obs_label_sorted, c->d_obs_tmp, c->d_in_xyz, c->d_in_rgb, c->d_in_label, c->d_label_range, c->d_gicp, c->d_icp_pcd, c->d_icp_normals};
     for (void* p : ptrs)

@@ -159,7 +159,15 @@ struct perch_ctx {
     uint32_t* d_ggrid_cell_start = nullptr;
     perch::ObsGridDev gicp_grid;
     float gicp_grid_h = 0.f;
+    double gicp_grid_avg = 1.0;  // points per non-empty cell of gicp_grid
     bool gicp_grid_valid = false;
+    // pyramid above gicp_grid (levels 1..): own buffers per level; d_gicp_levels = the ObsGridDev array incl. level 0
+    static constexpr int kGicpMaxLevels = 14;
+    float4* d_lvl_pts[kGicpMaxLevels] = {};
+    int* d_lvl_label[kGicpMaxLevels] = {};
+    uint32_t* d_lvl_cell_start[kGicpMaxLevels] = {};
+    perch::ObsGridDev* d_gicp_levels = nullptr;
+    int gicp_n_levels = 0;
 
     // per-call scratch (grown on demand, never shrunk)
     void* d_scratch = nullptr;

@@ -343,10 +343,13 @@ __device__ inline void ball_search(const ObsGridDev& g, float h, float qx, float
 #pragma unroll
             for (int u = 0; u < kBallRows; ++u) {
                 const int y = yb + u;
-                const bool live = y <= y1 && !(gz + gap2(qy, g.oy, y) > best * 1.0002f);
+                const float gyz = gz + gap2(qy, g.oy, min(y, y1));
+                const float wx = sqrtf(fmaxf(best * 1.0002f - gyz, 0.f)) * 1.0001f + slack;  // the ball's chord along x in this row
+                const int xa = max(x0, (int)floorf((qx - wx - g.ox) * g.inv_h)), xb = min(x1, (int)floorf((qx + wx - g.ox) * g.inv_h));
+                const bool live = y <= y1 && !(gyz > best * 1.0002f) && xa <= xb;
                 const int row = (z * g.dy + min(y, y1)) * g.dx;
-                rb[u] = live ? __ldg(g.cell_start + row + x0) : 0u;
-                re[u] = live ? __ldg(g.cell_start + row + x1 + 1) : 0u;
+                rb[u] = live ? __ldg(g.cell_start + row + xa) : 0u;
+                re[u] = live ? __ldg(g.cell_start + row + xb + 1) : 0u;
             }
 #pragma unroll
             for (int u = 0; u < kBallRows; ++u) scan_run(g, rb[u], re[u], qx, qy, qz, use_label, label, best, best_ref, best_pt);
@@ -445,10 +448,18 @@ __device__ inline void warm_search_warp(const GicpArgs& a, const float* pts, int
                 active = false;
             } else if (gz > best * 1.0002f) {
                 y = y1;  // the whole slice is out of reach: the next trip moves on to z + 1
-            } else if (!(gz + gap2(qy, g.oy, y) > best * 1.0002f)) {
-                const int row = (z * g.dy + y) * g.dx;
-                j = __ldg(g.cell_start + row + x0);
-                e = __ldg(g.cell_start + row + x1 + 1);
+            } else {
+                const float gyz = gz + gap2(qy, g.oy, y);
+                if (!(gyz > best * 1.0002f)) {
+                    // the ball's chord along x in this row: points of the row are at least sqrt(gyz) away in (y, z)
+                    const float wx = sqrtf(fmaxf(best * 1.0002f - gyz, 0.f)) * 1.0001f + slack;
+                    const int xa = max(x0, (int)floorf((qx - wx - g.ox) * g.inv_h)), xb = min(x1, (int)floorf((qx + wx - g.ox) * g.inv_h));
+                    if (xa <= xb) {
+                        const int row = (z * g.dy + y) * g.dx;
+                        j = __ldg(g.cell_start + row + xa);
+                        e = __ldg(g.cell_start + row + xb + 1);
+                    }
+                }
             }
         }
         if (active && j < e) {
@@ -459,6 +470,145 @@ __device__ inline void warm_search_warp(const GicpArgs& a, const float* pts, int
                 const uint32_t jj = min(j + u, e - 1);
                 p[u] = __ldg(g.pts + jj);
                 lab[u] = use_label ? __ldg(g.label + jj) : label;
+            }
+#pragma unroll
+            for (int u = 0; u < kScanUnroll; ++u) {
+                if (lab[u] != label) continue;
+                const float d = sqdist3(qx, qy, qz, p[u].x, p[u].y, p[u].z);
+                const int ref = __float_as_int(p[u].w);
+                if (d < best || (d == best && ref < best_ref)) { best = d; best_ref = ref; }
+            }
+            j += kScanUnroll;
+        }
+    }
+}
+
+// warm_search_warp on the pyramid of grids (GicpArgs::levels), for every linearisation including the first.
+// * Level: a ball of radius r opens ~ (r / h)^2 rows and tests ~ density * (2 r h + h^2) points on cells of size h, so the
+//   best cell size grows like cbrt(r / density): GicpArgs::level_k.  On the finest grid alone a query 5 cm from a sparse
+//   target opens ~ 700 rows (C1: 626 source points per pose, most of them centimetres from the observed cloud: 46 ms per
+//   2 000 poses x 20); on cells of r / 2 a dense target (40 points per cm^2) costs thousands of point tests per query.
+// * Seed: the previous correspondence when there is one; otherwise the first point (of the pose's label) in the query's own
+//   cell on the finest level where that cell holds one -- all levels are probed at once, the loads are independent -- and
+//   as a last resort the first point of the label's range.  Any seed gives the exact result: the ball search visits every
+//   cell that can hold a nearer point (or an equally near one with a lower index).
+// Same per-query arithmetic, pruning and tie-break as ball_search; the level only decides which cells are enumerated.
+__device__ inline void pyramid_search_warp(const GicpArgs& a, const float* pts, int n, const float* R, const float* t, int* refs,
+                                           bool use_label, int label, int lb, int le, bool use_prev, int lane, int warp) {
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const int n_mine = (n - warp + kGicpWarps - 1) / kGicpWarps;
+    const int L = a.n_levels;
+    int next = 0;
+    bool active = false;
+    int i = 0, best_ref = -1;
+    float qx = 0.f, qy = 0.f, qz = 0.f, best = 0.f, gz = 0.f;
+    float ox = 0.f, oy = 0.f, oz = 0.f, h = 1.f, slack = 0.f;
+    int dx = 1, dy = 1;
+    const uint32_t* cell_start = nullptr;
+    const float4* gpts = nullptr;
+    const int* glabel = nullptr;
+    int x0 = 0, x1 = 0, y0 = 0, y1 = 0, z1 = 0, y = 0, z = 0;
+    uint32_t j = 0, e = 0;
+    auto gap2 = [&](float q, float o, int c) {
+        const float lo = fmaf((float)c, h, o), d = fmaxf(fmaxf(lo - q, q - (lo + h)) - slack, 0.f);
+        return d * d;
+    };
+    for (;;) {
+        const unsigned idle = __ballot_sync(0xffffffffu, !active);
+        if (idle) {
+            const int my = next + __popc(idle & lt_mask);
+            next += __popc(idle);
+            if (!active && my < n_mine) {
+                i = warp + kGicpWarps * my;
+                const float ax = pts[3 * i], ay = pts[3 * i + 1], az = pts[3 * i + 2];
+                qx = R[0] * ax + R[1] * ay + R[2] * az + t[0];
+                qy = R[3] * ax + R[4] * ay + R[5] * az + t[1];
+                qz = R[6] * ax + R[7] * ay + R[8] * az + t[2];
+                int seed = use_prev ? refs[i] : -1;
+                if (seed < 0) {
+                    // the query's own cell on every level, finest first
+                    for (int l = 0; l < L && seed < 0; ++l) {
+                        const ObsGridDev& g = a.levels[l];
+                        const int cx = min(max((int)floorf((qx - g.ox) * g.inv_h), 0), g.dx - 1);
+                        const int cy = min(max((int)floorf((qy - g.oy) * g.inv_h), 0), g.dy - 1);
+                        const int cz = min(max((int)floorf((qz - g.oz) * g.inv_h), 0), g.dz - 1);
+                        const int c = (cz * g.dy + cy) * g.dx + cx;
+                        const uint32_t b0 = __ldg(g.cell_start + c), e0 = __ldg(g.cell_start + c + 1);
+                        // the nearest of the cell's first few points (of the pose's label): a closer seed is a smaller ball
+                        float sd = FLT_MAX;
+                        int seen = 0;
+                        for (uint32_t k = b0; k < e0 && seen < 8; ++k) {
+                            if (use_label && __ldg(g.label + k) != label) continue;
+                            const float4 p = __ldg(g.pts + k);
+                            const float d = sqdist3(qx, qy, qz, p.x, p.y, p.z);
+                            if (d < sd) { sd = d; seed = __float_as_int(p.w); }
+                            ++seen;
+                        }
+                    }
+                    if (seed < 0 && le > lb) seed = lb;  // any point of the label (the cloud is sorted by label)
+                }
+                if (seed < 0) {
+                    refs[i] = -1;  // no target point carries this label
+                } else {
+                    const float4 p0 = __ldg(a.tgt_sorted + seed);
+                    best = sqdist3(qx, qy, qz, p0.x, p0.y, p0.z);
+                    best_ref = seed;
+                    const float r0 = sqrtf(best);
+                    // level whose cells are nearest (in ratio) to h* = cbrt(level_k * r), but never so fine that the ball spans
+                    // more than ~16 cells per axis
+                    const float h_want = fmaxf(cbrtf(a.level_k * r0), r0 * 0.125f) * 0.70710678f;
+                    int l = 0;
+                    while (l + 1 < L && 1.0f / a.levels[l].inv_h < h_want) ++l;
+                    const ObsGridDev& g = a.levels[l];
+                    ox = g.ox; oy = g.oy; oz = g.oz; h = 1.0f / g.inv_h; slack = 1e-3f * h;
+                    dx = g.dx; dy = g.dy;
+                    cell_start = g.cell_start; gpts = g.pts; glabel = g.label;
+                    const float r = r0 * 1.0001f + slack;
+                    x0 = min(max((int)floorf((qx - r - ox) * g.inv_h), 0), g.dx - 1); x1 = min(max((int)floorf((qx + r - ox) * g.inv_h), 0), g.dx - 1);
+                    y0 = min(max((int)floorf((qy - r - oy) * g.inv_h), 0), g.dy - 1); y1 = min(max((int)floorf((qy + r - oy) * g.inv_h), 0), g.dy - 1);
+                    z = min(max((int)floorf((qz - r - oz) * g.inv_h), 0), g.dz - 1); z1 = min(max((int)floorf((qz + r - oz) * g.inv_h), 0), g.dz - 1);
+                    y = y0 - 1;
+                    gz = gap2(qz, oz, z);
+                    j = e = 0;
+                    active = true;
+                }
+            }
+        }
+        if (next >= n_mine && __ballot_sync(0xffffffffu, active) == 0u) break;
+        if (active && j >= e) {
+            ++y;
+            if (y > y1) {
+                ++z;
+                y = y0;
+                if (z <= z1) gz = gap2(qz, oz, z);
+            }
+            if (z > z1) {
+                refs[i] = best_ref;
+                active = false;
+            } else if (gz > best * 1.0002f) {
+                y = y1;
+            } else {
+                const float gyz = gz + gap2(qy, oy, y);
+                if (!(gyz > best * 1.0002f)) {
+                    const float wx = sqrtf(fmaxf(best * 1.0002f - gyz, 0.f)) * 1.0001f + slack;
+                    const float inv_h = 1.0f / h;
+                    const int xa = max(x0, (int)floorf((qx - wx - ox) * inv_h)), xb = min(x1, (int)floorf((qx + wx - ox) * inv_h));
+                    if (xa <= xb) {
+                        const int row = (z * dy + y) * dx;
+                        j = __ldg(cell_start + row + xa);
+                        e = __ldg(cell_start + row + xb + 1);
+                    }
+                }
+            }
+        }
+        if (active && j < e) {
+            float4 p[kScanUnroll];
+            int lab[kScanUnroll];
+#pragma unroll
+            for (int u = 0; u < kScanUnroll; ++u) {
+                const uint32_t jj = min(j + u, e - 1);
+                p[u] = __ldg(gpts + jj);
+                lab[u] = use_label ? __ldg(glabel + jj) : label;
             }
 #pragma unroll
             for (int u = 0; u < kScanUnroll; ++u) {
@@ -684,7 +834,9 @@ __global__ void __launch_bounds__(kGicpThreads, PERCH_GICP_MIN_BLOCKS) gicp_kern
         for (int i = 0; i < 3; ++i) t[i] = (float)s_T[9 + i];
         // ---- phase 1: correspondences of this linearisation -> refs[] ------------------------------------------------
         const bool flat = !stream_target && it > 0 && a.tgt_sorted != nullptr && a.warm_cells >= 1e5f;
-        if (flat) {
+        if (!stream_target && a.levels != nullptr && a.tgt_sorted != nullptr && a.warm_cells >= 1e5f) {
+            pyramid_search_warp(a, pts, n, R, t, refs, use_label, label, lb, le, it > 0, lane, warp);
+        } else if (flat) {
             warm_search_warp(a, pts, n, R, t, refs, use_label, label, lane, warp);
         } else {
             for (int i = tid; i < n; i += kGicpThreads) {

@@ -248,6 +248,14 @@ struct GicpArgs {
     // this many (fine) cell widths of the moved point; beyond it the search starts cold (PERCH_GICP_WARM_CELLS)
     float warm_cells = 1e6f;
     float stall_rel = 1e-3f;
+    // Pyramid of grids over the target (level 0 = `grid`, cells doubling per level, the last level has at most two cells per
+    // axis): a search whose ball has radius r runs on the level whose cells are about r / 2 wide, so it opens a bounded
+    // number of rows whatever r is (a far query on the finest grid opens (2r / h)^2 of them).  Device array, or null.
+    const ObsGridDev* levels = nullptr;
+    int n_levels = 0;
+    // level choice: rows opened ~ (r / h)^2, points tested ~ density * (2 r h + h^2) => best cell size h* = cbrt(level_k * r)
+    // with level_k = kappa * h0^2 / (points per non-empty level-0 cell); kappa = cost of a row step in point tests
+    float level_k = 0.f;
 };
 size_t gicp_smem_bytes(int smem_points);
 cudaError_t launch_gicp(const GicpArgs& a, int n_poses, cudaStream_t stream);

@@ -33,6 +33,13 @@ if default_wc is None:
     os.environ.pop("PERCH_GICP_WARM_CELLS", None)
 else:
     os.environ["PERCH_GICP_WARM_CELLS"] = default_wc
+for kap in ([] if not os.environ.get("PERCH_PROBE_KAPPA_SWEEP") else (2, 5, 10, 20, 40, 80, 160, 400)):
+    os.environ["PERCH_GICP_LEVEL_KAPPA_X10"] = str(kap)
+    ms2 = []
+    for _ in range(3):
+        g2 = r.gicp(wl["poses"], wl["pmm"], None, **args); ms2.append(r.last_timing()[0])
+    print("kappa x10", kap, "kernel ms", np.median(ms2), "same transforms", np.array_equal(g2["transforms"], g["transforms"]))
+os.environ.pop("PERCH_GICP_LEVEL_KAPPA_X10", None)
 # points per cell (x10) of the finer grid GICP builds for dense clouds: PERCH_GICP_GRID_TARGET_X10 (read when the grid is built)
 for tgt in ([] if not os.environ.get("PERCH_PROBE_GRID_SWEEP") else (10, 20, 30, 50, 80, 120)):
     os.environ["PERCH_GICP_GRID_TARGET_X10"] = str(tgt)
