@@ -222,8 +222,8 @@ def test_gicp_edge_cases(orc):
 @pytest.mark.gpu
 def test_gicp_dense_scene_cloud_grids_agree(orc, monkeypatch):
     """BASELINE configs[3] in shape: the target is the FULL-resolution scene cloud (stride 1).  GICP then searches its own
-    finer grid, falls back to the cost grid and finally to a linear scan; all three are exact, so the refined poses must
-    not depend on which one answers.  Forced three ways: fine grid (default), cost grid only, and a fine grid so fine
+    finer grid, falls back to the cost grid and finally to a linear scan, or searches a pyramid of grids; all are exact, so the
+    refined poses must not depend on which one answers.  Forced three ways: fine grid (default), cost grid only, and a fine grid so fine
     that most queries leave it.  (The cost-grid path is the one held to the double-precision oracle by the tests above; the
     oracle's brute-force normals are O(N^2) and out of reach at 200k points.)"""
     from perception_b200 import synth
@@ -238,10 +238,13 @@ def test_gicp_dense_scene_cloud_grids_agree(orc, monkeypatch):
     outs = []
     # last entry: target normals from the N x N k-NN kernel instead of the ring search through the grid (same 10 neighbours
     # in the same order => bit-identical normals => identical poses)
-    for density, target, brute in (("8", "60", "0"), ("1000000", "60", "0"), ("8", "3", "0"), ("8", "60", "1"), ("8", "200", "0")):
+    # 4th field: PERCH_GICP_PYRAMID (1 = default: pyramid of grids for sparse targets only; 2 = forced on; 0 = off)
+    for density, target, brute, pyramid in (("8", "60", "0", "1"), ("1000000", "60", "0", "1"), ("8", "3", "0", "1"), ("8", "60", "1", "1"),
+                                            ("8", "200", "0", "1"), ("8", "60", "0", "2"), ("1000000", "60", "0", "0")):
         monkeypatch.setenv("PERCH_GICP_GRID_DENSITY", density)
         monkeypatch.setenv("PERCH_GICP_GRID_TARGET_X10", target)
         monkeypatch.setenv("PERCH_GICP_NORMALS_BRUTE", brute)
+        monkeypatch.setenv("PERCH_GICP_PYRAMID", pyramid)
         with Renderer(0) as r:
             r.set_camera(case.width, case.height, case.proj, *cam)
             r.set_models(s.tris, s.tris_model_count)
