@@ -266,6 +266,7 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
     __shared__ float s_apx[20];
     __shared__ int s_big[kBigCap];
     __shared__ int s_n, s_c, s_e;
+    __shared__ float s_band[4];
     __shared__ float s_minz;  // smallest camera-space depth of the posed model AABB (0: unknown / not in front)
 
     const int pose_i = blockIdx.x;
@@ -369,13 +370,19 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
             const int by1 = min(by0 + band_rows - 1, ry1);
             const int band_cells = tile_w * (by1 - by0 + 1);
             for (int c = tid; c < band_cells; c += kThreads) zbuf[c] = Z::empty();
-            if (tid == 0) { s_qcount = 0; s_bigcount = 0; }
+            if (tid == 0) {
+                s_qcount = 0; s_bigcount = 0;
+                // Band limits in lattice coordinates for the candidate test: columns ux in [rx0, rx1]; raster rows
+                // P1 = H-1-ly*s for ly in [by0, by1], i.e. uy = (H-1-row_phase)/s - ly.  Computed once and handed to every
+                // thread through shared memory: as expressions of (rx0, by0, inv_s ...) the compiler re-derived them inside
+                // the culling loops (I2FP + FFMA per use).  C2 1.245 -> 1.238 ms; doing the same with the margins and the
+                // sphere constants (m_lo3, Kg ...) was measured too and is slower again (1.249 ms).
+                const float rows_k = (float)((H - 1) / s);
+                s_band[0] = (float)rx0 - 0.5f * inv_s; s_band[1] = (float)rx1;
+                s_band[2] = (rows_k - (float)by1) - 0.5f * inv_s; s_band[3] = rows_k - (float)by0;
+            }
             __syncthreads();
-            // band limits in lattice coordinates for the candidate test: columns ux in [rx0, rx1]; raster rows
-            // P1 = H-1-ly*s for ly in [by0, by1], i.e. uy = (H-1-row_phase)/s - ly
-            const float rows_k = (float)((H - 1) / s);
-            const float band_lo_x = (float)rx0 - 0.5f * inv_s, band_hi_x = (float)rx1;
-            const float band_lo_y = (rows_k - (float)by1) - 0.5f * inv_s, band_hi_y = rows_k - (float)by0;
+            const float band_lo_x = s_band[0], band_hi_x = s_band[1], band_lo_y = s_band[2], band_hi_y = s_band[3];
 
             // Exact path for one triangle: the reference's float sequence (exact_math.cuh), its bbox loops restricted
             // to lattice pixels of this band, z-test with atomicMin.  `coop` = all threads of the CTA share the work.
