@@ -682,6 +682,11 @@ int perch_set_camera(perch_ctx* c, int width, int height, const float proj16[16]
         c->d_cmp_depth = nullptr;
         c->d_cmp_label = nullptr;
         c->composed = false;
+        // ... and so are the resident scene images (perch_set_scene / perch_set_input re-allocate for the new size)
+        cudaFree(c->d_src_depth); cudaFree(c->d_src_label); cudaFree(c->d_src_rgb);
+        c->d_src_depth = nullptr; c->d_src_label = nullptr; c->d_src_rgb = nullptr;
+        c->src_px = 0;
+        c->scene = perch::SceneDev{};
     }
     c->cam.width = width;
     c->cam.height = height;
@@ -695,6 +700,27 @@ int perch_set_camera(perch_ctx* c, int width, int height, const float proj16[16]
 }  // extern "C"
 
 namespace {
+// Two independent multiply-rotate lanes over a byte range (8 bytes at a time, the tail zero-padded).
+void digest_bytes(const void* data, size_t bytes, uint64_t h[2]) {
+    const unsigned char* base = static_cast<const unsigned char*>(data);
+    auto mix = [&](uint64_t w) {
+        h[0] = (h[0] ^ w) * 0xFF51AFD7ED558CCDull; h[0] = (h[0] << 31) | (h[0] >> 33);
+        h[1] = (h[1] + w) * 0xC4CEB9FE1A85EC53ull; h[1] ^= h[1] >> 29;
+    };
+    size_t i = 0;
+    for (; i + 8 <= bytes; i += 8) {
+        uint64_t w;
+        memcpy(&w, base + i, 8);
+        mix(w);
+    }
+    if (i < bytes) {
+        uint64_t w = 0;
+        memcpy(&w, base + i, bytes - i);
+        mix(w);
+    }
+    mix((uint64_t)bytes);
+}
+
 // Two independent multiply-rotate lanes over the 8-byte words of the triangle array, then the counts.
 void models_digest(const perch_triangle* tris, int64_t n_tris, const int* counts, int n_models, uint64_t out[2]) {
     uint64_t h0 = 0x9E3779B97F4A7C15ull ^ (uint64_t)n_tris, h1 = 0xC2B2AE3D27D4EB4Full ^ (uint64_t)n_models;
@@ -894,10 +920,22 @@ int perch_set_scene(perch_ctx* c, const int32_t* depth, const uint8_t* red, cons
     if (!c->have_cam) return fail(PERCH_ERR_INVALID, "perch_set_camera must be called before perch_set_scene");
     DeviceGuard g(c->device);
     const size_t npx = (size_t)c->cam.width * c->cam.height;
-    int rc;
-    if ((rc = upload(&c->d_src_depth, depth, npx, c->stream))) return rc;
-    if ((rc = upload<uint8_t>(&c->d_src_label, label, label ? npx : 0, c->stream))) return rc;
-    if ((rc = upload<uint8_t>(&c->d_src_rgb, nullptr, 3 * npx, c->stream))) return rc;
+    // The buffers are kept across calls of the same image size (the reference's calling pattern sets the scene with every
+    // render call: a cudaFree + cudaMalloc per buffer per call cost more than the copies).
+    bool grew = false;
+    if (c->src_px != npx) {
+        cudaFree(c->d_src_depth); cudaFree(c->d_src_label); cudaFree(c->d_src_rgb);
+        c->d_src_depth = nullptr; c->d_src_label = nullptr; c->d_src_rgb = nullptr;
+        c->src_px = 0;
+        CU(cudaMalloc(&c->d_src_depth, npx * sizeof(int32_t)));
+        CU(cudaMalloc(&c->d_src_rgb, 3 * npx));
+        c->src_px = npx;
+        grew = true;
+    }
+    if (label && !c->d_src_label) { CU(cudaMalloc(&c->d_src_label, npx)); grew = true; }
+    if (!label && c->d_src_label) { cudaFree(c->d_src_label); c->d_src_label = nullptr; }  // d_src_label != NULL means "labelled scene"
+    CU(cudaMemcpyAsync(c->d_src_depth, depth, npx * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
+    if (label) CU(cudaMemcpyAsync(c->d_src_label, label, npx, cudaMemcpyHostToDevice, c->stream));
     const uint8_t* planes[3] = {red, green, blue};
     for (int k = 0; k < 3; ++k) {
         if (planes[k]) CU(cudaMemcpyAsync(c->d_src_rgb + k * npx, planes[k], npx, cudaMemcpyHostToDevice, c->stream));
@@ -911,7 +949,7 @@ int perch_set_scene(perch_ctx* c, const int32_t* depth, const uint8_t* red, cons
     c->scene.g = c->d_src_rgb + npx;
     c->scene.b = c->d_src_rgb + 2 * npx;
     c->have_scene = true;
-    note_memory(c);
+    if (grew) note_memory(c);
     return PERCH_OK;
 }
 
@@ -919,6 +957,16 @@ int perch_set_observed(perch_ctx* c, const float* xyz_aos, const uint8_t* rgb_so
     if (!c || n_obs < 0 || (n_obs > 0 && !xyz_aos)) return fail(PERCH_ERR_INVALID, "bad set_observed argument");
     if (n_obs > (1 << 24)) return fail(PERCH_ERR_CAPACITY, "observed cloud larger than 16M points");
     DeviceGuard g(c->device);
+    // An observed cloud identical to the resident one (the reference passes it with every render call, renderer.cu:1668,
+    // 1881) keeps everything built from it: sorted copy, colours, nearest-neighbour grids, target normals.
+    uint64_t digest[2] = {0x9E3779B97F4A7C15ull ^ (uint64_t)n_obs, 0xC2B2AE3D27D4EB4Full ^ (uint64_t)(label != nullptr) ^ ((uint64_t)(rgb_soa != nullptr) << 1)};
+    digest_bytes(xyz_aos, 12 * (size_t)n_obs, digest);
+    if (rgb_soa) digest_bytes(rgb_soa, 3 * (size_t)n_obs, digest);
+    if (label) digest_bytes(label, 4 * (size_t)n_obs, digest);
+    if (c->have_obs && c->obs_digest_valid && c->n_obs == n_obs && digest[0] == c->obs_digest[0] && digest[1] == c->obs_digest[1] &&
+        !env_int("PERCH_SET_OBSERVED_ALWAYS", 0))
+        return PERCH_OK;
+    c->obs_digest_valid = false;
     c->n_obs = n_obs;
     c->obs_has_label = label != nullptr;
     c->h_obs_xyz.assign(xyz_aos, xyz_aos + 3 * (size_t)n_obs);
@@ -980,6 +1028,9 @@ int perch_set_observed(perch_ctx* c, const float* xyz_aos, const uint8_t* rgb_so
     c->grid_res = -1.f;  // grid is (re)built on the next cost call, when sensor_resolution is known
     c->tgt_normals_k = 0;
     c->have_obs = true;
+    c->obs_digest[0] = digest[0];
+    c->obs_digest[1] = digest[1];
+    c->obs_digest_valid = true;
     ++c->obs_version;
     note_memory(c);
     return PERCH_OK;
@@ -1014,6 +1065,7 @@ int perch_detail::ensure_obs_host(perch_ctx* c) {
 int perch_detail::install_observed_device(perch_ctx* c, const float* d_aos, const uint8_t* d_rgb, size_t rgb_stride,
                                           const int* d_label, int n) {
     if (n > (1 << 24)) return fail(PERCH_ERR_CAPACITY, "observed cloud larger than 16M points");
+    c->obs_digest_valid = false;
     c->n_obs = n;
     c->obs_has_label = d_label != nullptr;
     c->obs_nonfinite = false;

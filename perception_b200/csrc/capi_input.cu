@@ -98,9 +98,16 @@ int perch_set_input(perch_ctx* c, const perch_input* in, int* observed_point_num
         PERCH_CU(perch::launch_divide_depth(d_depth, in->source_division_factor, d_source, (int)npx, c->stream));
         d_src = d_source;
     }
-    if (!c->d_src_depth) PERCH_CU(cudaMalloc(&c->d_src_depth, npx * 4));
-    if (!c->d_src_rgb) PERCH_CU(cudaMalloc(&c->d_src_rgb, 3 * npx));
+    if (c->src_px != npx) {  // buffers of another image size (perch_set_camera frees them; kept as a second line of defence)
+        cudaFree(c->d_src_depth); cudaFree(c->d_src_label); cudaFree(c->d_src_rgb);
+        c->d_src_depth = nullptr; c->d_src_label = nullptr; c->d_src_rgb = nullptr;
+        c->src_px = 0;
+        PERCH_CU(cudaMalloc(&c->d_src_depth, npx * 4));
+        PERCH_CU(cudaMalloc(&c->d_src_rgb, 3 * npx));
+        c->src_px = npx;
+    }
     if (in->predicted_mask && !c->d_src_label) PERCH_CU(cudaMalloc(&c->d_src_label, npx));
+    if (!in->predicted_mask && c->d_src_label) { cudaFree(c->d_src_label); c->d_src_label = nullptr; }  // non-null = labelled scene (capi_compose.cu)
     PERCH_CU(cudaMemcpyAsync(c->d_src_depth, d_src, npx * 4, cudaMemcpyDeviceToDevice, c->stream));
     for (int ch = 0; ch < 3; ++ch)
         PERCH_CU(cudaMemcpyAsync(c->d_src_rgb + ch * npx, d_planes[ch], npx, cudaMemcpyDeviceToDevice, c->stream));

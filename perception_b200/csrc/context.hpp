@@ -67,6 +67,9 @@ struct StatesCtx;  // capi_states.cu
 struct perch_ctx {
     // 128-bit digest of the last perch_set_models input (triangles + counts): an identical call returns at once
     uint64_t models_digest[2] = {0, 0};
+    // the same for perch_set_observed (host cloud); cleared whenever the observed cloud is replaced any other way
+    uint64_t obs_digest[2] = {0, 0};
+    bool obs_digest_valid = false;
     int device = 0;
     int sm_count = 0;
     int max_smem_optin = 0;
@@ -102,6 +105,7 @@ struct perch_ctx {
     bool have_models = false;
 
     // scene
+    size_t src_px = 0;  // pixels d_src_depth / d_src_rgb (and d_src_label, when present) are allocated for
     int32_t* d_src_depth = nullptr;
     uint8_t* d_src_label = nullptr;
     uint8_t* d_src_rgb = nullptr;  // 3 planes

@@ -133,3 +133,41 @@ def test_median_blur_kernel_sizes_and_errors():
             r.set_input(img, stride=5)
         with pytest.raises(Exception, match="8-bit"):
             r.set_input(img.astype(np.uint16), median_blur_ksize=3, stride=2)
+
+
+@gpu
+@pytest.mark.skipif(not has_gpu(), reason="needs a B200")
+def test_scene_buffers_follow_the_camera_size():
+    """A context that held a SMALL scene and is then given a larger camera must not reuse the small scene buffers:
+    perch_set_input used to copy the new image into whatever allocation was there (device memory overrun).  The large
+    scene set after the small one must score exactly like the same scene on a fresh context, and going back to the small
+    size must work too."""
+    from perception_b200.renderer import Renderer
+    small, big = make_case(300, 3, 7, 160, 120), make_case()
+    sb = big.scene
+    depth8 = _scene_u8(big)
+    T_tc = np.linalg.inv(sb.T_cam_table)
+    bounds = synth.table_bounds(sb)
+    poses, pmm, _ = poses_near_gt(big, 16)
+    kw = dict(stride=4, cost_type=0, sensor_resolution=0.0075)
+
+    def big_scene(r):
+        r.set_camera(big.width, big.height, big.proj, big.cx, big.cy, big.fx, big.fy, 100.0)
+        r.set_models(sb.tris, sb.tris_model_count)
+        n = r.set_input(depth8, sb.source_color, depth_factor=100.0, stride=4, bounds=bounds, camera_transform=T_tc)
+        return r.render_cuda_multi_unified("COST", poses, pmm, None, np.full(len(poses), float(n), np.float32), **kw)
+
+    with Renderer(0) as r:
+        ss = small.scene
+        r.set_camera(small.width, small.height, small.proj, small.cx, small.cy, small.fx, small.fy, 100.0)
+        r.set_models(ss.tris, ss.tris_model_count)
+        r.set_scene(ss.source_depth, ss.source_color, ss.source_label)   # 160 x 120 buffers, labelled
+        after_small = big_scene(r)                                       # 640 x 480, unlabelled, through perch_set_input
+        r.set_camera(small.width, small.height, small.proj, small.cx, small.cy, small.fx, small.fy, 100.0)
+        r.set_scene(ss.source_depth, ss.source_color, None)
+        assert r.get_source_depth().shape == (small.height, small.width)
+    with Renderer(0) as r:
+        fresh = big_scene(r)
+    for key in ("rendered_cost", "observed_cost", "points_diff_cost", "counts"):
+        assert np.array_equal(after_small[key], fresh[key], equal_nan=True), key
+    assert (fresh["counts"][0] > 0).any()

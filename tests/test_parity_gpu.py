@@ -631,3 +631,29 @@ def test_set_models_is_idempotent_and_notices_changes(orc):
     assert np.array_equal(b["counts"], b_fresh["counts"]) and np.array_equal(b["rendered_cost"], b_fresh["rendered_cost"])
     assert not np.array_equal(a["counts"], b["counts"]), "the moved mesh must score differently"
     assert t_same < t_new, (t_same, t_new)
+
+
+@pytest.mark.gpu
+def test_set_observed_is_idempotent_and_notices_changes(orc):
+    """Same contract for the observed cloud (passed with every call by the reference, renderer.cu:1668): an identical
+    cloud keeps the resident copy and its grids, a cloud that differs in one coordinate, colour or label replaces them."""
+    case, obs, poses, pmm, lab, tot = _cost_case(orc, 5000, 8, True, 24)
+    kw = dict(stride=8, cost_type=2, sensor_resolution=0.01)
+    moved = obs["aos"].copy()
+    moved[: len(moved) // 2, 2] += np.float32(0.05)          # half the cloud 5 cm farther away
+    with make_renderer(case, with_label=True) as r:
+        r.set_observed(obs["aos"], obs["rgb"], obs["label"])
+        a = r.render_cuda_multi_unified("COST", poses, pmm, lab, tot, **kw)
+        r.set_observed(obs["aos"], obs["rgb"], obs["label"])  # unchanged: no-op
+        a2 = r.render_cuda_multi_unified("COST", poses, pmm, lab, tot, **kw)
+        r.set_observed(moved, obs["rgb"], obs["label"])
+        b = r.render_cuda_multi_unified("COST", poses, pmm, lab, tot, **kw)
+        r.set_observed(obs["aos"], obs["rgb"], obs["label"])  # and back
+        a3 = r.render_cuda_multi_unified("COST", poses, pmm, lab, tot, **kw)
+    with make_renderer(case, with_label=True) as r:
+        r.set_observed(moved, obs["rgb"], obs["label"])
+        b_fresh = r.render_cuda_multi_unified("COST", poses, pmm, lab, tot, **kw)
+    for x in (a2, a3):
+        assert np.array_equal(a["counts"], x["counts"]) and np.array_equal(a["observed_cost"], x["observed_cost"], equal_nan=True)
+    assert np.array_equal(b["counts"], b_fresh["counts"])
+    assert not np.array_equal(a["counts"], b["counts"]), "the moved cloud must score differently"
