@@ -113,7 +113,9 @@ int perch_set_camera(perch_ctx* ctx, int width, int height, const float proj16[1
 
 /* ---- models / scene ------------------------------------------------------------------------------------- */
 /* @tris, @tris_model_count of render_cuda_multi_unified (renderer.cu:1433,1436): all models' triangles
- * concatenated, in the reference's 64-byte Triangle layout. */
+ * concatenated, in the reference's 64-byte Triangle layout.  The three setters below may be called with every render
+ * call, as the reference passes these arguments every time: perch_set_models and perch_set_observed return at once when the
+ * input equals the resident one (128-bit digest of all bytes), perch_set_scene re-uploads into buffers it keeps. */
 int perch_set_models(perch_ctx* ctx, const perch_triangle* tris, int64_t n_tris, const int* tris_model_count,
                      int n_models);
 /* @source_depth, @source_color (3 planes), @source_mask_label (may be NULL) (renderer.cu:1438-1442). */
