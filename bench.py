@@ -895,7 +895,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--e2e-contexts", type=int, default=2,
+    ap.add_argument("--e2e-contexts", type=int, default=3,
                     help="contexts (one host thread each) the e2e leg spreads its steps over; 1 = strictly serial calls")
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference", "reference-cuda"])
