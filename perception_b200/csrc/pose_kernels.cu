@@ -578,13 +578,28 @@ __global__ void __launch_bounds__(kThreads, kMinCtas) pose_kernel(PoseArgs a) {
                     float4 bnd[kLaneQuads];
 #pragma unroll
                     for (int k = 0; k < kLaneQuads; ++k) bnd[k] = __ldg(a.models.q_bounds + min(qb + 32 * k, q_high - 1));
+                    // survivors of the claim's kClaim spheres go to the warp's list with ONE compaction (a lane's kept
+                    // quads, then a shuffle scan over the lanes) instead of a ballot + popc + store per 32 spheres:
+                    // C2 1.239 -> 1.230 ms, C3 1.292 -> 1.276 ms.  The list order changes, the set does not.
+                    unsigned keepmask = 0u;
 #pragma unroll
                     for (int k = 0; k < kLaneQuads; ++k) {
                         const int q = qb + 32 * k;
-                        const bool keep = (q < q_high) && !sphere_rejects(bnd[k]);
-                        const unsigned bal = __ballot_sync(0xffffffffu, keep);
-                        if (keep && IDX_OK(npend + __popc(bal & lt_mask), kPendCap)) wpend[npend + __popc(bal & lt_mask)] = q;
-                        npend += __popc(bal);
+                        if ((q < q_high) && !sphere_rejects(bnd[k])) keepmask |= 1u << k;
+                    }
+                    {
+                        const int cnt = __popc(keepmask);
+                        int incl = cnt;
+#pragma unroll
+                        for (int o = 1; o < 32; o <<= 1) {
+                            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+                            if (lane >= o) incl += v;
+                        }
+                        int slot = npend + incl - cnt;
+#pragma unroll
+                        for (int k = 0; k < kLaneQuads; ++k)
+                            if ((keepmask >> k) & 1u) { if (IDX_OK(slot, kPendCap)) wpend[slot] = qb + 32 * k; ++slot; }
+                        npend += __shfl_sync(0xffffffffu, incl, 31);
                     }
                     if (lane == 0) { STAT(0, min(kClaim, q_high - (q_low + g * kClaim))); }
                     __syncwarp();
